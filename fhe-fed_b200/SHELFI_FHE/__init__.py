@@ -1,0 +1,251 @@
+"""SHELFI_FHE — drop-in for the reference's pybind module of the same name, backed by the B200 engine.
+
+Mirrors /root/reference/palisade_pybind/SHELFI_FHE/src/binding.cpp:14-50: classes ``Scheme`` and
+``CKKS(scheme="ckks", batchSize=4096, scaleFactorBits=52, cryptodir="../resources/cryptoparams/")``
+with ``loadCryptoParams``, ``genCryptoContextAndKeyGen``, ``encrypt``, ``decrypt``,
+``computeWeightedAverage`` and the three ``*_cpp`` aliases (binding.cpp:27,29,31 bind those names to
+the same methods), plus ``__version__``.
+
+All arithmetic happens in ``libshelfi_b200.so`` (hand-written sm_100a CUDA behind the C ABI of
+``include/shelfi_b200.h``), loaded with ctypes.  There is no CPU path: without the library or
+without a CUDA device the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+__version__ = "0.1.0-b200"
+
+_PKG = Path(__file__).resolve().parent.parent
+_LIB_PATH = Path(os.environ.get("SHELFI_B200_LIB", _PKG / "lib" / "libshelfi_b200.so"))
+
+ERR_NAMES = {0: "OK", -1: "ARG", -2: "NOT_LOADED", -3: "FORMAT", -4: "PARAMS", -5: "CUDA", -6: "IO", -7: "UNSUPPORTED"}
+
+
+class ShelfiError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"[{ERR_NAMES.get(code, code)}] {message}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libshelfi_b200.so (built by fhe-fed_b200/Makefile or __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise ImportError(f"{_LIB_PATH} not found: build it with `make -C {_PKG}` (nvcc, sm_100a); "
+                          "SHELFI_FHE has no CPU fallback")
+    L = C.CDLL(str(_LIB_PATH))
+    vp, u8p, u32, u64, i64, f64 = C.c_void_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint64, C.c_int64, C.c_double
+    u64p = C.POINTER(C.c_uint64)
+    sig = {
+        "shelfi_ckks_create": (C.c_int, [C.c_char_p, u32, u32, C.c_char_p, C.c_int, C.POINTER(vp)]),
+        "shelfi_ckks_destroy": (None, [vp]),
+        "shelfi_last_error": (C.c_char_p, [vp]),
+        "shelfi_load_crypto_params": (C.c_int, [vp]),
+        "shelfi_load_crypto_params_from_memory": (C.c_int, [vp, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
+                                                             C.c_char_p, C.c_size_t]),
+        "shelfi_gen_crypto_context_and_keygen": (C.c_int, [vp]),
+        "shelfi_set_sampler_seed": (C.c_int, [vp, u64]),
+        "shelfi_clear_sampler_seed": (C.c_int, [vp]),
+        "shelfi_ring_dim": (u32, [vp]),
+        "shelfi_num_limbs": (u32, [vp]),
+        "shelfi_slots": (u32, [vp]),
+        "shelfi_batch_size": (u32, [vp]),
+        "shelfi_modulus": (u64, [vp, u32]),
+        "shelfi_root_of_unity": (u64, [vp, u32]),
+        "shelfi_scaling_factor": (f64, [vp]),
+        "shelfi_key_tag": (C.c_int, [vp, C.c_char_p]),
+        "shelfi_num_ciphertexts": (u64, [vp, u64]),
+        "shelfi_ciphertext_words": (u64, [vp]),
+        "shelfi_blob_size": (u64, [vp, u64]),
+        "shelfi_weight_constant": (i64, [vp, C.c_float]),
+        "shelfi_encrypt": (C.c_int, [vp, vp, u64, C.POINTER(vp), u64p]),
+        "shelfi_encrypt_into": (C.c_int, [vp, vp, u64, vp, u64, u64p]),
+        "shelfi_compute_weighted_average": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32,
+                                                       C.POINTER(vp), u64p]),
+        "shelfi_compute_weighted_average_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, vp, u64,
+                                                            u64p]),
+        "shelfi_decrypt": (C.c_int, [vp, vp, u64, u64, vp]),
+        "shelfi_free": (None, [vp]),
+        "shelfi_host_alloc": (vp, [C.c_size_t]),
+        "shelfi_host_free": (None, [vp]),
+        "shelfi_encrypt_device": (C.c_int, [vp, vp, u64, u64, vp, vp]),
+        "shelfi_weighted_sum_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_float), u32, u64, vp, vp]),
+        "shelfi_decrypt_device": (C.c_int, [vp, vp, u64, f64, vp, u64, vp]),
+        "shelfi_pack_device": (C.c_int, [vp, vp, u64, vp, vp]),
+        "shelfi_unpack_device": (C.c_int, [vp, vp, u64, vp, vp]),
+        "shelfi_ntt_forward_device": (C.c_int, [vp, vp, u32, vp]),
+        "shelfi_ntt_inverse_device": (C.c_int, [vp, vp, u32, vp]),
+        "shelfi_encode_device": (C.c_int, [vp, vp, u64, vp, vp]),
+        "shelfi_decrypt_integer_device": (C.c_int, [vp, vp, u64, vp, vp, vp]),
+        "shelfi_version": (C.c_char_p, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def _as_bytes(blob) -> bytes:
+    # pybind11 2.6.1's permissive std::string caster takes bytes or str (ckks.cpp:170,276)
+    if isinstance(blob, (bytes, bytearray, memoryview)):
+        return bytes(blob) if not isinstance(blob, bytes) else blob
+    if isinstance(blob, str):
+        return blob.encode("latin-1")
+    raise TypeError("ciphertext blob must be bytes or str")
+
+
+class Scheme:
+    """Opaque base class, as bound at binding.cpp:16 (include/scheme.h:15-32)."""
+
+    def __init__(self, scheme: str = "ckks"):
+        self.scheme = scheme
+
+
+class CKKS(Scheme):
+    """CKKS helper with the reference's constructor and methods (binding.cpp:18-31)."""
+
+    def __init__(self, scheme: str = "ckks", batchSize: int = 4096, scaleFactorBits: int = 52,
+                 cryptodir: str = "../resources/cryptoparams/", device: int | None = None):
+        super().__init__(scheme)
+        self.batchSize, self.scaleFactorBits, self.cryptodir = int(batchSize), int(scaleFactorBits), str(cryptodir)
+        if device is None:
+            device = int(os.environ.get("SHELFI_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+        self.device = device
+        h = C.c_void_p()
+        rc = lib().shelfi_ckks_create(scheme.encode(), self.batchSize, self.scaleFactorBits, self.cryptodir.encode(),
+                                      device, C.byref(h))
+        if rc:
+            raise ShelfiError(rc, "could not create CKKS handle")
+        self._h = h
+        self.load_status = None
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _lib is not None:
+            _lib.shelfi_ckks_destroy(h)
+            self._h = None
+
+    # ---- helpers ----
+    def _err(self) -> str:
+        return lib().shelfi_last_error(self._h).decode(errors="replace")
+
+    def _check(self, rc: int):
+        if rc < 0:
+            raise ShelfiError(rc, self._err())
+
+    # ---- reference API ----
+    def loadCryptoParams(self) -> None:
+        """ckks.cpp:11-23: read cryptocontext.txt / key-public.txt / key-private.txt from cryptodir.
+
+        Like the reference, a missing file is reported on stderr-ish output and does not raise; the
+        status mask (1 context, 2 public key, 4 private key) is kept in ``load_status``.  A missing CUDA
+        device does raise: nothing can run without it.
+        """
+        rc = lib().shelfi_load_crypto_params(self._h)
+        self._check(rc)
+        self.load_status = rc
+        if rc & 1:  # same words as ckks.cpp:13,17,21
+            print("Could not read serialization from " + self.cryptodir + "cryptocontext.txt")
+        if rc & 2:
+            print("Could not read public key")
+        if rc & 4:
+            print("Could not read secret key", file=sys.stderr)
+
+    def genCryptoContextAndKeyGen(self) -> int:
+        """ckks.cpp:25-59: write a fresh context and key pair into cryptodir; returns 1 or 0; does not load."""
+        ok = lib().shelfi_gen_crypto_context_and_keygen(self._h)
+        if not ok:
+            print("Error generating crypto context and keys: " + self._err())
+        return int(ok)
+
+    def encrypt(self, data_array) -> bytes:
+        """ckks.cpp:61-104: any array-like convertible to float64 (flattened) -> serialized ciphertext vector."""
+        x = np.ascontiguousarray(data_array, dtype=np.float64).ravel()
+        out, n = C.c_void_p(), C.c_uint64()
+        self._check(lib().shelfi_encrypt(self._h, x.ctypes.data, x.size, C.byref(out), C.byref(n)))
+        try:
+            return C.string_at(out.value, n.value)
+        finally:
+            lib().shelfi_free(out)
+
+    def computeWeightedAverage(self, learner_data, scaling_factors) -> bytes:
+        """ckks.cpp:264-320: sum_i float32(w_i) * ct_i over learners; size mismatch prints and returns b""."""
+        learner_data, scaling_factors = list(learner_data), list(scaling_factors)
+        if len(learner_data) != len(scaling_factors):
+            print("Error: learner_data and scaling_factors size mismatch")  # ckks.cpp:266
+            return b""
+        blobs = [_as_bytes(b) for b in learner_data]
+        k = len(blobs)
+        ptrs = (C.c_void_p * k)(*[C.cast(C.c_char_p(b), C.c_void_p) for b in blobs])
+        lens = (C.c_uint64 * k)(*[len(b) for b in blobs])
+        w = (C.c_float * k)(*[float(v) for v in scaling_factors])
+        out, n = C.c_void_p(), C.c_uint64()
+        self._check(lib().shelfi_compute_weighted_average(self._h, ptrs, lens, w, k, C.byref(out), C.byref(n)))
+        try:
+            return C.string_at(out.value, n.value)
+        finally:
+            lib().shelfi_free(out)
+
+    def decrypt(self, learner_data, data_dimensions: int) -> np.ndarray:
+        """ckks.cpp:170-213: serialized ciphertext vector -> float64[data_dimensions]."""
+        blob = _as_bytes(learner_data)
+        n = int(data_dimensions)
+        out = np.empty(n, dtype=np.float64)
+        self._check(lib().shelfi_decrypt(self._h, blob, len(blob), n, out.ctypes.data))
+        return out
+
+    encrypt_cpp = encrypt
+    decrypt_cpp = decrypt
+    computeWeightedAverage_cpp = computeWeightedAverage
+
+    # ---- extras beyond the reference (tests, benchmarks, sharded callers) ----
+    def set_sampler_seed(self, seed: int | None) -> None:
+        if seed is None:
+            lib().shelfi_clear_sampler_seed(self._h)
+        else:
+            lib().shelfi_set_sampler_seed(self._h, int(seed) & (2**64 - 1))
+
+    def load_from_memory(self, cc: bytes | None, pk: bytes | None, sk: bytes | None) -> int:
+        rc = lib().shelfi_load_crypto_params_from_memory(self._h, cc, len(cc or b""), pk, len(pk or b""), sk,
+                                                         len(sk or b""))
+        self._check(rc)
+        self.load_status = rc
+        return rc
+
+    @property
+    def handle(self) -> C.c_void_p:
+        return self._h
+
+    @property
+    def ring_dim(self) -> int: return lib().shelfi_ring_dim(self._h)
+    @property
+    def num_limbs(self) -> int: return lib().shelfi_num_limbs(self._h)
+    @property
+    def slots(self) -> int: return lib().shelfi_slots(self._h)
+    @property
+    def scaling_factor(self) -> float: return lib().shelfi_scaling_factor(self._h)
+    @property
+    def ciphertext_words(self) -> int: return lib().shelfi_ciphertext_words(self._h)
+
+    def modulus(self, limb: int) -> int: return lib().shelfi_modulus(self._h, limb)
+    def root_of_unity(self, limb: int) -> int: return lib().shelfi_root_of_unity(self._h, limb)
+    def num_ciphertexts(self, n: int) -> int: return lib().shelfi_num_ciphertexts(self._h, n)
+    def blob_size(self, n_ct: int) -> int: return lib().shelfi_blob_size(self._h, n_ct)
+    def weight_constant(self, w: float) -> int: return lib().shelfi_weight_constant(self._h, w)
+
+    def key_tag(self) -> str:
+        buf = C.create_string_buffer(33)
+        lib().shelfi_key_tag(self._h, buf)
+        return buf.value.decode()

@@ -1,0 +1,646 @@
+// ckks_core.cuh — per-thread building blocks of the SHELFI CKKS hot path (sm_100a).
+//
+// Everything here is a `__host__ __device__` function of (thread id, shared-memory tile, limb
+// constants): the CUDA kernels in kernels.cu call these between __syncthreads(), and the test
+// harness tests/emu/ (g++, no GPU) replays the same phases thread by thread so index math and
+// modular arithmetic can be checked bit for bit on a CPU-only box.  The harness is test
+// infrastructure; the product path is the kernels.
+//
+// Reference semantics being reproduced (PALISADE, called from
+// palisade_pybind/SHELFI_FHE/src/ckks.cpp:80-81,189,288,296):
+//   * ChineseRemainderTransformFTT::ForwardTransformToBitReverse  -> fwd_* phases
+//   * ChineseRemainderTransformFTT::InverseTransformFromBitReverse -> inv_* phases
+//   * DiscreteFourierTransform::FFTSpecial / FFTSpecialInv        -> fft_* phases
+//   * DCRTPoly::CRTInterpolate + CKKSPackedEncoding::Decode        -> crt2_centered / i128_to_double
+#pragma once
+#include <stdint.h>
+#include <math.h>
+
+#ifdef __CUDACC__
+#define HD __host__ __device__ __forceinline__
+#else
+#define HD inline
+#endif
+
+namespace shelfi {
+
+typedef uint64_t u64;
+typedef int64_t i64;
+typedef unsigned int u32;
+typedef int i32;
+
+constexpr int kMaxLimbs = 8;
+constexpr int kLogN = 13;            // ring dimension 8192: the only one SHELFI's multDepth=1 contexts produce
+constexpr int kN = 1 << kLogN;
+constexpr int kNttThreads = 256;     // one CTA per limb polynomial, 32 coefficients per thread
+constexpr int kFftThreads = 256;
+
+struct __attribute__((aligned(16))) tw_t { u64 w, ws; };  // twiddle and its Shoup companion floor(w*2^64/q)
+
+// Per-limb constants, passed to kernels by value inside RingConst.
+struct LimbConst {
+    u64 q;          // modulus (<= 60 bits)
+    u64 q2;         // 2q
+    u64 mu;         // floor(2^64 / q): generic Barrett quotient estimate
+    u64 ninv, ninv_s;       // N^-1 mod q and Shoup companion
+    u64 wninv, wninv_s;     // itw[1] * N^-1 mod q (last inverse stage with the scaling folded in)
+    u64 r64, r64_s;         // 2^64 mod q and Shoup companion (128-bit accumulator reduction)
+    u32 rshift;     // quick-reduce shift
+    u32 rmode;      // 0: q just below 2^rshift; 1: q just above 2^rshift; 2: generic (mulhi by mu)
+    u32 fwd_mask;   // bit p: quick-reduce to [0,2q) at the end of forward pass p (0..3)
+    u32 pad;
+    const tw_t *tw;   // forward table, index 1..N-1: psi^bitrev(i)      (PALISADE rootOfUnityReverseTable)
+    const tw_t *itw;  // inverse table:                psi^-bitrev(i)
+};
+
+struct RingConst {
+    u32 n, logn, limbs, slots;
+    LimbConst limb[kMaxLimbs];
+};
+
+// ------------------------------------------------------------------------------------------
+// 64-bit modular arithmetic on the integer pipes
+// ------------------------------------------------------------------------------------------
+HD u64 mulhi(u64 a, u64 b) {
+#ifdef __CUDA_ARCH__
+    return __umul64hi(a, b);
+#else
+    return (u64)(((unsigned __int128)a * b) >> 64);
+#endif
+}
+HD u32 mulhi32(u32 a, u32 b) {
+#ifdef __CUDA_ARCH__
+    return __umulhi(a, b);
+#else
+    return (u32)(((uint64_t)a * b) >> 32);
+#endif
+}
+// Shoup product, lazy: x*w - floor(x*ws/2^64)*q, in [0, 2q) for ANY 64-bit x (w < q).
+HD u64 shoup_lazy(u64 x, u64 w, u64 ws, u64 q) { return x * w - mulhi(x, ws) * q; }
+HD u64 csub(u64 x, u64 m) { return x >= m ? x - m : x; }
+// x (any value the caller's bound analysis allows) -> [0, 2q)
+HD u64 quick_reduce(u64 x, const LimbConst &lc) {
+    if (lc.rmode == 0) return x - (x >> lc.rshift) * lc.q;
+    if (lc.rmode == 1) return x - (x >> lc.rshift) * lc.q + lc.q;
+    return x - mulhi(x, lc.mu) * lc.q;
+}
+HD u64 full_reduce(u64 x, const LimbConst &lc) { return csub(quick_reduce(x, lc), lc.q); }
+// any 64-bit x -> [0, q)
+HD u64 barrett_reduce(u64 x, const LimbConst &lc) { return csub(x - mulhi(x, lc.mu) * lc.q, lc.q); }
+HD u64 signed_to_mod(i64 x, const LimbConst &lc) {
+    u64 mag = x < 0 ? (u64)0 - (u64)x : (u64)x;
+    u64 r = barrett_reduce(mag, lc);
+    return (x < 0 && r) ? lc.q - r : r;
+}
+
+// shared-memory swizzle: XOR address bits 3..1 with bits 6..4.  Keeps (2i, 2i+1) adjacent (128-bit
+// accesses in the radix-2 pass) and makes every radix-8 pass's 64-bit accesses conflict-free.
+HD u32 swz(u32 i) { return i ^ ((i >> 3) & 0xEu); }
+
+// Cooley-Tukey butterfly, Harvey lazy form: no per-butterfly correction, bounds grow by 2q per stage
+// and are brought back by quick_reduce at the pass boundaries named in LimbConst::fwd_mask.
+HD void ct_bfly(u64 &x, u64 &y, const tw_t &w, u64 q, u64 q2) {
+    u64 t = shoup_lazy(y, w.w, w.ws, q);
+    y = x + q2 - t;
+    x = x + t;
+}
+// radix-8 register pass: a[k], k = (b2 b1 b0) with b2 the address bit of the first stage.
+HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 q, u64 q2) {
+    tw_t w = tw[t0];
+#pragma unroll
+    for (int k = 0; k < 4; k++) ct_bfly(a[k], a[k + 4], w, q, q2);
+    tw_t w0 = tw[2 * t0], w1 = tw[2 * t0 + 1];
+    ct_bfly(a[0], a[2], w0, q, q2); ct_bfly(a[1], a[3], w0, q, q2);
+    ct_bfly(a[4], a[6], w1, q, q2); ct_bfly(a[5], a[7], w1, q, q2);
+#pragma unroll
+    for (int k = 0; k < 4; k++) ct_bfly(a[2 * k], a[2 * k + 1], tw[4 * t0 + k], q, q2);
+}
+
+// ---- forward NTT phases (natural order in, bit-reversed order out), 8192 points, 256 threads ----
+// Pass A: stages 0-2 (address bits 12,11,10) straight from the loader into shared memory.
+template <class Load>
+HD void fwd_phase_a(int tid, u64 *sm, const LimbConst &lc, Load ld) {
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = ld((u32)(k << 10) | vt);
+        ct_radix8(a, lc.tw, 1u, lc.q, lc.q2);
+        if (lc.fwd_mask & 1u) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[swz((u32)(k << 10) | vt)] = a[k];
+    }
+}
+// Passes B, C, D: LO = 7, 4, 1 (lowest of the three address bits held in registers).
+template <int LO>
+HD void fwd_phase_mid(int tid, u64 *sm, const LimbConst &lc) {
+    constexpr int PASS = (10 - LO) / 3;               // 1, 2, 3
+    constexpr u32 S0 = 12 - (LO + 2);                 // first stage of the pass: 3, 6, 9
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO;
+        u32 base = (high << (LO + 3)) | low;
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = sm[swz(base | (u32)(k << LO))];
+        ct_radix8(a, lc.tw, (1u << S0) + high, lc.q, lc.q2);
+        if (lc.fwd_mask & (1u << PASS)) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[swz(base | (u32)(k << LO))] = a[k];
+    }
+}
+// Pass E: stage 12 (address bit 0); st(pair index, x, y) receives lazily reduced values in
+// [0, (B+2)q) — the storer applies full_reduce or folds further work in first.
+template <class Store>
+HD void fwd_phase_e(int tid, const u64 *sm, const LimbConst &lc, Store st) {
+    for (int r = 0; r < 16; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u32 p = swz(2u * vt);
+        u64 x = sm[p], y = sm[p + 1];
+        ct_bfly(x, y, lc.tw[(kN >> 1) + vt], lc.q, lc.q2);
+        st(vt, x, y);
+    }
+}
+
+// ---- inverse NTT phases (bit-reversed in, natural out), Gentleman-Sande ----
+// Inputs to a pass are < 2q; X' = X + Y doubles the bound per stage, Y' = (X - Y + c)*w with
+// c = (bound of Y) so the difference stays non-negative.  Every pass ends with quick_reduce.
+HD void gs_bfly(u64 &x, u64 &y, const tw_t &w, u64 q, u64 c) {
+    u64 t = x + c - y;
+    x = x + y;
+    y = shoup_lazy(t, w.w, w.ws, q);
+}
+// radix-8 GS pass over address bits LO, LO+1, LO+2 (a[k]: k bit j <-> address bit LO+j).
+// Stage for address bit b uses m = N >> (b+1) groups: twiddle index m + (x >> (b+1)).
+HD void gs_radix8(u64 (&a)[8], const tw_t *__restrict__ itw, u32 t2, u64 q, u64 q2) {
+    // t2 = index for the LAST of the three stages (bit LO+2): (N >> (LO+3)) + high
+    // first stage, bit LO: index 4*t2 + (k >> 1) pairs (k, k+1) for even k ... bounds 2q -> 4q
+#pragma unroll
+    for (int k = 0; k < 4; k++) gs_bfly(a[2 * k], a[2 * k + 1], itw[4 * t2 + k], q, q2);
+    // second stage, bit LO+1: x elements < 4q, y elements < 2q (fresh products)
+    tw_t w0 = itw[2 * t2], w1 = itw[2 * t2 + 1];
+    gs_bfly(a[0], a[2], w0, q, 2 * q2); gs_bfly(a[1], a[3], w0, q, 2 * q2);
+    gs_bfly(a[4], a[6], w1, q, 2 * q2); gs_bfly(a[5], a[7], w1, q, 2 * q2);
+    // third stage, bit LO+2: bound 8q
+    tw_t w = itw[t2];
+#pragma unroll
+    for (int k = 0; k < 4; k++) gs_bfly(a[k], a[k + 4], w, q, 4 * q2);
+}
+// Pass E': address bit 0 from the loader (pairs), result quick-reduced into shared memory.
+// ld(pair index, &x, &y) must deliver values < 4q.
+template <class Load>
+HD void inv_phase_e(int tid, u64 *sm, const LimbConst &lc, Load ld) {
+    for (int r = 0; r < 16; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u64 x, y;
+        ld(vt, x, y);
+        gs_bfly(x, y, lc.itw[(kN >> 1) + vt], lc.q, 2 * lc.q2);
+        u32 p = swz(2u * vt);
+        sm[p] = quick_reduce(x, lc);
+        sm[p + 1] = y;
+    }
+}
+template <int LO>  // LO = 1, 4, 7
+HD void inv_phase_mid(int tid, u64 *sm, const LimbConst &lc) {
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO;
+        u32 base = (high << (LO + 3)) | low;
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = sm[swz(base | (u32)(k << LO))];
+        gs_radix8(a, lc.itw, (u32)(kN >> (LO + 3)) + high, lc.q, lc.q2);
+#pragma unroll
+        for (int k = 0; k < 8; k++) sm[swz(base | (u32)(k << LO))] = quick_reduce(a[k], lc);
+    }
+}
+// Last pass: address bits 10, 11, 12 with N^-1 folded into the final stage; st(index, value in [0,q)).
+template <class Store>
+HD void inv_phase_last(int tid, const u64 *sm, const LimbConst &lc, Store st) {
+    const u64 q = lc.q, q2 = lc.q2;
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = sm[swz((u32)(k << 10) | vt)];
+#pragma unroll
+        for (int k = 0; k < 4; k++) gs_bfly(a[2 * k], a[2 * k + 1], lc.itw[4 + k], q, q2);
+        tw_t w0 = lc.itw[2], w1 = lc.itw[3];
+        gs_bfly(a[0], a[2], w0, q, 2 * q2); gs_bfly(a[1], a[3], w0, q, 2 * q2);
+        gs_bfly(a[4], a[6], w1, q, 2 * q2); gs_bfly(a[5], a[7], w1, q, 2 * q2);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {  // x' = (x+y)/N, y' = (x-y)*w/N ; inputs < 8q
+            u64 x = a[k], y = a[k + 4];
+            u64 s = x + y, d = x + 4 * q2 - y;
+            a[k] = csub(shoup_lazy(s, lc.ninv, lc.ninv_s, q), q);
+            a[k + 4] = csub(shoup_lazy(d, lc.wninv, lc.wninv_s, q), q);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, a[k]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// sampler: Philox4x32-10, counter layout shared with the CPU oracle
+// ------------------------------------------------------------------------------------------
+HD void philox4x32_10(u64 seed, u32 c0, u32 c1, u32 c2, u32 c3, u32 (&out)[4]) {
+    u32 k0 = (u32)seed, k1 = (u32)(seed >> 32);
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        u32 h0 = mulhi32(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        u32 h1 = mulhi32(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        u32 n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+enum { kStreamGauss = 0, kStreamTernary = 1, kStreamKeyS = 2, kStreamKeyE = 3, kStreamKeyA = 4 };
+// magnitude = #{k : u >= cdf[k]} over a 32-entry table of floor(2^64 * P(|X| <= k)); bit 63 of r is the sign
+HD int gauss_from_u64(const u64 *cdf, u64 r) {
+    u64 u = r << 1;
+    int lo = 0;
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1)
+        if (u >= cdf[lo + step - 1]) lo += step;
+    if (lo > 31) lo = 31;
+    return (r >> 63) ? -lo : lo;
+}
+HD int ternary_from_u32(u32 r) { return (int)mulhi32(r, 3u) - 1; }
+
+// ------------------------------------------------------------------------------------------
+// canonical-embedding FFT (FFTSpecial / FFTSpecialInv), FP64, no fused multiply-add: llround()
+// results must match the reference's unfused butterflies bit for bit.
+// ------------------------------------------------------------------------------------------
+struct __attribute__((aligned(16))) cplx { double re, im; };
+HD double fmul(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dmul_rn(a, b);
+#else
+    return a * b;
+#endif
+}
+HD double fadd(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dadd_rn(a, b);
+#else
+    return a + b;
+#endif
+}
+HD double fsub(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dsub_rn(a, b);
+#else
+    return a - b;
+#endif
+}
+HD u32 bitrev32(u32 x, int bits) {
+#ifdef __CUDA_ARCH__
+    return __brev(x) >> (32 - bits);
+#else
+    u32 r = 0;
+    for (int i = 0; i < bits; i++) r |= ((x >> i) & 1u) << (bits - 1 - i);
+    return r;
+#endif
+}
+// One stage of FFTSpecialInv (decimation in frequency): butterflies j of block length `len`.
+// twi = per-stage table, entry (len/2 - 1) + j  holds ksi[(lenq - rot[j] % lenq) * M/lenq].
+HD void fft_inv_stage(int tid, int nthreads, cplx *z, u32 size, u32 len, const cplx *__restrict__ twi) {
+    u32 lenh = len >> 1;
+    for (u32 b = tid; b < (size >> 1); b += nthreads) {
+        u32 j = b & (lenh - 1), i = (b / lenh) * len;
+        cplx w = twi[lenh - 1 + j];
+        cplx u = z[i + j], v = z[i + j + lenh];
+        double dr = fsub(u.re, v.re), di = fsub(u.im, v.im);
+        z[i + j].re = fadd(u.re, v.re); z[i + j].im = fadd(u.im, v.im);
+        z[i + j + lenh].re = fsub(fmul(dr, w.re), fmul(di, w.im));
+        z[i + j + lenh].im = fadd(fmul(dr, w.im), fmul(di, w.re));
+    }
+}
+// One stage of FFTSpecial (decimation in time, input already bit-reversed).
+HD void fft_fwd_stage(int tid, int nthreads, cplx *z, u32 size, u32 len, const cplx *__restrict__ twf) {
+    u32 lenh = len >> 1;
+    for (u32 b = tid; b < (size >> 1); b += nthreads) {
+        u32 j = b & (lenh - 1), i = (b / lenh) * len;
+        cplx w = twf[lenh - 1 + j];
+        cplx u = z[i + j], v = z[i + j + lenh];
+        double vr = fsub(fmul(v.re, w.re), fmul(v.im, w.im));
+        double vi = fadd(fmul(v.re, w.im), fmul(v.im, w.re));
+        z[i + j].re = fadd(u.re, vr); z[i + j].im = fadd(u.im, vi);
+        z[i + j + lenh].re = fsub(u.re, vr); z[i + j + lenh].im = fsub(u.im, vi);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// decode helpers: two-limb CRT to a centred 128-bit integer, correctly rounded to double
+// ------------------------------------------------------------------------------------------
+struct Crt2Const {
+    u64 q0, q1;
+    u64 q0inv, q0inv_s;    // q0^-1 mod q1 and Shoup companion
+    u64 mu1;               // floor(2^64 / q1)
+    u64 Q_hi, Q_lo;        // Q = q0*q1
+    u64 Qh_hi, Qh_lo;      // floor(Q / 2)
+};
+HD void mul64x64(u64 a, u64 b, u64 &hi, u64 &lo) { lo = a * b; hi = mulhi(a, b); }
+// sign/magnitude of the centred representative of x = a0 (mod q0), a1 (mod q1)
+HD void crt2_centered(u64 a0, u64 a1, const Crt2Const &c, bool &neg, u64 &mag_hi, u64 &mag_lo) {
+    u64 a0m = csub(a0 - mulhi(a0, c.mu1) * c.q1, c.q1);       // a0 mod q1
+    u64 diff = a1 >= a0m ? a1 - a0m : a1 + c.q1 - a0m;
+    u64 d = csub(shoup_lazy(diff, c.q0inv, c.q0inv_s, c.q1), c.q1);
+    u64 hi, lo;
+    mul64x64(c.q0, d, hi, lo);
+    u64 xlo = lo + a0;
+    u64 xhi = hi + (xlo < lo ? 1 : 0);
+    bool gt = xhi > c.Qh_hi || (xhi == c.Qh_hi && xlo > c.Qh_lo);  // x > floor(Q/2) -> x - Q
+    if (gt) {
+        u64 rlo = c.Q_lo - xlo;
+        u64 rhi = c.Q_hi - xhi - (c.Q_lo < xlo ? 1 : 0);
+        neg = true; mag_hi = rhi; mag_lo = rlo;
+    } else {
+        neg = false; mag_hi = xhi; mag_lo = xlo;
+    }
+}
+HD int clz64(u64 x) {
+#ifdef __CUDA_ARCH__
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+// (double) of a signed 128-bit integer, round to nearest even in ONE rounding (same as gcc's __floattidf)
+HD double i128_to_double(bool neg, u64 hi, u64 lo) {
+    double r;
+    if (hi == 0) {
+        r = (double)lo;
+    } else {
+        int s = clz64(hi);                         // 0..63
+        u64 top = s ? (hi << s) | (lo >> (64 - s)) : hi;
+        u64 rest = s ? (lo << s) : lo;
+        if (rest) top |= 1ull;                     // sticky bit below the 64-bit window
+        r = ldexp((double)top, 64 - s);
+    }
+    return neg ? -r : r;
+}
+
+}  // namespace shelfi
+
+// ==========================================================================================
+// kernel argument blocks and the remaining per-thread phases
+// ==========================================================================================
+namespace shelfi {
+
+constexpr int kMaxLearnersPerLaunch = 16;
+
+struct SamplerConst {
+    u64 seed;
+    u64 ct_index0;       // global index of the first ciphertext of this launch (shards draw the oracle's stream)
+    u64 gauss_cdf[32];   // floor(2^64 * P(|X| <= k)), k = 0..31
+};
+
+struct EncodeConst {
+    u32 slots, gap, log_slots, batch;  // context slots, N/2/slots, log2(slots), ctor batchSize (chunk length)
+    double pow_p;                      // scaling factor (q_last as double)
+    double inv_size;                   // 1 / slots (exact power of two)
+    const cplx *tw_inv;                // slots-1 per-stage twiddles of FFTSpecialInv
+    const cplx *tw_fwd;                // ... of FFTSpecial
+};
+
+struct DecodeConst {
+    Crt2Const crt;
+    double pre;     // scalingFactor^-1 * 2^p
+    double pow_p;   // 2^-p
+};
+
+struct WavgArgs {
+    const u64 *in[kMaxLearnersPerLaunch];
+    u64 c[kMaxLearnersPerLaunch][kMaxLimbs];  // EvalMult constant reduced into every limb
+    u32 k;
+    u32 accumulate;  // add the values already in `out` (chained launches for > kMaxLearnersPerLaunch learners)
+};
+
+struct LimbScalars { u64 c[kMaxLimbs]; };
+
+// byte offsets of the 2L coefficient runs of a serialized vector<Ciphertext> (wire.h)
+struct BlobRuns {
+    u64 off0[2 * kMaxLimbs];   // ciphertext 0
+    u64 off1[2 * kMaxLimbs];   // ciphertext 1 (absolute); ciphertext j >= 1: off1[r] + (j-1)*stride
+    u64 stride;
+    u32 runs;                  // 2L
+    u32 pad;
+};
+HD u64 run_offset(const BlobRuns &br, u64 ct, u32 r) { return ct == 0 ? br.off0[r] : br.off1[r] + (ct - 1) * br.stride; }
+
+// ---- encode: MakeCKKSPackedPlaintext up to the integer coefficients (ckks.cpp:80) ----
+// phase 0: chunk of x -> z (zero padded)
+HD void encode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid) {
+    for (u32 i = tid; i < ec.slots; i += nthreads) {
+        z[i].re = i < n_valid ? x[i] : 0.0;
+        z[i].im = 0.0;
+    }
+}
+// phases 1..log_slots: fft_inv_stage(len = slots >> (p-1))
+// final phase: bit reversal, 1/size, *Delta, llround — in place, z[i] reinterpreted as two int64
+HD void encode_finalize(int tid, int nthreads, cplx *z, const EncodeConst &ec) {
+    i64 *zi = reinterpret_cast<i64 *>(z);
+    for (u32 i = tid; i < ec.slots; i += nthreads) {
+        u32 j = bitrev32(i, (int)ec.log_slots);
+        if (i > j) continue;
+        cplx a = z[i], b = z[j];
+        i64 ar = llround(fmul(fmul(a.re, ec.inv_size), ec.pow_p)), ai = llround(fmul(fmul(a.im, ec.inv_size), ec.pow_p));
+        i64 br = llround(fmul(fmul(b.re, ec.inv_size), ec.pow_p)), bi = llround(fmul(fmul(b.im, ec.inv_size), ec.pow_p));
+        zi[2 * j] = ar; zi[2 * j + 1] = ai;
+        zi[2 * i] = br; zi[2 * i + 1] = bi;
+    }
+}
+// coefficient j of the plaintext polynomial from the finalized tile
+HD i64 encode_coeff(const cplx *z, const EncodeConst &ec, u32 j) {
+    const i64 *zi = reinterpret_cast<const i64 *>(z);
+    u32 nh = kN >> 1;
+    u32 half = j >= nh ? 1u : 0u, idx = j - half * nh;
+    if (idx & (ec.gap - 1)) return 0;
+    return zi[2 * (idx / ec.gap) + half];
+}
+// sampling + output of one group of four coefficients (ternary v, Gaussian e0, e1): [PAL] Encrypt's draws
+HD void sample_group(u32 j4, u64 ct_index, const SamplerConst &sc, const u64 *cdf, int (&v)[4], int (&e0)[4],
+                     int (&e1)[4]) {
+    u32 o[4];
+    philox4x32_10(sc.seed, j4, (u32)ct_index, (u32)(ct_index >> 32), kStreamTernary, o);
+#pragma unroll
+    for (int i = 0; i < 4; i++) v[i] = ternary_from_u32(o[i]);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        philox4x32_10(sc.seed, 4 * j4 + i, (u32)ct_index, (u32)(ct_index >> 32), kStreamGauss, o);
+        e0[i] = gauss_from_u64(cdf, ((u64)o[1] << 32) | o[0]);
+        e1[i] = gauss_from_u64(cdf, ((u64)o[3] << 32) | o[2]);
+    }
+}
+HD void encode_sample_emit(int tid, int nthreads, const cplx *z, const EncodeConst &ec, const SamplerConst &sc,
+                           const u64 *cdf, u64 ct_index, i64 *m_e0, uint16_t *ve) {
+    for (u32 j4 = tid; j4 < (u32)(kN >> 2); j4 += nthreads) {
+        int v[4], e0[4], e1[4];
+        sample_group(j4, ct_index, sc, cdf, v, e0, e1);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            u32 j = 4 * j4 + i;
+            m_e0[j] = encode_coeff(z, ec, j) + (i64)e0[i];
+            ve[j] = (uint16_t)(((u32)v[i] & 0xFFu) | (((u32)e1[i] & 0xFFu) << 8));
+        }
+    }
+}
+HD u64 small_to_mod(int x, u64 q) { return x >= 0 ? (u64)x : q - (u64)(-x); }
+
+// ---- decode: CRTInterpolate -> double -> FFTSpecial (ckks.cpp:189-199) ----
+// phase 0: coefficients (limb-major, natural order) -> z in bit-reversed slot order
+HD void decode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const DecodeConst &dc, u32 limbs,
+                    const u64 *coeff, i64 *tap_hi, u64 *tap_lo) {
+    u32 nh = kN >> 1;
+    for (u32 j = tid; j < (u32)kN; j += nthreads) {
+        bool neg; u64 hi, lo;
+        if (limbs == 1) {
+            u64 a = coeff[j], q = dc.crt.q0;
+            neg = a > (q >> 1); hi = 0; lo = neg ? q - a : a;
+        } else {
+            crt2_centered(coeff[j], coeff[kN + j], dc.crt, neg, hi, lo);
+        }
+        if (tap_hi) {  // two's complement of the centred integer, for the bit-exact integer tier
+            u64 th = hi, tl = lo;
+            if (neg) { tl = ~lo + 1; th = ~hi + (tl == 0 ? 1 : 0); }
+            tap_hi[j] = (i64)th; tap_lo[j] = tl;
+        }
+        u32 half = j >= nh ? 1u : 0u, idx = j - half * nh;
+        if (idx & (ec.gap - 1)) continue;
+        u32 slot = bitrev32(idx / ec.gap, (int)ec.log_slots);
+        double val = fmul(i128_to_double(neg, hi, lo), dc.pre);
+        if (half) z[slot].im = val; else z[slot].re = val;
+    }
+}
+// phases 1..log_slots: fft_fwd_stage(len = 2 << (p-1)); last phase: real parts * 2^-p
+HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc, double *out, u64 length) {
+    for (u32 i = tid; i < length; i += nthreads) out[i] = fmul(z[i].re, dc.pow_p);
+}
+
+// ---- weighted sum: EvalMult(ct, const) + EvalAdd over learners (ckks.cpp:286-297) ----
+struct acc128 { u64 lo, hi; };
+HD void mac128(acc128 &a, u64 x, u64 c) {
+    u64 lo = x * c, hi = mulhi(x, c);
+    a.lo += lo;
+    a.hi += hi + (a.lo < lo ? 1 : 0);
+}
+HD u64 reduce128(const acc128 &a, const LimbConst &lc) {
+    u64 t1 = shoup_lazy(a.hi, lc.r64, lc.r64_s, lc.q);       // hi * 2^64 mod q, < 2q
+    u64 t2 = a.lo - mulhi(a.lo, lc.mu) * lc.q;               // < 2q
+    return csub(csub(t1 + t2, lc.q2), lc.q);
+}
+
+// ---- serialized image <-> dense: coefficient runs start at arbitrary byte offsets ----
+HD u64 load_unaligned(const u64 *image, u64 byte_off) {
+    u64 w = byte_off >> 3;
+    u32 sh = (u32)(byte_off & 7u) * 8u;
+    u64 a = image[w];
+    if (sh == 0) return a;
+    return (a >> sh) | (image[w + 1] << (64u - sh));
+}
+// word `widx` of the image, overlapping the run that starts at byte a0 and holds kN values
+HD void pack_word(u64 *image, u64 a0, u64 widx, const u64 *run) {
+    i64 o = (i64)(widx * 8) - (i64)a0;                 // run byte offset of the word's first byte: -7 .. 8N-1
+    i64 i = o >= 0 ? (o >> 3) : -1;
+    u32 t = (u32)(o - i * 8);                          // 0..7
+    u64 lo = i >= 0 ? run[i] : 0ull;
+    u64 hi = (t && i + 1 < (i64)kN) ? run[i + 1] : 0ull;
+    u64 val = t ? (lo >> (8 * t)) | (hi << (64 - 8 * t)) : lo;
+    if (o >= 0 && o + 8 <= (i64)kN * 8) { image[widx] = val; return; }
+    unsigned char *bytes = reinterpret_cast<unsigned char *>(image + widx);
+    for (int b = 0; b < 8; b++) {
+        i64 ob = o + b;
+        if (ob >= 0 && ob < (i64)kN * 8) bytes[b] = (unsigned char)(val >> (8 * b));
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// loaders / storers plugged into the NTT phases by the kernels (and by the CPU replay harness)
+// ------------------------------------------------------------------------------------------
+struct __attribute__((aligned(16))) u64x2 { u64 x, y; };
+HD u64x2 ld_readonly(const u64x2 *p) {
+#ifdef __CUDA_ARCH__
+    ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(p));
+    return u64x2{v.x, v.y};
+#else
+    return *p;
+#endif
+}
+struct LoadGlobal {
+    const u64 *p;
+    HD u64 operator()(u32 i) const { return p[i]; }
+};
+struct StoreFullReducePair {
+    u64 *p; const LimbConst *lc;
+    HD void operator()(u32 vt, u64 x, u64 y) const {
+        reinterpret_cast<u64x2 *>(p)[vt] = u64x2{full_reduce(x, *lc), full_reduce(y, *lc)};
+    }
+};
+struct LoadPairGlobal {
+    const u64 *p;
+    HD void operator()(u32 vt, u64 &x, u64 &y) const {
+        u64x2 v = reinterpret_cast<const u64x2 *>(p)[vt];
+        x = v.x; y = v.y;
+    }
+};
+struct StoreGlobal {
+    u64 *p;
+    HD void operator()(u32 i, u64 v) const { p[i] = v; }
+};
+// encrypt: ve[j] = v (low byte, int8) | e1 (high byte, int8); m[j] = m + e0 (signed)
+struct LoadTernary {
+    const uint16_t *ve; u64 q;
+    HD u64 operator()(u32 i) const { return small_to_mod((int)(int8_t)(ve[i] & 0xFF), q); }
+};
+struct LoadGaussHi {
+    const uint16_t *ve; u64 q;
+    HD u64 operator()(u32 i) const { return small_to_mod((int)(int8_t)(ve[i] >> 8), q); }
+};
+struct LoadSigned {
+    const i64 *m; const LimbConst *lc;
+    HD u64 operator()(u32 i) const { return signed_to_mod(m[i], *lc); }
+};
+// NTT(v) epilogue: park b*v^ and a*v^ (lazy, < 2q) in the output rows
+struct StorePkProducts {
+    const tw_t *b, *a; u64 *c0, *c1; u64 q;
+    HD void operator()(u32 vt, u64 x, u64 y) const {
+        const u64x2 *bp = reinterpret_cast<const u64x2 *>(b) + 2 * vt;
+        const u64x2 *ap = reinterpret_cast<const u64x2 *>(a) + 2 * vt;
+        u64x2 b0 = ld_readonly(bp), b1 = ld_readonly(bp + 1), a0 = ld_readonly(ap), a1 = ld_readonly(ap + 1);
+        reinterpret_cast<u64x2 *>(c0)[vt] = u64x2{shoup_lazy(x, b0.x, b0.y, q), shoup_lazy(y, b1.x, b1.y, q)};
+        reinterpret_cast<u64x2 *>(c1)[vt] = u64x2{shoup_lazy(x, a0.x, a0.y, q), shoup_lazy(y, a1.x, a1.y, q)};
+    }
+};
+// NTT(m + e0) / NTT(e1) epilogue: add to the parked product (read back by the thread that wrote it)
+struct StoreAddParked {
+    u64 *c; const LimbConst *lc;
+    HD void operator()(u32 vt, u64 x, u64 y) const {
+        u64x2 p = reinterpret_cast<u64x2 *>(c)[vt];
+        u64 q = lc->q, q2 = lc->q2;
+        p.x = csub(csub(p.x + quick_reduce(x, *lc), q2), q);
+        p.y = csub(csub(p.y + quick_reduce(y, *lc), q2), q);
+        reinterpret_cast<u64x2 *>(c)[vt] = p;
+    }
+};
+// decrypt: t = c0 + c1*s on the way into the inverse transform (< 3q for reduced input)
+struct LoadDecryptPair {
+    const u64 *c0, *c1; const tw_t *s; u64 q;
+    HD void operator()(u32 vt, u64 &x, u64 &y) const {
+        u64x2 u = ld_readonly(reinterpret_cast<const u64x2 *>(c0) + vt);
+        u64x2 v = ld_readonly(reinterpret_cast<const u64x2 *>(c1) + vt);
+        const u64x2 *sp = reinterpret_cast<const u64x2 *>(s) + 2 * vt;
+        u64x2 s0 = ld_readonly(sp), s1 = ld_readonly(sp + 1);
+        x = u.x + shoup_lazy(v.x, s0.x, s0.y, q);
+        y = u.y + shoup_lazy(v.y, s1.x, s1.y, q);
+    }
+};
+
+}  // namespace shelfi

@@ -1,0 +1,796 @@
+// engine.cpp — the C ABI of include/shelfi_b200.h: handle, parameter/table setup, and the three
+// reference-facing calls built from the kernels in kernels.cu.  Host code only orchestrates; every
+// coefficient is touched on the GPU.  No CPU fallback: without a CUDA device every call fails.
+#include "../../include/shelfi_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "numtheory.h"
+#include "tables.h"
+#include "wire.h"
+
+using namespace shelfi;
+
+namespace {
+
+struct DeviceBuffer {  // grow-only device scratch
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return static_cast<T *>(p); }
+};
+
+}  // namespace
+
+struct shelfi_ckks {
+    std::string scheme, cryptodir, err;
+    uint32_t batch = 0, scale_bits = 0;
+    int device = 0;
+    bool cuda_ready = false;
+    bool have_cc = false, have_pk = false, have_sk = false;
+    wire::ContextParams ctx;
+    std::string key_tag;
+    RingConst rc{};
+    EncodeConst ec{};
+    Crt2Const crt{};
+    uint64_t gauss_cdf[32] = {0};
+    // device-resident parameters
+    DeviceBuffer d_tw, d_itw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
+    // scratch
+    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_out;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    cudaStream_t copy_stream = nullptr;
+    bool seeded = false;
+    uint64_t seed = 0;
+    std::mutex mu;
+};
+
+namespace {
+
+int fail(shelfi_ckks *h, int code, const std::string &msg) {
+    if (h) h->err = msg;
+    return code;
+}
+int cuda_fail(shelfi_ckks *h, cudaError_t e, const char *where) {
+    return fail(h, SHELFI_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                                   \
+    do {                                                           \
+        cudaError_t e__ = (call);                                  \
+        if (e__ != cudaSuccess) return cuda_fail(h, e__, #call);   \
+    } while (0)
+
+int ensure_cuda(shelfi_ckks *h) {
+    if (h->cuda_ready) {
+        CU(cudaSetDevice(h->device));
+        return 0;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(h, SHELFI_ERR_CUDA,
+                    std::string("no CUDA device: this engine has no CPU path (") + cudaGetErrorString(e) + ")");
+    if (h->device < 0 || h->device >= count) return fail(h, SHELFI_ERR_ARG, "device ordinal out of range");
+    CU(cudaSetDevice(h->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, h->device));
+    if (prop.major < 10)
+        return fail(h, SHELFI_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100-class; kernels are built for sm_100a only");
+    CU(kernels_init());
+    CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+        CU(cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+    }
+    h->cuda_ready = true;
+    return 0;
+}
+
+bool read_file(const std::string &path, std::vector<uint8_t> *out) {
+    FILE *f = std::fopen(path.c_str(), "rb");
+    if (!f) return false;
+    std::fseek(f, 0, SEEK_END);
+    long n = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    out->resize(n > 0 ? (size_t)n : 0);
+    bool ok = n >= 0 && std::fread(out->data(), 1, out->size(), f) == out->size();
+    std::fclose(f);
+    return ok;
+}
+bool write_file(const std::string &path, const std::vector<uint8_t> &data) {
+    FILE *f = std::fopen(path.c_str(), "wb");
+    if (!f) return false;
+    bool ok = std::fwrite(data.data(), 1, data.size(), f) == data.size();
+    return std::fclose(f) == 0 && ok;
+}
+
+void free_params(shelfi_ckks *h) {
+    h->d_tw.release(); h->d_itw.release(); h->d_pk_b.release(); h->d_pk_a.release(); h->d_sk.release();
+    h->d_fft_inv.release(); h->d_fft_fwd.release();
+}
+
+int upload(shelfi_ckks *h, DeviceBuffer *buf, const void *src, size_t bytes) {
+    CU(buf->reserve(bytes));
+    CU(cudaMemcpy(buf->p, src, bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
+    if (p.ring_dim != (uint32_t)kN || p.cyclotomic_order != 2u * kN)
+        return fail(h, SHELFI_ERR_UNSUPPORTED, "ring dimension " + std::to_string(p.ring_dim) +
+                                                   " not supported: kernels are specialised for N = 8192");
+    if (p.batch_size == 0 || (p.batch_size & (p.batch_size - 1)) || p.batch_size > (uint32_t)kN / 2)
+        return fail(h, SHELFI_ERR_UNSUPPORTED, "context batch size must be a power of two <= N/2");
+    if (p.limbs < 1 || p.limbs > (uint32_t)kMaxLimbs) return fail(h, SHELFI_ERR_UNSUPPORTED, "unsupported tower count");
+    RingConst rc{};
+    rc.n = kN; rc.logn = kLogN; rc.limbs = p.limbs; rc.slots = p.batch_size;
+    std::vector<tw_t> tw_all((size_t)p.limbs * kN), itw_all((size_t)p.limbs * kN), tw, itw;
+    for (uint32_t l = 0; l < p.limbs; l++) {
+        std::string e = make_limb_const(p.modulus[l], p.root[l], &rc.limb[l], &tw, &itw);
+        if (!e.empty()) return fail(h, SHELFI_ERR_UNSUPPORTED, "limb " + std::to_string(l) + ": " + e);
+        std::memcpy(&tw_all[(size_t)l * kN], tw.data(), sizeof(tw_t) * kN);
+        std::memcpy(&itw_all[(size_t)l * kN], itw.data(), sizeof(tw_t) * kN);
+    }
+    int rcode;
+    if ((rcode = upload(h, &h->d_tw, tw_all.data(), tw_all.size() * sizeof(tw_t)))) return rcode;
+    if ((rcode = upload(h, &h->d_itw, itw_all.data(), itw_all.size() * sizeof(tw_t)))) return rcode;
+    for (uint32_t l = 0; l < p.limbs; l++) {
+        rc.limb[l].tw = h->d_tw.as<tw_t>() + (size_t)l * kN;
+        rc.limb[l].itw = h->d_itw.as<tw_t>() + (size_t)l * kN;
+    }
+    const uint32_t slots = p.batch_size;
+    std::vector<cplx> t_inv, t_fwd;
+    make_fft_tables(p.cyclotomic_order, slots, &t_inv, &t_fwd);
+    if ((rcode = upload(h, &h->d_fft_inv, t_inv.data(), slots * sizeof(cplx)))) return rcode;
+    if ((rcode = upload(h, &h->d_fft_fwd, t_fwd.data(), slots * sizeof(cplx)))) return rcode;
+    EncodeConst ec{};
+    ec.slots = slots; ec.gap = (kN / 2) / slots; ec.batch = h->batch;
+    ec.log_slots = 0;
+    while ((1u << ec.log_slots) < slots) ec.log_slots++;
+    ec.pow_p = (double)p.modulus[p.limbs - 1];
+    ec.inv_size = 1.0 / (double)slots;
+    ec.tw_inv = h->d_fft_inv.as<cplx>();
+    ec.tw_fwd = h->d_fft_fwd.as<cplx>();
+    Crt2Const crt = make_crt2(p.modulus[0], p.limbs >= 2 ? p.modulus[1] : 0);
+    build_gauss_cdf((double)p.sigma, h->gauss_cdf);
+    h->ctx = p; h->rc = rc; h->ec = ec; h->crt = crt;
+    h->have_cc = true;
+    return 0;
+}
+
+// key polynomial rows -> {value, Shoup companion} pairs on the device
+int upload_key_poly(shelfi_ckks *h, DeviceBuffer *buf, const uint64_t *rows) {
+    const uint32_t L = h->ctx.limbs;
+    std::vector<tw_t> packed((size_t)L * kN);
+    for (uint32_t l = 0; l < L; l++)
+        for (uint32_t j = 0; j < (uint32_t)kN; j++) {
+            uint64_t v = rows[(size_t)l * kN + j];
+            if (v >= h->ctx.modulus[l]) return fail(h, SHELFI_ERR_FORMAT, "key coefficient not reduced");
+            packed[(size_t)l * kN + j] = tw_t{v, nt::shoup(v, h->ctx.modulus[l])};
+        }
+    return upload(h, buf, packed.data(), packed.size() * sizeof(tw_t));
+}
+
+bool same_ring(const wire::ContextParams &a, const wire::ContextParams &b) {
+    return a.ring_dim == b.ring_dim && a.limbs == b.limbs &&
+           !std::memcmp(a.modulus, b.modulus, sizeof(uint64_t) * a.limbs) &&
+           !std::memcmp(a.root, b.root, sizeof(uint64_t) * a.limbs);
+}
+
+BlobRuns to_runs(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t L) {
+    BlobRuns br{};
+    br.runs = 2 * L;
+    for (uint32_t r = 0; r < 2 * L; r++) { br.off0[r] = run0[r]; br.off1[r] = run1[r]; }
+    br.stride = stride;
+    return br;
+}
+size_t image_bytes(uint64_t blob_size) { return ((size_t)blob_size + 7) / 8 * 8 + 8; }
+
+int64_t weight_constant(const shelfi_ckks *h, float w) {
+    double sc = (double)w;  // ckks.cpp:287 narrows to float32; PALISADE's EvalMult(ct, double) widens it back
+    return (int64_t)(sc * (double)h->ctx.modulus[h->ctx.limbs - 1] + 0.5);
+}
+
+uint64_t fresh_seed() {
+    std::random_device rd;
+    return ((uint64_t)rd() << 32) ^ (uint64_t)rd() ^ ((uint64_t)rd() << 16);
+}
+
+// --- stage drivers (all asynchronous on `s`) ---
+int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct, cudaStream_t s) {
+    uint64_t n_ct = (n + h->batch - 1) / h->batch;
+    if (n_ct > 0x7fffffffull / (2 * kMaxLimbs)) return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
+    CU(h->s_m.reserve(n_ct * kN * sizeof(int64_t)));
+    CU(h->s_ve.reserve(n_ct * kN * sizeof(uint16_t)));
+    SamplerConst sc{};
+    sc.seed = h->seeded ? h->seed : fresh_seed();
+    sc.ct_index0 = ct_index0;
+    std::memcpy(sc.gauss_cdf, h->gauss_cdf, sizeof sc.gauss_cdf);
+    launch_encode_sample(h->rc, h->ec, sc, d_x, n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s);
+    launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), d_ct,
+                   (u32)n_ct, s);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
+                  cudaStream_t s) {
+    if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "decode implements the 1- and 2-limb CRT only");
+    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * kN * sizeof(uint64_t)));
+    launch_decrypt_intt(h->rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
+    DecodeConst dc{};
+    dc.crt = h->crt;
+    double p = (double)h->ctx.plaintext_modulus;
+    dc.pre = std::pow(sf, -1) * std::pow(2, p);   // [PAL] Decode: scale to 2^p before the FFT, back after it
+    dc.pow_p = std::pow(2, -p);
+    launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int check_stage(shelfi_ckks *h, bool need_pk, bool need_sk) {
+    if (!h) return SHELFI_ERR_ARG;
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (!h->have_cc) return fail(h, SHELFI_ERR_NOT_LOADED, "crypto context not loaded (call loadCryptoParams)");
+    if (need_pk && !h->have_pk) return fail(h, SHELFI_ERR_NOT_LOADED, "public key not loaded");
+    if (need_sk && !h->have_sk) return fail(h, SHELFI_ERR_NOT_LOADED, "private key not loaded");
+    if (h->batch == 0 || h->batch > h->ctx.batch_size)
+        return fail(h, SHELFI_ERR_PARAMS, "batchSize exceeds the slots of the loaded context");
+    return 0;
+}
+
+// copy the header segments of a planned blob around the coefficient runs already in `dst`
+void write_segments(const wire::BlobPlan &plan, uint8_t *dst) {
+    for (const auto &seg : plan.segments) std::memcpy(dst + seg.offset, seg.bytes.data(), seg.bytes.size());
+}
+
+int encrypt_host(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint64_t cap, uint8_t **alloc_out,
+                 uint64_t *blob_len) {
+    int rcode = check_stage(h, true, false);
+    if (rcode) return rcode;
+    if (!x || !blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    if (n == 0) return fail(h, SHELFI_ERR_ARG, "empty input (undefined behaviour in the reference, ckks.cpp:66,95)");
+    const uint64_t n_ct = (n + h->batch - 1) / h->batch;
+    std::vector<wire::CiphertextMeta> meta(1);
+    meta[0].depth = 1; meta[0].level = 0; meta[0].encoding_type = 4;
+    meta[0].scaling_factor = (double)h->ctx.modulus[h->ctx.limbs - 1];
+    std::memcpy(meta[0].tag, h->key_tag.c_str(), 32);
+    wire::BlobPlan plan = wire::plan_ciphertext_blob(h->ctx, n_ct, meta);
+    if (alloc_out) {
+        dst = static_cast<uint8_t *>(std::malloc(plan.size));
+        if (!dst) return fail(h, SHELFI_ERR_ARG, "out of host memory");
+    } else if (!dst || cap < plan.size) {
+        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
+    }
+    cudaStream_t s = h->stream;
+    const uint64_t ct_words = 2ull * h->ctx.limbs * kN;
+    auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
+#define CUB(call)                                                              \
+    do {                                                                       \
+        cudaError_t e__ = (call);                                              \
+        if (e__ != cudaSuccess) return bail(cuda_fail(h, e__, #call));         \
+    } while (0)
+    CUB(h->s_x.reserve(n * sizeof(double)));
+    CUB(h->s_dense.reserve(n_ct * ct_words * 8));
+    CUB(h->s_image.reserve(image_bytes(plan.size)));
+    CUB(cudaMemcpyAsync(h->s_x.p, x, n * sizeof(double), cudaMemcpyHostToDevice, s));
+    if ((rcode = encrypt_dense(h, h->s_x.as<double>(), n, 0, h->s_dense.as<u64>(), s))) return bail(rcode);
+    launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), h->s_dense.as<u64>(),
+                h->s_image.as<u64>(), n_ct, s);
+    CUB(cudaGetLastError());
+    CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
+    CUB(cudaStreamSynchronize(s));
+    write_segments(plan, dst);
+    if (alloc_out) *alloc_out = dst;
+    *blob_len = plan.size;
+    return 0;
+}
+
+int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *lens, const float *w, uint32_t k,
+              uint8_t *dst, uint64_t cap, uint8_t **alloc_out, uint64_t *blob_len) {
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!blobs || !lens || !w || !blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    if (k == 0) return fail(h, SHELFI_ERR_ARG, "no learners");
+    const uint32_t L = h->ctx.limbs;
+    const double sf0 = (double)h->ctx.modulus[L - 1];
+    std::vector<wire::BlobMap> maps(k);
+    for (uint32_t i = 0; i < k; i++) {  // ckks.cpp:278-281 Deserialize, minus the payload copy
+        if (!blobs[i]) return fail(h, SHELFI_ERR_ARG, "null blob");
+        std::string e = wire::map_ciphertext_blob(blobs[i], lens[i], false, &maps[i]);
+        if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, "learner " + std::to_string(i) + ": " + e);
+        if (!same_ring(maps[i].ctx, h->ctx))
+            return fail(h, SHELFI_ERR_PARAMS, "learner " + std::to_string(i) + ": ciphertext parameters differ from the loaded context");
+        if (maps[i].n_ct != maps[0].n_ct)
+            return fail(h, SHELFI_ERR_PARAMS, "learner " + std::to_string(i) + ": ciphertext count differs");
+        for (const auto &m : maps[i].meta)
+            if (m.depth != 1 || m.level != 0)
+                return fail(h, SHELFI_ERR_UNSUPPORTED, "learner " + std::to_string(i) + ": only fresh depth-1 level-0 ciphertexts are supported");
+    }
+    const uint64_t n_ct = maps[0].n_ct;
+    std::vector<wire::CiphertextMeta> meta = maps[0].meta;  // ckks.cpp:291-292: result starts as learner 0's vector
+    for (auto &m : meta) { m.depth += 1; m.scaling_factor *= sf0; }  // [PAL] EvalMult(ct, double), no rescale
+    wire::BlobPlan plan = wire::plan_ciphertext_blob(maps[0].ctx, n_ct, meta);
+    if (alloc_out) {
+        dst = static_cast<uint8_t *>(std::malloc(plan.size));
+        if (!dst) return fail(h, SHELFI_ERR_ARG, "out of host memory");
+    } else if (!dst || cap < plan.size) {
+        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
+    }
+    auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
+    cudaStream_t s = h->stream, cs = h->copy_stream;
+    const uint64_t ct_words = 2ull * L * kN;
+    size_t max_image = 0;
+    for (uint32_t i = 0; i < k; i++) max_image = std::max(max_image, image_bytes(lens[i]));
+    CUB(h->s_dense.reserve(n_ct * ct_words * 8));
+    CUB(h->s_image.reserve(std::max(max_image, image_bytes(plan.size))));
+    CUB(h->s_image2.reserve(max_image));
+    DeviceBuffer *img[2] = {&h->s_image, &h->s_image2};
+    // learner i+1 streams in over PCIe while learner i is folded into the accumulator
+    for (uint32_t i = 0; i < k; i++) {
+        int b = i & 1;
+        if (i >= 2) CUB(cudaStreamWaitEvent(cs, h->ev_done[b], 0));
+        CUB(cudaMemcpyAsync(img[b]->p, blobs[i], lens[i], cudaMemcpyHostToDevice, cs));
+        CUB(cudaEventRecord(h->ev_copy[b], cs));
+        CUB(cudaStreamWaitEvent(s, h->ev_copy[b], 0));
+        int64_t sc = weight_constant(h, w[i]);
+        LimbScalars cs_l{};
+        for (uint32_t l = 0; l < L; l++) cs_l.c[l] = nt::signed_mod(sc, h->ctx.modulus[l]);
+        launch_unpack_scale_accumulate(h->rc, to_runs(maps[i].run0, maps[i].run1, maps[i].stride, L), img[b]->as<u64>(),
+                                       cs_l, i == 0 ? 1u : 0u, h->s_dense.as<u64>(), n_ct, s);
+        CUB(cudaGetLastError());
+        CUB(cudaEventRecord(h->ev_done[b], s));
+    }
+    launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, L), h->s_dense.as<u64>(), h->s_image.as<u64>(), n_ct, s);
+    CUB(cudaGetLastError());
+    CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
+    CUB(cudaStreamSynchronize(s));
+    write_segments(plan, dst);
+    if (alloc_out) *alloc_out = dst;
+    *blob_len = plan.size;
+    return 0;
+}
+
+int decrypt_host(shelfi_ckks *h, const uint8_t *blob, uint64_t len, uint64_t n, double *out) {
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!blob || !out) return fail(h, SHELFI_ERR_ARG, "null argument");
+    wire::BlobMap map;
+    std::string e = wire::map_ciphertext_blob(blob, len, false, &map);
+    if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, e);
+    if (!same_ring(map.ctx, h->ctx)) return fail(h, SHELFI_ERR_PARAMS, "ciphertext parameters differ from the loaded context");
+    const uint64_t n_ct = map.n_ct, batch = h->batch;
+    if (n == 0 || n > n_ct * batch || n + batch <= n_ct * batch)
+        return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
+    const uint32_t L = h->ctx.limbs;
+    const uint64_t ct_words = 2ull * L * kN;
+    cudaStream_t s = h->stream;
+    CU(h->s_image.reserve(image_bytes(len)));
+    CU(h->s_dense.reserve(n_ct * ct_words * 8));
+    CU(h->s_out.reserve(n * sizeof(double)));
+    CU(cudaMemcpyAsync(h->s_image.p, blob, len, cudaMemcpyHostToDevice, s));
+    launch_unpack(h->rc, to_runs(map.run0, map.run1, map.stride, L), h->s_image.as<u64>(), h->s_dense.as<u64>(), n_ct, s);
+    CU(cudaGetLastError());
+    // ciphertexts usually share one scaling factor; split the launch where they do not
+    uint64_t j0 = 0;
+    while (j0 < n_ct) {
+        uint64_t j1 = j0 + 1;
+        while (j1 < n_ct && map.meta[j1].scaling_factor == map.meta[j0].scaling_factor) j1++;
+        uint64_t first = j0 * batch, last = std::min(n, j1 * batch);
+        if ((rcode = decrypt_dense(h, h->s_dense.as<u64>() + j0 * ct_words, j1 - j0, map.meta[j0].scaling_factor,
+                                   h->s_out.as<double>() + first, last - first, s)))
+            return rcode;
+        CU(cudaStreamSynchronize(s));  // decrypt_dense reuses one coefficient scratch
+        j0 = j1;
+    }
+    CU(cudaMemcpyAsync(out, h->s_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return 0;
+}
+
+}  // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+const char *shelfi_version(void) { return "0.1.0-b200"; }
+
+int shelfi_ckks_create(const char *scheme, uint32_t batch_size, uint32_t scale_factor_bits, const char *cryptodir,
+                       int device, shelfi_ckks **out) {
+    if (!out) return SHELFI_ERR_ARG;
+    shelfi_ckks *h = new shelfi_ckks();
+    h->scheme = scheme ? scheme : "ckks";
+    h->batch = batch_size;
+    h->scale_bits = scale_factor_bits;
+    h->cryptodir = cryptodir ? cryptodir : "";
+    h->device = device;
+    *out = h;
+    return 0;
+}
+
+void shelfi_ckks_destroy(shelfi_ckks *h) {
+    if (!h) return;
+    if (h->cuda_ready) {
+        cudaSetDevice(h->device);
+        cudaDeviceSynchronize();
+        free_params(h);
+        for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_out})
+            b->release();
+        for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_copy[i]); cudaEventDestroy(h->ev_done[i]); }
+        cudaStreamDestroy(h->stream);
+        cudaStreamDestroy(h->copy_stream);
+    }
+    delete h;
+}
+
+const char *shelfi_last_error(const shelfi_ckks *h) { return h ? h->err.c_str() : "null handle"; }
+
+int shelfi_load_crypto_params_from_memory(shelfi_ckks *h, const uint8_t *cc, size_t cc_len, const uint8_t *pk,
+                                          size_t pk_len, const uint8_t *sk, size_t sk_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    h->have_cc = h->have_pk = h->have_sk = false;
+    int missing = 0;
+    std::string detail;
+    wire::ContextParams ctx;
+    std::string e = cc ? wire::parse_context(cc, cc_len, &ctx) : std::string("file missing");
+    if (e.empty()) {
+        rcode = install_context(h, ctx);
+        if (rcode) return rcode;
+    } else {
+        missing |= 1;
+        detail += "cryptocontext: " + e + "; ";
+    }
+    wire::KeyFile key;
+    e = !h->have_cc ? std::string("no context") : pk ? wire::parse_public_key(pk, pk_len, &key) : std::string("file missing");
+    if (e.empty() && !same_ring(key.ctx, h->ctx)) e = "key belongs to different parameters";
+    if (e.empty()) {
+        size_t words = (size_t)h->ctx.limbs * kN;
+        if ((rcode = upload_key_poly(h, &h->d_pk_b, key.polys.data()))) return rcode;
+        if ((rcode = upload_key_poly(h, &h->d_pk_a, key.polys.data() + words))) return rcode;
+        h->key_tag = key.tag;
+        h->have_pk = true;
+    } else {
+        missing |= 2;
+        detail += "key-public: " + e + "; ";
+    }
+    wire::KeyFile skey;
+    e = !h->have_cc ? std::string("no context") : sk ? wire::parse_private_key(sk, sk_len, &skey) : std::string("file missing");
+    if (e.empty() && !same_ring(skey.ctx, h->ctx)) e = "key belongs to different parameters";
+    if (e.empty()) {
+        if ((rcode = upload_key_poly(h, &h->d_sk, skey.polys.data()))) return rcode;
+        if (!h->have_pk) h->key_tag = skey.tag;
+        h->have_sk = true;
+    } else {
+        missing |= 4;
+        detail += "key-private: " + e + "; ";
+    }
+    h->err = detail;
+    return missing;
+}
+
+int shelfi_load_crypto_params(shelfi_ckks *h) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::vector<uint8_t> f[3];
+    bool ok[3];
+    static const char *names[3] = {"cryptocontext.txt", "key-public.txt", "key-private.txt"};
+    for (int i = 0; i < 3; i++) ok[i] = read_file(h->cryptodir + names[i], &f[i]);  // ckks.cpp:12,16,20
+    return shelfi_load_crypto_params_from_memory(h, ok[0] ? f[0].data() : nullptr, f[0].size(),
+                                                 ok[1] ? f[1].data() : nullptr, f[1].size(),
+                                                 ok[2] ? f[2].data() : nullptr, f[2].size());
+}
+
+int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h) {
+    // ckks.cpp:25-59: genCryptoContextCKKS(multDepth = 1, scaleFactorBits, batchSize), Enable(ENCRYPTION | SHE),
+    // KeyGen, three SerializeToFile calls; the object's own context/keys stay untouched.
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (ensure_cuda(h)) return 0;
+    const uint32_t bits = h->scale_bits, batch = h->batch;
+    if (bits < 14 || bits > 59) { fail(h, SHELFI_ERR_ARG, "scaleFactorBits must be in [14, 59]"); return 0; }
+    const uint32_t N = nt::select_ring_dim(bits);
+    if (N != (uint32_t)kN) { fail(h, SHELFI_ERR_UNSUPPORTED, "parameter set needs a ring dimension other than 8192"); return 0; }
+    if (batch == 0 || (batch & (batch - 1)) || batch > N / 2) {
+        fail(h, SHELFI_ERR_ARG, "batchSize must be a power of two <= N/2");
+        return 0;
+    }
+    wire::ContextParams p;
+    p.ring_dim = N; p.cyclotomic_order = 2 * N; p.limbs = 2;
+    p.modulus[1] = nt::first_prime(bits, 2 * N);                            // scaling prime = level-0 scaling factor
+    p.modulus[0] = nt::previous_prime(nt::first_prime(60, 2 * N), 2 * N);   // 60-bit first modulus
+    for (int l = 0; l < 2; l++) p.root[l] = nt::min_primitive_root(2 * N, p.modulus[l]);
+    wire::set_big_modulus(&p);
+    p.plaintext_modulus = bits; p.batch_size = batch;
+    p.sigma = 3.19f; p.assurance = 9.0f; p.hermite = 1.006f;
+    // relinWindow, depth, maxDepth, [extra word of newer PALISADE], mode OPTIMIZED, HEStd_128_classic,
+    // EXACTRESCALE, HYBRID, dnum
+    const char *variant = std::getenv("SHELFI_WIRE_VARIANT");
+    if (variant && std::atoi(variant) == 8) {
+        const uint32_t v[8] = {0, 1, 2, 1, 0, 2, 1, 2};
+        std::memcpy(p.rlwe_ints, v, sizeof v); p.rlwe_int_count = 8;
+    } else {
+        const uint32_t v[9] = {0, 1, 2, 0, 1, 0, 2, 1, 2};
+        std::memcpy(p.rlwe_ints, v, sizeof v); p.rlwe_int_count = 9;
+    }
+    p.enabled_features = 5;  // ENCRYPTION | SHE (ckks.cpp:32-33)
+    if (!write_file(h->cryptodir + "cryptocontext.txt", wire::emit_context(p))) {  // ckks.cpp:41
+        fail(h, SHELFI_ERR_IO, "cannot write cryptocontext.txt");
+        return 0;
+    }
+    // [PAL] KeyGen: s <- ternary, e <- Gaussian, a <- uniform (EVALUATION), b = e - a*s.  The transforms
+    // run on the device through a scratch handle so this object's loaded state is left alone.
+    shelfi_ckks tmp;
+    tmp.device = h->device; tmp.batch = batch; tmp.scale_bits = bits;
+    auto cleanup = [&]() { free_params(&tmp); tmp.s_dense.release(); if (tmp.stream) cudaStreamDestroy(tmp.stream);
+                           if (tmp.copy_stream) cudaStreamDestroy(tmp.copy_stream);
+                           for (int i = 0; i < 2; i++) { if (tmp.ev_copy[i]) cudaEventDestroy(tmp.ev_copy[i]);
+                                                         if (tmp.ev_done[i]) cudaEventDestroy(tmp.ev_done[i]); } };
+    if (ensure_cuda(&tmp) || install_context(&tmp, p)) { h->err = tmp.err; cleanup(); return 0; }
+    const uint64_t seed = h->seeded ? h->seed : fresh_seed();
+    std::vector<uint64_t> rows(4 * (size_t)N);  // s limb0, s limb1, e limb0, e limb1
+    u32 o[4];
+    for (uint32_t j = 0; j < N; j++) {
+        philox4x32_10(seed, j >> 2, 0, 0, kStreamKeyS, o);
+        int sv = ternary_from_u32(o[j & 3]);
+        philox4x32_10(seed, j, 0, 0, kStreamKeyE, o);
+        int ev = gauss_from_u64(tmp.gauss_cdf, ((uint64_t)o[1] << 32) | o[0]);
+        for (int l = 0; l < 2; l++) {
+            rows[(size_t)l * N + j] = nt::signed_mod(sv, p.modulus[l]);
+            rows[(size_t)(2 + l) * N + j] = nt::signed_mod(ev, p.modulus[l]);
+        }
+    }
+    bool ok = tmp.s_dense.reserve(rows.size() * 8) == cudaSuccess &&
+              cudaMemcpy(tmp.s_dense.p, rows.data(), rows.size() * 8, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok) {
+        launch_ntt_forward(tmp.rc, tmp.s_dense.as<u64>(), 4, tmp.stream);
+        ok = cudaStreamSynchronize(tmp.stream) == cudaSuccess &&
+             cudaMemcpy(rows.data(), tmp.s_dense.p, rows.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess;
+    }
+    if (!ok) { fail(h, SHELFI_ERR_CUDA, "key generation transforms failed"); cleanup(); return 0; }
+    wire::KeyFile pub, priv;
+    pub.ctx = p; priv.ctx = p;
+    pub.polys.assign(4 * (size_t)N, 0);
+    priv.polys.assign(rows.begin(), rows.begin() + 2 * (size_t)N);
+    for (int l = 0; l < 2; l++) {
+        const uint64_t q = p.modulus[l];
+        const int qbits = 64 - __builtin_clzll(q);
+        for (uint32_t j = 0; j < N; j++) {
+            uint64_t a;
+            uint32_t tries = 0;
+            do {  // uniform below q by rejection on the top bits of a 64-bit draw
+                philox4x32_10(seed, j, (u32)l, tries++, kStreamKeyA, o);
+                a = (((uint64_t)o[1] << 32) | o[0]) >> (64 - qbits);
+            } while (a >= q);
+            uint64_t sv = rows[(size_t)l * N + j], ev = rows[(size_t)(2 + l) * N + j];
+            pub.polys[(size_t)(2 + l) * N + j] = a;
+            pub.polys[(size_t)l * N + j] = nt::sub_mod(ev, nt::mul_mod(a, sv, q), q);
+        }
+    }
+    char tag[33];
+    for (int i = 0; i < 8; i++) {  // [PAL] GenerateUniqueKeyID: 32 hex characters
+        philox4x32_10(seed, (u32)i, 0, 0, 99, o);
+        std::snprintf(tag + 4 * i, 5, "%04x", o[0] & 0xffff);
+    }
+    pub.tag = tag; priv.tag = tag;
+    cleanup();
+    if (!write_file(h->cryptodir + "key-public.txt", wire::emit_public_key(pub))) {  // ckks.cpp:48
+        fail(h, SHELFI_ERR_IO, "cannot write key-public.txt");
+        return 0;
+    }
+    if (!write_file(h->cryptodir + "key-private.txt", wire::emit_private_key(priv))) {  // ckks.cpp:53
+        fail(h, SHELFI_ERR_IO, "cannot write key-private.txt");
+        return 0;
+    }
+    return 1;
+}
+
+int shelfi_set_sampler_seed(shelfi_ckks *h, uint64_t seed) {
+    if (!h) return SHELFI_ERR_ARG;
+    h->seeded = true; h->seed = seed;
+    return 0;
+}
+int shelfi_clear_sampler_seed(shelfi_ckks *h) {
+    if (!h) return SHELFI_ERR_ARG;
+    h->seeded = false;
+    return 0;
+}
+
+uint32_t shelfi_ring_dim(const shelfi_ckks *h) { return h && h->have_cc ? h->ctx.ring_dim : 0; }
+uint32_t shelfi_num_limbs(const shelfi_ckks *h) { return h && h->have_cc ? h->ctx.limbs : 0; }
+uint32_t shelfi_slots(const shelfi_ckks *h) { return h && h->have_cc ? h->ctx.batch_size : 0; }
+uint32_t shelfi_batch_size(const shelfi_ckks *h) { return h ? h->batch : 0; }
+uint64_t shelfi_modulus(const shelfi_ckks *h, uint32_t l) { return h && h->have_cc && l < h->ctx.limbs ? h->ctx.modulus[l] : 0; }
+uint64_t shelfi_root_of_unity(const shelfi_ckks *h, uint32_t l) { return h && h->have_cc && l < h->ctx.limbs ? h->ctx.root[l] : 0; }
+double shelfi_scaling_factor(const shelfi_ckks *h) { return h && h->have_cc ? (double)h->ctx.modulus[h->ctx.limbs - 1] : 0.0; }
+int shelfi_key_tag(const shelfi_ckks *h, char out[33]) {
+    if (!h || !out) return SHELFI_ERR_ARG;
+    std::memset(out, 0, 33);
+    std::memcpy(out, h->key_tag.c_str(), std::min<size_t>(32, h->key_tag.size()));
+    return 0;
+}
+uint64_t shelfi_num_ciphertexts(const shelfi_ckks *h, uint64_t n) { return h && h->batch ? (n + h->batch - 1) / h->batch : 0; }
+uint64_t shelfi_ciphertext_words(const shelfi_ckks *h) { return h && h->have_cc ? 2ull * h->ctx.limbs * kN : 0; }
+uint64_t shelfi_blob_size(const shelfi_ckks *h, uint64_t n_ct) {
+    return h && h->have_cc && n_ct ? wire::ciphertext_blob_size(h->ctx, n_ct) : 0;
+}
+int64_t shelfi_weight_constant(const shelfi_ckks *h, float w) { return h && h->have_cc ? weight_constant(h, w) : 0; }
+
+int shelfi_encrypt(shelfi_ckks *h, const double *x, uint64_t n, uint8_t **blob, uint64_t *blob_len) {
+    if (!h || !blob) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return encrypt_host(h, x, n, nullptr, 0, blob, blob_len);
+}
+int shelfi_encrypt_into(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint64_t cap, uint64_t *blob_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return encrypt_host(h, x, n, dst, cap, nullptr, blob_len);
+}
+int shelfi_compute_weighted_average(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                    const float *weights, uint32_t k, uint8_t **blob, uint64_t *blob_len) {
+    if (!h || !blob) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return wavg_host(h, blobs, blob_lens, weights, k, nullptr, 0, blob, blob_len);
+}
+int shelfi_compute_weighted_average_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                         const float *weights, uint32_t k, uint8_t *dst, uint64_t cap,
+                                         uint64_t *blob_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return wavg_host(h, blobs, blob_lens, weights, k, dst, cap, nullptr, blob_len);
+}
+int shelfi_decrypt(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint64_t n, double *out) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return decrypt_host(h, blob, blob_len, n, out);
+}
+
+void shelfi_free(void *p) { std::free(p); }
+void *shelfi_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    return cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? p : nullptr;
+}
+void shelfi_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int shelfi_encrypt_device(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct,
+                          void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, true, false);
+    if (rcode) return rcode;
+    if (!d_x || !d_ct || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    return encrypt_dense(h, d_x, n, ct_index0, d_ct, static_cast<cudaStream_t>(stream));
+}
+
+int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
+                               uint64_t n_ct, uint64_t *d_out, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!d_cts || !weights || !d_out || k == 0 || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    const uint32_t L = h->ctx.limbs;
+    for (uint32_t base = 0; base < k; base += kMaxLearnersPerLaunch) {
+        WavgArgs wa{};
+        wa.k = std::min<uint32_t>(kMaxLearnersPerLaunch, k - base);
+        wa.accumulate = base ? 1u : 0u;
+        for (uint32_t i = 0; i < wa.k; i++) {
+            wa.in[i] = reinterpret_cast<const u64 *>(d_cts[base + i]);
+            int64_t sc = weight_constant(h, weights[base + i]);
+            for (uint32_t l = 0; l < L; l++) wa.c[i][l] = nt::signed_mod(sc, h->ctx.modulus[l]);
+        }
+        launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, static_cast<cudaStream_t>(stream));
+    }
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
+                          uint64_t n, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!d_ct || !d_out || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    if (n == 0 || n > n_ct * h->batch || n + h->batch <= n_ct * h->batch)
+        return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
+    return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n,
+                         static_cast<cudaStream_t>(stream));
+}
+
+int shelfi_pack_device(shelfi_ckks *h, const uint64_t *d_dense, uint64_t n_ct, uint8_t *d_image, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    std::vector<wire::CiphertextMeta> meta(1);
+    wire::BlobPlan plan = wire::plan_ciphertext_blob(h->ctx, n_ct, meta);
+    launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), reinterpret_cast<const u64 *>(d_dense),
+                reinterpret_cast<u64 *>(d_image), n_ct, static_cast<cudaStream_t>(stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+int shelfi_unpack_device(shelfi_ckks *h, const uint8_t *d_image, uint64_t n_ct, uint64_t *d_dense, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    std::vector<wire::CiphertextMeta> meta(1);
+    wire::BlobPlan plan = wire::plan_ciphertext_blob(h->ctx, n_ct, meta);
+    launch_unpack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), reinterpret_cast<const u64 *>(d_image),
+                  reinterpret_cast<u64 *>(d_dense), n_ct, static_cast<cudaStream_t>(stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    launch_ntt_forward(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+int shelfi_ntt_inverse_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    launch_ntt_inverse(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+int shelfi_encode_device(shelfi_ckks *h, const double *d_x, uint64_t n, int64_t *d_coeff, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!d_x || !d_coeff || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    uint64_t n_ct = (n + h->batch - 1) / h->batch;
+    launch_encode_only(h->rc, h->ec, d_x, n, (u32)n_ct, reinterpret_cast<i64 *>(d_coeff), static_cast<cudaStream_t>(stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, int64_t *d_hi, uint64_t *d_lo,
+                                  void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "decode implements the 1- and 2-limb CRT only");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * kN * sizeof(uint64_t)));
+    launch_decrypt_intt(h->rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
+    DecodeConst dc{};
+    dc.crt = h->crt;
+    launch_crt_only(h->rc, dc, h->s_coeff.as<u64>(), (u32)n_ct, reinterpret_cast<i64 *>(d_hi), reinterpret_cast<u64 *>(d_lo), s);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,42 @@
+// kernels.h — host-side launchers of the sm_100a kernels (kernels.cu).  Plain C++ signatures, no
+// CUDA types beyond cudaStream_t, so engine.cpp stays ordinary host code.
+#pragma once
+#include <cuda_runtime.h>
+#include "ckks_core.cuh"
+
+namespace shelfi {
+
+cudaError_t kernels_init();  // opt-in shared-memory sizes; call once per device
+
+// in-place transforms of `rows` limb polynomials laid out [row][N], limb = row % L
+void launch_ntt_forward(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
+void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
+
+// encode + sample: x[n] -> m_e0[n_ct][N] (m + e0, signed) and ve[n_ct][N] (v in the low byte, e1 in the high byte)
+void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
+                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s);
+// encrypt: three forward NTTs per (ciphertext, limb) + public-key combine -> ct[n_ct][2][L][N]
+void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
+                    u64 *ct, u32 n_ct, cudaStream_t s);
+// decrypt stage 1: c0 + c1*s, inverse NTT -> coeff[n_ct][L][N]
+void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s);
+// decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
+void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
+                   double *out, u64 n, cudaStream_t s);
+// debug/parity taps of the two halves above
+void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
+                        cudaStream_t s);
+void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coeff, u32 n_ct, i64 *hi, u64 *lo,
+                     cudaStream_t s);
+
+// out = sum_k c_k * in_k mod q over dense payloads of n_ct ciphertexts
+void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 n_ct, cudaStream_t s);
+
+// serialized blob image <-> dense payload
+void launch_unpack(const RingConst &rc, const BlobRuns &br, const u64 *image, u64 *dense, u64 n_ct, cudaStream_t s);
+void launch_pack(const RingConst &rc, const BlobRuns &br, const u64 *dense, u64 *image, u64 n_ct, cudaStream_t s);
+// acc (+)= c * unpack(image) : one learner streamed into the resident accumulator
+void launch_unpack_scale_accumulate(const RingConst &rc, const BlobRuns &br, const u64 *image, const LimbScalars &cs,
+                                    u32 first, u64 *acc, u64 n_ct, cudaStream_t s);
+
+}  // namespace shelfi

@@ -1,0 +1,142 @@
+/*
+ * shelfi_b200.h — C ABI of the B200-native CKKS aggregation engine (libshelfi_b200.so).
+ *
+ * Drop-in boundary for the reference's SHELFI_FHE pybind module.  Every entry point names the
+ * reference interface it replaces; paths are relative to the reference repository
+ * (wzjin2017/fhe-fed), directory palisade_pybind/SHELFI_FHE/.
+ *
+ *   reference (pybind, src/binding.cpp:18-31)            this library
+ *   ------------------------------------------------    ------------------------------------------
+ *   CKKS(scheme, batchSize, scaleFactorBits, cryptodir)  shelfi_ckks_create          (src/ckks.cpp:5-9)
+ *   CKKS::loadCryptoParams()                             shelfi_load_crypto_params   (src/ckks.cpp:11-23)
+ *   CKKS::genCryptoContextAndKeyGen()                    shelfi_gen_crypto_context_and_keygen (src/ckks.cpp:25-59)
+ *   CKKS::encrypt(ndarray) -> bytes                      shelfi_encrypt[_into]       (src/ckks.cpp:61-104)
+ *   CKKS::computeWeightedAverage(list, list) -> bytes    shelfi_compute_weighted_average[_into] (src/ckks.cpp:264-320)
+ *   CKKS::decrypt(bytes, n) -> ndarray                   shelfi_decrypt              (src/ckks.cpp:170-213)
+ *   encrypt_cpp / decrypt_cpp / computeWeightedAverage_cpp  same three calls (binding.cpp:27,29,31 bind the
+ *                                                        *_cpp names to the same methods; include/ckks.h:46-52)
+ *
+ * All hot-path work runs in hand-written sm_100a CUDA kernels; there is no CPU fallback: every call
+ * fails with SHELFI_ERR_CUDA when no usable device is present.
+ *
+ * Conventions: functions return 0 on success or a negative SHELFI_ERR_* code (exceptions noted);
+ * shelfi_last_error(h) describes the last failure on that handle.  Inputs are borrowed for the
+ * duration of the call; outputs returned through `uint8_t **` are owned by the library and released
+ * with shelfi_free.  A handle serialises its calls internally (the reference object is not
+ * thread-safe either, binding.cpp holds the GIL throughout).
+ */
+#ifndef SHELFI_B200_H
+#define SHELFI_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct shelfi_ckks shelfi_ckks;
+
+enum {
+    SHELFI_OK = 0,
+    SHELFI_ERR_ARG = -1,        /* bad argument (null, zero length, mismatched sizes) */
+    SHELFI_ERR_NOT_LOADED = -2, /* context / key needed by the call is not loaded */
+    SHELFI_ERR_FORMAT = -3,     /* malformed or unsupported serialized object */
+    SHELFI_ERR_PARAMS = -4,     /* object belongs to different crypto parameters */
+    SHELFI_ERR_CUDA = -5,       /* CUDA runtime failure (including: no device) */
+    SHELFI_ERR_IO = -6,         /* file could not be read / written */
+    SHELFI_ERR_UNSUPPORTED = -7 /* outside what the engine implements (e.g. ring dimension != 8192) */
+};
+
+/* ---- lifecycle: CKKS::CKKS (src/ckks.cpp:5-9, defaults src/binding.cpp:19-23) ---- */
+/* cryptodir is concatenated raw with the three file names, so it must end in '/', as in the reference.
+ * device = CUDA ordinal (one process per GPU: pass LOCAL_RANK). */
+int shelfi_ckks_create(const char *scheme, uint32_t batch_size, uint32_t scale_factor_bits, const char *cryptodir,
+                       int device, shelfi_ckks **out);
+void shelfi_ckks_destroy(shelfi_ckks *h);
+const char *shelfi_last_error(const shelfi_ckks *h);
+
+/* CKKS::loadCryptoParams (src/ckks.cpp:11-23).  Returns a bit mask of what could NOT be loaded
+ * (1 context, 2 public key, 4 private key; 0 = all three) — the reference prints and carries on; the
+ * Python shim reproduces that.  A negative value is a SHELFI_ERR_* (e.g. no CUDA device). */
+int shelfi_load_crypto_params(shelfi_ckks *h);
+/* same, from memory images of cryptocontext.txt / key-public.txt / key-private.txt (any may be NULL) */
+int shelfi_load_crypto_params_from_memory(shelfi_ckks *h, const uint8_t *cc, size_t cc_len, const uint8_t *pk,
+                                          size_t pk_len, const uint8_t *sk, size_t sk_len);
+/* CKKS::genCryptoContextAndKeyGen (src/ckks.cpp:25-59): multDepth 1, writes the three files into
+ * cryptodir, does not load them.  Returns 1 on success, 0 on failure — the reference's convention. */
+int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h);
+
+/* Encryption randomness comes from the OS by default.  A fixed seed makes the device sampler
+ * reproducible (tests, parity against the CPU oracle); never use it for real data. */
+int shelfi_set_sampler_seed(shelfi_ckks *h, uint64_t seed);
+int shelfi_clear_sampler_seed(shelfi_ckks *h);
+
+/* ---- introspection ---- */
+uint32_t shelfi_ring_dim(const shelfi_ckks *h);
+uint32_t shelfi_num_limbs(const shelfi_ckks *h);
+uint32_t shelfi_slots(const shelfi_ckks *h);
+uint32_t shelfi_batch_size(const shelfi_ckks *h);
+uint64_t shelfi_modulus(const shelfi_ckks *h, uint32_t limb);
+uint64_t shelfi_root_of_unity(const shelfi_ckks *h, uint32_t limb);
+double shelfi_scaling_factor(const shelfi_ckks *h);               /* q_last as double: level-0 scaling factor */
+int shelfi_key_tag(const shelfi_ckks *h, char out[33]);
+uint64_t shelfi_num_ciphertexts(const shelfi_ckks *h, uint64_t n); /* ceil(n / batchSize), src/ckks.cpp:65 */
+uint64_t shelfi_ciphertext_words(const shelfi_ckks *h);            /* 2 * L * N u64 per ciphertext (dense form) */
+uint64_t shelfi_blob_size(const shelfi_ckks *h, uint64_t n_ct);    /* bytes of a serialized vector of n_ct ciphertexts */
+/* EvalMult constant for a learner weight: (int64)((double)(float)w * scalingFactor + 0.5)  (src/ckks.cpp:287-288) */
+int64_t shelfi_weight_constant(const shelfi_ckks *h, float w);
+
+/* ---- reference-facing calls: host buffers in, host buffers out ---- */
+/* CKKS::encrypt (src/ckks.cpp:61-104): n doubles -> serialized vector<Ciphertext<DCRTPoly>>. */
+int shelfi_encrypt(shelfi_ckks *h, const double *x, uint64_t n, uint8_t **blob, uint64_t *blob_len);
+/* same, into a caller buffer of at least shelfi_blob_size(h, shelfi_num_ciphertexts(h, n)) bytes
+ * (pinned memory from shelfi_host_alloc avoids the staging copy) */
+int shelfi_encrypt_into(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint64_t cap, uint64_t *blob_len);
+/* CKKS::computeWeightedAverage (src/ckks.cpp:264-320): k blobs, k weights (float on purpose: the
+ * reference narrows each Python float to float32, src/ckks.cpp:287) -> one blob, depth 2. */
+int shelfi_compute_weighted_average(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                    const float *weights, uint32_t k, uint8_t **blob, uint64_t *blob_len);
+int shelfi_compute_weighted_average_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                         const float *weights, uint32_t k, uint8_t *dst, uint64_t cap,
+                                         uint64_t *blob_len);
+/* CKKS::decrypt (src/ckks.cpp:170-213): blob -> n doubles (n = data_dimensions). */
+int shelfi_decrypt(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint64_t n, double *out);
+
+void shelfi_free(void *p);
+/* page-locked host memory for the *_into calls and for inputs */
+void *shelfi_host_alloc(size_t bytes);
+void shelfi_host_free(void *p);
+
+/* ---- device-resident calls: the same three stages with inputs and outputs in HBM ----
+ * Ciphertext batches are dense limb-major u64 [n_ct][2][L][N] (the coefficient runs of the wire
+ * format, in wire order, without the bytes between them).  `stream` is a cudaStream_t (NULL =
+ * default stream); calls are asynchronous on it.  ct_index0 is the global index of the first
+ * ciphertext so that a shard draws the same sampler stream as the unsharded call. */
+int shelfi_encrypt_device(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct,
+                          void *stream);
+int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
+                               uint64_t n_ct, uint64_t *d_out, void *stream);
+int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
+                          uint64_t n, void *stream);
+/* dense <-> serialized image on the device (image buffers must be 8-byte aligned and hold
+ * shelfi_blob_size bytes rounded up to 8, plus 8) */
+int shelfi_pack_device(shelfi_ckks *h, const uint64_t *d_dense, uint64_t n_ct, uint8_t *d_image, void *stream);
+int shelfi_unpack_device(shelfi_ckks *h, const uint8_t *d_image, uint64_t n_ct, uint64_t *d_dense, void *stream);
+
+/* ---- primitives, exposed for parity tests and the NTT bandwidth metric ---- */
+/* rows limb polynomials [rows][N], limb = row % L; PALISADE ForwardTransformToBitReverse /
+ * InverseTransformFromBitReverse semantics, in place */
+int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream);
+int shelfi_ntt_inverse_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream);
+/* MakeCKKSPackedPlaintext up to the integer coefficients: n doubles -> int64 [n_ct][N] */
+int shelfi_encode_device(shelfi_ckks *h, const double *d_x, uint64_t n, int64_t *d_coeff, void *stream);
+/* Decrypt up to the centred CRT integer of every coefficient (two's complement hi/lo words) */
+int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, int64_t *d_hi, uint64_t *d_lo,
+                                  void *stream);
+
+const char *shelfi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

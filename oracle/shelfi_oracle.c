@@ -80,8 +80,7 @@ static int is_prime64(uint64_t n) {
 /* [PAL] FirstPrime<NativeInteger>(nBits, m): smallest prime q >= 2^nBits with q = 1 (mod m) */
 uint64_t orc_first_prime(uint32_t bits, uint32_t m) {
     uint64_t r = (uint64_t)1 << bits;
-    uint64_t q = r + ((m - (r % m)) % m) + 1; /* first value = 1 mod m above 2^bits */
-    if (q <= r) q += m;
+    uint64_t q = r + (m - (r % m)) + 1; /* [PAL] qNew = 2^nBits + (m - 2^nBits mod m) + 1 */
     while (!is_prime64(q)) q += m;
     return q;
 }

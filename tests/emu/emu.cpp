@@ -1,0 +1,259 @@
+// emu.cpp — CPU replay harness for the device code.  TEST INFRASTRUCTURE ONLY (tests/ is the only user).
+//
+// Compiles fhe-fed_b200/csrc/ckks_core.cuh with g++ (HD functions become plain inline functions) and
+// replays each kernel of kernels.cu phase by phase: every phase runs for all thread ids before the
+// next one starts, which is exactly what __syncthreads() guarantees on the GPU.  It lets the CPU-only
+// test suite check index math, lazy-reduction bounds and wire-format code bit for bit against the
+// oracle.  It is NOT a fallback: nothing in the product links or loads it.
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../fhe-fed_b200/csrc/ckks_core.cuh"
+#include "../../fhe-fed_b200/csrc/numtheory.h"
+#include "../../fhe-fed_b200/csrc/tables.h"
+#include "../../fhe-fed_b200/csrc/wire.h"
+
+using namespace shelfi;
+
+struct Emu {
+    RingConst rc;
+    EncodeConst ec;
+    Crt2Const crt;
+    uint64_t cdf[32];
+    std::vector<tw_t> tw[kMaxLimbs], itw[kMaxLimbs];
+    std::vector<cplx> fft_inv, fft_fwd;
+    std::string err;
+};
+
+#define FOR_THREADS(n) for (int tid = 0; tid < (n); tid++)
+
+template <class Load, class Store>
+static void replay_forward(u64 *sm, const LimbConst &lc, Load ld, Store st) {
+    FOR_THREADS(kNttThreads) fwd_phase_a(tid, sm, lc, ld);
+    FOR_THREADS(kNttThreads) fwd_phase_mid<7>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) fwd_phase_mid<4>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) fwd_phase_mid<1>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) fwd_phase_e(tid, sm, lc, st);
+}
+template <class Load, class Store>
+static void replay_inverse(u64 *sm, const LimbConst &lc, Load ld, Store st) {
+    FOR_THREADS(kNttThreads) inv_phase_e(tid, sm, lc, ld);
+    FOR_THREADS(kNttThreads) inv_phase_mid<1>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) inv_phase_mid<4>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) inv_phase_mid<7>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) inv_phase_last(tid, sm, lc, st);
+}
+
+extern "C" {
+
+Emu *emu_create(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint32_t slots, uint32_t batch, double sigma) {
+    Emu *e = new Emu();
+    std::memset(&e->rc, 0, sizeof e->rc);
+    e->rc.n = kN; e->rc.logn = kLogN; e->rc.limbs = limbs; e->rc.slots = slots;
+    for (uint32_t l = 0; l < limbs; l++) {
+        e->err = make_limb_const(q[l], psi[l], &e->rc.limb[l], &e->tw[l], &e->itw[l]);
+        if (!e->err.empty()) return e;
+        e->rc.limb[l].tw = e->tw[l].data();
+        e->rc.limb[l].itw = e->itw[l].data();
+    }
+    make_fft_tables(2 * kN, slots, &e->fft_inv, &e->fft_fwd);
+    std::memset(&e->ec, 0, sizeof e->ec);
+    e->ec.slots = slots; e->ec.gap = (kN / 2) / slots; e->ec.batch = batch;
+    while ((1u << e->ec.log_slots) < slots) e->ec.log_slots++;
+    e->ec.pow_p = (double)q[limbs - 1];
+    e->ec.inv_size = 1.0 / (double)slots;
+    e->ec.tw_inv = e->fft_inv.data();
+    e->ec.tw_fwd = e->fft_fwd.data();
+    e->crt = make_crt2(q[0], limbs >= 2 ? q[1] : 0);
+    build_gauss_cdf(sigma, e->cdf);
+    return e;
+}
+void emu_destroy(Emu *e) { delete e; }
+const char *emu_error(const Emu *e) { return e->err.c_str(); }
+uint32_t emu_fwd_mask(const Emu *e, uint32_t l) { return e->rc.limb[l].fwd_mask; }
+uint32_t emu_rmode(const Emu *e, uint32_t l) { return e->rc.limb[l].rmode; }
+
+// ntt_forward_kernel / ntt_inverse_kernel, one row
+void emu_ntt_forward(const Emu *e, uint32_t limb, uint64_t *row) {
+    std::vector<u64> sm(kN);
+    const LimbConst lc = e->rc.limb[limb];
+    replay_forward(sm.data(), lc, LoadGlobal{row}, StoreFullReducePair{row, &lc});
+}
+void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
+    std::vector<u64> sm(kN);
+    const LimbConst lc = e->rc.limb[limb];
+    replay_inverse(sm.data(), lc, LoadPairGlobal{row}, StoreGlobal{row});
+}
+
+// encode_kernel<SAMPLE>: one ciphertext
+static void replay_encode(const Emu *e, const double *x, uint64_t n_valid, std::vector<cplx> &z) {
+    z.assign(e->ec.slots, cplx{0, 0});
+    FOR_THREADS(kFftThreads) encode_load(tid, kFftThreads, z.data(), e->ec, x, n_valid);
+    for (u32 len = e->ec.slots; len >= 2; len >>= 1)
+        FOR_THREADS(kFftThreads) fft_inv_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_inv);
+    FOR_THREADS(kFftThreads) encode_finalize(tid, kFftThreads, z.data(), e->ec);
+}
+void emu_encode(const Emu *e, const double *x, uint64_t n_valid, int64_t *m) {
+    std::vector<cplx> z;
+    replay_encode(e, x, n_valid, z);
+    FOR_THREADS(kFftThreads)
+        for (u32 j = tid; j < (u32)kN; j += kFftThreads) m[j] = encode_coeff(z.data(), e->ec, j);
+}
+void emu_encode_sample(const Emu *e, const double *x, uint64_t n_valid, uint64_t seed, uint64_t ct_index, int64_t *m_e0,
+                       uint16_t *ve) {
+    std::vector<cplx> z;
+    replay_encode(e, x, n_valid, z);
+    SamplerConst sc;
+    std::memset(&sc, 0, sizeof sc);
+    sc.seed = seed;
+    FOR_THREADS(kFftThreads)
+        encode_sample_emit(tid, kFftThreads, z.data(), e->ec, sc, e->cdf, ct_index, (i64 *)m_e0, ve);
+}
+
+// encrypt_kernel: one ciphertext, all limbs; pk_b / pk_a: [L][N] {value, shoup}; out: [2][L][N]
+void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const uint64_t *pk_b, const uint64_t *pk_a,
+                 uint64_t *out) {
+    const u32 L = e->rc.limbs;
+    std::vector<u64> sm(kN);
+    for (u32 l = 0; l < L; l++) {
+        const LimbConst lc = e->rc.limb[l];
+        std::vector<tw_t> b(kN), a(kN);
+        for (int j = 0; j < kN; j++) {
+            b[j] = tw_t{pk_b[(size_t)l * kN + j], nt::shoup(pk_b[(size_t)l * kN + j], lc.q)};
+            a[j] = tw_t{pk_a[(size_t)l * kN + j], nt::shoup(pk_a[(size_t)l * kN + j], lc.q)};
+        }
+        u64 *c0 = out + (size_t)(0 * L + l) * kN, *c1 = out + (size_t)(1 * L + l) * kN;
+        replay_forward(sm.data(), lc, LoadTernary{ve, lc.q}, StorePkProducts{b.data(), a.data(), c0, c1, lc.q});
+        replay_forward(sm.data(), lc, LoadSigned{(const i64 *)m_e0, &lc}, StoreAddParked{c0, &lc});
+        replay_forward(sm.data(), lc, LoadGaussHi{ve, lc.q}, StoreAddParked{c1, &lc});
+    }
+}
+
+// decrypt_intt_kernel + decode_kernel: one ciphertext; sk: [L][N]; out: slots doubles (first `length` written)
+void emu_decrypt(const Emu *e, const uint64_t *ct, const uint64_t *sk, double pre, double pow_p, double *out,
+                 uint64_t length, int64_t *tap_hi, uint64_t *tap_lo) {
+    const u32 L = e->rc.limbs;
+    std::vector<u64> sm(kN), coeff((size_t)L * kN);
+    for (u32 l = 0; l < L; l++) {
+        const LimbConst lc = e->rc.limb[l];
+        std::vector<tw_t> s(kN);
+        for (int j = 0; j < kN; j++) s[j] = tw_t{sk[(size_t)l * kN + j], nt::shoup(sk[(size_t)l * kN + j], lc.q)};
+        replay_inverse(sm.data(), lc,
+                       LoadDecryptPair{ct + (size_t)(0 * L + l) * kN, ct + (size_t)(1 * L + l) * kN, s.data(), lc.q},
+                       StoreGlobal{coeff.data() + (size_t)l * kN});
+    }
+    DecodeConst dc;
+    dc.crt = e->crt; dc.pre = pre; dc.pow_p = pow_p;
+    std::vector<cplx> z(e->ec.slots);
+    FOR_THREADS(kFftThreads)
+        decode_load(tid, kFftThreads, z.data(), e->ec, dc, L, coeff.data(), (i64 *)tap_hi, (u64 *)tap_lo);
+    for (u32 len = 2; len <= e->ec.slots; len <<= 1)
+        FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_fwd);
+    FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length);
+}
+
+// weighted_sum_kernel arithmetic on one limb row: out[j] = sum_k c[k] * in[k][j] mod q
+void emu_weighted_sum(const Emu *e, uint32_t limb, const uint64_t *const *in, const uint64_t *c, uint32_t k,
+                      uint64_t *out, uint32_t count) {
+    const LimbConst lc = e->rc.limb[limb];
+    for (u32 j = 0; j < count; j++) {
+        acc128 a{0, 0};
+        for (u32 i = 0; i < k; i++) mac128(a, in[i][j], c[i]);
+        out[j] = reduce128(a, lc);
+    }
+}
+
+// pack_kernel / unpack_kernel over a whole blob image
+static BlobRuns runs_of(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs) {
+    BlobRuns br;
+    std::memset(&br, 0, sizeof br);
+    br.runs = runs; br.stride = stride;
+    for (u32 r = 0; r < runs; r++) { br.off0[r] = run0[r]; br.off1[r] = run1[r]; }
+    return br;
+}
+void emu_unpack(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint64_t n_ct,
+                const uint64_t *image, uint64_t *dense) {
+    BlobRuns br = runs_of(run0, run1, stride, runs);
+    for (u64 run = 0; run < n_ct * runs; run++) {
+        u64 a0 = run_offset(br, run / runs, (u32)(run % runs));
+        for (u32 i = 0; i < (u32)kN; i++) dense[run * kN + i] = load_unaligned(image, a0 + 8ull * i);
+    }
+}
+void emu_pack(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint64_t n_ct,
+              const uint64_t *dense, uint64_t *image) {
+    BlobRuns br = runs_of(run0, run1, stride, runs);
+    for (u64 run = 0; run < n_ct * runs; run++) {
+        u64 a0 = run_offset(br, run / runs, (u32)(run % runs));
+        for (u64 w = a0 >> 3; w <= (a0 + 8ull * kN - 1) >> 3; w++) pack_word(image, a0, w, dense + run * kN);
+    }
+}
+
+// ---- wire format (wire.cpp is plain host code; exercised here without the CUDA library) ----
+// kind 0 context, 1 public key, 2 private key: parse then emit; returns malloc'd bytes or NULL (+ error text)
+uint8_t *emu_wire_reemit(int kind, const uint8_t *in, uint64_t len, uint64_t *out_len, char *err, size_t err_cap) {
+    std::string e;
+    std::vector<uint8_t> out;
+    if (kind == 0) {
+        wire::ContextParams p;
+        e = wire::parse_context(in, len, &p);
+        if (e.empty()) out = wire::emit_context(p);
+    } else {
+        wire::KeyFile k;
+        e = kind == 1 ? wire::parse_public_key(in, len, &k) : wire::parse_private_key(in, len, &k);
+        if (e.empty()) out = kind == 1 ? wire::emit_public_key(k) : wire::emit_private_key(k);
+    }
+    if (!e.empty()) { std::snprintf(err, err_cap, "%s", e.c_str()); return nullptr; }
+    uint8_t *p = (uint8_t *)std::malloc(out.size() ? out.size() : 1);
+    std::memcpy(p, out.data(), out.size());
+    *out_len = out.size();
+    return p;
+}
+// map a blob; fills runs (2L each), stride, n_ct, first ciphertext's metadata
+int emu_wire_map(const uint8_t *in, uint64_t len, int single, uint64_t *n_ct, uint32_t *limbs, uint64_t *run0,
+                 uint64_t *run1, uint64_t *stride, uint64_t *depth, uint64_t *level, double *sf, char *tag, char *err,
+                 size_t err_cap) {
+    wire::BlobMap m;
+    std::string e = wire::map_ciphertext_blob(in, len, single != 0, &m);
+    if (!e.empty()) { std::snprintf(err, err_cap, "%s", e.c_str()); return -1; }
+    *n_ct = m.n_ct; *limbs = m.ctx.limbs; *stride = m.stride;
+    std::memcpy(run0, m.run0, sizeof m.run0);
+    std::memcpy(run1, m.run1, sizeof m.run1);
+    *depth = m.meta[0].depth; *level = m.meta[0].level; *sf = m.meta[0].scaling_factor;
+    std::memcpy(tag, m.meta[0].tag, 33);
+    return 0;
+}
+// re-create a blob from its own map: plan headers, pack payload with the replayed pack kernel
+uint8_t *emu_wire_rebuild(const uint8_t *in, uint64_t len, uint64_t *out_len, char *err, size_t err_cap) {
+    wire::BlobMap m;
+    std::string e = wire::map_ciphertext_blob(in, len, false, &m);
+    if (!e.empty()) { std::snprintf(err, err_cap, "%s", e.c_str()); return nullptr; }
+    const uint32_t runs = 2 * m.ctx.limbs;
+    std::vector<uint64_t> image((len + 7) / 8 + 1, 0), dense(m.n_ct * runs * (size_t)kN);
+    std::memcpy(image.data(), in, len);
+    emu_unpack(m.run0, m.run1, m.stride, runs, m.n_ct, image.data(), dense.data());
+    wire::BlobPlan plan = wire::plan_ciphertext_blob(m.ctx, m.n_ct, m.meta);
+    std::vector<uint64_t> out_image((plan.size + 7) / 8 + 1, 0xA5A5A5A5A5A5A5A5ull);
+    emu_pack(plan.run0, plan.run1, plan.stride, runs, m.n_ct, dense.data(), out_image.data());
+    uint8_t *out = (uint8_t *)std::malloc(plan.size);
+    std::memcpy(out, out_image.data(), plan.size);
+    for (const auto &seg : plan.segments) std::memcpy(out + seg.offset, seg.bytes.data(), seg.bytes.size());
+    *out_len = plan.size;
+    return out;
+}
+uint64_t emu_wire_blob_size(const uint8_t *ctx_file, uint64_t len, uint64_t n_ct) {
+    wire::ContextParams p;
+    if (!wire::parse_context(ctx_file, len, &p).empty()) return 0;
+    return wire::ciphertext_blob_size(p, n_ct);
+}
+void emu_free(void *p) { std::free(p); }
+
+// parameter generation rules
+uint64_t emu_first_prime(uint32_t bits, uint32_t m) { return nt::first_prime(bits, m); }
+uint64_t emu_previous_prime(uint64_t q, uint32_t m) { return nt::previous_prime(q, m); }
+uint64_t emu_min_primitive_root(uint32_t m, uint64_t q) { return nt::min_primitive_root(m, q); }
+uint32_t emu_select_ring_dim(uint32_t bits) { return nt::select_ring_dim(bits); }
+
+}  // extern "C"
