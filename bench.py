@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""bench.py — encrypted FedAvg throughput (enc + wavg + dec) of the B200 CKKS engine.
+
+Contract (one JSON line on stdout from rank 0):
+  value   params/s with inputs resident in HBM: K learner encryptions + weighted average + decrypt of one
+          P-parameter model per GPU, timed with CUDA events over `steps` passes, max over ranks;
+          whole-job aggregate = n_gpus * P * steps / time ("weak": every GPU aggregates its own P-slice).
+  e2e     the same pass through the reference-facing C-ABI calls with HOST buffers (pinned): K x
+          shelfi_encrypt_into, shelfi_compute_weighted_average_into, shelfi_decrypt; H2D/D2H inside the timer.
+  roofline  dominant kernel (encrypt_kernel), live CUDA-event time from the library's per-kernel timers.
+  cpu_baseline  the CPU oracle (a port of the reference path; PALISADE itself cannot be built offline) on a
+          bounded sample of the same workload, all host threads.
+`--impl reference` times only that CPU arm on the same config.
+
+Workload = BASELINE.json configs[1]: CKKS N=8192, 2 limbs, 10 learners x 1,663,370-parameter CNN
+(code/benchmark.py:152-219), weights 1/K, synthetic normal(0, 0.05) float32 parameters.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+for p in (ROOT, ROOT / "fhe-fed_b200"):
+    if str(p) not in sys.path:
+        sys.path.insert(0, str(p))
+
+CRYPTODIR = str(ROOT / "tests" / "golden" / "pybind_cryptoparams") + "/"
+P_MODEL = 1_663_370          # CNN_OriginalFedAvg (code/benchmark.py:152-219); BASELINE's "~1.2M" is nominal
+K_LEARNERS = 10
+BATCH, N_RING, LIMBS = 4096, 8192, 2
+METRIC = "encrypted FedAvg params/sec (enc+wavg+dec), N=2^13"
+UNIT = "params/s"
+
+
+def make_inputs(rank: int):
+    rng = np.random.default_rng(2 + 1000 * rank)
+    return [rng.normal(0, 0.05, P_MODEL).astype(np.float32).astype(np.float64) for _ in range(K_LEARNERS)]
+
+
+def bytes_per_param(k: int, limbs: int) -> int:
+    # K*(8 + 32L) encrypt + (K+1)*32L weighted average + (32L + 8) decrypt
+    return k * (8 + 32 * limbs) + (k + 1) * 32 * limbs + (32 * limbs + 8)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled during the timed region
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.stop = index, [], threading.Event()
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [s.strip() for s in out.strip().split(",")]
+                if len(f) >= 7:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[3 + i] == "Active" for s in self.samples)]
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle on a bounded sample of the same workload
+# ------------------------------------------------------------------------------------------------
+def cpu_arm(sample_cts: int, repeats: int = 1):
+    """K learners x sample_cts ciphertexts through oracle encrypt / weighted average / decrypt."""
+    import oracle
+    o = oracle.Oracle("ckks", BATCH, 52, CRYPTODIR)
+    assert o.loadCryptoParams() == 0
+    n = sample_cts * BATCH
+    rng = np.random.default_rng(2)
+    xs = [rng.normal(0, 0.05, n).astype(np.float32).astype(np.float64) for _ in range(K_LEARNERS)]
+    w = [1.0 / K_LEARNERS] * K_LEARNERS
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        blobs = [o.encrypt(x, seed=i) for i, x in enumerate(xs)]
+        t1 = time.perf_counter()
+        avg = o.computeWeightedAverage(blobs, w)
+        t2 = time.perf_counter()
+        out = o.decrypt(avg, n)
+        t3 = time.perf_counter()
+        assert out.shape == (n,)
+        if best is None or t3 - t0 < best[0]:
+            best = (t3 - t0, t1 - t0, t2 - t1, t3 - t2)
+    total, te, ta, td = best
+    return {"value": n / total, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+            "sample": f"{K_LEARNERS} learners x {sample_cts} ciphertexts ({n} params) of the config-2 workload; "
+                      f"enc {te:.2f}s agg {ta:.2f}s dec {td:.2f}s",
+            "seconds": total}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_cts = 48
+    cpu_arm(4)  # warm caches / OpenMP pool
+    times = []
+    for _ in range(max(1, args.steps)):
+        r = cpu_arm(sample_cts)
+        times.append(r)
+    best = max(times, key=lambda r: r["value"])
+    value = float(np.mean([r["value"] for r in times]))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean([r["seconds"] for r in times])),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": workload_config(),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                             "sample": best["sample"]},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "PALISADE is not vendored in the reference and cannot be built offline; this arm is the C oracle "
+                    "(oracle/shelfi_oracle.c), a port of ckks.cpp:61-104,170-213,264-320 with OpenMP over ciphertexts"}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config():
+    return {"workload": "configs[1]: CKKS N=8192, L=2 (60+52 bit), batch 4096, 10 learners x 1,663,370-param CNN, "
+                        "weights 1/K, shipped fixture keys", "learners": K_LEARNERS, "params": P_MODEL,
+            "ciphertexts_per_learner": -(-P_MODEL // BATCH), "ring_dim": N_RING, "limbs": LIMBS,
+            "l2": "inputs larger than L2: 1.07 GB of ciphertext per step per GPU vs 126 MB L2",
+            "sharding": "weak: one P-parameter slice per GPU, no data-path collective"}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import SHELFI_FHE
+    L = SHELFI_FHE.lib()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    h = SHELFI_FHE.CKKS("ckks", BATCH, 52, CRYPTODIR, device=local)
+    h.loadCryptoParams()
+    assert h.load_status == 0
+    n_ct = h.num_ciphertexts(P_MODEL)
+    ct_words = h.ciphertext_words
+    K = K_LEARNERS
+    xs_host = make_inputs(rank)
+    w = (C.c_float * K)(*[1.0 / K] * K)
+    stream = torch.cuda.current_stream()
+    sp = C.c_void_p(stream.cuda_stream)
+
+    def ck(rc):
+        if rc:
+            raise RuntimeError(h._err())
+
+    # ---------------- device-resident pass ----------------
+    d_x = [torch.from_numpy(x).cuda() for x in xs_host]
+    d_ct = [torch.empty(n_ct * ct_words, dtype=torch.int64, device="cuda") for _ in range(K)]
+    d_avg = torch.empty(n_ct * ct_words, dtype=torch.int64, device="cuda")
+    d_out = torch.empty(P_MODEL, dtype=torch.float64, device="cuda")
+    ct_ptrs = (C.c_void_p * K)(*[t.data_ptr() for t in d_ct])
+    sf2 = h.scaling_factor * h.scaling_factor
+    ct0 = rank * n_ct
+
+    def device_step():
+        for k in range(K):
+            ck(L.shelfi_encrypt_device(h.handle, C.c_void_p(d_x[k].data_ptr()), P_MODEL, ct0, C.c_void_p(d_ct[k].data_ptr()), sp))
+        ck(L.shelfi_weighted_sum_device(h.handle, ct_ptrs, w, K, n_ct, C.c_void_p(d_avg.data_ptr()), sp))
+        ck(L.shelfi_decrypt_device(h.handle, C.c_void_p(d_avg.data_ptr()), n_ct, sf2, C.c_void_p(d_out.data_ptr()), P_MODEL, sp))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        device_step()
+    barrier()
+    # correctness gate inside the harness: decoded average vs plaintext, 1e-6 relative
+    expect = sum(np.float64(np.float32(1.0 / K)) * x for x in xs_host)
+    got = d_out.cpu().numpy()
+    rel = float(np.abs(got - expect).max() / np.abs(expect).max())
+    assert rel < 1e-6, f"decoded average off by {rel}"
+
+    L.shelfi_profile_reset(h.handle)
+    L.shelfi_profile_enable(h.handle, 1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            device_step()
+        e1.record(stream)
+        barrier()
+    L.shelfi_profile_enable(h.handle, 0)
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * P_MODEL * args.steps / (ms_max / 1e3)
+
+    # per-kernel times from the library's CUDA-event timers (same stream, same timed region)
+    names = ["encode_sample", "encrypt", "weighted_sum", "decrypt_intt", "decode"]
+    prof = {}
+    for i, name in enumerate(names):
+        tot, cnt = C.c_double(), C.c_uint64()
+        L.shelfi_profile_get(h.handle, i, C.byref(tot), C.byref(cnt))
+        prof[name] = {"ms_total": tot.value, "launches": cnt.value}
+    launches = sum(p["launches"] for p in prof.values())
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    enc = prof["encrypt"]
+    params_per_launch = n_ct * BATCH
+    algo_bytes = (8 + 32 * LIMBS) * params_per_launch          # encrypt stage, per parameter
+    enc_ms = enc["ms_total"] / max(1, enc["launches"])
+    achieved = algo_bytes / (enc_ms / 1e3) / 1e9 if enc_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "encrypt_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                "ms_per_launch": enc_ms, "share_of_step": enc["ms_total"] / ms if ms > 0 else None,
+                "note": "integer-pipe bound: 3 NTTs per limb in shared memory per 72 algorithmic bytes/param (DESIGN.md §4)"}
+    path_gbs = bytes_per_param(K, LIMBS) * P_MODEL * args.steps / (ms / 1e3) / 1e9
+
+    # ---------------- standalone NTT bandwidth (second half of BASELINE's metric) ----------------
+    rows = K * n_ct * LIMBS
+    d_rows = torch.randint(0, 2**50, (rows * N_RING,), dtype=torch.int64, device="cuda")
+    for _ in range(3):
+        ck(L.shelfi_ntt_forward_device(h.handle, C.c_void_p(d_rows.data_ptr()), rows, sp))
+    n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    n0.record(stream)
+    reps = 5
+    for _ in range(reps):
+        ck(L.shelfi_ntt_forward_device(h.handle, C.c_void_p(d_rows.data_ptr()), rows, sp))
+    n1.record(stream)
+    torch.cuda.synchronize()
+    ntt_ms = n0.elapsed_time(n1) / reps
+    ntt_gbs = 16 * N_RING * rows / (ntt_ms / 1e3) / 1e9
+    del d_rows
+
+    # ---------------- end to end through the host-buffer C ABI ----------------
+    blob_cap = h.blob_size(n_ct)
+    pin_x = [torch.from_numpy(x).pin_memory() for x in xs_host]
+    pin_blob = [torch.empty(blob_cap, dtype=torch.uint8).pin_memory() for _ in range(K)]
+    pin_avg = torch.empty(blob_cap, dtype=torch.uint8).pin_memory()
+    pin_out = torch.empty(P_MODEL, dtype=torch.float64).pin_memory()
+    blob_ptrs = (C.c_void_p * K)(*[t.data_ptr() for t in pin_blob])
+    blob_lens = (C.c_uint64 * K)(*[blob_cap] * K)
+    olen = C.c_uint64()
+
+    def host_step():
+        for k in range(K):
+            ck(L.shelfi_encrypt_into(h.handle, C.c_void_p(pin_x[k].data_ptr()), P_MODEL, C.c_void_p(pin_blob[k].data_ptr()),
+                                     blob_cap, C.byref(olen)))
+        ck(L.shelfi_compute_weighted_average_into(h.handle, blob_ptrs, blob_lens, w, K, C.c_void_p(pin_avg.data_ptr()),
+                                                  blob_cap, C.byref(olen)))
+        ck(L.shelfi_decrypt(h.handle, C.c_void_p(pin_avg.data_ptr()), olen.value, P_MODEL, C.c_void_p(pin_out.data_ptr())))
+
+    host_step()
+    rel_h = float(np.abs(pin_out.numpy() - expect).max() / np.abs(expect).max())
+    assert rel_h < 1e-6, f"host path decoded average off by {rel_h}"
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        host_step()
+    torch.cuda.synchronize()
+    t_e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_value = world * P_MODEL * e2e_steps / float(t_e2e.item())
+    h2d = K * 8 * P_MODEL + K * blob_cap + blob_cap
+    d2h = K * blob_cap + blob_cap + 8 * P_MODEL
+
+    # optional reassembly of the decoded model: ONE all-gather over NVLink, outside the timed step
+    gather_ms = None
+    if world > 1:
+        full = torch.empty(world * P_MODEL, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(full, d_out)
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        g0.record(stream)
+        dist.all_gather_into_tensor(full, d_out)
+        g1.record(stream)
+        barrier()
+        gather_ms = g0.elapsed_time(g1)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu_arm(4)
+        cpu = cpu_arm(48)
+        cpu.pop("seconds", None)
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(3, args.warmup), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": workload_config(),
+                "clocks": clocks.summary(),
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "steps": e2e_steps, "api": "shelfi_encrypt_into x K, shelfi_compute_weighted_average_into, "
+                                                   "shelfi_decrypt on pinned host buffers"},
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                "path_hbm": {"algorithmic_GBps": path_gbs, "bytes_per_param": bytes_per_param(K, LIMBS),
+                             "frac_of_peak": path_gbs / peak},
+                "ntt": {"GBps": ntt_gbs, "frac_of_peak": ntt_gbs / peak, "rows": rows, "ms": ntt_ms,
+                        "bytes_per_row": 16 * N_RING},
+                "kernels": prof, "gather_ms": gather_ms,
+                "parity": {"max_rel_err_vs_plaintext": rel, "host_path": rel_h}}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

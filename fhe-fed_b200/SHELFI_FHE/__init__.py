@@ -88,6 +88,9 @@ def lib() -> C.CDLL:
         "shelfi_ntt_inverse_device": (C.c_int, [vp, vp, u32, vp]),
         "shelfi_encode_device": (C.c_int, [vp, vp, u64, vp, vp]),
         "shelfi_decrypt_integer_device": (C.c_int, [vp, vp, u64, vp, vp, vp]),
+        "shelfi_profile_enable": (C.c_int, [vp, C.c_int]),
+        "shelfi_profile_reset": (C.c_int, [vp]),
+        "shelfi_profile_get": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), u64p]),
         "shelfi_version": (C.c_char_p, []),
     }
     for name, (res, args) in sig.items():

@@ -38,6 +38,40 @@ struct DeviceBuffer {  // grow-only device scratch
     template <class T> T *as() const { return static_cast<T *>(p); }
 };
 
+// Optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
+enum KernelId { kKEncodeSample, kKEncrypt, kKWeightedSum, kKDecryptIntt, kKDecode, kKPack, kKUnpack,
+                kKUnpackScaleAcc, kKNttForward, kKNttInverse, kKernelCount };
+struct Profiler {
+    bool on = false;
+    struct Rec { int id; cudaEvent_t a, b; };
+    std::vector<Rec> pending;
+    std::vector<cudaEvent_t> spare;
+    double total_ms[kKernelCount] = {0};
+    uint64_t launches[kKernelCount] = {0};
+    cudaEvent_t take() {
+        if (!spare.empty()) { cudaEvent_t e = spare.back(); spare.pop_back(); return e; }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void drain() {
+        for (auto &r : pending) {
+            float ms = 0;
+            if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+                total_ms[r.id] += ms;
+                launches[r.id]++;
+            }
+            spare.push_back(r.a); spare.push_back(r.b);
+        }
+        pending.clear();
+    }
+    void release() {
+        drain();
+        for (cudaEvent_t e : spare) cudaEventDestroy(e);
+        spare.clear();
+    }
+};
+
 }  // namespace
 
 struct shelfi_ckks {
@@ -61,6 +95,7 @@ struct shelfi_ckks {
     cudaStream_t copy_stream = nullptr;
     bool seeded = false;
     uint64_t seed = 0;
+    Profiler prof;
     std::mutex mu;
 };
 
@@ -78,6 +113,16 @@ int cuda_fail(shelfi_ckks *h, cudaError_t e, const char *where) {
         cudaError_t e__ = (call);                                  \
         if (e__ != cudaSuccess) return cuda_fail(h, e__, #call);   \
     } while (0)
+
+template <class F>
+void timed(shelfi_ckks *h, int id, cudaStream_t s, F &&launch) {
+    if (!h->prof.on || h->prof.pending.size() >= 65536) { launch(); return; }
+    Profiler::Rec r{id, h->prof.take(), h->prof.take()};
+    cudaEventRecord(r.a, s);
+    launch();
+    cudaEventRecord(r.b, s);
+    h->prof.pending.push_back(r);
+}
 
 int ensure_cuda(shelfi_ckks *h) {
     if (h->cuda_ready) {
@@ -226,9 +271,13 @@ int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_ind
     sc.seed = h->seeded ? h->seed : fresh_seed();
     sc.ct_index0 = ct_index0;
     std::memcpy(sc.gauss_cdf, h->gauss_cdf, sizeof sc.gauss_cdf);
-    launch_encode_sample(h->rc, h->ec, sc, d_x, n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s);
-    launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), d_ct,
-                   (u32)n_ct, s);
+    timed(h, kKEncodeSample, s, [&] {
+        launch_encode_sample(h->rc, h->ec, sc, d_x, n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s);
+    });
+    timed(h, kKEncrypt, s, [&] {
+        launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), d_ct,
+                       (u32)n_ct, s);
+    });
     CU(cudaGetLastError());
     return 0;
 }
@@ -237,13 +286,13 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
                   cudaStream_t s) {
     if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "decode implements the 1- and 2-limb CRT only");
     CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * kN * sizeof(uint64_t)));
-    launch_decrypt_intt(h->rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
+    timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(h->rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
     DecodeConst dc{};
     dc.crt = h->crt;
     double p = (double)h->ctx.plaintext_modulus;
     dc.pre = std::pow(sf, -1) * std::pow(2, p);   // [PAL] Decode: scale to 2^p before the FFT, back after it
     dc.pow_p = std::pow(2, -p);
-    launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s);
+    timed(h, kKDecode, s, [&] { launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s); });
     CU(cudaGetLastError());
     return 0;
 }
@@ -296,8 +345,10 @@ int encrypt_host(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint
     CUB(h->s_image.reserve(image_bytes(plan.size)));
     CUB(cudaMemcpyAsync(h->s_x.p, x, n * sizeof(double), cudaMemcpyHostToDevice, s));
     if ((rcode = encrypt_dense(h, h->s_x.as<double>(), n, 0, h->s_dense.as<u64>(), s))) return bail(rcode);
-    launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), h->s_dense.as<u64>(),
-                h->s_image.as<u64>(), n_ct, s);
+    timed(h, kKPack, s, [&] {
+        launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), h->s_dense.as<u64>(),
+                    h->s_image.as<u64>(), n_ct, s);
+    });
     CUB(cudaGetLastError());
     CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
     CUB(cudaStreamSynchronize(s));
@@ -357,12 +408,16 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *lens,
         int64_t sc = weight_constant(h, w[i]);
         LimbScalars cs_l{};
         for (uint32_t l = 0; l < L; l++) cs_l.c[l] = nt::signed_mod(sc, h->ctx.modulus[l]);
-        launch_unpack_scale_accumulate(h->rc, to_runs(maps[i].run0, maps[i].run1, maps[i].stride, L), img[b]->as<u64>(),
-                                       cs_l, i == 0 ? 1u : 0u, h->s_dense.as<u64>(), n_ct, s);
+        timed(h, kKUnpackScaleAcc, s, [&] {
+            launch_unpack_scale_accumulate(h->rc, to_runs(maps[i].run0, maps[i].run1, maps[i].stride, L),
+                                           img[b]->as<u64>(), cs_l, i == 0 ? 1u : 0u, h->s_dense.as<u64>(), n_ct, s);
+        });
         CUB(cudaGetLastError());
         CUB(cudaEventRecord(h->ev_done[b], s));
     }
-    launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, L), h->s_dense.as<u64>(), h->s_image.as<u64>(), n_ct, s);
+    timed(h, kKPack, s, [&] {
+        launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, L), h->s_dense.as<u64>(), h->s_image.as<u64>(), n_ct, s);
+    });
     CUB(cudaGetLastError());
     CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
     CUB(cudaStreamSynchronize(s));
@@ -390,7 +445,9 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *blob, uint64_t len, uint64_t n, 
     CU(h->s_dense.reserve(n_ct * ct_words * 8));
     CU(h->s_out.reserve(n * sizeof(double)));
     CU(cudaMemcpyAsync(h->s_image.p, blob, len, cudaMemcpyHostToDevice, s));
-    launch_unpack(h->rc, to_runs(map.run0, map.run1, map.stride, L), h->s_image.as<u64>(), h->s_dense.as<u64>(), n_ct, s);
+    timed(h, kKUnpack, s, [&] {
+        launch_unpack(h->rc, to_runs(map.run0, map.run1, map.stride, L), h->s_image.as<u64>(), h->s_dense.as<u64>(), n_ct, s);
+    });
     CU(cudaGetLastError());
     // ciphertexts usually share one scaling factor; split the launch where they do not
     uint64_t j0 = 0;
@@ -436,6 +493,7 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
     if (h->cuda_ready) {
         cudaSetDevice(h->device);
         cudaDeviceSynchronize();
+        h->prof.release();
         free_params(h);
         for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_out})
             b->release();
@@ -620,6 +678,28 @@ int shelfi_clear_sampler_seed(shelfi_ckks *h) {
     return 0;
 }
 
+int shelfi_profile_enable(shelfi_ckks *h, int on) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->prof.on = on != 0;
+    return 0;
+}
+int shelfi_profile_reset(shelfi_ckks *h) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->prof.drain();
+    for (int i = 0; i < kKernelCount; i++) { h->prof.total_ms[i] = 0; h->prof.launches[i] = 0; }
+    return 0;
+}
+int shelfi_profile_get(shelfi_ckks *h, int kernel, double *ms_total, uint64_t *launches) {
+    if (!h || kernel < 0 || kernel >= kKernelCount) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->prof.drain();
+    if (ms_total) *ms_total = h->prof.total_ms[kernel];
+    if (launches) *launches = h->prof.launches[kernel];
+    return 0;
+}
+
 uint32_t shelfi_ring_dim(const shelfi_ckks *h) { return h && h->have_cc ? h->ctx.ring_dim : 0; }
 uint32_t shelfi_num_limbs(const shelfi_ckks *h) { return h && h->have_cc ? h->ctx.limbs : 0; }
 uint32_t shelfi_slots(const shelfi_ckks *h) { return h && h->have_cc ? h->ctx.batch_size : 0; }
@@ -703,7 +783,9 @@ int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, con
             int64_t sc = weight_constant(h, weights[base + i]);
             for (uint32_t l = 0; l < L; l++) wa.c[i][l] = nt::signed_mod(sc, h->ctx.modulus[l]);
         }
-        launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, static_cast<cudaStream_t>(stream));
+        timed(h, kKWeightedSum, static_cast<cudaStream_t>(stream), [&] {
+            launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, static_cast<cudaStream_t>(stream));
+        });
     }
     CU(cudaGetLastError());
     return 0;
@@ -752,7 +834,9 @@ int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, v
     std::lock_guard<std::mutex> lock(h->mu);
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
-    launch_ntt_forward(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
+    timed(h, kKNttForward, static_cast<cudaStream_t>(stream), [&] {
+        launch_ntt_forward(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
+    });
     CU(cudaGetLastError());
     return 0;
 }
@@ -761,7 +845,9 @@ int shelfi_ntt_inverse_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, v
     std::lock_guard<std::mutex> lock(h->mu);
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
-    launch_ntt_inverse(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
+    timed(h, kKNttInverse, static_cast<cudaStream_t>(stream), [&] {
+        launch_ntt_inverse(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
+    });
     CU(cudaGetLastError());
     return 0;
 }

@@ -134,6 +134,13 @@ int shelfi_encode_device(shelfi_ckks *h, const double *d_x, uint64_t n, int64_t 
 int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, int64_t *d_hi, uint64_t *d_lo,
                                   void *stream);
 
+/* ---- per-kernel timing (benchmarks): CUDA events on the launching stream around every launch ----
+ * kernel ids: 0 encode+sample, 1 encrypt, 2 weighted sum, 3 decrypt inverse NTT, 4 decode, 5 pack, 6 unpack,
+ * 7 unpack-scale-accumulate, 8 forward NTT, 9 inverse NTT.  shelfi_profile_get waits for recorded launches. */
+int shelfi_profile_enable(shelfi_ckks *h, int on);
+int shelfi_profile_reset(shelfi_ckks *h);
+int shelfi_profile_get(shelfi_ckks *h, int kernel, double *ms_total, uint64_t *launches);
+
 const char *shelfi_version(void);
 
 #ifdef __cplusplus

@@ -1,0 +1,298 @@
+"""Parity of the CUDA path, called through the C ABI, against the CPU oracle on identical inputs.
+
+Tiers: bit-exact for every integer / byte stage (NTT, encrypt with the shared sampler
+spec, weighted average, wire bytes, the CRT integers of decrypt); decoded doubles are compared both
+exactly against the oracle (same unfused FFT order) and within RTOL = 1e-6 relative against the plaintext
+weighted average — the tolerance BASELINE.json's north_star states for PALISADE's own decrypt.
+"""
+import ctypes as C
+import hashlib
+import math
+
+import numpy as np
+import pytest
+
+from conftest import FIXTURE_DIRS, GOLDEN
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+from gpu_util import check, dev_u64, host_u64, ptr, stream  # noqa: E402
+
+RTOL = 1e-6
+N = 8192
+
+
+def rel_err(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-3)
+
+
+def test_context_loaded(gpu_ckks, oracles, fixture_name):
+    h, o = gpu_ckks[fixture_name], oracles[fixture_name]
+    assert (h.ring_dim, h.num_limbs, h.slots) == (o.ring_dim, o.num_limbs, o.slots)
+    assert [h.modulus(l) for l in range(2)] == [o.modulus(l) for l in range(2)]
+    assert [h.root_of_unity(l) for l in range(2)] == [o.psi(l) for l in range(2)]
+    assert h.key_tag() == o.key_tag() and h.scaling_factor == o.scaling_factor
+    for w in (0.5, 0.2, 0.3, 1.0, 0.1, -0.25, 1e-3):
+        assert h.weight_constant(w) == o.weight_constant(w)
+
+
+@pytest.mark.parametrize("rows", [2, 6, 1000])
+def test_ntt_bit_exact(shelfi, gpu_ckks, oracles, rows):
+    h, o = gpu_ckks["pybind"], oracles["pybind"]
+    rng = np.random.default_rng(rows)
+    a = np.empty((rows, N), np.uint64)
+    for r in range(rows):
+        a[r] = rng.integers(0, o.modulus(r % 2), N, dtype=np.uint64)
+    a[0] = o.modulus(0) - 1
+    a[1] = o.modulus(1) - 1
+    d = dev_u64(a)
+    check(h, shelfi.lib().shelfi_ntt_forward_device(h.handle, ptr(d), rows, stream()))
+    f = host_u64(d)
+    for r in list(range(min(rows, 6))) + [rows - 1]:
+        assert np.array_equal(f[r], o.ntt_forward(r % 2, a[r])), r
+    check(h, shelfi.lib().shelfi_ntt_inverse_device(h.handle, ptr(d), rows, stream()))
+    assert np.array_equal(host_u64(d), a)            # round trip on every row
+    d = dev_u64(a)
+    check(h, shelfi.lib().shelfi_ntt_inverse_device(h.handle, ptr(d), rows, stream()))
+    b = host_u64(d)
+    for r in range(min(rows, 4)):
+        assert np.array_equal(b[r], o.ntt_inverse(r % 2, a[r])), r
+
+
+@pytest.mark.parametrize("n,scale", [(4096, 1.0), (10000, 100.0), (1, 1.0), (4097, 0.05)])
+def test_encode_bit_exact(shelfi, gpu_ckks, oracles, n, scale):
+    h, o = gpu_ckks["code"], oracles["code"]
+    x = (np.random.default_rng(n).random(n) - 0.5) * 2 * scale
+    n_ct = -(-n // 4096)
+    dx = torch.from_numpy(x).cuda()
+    dm = torch.empty((n_ct, N), dtype=torch.int64, device="cuda")
+    check(h, shelfi.lib().shelfi_encode_device(h.handle, ptr(dx), n, ptr(dm), stream()))
+    m = dm.cpu().numpy()
+    for i in range(n_ct):
+        assert np.array_equal(m[i], o.encode_coeffs(x[i * 4096:(i + 1) * 4096])), i
+
+
+@pytest.mark.parametrize("n", [1, 4096, 4097, 10000, 100000])
+def test_encrypt_blob_bit_exact(gpu_ckks, oracles, fixture_name, n):
+    """Same sampler spec on both sides => the serialized bytes are identical (ckks.cpp:61-104)."""
+    h, o = gpu_ckks[fixture_name], oracles[fixture_name]
+    x = np.random.default_rng(n).normal(0, 1.0, n)
+    h.set_sampler_seed(4242)
+    blob = h.encrypt(x)
+    h.set_sampler_seed(None)
+    ref = o.encrypt(x, seed=4242)
+    assert len(blob) == len(ref) == h.blob_size(h.num_ciphertexts(n))
+    assert hashlib.sha256(blob).digest() == hashlib.sha256(ref).digest()
+
+
+def test_encrypt_device_sharded_draws_the_same_stream(shelfi, gpu_ckks, oracles):
+    """A shard that starts at ciphertext 3 produces ciphertexts 3.. of the unsharded call."""
+    h, o = gpu_ckks["pybind"], oracles["pybind"]
+    x = np.random.default_rng(0).random(5 * 4096)
+    h.set_sampler_seed(77)
+    dx = torch.from_numpy(x[3 * 4096:]).cuda()
+    dct = torch.empty((2, 2, 2, N), dtype=torch.int64, device="cuda")
+    check(h, shelfi.lib().shelfi_encrypt_device(h.handle, ptr(dx), 2 * 4096, 3, ptr(dct), stream()))
+    h.set_sampler_seed(None)
+    got = host_u64(dct)
+    for j in range(2):
+        assert np.array_equal(got[j], o.encrypt_ct(x[(3 + j) * 4096:(4 + j) * 4096], 77, 3 + j))
+
+
+def test_unseeded_encryptions_differ_but_decrypt_equal(gpu_ckks):
+    h = gpu_ckks["pybind"]
+    x = np.random.default_rng(9).random(5000)
+    b1, b2 = h.encrypt(x), h.encrypt(x)
+    assert b1 != b2
+    assert rel_err(h.decrypt(b1, 5000), x) < RTOL and rel_err(h.decrypt(b2, 5000), x) < RTOL
+
+
+@pytest.mark.parametrize("k,n", [(3, 10000), (1, 4096), (20, 9000)])
+def test_weighted_average_blob_bit_exact(gpu_ckks, oracles, fixture_name, k, n):
+    """Tier 1: identical input blobs -> identical output blob (ckks.cpp:264-320)."""
+    h, o = gpu_ckks[fixture_name], oracles[fixture_name]
+    rng = np.random.default_rng(k * 1000 + n)
+    w = [0.5, 0.2, 0.3] if k == 3 else list(rng.random(k) / k)
+    blobs = [o.encrypt(rng.normal(0, 0.05, n), seed=100 + i) for i in range(k)]
+    ref = o.computeWeightedAverage(blobs, w)
+    got = h.computeWeightedAverage(blobs, w)
+    assert hashlib.sha256(got).digest() == hashlib.sha256(ref).digest()
+
+
+def test_weighted_sum_device_bit_exact(shelfi, gpu_ckks, oracles, oracle_mod):
+    h, o = gpu_ckks["pybind"], oracles["pybind"]
+    rng = np.random.default_rng(21)
+    k, n = 19, 3 * 4096                                  # > 16 learners: two chained launches
+    w = [float(np.float32(v)) for v in rng.random(k)]
+    blobs = [o.encrypt(rng.random(n), seed=i) for i in range(k)]
+    payloads = [oracle_mod.blob_parse(b)[1] for b in blobs]
+    _, ref = oracle_mod.blob_parse(o.computeWeightedAverage(blobs, w))
+    dev = [dev_u64(p) for p in payloads]
+    ptrs = (C.c_void_p * k)(*[t.data_ptr() for t in dev])
+    wa = (C.c_float * k)(*w)
+    out = torch.empty_like(dev[0])
+    check(h, shelfi.lib().shelfi_weighted_sum_device(h.handle, ptrs, wa, k, 3, ptr(out), stream()))
+    assert np.array_equal(host_u64(out), ref)
+
+
+@pytest.mark.parametrize("n", [1, 4096, 10000])
+def test_decrypt_matches_oracle(shelfi, gpu_ckks, oracles, oracle_mod, fixture_name, n):
+    h, o = gpu_ckks[fixture_name], oracles[fixture_name]
+    rng = np.random.default_rng(n + 1)
+    xs = [rng.normal(0, 1.0, n) for _ in range(3)]
+    w = [0.5, 0.2, 0.3]
+    fresh = o.encrypt(xs[0], seed=5)
+    avg = o.computeWeightedAverage([o.encrypt(x, seed=6 + i) for i, x in enumerate(xs)], w)
+    for blob, expect in ((fresh, xs[0]), (avg, sum(float(np.float32(wi)) * x for wi, x in zip(w, xs)))):
+        got, ref = h.decrypt(blob, n), o.decrypt(blob, n)
+        assert rel_err(got, ref) < RTOL                   # the tier north_star states
+        assert np.array_equal(got, ref)                   # and in fact identical: same unfused FFT order
+        assert rel_err(got, expect) < RTOL
+    # integer stage: centred CRT value of every coefficient (bit-exact tier)
+    info, payload = oracle_mod.blob_parse(avg)
+    d = dev_u64(payload)
+    hi = torch.empty((info.n_ct, N), dtype=torch.int64, device="cuda")
+    lo = torch.empty((info.n_ct, N), dtype=torch.int64, device="cuda")
+    check(h, shelfi.lib().shelfi_decrypt_integer_device(h.handle, ptr(d), info.n_ct, ptr(hi), ptr(lo), stream()))
+    for j in range(info.n_ct):
+        _, rhi, rlo = o.decrypt_ct(payload[j], info.scaling_factor, want_coeffs=True)
+        assert np.array_equal(hi[j].cpu().numpy(), rhi) and np.array_equal(host_u64(lo[j]), rlo)
+
+
+def test_pythonapi_example(gpu_ckks):
+    """pythonApi/ckks_example.py:8-10,54-112 as an asserting test: 3 learners x 100,000, weights .5/.2/.3."""
+    h = gpu_ckks["pybind"]
+    rng = np.random.default_rng(1)
+    n = 100000
+    xs = [rng.random(n) for _ in range(3)]
+    w = [0.5, 0.2, 0.3]
+    blobs = [h.encrypt(x) for x in xs]
+    out = h.decrypt(h.computeWeightedAverage(blobs, w), n)
+    assert out.dtype == np.float64 and out.shape == (n,)
+    assert rel_err(out, sum(float(np.float32(wi)) * x for wi, x in zip(w, xs))) < RTOL
+
+
+def test_main_cpp_example(gpu_ckks):
+    """src/main.cpp:8-23,28-78: 100 values in [0,100), three copies, weights .5/.3/.5 (sum 1.3)."""
+    h = gpu_ckks["pybind"]
+    x = np.random.default_rng(2).random(100) * 100
+    blob = h.encrypt_cpp(x)
+    out = h.decrypt_cpp(h.computeWeightedAverage_cpp([blob] * 3, [0.5, 0.3, 0.5]), 100)
+    assert rel_err(out, x * (0.5 + float(np.float32(0.3)) + 0.5)) < RTOL
+
+
+def test_float32_input_and_str_blobs(gpu_ckks):
+    """benchmark.py passes float32 tensors (function_helper.py:7-26); pybind11 2.6.1 also takes str blobs."""
+    h = gpu_ckks["code"]
+    x = np.random.default_rng(3).normal(0, 0.05, (37, 11)).astype(np.float32)
+    blob = h.encrypt(x)
+    out = h.decrypt(blob.decode("latin-1"), x.size)
+    assert rel_err(out, x.ravel().astype(np.float64)) < RTOL
+
+
+def test_pack_unpack_device_roundtrip(shelfi, gpu_ckks, oracles, oracle_mod):
+    h, o = gpu_ckks["code"], oracles["code"]
+    blob = o.encrypt(np.random.default_rng(4).random(3 * 4096), seed=1)
+    _, payload = oracle_mod.blob_parse(blob)
+    size = h.blob_size(3)
+    image = torch.zeros(((size + 7) // 8 + 1,), dtype=torch.int64, device="cuda")
+    d = dev_u64(payload)
+    check(h, shelfi.lib().shelfi_pack_device(h.handle, ptr(d), 3, ptr(image), stream()))
+    back = torch.zeros_like(d)
+    check(h, shelfi.lib().shelfi_unpack_device(h.handle, ptr(image), 3, ptr(back), stream()))
+    assert np.array_equal(host_u64(back), payload)
+    raw = image.cpu().numpy().tobytes()[:size]
+    info, _ = oracle_mod.blob_parse(blob, want_payload=False)
+    off = info.first_data_offset
+    assert raw[off:off + 8 * N] == blob[off:off + 8 * N]
+
+
+def test_error_paths(shelfi, gpu_ckks):
+    h = gpu_ckks["pybind"]
+    with pytest.raises(shelfi.ShelfiError):                    # n == 0 is UB in the reference (ckks.cpp:66,95)
+        h.encrypt(np.zeros(0))
+    with pytest.raises(shelfi.ShelfiError) as e:
+        h.decrypt(b"\x01garbage", 10)
+    assert e.value.code == -3
+    blob = h.encrypt(np.ones(5000))
+    with pytest.raises(shelfi.ShelfiError):
+        h.decrypt(blob, 3 * 4096 + 1)                          # more values than two ciphertexts hold
+    with pytest.raises(shelfi.ShelfiError):
+        h.decrypt(blob[:-7], 5000)
+    assert h.computeWeightedAverage([blob], [0.5, 0.5]) == b""  # ckks.cpp:265-268
+    with pytest.raises(shelfi.ShelfiError) as e:               # a ciphertext of another context (q1 = 2^50 + ...)
+        ct = (GOLDEN / "mkhe" / "CT1.txt").read_bytes()
+        vec = b"\x01" + (1).to_bytes(8, "little") + ct[1:]
+        h.decrypt(vec, 10)
+    assert e.value.code == -4
+    other = shelfi.CKKS("ckks", 4096, 52, "/nonexistent/dir/", device=0)
+    other.loadCryptoParams()
+    assert other.load_status == 7
+    with pytest.raises(shelfi.ShelfiError) as e:
+        other.encrypt(np.ones(4))
+    assert e.value.code == -2
+
+
+def test_keygen_matches_oracle_and_roundtrips(shelfi, oracle_mod, tmp_path):
+    """ckks.cpp:25-59 on the device engine; with a fixed seed the three files equal the oracle's, byte for byte."""
+    for bits, batch in ((52, 4096), (40, 2048), (20, 1024)):     # code/benchmark_crypto.py:123-124
+        d_gpu, d_cpu = tmp_path / f"gpu{bits}", tmp_path / f"cpu{bits}"
+        d_gpu.mkdir(); d_cpu.mkdir()
+        g = shelfi.CKKS("ckks", batch, bits, str(d_gpu) + "/", device=0)
+        g.set_sampler_seed(31337)
+        assert g.genCryptoContextAndKeyGen() == 1
+        assert g.ring_dim == 0                                   # generating does not load (ckks.cpp:28)
+        o = oracle_mod.Oracle("ckks", batch, bits, str(d_cpu) + "/")
+        assert o.genCryptoContextAndKeyGen(seed=31337, nine_int=True) == 1
+        for name in ("cryptocontext.txt", "key-public.txt", "key-private.txt"):
+            assert (d_gpu / name).read_bytes() == (d_cpu / name).read_bytes(), (bits, name)
+        g.set_sampler_seed(None)
+        g.loadCryptoParams()
+        assert g.load_status == 0 and g.slots == batch
+        x = np.random.default_rng(bits).normal(0, 0.05, 3 * batch + 17)
+        w = [0.25, 0.75]
+        out = g.decrypt(g.computeWeightedAverage([g.encrypt(x), g.encrypt(-x)], w), x.size)
+        tol = max(RTOL, 2.0 ** (18 - bits))                      # params_results.csv: low bit counts are lossy
+        assert np.abs(out - (0.25 * x - 0.75 * x)).max() < tol * max(1.0, np.abs(x).max())
+        assert o.loadCryptoParams() == 0                         # sparse packing parity (batch < N/2)
+        g.set_sampler_seed(5)
+        assert g.encrypt(x) == o.encrypt(x, seed=5)
+        g.set_sampler_seed(None)
+
+
+def test_golden_vectors(gpu_ckks):
+    """Committed oracle outputs (tests/golden/make_vectors.py): the GPU path reproduces them."""
+    for name in ("pybind", "code"):
+        v = np.load(GOLDEN / f"vectors_{name}.npz")
+        h = gpu_ckks[name]
+        h.set_sampler_seed(int(v["seed"]))
+        blobs = [h.encrypt(x) for x in v["inputs"]]
+        h.set_sampler_seed(None)
+        assert [hashlib.sha256(b).hexdigest() for b in blobs] == [str(s) for s in v["encrypt_sha256"]]
+        avg = h.computeWeightedAverage(blobs, [float(t) for t in v["weights"]])
+        assert hashlib.sha256(avg).hexdigest() == str(v["wavg_sha256"])
+        out = h.decrypt(avg, v["inputs"].shape[1])
+        assert np.array_equal(out, v["decrypted"])
+
+
+def test_full_size_properties(gpu_ckks):
+    """BASELINE config 2 size (10 learners x 1,663,370 params): round trip, linearity, checksum of checksums."""
+    h = gpu_ckks["pybind"]
+    P, K = 1663370, 10
+    rng = np.random.default_rng(2)
+    xs = [rng.normal(0, 0.05, P).astype(np.float32).astype(np.float64) for _ in range(K)]
+    w = [1.0 / K] * K
+    blobs = [h.encrypt(x) for x in xs]
+    n_ct = h.num_ciphertexts(P)
+    assert n_ct == 407 and all(len(b) == h.blob_size(n_ct) for b in blobs)
+    avg = h.computeWeightedAverage(blobs, w)
+    out = h.decrypt(avg, P)
+    expect = sum(float(np.float32(wi)) * x for wi, x in zip(w, xs))
+    assert rel_err(out, expect) < RTOL
+    # linearity: wavg of (A, B) with weights (1, 1) decrypts to dec(A) + dec(B)
+    s = h.decrypt(h.computeWeightedAverage(blobs[:2], [1.0, 1.0]), P)
+    assert rel_err(s, xs[0] + xs[1]) < RTOL
+    # order independence of the accumulation, bit for bit
+    a1 = h.computeWeightedAverage(blobs[:3], [0.5, 0.25, 0.25])
+    a2 = h.computeWeightedAverage([blobs[2], blobs[0], blobs[1]], [0.25, 0.5, 0.25])
+    assert a1 == a2

@@ -1,0 +1,118 @@
+"""Device code replayed on the CPU (tests/emu) against the oracle: the same ckks_core.cuh phases the
+kernels run, thread by thread.  Bit-exact for integer work and — because the FFT butterflies are unfused
+and follow the reference's order — for encode/decode as well."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+N = 8192
+
+
+def vp(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+def test_reduction_schedule(emu, emu_ctx):
+    # 60-bit q0: one mid-transform reduction (end of pass 1), shift-type quick reduce;
+    # 52-bit q1: no mid reduction, "just above a power of two" quick reduce
+    h = emu_ctx["pybind"]
+    assert (emu.L.emu_fwd_mask(h, 0), emu.L.emu_rmode(h, 0)) == (2, 0)
+    assert (emu.L.emu_fwd_mask(h, 1), emu.L.emu_rmode(h, 1)) == (0, 1)
+
+
+@pytest.mark.parametrize("pattern", ["random", "max", "zero", "delta", "alternating"])
+def test_ntt_matches_oracle(emu, emu_ctx, oracles, pattern):
+    o, h = oracles["pybind"], emu_ctx["pybind"]
+    rng = np.random.default_rng(7)
+    for l in range(2):
+        q = o.modulus(l)
+        a = {"random": rng.integers(0, q, N, dtype=np.uint64), "max": np.full(N, q - 1, np.uint64),
+             "zero": np.zeros(N, np.uint64), "delta": np.eye(1, N, 5, dtype=np.uint64)[0] * np.uint64(q - 1),
+             "alternating": np.where(np.arange(N) % 2 == 0, q - 1, 0).astype(np.uint64)}[pattern]
+        f = a.copy(); emu.L.emu_ntt_forward(h, l, vp(f))
+        assert np.array_equal(f, o.ntt_forward(l, a))
+        b = a.copy(); emu.L.emu_ntt_inverse(h, l, vp(b))
+        assert np.array_equal(b, o.ntt_inverse(l, a))
+
+
+def test_generic_modulus_uses_barrett_path(emu, oracle_mod):
+    """A prime far from a power of two (quick-reduce mode 2) transforms correctly: inverse(forward) = identity."""
+    M = 2 * N
+    q = oracle_mod.previous_prime((3 << 43) + 1, M)      # 1.5 * 2^44: nowhere near a power of two
+    psi = oracle_mod.min_root_of_unity(M, q)
+    h = emu.context([q], [psi])
+    assert emu.L.emu_rmode(h, 0) == 2
+    a = np.random.default_rng(0).integers(0, q, N, dtype=np.uint64)
+    b = a.copy()
+    emu.L.emu_ntt_forward(h, 0, vp(b))
+    assert not np.array_equal(a, b)
+    emu.L.emu_ntt_inverse(h, 0, vp(b))
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("n_valid,scale", [(4096, 1.0), (4096, 100.0), (1, 1.0), (1000, 0.05), (4095, 7.0)])
+def test_encode_matches_oracle(emu, emu_ctx, oracles, n_valid, scale):
+    o, h = oracles["code"], emu_ctx["code"]
+    x = (np.random.default_rng(n_valid).random(n_valid) - 0.5) * 2 * scale
+    m = np.empty(N, np.int64)
+    emu.L.emu_encode(h, vp(x), n_valid, vp(m))
+    assert np.array_equal(m, o.encode_coeffs(x))
+
+
+def test_sampler_matches_oracle_and_distribution(emu, emu_ctx, oracles):
+    o, h = oracles["pybind"], emu_ctx["pybind"]
+    x = np.zeros(4096)
+    vs, es = [], []
+    for ct in (0, 1, 2**32 + 5):
+        m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint16)
+        emu.L.emu_encode_sample(h, vp(x), 4096, 99, ct, vp(m_e0), vp(ve))
+        v, e0, e1 = o.sample_noise(99, ct)
+        assert np.array_equal(m_e0, e0)                      # x = 0 -> m = 0
+        assert np.array_equal((ve & 0xFF).astype(np.int8), v.astype(np.int8))
+        assert np.array_equal((ve >> 8).astype(np.int8), e1.astype(np.int8))
+        vs.append(v); es += [e0, e1]
+    v, e = np.concatenate(vs), np.concatenate(es)
+    assert set(np.unique(v)) == {-1, 0, 1}
+    assert abs(np.mean(v == 0) - 1 / 3) < 0.02
+    assert abs(e.std() - 3.19) < 0.08 and abs(e.mean()) < 0.08 and np.abs(e).max() <= 31
+
+
+def test_encrypt_decrypt_match_oracle(emu, emu_ctx, oracles, fixture_name):
+    o, h = oracles[fixture_name], emu_ctx[fixture_name]
+    x = np.random.default_rng(3).normal(0, 0.05, 4096)
+    m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint16)
+    emu.L.emu_encode_sample(h, vp(x), 4096, 1234, 7, vp(m_e0), vp(ve))
+    b, a = o.public_key()
+    ct = np.empty((2, 2, N), np.uint64)
+    emu.L.emu_encrypt(h, vp(m_e0), vp(ve), vp(b), vp(a), vp(ct))
+    ref = o.encrypt_ct(x, 1234, 7)
+    assert np.array_equal(ct, ref)
+    s = o.secret_key()
+    sf = o.scaling_factor
+    out_ref, hi_ref, lo_ref = o.decrypt_ct(ref, sf, want_coeffs=True)
+    out, hi, lo = np.zeros(4096), np.empty(N, np.int64), np.empty(N, np.uint64)
+    emu.L.emu_decrypt(h, vp(ct), vp(s), math.pow(sf, -1) * math.pow(2, 52), math.pow(2, -52), vp(out), 4096, vp(hi),
+                      vp(lo))
+    assert np.array_equal(hi, hi_ref) and np.array_equal(lo, lo_ref)
+    assert np.array_equal(out, out_ref)
+    assert np.abs(out - x).max() < 1e-9
+
+
+def test_weighted_sum_arithmetic_matches_oracle(emu, emu_ctx, oracles):
+    o, h = oracles["pybind"], emu_ctx["pybind"]
+    rng = np.random.default_rng(11)
+    for l in range(2):
+        q = o.modulus(l)
+        k = 16
+        ins = [rng.integers(0, q, 512, dtype=np.uint64) for _ in range(k)]
+        ins[0][:] = q - 1
+        w = [np.float32(v) for v in rng.random(k)]
+        w[0] = np.float32(1.0)
+        c = np.array([o.weight_constant(float(v)) % q for v in w], dtype=np.uint64)
+        ptrs = (C.c_void_p * k)(*[a.ctypes.data for a in ins])
+        out = np.empty(512, np.uint64)
+        emu.L.emu_weighted_sum(h, l, ptrs, vp(c), k, vp(out), 512)
+        ref = [sum(int(ci) * int(a[j]) for ci, a in zip(c, ins)) % q for j in range(512)]
+        assert out.tolist() == ref
