@@ -36,11 +36,13 @@ constexpr int kNttThreads = 256;     // one CTA per limb polynomial, 32 coeffici
 constexpr int kFftThreads = 256;
 
 struct __attribute__((aligned(16))) tw_t { u64 w, ws; };  // twiddle and its Shoup companion floor(w*2^64/q)
+struct __attribute__((aligned(16))) u64x2 { u64 x, y; };
 
 // Per-limb constants, passed to kernels by value inside RingConst.
 struct LimbConst {
     u64 q;          // modulus (<= 60 bits)
     u64 q2;         // 2q
+    u64 nq;         // 2^64 - q: x*w + h*nq == x*w - h*q (mod 2^64) with the subtraction folded into the multiply-add
     u64 mu;         // floor(2^64 / q): generic Barrett quotient estimate
     u64 ninv, ninv_s;       // N^-1 mod q and Shoup companion
     u64 wninv, wninv_s;     // itw[1] * N^-1 mod q (last inverse stage with the scaling folded in)
@@ -77,6 +79,34 @@ HD u32 mulhi32(u32 a, u32 b) {
 }
 // Shoup product, lazy: x*w - floor(x*ws/2^64)*q, in [0, 2q) for ANY 64-bit x (w < q).
 HD u64 shoup_lazy(u64 x, u64 w, u64 ws, u64 q) { return x * w - mulhi(x, ws) * q; }
+// same value, written as two multiply-adds (nq = 2^64 - q): no negate / 64-bit subtract on the ALU pipe
+HD u64 shoup_lazy_nq(u64 x, u64 w, u64 ws, u64 nq) {
+#ifdef __CUDA_ARCH__
+    // 2 IMAD.WIDE + 4 IMAD on the fma pipe, nothing on the ALU pipe: both low products accumulate into one
+    // 64-bit register, the four cross terms ride on IMAD's 32-bit addend.
+    u64 h = __umul64hi(x, ws);
+    u32 xl = (u32)x, xh = (u32)(x >> 32), wl = (u32)w, wh = (u32)(w >> 32);
+    u32 hl = (u32)h, hh = (u32)(h >> 32), nl = (u32)nq, nh = (u32)(nq >> 32);
+    u64 r;
+    asm("{\n\t"
+        ".reg .u64 t;\n\t"
+        ".reg .u32 lo, hi;\n\t"
+        "mul.wide.u32 t, %1, %3;\n\t"
+        "mad.wide.u32 t, %5, %7, t;\n\t"
+        "mov.b64 {lo, hi}, t;\n\t"
+        "mad.lo.u32 hi, %1, %4, hi;\n\t"
+        "mad.lo.u32 hi, %2, %3, hi;\n\t"
+        "mad.lo.u32 hi, %5, %8, hi;\n\t"
+        "mad.lo.u32 hi, %6, %7, hi;\n\t"
+        "mov.b64 %0, {lo, hi};\n\t"
+        "}"
+        : "=l"(r)
+        : "r"(xl), "r"(xh), "r"(wl), "r"(wh), "r"(hl), "r"(hh), "r"(nl), "r"(nh));
+    return r;
+#else
+    return x * w + mulhi(x, ws) * nq;
+#endif
+}
 HD u64 csub(u64 x, u64 m) { return x >= m ? x - m : x; }
 // x (any value the caller's bound analysis allows) -> [0, 2q)
 HD u64 quick_reduce(u64 x, const LimbConst &lc) {
@@ -97,149 +127,191 @@ HD u64 signed_to_mod(i64 x, const LimbConst &lc) {
 // accesses in the radix-2 pass) and makes every radix-8 pass's 64-bit accesses conflict-free.
 HD u32 swz(u32 i) { return i ^ ((i >> 3) & 0xEu); }
 
+// Shared-memory tile addressing.  All offsets are BYTE offsets into the 64 KiB tile; with the swizzle above every
+// access of a pass is `thread constant (+/^) compile-time constant`, so the hardware addressing modes absorb it:
+//   pass A/B (LO >= 7): bits 6..4 of the element index come from the thread only -> one XOR per thread, then
+//                       immediate offsets k << (LO+3) and round * 2048*8 (A) / 16384 (B)
+//   pass C   (LO == 4): the register index k sits in bits 6..4 -> offset ^ (k << 4), one LOP3 per access
+//   pass D   (LO == 1): k sits in bits 3..1 and is XORed with a thread constant -> (base | h3 << 4) ^ (k << 4)
+//   pass E            : pairs (2vt, 2vt+1): 16*vt ^ (((vt >> 3) & 7) << 4), rounds add 4096
+HD u64 &tile(char *sm, u32 byte_off) { return *reinterpret_cast<u64 *>(sm + byte_off); }
+HD const u64 &tile(const char *sm, u32 byte_off) { return *reinterpret_cast<const u64 *>(sm + byte_off); }
+template <int LO> HD u32 tile_base(u32 vt) {  // byte offset of the k = 0 element of virtual thread vt
+    if (LO >= 7) {
+        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO;
+        u32 e = (high << (LO + 3)) | low;
+        return (e ^ ((e >> 3) & 0xEu)) << 3;
+    } else if (LO == 4) {
+        return (((vt >> 4) << 7) | (vt & 15u)) << 3;
+    } else {  // LO == 1
+        u32 high = vt >> 1;
+        return (((high << 4) | (vt & 1u)) << 3) | ((high & 7u) << 4);
+    }
+}
+template <int LO> HD u32 tile_off(u32 base, int k) {
+    if (LO >= 7) return base + ((u32)k << (LO + 3));
+    if (LO == 4) return (base ^ ((u32)k << 4)) + ((u32)k << 7);
+    return base ^ ((u32)k << 4);
+}
+HD u32 tile_pair(u32 vt) { return (vt << 4) ^ (((vt >> 3) & 7u) << 4); }
+
 // Cooley-Tukey butterfly, Harvey lazy form: no per-butterfly correction, bounds grow by 2q per stage
 // and are brought back by quick_reduce at the pass boundaries named in LimbConst::fwd_mask.
-HD void ct_bfly(u64 &x, u64 &y, const tw_t &w, u64 q, u64 q2) {
-    u64 t = shoup_lazy(y, w.w, w.ws, q);
+HD void ct_bfly(u64 &x, u64 &y, const tw_t &w, u64 nq, u64 q2) {
+    u64 t = shoup_lazy_nq(y, w.w, w.ws, nq);
     y = x + q2 - t;
     x = x + t;
 }
 // radix-8 register pass: a[k], k = (b2 b1 b0) with b2 the address bit of the first stage.
-HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 q, u64 q2) {
+HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 nq, u64 q2) {
     tw_t w = tw[t0];
 #pragma unroll
-    for (int k = 0; k < 4; k++) ct_bfly(a[k], a[k + 4], w, q, q2);
+    for (int k = 0; k < 4; k++) ct_bfly(a[k], a[k + 4], w, nq, q2);
     tw_t w0 = tw[2 * t0], w1 = tw[2 * t0 + 1];
-    ct_bfly(a[0], a[2], w0, q, q2); ct_bfly(a[1], a[3], w0, q, q2);
-    ct_bfly(a[4], a[6], w1, q, q2); ct_bfly(a[5], a[7], w1, q, q2);
+    ct_bfly(a[0], a[2], w0, nq, q2); ct_bfly(a[1], a[3], w0, nq, q2);
+    ct_bfly(a[4], a[6], w1, nq, q2); ct_bfly(a[5], a[7], w1, nq, q2);
 #pragma unroll
-    for (int k = 0; k < 4; k++) ct_bfly(a[2 * k], a[2 * k + 1], tw[4 * t0 + k], q, q2);
+    for (int k = 0; k < 4; k++) ct_bfly(a[2 * k], a[2 * k + 1], tw[4 * t0 + k], nq, q2);
 }
 
 // ---- forward NTT phases (natural order in, bit-reversed order out), 8192 points, 256 threads ----
 // Pass A: stages 0-2 (address bits 12,11,10) straight from the loader into shared memory.
 template <class Load>
-HD void fwd_phase_a(int tid, u64 *sm, const LimbConst &lc, Load ld) {
+HD void fwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const u64 nq = lc.nq, q2 = lc.q2;
+#pragma unroll 1
     for (int r = 0; r < 4; r++) {
         u32 vt = tid + kNttThreads * r;
         u64 a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = ld((u32)(k << 10) | vt);
-        ct_radix8(a, lc.tw, 1u, lc.q, lc.q2);
+        ct_radix8(a, lc.tw, 1u, nq, q2);
         if (lc.fwd_mask & 1u) {
 #pragma unroll
             for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
         }
+        u32 base = tile_base<10>(vt);
 #pragma unroll
-        for (int k = 0; k < 8; k++) sm[swz((u32)(k << 10) | vt)] = a[k];
+        for (int k = 0; k < 8; k++) tile(sm, tile_off<10>(base, k)) = a[k];
     }
 }
 // Passes B, C, D: LO = 7, 4, 1 (lowest of the three address bits held in registers).
 template <int LO>
-HD void fwd_phase_mid(int tid, u64 *sm, const LimbConst &lc) {
+HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
     constexpr int PASS = (10 - LO) / 3;               // 1, 2, 3
     constexpr u32 S0 = 12 - (LO + 2);                 // first stage of the pass: 3, 6, 9
+    char *sm = reinterpret_cast<char *>(smem);
+    const u64 nq = lc.nq, q2 = lc.q2;
+#pragma unroll 1
     for (int r = 0; r < 4; r++) {
         u32 vt = tid + kNttThreads * r;
-        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO;
-        u32 base = (high << (LO + 3)) | low;
+        u32 base = tile_base<LO>(vt);
         u64 a[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) a[k] = sm[swz(base | (u32)(k << LO))];
-        ct_radix8(a, lc.tw, (1u << S0) + high, lc.q, lc.q2);
+        for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<LO>(base, k));
+        ct_radix8(a, lc.tw, (1u << S0) + (vt >> LO), nq, q2);
         if (lc.fwd_mask & (1u << PASS)) {
 #pragma unroll
             for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
         }
 #pragma unroll
-        for (int k = 0; k < 8; k++) sm[swz(base | (u32)(k << LO))] = a[k];
+        for (int k = 0; k < 8; k++) tile(sm, tile_off<LO>(base, k)) = a[k];
     }
 }
 // Pass E: stage 12 (address bit 0); st(pair index, x, y) receives lazily reduced values in
 // [0, (B+2)q) — the storer applies full_reduce or folds further work in first.
 template <class Store>
-HD void fwd_phase_e(int tid, const u64 *sm, const LimbConst &lc, Store st) {
+HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+    const char *sm = reinterpret_cast<const char *>(smem);
+    const u64 nq = lc.nq, q2 = lc.q2;
+#pragma unroll 2
     for (int r = 0; r < 16; r++) {
         u32 vt = tid + kNttThreads * r;
-        u32 p = swz(2u * vt);
-        u64 x = sm[p], y = sm[p + 1];
-        ct_bfly(x, y, lc.tw[(kN >> 1) + vt], lc.q, lc.q2);
-        st(vt, x, y);
+        u64x2 v = *reinterpret_cast<const u64x2 *>(sm + tile_pair(vt));
+        ct_bfly(v.x, v.y, lc.tw[(kN >> 1) + vt], nq, q2);
+        st(vt, v.x, v.y);
     }
 }
 
 // ---- inverse NTT phases (bit-reversed in, natural out), Gentleman-Sande ----
 // Inputs to a pass are < 2q; X' = X + Y doubles the bound per stage, Y' = (X - Y + c)*w with
 // c = (bound of Y) so the difference stays non-negative.  Every pass ends with quick_reduce.
-HD void gs_bfly(u64 &x, u64 &y, const tw_t &w, u64 q, u64 c) {
+HD void gs_bfly(u64 &x, u64 &y, const tw_t &w, u64 nq, u64 c) {
     u64 t = x + c - y;
     x = x + y;
-    y = shoup_lazy(t, w.w, w.ws, q);
+    y = shoup_lazy_nq(t, w.w, w.ws, nq);
 }
 // radix-8 GS pass over address bits LO, LO+1, LO+2 (a[k]: k bit j <-> address bit LO+j).
 // Stage for address bit b uses m = N >> (b+1) groups: twiddle index m + (x >> (b+1)).
-HD void gs_radix8(u64 (&a)[8], const tw_t *__restrict__ itw, u32 t2, u64 q, u64 q2) {
+HD void gs_radix8(u64 (&a)[8], const tw_t *__restrict__ itw, u32 t2, u64 nq, u64 q2) {
     // t2 = index for the LAST of the three stages (bit LO+2): (N >> (LO+3)) + high
-    // first stage, bit LO: index 4*t2 + (k >> 1) pairs (k, k+1) for even k ... bounds 2q -> 4q
+    // first stage, bit LO: index 4*t2 + (k >> 1), pairs (k, k+1) for even k; bounds 2q -> 4q
 #pragma unroll
-    for (int k = 0; k < 4; k++) gs_bfly(a[2 * k], a[2 * k + 1], itw[4 * t2 + k], q, q2);
+    for (int k = 0; k < 4; k++) gs_bfly(a[2 * k], a[2 * k + 1], itw[4 * t2 + k], nq, q2);
     // second stage, bit LO+1: x elements < 4q, y elements < 2q (fresh products)
     tw_t w0 = itw[2 * t2], w1 = itw[2 * t2 + 1];
-    gs_bfly(a[0], a[2], w0, q, 2 * q2); gs_bfly(a[1], a[3], w0, q, 2 * q2);
-    gs_bfly(a[4], a[6], w1, q, 2 * q2); gs_bfly(a[5], a[7], w1, q, 2 * q2);
+    gs_bfly(a[0], a[2], w0, nq, 2 * q2); gs_bfly(a[1], a[3], w0, nq, 2 * q2);
+    gs_bfly(a[4], a[6], w1, nq, 2 * q2); gs_bfly(a[5], a[7], w1, nq, 2 * q2);
     // third stage, bit LO+2: bound 8q
     tw_t w = itw[t2];
 #pragma unroll
-    for (int k = 0; k < 4; k++) gs_bfly(a[k], a[k + 4], w, q, 4 * q2);
+    for (int k = 0; k < 4; k++) gs_bfly(a[k], a[k + 4], w, nq, 4 * q2);
 }
 // Pass E': address bit 0 from the loader (pairs), result quick-reduced into shared memory.
 // ld(pair index, &x, &y) must deliver values < 4q.
 template <class Load>
-HD void inv_phase_e(int tid, u64 *sm, const LimbConst &lc, Load ld) {
+HD void inv_phase_e(int tid, u64 *smem, const LimbConst &lc, Load ld) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const u64 nq = lc.nq, q2 = lc.q2;
+#pragma unroll 2
     for (int r = 0; r < 16; r++) {
         u32 vt = tid + kNttThreads * r;
         u64 x, y;
         ld(vt, x, y);
-        gs_bfly(x, y, lc.itw[(kN >> 1) + vt], lc.q, 2 * lc.q2);
-        u32 p = swz(2u * vt);
-        sm[p] = quick_reduce(x, lc);
-        sm[p + 1] = y;
+        gs_bfly(x, y, lc.itw[(kN >> 1) + vt], nq, 2 * q2);
+        *reinterpret_cast<u64x2 *>(sm + tile_pair(vt)) = u64x2{quick_reduce(x, lc), y};
     }
 }
 template <int LO>  // LO = 1, 4, 7
-HD void inv_phase_mid(int tid, u64 *sm, const LimbConst &lc) {
+HD void inv_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const u64 nq = lc.nq, q2 = lc.q2;
+#pragma unroll 1
     for (int r = 0; r < 4; r++) {
         u32 vt = tid + kNttThreads * r;
-        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO;
-        u32 base = (high << (LO + 3)) | low;
+        u32 base = tile_base<LO>(vt);
         u64 a[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) a[k] = sm[swz(base | (u32)(k << LO))];
-        gs_radix8(a, lc.itw, (u32)(kN >> (LO + 3)) + high, lc.q, lc.q2);
+        for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<LO>(base, k));
+        gs_radix8(a, lc.itw, (u32)(kN >> (LO + 3)) + (vt >> LO), nq, q2);
 #pragma unroll
-        for (int k = 0; k < 8; k++) sm[swz(base | (u32)(k << LO))] = quick_reduce(a[k], lc);
+        for (int k = 0; k < 8; k++) tile(sm, tile_off<LO>(base, k)) = quick_reduce(a[k], lc);
     }
 }
 // Last pass: address bits 10, 11, 12 with N^-1 folded into the final stage; st(index, value in [0,q)).
 template <class Store>
-HD void inv_phase_last(int tid, const u64 *sm, const LimbConst &lc, Store st) {
-    const u64 q = lc.q, q2 = lc.q2;
+HD void inv_phase_last(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+    const char *sm = reinterpret_cast<const char *>(smem);
+    const u64 q = lc.q, q2 = lc.q2, nq = lc.nq;
+#pragma unroll 1
     for (int r = 0; r < 4; r++) {
         u32 vt = tid + kNttThreads * r;
+        u32 base = tile_base<10>(vt);
         u64 a[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) a[k] = sm[swz((u32)(k << 10) | vt)];
+        for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<10>(base, k));
 #pragma unroll
-        for (int k = 0; k < 4; k++) gs_bfly(a[2 * k], a[2 * k + 1], lc.itw[4 + k], q, q2);
+        for (int k = 0; k < 4; k++) gs_bfly(a[2 * k], a[2 * k + 1], lc.itw[4 + k], nq, q2);
         tw_t w0 = lc.itw[2], w1 = lc.itw[3];
-        gs_bfly(a[0], a[2], w0, q, 2 * q2); gs_bfly(a[1], a[3], w0, q, 2 * q2);
-        gs_bfly(a[4], a[6], w1, q, 2 * q2); gs_bfly(a[5], a[7], w1, q, 2 * q2);
+        gs_bfly(a[0], a[2], w0, nq, 2 * q2); gs_bfly(a[1], a[3], w0, nq, 2 * q2);
+        gs_bfly(a[4], a[6], w1, nq, 2 * q2); gs_bfly(a[5], a[7], w1, nq, 2 * q2);
 #pragma unroll
         for (int k = 0; k < 4; k++) {  // x' = (x+y)/N, y' = (x-y)*w/N ; inputs < 8q
             u64 x = a[k], y = a[k + 4];
             u64 s = x + y, d = x + 4 * q2 - y;
-            a[k] = csub(shoup_lazy(s, lc.ninv, lc.ninv_s, q), q);
-            a[k + 4] = csub(shoup_lazy(d, lc.wninv, lc.wninv_s, q), q);
+            a[k] = csub(shoup_lazy_nq(s, lc.ninv, lc.ninv_s, nq), q);
+            a[k + 4] = csub(shoup_lazy_nq(d, lc.wninv, lc.wninv_s, nq), q);
         }
 #pragma unroll
         for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, a[k]);
@@ -565,7 +637,6 @@ HD void pack_word(u64 *image, u64 a0, u64 widx, const u64 *run) {
 // ------------------------------------------------------------------------------------------
 // loaders / storers plugged into the NTT phases by the kernels (and by the CPU replay harness)
 // ------------------------------------------------------------------------------------------
-struct __attribute__((aligned(16))) u64x2 { u64 x, y; };
 HD u64x2 ld_readonly(const u64x2 *p) {
 #ifdef __CUDA_ARCH__
     ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(p));

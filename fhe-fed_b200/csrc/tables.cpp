@@ -39,6 +39,7 @@ std::string make_limb_const(uint64_t q, uint64_t psi, LimbConst *lc, std::vector
     std::memset(lc, 0, sizeof *lc);
     lc->q = q;
     lc->q2 = 2 * q;
+    lc->nq = (uint64_t)0 - q;
     lc->mu = (uint64_t)((((u128)1) << 64) / q);
     uint64_t ipsi = nt::inv_mod(psi, q);
     tw->assign(kN, tw_t{0, 0});
