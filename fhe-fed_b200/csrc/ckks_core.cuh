@@ -381,6 +381,21 @@ HD u32 bitrev32(u32 x, int bits) {
     return r;
 #endif
 }
+// FFT tile swizzle (16-byte complex elements): XOR index bits 2..0 with bits 5..3 so that both "8 consecutive
+// lanes read 8 consecutive elements" and "8 consecutive lanes read elements 8 apart" are conflict-free.
+HD u32 zsw(u32 i) { return i ^ ((i >> 3) & 7u); }
+HD void dif_bfly(cplx &a, cplx &b, const cplx &w) {  // FFTSpecialInv: u = a + b, v = (a - b) * w
+    double dr = fsub(a.re, b.re), di = fsub(a.im, b.im);
+    a.re = fadd(a.re, b.re); a.im = fadd(a.im, b.im);
+    b.re = fsub(fmul(dr, w.re), fmul(di, w.im));
+    b.im = fadd(fmul(dr, w.im), fmul(di, w.re));
+}
+HD void dit_bfly(cplx &a, cplx &b, const cplx &w) {  // FFTSpecial: v = b * w, a' = a + v, b' = a - v
+    double vr = fsub(fmul(b.re, w.re), fmul(b.im, w.im));
+    double vi = fadd(fmul(b.re, w.im), fmul(b.im, w.re));
+    b.re = fsub(a.re, vr); b.im = fsub(a.im, vi);
+    a.re = fadd(a.re, vr); a.im = fadd(a.im, vi);
+}
 // One stage of FFTSpecialInv (decimation in frequency): butterflies j of block length `len`.
 // twi = per-stage table, entry (len/2 - 1) + j  holds ksi[(lenq - rot[j] % lenq) * M/lenq].
 HD void fft_inv_stage(int tid, int nthreads, cplx *z, u32 size, u32 len, const cplx *__restrict__ twi) {
@@ -388,11 +403,9 @@ HD void fft_inv_stage(int tid, int nthreads, cplx *z, u32 size, u32 len, const c
     for (u32 b = tid; b < (size >> 1); b += nthreads) {
         u32 j = b & (lenh - 1), i = (b / lenh) * len;
         cplx w = twi[lenh - 1 + j];
-        cplx u = z[i + j], v = z[i + j + lenh];
-        double dr = fsub(u.re, v.re), di = fsub(u.im, v.im);
-        z[i + j].re = fadd(u.re, v.re); z[i + j].im = fadd(u.im, v.im);
-        z[i + j + lenh].re = fsub(fmul(dr, w.re), fmul(di, w.im));
-        z[i + j + lenh].im = fadd(fmul(dr, w.im), fmul(di, w.re));
+        cplx u = z[zsw(i + j)], v = z[zsw(i + j + lenh)];
+        dif_bfly(u, v, w);
+        z[zsw(i + j)] = u; z[zsw(i + j + lenh)] = v;
     }
 }
 // One stage of FFTSpecial (decimation in time, input already bit-reversed).
@@ -401,11 +414,71 @@ HD void fft_fwd_stage(int tid, int nthreads, cplx *z, u32 size, u32 len, const c
     for (u32 b = tid; b < (size >> 1); b += nthreads) {
         u32 j = b & (lenh - 1), i = (b / lenh) * len;
         cplx w = twf[lenh - 1 + j];
-        cplx u = z[i + j], v = z[i + j + lenh];
-        double vr = fsub(fmul(v.re, w.re), fmul(v.im, w.im));
-        double vi = fadd(fmul(v.re, w.im), fmul(v.im, w.re));
-        z[i + j].re = fadd(u.re, vr); z[i + j].im = fadd(u.im, vi);
-        z[i + j + lenh].re = fsub(u.re, vr); z[i + j + lenh].im = fsub(u.im, vi);
+        cplx u = z[zsw(i + j)], v = z[zsw(i + j + lenh)];
+        dit_bfly(u, v, w);
+        z[zsw(i + j)] = u; z[zsw(i + j + lenh)] = v;
+    }
+}
+// Full packing (4096 slots, the reference's default): the same butterflies grouped into four radix-8 register
+// passes (3 stages each, 8 complex values per thread, 2 rounds of 256 threads) — 4 shared-memory round trips
+// and barriers instead of 12.  LO = lowest of the three index bits held in registers.
+constexpr u32 kFftFast = 4096;
+template <int LO>  // LO = 9, 6, 3, 0 in that order
+HD void fft_inv_pass8(int tid, cplx *z, const cplx *__restrict__ twi) {
+#pragma unroll 1
+    for (int r = 0; r < 2; r++) {
+        u32 vt = tid + kFftThreads * r;
+        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO, base = (high << (LO + 3)) | low;
+        cplx a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = z[zsw(base | ((u32)k << LO))];
+        {   // stage on bit LO+2: lenh = 2^(LO+2), j = (k & 3) << LO | low
+            const cplx *t = twi + ((1u << (LO + 2)) - 1u) + low;
+#pragma unroll
+            for (int k = 0; k < 4; k++) dif_bfly(a[k], a[k + 4], t[(u32)k << LO]);
+        }
+        {   // bit LO+1: lenh = 2^(LO+1), j = (k & 1) << LO | low
+            const cplx *t = twi + ((1u << (LO + 1)) - 1u) + low;
+            cplx w0 = t[0], w1 = t[1u << LO];
+            dif_bfly(a[0], a[2], w0); dif_bfly(a[1], a[3], w1);
+            dif_bfly(a[4], a[6], w0); dif_bfly(a[5], a[7], w1);
+        }
+        {   // bit LO: lenh = 2^LO, j = low
+            cplx w = twi[((1u << LO) - 1u) + low];
+#pragma unroll
+            for (int k = 0; k < 4; k++) dif_bfly(a[2 * k], a[2 * k + 1], w);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) z[zsw(base | ((u32)k << LO))] = a[k];
+    }
+}
+template <int LO>  // LO = 0, 3, 6, 9 in that order
+HD void fft_fwd_pass8(int tid, cplx *z, const cplx *__restrict__ twf) {
+#pragma unroll 1
+    for (int r = 0; r < 2; r++) {
+        u32 vt = tid + kFftThreads * r;
+        u32 low = vt & ((1u << LO) - 1u), high = vt >> LO, base = (high << (LO + 3)) | low;
+        cplx a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = z[zsw(base | ((u32)k << LO))];
+        {   // bit LO
+            cplx w = twf[((1u << LO) - 1u) + low];
+#pragma unroll
+            for (int k = 0; k < 4; k++) dit_bfly(a[2 * k], a[2 * k + 1], w);
+        }
+        {   // bit LO+1
+            const cplx *t = twf + ((1u << (LO + 1)) - 1u) + low;
+            cplx w0 = t[0], w1 = t[1u << LO];
+            dit_bfly(a[0], a[2], w0); dit_bfly(a[1], a[3], w1);
+            dit_bfly(a[4], a[6], w0); dit_bfly(a[5], a[7], w1);
+        }
+        {   // bit LO+2
+            const cplx *t = twf + ((1u << (LO + 2)) - 1u) + low;
+#pragma unroll
+            for (int k = 0; k < 4; k++) dit_bfly(a[k], a[k + 4], t[(u32)k << LO]);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) z[zsw(base | ((u32)k << LO))] = a[k];
     }
 }
 
@@ -512,8 +585,8 @@ HD u64 run_offset(const BlobRuns &br, u64 ct, u32 r) { return ct == 0 ? br.off0[
 // phase 0: chunk of x -> z (zero padded)
 HD void encode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid) {
     for (u32 i = tid; i < ec.slots; i += nthreads) {
-        z[i].re = i < n_valid ? x[i] : 0.0;
-        z[i].im = 0.0;
+        z[zsw(i)].re = i < n_valid ? x[i] : 0.0;
+        z[zsw(i)].im = 0.0;
     }
 }
 // phases 1..log_slots: fft_inv_stage(len = slots >> (p-1))
@@ -523,11 +596,12 @@ HD void encode_finalize(int tid, int nthreads, cplx *z, const EncodeConst &ec) {
     for (u32 i = tid; i < ec.slots; i += nthreads) {
         u32 j = bitrev32(i, (int)ec.log_slots);
         if (i > j) continue;
-        cplx a = z[i], b = z[j];
+        u32 pi = zsw(i), pj = zsw(j);
+        cplx a = z[pi], b = z[pj];
         i64 ar = llround(fmul(fmul(a.re, ec.inv_size), ec.pow_p)), ai = llround(fmul(fmul(a.im, ec.inv_size), ec.pow_p));
         i64 br = llround(fmul(fmul(b.re, ec.inv_size), ec.pow_p)), bi = llround(fmul(fmul(b.im, ec.inv_size), ec.pow_p));
-        zi[2 * j] = ar; zi[2 * j + 1] = ai;
-        zi[2 * i] = br; zi[2 * i + 1] = bi;
+        zi[2 * pj] = ar; zi[2 * pj + 1] = ai;
+        zi[2 * pi] = br; zi[2 * pi + 1] = bi;
     }
 }
 // coefficient j of the plaintext polynomial from the finalized tile
@@ -536,7 +610,7 @@ HD i64 encode_coeff(const cplx *z, const EncodeConst &ec, u32 j) {
     u32 nh = kN >> 1;
     u32 half = j >= nh ? 1u : 0u, idx = j - half * nh;
     if (idx & (ec.gap - 1)) return 0;
-    return zi[2 * (idx / ec.gap) + half];
+    return zi[2 * zsw(idx / ec.gap) + half];
 }
 // sampling + output of one group of four coefficients (ternary v, Gaussian e0, e1): [PAL] Encrypt's draws
 HD void sample_group(u32 j4, u64 ct_index, const SamplerConst &sc, const u64 *cdf, int (&v)[4], int (&e0)[4],
@@ -587,14 +661,14 @@ HD void decode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const
         }
         u32 half = j >= nh ? 1u : 0u, idx = j - half * nh;
         if (idx & (ec.gap - 1)) continue;
-        u32 slot = bitrev32(idx / ec.gap, (int)ec.log_slots);
+        u32 slot = zsw(bitrev32(idx / ec.gap, (int)ec.log_slots));
         double val = fmul(i128_to_double(neg, hi, lo), dc.pre);
         if (half) z[slot].im = val; else z[slot].re = val;
     }
 }
 // phases 1..log_slots: fft_fwd_stage(len = 2 << (p-1)); last phase: real parts * 2^-p
 HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc, double *out, u64 length) {
-    for (u32 i = tid; i < length; i += nthreads) out[i] = fmul(z[i].re, dc.pow_p);
+    for (u32 i = tid; i < length; i += nthreads) out[i] = fmul(z[zsw(i)].re, dc.pow_p);
 }
 
 // ---- weighted sum: EvalMult(ct, const) + EvalAdd over learners (ckks.cpp:286-297) ----

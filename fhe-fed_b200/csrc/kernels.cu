@@ -62,9 +62,16 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
     u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
     encode_load(tid, kFftThreads, z, ec, x + first, n_valid);
     __syncthreads();
-    for (u32 len = ec.slots; len >= 2; len >>= 1) {
-        fft_inv_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_inv);
-        __syncthreads();
+    if (ec.slots == kFftFast) {
+        fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<6>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<3>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<0>(tid, z, ec.tw_inv); __syncthreads();
+    } else {
+        for (u32 len = ec.slots; len >= 2; len >>= 1) {
+            fft_inv_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_inv);
+            __syncthreads();
+        }
     }
     encode_finalize(tid, kFftThreads, z, ec);
     __syncthreads();
@@ -154,9 +161,16 @@ __global__ void __launch_bounds__(kFftThreads) decode_kernel(const __grid_consta
                 tap_hi ? tap_hi + ct * (u64)kN : nullptr, tap_lo ? tap_lo + ct * (u64)kN : nullptr);
     if (!out) return;
     __syncthreads();
-    for (u32 len = 2; len <= ec.slots; len <<= 1) {
-        fft_fwd_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_fwd);
-        __syncthreads();
+    if (ec.slots == kFftFast) {
+        fft_fwd_pass8<0>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<3>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<6>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<9>(tid, z, ec.tw_fwd); __syncthreads();
+    } else {
+        for (u32 len = 2; len <= ec.slots; len <<= 1) {
+            fft_fwd_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_fwd);
+            __syncthreads();
+        }
     }
     u64 first = ct * ec.batch;
     if (first >= n) return;

@@ -92,8 +92,15 @@ void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
 static void replay_encode(const Emu *e, const double *x, uint64_t n_valid, std::vector<cplx> &z) {
     z.assign(e->ec.slots, cplx{0, 0});
     FOR_THREADS(kFftThreads) encode_load(tid, kFftThreads, z.data(), e->ec, x, n_valid);
-    for (u32 len = e->ec.slots; len >= 2; len >>= 1)
-        FOR_THREADS(kFftThreads) fft_inv_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_inv);
+    if (e->ec.slots == kFftFast) {
+        FOR_THREADS(kFftThreads) fft_inv_pass8<9>(tid, z.data(), e->ec.tw_inv);
+        FOR_THREADS(kFftThreads) fft_inv_pass8<6>(tid, z.data(), e->ec.tw_inv);
+        FOR_THREADS(kFftThreads) fft_inv_pass8<3>(tid, z.data(), e->ec.tw_inv);
+        FOR_THREADS(kFftThreads) fft_inv_pass8<0>(tid, z.data(), e->ec.tw_inv);
+    } else {
+        for (u32 len = e->ec.slots; len >= 2; len >>= 1)
+            FOR_THREADS(kFftThreads) fft_inv_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_inv);
+    }
     FOR_THREADS(kFftThreads) encode_finalize(tid, kFftThreads, z.data(), e->ec);
 }
 void emu_encode(const Emu *e, const double *x, uint64_t n_valid, int64_t *m) {
@@ -150,8 +157,15 @@ void emu_decrypt(const Emu *e, const uint64_t *ct, const uint64_t *sk, double pr
     std::vector<cplx> z(e->ec.slots);
     FOR_THREADS(kFftThreads)
         decode_load(tid, kFftThreads, z.data(), e->ec, dc, L, coeff.data(), (i64 *)tap_hi, (u64 *)tap_lo);
-    for (u32 len = 2; len <= e->ec.slots; len <<= 1)
-        FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_fwd);
+    if (e->ec.slots == kFftFast) {
+        FOR_THREADS(kFftThreads) fft_fwd_pass8<0>(tid, z.data(), e->ec.tw_fwd);
+        FOR_THREADS(kFftThreads) fft_fwd_pass8<3>(tid, z.data(), e->ec.tw_fwd);
+        FOR_THREADS(kFftThreads) fft_fwd_pass8<6>(tid, z.data(), e->ec.tw_fwd);
+        FOR_THREADS(kFftThreads) fft_fwd_pass8<9>(tid, z.data(), e->ec.tw_fwd);
+    } else {
+        for (u32 len = 2; len <= e->ec.slots; len <<= 1)
+            FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_fwd);
+    }
     FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length);
 }
 
