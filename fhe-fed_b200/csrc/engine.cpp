@@ -271,12 +271,9 @@ int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_ind
     sc.seed = h->seeded ? h->seed : fresh_seed();
     sc.ct_index0 = ct_index0;
     std::memcpy(sc.gauss_cdf, h->gauss_cdf, sizeof sc.gauss_cdf);
-    timed(h, kKEncodeSample, s, [&] {
-        launch_encode_sample(h->rc, h->ec, sc, d_x, n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s);
-    });
     timed(h, kKEncrypt, s, [&] {
-        launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), d_ct,
-                       (u32)n_ct, s);
+        launch_encrypt_fused(h->rc, h->ec, sc, d_x, n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(),
+                             h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), d_ct, s);
     });
     CU(cudaGetLastError());
     return 0;

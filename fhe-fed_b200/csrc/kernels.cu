@@ -122,6 +122,58 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreAddParked{c1, &lc});
 }
 
+// Fused encrypt: one CTA per ciphertext does encode + sampling (FFT tile), parks m+e0 / (v,e1) in global scratch
+// (L2-resident, 80 KiB per ciphertext), then reuses the same 64 KiB tile for the 3 NTTs of every limb.  Compared
+// with encode_kernel + encrypt_kernel this samples once per ciphertext, removes one launch and its partial
+// wave, and lets the latency-bound FFT/sampler phases of one CTA hide under the integer work of its two
+// co-resident CTAs.
+__global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __grid_constant__ RingConst rc,
+                                                                       const __grid_constant__ EncodeConst ec,
+                                                                       const __grid_constant__ SamplerConst sc,
+                                                                       const double *x, u64 n, i64 *m_e0, uint16_t *ve,
+                                                                       const tw_t *pk_b, const tw_t *pk_a, u64 *ct_out) {
+    extern __shared__ __align__(16) u64 sm[];
+    cplx *z = reinterpret_cast<cplx *>(sm);
+    __shared__ u64 cdf[32];
+    const int tid = threadIdx.x;
+    const u64 ct = blockIdx.x;
+    if (tid < 32) cdf[tid] = sc.gauss_cdf[tid];
+    const u64 first = ct * ec.batch;
+    const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
+    i64 *m_row = m_e0 + ct * (u64)kN;
+    uint16_t *ve_row = ve + ct * (u64)kN;
+    encode_load(tid, kNttThreads, z, ec, x + first, n_valid);
+    __syncthreads();
+    if (ec.slots == kFftFast) {
+        fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<6>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<3>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<0>(tid, z, ec.tw_inv); __syncthreads();
+    } else {
+        for (u32 len = ec.slots; len >= 2; len >>= 1) {
+            fft_inv_stage(tid, kNttThreads, z, ec.slots, len, ec.tw_inv);
+            __syncthreads();
+        }
+    }
+    encode_finalize(tid, kNttThreads, z, ec);
+    __syncthreads();
+    encode_sample_emit(tid, kNttThreads, z, ec, sc, cdf, sc.ct_index0 + ct, m_row, ve_row);
+    __syncthreads();  // scratch rows written by this block are visible to all of its threads; tile is free
+    const u32 L = rc.limbs;
+    for (u32 l = 0; l < L; l++) {
+        const LimbConst lc = rc.limb[l];
+        u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
+        u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
+        ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
+                         StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.q});
+        __syncthreads();
+        ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreAddParked{c0, &lc});
+        __syncthreads();
+        ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreAddParked{c1, &lc});
+        __syncthreads();
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // decrypt stage 1: t = c0 + c1*s per limb, inverse NTT to coefficients
 // ------------------------------------------------------------------------------------------
@@ -289,6 +341,7 @@ cudaError_t kernels_init() {
     OPT_IN(ntt_forward_kernel, NTT_SMEM_BYTES)
     OPT_IN(ntt_inverse_kernel, NTT_SMEM_BYTES)
     OPT_IN(encrypt_kernel, NTT_SMEM_BYTES)
+    OPT_IN(encrypt_fused_kernel, NTT_SMEM_BYTES)
     OPT_IN(decrypt_intt_kernel, NTT_SMEM_BYTES)
     OPT_IN(encode_kernel<true>, (kN / 2) * sizeof(cplx))
     OPT_IN(encode_kernel<false>, (kN / 2) * sizeof(cplx))
@@ -315,6 +368,11 @@ void launch_encode_only(const RingConst &, const EncodeConst &ec, const double *
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s) {
     if (n_ct) encrypt_kernel<<<n_ct * rc.limbs, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, m_e0, ve, pk_b, pk_a, ct);
+}
+void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
+                          u32 n_ct, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, u64 *ct, cudaStream_t s) {
+    if (n_ct)
+        encrypt_fused_kernel<<<n_ct, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, sc, x, n, m_e0, ve, pk_b, pk_a, ct);
 }
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s) {
     if (n_ct) decrypt_intt_kernel<<<n_ct * rc.limbs, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ct, sk, coeff);

@@ -18,6 +18,9 @@ void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const Samp
 // encrypt: three forward NTTs per (ciphertext, limb) + public-key combine -> ct[n_ct][2][L][N]
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s);
+// encode + sample + encrypt in one kernel, one CTA per ciphertext (m_e0 / ve are scratch)
+void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
+                          u32 n_ct, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, u64 *ct, cudaStream_t s);
 // decrypt stage 1: c0 + c1*s, inverse NTT -> coeff[n_ct][L][N]
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s);
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
