@@ -65,6 +65,24 @@ class ClockSampler:
         self.thread = threading.Thread(target=self._run, daemon=True)
 
     def _run(self):
+        try:  # NVML: sub-millisecond queries, so even a 50 ms timed region gets several samples
+            import pynvml as nv
+            nv.nvmlInit()
+            dev = nv.nvmlDeviceGetHandleByIndex(self.index)
+            mx = nv.nvmlDeviceGetMaxClockInfo(dev, nv.NVML_CLOCK_SM)
+            bits = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                    ("sw_power_cap", 0x4)]
+            while not self.stop.is_set():
+                sm = nv.nvmlDeviceGetClockInfo(dev, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(dev)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(dev)
+                self.samples.append([str(sm), str(mx), hex(r)] + ["Active" if r & b else "Not Active" for _, b in bits])
+                self.stop.wait(0.005)
+            return
+        except Exception:
+            pass
         while not self.stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
@@ -240,7 +258,7 @@ def run_ours(args):
     value = world * P_MODEL * args.steps / (ms_max / 1e3)
 
     # per-kernel times from the library's CUDA-event timers (same stream, same timed region)
-    names = ["encode_sample", "encrypt", "weighted_sum", "decrypt_intt", "decode"]
+    names = ["encode_sample_unfused", "encrypt", "weighted_sum", "decrypt_intt", "decode"]
     prof = {}
     for i, name in enumerate(names):
         tot, cnt = C.c_double(), C.c_uint64()
@@ -258,10 +276,10 @@ def run_ours(args):
     algo_bytes = (8 + 32 * LIMBS) * params_per_launch          # encrypt stage, per parameter
     enc_ms = enc["ms_total"] / max(1, enc["launches"])
     achieved = algo_bytes / (enc_ms / 1e3) / 1e9 if enc_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "encrypt_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "encrypt_fused_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_source": "measured" if peaks else "fallback",
                 "ms_per_launch": enc_ms, "share_of_step": enc["ms_total"] / ms if ms > 0 else None,
-                "note": "integer-pipe bound: 3 NTTs per limb in shared memory per 72 algorithmic bytes/param (DESIGN.md §4)"}
+                "note": "integer-pipe bound (fmaheavy/IMAD): FFT + sampler + 3 NTTs per limb in shared memory per 72 algorithmic bytes/param; DESIGN.md 4.1, profiles/"}
     path_gbs = bytes_per_param(K, LIMBS) * P_MODEL * args.steps / (ms / 1e3) / 1e9
 
     # ---------------- standalone NTT bandwidth (second half of BASELINE's metric) ----------------
@@ -356,7 +374,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

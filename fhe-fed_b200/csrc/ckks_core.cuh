@@ -119,7 +119,7 @@ HD u64 full_reduce(u64 x, const LimbConst &lc) { return csub(quick_reduce(x, lc)
 HD u64 barrett_reduce(u64 x, const LimbConst &lc) { return csub(x - mulhi(x, lc.mu) * lc.q, lc.q); }
 HD u64 signed_to_mod(i64 x, const LimbConst &lc) {
     u64 mag = x < 0 ? (u64)0 - (u64)x : (u64)x;
-    u64 r = barrett_reduce(mag, lc);
+    u64 r = csub(quick_reduce(mag, lc), lc.q);   // quick_reduce is valid for every 64-bit value (tables.cpp)
     return (x < 0 && r) ? lc.q - r : r;
 }
 
@@ -225,12 +225,20 @@ template <class Store>
 HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
     const char *sm = reinterpret_cast<const char *>(smem);
     const u64 nq = lc.nq, q2 = lc.q2;
-#pragma unroll 2
-    for (int r = 0; r < 16; r++) {
-        u32 vt = tid + kNttThreads * r;
-        u64x2 v = *reinterpret_cast<const u64x2 *>(sm + tile_pair(vt));
-        ct_bfly(v.x, v.y, lc.tw[(kN >> 1) + vt], nq, q2);
-        st(vt, v.x, v.y);
+    const tw_t *__restrict__ tw = lc.tw + (kN >> 1);
+#pragma unroll 1
+    for (int r0 = 0; r0 < 16; r0 += 4) {  // four rounds in flight: twiddle loads (L2) and tile loads issued together
+        tw_t w[4];
+        u64x2 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[i] = tw[tid + kNttThreads * (r0 + i)];
+#pragma unroll
+        for (int i = 0; i < 4; i++) v[i] = *reinterpret_cast<const u64x2 *>(sm + tile_pair(tid + kNttThreads * (r0 + i)));
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            ct_bfly(v[i].x, v[i].y, w[i], nq, q2);
+            st((u32)(tid + kNttThreads * (r0 + i)), v[i].x, v[i].y);
+        }
     }
 }
 
@@ -755,13 +763,13 @@ struct LoadSigned {
 };
 // NTT(v) epilogue: park b*v^ and a*v^ (lazy, < 2q) in the output rows
 struct StorePkProducts {
-    const tw_t *b, *a; u64 *c0, *c1; u64 q;
+    const tw_t *b, *a; u64 *c0, *c1; u64 nq;
     HD void operator()(u32 vt, u64 x, u64 y) const {
         const u64x2 *bp = reinterpret_cast<const u64x2 *>(b) + 2 * vt;
         const u64x2 *ap = reinterpret_cast<const u64x2 *>(a) + 2 * vt;
         u64x2 b0 = ld_readonly(bp), b1 = ld_readonly(bp + 1), a0 = ld_readonly(ap), a1 = ld_readonly(ap + 1);
-        reinterpret_cast<u64x2 *>(c0)[vt] = u64x2{shoup_lazy(x, b0.x, b0.y, q), shoup_lazy(y, b1.x, b1.y, q)};
-        reinterpret_cast<u64x2 *>(c1)[vt] = u64x2{shoup_lazy(x, a0.x, a0.y, q), shoup_lazy(y, a1.x, a1.y, q)};
+        reinterpret_cast<u64x2 *>(c0)[vt] = u64x2{shoup_lazy_nq(x, b0.x, b0.y, nq), shoup_lazy_nq(y, b1.x, b1.y, nq)};
+        reinterpret_cast<u64x2 *>(c1)[vt] = u64x2{shoup_lazy_nq(x, a0.x, a0.y, nq), shoup_lazy_nq(y, a1.x, a1.y, nq)};
     }
 };
 // NTT(m + e0) / NTT(e1) epilogue: add to the parked product (read back by the thread that wrote it)
@@ -783,8 +791,8 @@ struct LoadDecryptPair {
         u64x2 v = ld_readonly(reinterpret_cast<const u64x2 *>(c1) + vt);
         const u64x2 *sp = reinterpret_cast<const u64x2 *>(s) + 2 * vt;
         u64x2 s0 = ld_readonly(sp), s1 = ld_readonly(sp + 1);
-        x = u.x + shoup_lazy(v.x, s0.x, s0.y, q);
-        y = u.y + shoup_lazy(v.y, s1.x, s1.y, q);
+        x = u.x + shoup_lazy_nq(v.x, s0.x, s0.y, (u64)0 - q);
+        y = u.y + shoup_lazy_nq(v.y, s1.x, s1.y, (u64)0 - q);
     }
 };
 

@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
     u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
     ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
-                     StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.q});
+                     StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.nq});
     __syncthreads();
     ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreAddParked{c0, &lc});
     __syncthreads();
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
         u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
         u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
         ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
-                         StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.q});
+                         StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.nq});
         __syncthreads();
         ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreAddParked{c0, &lc});
         __syncthreads();
