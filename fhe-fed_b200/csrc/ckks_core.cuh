@@ -221,23 +221,30 @@ HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
 }
 // Pass E: stage 12 (address bit 0); st(pair index, x, y) receives lazily reduced values in
 // [0, (B+2)q) — the storer applies full_reduce or folds further work in first.
+// Storer protocol: `typename Store::Aux`, `Store::kGroup` rounds in flight, `fetch(vt)` issues the epilogue's own
+// global loads (parked data, key material) together with the twiddle loads, `operator()(vt, x, y, aux)` finishes.
+struct NoAux {};
 template <class Store>
 HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+    constexpr int G = Store::kGroup;
     const char *sm = reinterpret_cast<const char *>(smem);
     const u64 nq = lc.nq, q2 = lc.q2;
     const tw_t *__restrict__ tw = lc.tw + (kN >> 1);
 #pragma unroll 1
-    for (int r0 = 0; r0 < 16; r0 += 4) {  // four rounds in flight: twiddle loads (L2) and tile loads issued together
-        tw_t w[4];
-        u64x2 v[4];
+    for (int r0 = 0; r0 < 16; r0 += G) {  // G rounds in flight: every long-latency load is issued before any math
+        tw_t w[G];
+        u64x2 v[G];
+        typename Store::Aux aux[G];
 #pragma unroll
-        for (int i = 0; i < 4; i++) w[i] = tw[tid + kNttThreads * (r0 + i)];
+        for (int i = 0; i < G; i++) w[i] = tw[tid + kNttThreads * (r0 + i)];
 #pragma unroll
-        for (int i = 0; i < 4; i++) v[i] = *reinterpret_cast<const u64x2 *>(sm + tile_pair(tid + kNttThreads * (r0 + i)));
+        for (int i = 0; i < G; i++) aux[i] = st.fetch((u32)(tid + kNttThreads * (r0 + i)));
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
+        for (int i = 0; i < G; i++) v[i] = *reinterpret_cast<const u64x2 *>(sm + tile_pair(tid + kNttThreads * (r0 + i)));
+#pragma unroll
+        for (int i = 0; i < G; i++) {
             ct_bfly(v[i].x, v[i].y, w[i], nq, q2);
-            st((u32)(tid + kNttThreads * (r0 + i)), v[i].x, v[i].y);
+            st((u32)(tid + kNttThreads * (r0 + i)), v[i].x, v[i].y, aux[i]);
         }
     }
 }
@@ -732,8 +739,11 @@ struct LoadGlobal {
     HD u64 operator()(u32 i) const { return p[i]; }
 };
 struct StoreFullReducePair {
+    typedef NoAux Aux;
+    static constexpr int kGroup = 4;
     u64 *p; const LimbConst *lc;
-    HD void operator()(u32 vt, u64 x, u64 y) const {
+    HD Aux fetch(u32) const { return Aux{}; }
+    HD void operator()(u32 vt, u64 x, u64 y, const Aux &) const {
         reinterpret_cast<u64x2 *>(p)[vt] = u64x2{full_reduce(x, *lc), full_reduce(y, *lc)};
     }
 };
@@ -761,26 +771,30 @@ struct LoadSigned {
     const i64 *m; const LimbConst *lc;
     HD u64 operator()(u32 i) const { return signed_to_mod(m[i], *lc); }
 };
-// NTT(v) epilogue: park b*v^ and a*v^ (lazy, < 2q) in the output rows
-struct StorePkProducts {
-    const tw_t *b, *a; u64 *c0, *c1; u64 nq;
-    HD void operator()(u32 vt, u64 x, u64 y) const {
-        const u64x2 *bp = reinterpret_cast<const u64x2 *>(b) + 2 * vt;
-        const u64x2 *ap = reinterpret_cast<const u64x2 *>(a) + 2 * vt;
-        u64x2 b0 = ld_readonly(bp), b1 = ld_readonly(bp + 1), a0 = ld_readonly(ap), a1 = ld_readonly(ap + 1);
-        reinterpret_cast<u64x2 *>(c0)[vt] = u64x2{shoup_lazy_nq(x, b0.x, b0.y, nq), shoup_lazy_nq(y, b1.x, b1.y, nq)};
-        reinterpret_cast<u64x2 *>(c1)[vt] = u64x2{shoup_lazy_nq(x, a0.x, a0.y, nq), shoup_lazy_nq(y, a1.x, a1.y, nq)};
-    }
+// encrypt epilogues.  NTT(v) parks v^ itself (lazy, any 64-bit value) in the c1 row; NTT(m + e0) then forms
+// c0 = b*v^ + . and NTT(e1) overwrites the parked row with c1 = a*v^ + . — each thread re-reads only what it
+// wrote itself, so no fence is needed, and the key material is fetched 32 bytes per pair per pass.
+struct StoreLazyPair {
+    typedef NoAux Aux;
+    static constexpr int kGroup = 4;
+    u64 *park;
+    HD Aux fetch(u32) const { return Aux{}; }
+    HD void operator()(u32 vt, u64 x, u64 y, const Aux &) const { reinterpret_cast<u64x2 *>(park)[vt] = u64x2{x, y}; }
 };
-// NTT(m + e0) / NTT(e1) epilogue: add to the parked product (read back by the thread that wrote it)
-struct StoreAddParked {
-    u64 *c; const LimbConst *lc;
-    HD void operator()(u32 vt, u64 x, u64 y) const {
-        u64x2 p = reinterpret_cast<u64x2 *>(c)[vt];
-        u64 q = lc->q, q2 = lc->q2;
-        p.x = csub(csub(p.x + quick_reduce(x, *lc), q2), q);
-        p.y = csub(csub(p.y + quick_reduce(y, *lc), q2), q);
-        reinterpret_cast<u64x2 *>(c)[vt] = p;
+struct PkAux { u64x2 v, k0, k1; };
+struct StoreMulAdd {
+    typedef PkAux Aux;
+    static constexpr int kGroup = 2;
+    const tw_t *key; const u64 *park; u64 *out; const LimbConst *lc;
+    HD Aux fetch(u32 vt) const {
+        const u64x2 *kp = reinterpret_cast<const u64x2 *>(key) + 2 * vt;
+        return Aux{reinterpret_cast<const u64x2 *>(park)[vt], ld_readonly(kp), ld_readonly(kp + 1)};
+    }
+    HD void operator()(u32 vt, u64 x, u64 y, const Aux &a) const {
+        const u64 q = lc->q, q2 = lc->q2, nq = lc->nq;
+        u64 r0 = shoup_lazy_nq(a.v.x, a.k0.x, a.k0.y, nq) + quick_reduce(x, *lc);   // < 4q
+        u64 r1 = shoup_lazy_nq(a.v.y, a.k1.x, a.k1.y, nq) + quick_reduce(y, *lc);
+        reinterpret_cast<u64x2 *>(out)[vt] = u64x2{csub(csub(r0, q2), q), csub(csub(r1, q2), q)};
     }
 };
 // decrypt: t = c0 + c1*s on the way into the inverse transform (< 3q for reduced input)

@@ -85,8 +85,8 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
 
 // ------------------------------------------------------------------------------------------
 // encrypt: per (ciphertext, limb) CTA, three forward NTTs through one shared-memory tile.
-//   NTT(v)      -> P0 = b*v^, P1 = a*v^ parked in the output rows (re-read by the same thread, L2-resident)
-//   NTT(m + e0) -> c0 = P0 + .     NTT(e1) -> c1 = P1 + .
+//   NTT(v)      -> v^ parked in the c1 row (re-read by the same thread, L2-resident)
+//   NTT(m + e0) -> c0 = b*v^ + .     NTT(e1) -> c1 = a*v^ + .  (overwrites the parked row)
 // ------------------------------------------------------------------------------------------
 template <class Load, class Store>
 __device__ __forceinline__ void ntt_forward_tile(int tid, u64 *sm, const LimbConst &lc, Load ld, Store st) {
@@ -115,11 +115,11 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
     u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
     ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
-                     StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.nq});
+                     StoreLazyPair{c1});
     __syncthreads();
-    ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreAddParked{c0, &lc});
+    ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
     __syncthreads();
-    ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreAddParked{c1, &lc});
+    ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
 }
 
 // Fused encrypt: one CTA per ciphertext does encode + sampling (FFT tile), parks m+e0 / (v,e1) in global scratch
@@ -165,11 +165,11 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
         u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
         u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
         ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
-                         StorePkProducts{pk_b + (size_t)l * kN, pk_a + (size_t)l * kN, c0, c1, lc.nq});
+                         StoreLazyPair{c1});
         __syncthreads();
-        ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreAddParked{c0, &lc});
+        ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
         __syncthreads();
-        ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreAddParked{c1, &lc});
+        ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
         __syncthreads();
     }
 }

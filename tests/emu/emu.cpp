@@ -133,9 +133,9 @@ void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const ui
             a[j] = tw_t{pk_a[(size_t)l * kN + j], nt::shoup(pk_a[(size_t)l * kN + j], lc.q)};
         }
         u64 *c0 = out + (size_t)(0 * L + l) * kN, *c1 = out + (size_t)(1 * L + l) * kN;
-        replay_forward(sm.data(), lc, LoadTernary{ve, lc.q}, StorePkProducts{b.data(), a.data(), c0, c1, lc.nq});
-        replay_forward(sm.data(), lc, LoadSigned{(const i64 *)m_e0, &lc}, StoreAddParked{c0, &lc});
-        replay_forward(sm.data(), lc, LoadGaussHi{ve, lc.q}, StoreAddParked{c1, &lc});
+        replay_forward(sm.data(), lc, LoadTernary{ve, lc.q}, StoreLazyPair{c1});
+        replay_forward(sm.data(), lc, LoadSigned{(const i64 *)m_e0, &lc}, StoreMulAdd{b.data(), c1, c0, &lc});
+        replay_forward(sm.data(), lc, LoadGaussHi{ve, lc.q}, StoreMulAdd{a.data(), c1, c1, &lc});
     }
 }
 
