@@ -586,6 +586,15 @@ struct WavgArgs {
 
 struct LimbScalars { u64 c[kMaxLimbs]; };
 
+// one launch may encrypt several learners' vectors (same length n): block b -> learner b / n_ct, ciphertext b % n_ct
+constexpr int kMaxEncryptBatch = 16;
+struct EncryptBatch {
+    const double *x[kMaxEncryptBatch];
+    u64 *ct[kMaxEncryptBatch];
+    u64 seed[kMaxEncryptBatch];
+    u32 k, n_ct;
+};
+
 // byte offsets of the 2L coefficient runs of a serialized vector<Ciphertext> (wire.h)
 struct BlobRuns {
     u64 off0[2 * kMaxLimbs];   // ciphertext 0

@@ -262,21 +262,36 @@ uint64_t fresh_seed() {
 }
 
 // --- stage drivers (all asynchronous on `s`) ---
-int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct, cudaStream_t s) {
+// k learners' vectors (all of length n) in one launch: the grid covers k * n_ct ciphertexts, so small models still
+// fill the machine and co-resident CTAs are out of phase with one another.
+int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uint64_t n, uint64_t ct_index0,
+                       uint64_t *const *d_ct, cudaStream_t s) {
     uint64_t n_ct = (n + h->batch - 1) / h->batch;
-    if (n_ct > 0x7fffffffull / (2 * kMaxLimbs)) return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
-    CU(h->s_m.reserve(n_ct * kN * sizeof(int64_t)));
-    CU(h->s_ve.reserve(n_ct * kN * sizeof(uint16_t)));
+    if (n_ct * k > 0x7fffffffull / (2 * kMaxLimbs)) return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
     SamplerConst sc{};
-    sc.seed = h->seeded ? h->seed : fresh_seed();
     sc.ct_index0 = ct_index0;
     std::memcpy(sc.gauss_cdf, h->gauss_cdf, sizeof sc.gauss_cdf);
-    timed(h, kKEncrypt, s, [&] {
-        launch_encrypt_fused(h->rc, h->ec, sc, d_x, n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(),
-                             h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), d_ct, s);
-    });
+    for (uint32_t base = 0; base < k; base += kMaxEncryptBatch) {
+        EncryptBatch eb{};
+        eb.k = std::min<uint32_t>(kMaxEncryptBatch, k - base);
+        eb.n_ct = (u32)n_ct;
+        CU(h->s_m.reserve((size_t)eb.k * n_ct * kN * sizeof(int64_t)));
+        CU(h->s_ve.reserve((size_t)eb.k * n_ct * kN * sizeof(uint16_t)));
+        for (uint32_t i = 0; i < eb.k; i++) {
+            eb.x[i] = d_x[base + i];
+            eb.ct[i] = reinterpret_cast<u64 *>(d_ct[base + i]);
+            eb.seed[i] = h->seeded ? h->seed : fresh_seed();
+        }
+        timed(h, kKEncrypt, s, [&] {
+            launch_encrypt_fused(h->rc, h->ec, sc, eb, n, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(),
+                                 h->d_pk_a.as<tw_t>(), s);
+        });
+    }
     CU(cudaGetLastError());
     return 0;
+}
+int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct, cudaStream_t s) {
+    return encrypt_dense_many(h, &d_x, 1, n, ct_index0, &d_ct, s);
 }
 
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
@@ -761,6 +776,18 @@ int shelfi_encrypt_device(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_
     if (rcode) return rcode;
     if (!d_x || !d_ct || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
     return encrypt_dense(h, d_x, n, ct_index0, d_ct, static_cast<cudaStream_t>(stream));
+}
+
+int shelfi_encrypt_many_device(shelfi_ckks *h, const double *const *d_x, uint32_t k, uint64_t n, uint64_t ct_index0,
+                               uint64_t *const *d_ct, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, true, false);
+    if (rcode) return rcode;
+    if (!d_x || !d_ct || n == 0 || k == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    for (uint32_t i = 0; i < k; i++)
+        if (!d_x[i] || !d_ct[i]) return fail(h, SHELFI_ERR_ARG, "null learner buffer");
+    return encrypt_dense_many(h, d_x, k, n, ct_index0, d_ct, static_cast<cudaStream_t>(stream));
 }
 
 int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,

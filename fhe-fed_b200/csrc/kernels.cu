@@ -130,18 +130,24 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
 __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __grid_constant__ RingConst rc,
                                                                        const __grid_constant__ EncodeConst ec,
                                                                        const __grid_constant__ SamplerConst sc,
-                                                                       const double *x, u64 n, i64 *m_e0, uint16_t *ve,
-                                                                       const tw_t *pk_b, const tw_t *pk_a, u64 *ct_out) {
+                                                                       const __grid_constant__ EncryptBatch eb,
+                                                                       u64 n, i64 *m_e0, uint16_t *ve,
+                                                                       const tw_t *pk_b, const tw_t *pk_a) {
     extern __shared__ __align__(16) u64 sm[];
     cplx *z = reinterpret_cast<cplx *>(sm);
     __shared__ u64 cdf[32];
     const int tid = threadIdx.x;
-    const u64 ct = blockIdx.x;
+    const u32 learner = blockIdx.x / eb.n_ct;
+    const u64 ct = blockIdx.x % eb.n_ct;
+    const double *x = eb.x[learner];
+    u64 *ct_out = eb.ct[learner];
+    SamplerConst sl;   // per-learner seed; the CDF lives in shared memory
+    sl.seed = eb.seed[learner]; sl.ct_index0 = sc.ct_index0;
     if (tid < 32) cdf[tid] = sc.gauss_cdf[tid];
     const u64 first = ct * ec.batch;
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
-    i64 *m_row = m_e0 + ct * (u64)kN;
-    uint16_t *ve_row = ve + ct * (u64)kN;
+    i64 *m_row = m_e0 + (u64)blockIdx.x * (u64)kN;
+    uint16_t *ve_row = ve + (u64)blockIdx.x * (u64)kN;
     encode_load(tid, kNttThreads, z, ec, x + first, n_valid);
     __syncthreads();
     if (ec.slots == kFftFast) {
@@ -157,7 +163,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     }
     encode_finalize(tid, kNttThreads, z, ec);
     __syncthreads();
-    encode_sample_emit(tid, kNttThreads, z, ec, sc, cdf, sc.ct_index0 + ct, m_row, ve_row);
+    encode_sample_emit(tid, kNttThreads, z, ec, sl, cdf, sl.ct_index0 + ct, m_row, ve_row);
     __syncthreads();  // scratch rows written by this block are visible to all of its threads; tile is free
     const u32 L = rc.limbs;
     for (u32 l = 0; l < L; l++) {
@@ -369,10 +375,10 @@ void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, co
                     u64 *ct, u32 n_ct, cudaStream_t s) {
     if (n_ct) encrypt_kernel<<<n_ct * rc.limbs, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, m_e0, ve, pk_b, pk_a, ct);
 }
-void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, u64 *ct, cudaStream_t s) {
-    if (n_ct)
-        encrypt_fused_kernel<<<n_ct, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, sc, x, n, m_e0, ve, pk_b, pk_a, ct);
+void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const EncryptBatch &eb,
+                          u64 n, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s) {
+    if (eb.n_ct && eb.k)
+        encrypt_fused_kernel<<<eb.n_ct * eb.k, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, sc, eb, n, m_e0, ve, pk_b, pk_a);
 }
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s) {
     if (n_ct) decrypt_intt_kernel<<<n_ct * rc.limbs, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ct, sk, coeff);

@@ -19,8 +19,8 @@ void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const Samp
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s);
 // encode + sample + encrypt in one kernel, one CTA per ciphertext (m_e0 / ve are scratch)
-void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, u64 *ct, cudaStream_t s);
+void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const EncryptBatch &eb,
+                          u64 n, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s);
 // decrypt stage 1: c0 + c1*s, inverse NTT -> coeff[n_ct][L][N]
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s);
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)

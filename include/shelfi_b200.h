@@ -114,6 +114,10 @@ void shelfi_host_free(void *p);
  * ciphertext so that a shard draws the same sampler stream as the unsharded call. */
 int shelfi_encrypt_device(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct,
                           void *stream);
+/* k learners' vectors of equal length n in ONE launch (a server simulating its clients, as code/benchmark.py:490-493
+ * does on the CPU): same result as k shelfi_encrypt_device calls, better machine fill for small models. */
+int shelfi_encrypt_many_device(shelfi_ckks *h, const double *const *d_x, uint32_t k, uint64_t n, uint64_t ct_index0,
+                               uint64_t *const *d_ct, void *stream);
 int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
                                uint64_t n_ct, uint64_t *d_out, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,

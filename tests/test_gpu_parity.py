@@ -99,6 +99,25 @@ def test_encrypt_device_sharded_draws_the_same_stream(shelfi, gpu_ckks, oracles)
         assert np.array_equal(got[j], o.encrypt_ct(x[(3 + j) * 4096:(4 + j) * 4096], 77, 3 + j))
 
 
+def test_encrypt_many_equals_separate_calls(shelfi, gpu_ckks, oracles):
+    """One batched launch over k learners == k single-learner launches == the oracle, bit for bit."""
+    h, o = gpu_ckks["pybind"], oracles["pybind"]
+    rng = np.random.default_rng(12)
+    k, n = 3, 2 * 4096 + 100
+    xs = [rng.normal(0, 0.05, n) for _ in range(k)]
+    dx = [torch.from_numpy(x).cuda() for x in xs]
+    dct = [torch.empty((3, 2, 2, N), dtype=torch.int64, device="cuda") for _ in range(k)]
+    xp = (C.c_void_p * k)(*[t.data_ptr() for t in dx])
+    cp = (C.c_void_p * k)(*[t.data_ptr() for t in dct])
+    h.set_sampler_seed(99)
+    check(h, shelfi.lib().shelfi_encrypt_many_device(h.handle, xp, k, n, 0, cp, stream()))
+    h.set_sampler_seed(None)
+    for i in range(k):
+        got = host_u64(dct[i])
+        for j in range(3):
+            assert np.array_equal(got[j], o.encrypt_ct(xs[i][j * 4096:(j + 1) * 4096], 99, j)), (i, j)
+
+
 def test_unseeded_encryptions_differ_but_decrypt_equal(gpu_ckks):
     h = gpu_ckks["pybind"]
     x = np.random.default_rng(9).random(5000)
