@@ -266,22 +266,31 @@ void orc_free(void *p) { free(p); }
 /* ------------------------------------------------------------------------------------------- */
 /* NTT — [PAL] ChineseRemainderTransformFTT::ForwardTransformToBitReverse / InverseTransformFromBitReverse */
 /* ------------------------------------------------------------------------------------------- */
+/* Harvey lazy butterflies (values kept in [0,4q) forward, [0,2q) inverse, q < 2^60), branch-free, with one final
+ * correction pass: the same arrangement PALISADE's native transform uses; results are the canonical residues. */
+static inline uint64_t shoup_lazy(uint64_t x, uint64_t w, uint64_t wp, uint64_t q) { /* in [0, 2q) */
+    return x * w - (uint64_t)(((u128)x * wp) >> 64) * q;
+}
+static inline uint64_t csub(uint64_t x, uint64_t m) { return x - (m & -(uint64_t)(x >= m)); }
 static void ntt_fwd(uint64_t *a, uint32_t N, uint64_t q, const uint64_t *tw, const uint64_t *twp) {
+    const uint64_t q2 = 2 * q;
     uint32_t t = N >> 1;
     for (uint32_t m = 1; m < N; m <<= 1, t >>= 1) {
         for (uint32_t i = 0; i < m; i++) {
             uint64_t w = tw[m + i], wp = twp[m + i];
             uint64_t *x = a + 2 * i * t, *y = x + t;
             for (uint32_t j = 0; j < t; j++) {
-                uint64_t u = x[j], v = shoup_mul(y[j], w, wp, q);
-                x[j] = addmod(u, v, q);
-                y[j] = submod(u, v, q);
+                uint64_t u = csub(x[j], q2), v = shoup_lazy(y[j], w, wp, q);
+                x[j] = u + v;
+                y[j] = u + q2 - v;
             }
         }
     }
+    for (uint32_t j = 0; j < N; j++) a[j] = csub(csub(a[j], q2), q);
 }
 static void ntt_inv(uint64_t *a, uint32_t N, uint64_t q, const uint64_t *itw, const uint64_t *itwp, uint64_t ninv,
                     uint64_t ninvp) {
+    const uint64_t q2 = 2 * q;
     uint32_t t = 1;
     for (uint32_t m = N >> 1; m >= 1; m >>= 1, t <<= 1) {
         for (uint32_t i = 0; i < m; i++) {
@@ -289,12 +298,12 @@ static void ntt_inv(uint64_t *a, uint32_t N, uint64_t q, const uint64_t *itw, co
             uint64_t *x = a + 2 * i * t, *y = x + t;
             for (uint32_t j = 0; j < t; j++) {
                 uint64_t u = x[j], v = y[j];
-                x[j] = addmod(u, v, q);
-                y[j] = shoup_mul(submod(u, v, q), w, wp, q);
+                x[j] = csub(u + v, q2);
+                y[j] = shoup_lazy(u + q2 - v, w, wp, q);
             }
         }
     }
-    for (uint32_t j = 0; j < N; j++) a[j] = shoup_mul(a[j], ninv, ninvp, q);
+    for (uint32_t j = 0; j < N; j++) a[j] = csub(shoup_lazy(a[j], ninv, ninvp, q), q);
 }
 void orc_ntt_forward(const orc_ctx *c, int l, uint64_t *a) { ntt_fwd(a, c->wp.N, c->wp.q[l], c->tw[l], c->twp[l]); }
 void orc_ntt_inverse(const orc_ctx *c, int l, uint64_t *a) {
