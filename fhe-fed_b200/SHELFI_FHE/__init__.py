@@ -55,6 +55,7 @@ def lib() -> C.CDLL:
         "shelfi_load_crypto_params_from_memory": (C.c_int, [vp, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t,
                                                              C.c_char_p, C.c_size_t]),
         "shelfi_gen_crypto_context_and_keygen": (C.c_int, [vp]),
+        "shelfi_gen_crypto_context_and_keygen_ex": (C.c_int, [vp, u32, u32]),
         "shelfi_set_sampler_seed": (C.c_int, [vp, u64]),
         "shelfi_clear_sampler_seed": (C.c_int, [vp]),
         "shelfi_ring_dim": (u32, [vp]),
@@ -89,6 +90,7 @@ def lib() -> C.CDLL:
         "shelfi_ntt_inverse_device": (C.c_int, [vp, vp, u32, vp]),
         "shelfi_encode_device": (C.c_int, [vp, vp, u64, vp, vp]),
         "shelfi_decrypt_integer_device": (C.c_int, [vp, vp, u64, vp, vp, vp]),
+        "shelfi_decrypt_words_device": (C.c_int, [vp, vp, u64, vp, vp]),
         "shelfi_profile_enable": (C.c_int, [vp, C.c_int]),
         "shelfi_profile_reset": (C.c_int, [vp]),
         "shelfi_profile_get": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), u64p]),
@@ -167,9 +169,14 @@ class CKKS(Scheme):
         if rc & 4:
             print("Could not read secret key", file=sys.stderr)
 
-    def genCryptoContextAndKeyGen(self) -> int:
-        """ckks.cpp:25-59: write a fresh context and key pair into cryptodir; returns 1 or 0; does not load."""
-        ok = lib().shelfi_gen_crypto_context_and_keygen(self._h)
+    def genCryptoContextAndKeyGen(self, mult_depth: int = 1, ring_dim: int = 0) -> int:
+        """ckks.cpp:25-59: write a fresh context and key pair into cryptodir; returns 1 or 0; does not load.
+
+        The reference takes no arguments (multDepth = 1 is hard-coded at ckks.cpp:26, the ring dimension is
+        PALISADE's choice); ``mult_depth`` / ``ring_dim`` are extensions for deeper modulus chains and larger
+        rings (BASELINE configs 3-4: (3, 0) -> N = 16384, 4 limbs; (7, 0) -> N = 32768, 8 limbs at 52 bits).
+        """
+        ok = lib().shelfi_gen_crypto_context_and_keygen_ex(self._h, int(mult_depth), int(ring_dim))
         if not ok:
             print("Error generating crypto context and keys: " + self._err())
         return int(ok)

@@ -30,9 +30,15 @@ typedef unsigned int u32;
 typedef int i32;
 
 constexpr int kMaxLimbs = 8;
-constexpr int kLogN = 13;            // ring dimension 8192: the only one SHELFI's multDepth=1 contexts produce
-constexpr int kN = 1 << kLogN;
-constexpr int kNttThreads = 256;     // one CTA per limb polynomial, 32 coefficients per thread
+// The NTT working set is one 8192-point tile (64 KiB of shared memory, 3 CTAs per SM).  Ring dimension 8192 —
+// all that SHELFI's multDepth = 1 contexts produce — is exactly one tile.  Ring dimensions 2^(13+d), d = 1, 2
+// (BASELINE configs 3-4) split every limb polynomial into 2^d tiles: the d outermost Cooley-Tukey stages are
+// applied by the tile's loader (HeadLoad), the d outermost Gentleman-Sande stages by a streaming tail pass,
+// and the 13 inner stages run on the tile with twiddle indices offset by the tile number (`hb` below).
+constexpr int kLogN = 13;
+constexpr int kN = 1 << kLogN;       // tile points (NOT the ring dimension: that is RingConst::n)
+constexpr int kMaxLogBlocks = 2;     // ring dimension <= 32768
+constexpr int kNttThreads = 256;     // one CTA per tile, 32 coefficients per thread
 constexpr int kFftThreads = 256;
 
 struct __attribute__((aligned(16))) tw_t { u64 w, ws; };  // twiddle and its Shoup companion floor(w*2^64/q)
@@ -57,8 +63,13 @@ struct LimbConst {
 
 struct RingConst {
     u32 n, logn, limbs, slots;
+    u32 log_blocks;   // d = logn - 13: tiles per limb polynomial = 1 << d
+    u32 pad;
     LimbConst limb[kMaxLimbs];
 };
+// "head bits" of tile blk of a polynomial split into 2^d tiles: the twiddle index of stage s inside the tile is
+// (hb << s) + (local index bits), hb = 2^d | blk; one tile per polynomial gives hb = 1 (the plain tables).
+HD u32 head_bits(u32 d, u32 blk) { return (1u << d) | blk; }
 
 // ------------------------------------------------------------------------------------------
 // 64-bit modular arithmetic on the integer pipes
@@ -177,7 +188,7 @@ HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 nq, u64 
 // ---- forward NTT phases (natural order in, bit-reversed order out), 8192 points, 256 threads ----
 // Pass A: stages 0-2 (address bits 12,11,10) straight from the loader into shared memory.
 template <class Load>
-HD void fwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
+HD void fwd_phase_a(int tid, u64 *smem, const LimbConst &lc, u32 hb, Load ld) {
     char *sm = reinterpret_cast<char *>(smem);
     const u64 nq = lc.nq, q2 = lc.q2;
 #pragma unroll 1
@@ -186,7 +197,7 @@ HD void fwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
         u64 a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = ld((u32)(k << 10) | vt);
-        ct_radix8(a, lc.tw, 1u, nq, q2);
+        ct_radix8(a, lc.tw, hb, nq, q2);
         if (lc.fwd_mask & 1u) {
 #pragma unroll
             for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
@@ -198,7 +209,7 @@ HD void fwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
 }
 // Passes B, C, D: LO = 7, 4, 1 (lowest of the three address bits held in registers).
 template <int LO>
-HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
+HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
     constexpr int PASS = (10 - LO) / 3;               // 1, 2, 3
     constexpr u32 S0 = 12 - (LO + 2);                 // first stage of the pass: 3, 6, 9
     char *sm = reinterpret_cast<char *>(smem);
@@ -210,7 +221,7 @@ HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
         u64 a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<LO>(base, k));
-        ct_radix8(a, lc.tw, (1u << S0) + (vt >> LO), nq, q2);
+        ct_radix8(a, lc.tw, (hb << S0) + (vt >> LO), nq, q2);
         if (lc.fwd_mask & (1u << PASS)) {
 #pragma unroll
             for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
@@ -225,11 +236,11 @@ HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
 // global loads (parked data, key material) together with the twiddle loads, `operator()(vt, x, y, aux)` finishes.
 struct NoAux {};
 template <class Store>
-HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store st) {
     constexpr int G = Store::kGroup;
     const char *sm = reinterpret_cast<const char *>(smem);
     const u64 nq = lc.nq, q2 = lc.q2;
-    const tw_t *__restrict__ tw = lc.tw + (kN >> 1);
+    const tw_t *__restrict__ tw = lc.tw + ((size_t)hb << (kLogN - 1));
 #pragma unroll 1
     for (int r0 = 0; r0 < 16; r0 += G) {  // G rounds in flight: every long-latency load is issued before any math
         tw_t w[G];
@@ -276,7 +287,7 @@ HD void gs_radix8(u64 (&a)[8], const tw_t *__restrict__ itw, u32 t2, u64 nq, u64
 // Pass E': address bit 0 from the loader (pairs), result quick-reduced into shared memory.
 // ld(pair index, &x, &y) must deliver values < 4q.
 template <class Load>
-HD void inv_phase_e(int tid, u64 *smem, const LimbConst &lc, Load ld) {
+HD void inv_phase_e(int tid, u64 *smem, const LimbConst &lc, u32 hb, Load ld) {
     char *sm = reinterpret_cast<char *>(smem);
     const u64 nq = lc.nq, q2 = lc.q2;
 #pragma unroll 2
@@ -284,12 +295,12 @@ HD void inv_phase_e(int tid, u64 *smem, const LimbConst &lc, Load ld) {
         u32 vt = tid + kNttThreads * r;
         u64 x, y;
         ld(vt, x, y);
-        gs_bfly(x, y, lc.itw[(kN >> 1) + vt], nq, 2 * q2);
+        gs_bfly(x, y, lc.itw[((size_t)hb << (kLogN - 1)) + vt], nq, 2 * q2);
         *reinterpret_cast<u64x2 *>(sm + tile_pair(vt)) = u64x2{quick_reduce(x, lc), y};
     }
 }
 template <int LO>  // LO = 1, 4, 7
-HD void inv_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
+HD void inv_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
     char *sm = reinterpret_cast<char *>(smem);
     const u64 nq = lc.nq, q2 = lc.q2;
 #pragma unroll 1
@@ -299,7 +310,7 @@ HD void inv_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
         u64 a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<LO>(base, k));
-        gs_radix8(a, lc.itw, (u32)(kN >> (LO + 3)) + (vt >> LO), nq, q2);
+        gs_radix8(a, lc.itw, (hb << (10 - LO)) + (vt >> LO), nq, q2);
 #pragma unroll
         for (int k = 0; k < 8; k++) tile(sm, tile_off<LO>(base, k)) = quick_reduce(a[k], lc);
     }
@@ -332,6 +343,70 @@ HD void inv_phase_last(int tid, const u64 *smem, const LimbConst &lc, Store st) 
         for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, a[k]);
     }
 }
+
+// Ring dimensions above one tile: the tile's last pass is an ordinary radix-8 pass (address bits 10-12 of the
+// tile, twiddles offset by hb) whose lazily reduced results (< 2q) go back to global memory; inv_tail finishes.
+template <class Store>
+HD void inv_phase_last_lazy(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store st) {
+    const char *sm = reinterpret_cast<const char *>(smem);
+    const u64 q2 = lc.q2, nq = lc.nq;
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u32 base = tile_base<10>(vt);
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<10>(base, k));
+        gs_radix8(a, lc.itw, hb, nq, q2);
+#pragma unroll
+        for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, quick_reduce(a[k], lc));
+    }
+}
+// The d outermost Gentleman-Sande stages (address bits 13..13+d-1) with N^-1 folded into the last one, on the
+// 2^d values a[blk] that share one tile-local index.  Inputs < 2q, outputs in [0, q).
+template <int D>
+HD void inv_tail(u64 (&a)[1 << D], const LimbConst &lc) {
+    const u64 q = lc.q, q2 = lc.q2, nq = lc.nq;
+    if (D == 1) {
+        u64 s = a[0] + a[1], d = a[0] + q2 - a[1];
+        a[0] = csub(shoup_lazy_nq(s, lc.ninv, lc.ninv_s, nq), q);
+        a[1] = csub(shoup_lazy_nq(d, lc.wninv, lc.wninv_s, nq), q);
+    } else if (D == 2) {
+        gs_bfly(a[0], a[1], lc.itw[2], nq, q2);   // address bit 13: a[0], a[2] < 4q; a[1], a[3] < 2q
+        gs_bfly(a[2], a[3], lc.itw[3], nq, q2);
+        u64 s0 = a[0] + a[2], d0 = a[0] + 2 * q2 - a[2];   // address bit 14 with N^-1
+        u64 s1 = a[1] + a[3], d1 = a[1] + q2 - a[3];
+        a[0] = csub(shoup_lazy_nq(s0, lc.ninv, lc.ninv_s, nq), q);
+        a[2] = csub(shoup_lazy_nq(d0, lc.wninv, lc.wninv_s, nq), q);
+        a[1] = csub(shoup_lazy_nq(s1, lc.ninv, lc.ninv_s, nq), q);
+        a[3] = csub(shoup_lazy_nq(d1, lc.wninv, lc.wninv_s, nq), q);
+    }
+}
+// The d outermost Cooley-Tukey stages seen from tile blk: value at tile-local index i after those stages, from
+// the 2^d inputs in(i + k*8192) (each < q).  Redundant across the tiles of a polynomial (one extra modmul per
+// coefficient for d = 1, three for d = 2) but keeps the whole transform in one kernel with no global round trip.
+// Result < (1 + 2d) q: LimbConst::fwd_mask is scheduled from that bound (tables.cpp).
+template <int D, class Inner>
+struct HeadLoad {
+    Inner in; const LimbConst *lc; u32 blk;
+    HD u64 operator()(u32 i) const {
+        if (D == 0) return in(i);
+        const u64 nq = lc->nq, q2 = lc->q2;
+        const tw_t *__restrict__ tw = lc->tw;
+        if (D == 1) {
+            u64 x = in(i), y = in(i + kN);
+            u64 t = shoup_lazy_nq(y, tw[1].w, tw[1].ws, nq);
+            return blk ? x + q2 - t : x + t;
+        }
+        u64 x0 = in(i), x1 = in(i + kN), x2 = in(i + 2 * kN), x3 = in(i + 3 * kN);
+        u64 t0 = shoup_lazy_nq(x2, tw[1].w, tw[1].ws, nq), t1 = shoup_lazy_nq(x3, tw[1].w, tw[1].ws, nq);
+        u64 s0, s1;
+        if (blk < 2) { s0 = x0 + t0; s1 = x1 + t1; } else { s0 = x0 + q2 - t0; s1 = x1 + q2 - t1; }
+        tw_t w = tw[2 + (blk >> 1)];
+        u64 t = shoup_lazy_nq(s1, w.w, w.ws, nq);
+        return (blk & 1u) ? s0 + q2 - t : s0 + t;
+    }
+};
 
 // ------------------------------------------------------------------------------------------
 // sampler: Philox4x32-10, counter layout shared with the CPU oracle
@@ -389,7 +464,7 @@ HD double fsub(double a, double b) {
 }
 HD u32 bitrev32(u32 x, int bits) {
 #ifdef __CUDA_ARCH__
-    return __brev(x) >> (32 - bits);
+    return bits ? __brev(x) >> (32 - bits) : 0u;
 #else
     u32 r = 0;
     for (int i = 0; i < bits; i++) r |= ((x >> i) & 1u) << (bits - 1 - i);
@@ -548,6 +623,95 @@ HD double i128_to_double(bool neg, u64 hi, u64 lo) {
     return neg ? -r : r;
 }
 
+
+// ---- chains deeper than two limbs: Garner mixed-radix digits + Horner into L 64-bit words ----
+// ([PAL] DCRTPoly::CRTInterpolate yields the same integer in [0, Q); every q_i < 2^60 so Q fits L words)
+struct CrtNConst {
+    u32 limbs, pad;
+    u64 q[kMaxLimbs], mu[kMaxLimbs];                    // mu = floor(2^64 / q)
+    u64 inv[kMaxLimbs][kMaxLimbs], inv_s[kMaxLimbs][kMaxLimbs];   // inv[i][j] = q_j^-1 mod q_i (j < i) + Shoup
+    u64 Q[kMaxLimbs], Qh[kMaxLimbs];                    // Q and floor(Q / 2), little-endian words
+};
+// sign / magnitude (L little-endian words) of the centred representative of x = a[i] (mod q_i)
+template <int L>
+HD void crtn_centered(const u64 (&a)[L], const CrtNConst &c, bool &neg, u64 (&mag)[L]) {
+    u64 v[L];
+#pragma unroll
+    for (int i = 0; i < L; i++) {
+        const u64 qi = c.q[i];
+        u64 t = a[i];
+#pragma unroll
+        for (int j = 0; j < i; j++) {
+            u64 vj = csub(v[j] - mulhi(v[j], c.mu[i]) * qi, qi);   // v_j mod q_i
+            u64 diff = t >= vj ? t - vj : t + qi - vj;
+            t = csub(shoup_lazy(diff, c.inv[i][j], c.inv_s[i][j], qi), qi);
+        }
+        v[i] = t;
+    }
+    u64 x[L];
+#pragma unroll
+    for (int i = 0; i < L; i++) x[i] = 0;
+    x[0] = v[L - 1];
+#pragma unroll
+    for (int i = L - 2; i >= 0; i--) {   // x = x * q_i + v_i ; x has L-1-i words before the step
+        const u64 qi = c.q[i];
+        u64 carry = v[i];
+#pragma unroll
+        for (int k = 0; k < L - 1 - i; k++) {
+            u64 hi, lo;
+            mul64x64(x[k], qi, hi, lo);
+            lo += carry;
+            hi += lo < carry ? 1 : 0;
+            x[k] = lo; carry = hi;
+        }
+        x[L - 1 - i] = carry;
+    }
+    bool gt = false, decided = false;   // x > floor(Q/2) ?
+#pragma unroll
+    for (int k = L - 1; k >= 0; k--) {
+        if (!decided && x[k] != c.Qh[k]) { gt = x[k] > c.Qh[k]; decided = true; }
+    }
+    if (gt) {
+        u64 borrow = 0;
+#pragma unroll
+        for (int k = 0; k < L; k++) {
+            u64 qk = c.Q[k], xk = x[k], d = qk - xk - borrow;
+            borrow = (qk < xk || (qk == xk && borrow)) ? 1 : 0;
+            mag[k] = d;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < L; k++) mag[k] = x[k];
+    }
+    neg = gt;
+}
+// (double) of a sign/magnitude integer of L words, ONE round-to-nearest-even (i128_to_double for any width)
+template <int L>
+HD double words_to_double(bool neg, const u64 (&m)[L]) {
+    u64 hi = 0, lo = 0;
+    int top = 0;
+    bool sticky = false;
+#pragma unroll
+    for (int i = L - 1; i >= 0; i--) {
+        if (hi == 0) {
+            if (m[i]) { hi = m[i]; top = i; lo = i > 0 ? m[i > 0 ? i - 1 : 0] : 0; }
+        } else if (i < top - 1) {
+            sticky = sticky || m[i] != 0;
+        }
+    }
+    double r;
+    if (top == 0) {
+        r = (double)hi;
+    } else {
+        int s = clz64(hi);
+        u64 win = s ? (hi << s) | (lo >> (64 - s)) : hi;
+        u64 rest = s ? (lo << s) : lo;
+        if (rest || sticky) win |= 1ull;
+        r = ldexp((double)win, 64 * top - s);
+    }
+    return neg ? -r : r;
+}
+
 }  // namespace shelfi
 
 // ==========================================================================================
@@ -601,7 +765,7 @@ struct BlobRuns {
     u64 off1[2 * kMaxLimbs];   // ciphertext 1 (absolute); ciphertext j >= 1: off1[r] + (j-1)*stride
     u64 stride;
     u32 runs;                  // 2L
-    u32 pad;
+    u32 n;                     // values per run (ring dimension)
 };
 HD u64 run_offset(const BlobRuns &br, u64 ct, u32 r) { return ct == 0 ? br.off0[r] : br.off1[r] + (ct - 1) * br.stride; }
 
@@ -695,6 +859,131 @@ HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc
     for (u32 i = tid; i < length; i += nthreads) out[i] = fmul(z[zsw(i)].re, dc.pow_p);
 }
 
+// ---- slot counts above one FFT tile (4096 complex values, 64 KiB) and ring dimensions above one NTT tile ----
+// FFTSpecialInv is decimation in frequency: after the df = log2(slots / 4096) outermost stages the array falls
+// apart into 2^df independent 4096-point blocks.  Block fb's loader applies those stages to the 2^df inputs
+// that share its tile-local index (same butterflies, same order as the reference => same doubles), the tile
+// runs the 12 inner stages, and the bit reversal sends tile position r to slot (r << df) | bitrev(fb).
+HD cplx encode_input(const double *x, u64 n_valid, u32 j) { return cplx{j < n_valid ? x[j] : 0.0, 0.0}; }
+template <int DF>
+HD cplx encode_head(const EncodeConst &ec, const double *x, u64 n_valid, u32 fb, u32 i) {
+    if (DF == 0) return encode_input(x, n_valid, i);
+    const cplx *__restrict__ twi = ec.tw_inv;
+    if (DF == 1) {
+        cplx a = encode_input(x, n_valid, i), b = encode_input(x, n_valid, i + kFftFast);
+        dif_bfly(a, b, twi[kFftFast - 1 + i]);
+        return fb ? b : a;
+    }
+    cplx a0 = encode_input(x, n_valid, i), a1 = encode_input(x, n_valid, i + kFftFast);
+    cplx a2 = encode_input(x, n_valid, i + 2 * kFftFast), a3 = encode_input(x, n_valid, i + 3 * kFftFast);
+    dif_bfly(a0, a2, twi[2 * kFftFast - 1 + i]);               // len = 16384: pairs (j, j + 8192)
+    dif_bfly(a1, a3, twi[2 * kFftFast - 1 + i + kFftFast]);
+    if (fb < 2) { dif_bfly(a0, a1, twi[kFftFast - 1 + i]); return fb ? a1 : a0; }   // len = 8192, first half
+    dif_bfly(a2, a3, twi[kFftFast - 1 + i]);                                        // second half
+    return (fb & 1u) ? a3 : a2;
+}
+template <int DF>
+HD void encode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid, u32 fb) {
+    const u32 tile_slots = ec.slots < kFftFast ? ec.slots : kFftFast;
+    for (u32 i = tid; i < tile_slots; i += nthreads) z[zsw(i)] = encode_head<DF>(ec, x, n_valid, fb, i);
+}
+// tile (finalized: bit-reversed within the tile, scaled, rounded) -> coefficients m[gap*slot], m[gap*slot + nh]
+template <int DF>
+HD void encode_emit_block(int tid, int nthreads, const cplx *z, const EncodeConst &ec, u32 fb, u32 nh, i64 *m) {
+    const i64 *zi = reinterpret_cast<const i64 *>(z);
+    const u32 tile_slots = ec.slots < kFftFast ? ec.slots : kFftFast;
+    const u32 fbr = DF ? bitrev32(fb, DF) : 0u;
+    for (u32 r = tid; r < tile_slots; r += nthreads) {
+        u32 idx = (((r << DF) | fbr)) * ec.gap;
+        m[idx] = zi[2 * zsw(r)];
+        m[idx + nh] = zi[2 * zsw(r) + 1];
+        for (u32 g = 1; g < ec.gap; g++) { m[idx + g] = 0; m[idx + nh + g] = 0; }
+    }
+}
+// m += e0 ; ve = (v, e1): the sampler as a streaming pass over one ciphertext's N coefficients
+HD void sample_add_group(u32 j4, u64 ct_index, const SamplerConst &sc, const u64 *cdf, i64 *m_e0, uint16_t *ve) {
+    int v[4], e0[4], e1[4];
+    sample_group(j4, ct_index, sc, cdf, v, e0, e1);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        u32 j = 4 * j4 + i;
+        m_e0[j] += (i64)e0[i];
+        ve[j] = (uint16_t)(((u32)v[i] & 0xFFu) | (((u32)e1[i] & 0xFFu) << 8));
+    }
+}
+
+// centred CRT value of coefficient j of a polynomial stored [L][n] -> double (and optionally its words)
+template <int L>
+HD double decode_value(const u64 *coeff, u32 n, u32 j, const Crt2Const &c2, const CrtNConst &cn, u64 *tap8) {
+    bool neg;
+    if (L <= 2) {
+        u64 hi, lo;
+        if (L == 1) {
+            u64 a = coeff[j], q = c2.q0;
+            neg = a > (q >> 1); hi = 0; lo = neg ? q - a : a;
+        } else {
+            crt2_centered(coeff[j], coeff[n + j], c2, neg, hi, lo);
+        }
+        if (tap8) {
+            u64 th = hi, tl = lo;
+            if (neg) { tl = ~lo + 1; th = ~hi + (tl == 0 ? 1 : 0); }
+            u64 ext = neg ? ~0ull : 0ull;
+            tap8[0] = tl; tap8[1] = th;
+            for (int k = 2; k < 8; k++) tap8[k] = ext;
+        }
+        return i128_to_double(neg, hi, lo);
+    } else {
+        u64 a[L], mag[L];
+#pragma unroll
+        for (int l = 0; l < L; l++) a[l] = coeff[(size_t)l * n + j];
+        crtn_centered<L>(a, cn, neg, mag);
+        if (tap8) {   // two's complement, sign-extended to 8 words
+            u64 carry = 1;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                u64 mk = k < L ? mag[k < L ? k : 0] : 0ull;
+                if (neg) { u64 t = ~mk + carry; carry = (carry && t == 0) ? 1 : 0; tap8[k] = t; }
+                else tap8[k] = mk;
+            }
+        }
+        return words_to_double<L>(neg, mag);
+    }
+}
+// FFTSpecial is decimation in time on the bit-reversed array: tile fb holds positions [fb*4096, (fb+1)*4096) of it,
+// i.e. slots (bitrev(p) << df) | bitrev(fb); the df outermost stages run in decode_tail.
+template <int DF>
+HD void decode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec, u32 fb, u32 n, const double *vals) {
+    const u32 nh = n >> 1;
+    const u32 tile_slots = ec.slots < kFftFast ? ec.slots : kFftFast;
+    const int tile_log = (int)ec.log_slots - DF;
+    const u32 fbr = DF ? bitrev32(fb, DF) : 0u;
+    for (u32 p = tid; p < tile_slots; p += nthreads) {
+        u32 idx = ((bitrev32(p, tile_log) << DF) | fbr) * ec.gap;
+        z[zsw(p)] = cplx{vals[idx], vals[idx + nh]};
+    }
+}
+// the df outermost FFTSpecial stages on the 2^df values sharing tile-local index i, then real parts * 2^-p
+template <int DF>
+HD void decode_tail(u32 i, const cplx *zs, const EncodeConst &ec, const DecodeConst &dc, double *out, u64 length) {
+    const cplx *__restrict__ twf = ec.tw_fwd;
+    cplx a[1 << DF];
+#pragma unroll
+    for (int k = 0; k < (1 << DF); k++) a[k] = zs[i + (u32)k * kFftFast];
+    if (DF == 1) {
+        dit_bfly(a[0], a[1], twf[kFftFast - 1 + i]);
+    } else if (DF == 2) {
+        dit_bfly(a[0], a[1], twf[kFftFast - 1 + i]);               // len = 8192 on both halves
+        dit_bfly(a[2], a[3], twf[kFftFast - 1 + i]);
+        dit_bfly(a[0], a[2], twf[2 * kFftFast - 1 + i]);           // len = 16384
+        dit_bfly(a[1], a[3], twf[2 * kFftFast - 1 + i + kFftFast]);
+    }
+#pragma unroll
+    for (int k = 0; k < (1 << DF); k++) {
+        u64 slot = i + (u64)k * kFftFast;
+        if (slot < length) out[slot] = fmul(a[k].re, dc.pow_p);
+    }
+}
+
 // ---- weighted sum: EvalMult(ct, const) + EvalAdd over learners (ckks.cpp:286-297) ----
 struct acc128 { u64 lo, hi; };
 HD void mac128(acc128 &a, u64 x, u64 c) {
@@ -716,19 +1005,19 @@ HD u64 load_unaligned(const u64 *image, u64 byte_off) {
     if (sh == 0) return a;
     return (a >> sh) | (image[w + 1] << (64u - sh));
 }
-// word `widx` of the image, overlapping the run that starts at byte a0 and holds kN values
-HD void pack_word(u64 *image, u64 a0, u64 widx, const u64 *run) {
+// word `widx` of the image, overlapping the run that starts at byte a0 and holds n values
+HD void pack_word(u64 *image, u64 a0, u64 widx, const u64 *run, u32 n) {
     i64 o = (i64)(widx * 8) - (i64)a0;                 // run byte offset of the word's first byte: -7 .. 8N-1
     i64 i = o >= 0 ? (o >> 3) : -1;
     u32 t = (u32)(o - i * 8);                          // 0..7
     u64 lo = i >= 0 ? run[i] : 0ull;
-    u64 hi = (t && i + 1 < (i64)kN) ? run[i + 1] : 0ull;
+    u64 hi = (t && i + 1 < (i64)n) ? run[i + 1] : 0ull;
     u64 val = t ? (lo >> (8 * t)) | (hi << (64 - 8 * t)) : lo;
-    if (o >= 0 && o + 8 <= (i64)kN * 8) { image[widx] = val; return; }
+    if (o >= 0 && o + 8 <= (i64)n * 8) { image[widx] = val; return; }
     unsigned char *bytes = reinterpret_cast<unsigned char *>(image + widx);
     for (int b = 0; b < 8; b++) {
         i64 ob = o + b;
-        if (ob >= 0 && ob < (i64)kN * 8) bytes[b] = (unsigned char)(val >> (8 * b));
+        if (ob >= 0 && ob < (i64)n * 8) bytes[b] = (unsigned char)(val >> (8 * b));
     }
 }
 

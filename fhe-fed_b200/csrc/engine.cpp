@@ -85,11 +85,12 @@ struct shelfi_ckks {
     RingConst rc{};
     EncodeConst ec{};
     Crt2Const crt{};
+    CrtNConst crtn{};
     uint64_t gauss_cdf[32] = {0};
     // device-resident parameters
     DeviceBuffer d_tw, d_itw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
     // scratch
-    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_out;
+    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_out, s_vals, s_zs, s_rows;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
     cudaStream_t copy_stream = nullptr;
@@ -181,27 +182,31 @@ int upload(shelfi_ckks *h, DeviceBuffer *buf, const void *src, size_t bytes) {
 }
 
 int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
-    if (p.ring_dim != (uint32_t)kN || p.cyclotomic_order != 2u * kN)
+    uint32_t logn = 0;
+    while ((1u << logn) < p.ring_dim) logn++;
+    if (p.ring_dim != (1u << logn) || logn < (uint32_t)kLogN || logn > (uint32_t)(kLogN + kMaxLogBlocks) ||
+        p.cyclotomic_order != 2u * p.ring_dim)
         return fail(h, SHELFI_ERR_UNSUPPORTED, "ring dimension " + std::to_string(p.ring_dim) +
-                                                   " not supported: kernels are specialised for N = 8192");
-    if (p.batch_size == 0 || (p.batch_size & (p.batch_size - 1)) || p.batch_size > (uint32_t)kN / 2)
+                                                   " not supported: the kernels cover N = 8192, 16384, 32768");
+    const uint32_t N = p.ring_dim;
+    if (p.batch_size == 0 || (p.batch_size & (p.batch_size - 1)) || p.batch_size > N / 2)
         return fail(h, SHELFI_ERR_UNSUPPORTED, "context batch size must be a power of two <= N/2");
     if (p.limbs < 1 || p.limbs > (uint32_t)kMaxLimbs) return fail(h, SHELFI_ERR_UNSUPPORTED, "unsupported tower count");
     RingConst rc{};
-    rc.n = kN; rc.logn = kLogN; rc.limbs = p.limbs; rc.slots = p.batch_size;
-    std::vector<tw_t> tw_all((size_t)p.limbs * kN), itw_all((size_t)p.limbs * kN), tw, itw;
+    rc.n = N; rc.logn = logn; rc.log_blocks = logn - kLogN; rc.limbs = p.limbs; rc.slots = p.batch_size;
+    std::vector<tw_t> tw_all((size_t)p.limbs * N), itw_all((size_t)p.limbs * N), tw, itw;
     for (uint32_t l = 0; l < p.limbs; l++) {
-        std::string e = make_limb_const(p.modulus[l], p.root[l], &rc.limb[l], &tw, &itw);
+        std::string e = make_limb_const(p.modulus[l], p.root[l], logn, &rc.limb[l], &tw, &itw);
         if (!e.empty()) return fail(h, SHELFI_ERR_UNSUPPORTED, "limb " + std::to_string(l) + ": " + e);
-        std::memcpy(&tw_all[(size_t)l * kN], tw.data(), sizeof(tw_t) * kN);
-        std::memcpy(&itw_all[(size_t)l * kN], itw.data(), sizeof(tw_t) * kN);
+        std::memcpy(&tw_all[(size_t)l * N], tw.data(), sizeof(tw_t) * N);
+        std::memcpy(&itw_all[(size_t)l * N], itw.data(), sizeof(tw_t) * N);
     }
     int rcode;
     if ((rcode = upload(h, &h->d_tw, tw_all.data(), tw_all.size() * sizeof(tw_t)))) return rcode;
     if ((rcode = upload(h, &h->d_itw, itw_all.data(), itw_all.size() * sizeof(tw_t)))) return rcode;
     for (uint32_t l = 0; l < p.limbs; l++) {
-        rc.limb[l].tw = h->d_tw.as<tw_t>() + (size_t)l * kN;
-        rc.limb[l].itw = h->d_itw.as<tw_t>() + (size_t)l * kN;
+        rc.limb[l].tw = h->d_tw.as<tw_t>() + (size_t)l * N;
+        rc.limb[l].itw = h->d_itw.as<tw_t>() + (size_t)l * N;
     }
     const uint32_t slots = p.batch_size;
     std::vector<cplx> t_inv, t_fwd;
@@ -209,7 +214,7 @@ int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
     if ((rcode = upload(h, &h->d_fft_inv, t_inv.data(), slots * sizeof(cplx)))) return rcode;
     if ((rcode = upload(h, &h->d_fft_fwd, t_fwd.data(), slots * sizeof(cplx)))) return rcode;
     EncodeConst ec{};
-    ec.slots = slots; ec.gap = (kN / 2) / slots; ec.batch = h->batch;
+    ec.slots = slots; ec.gap = (N / 2) / slots; ec.batch = h->batch;
     ec.log_slots = 0;
     while ((1u << ec.log_slots) < slots) ec.log_slots++;
     ec.pow_p = (double)p.modulus[p.limbs - 1];
@@ -219,19 +224,20 @@ int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
     Crt2Const crt = make_crt2(p.modulus[0], p.limbs >= 2 ? p.modulus[1] : 0);
     build_gauss_cdf((double)p.sigma, h->gauss_cdf);
     h->ctx = p; h->rc = rc; h->ec = ec; h->crt = crt;
+    h->crtn = make_crtn(p.modulus, p.limbs);
     h->have_cc = true;
     return 0;
 }
 
 // key polynomial rows -> {value, Shoup companion} pairs on the device
 int upload_key_poly(shelfi_ckks *h, DeviceBuffer *buf, const uint64_t *rows) {
-    const uint32_t L = h->ctx.limbs;
-    std::vector<tw_t> packed((size_t)L * kN);
+    const uint32_t L = h->ctx.limbs, N = h->ctx.ring_dim;
+    std::vector<tw_t> packed((size_t)L * N);
     for (uint32_t l = 0; l < L; l++)
-        for (uint32_t j = 0; j < (uint32_t)kN; j++) {
-            uint64_t v = rows[(size_t)l * kN + j];
+        for (uint32_t j = 0; j < N; j++) {
+            uint64_t v = rows[(size_t)l * N + j];
             if (v >= h->ctx.modulus[l]) return fail(h, SHELFI_ERR_FORMAT, "key coefficient not reduced");
-            packed[(size_t)l * kN + j] = tw_t{v, nt::shoup(v, h->ctx.modulus[l])};
+            packed[(size_t)l * N + j] = tw_t{v, nt::shoup(v, h->ctx.modulus[l])};
         }
     return upload(h, buf, packed.data(), packed.size() * sizeof(tw_t));
 }
@@ -242,9 +248,11 @@ bool same_ring(const wire::ContextParams &a, const wire::ContextParams &b) {
            !std::memcmp(a.root, b.root, sizeof(uint64_t) * a.limbs);
 }
 
-BlobRuns to_runs(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t L) {
+BlobRuns to_runs(const shelfi_ckks *h, const uint64_t *run0, const uint64_t *run1, uint64_t stride) {
+    const uint32_t L = h->ctx.limbs;
     BlobRuns br{};
     br.runs = 2 * L;
+    br.n = h->ctx.ring_dim;
     for (uint32_t r = 0; r < 2 * L; r++) { br.off0[r] = run0[r]; br.off1[r] = run1[r]; }
     br.stride = stride;
     return br;
@@ -267,16 +275,36 @@ uint64_t fresh_seed() {
 int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uint64_t n, uint64_t ct_index0,
                        uint64_t *const *d_ct, cudaStream_t s) {
     uint64_t n_ct = (n + h->batch - 1) / h->batch;
-    if (n_ct * k > 0x7fffffffull / (2 * kMaxLimbs)) return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
+    const uint64_t N = h->ctx.ring_dim;
+    if (n_ct * k > (0x7fffffffull / (2 * kMaxLimbs)) >> h->rc.log_blocks)
+        return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
     SamplerConst sc{};
     sc.ct_index0 = ct_index0;
     std::memcpy(sc.gauss_cdf, h->gauss_cdf, sizeof sc.gauss_cdf);
+    if (h->rc.log_blocks > 0) {
+        // ring dimension above one tile: encode per FFT block, sampler pass, then one CTA per (ciphertext, limb, tile);
+        // a single learner already gives thousands of CTAs, so learners go one after another
+        CU(h->s_m.reserve((size_t)n_ct * N * sizeof(int64_t)));
+        CU(h->s_ve.reserve((size_t)n_ct * N * sizeof(uint16_t)));
+        for (uint32_t i = 0; i < k; i++) {
+            sc.seed = h->seeded ? h->seed : fresh_seed();
+            timed(h, kKEncodeSample, s, [&] {
+                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s);
+            });
+            timed(h, kKEncrypt, s, [&] {
+                launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(),
+                               reinterpret_cast<u64 *>(d_ct[i]), (u32)n_ct, s);
+            });
+        }
+        CU(cudaGetLastError());
+        return 0;
+    }
     for (uint32_t base = 0; base < k; base += kMaxEncryptBatch) {
         EncryptBatch eb{};
         eb.k = std::min<uint32_t>(kMaxEncryptBatch, k - base);
         eb.n_ct = (u32)n_ct;
-        CU(h->s_m.reserve((size_t)eb.k * n_ct * kN * sizeof(int64_t)));
-        CU(h->s_ve.reserve((size_t)eb.k * n_ct * kN * sizeof(uint16_t)));
+        CU(h->s_m.reserve((size_t)eb.k * n_ct * N * sizeof(int64_t)));
+        CU(h->s_ve.reserve((size_t)eb.k * n_ct * N * sizeof(uint16_t)));
         for (uint32_t i = 0; i < eb.k; i++) {
             eb.x[i] = d_x[base + i];
             eb.ct[i] = reinterpret_cast<u64 *>(d_ct[base + i]);
@@ -294,17 +322,29 @@ int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_ind
     return encrypt_dense_many(h, &d_x, 1, n, ct_index0, &d_ct, s);
 }
 
+bool general_decode(const shelfi_ckks *h) { return h->rc.log_blocks > 0 || h->ctx.limbs > 2; }
+
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
                   cudaStream_t s) {
-    if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "decode implements the 1- and 2-limb CRT only");
-    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * kN * sizeof(uint64_t)));
+    const uint64_t N = h->ctx.ring_dim;
+    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * N * sizeof(uint64_t)));
     timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(h->rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
     DecodeConst dc{};
     dc.crt = h->crt;
     double p = (double)h->ctx.plaintext_modulus;
     dc.pre = std::pow(sf, -1) * std::pow(2, p);   // [PAL] Decode: scale to 2^p before the FFT, back after it
     dc.pow_p = std::pow(2, -p);
-    timed(h, kKDecode, s, [&] { launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s); });
+    if (!general_decode(h)) {
+        timed(h, kKDecode, s, [&] { launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s); });
+    } else {
+        CU(h->s_vals.reserve(n_ct * N * sizeof(double)));
+        if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(n_ct * (size_t)h->ec.slots * sizeof(cplx)));
+        timed(h, kKDecode, s, [&] {
+            launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, h->s_vals.as<double>(), nullptr, nullptr,
+                       nullptr, s);
+            launch_decode_fft(h->rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s);
+        });
+    }
     CU(cudaGetLastError());
     return 0;
 }
@@ -345,7 +385,7 @@ int encrypt_host(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint
         return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
     }
     cudaStream_t s = h->stream;
-    const uint64_t ct_words = 2ull * h->ctx.limbs * kN;
+    const uint64_t ct_words = 2ull * h->ctx.limbs * h->ctx.ring_dim;
     auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
 #define CUB(call)                                                              \
     do {                                                                       \
@@ -358,7 +398,7 @@ int encrypt_host(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint
     CUB(cudaMemcpyAsync(h->s_x.p, x, n * sizeof(double), cudaMemcpyHostToDevice, s));
     if ((rcode = encrypt_dense(h, h->s_x.as<double>(), n, 0, h->s_dense.as<u64>(), s))) return bail(rcode);
     timed(h, kKPack, s, [&] {
-        launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), h->s_dense.as<u64>(),
+        launch_pack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride), h->s_dense.as<u64>(),
                     h->s_image.as<u64>(), n_ct, s);
     });
     CUB(cudaGetLastError());
@@ -403,7 +443,7 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *lens,
     }
     auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
     cudaStream_t s = h->stream, cs = h->copy_stream;
-    const uint64_t ct_words = 2ull * L * kN;
+    const uint64_t ct_words = 2ull * L * h->ctx.ring_dim;
     size_t max_image = 0;
     for (uint32_t i = 0; i < k; i++) max_image = std::max(max_image, image_bytes(lens[i]));
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
@@ -421,14 +461,14 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *lens,
         LimbScalars cs_l{};
         for (uint32_t l = 0; l < L; l++) cs_l.c[l] = nt::signed_mod(sc, h->ctx.modulus[l]);
         timed(h, kKUnpackScaleAcc, s, [&] {
-            launch_unpack_scale_accumulate(h->rc, to_runs(maps[i].run0, maps[i].run1, maps[i].stride, L),
+            launch_unpack_scale_accumulate(h->rc, to_runs(h, maps[i].run0, maps[i].run1, maps[i].stride),
                                            img[b]->as<u64>(), cs_l, i == 0 ? 1u : 0u, h->s_dense.as<u64>(), n_ct, s);
         });
         CUB(cudaGetLastError());
         CUB(cudaEventRecord(h->ev_done[b], s));
     }
     timed(h, kKPack, s, [&] {
-        launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, L), h->s_dense.as<u64>(), h->s_image.as<u64>(), n_ct, s);
+        launch_pack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride), h->s_dense.as<u64>(), h->s_image.as<u64>(), n_ct, s);
     });
     CUB(cudaGetLastError());
     CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
@@ -451,14 +491,14 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *blob, uint64_t len, uint64_t n, 
     if (n == 0 || n > n_ct * batch || n + batch <= n_ct * batch)
         return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
     const uint32_t L = h->ctx.limbs;
-    const uint64_t ct_words = 2ull * L * kN;
+    const uint64_t ct_words = 2ull * L * h->ctx.ring_dim;
     cudaStream_t s = h->stream;
     CU(h->s_image.reserve(image_bytes(len)));
     CU(h->s_dense.reserve(n_ct * ct_words * 8));
     CU(h->s_out.reserve(n * sizeof(double)));
     CU(cudaMemcpyAsync(h->s_image.p, blob, len, cudaMemcpyHostToDevice, s));
     timed(h, kKUnpack, s, [&] {
-        launch_unpack(h->rc, to_runs(map.run0, map.run1, map.stride, L), h->s_image.as<u64>(), h->s_dense.as<u64>(), n_ct, s);
+        launch_unpack(h->rc, to_runs(h, map.run0, map.run1, map.stride), h->s_image.as<u64>(), h->s_dense.as<u64>(), n_ct, s);
     });
     CU(cudaGetLastError());
     // ciphertexts usually share one scaling factor; split the launch where they do not
@@ -507,7 +547,8 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         cudaDeviceSynchronize();
         h->prof.release();
         free_params(h);
-        for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_out})
+        for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_out,
+                                &h->s_vals, &h->s_zs, &h->s_rows})
             b->release();
         for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_copy[i]); cudaEventDestroy(h->ev_done[i]); }
         cudaStreamDestroy(h->stream);
@@ -540,7 +581,7 @@ int shelfi_load_crypto_params_from_memory(shelfi_ckks *h, const uint8_t *cc, siz
     e = !h->have_cc ? std::string("no context") : pk ? wire::parse_public_key(pk, pk_len, &key) : std::string("file missing");
     if (e.empty() && !same_ring(key.ctx, h->ctx)) e = "key belongs to different parameters";
     if (e.empty()) {
-        size_t words = (size_t)h->ctx.limbs * kN;
+        size_t words = (size_t)h->ctx.limbs * h->ctx.ring_dim;
         if ((rcode = upload_key_poly(h, &h->d_pk_b, key.polys.data()))) return rcode;
         if ((rcode = upload_key_poly(h, &h->d_pk_a, key.polys.data() + words))) return rcode;
         h->key_tag = key.tag;
@@ -576,35 +617,44 @@ int shelfi_load_crypto_params(shelfi_ckks *h) {
 }
 
 int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h) {
-    // ckks.cpp:25-59: genCryptoContextCKKS(multDepth = 1, scaleFactorBits, batchSize), Enable(ENCRYPTION | SHE),
+    return shelfi_gen_crypto_context_and_keygen_ex(h, 1, 0);   // ckks.cpp:26: multDepth = 1, automatic ring dimension
+}
+
+int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth, uint32_t ring_dim) {
+    // ckks.cpp:25-59: genCryptoContextCKKS(multDepth, scaleFactorBits, batchSize), Enable(ENCRYPTION | SHE),
     // KeyGen, three SerializeToFile calls; the object's own context/keys stay untouched.
     if (!h) return 0;
     std::lock_guard<std::mutex> lock(h->mu);
     if (ensure_cuda(h)) return 0;
     const uint32_t bits = h->scale_bits, batch = h->batch;
     if (bits < 14 || bits > 59) { fail(h, SHELFI_ERR_ARG, "scaleFactorBits must be in [14, 59]"); return 0; }
-    const uint32_t N = nt::select_ring_dim(bits);
-    if (N != (uint32_t)kN) { fail(h, SHELFI_ERR_UNSUPPORTED, "parameter set needs a ring dimension other than 8192"); return 0; }
+    if (mult_depth < 1 || mult_depth + 1 > (uint32_t)kMaxLimbs) { fail(h, SHELFI_ERR_ARG, "multDepth must be in [1, 7]"); return 0; }
+    const uint32_t N = ring_dim ? ring_dim : nt::select_ring_dim(bits, mult_depth);
+    if (N != 8192 && N != 16384 && N != 32768) {
+        fail(h, SHELFI_ERR_UNSUPPORTED, "parameter set needs ring dimension " + std::to_string(N) + "; supported: 8192, 16384, 32768");
+        return 0;
+    }
     if (batch == 0 || (batch & (batch - 1)) || batch > N / 2) {
         fail(h, SHELFI_ERR_ARG, "batchSize must be a power of two <= N/2");
         return 0;
     }
     wire::ContextParams p;
-    p.ring_dim = N; p.cyclotomic_order = 2 * N; p.limbs = 2;
-    p.modulus[1] = nt::first_prime(bits, 2 * N);                            // scaling prime = level-0 scaling factor
-    p.modulus[0] = nt::previous_prime(nt::first_prime(60, 2 * N), 2 * N);   // 60-bit first modulus
-    for (int l = 0; l < 2; l++) p.root[l] = nt::min_primitive_root(2 * N, p.modulus[l]);
+    p.ring_dim = N; p.cyclotomic_order = 2 * N;
+    const int L = nt::modulus_chain(bits, mult_depth, N, p.modulus);   // q_last = scaling prime, q_0 60 bits
+    p.limbs = (uint32_t)L;
+    for (int l = 0; l < L; l++) p.root[l] = nt::min_primitive_root(2 * N, p.modulus[l]);
     wire::set_big_modulus(&p);
     p.plaintext_modulus = bits; p.batch_size = batch;
     p.sigma = 3.19f; p.assurance = 9.0f; p.hermite = 1.006f;
     // relinWindow, depth, maxDepth, [extra word of newer PALISADE], mode OPTIMIZED, HEStd_128_classic,
     // EXACTRESCALE, HYBRID, dnum
+    const uint32_t dnum = nt::num_large_digits(mult_depth);
     const char *variant = std::getenv("SHELFI_WIRE_VARIANT");
     if (variant && std::atoi(variant) == 8) {
-        const uint32_t v[8] = {0, 1, 2, 1, 0, 2, 1, 2};
+        const uint32_t v[8] = {0, 1, 2, 1, 0, 2, 1, dnum};
         std::memcpy(p.rlwe_ints, v, sizeof v); p.rlwe_int_count = 8;
     } else {
-        const uint32_t v[9] = {0, 1, 2, 0, 1, 0, 2, 1, 2};
+        const uint32_t v[9] = {0, 1, 2, 0, 1, 0, 2, 1, dnum};
         std::memcpy(p.rlwe_ints, v, sizeof v); p.rlwe_int_count = 9;
     }
     p.enabled_features = 5;  // ENCRYPTION | SHE (ckks.cpp:32-33)
@@ -616,37 +666,39 @@ int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h) {
     // run on the device through a scratch handle so this object's loaded state is left alone.
     shelfi_ckks tmp;
     tmp.device = h->device; tmp.batch = batch; tmp.scale_bits = bits;
-    auto cleanup = [&]() { free_params(&tmp); tmp.s_dense.release(); if (tmp.stream) cudaStreamDestroy(tmp.stream);
+    auto cleanup = [&]() { free_params(&tmp); tmp.s_dense.release(); tmp.s_rows.release();
+                           if (tmp.stream) cudaStreamDestroy(tmp.stream);
                            if (tmp.copy_stream) cudaStreamDestroy(tmp.copy_stream);
                            for (int i = 0; i < 2; i++) { if (tmp.ev_copy[i]) cudaEventDestroy(tmp.ev_copy[i]);
                                                          if (tmp.ev_done[i]) cudaEventDestroy(tmp.ev_done[i]); } };
     if (ensure_cuda(&tmp) || install_context(&tmp, p)) { h->err = tmp.err; cleanup(); return 0; }
     const uint64_t seed = h->seeded ? h->seed : fresh_seed();
-    std::vector<uint64_t> rows(4 * (size_t)N);  // s limb0, s limb1, e limb0, e limb1
+    const size_t LN = (size_t)L * N;
+    std::vector<uint64_t> rows(2 * LN);  // s limbs 0..L-1, then e limbs 0..L-1
     u32 o[4];
     for (uint32_t j = 0; j < N; j++) {
         philox4x32_10(seed, j >> 2, 0, 0, kStreamKeyS, o);
         int sv = ternary_from_u32(o[j & 3]);
         philox4x32_10(seed, j, 0, 0, kStreamKeyE, o);
         int ev = gauss_from_u64(tmp.gauss_cdf, ((uint64_t)o[1] << 32) | o[0]);
-        for (int l = 0; l < 2; l++) {
+        for (int l = 0; l < L; l++) {
             rows[(size_t)l * N + j] = nt::signed_mod(sv, p.modulus[l]);
-            rows[(size_t)(2 + l) * N + j] = nt::signed_mod(ev, p.modulus[l]);
+            rows[LN + (size_t)l * N + j] = nt::signed_mod(ev, p.modulus[l]);
         }
     }
-    bool ok = tmp.s_dense.reserve(rows.size() * 8) == cudaSuccess &&
-              cudaMemcpy(tmp.s_dense.p, rows.data(), rows.size() * 8, cudaMemcpyHostToDevice) == cudaSuccess;
+    bool ok = tmp.s_rows.reserve(rows.size() * 8) == cudaSuccess && tmp.s_dense.reserve(rows.size() * 8) == cudaSuccess &&
+              cudaMemcpy(tmp.s_rows.p, rows.data(), rows.size() * 8, cudaMemcpyHostToDevice) == cudaSuccess;
     if (ok) {
-        launch_ntt_forward(tmp.rc, tmp.s_dense.as<u64>(), 4, tmp.stream);
+        launch_ntt_forward(tmp.rc, tmp.s_rows.as<u64>(), tmp.s_dense.as<u64>(), 2 * (u32)L, tmp.stream);
         ok = cudaStreamSynchronize(tmp.stream) == cudaSuccess &&
              cudaMemcpy(rows.data(), tmp.s_dense.p, rows.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess;
     }
     if (!ok) { fail(h, SHELFI_ERR_CUDA, "key generation transforms failed"); cleanup(); return 0; }
     wire::KeyFile pub, priv;
     pub.ctx = p; priv.ctx = p;
-    pub.polys.assign(4 * (size_t)N, 0);
-    priv.polys.assign(rows.begin(), rows.begin() + 2 * (size_t)N);
-    for (int l = 0; l < 2; l++) {
+    pub.polys.assign(2 * LN, 0);
+    priv.polys.assign(rows.begin(), rows.begin() + LN);
+    for (int l = 0; l < L; l++) {
         const uint64_t q = p.modulus[l];
         const int qbits = 64 - __builtin_clzll(q);
         for (uint32_t j = 0; j < N; j++) {
@@ -656,8 +708,8 @@ int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h) {
                 philox4x32_10(seed, j, (u32)l, tries++, kStreamKeyA, o);
                 a = (((uint64_t)o[1] << 32) | o[0]) >> (64 - qbits);
             } while (a >= q);
-            uint64_t sv = rows[(size_t)l * N + j], ev = rows[(size_t)(2 + l) * N + j];
-            pub.polys[(size_t)(2 + l) * N + j] = a;
+            uint64_t sv = rows[(size_t)l * N + j], ev = rows[LN + (size_t)l * N + j];
+            pub.polys[LN + (size_t)l * N + j] = a;
             pub.polys[(size_t)l * N + j] = nt::sub_mod(ev, nt::mul_mod(a, sv, q), q);
         }
     }
@@ -726,7 +778,7 @@ int shelfi_key_tag(const shelfi_ckks *h, char out[33]) {
     return 0;
 }
 uint64_t shelfi_num_ciphertexts(const shelfi_ckks *h, uint64_t n) { return h && h->batch ? (n + h->batch - 1) / h->batch : 0; }
-uint64_t shelfi_ciphertext_words(const shelfi_ckks *h) { return h && h->have_cc ? 2ull * h->ctx.limbs * kN : 0; }
+uint64_t shelfi_ciphertext_words(const shelfi_ckks *h) { return h && h->have_cc ? 2ull * h->ctx.limbs * h->ctx.ring_dim : 0; }
 uint64_t shelfi_blob_size(const shelfi_ckks *h, uint64_t n_ct) {
     return h && h->have_cc && n_ct ? wire::ciphertext_blob_size(h->ctx, n_ct) : 0;
 }
@@ -835,7 +887,7 @@ int shelfi_pack_device(shelfi_ckks *h, const uint64_t *d_dense, uint64_t n_ct, u
     if (rcode) return rcode;
     std::vector<wire::CiphertextMeta> meta(1);
     wire::BlobPlan plan = wire::plan_ciphertext_blob(h->ctx, n_ct, meta);
-    launch_pack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), reinterpret_cast<const u64 *>(d_dense),
+    launch_pack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride), reinterpret_cast<const u64 *>(d_dense),
                 reinterpret_cast<u64 *>(d_image), n_ct, static_cast<cudaStream_t>(stream));
     CU(cudaGetLastError());
     return 0;
@@ -847,7 +899,7 @@ int shelfi_unpack_device(shelfi_ckks *h, const uint8_t *d_image, uint64_t n_ct, 
     if (rcode) return rcode;
     std::vector<wire::CiphertextMeta> meta(1);
     wire::BlobPlan plan = wire::plan_ciphertext_blob(h->ctx, n_ct, meta);
-    launch_unpack(h->rc, to_runs(plan.run0, plan.run1, plan.stride, h->ctx.limbs), reinterpret_cast<const u64 *>(d_image),
+    launch_unpack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride), reinterpret_cast<const u64 *>(d_image),
                   reinterpret_cast<u64 *>(d_dense), n_ct, static_cast<cudaStream_t>(stream));
     CU(cudaGetLastError());
     return 0;
@@ -858,9 +910,15 @@ int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, v
     std::lock_guard<std::mutex> lock(h->mu);
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
-    timed(h, kKNttForward, static_cast<cudaStream_t>(stream), [&] {
-        launch_ntt_forward(h->rc, reinterpret_cast<u64 *>(d_rows), rows, static_cast<cudaStream_t>(stream));
-    });
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const u64 *src = reinterpret_cast<const u64 *>(d_rows);
+    if (h->rc.log_blocks > 0) {   // a tile's loader reads its whole row: transform from a copy
+        size_t bytes = (size_t)rows * h->ctx.ring_dim * sizeof(uint64_t);
+        CU(h->s_rows.reserve(bytes));
+        CU(cudaMemcpyAsync(h->s_rows.p, d_rows, bytes, cudaMemcpyDeviceToDevice, s));
+        src = h->s_rows.as<u64>();
+    }
+    timed(h, kKNttForward, s, [&] { launch_ntt_forward(h->rc, src, reinterpret_cast<u64 *>(d_rows), rows, s); });
     CU(cudaGetLastError());
     return 0;
 }
@@ -892,13 +950,34 @@ int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t
     std::lock_guard<std::mutex> lock(h->mu);
     int rcode = check_stage(h, false, true);
     if (rcode) return rcode;
-    if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "decode implements the 1- and 2-limb CRT only");
+    if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "128-bit tap covers 1 and 2 limbs; use shelfi_decrypt_words_device");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * kN * sizeof(uint64_t)));
+    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * h->ctx.ring_dim * sizeof(uint64_t)));
     launch_decrypt_intt(h->rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
     DecodeConst dc{};
     dc.crt = h->crt;
-    launch_crt_only(h->rc, dc, h->s_coeff.as<u64>(), (u32)n_ct, reinterpret_cast<i64 *>(d_hi), reinterpret_cast<u64 *>(d_lo), s);
+    if (!general_decode(h))
+        launch_crt_only(h->rc, dc, h->s_coeff.as<u64>(), (u32)n_ct, reinterpret_cast<i64 *>(d_hi), reinterpret_cast<u64 *>(d_lo), s);
+    else
+        launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, nullptr, nullptr, reinterpret_cast<i64 *>(d_hi),
+                   reinterpret_cast<u64 *>(d_lo), s);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint64_t *d_words, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!d_ct || !d_words || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * h->ctx.ring_dim * sizeof(uint64_t)));
+    launch_decrypt_intt(h->rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
+    DecodeConst dc{};
+    dc.crt = h->crt;
+    launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, nullptr, reinterpret_cast<u64 *>(d_words), nullptr,
+               nullptr, s);
     CU(cudaGetLastError());
     return 0;
 }

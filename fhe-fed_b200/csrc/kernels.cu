@@ -13,36 +13,67 @@ namespace shelfi {
 // ------------------------------------------------------------------------------------------
 // standalone forward / inverse NTT (parity taps, keygen, and the "NTT HBM GB/s" metric)
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_kernel(const __grid_constant__ RingConst rc, u64 *data) {
+// One CTA per 8192-point tile: a polynomial of ring dimension 2^(13+D) is 2^D tiles (ckks_core.cuh).  For D > 0 the
+// forward transform reads all tiles of its row (HeadLoad) and so must not run in place: `in` != `out`.
+template <int D>
+__global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_kernel(const __grid_constant__ RingConst rc, const u64 *in,
+                                                                     u64 *out) {
     extern __shared__ __align__(16) u64 sm[];
     const int tid = threadIdx.x;
-    const LimbConst lc = rc.limb[blockIdx.x % rc.limbs];
-    u64 *row = data + (size_t)blockIdx.x * kN;
-    fwd_phase_a(tid, sm, lc, LoadGlobal{row});
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u32 row = blockIdx.x >> D;
+    const u32 hb = D ? head_bits(D, blk) : 1u;
+    const LimbConst lc = rc.limb[row % rc.limbs];
+    const u64 *src = in + ((size_t)row << (kLogN + D));
+    u64 *dst = out + ((size_t)row << (kLogN + D)) + (size_t)blk * kN;
+    fwd_phase_a(tid, sm, lc, hb, HeadLoad<D, LoadGlobal>{LoadGlobal{src}, &lc, blk});
     __syncthreads();
-    fwd_phase_mid<7>(tid, sm, lc);
+    fwd_phase_mid<7>(tid, sm, lc, hb);
     __syncthreads();
-    fwd_phase_mid<4>(tid, sm, lc);
+    fwd_phase_mid<4>(tid, sm, lc, hb);
     __syncthreads();
-    fwd_phase_mid<1>(tid, sm, lc);
+    fwd_phase_mid<1>(tid, sm, lc, hb);
     __syncthreads();
-    fwd_phase_e(tid, sm, lc, StoreFullReducePair{row, &lc});
+    fwd_phase_e(tid, sm, lc, hb, StoreFullReducePair{dst, &lc});
 }
 
+// inverse: the 13 inner stages per tile in place; for D > 0 the results stay lazy (< 2q) and intt_tail_kernel
+// applies the D outermost stages and N^-1 as a streaming pass
+template <int D, class Load>
+__device__ __forceinline__ void intt_tile(int tid, u64 *sm, const LimbConst &lc, u32 hb, Load ld, u64 *dst) {
+    inv_phase_e(tid, sm, lc, hb, ld);
+    __syncthreads();
+    inv_phase_mid<1>(tid, sm, lc, hb);
+    __syncthreads();
+    inv_phase_mid<4>(tid, sm, lc, hb);
+    __syncthreads();
+    inv_phase_mid<7>(tid, sm, lc, hb);
+    __syncthreads();
+    if (D == 0) inv_phase_last(tid, sm, lc, StoreGlobal{dst});
+    else inv_phase_last_lazy(tid, sm, lc, hb, StoreGlobal{dst});
+}
+template <int D>
 __global__ void __launch_bounds__(kNttThreads, 3) ntt_inverse_kernel(const __grid_constant__ RingConst rc, u64 *data) {
     extern __shared__ __align__(16) u64 sm[];
-    const int tid = threadIdx.x;
-    const LimbConst lc = rc.limb[blockIdx.x % rc.limbs];
-    u64 *row = data + (size_t)blockIdx.x * kN;
-    inv_phase_e(tid, sm, lc, LoadPairGlobal{row});
-    __syncthreads();
-    inv_phase_mid<1>(tid, sm, lc);
-    __syncthreads();
-    inv_phase_mid<4>(tid, sm, lc);
-    __syncthreads();
-    inv_phase_mid<7>(tid, sm, lc);
-    __syncthreads();
-    inv_phase_last(tid, sm, lc, StoreGlobal{row});
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u32 row = blockIdx.x >> D;
+    const LimbConst lc = rc.limb[row % rc.limbs];
+    u64 *tile_ptr = data + (size_t)blockIdx.x * kN;   // tiles of a row are contiguous
+    intt_tile<D>(threadIdx.x, sm, lc, D ? head_bits(D, blk) : 1u, LoadPairGlobal{tile_ptr}, tile_ptr);
+}
+constexpr int kTailThreads = 256;
+template <int D>
+__global__ void __launch_bounds__(kTailThreads) intt_tail_kernel(const __grid_constant__ RingConst rc, u64 *data) {
+    const u32 row = blockIdx.y;
+    const u32 i = blockIdx.x * kTailThreads + threadIdx.x;      // tile-local index
+    const LimbConst &lc = rc.limb[row % rc.limbs];
+    u64 *p = data + ((size_t)row << (kLogN + D)) + i;
+    u64 a[1 << D];
+#pragma unroll
+    for (int k = 0; k < (1 << D); k++) a[k] = p[(size_t)k * kN];
+    inv_tail<D>(a, lc);
+#pragma unroll
+    for (int k = 0; k < (1 << D); k++) p[(size_t)k * kN] = a[k];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -83,43 +114,95 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
     }
 }
 
+// Ring dimensions / slot counts above one tile: one CTA per (ciphertext, FFT block), message coefficients only;
+// sample_add_kernel then adds e0 and writes (v, e1) as a streaming pass (the sampler draws per group of four
+// consecutive coefficients, the FFT blocks own strided ones).
+template <int DF>
+__global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_constant__ EncodeConst ec, u32 n_ring,
+                                                                   const double *x, u64 n, i64 *m) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    cplx *z = reinterpret_cast<cplx *>(smraw);
+    const int tid = threadIdx.x;
+    const u32 fb = DF ? blockIdx.x & ((1u << DF) - 1u) : 0u;
+    const u64 ct = blockIdx.x >> DF;
+    const u64 first = ct * ec.batch;
+    const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
+    encode_load_block<DF>(tid, kFftThreads, z, ec, x + first, n_valid, fb);
+    __syncthreads();
+    EncodeConst et = ec;                       // the tile's own geometry for the bit reversal
+    if (ec.slots >= kFftFast) {
+        et.slots = kFftFast; et.log_slots = 12;
+        fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<6>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<3>(tid, z, ec.tw_inv); __syncthreads();
+        fft_inv_pass8<0>(tid, z, ec.tw_inv); __syncthreads();
+    } else {
+        for (u32 len = ec.slots; len >= 2; len >>= 1) {
+            fft_inv_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_inv);
+            __syncthreads();
+        }
+    }
+    encode_finalize(tid, kFftThreads, z, et);
+    __syncthreads();
+    encode_emit_block<DF>(tid, kFftThreads, z, ec, fb, n_ring >> 1, m + ct * (u64)n_ring);
+}
+constexpr int kSampleThreads = 256;
+__global__ void __launch_bounds__(kSampleThreads) sample_add_kernel(const __grid_constant__ SamplerConst sc, u32 n_ring,
+                                                                    i64 *m_e0, uint16_t *ve) {
+    __shared__ u64 cdf[32];
+    if (threadIdx.x < 32) cdf[threadIdx.x] = sc.gauss_cdf[threadIdx.x];
+    __syncthreads();
+    const u64 ct = blockIdx.y;
+    const u32 j4 = blockIdx.x * kSampleThreads + threadIdx.x;
+    if (j4 < (n_ring >> 2))
+        sample_add_group(j4, sc.ct_index0 + ct, sc, cdf, m_e0 + ct * (u64)n_ring, ve + ct * (u64)n_ring);
+}
+
 // ------------------------------------------------------------------------------------------
 // encrypt: per (ciphertext, limb) CTA, three forward NTTs through one shared-memory tile.
 //   NTT(v)      -> v^ parked in the c1 row (re-read by the same thread, L2-resident)
 //   NTT(m + e0) -> c0 = b*v^ + .     NTT(e1) -> c1 = a*v^ + .  (overwrites the parked row)
 // ------------------------------------------------------------------------------------------
 template <class Load, class Store>
-__device__ __forceinline__ void ntt_forward_tile(int tid, u64 *sm, const LimbConst &lc, Load ld, Store st) {
-    fwd_phase_a(tid, sm, lc, ld);
+__device__ __forceinline__ void ntt_forward_tile(int tid, u64 *sm, const LimbConst &lc, u32 hb, Load ld, Store st) {
+    fwd_phase_a(tid, sm, lc, hb, ld);
     __syncthreads();
-    fwd_phase_mid<7>(tid, sm, lc);
+    fwd_phase_mid<7>(tid, sm, lc, hb);
     __syncthreads();
-    fwd_phase_mid<4>(tid, sm, lc);
+    fwd_phase_mid<4>(tid, sm, lc, hb);
     __syncthreads();
-    fwd_phase_mid<1>(tid, sm, lc);
+    fwd_phase_mid<1>(tid, sm, lc, hb);
     __syncthreads();
-    fwd_phase_e(tid, sm, lc, st);
+    fwd_phase_e(tid, sm, lc, hb, st);
 }
 
+template <int D>
 __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_constant__ RingConst rc, const i64 *m_e0,
                                                                  const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                                                                  u64 *ct_out) {
     extern __shared__ __align__(16) u64 sm[];
     const int tid = threadIdx.x;
     const u32 L = rc.limbs;
-    const u32 l = blockIdx.x % L;
-    const u64 ct = blockIdx.x / L;
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u32 hb = D ? head_bits(D, blk) : 1u;
+    const u32 poly = blockIdx.x >> D;          // ct * L + l
+    const u32 l = poly % L;
+    const u64 ct = poly / L;
+    const u64 n = (u64)kN << D;
     const LimbConst lc = rc.limb[l];
-    const uint16_t *ve_row = ve + ct * (u64)kN;
-    const i64 *m_row = m_e0 + ct * (u64)kN;
-    u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
-    u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
-    ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
-                     StoreLazyPair{c1});
+    const uint16_t *ve_row = ve + ct * n;
+    const i64 *m_row = m_e0 + ct * n;
+    const size_t tile_off = (size_t)blk * kN;
+    u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * n + tile_off;
+    u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * n + tile_off;
+    const tw_t *kb = pk_b + (size_t)l * n + tile_off, *ka = pk_a + (size_t)l * n + tile_off;
+    ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve_row, lc.q}, &lc, blk}, StoreLazyPair{c1});
     __syncthreads();
-    ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
+    ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadSigned>{LoadSigned{m_row, &lc}, &lc, blk},
+                     StoreMulAdd{kb, c1, c0, &lc});
     __syncthreads();
-    ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
+    ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadGaussHi>{LoadGaussHi{ve_row, lc.q}, &lc, blk},
+                     StoreMulAdd{ka, c1, c1, &lc});
 }
 
 // Fused encrypt: one CTA per ciphertext does encode + sampling (FFT tile), parks m+e0 / (v,e1) in global scratch
@@ -170,12 +253,12 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
         const LimbConst lc = rc.limb[l];
         u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
         u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
-        ntt_forward_tile(tid, sm, lc, LoadTernary{ve_row, lc.q},
+        ntt_forward_tile(tid, sm, lc, 1u, LoadTernary{ve_row, lc.q},
                          StoreLazyPair{c1});
         __syncthreads();
-        ntt_forward_tile(tid, sm, lc, LoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
+        ntt_forward_tile(tid, sm, lc, 1u, LoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
         __syncthreads();
-        ntt_forward_tile(tid, sm, lc, LoadGaussHi{ve_row, lc.q}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
+        ntt_forward_tile(tid, sm, lc, 1u, LoadGaussHi{ve_row, lc.q}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
         __syncthreads();
     }
 }
@@ -183,25 +266,22 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
 // ------------------------------------------------------------------------------------------
 // decrypt stage 1: t = c0 + c1*s per limb, inverse NTT to coefficients
 // ------------------------------------------------------------------------------------------
+template <int D>
 __global__ void __launch_bounds__(kNttThreads, 3) decrypt_intt_kernel(const __grid_constant__ RingConst rc,
                                                                       const u64 *ct_in, const tw_t *sk, u64 *coeff) {
     extern __shared__ __align__(16) u64 sm[];
-    const int tid = threadIdx.x;
     const u32 L = rc.limbs;
-    const u32 l = blockIdx.x % L;
-    const u64 ct = blockIdx.x / L;
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u32 poly = blockIdx.x >> D;
+    const u32 l = poly % L;
+    const u64 ct = poly / L;
+    const u64 n = (u64)kN << D;
     const LimbConst lc = rc.limb[l];
-    const u64 *c0 = ct_in + ((ct * 2 + 0) * L + l) * (u64)kN;
-    const u64 *c1 = ct_in + ((ct * 2 + 1) * L + l) * (u64)kN;
-    inv_phase_e(tid, sm, lc, LoadDecryptPair{c0, c1, sk + (size_t)l * kN, lc.q});
-    __syncthreads();
-    inv_phase_mid<1>(tid, sm, lc);
-    __syncthreads();
-    inv_phase_mid<4>(tid, sm, lc);
-    __syncthreads();
-    inv_phase_mid<7>(tid, sm, lc);
-    __syncthreads();
-    inv_phase_last(tid, sm, lc, StoreGlobal{coeff + (ct * L + l) * (u64)kN});
+    const size_t tile_off = (size_t)blk * kN;
+    const u64 *c0 = ct_in + ((ct * 2 + 0) * L + l) * n + tile_off;
+    const u64 *c1 = ct_in + ((ct * 2 + 1) * L + l) * n + tile_off;
+    intt_tile<D>(threadIdx.x, sm, lc, D ? head_bits(D, blk) : 1u,
+                 LoadDecryptPair{c0, c1, sk + (size_t)l * n + tile_off, lc.q}, coeff + (ct * L + l) * n + tile_off);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -236,6 +316,72 @@ __global__ void __launch_bounds__(kFftThreads) decode_kernel(const __grid_consta
     decode_store(tid, kFftThreads, z, dc, out + first, length);
 }
 
+// General decode (any ring dimension, limb count, slot count): crt_kernel turns the L residues of every coefficient
+// into the centred integer's double (x scalingFactor^-1 * 2^p), decode_fft_kernel runs FFTSpecial per 4096-slot
+// tile, decode_tail_kernel finishes slot counts above one tile.
+constexpr int kCrtThreads = 128;
+template <int L>
+__global__ void __launch_bounds__(kCrtThreads) crt_kernel(const __grid_constant__ DecodeConst dc,
+                                                           const __grid_constant__ CrtNConst cn, u32 n_ring,
+                                                           const u64 *coeff, double *vals, u64 *tap8, i64 *tap_hi,
+                                                           u64 *tap_lo) {
+    const u64 ct = blockIdx.y;
+    const u32 j = blockIdx.x * kCrtThreads + threadIdx.x;
+    if (j >= n_ring) return;
+    u64 t[8];
+    const bool tap = tap8 || tap_hi;
+    double v = decode_value<L>(coeff + ct * L * (u64)n_ring, n_ring, j, dc.crt, cn, tap ? t : nullptr);
+    if (vals) vals[ct * (u64)n_ring + j] = fmul(v, dc.pre);
+    if (tap8) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) tap8[(ct * (u64)n_ring + j) * 8 + k] = t[k];
+    }
+    if (tap_hi) { tap_hi[ct * (u64)n_ring + j] = (i64)t[1]; tap_lo[ct * (u64)n_ring + j] = t[0]; }
+}
+template <int DF>
+__global__ void __launch_bounds__(kFftThreads) decode_fft_kernel(const __grid_constant__ EncodeConst ec,
+                                                                 const __grid_constant__ DecodeConst dc, u32 n_ring,
+                                                                 const double *vals, cplx *zs, double *out, u64 n) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    cplx *z = reinterpret_cast<cplx *>(smraw);
+    const int tid = threadIdx.x;
+    const u32 fb = DF ? blockIdx.x & ((1u << DF) - 1u) : 0u;
+    const u64 ct = blockIdx.x >> DF;
+    decode_load_block<DF>(tid, kFftThreads, z, ec, fb, n_ring, vals + ct * (u64)n_ring);
+    __syncthreads();
+    if (ec.slots >= kFftFast) {
+        fft_fwd_pass8<0>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<3>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<6>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<9>(tid, z, ec.tw_fwd); __syncthreads();
+    } else {
+        for (u32 len = 2; len <= ec.slots; len <<= 1) {
+            fft_fwd_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_fwd);
+            __syncthreads();
+        }
+    }
+    if (DF == 0) {
+        u64 first = ct * ec.batch;
+        if (first >= n) return;
+        u64 length = n - first < ec.batch ? n - first : ec.batch;
+        decode_store(tid, kFftThreads, z, dc, out + first, length);
+    } else {
+        cplx *dst = zs + ct * (u64)ec.slots + (u64)fb * kFftFast;
+        for (u32 i = tid; i < kFftFast; i += kFftThreads) dst[i] = z[zsw(i)];
+    }
+}
+template <int DF>
+__global__ void __launch_bounds__(kTailThreads) decode_tail_kernel(const __grid_constant__ EncodeConst ec,
+                                                                   const __grid_constant__ DecodeConst dc,
+                                                                   const cplx *zs, double *out, u64 n) {
+    const u64 ct = blockIdx.y;
+    const u32 i = blockIdx.x * kTailThreads + threadIdx.x;
+    u64 first = ct * ec.batch;
+    if (first >= n) return;
+    u64 length = n - first < ec.batch ? n - first : ec.batch;
+    decode_tail<DF>(i, zs + ct * (u64)ec.slots, ec, dc, out + first, length);
+}
+
 // ------------------------------------------------------------------------------------------
 // weighted sum over learners: pure streaming, 128-bit lazy accumulation, one reduction per coefficient
 // ------------------------------------------------------------------------------------------
@@ -252,7 +398,7 @@ __device__ __forceinline__ ulonglong2 ld_stream(const ulonglong2 *p) {
 __global__ void __launch_bounds__(kWavgThreads) weighted_sum_kernel(const __grid_constant__ RingConst rc,
                                                                     const __grid_constant__ WavgArgs wa, u64 *out) {
     const u64 base = (u64)blockIdx.x * kWavgElemsPerCta;
-    const u32 l = (u32)((base / kN) % rc.limbs);
+    const u32 l = (u32)((base >> rc.logn) % rc.limbs);
     const LimbConst lc = rc.limb[l];
     acc128 acc[kWavgPairsPerThread][2];
 #pragma unroll
@@ -298,8 +444,8 @@ __global__ void __launch_bounds__(kPackThreads) unpack_kernel(const __grid_const
     const u64 ct = run / br.runs;
     const u32 r = (u32)(run % br.runs);
     const u64 a0 = run_offset(br, ct, r);
-    u64 *dst = dense + run * (u64)kN;
-    for (u32 i = blockIdx.y * kPackThreads + threadIdx.x; i < (u32)kN; i += gridDim.y * kPackThreads)
+    u64 *dst = dense + run * (u64)br.n;
+    for (u32 i = blockIdx.y * kPackThreads + threadIdx.x; i < br.n; i += gridDim.y * kPackThreads)
         dst[i] = load_unaligned(image, a0 + 8ull * i);
 }
 
@@ -309,10 +455,10 @@ __global__ void __launch_bounds__(kPackThreads) pack_kernel(const __grid_constan
     const u64 ct = run / br.runs;
     const u32 r = (u32)(run % br.runs);
     const u64 a0 = run_offset(br, ct, r);
-    const u64 w0 = a0 >> 3, w1 = (a0 + 8ull * kN - 1) >> 3;
-    const u64 *src = dense + run * (u64)kN;
+    const u64 w0 = a0 >> 3, w1 = (a0 + 8ull * br.n - 1) >> 3;
+    const u64 *src = dense + run * (u64)br.n;
     for (u64 w = w0 + blockIdx.y * kPackThreads + threadIdx.x; w <= w1; w += (u64)gridDim.y * kPackThreads)
-        pack_word(image, a0, w, src);
+        pack_word(image, a0, w, src, br.n);
 }
 
 // acc = (first ? 0 : acc) + c * unpack(image) mod q: one learner folded into the resident accumulator
@@ -328,8 +474,8 @@ __global__ void __launch_bounds__(kPackThreads) unpack_scale_accumulate_kernel(c
     const LimbConst lc = rc.limb[l];
     const u64 a0 = run_offset(br, ct, r);
     const u64 c = cs.c[l];
-    u64 *dst = acc + run * (u64)kN;
-    for (u32 i = blockIdx.y * kPackThreads + threadIdx.x; i < (u32)kN; i += gridDim.y * kPackThreads) {
+    u64 *dst = acc + run * (u64)br.n;
+    for (u32 i = blockIdx.y * kPackThreads + threadIdx.x; i < br.n; i += gridDim.y * kPackThreads) {
         acc128 a{first ? 0ull : dst[i], 0ull};
         mac128(a, load_unaligned(image, a0 + 8ull * i), c);
         dst[i] = reduce128(a, lc);
@@ -339,55 +485,116 @@ __global__ void __launch_bounds__(kPackThreads) unpack_scale_accumulate_kernel(c
 // ------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------
+// D (tiles per polynomial = 1 << D) and DF (FFT tiles per ciphertext = 1 << DF) are compile-time in the kernels
+#define DISPATCH_D(d, ...)                                   \
+    switch (d) {                                             \
+        case 0: { constexpr int D = 0; __VA_ARGS__; break; } \
+        case 1: { constexpr int D = 1; __VA_ARGS__; break; } \
+        default: { constexpr int D = 2; __VA_ARGS__; break; } \
+    }
+#define DISPATCH_L(l, ...)                                   \
+    switch (l) {                                             \
+        case 1: { constexpr int L = 1; __VA_ARGS__; break; } \
+        case 2: { constexpr int L = 2; __VA_ARGS__; break; } \
+        case 3: { constexpr int L = 3; __VA_ARGS__; break; } \
+        case 4: { constexpr int L = 4; __VA_ARGS__; break; } \
+        case 5: { constexpr int L = 5; __VA_ARGS__; break; } \
+        case 6: { constexpr int L = 6; __VA_ARGS__; break; } \
+        case 7: { constexpr int L = 7; __VA_ARGS__; break; } \
+        default: { constexpr int L = 8; __VA_ARGS__; break; } \
+    }
+static u32 fft_log_blocks(const EncodeConst &ec) { return ec.log_slots > 12 ? ec.log_slots - 12 : 0; }
+static size_t fft_smem(const EncodeConst &ec) { return (ec.slots < kFftFast ? ec.slots : kFftFast) * sizeof(cplx); }
+
 cudaError_t kernels_init() {
     cudaError_t e;
 #define OPT_IN(k, bytes)                                                                      \
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes));  \
     if (e != cudaSuccess) return e;
-    OPT_IN(ntt_forward_kernel, NTT_SMEM_BYTES)
-    OPT_IN(ntt_inverse_kernel, NTT_SMEM_BYTES)
-    OPT_IN(encrypt_kernel, NTT_SMEM_BYTES)
+#define OPT_IN_D(k, bytes) OPT_IN(k<0>, bytes) OPT_IN(k<1>, bytes) OPT_IN(k<2>, bytes)
+    OPT_IN_D(ntt_forward_kernel, NTT_SMEM_BYTES)
+    OPT_IN_D(ntt_inverse_kernel, NTT_SMEM_BYTES)
+    OPT_IN_D(encrypt_kernel, NTT_SMEM_BYTES)
+    OPT_IN_D(decrypt_intt_kernel, NTT_SMEM_BYTES)
     OPT_IN(encrypt_fused_kernel, NTT_SMEM_BYTES)
-    OPT_IN(decrypt_intt_kernel, NTT_SMEM_BYTES)
-    OPT_IN(encode_kernel<true>, (kN / 2) * sizeof(cplx))
-    OPT_IN(encode_kernel<false>, (kN / 2) * sizeof(cplx))
-    OPT_IN(decode_kernel, (kN / 2) * sizeof(cplx))
+    OPT_IN(encode_kernel<true>, kFftFast * sizeof(cplx))
+    OPT_IN(encode_kernel<false>, kFftFast * sizeof(cplx))
+    OPT_IN(decode_kernel, kFftFast * sizeof(cplx))
+    OPT_IN_D(encode_block_kernel, kFftFast * sizeof(cplx))
+    OPT_IN_D(decode_fft_kernel, kFftFast * sizeof(cplx))
+#undef OPT_IN_D
 #undef OPT_IN
     return cudaSuccess;
 }
 
-void launch_ntt_forward(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s) {
-    if (rows) ntt_forward_kernel<<<rows, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, data);
+void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s) {
+    if (!rows) return;
+    DISPATCH_D(rc.log_blocks, ntt_forward_kernel<D><<<rows << D, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, in, out))
 }
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s) {
-    if (rows) ntt_inverse_kernel<<<rows, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, data);
+    if (!rows) return;
+    DISPATCH_D(rc.log_blocks, ntt_inverse_kernel<D><<<rows << D, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, data))
+    if (rc.log_blocks == 1) intt_tail_kernel<1><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, data);
+    if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, data);
 }
-void launch_encode_sample(const RingConst &, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
+void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
                           u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s) {
-    if (n_ct) encode_kernel<true><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m_e0, ve);
+    if (!n_ct) return;
+    if (rc.log_blocks == 0) {
+        encode_kernel<true><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m_e0, ve);
+        return;
+    }
+    launch_encode_only(rc, ec, x, n, n_ct, m_e0, s);
+    sample_add_kernel<<<dim3((rc.n / 4 + kSampleThreads - 1) / kSampleThreads, n_ct), kSampleThreads, 0, s>>>(sc, rc.n,
+                                                                                                           m_e0, ve);
 }
-void launch_encode_only(const RingConst &, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
+void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
                         cudaStream_t s) {
-    SamplerConst sc{};
-    if (n_ct) encode_kernel<false><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m, nullptr);
+    if (!n_ct) return;
+    if (rc.log_blocks == 0) {
+        SamplerConst sc{};
+        encode_kernel<false><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m, nullptr);
+        return;
+    }
+    DISPATCH_D(fft_log_blocks(ec), encode_block_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, rc.n, x, n, m))
 }
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s) {
-    if (n_ct) encrypt_kernel<<<n_ct * rc.limbs, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, m_e0, ve, pk_b, pk_a, ct);
+    if (!n_ct) return;
+    DISPATCH_D(rc.log_blocks, encrypt_kernel<D><<<(n_ct * rc.limbs) << D, kNttThreads, NTT_SMEM_BYTES, s>>>(
+                                  rc, m_e0, ve, pk_b, pk_a, ct))
 }
 void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const EncryptBatch &eb,
                           u64 n, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s) {
-    if (eb.n_ct && eb.k)
+    if (eb.n_ct && eb.k)   // ring dimension 8192 only (one tile per polynomial); callers check rc.log_blocks == 0
         encrypt_fused_kernel<<<eb.n_ct * eb.k, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, sc, eb, n, m_e0, ve, pk_b, pk_a);
 }
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s) {
-    if (n_ct) decrypt_intt_kernel<<<n_ct * rc.limbs, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ct, sk, coeff);
+    if (!n_ct) return;
+    const u32 rows = n_ct * rc.limbs;
+    DISPATCH_D(rc.log_blocks, decrypt_intt_kernel<D><<<rows << D, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ct, sk, coeff))
+    if (rc.log_blocks == 1) intt_tail_kernel<1><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, coeff);
+    if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, coeff);
 }
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
                    double *out, u64 n, cudaStream_t s) {
-    if (n_ct)
+    if (n_ct)   // ring dimension 8192, at most two limbs: CRT and FFT in one kernel
         decode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, dc, rc.limbs, coeff, out, n, nullptr,
                                                                         nullptr);
+}
+void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,
+                double *vals, u64 *tap8, i64 *tap_hi, u64 *tap_lo, cudaStream_t s) {
+    if (!n_ct) return;
+    dim3 grid((rc.n + kCrtThreads - 1) / kCrtThreads, n_ct);
+    DISPATCH_L(rc.limbs, crt_kernel<L><<<grid, kCrtThreads, 0, s>>>(dc, cn, rc.n, coeff, vals, tap8, tap_hi, tap_lo))
+}
+void launch_decode_fft(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const double *vals, cplx *zs,
+                       u32 n_ct, double *out, u64 n, cudaStream_t s) {
+    if (!n_ct) return;
+    const u32 df = fft_log_blocks(ec);
+    DISPATCH_D(df, decode_fft_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, dc, rc.n, vals, zs, out, n))
+    if (df == 1) decode_tail_kernel<1><<<dim3(kFftFast / kTailThreads, n_ct), kTailThreads, 0, s>>>(ec, dc, zs, out, n);
+    if (df == 2) decode_tail_kernel<2><<<dim3(kFftFast / kTailThreads, n_ct), kTailThreads, 0, s>>>(ec, dc, zs, out, n);
 }
 void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coeff, u32 n_ct, i64 *hi, u64 *lo,
                      cudaStream_t s) {
@@ -397,10 +604,10 @@ void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coef
         decode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, dc, rc.limbs, coeff, nullptr, 0, hi, lo);
 }
 void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 n_ct, cudaStream_t s) {
-    u64 elems = n_ct * 2 * rc.limbs * (u64)kN;
+    u64 elems = n_ct * 2 * rc.limbs * (u64)rc.n;
     if (elems) weighted_sum_kernel<<<(unsigned)(elems / kWavgElemsPerCta), kWavgThreads, 0, s>>>(rc, wa, out);
 }
-static dim3 run_grid(const BlobRuns &br, u64 n_ct) { return dim3((unsigned)(n_ct * br.runs), 4); }
+static dim3 run_grid(const BlobRuns &br, u64 n_ct) { return dim3((unsigned)(n_ct * br.runs), br.n / 2048); }
 void launch_unpack(const RingConst &, const BlobRuns &br, const u64 *image, u64 *dense, u64 n_ct, cudaStream_t s) {
     if (n_ct) unpack_kernel<<<run_grid(br, n_ct), kPackThreads, 0, s>>>(br, image, dense);
 }

@@ -8,8 +8,9 @@ namespace shelfi {
 
 cudaError_t kernels_init();  // opt-in shared-memory sizes; call once per device
 
-// in-place transforms of `rows` limb polynomials laid out [row][N], limb = row % L
-void launch_ntt_forward(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
+// transforms of `rows` limb polynomials laid out [row][N], limb = row % L.  Forward: in == out is allowed only for
+// ring dimension 8192 (one tile per polynomial); inverse is in place.
+void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s);
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
 
 // encode + sample: x[n] -> m_e0[n_ct][N] (m + e0, signed) and ve[n_ct][N] (v in the low byte, e1 in the high byte)
@@ -26,6 +27,13 @@ void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
                    double *out, u64 n, cudaStream_t s);
+// general decode: CRT of any limb count -> vals[n_ct][N] doubles (x dc.pre), optional taps of the centred integer
+// (tap8: 8 two's-complement words per coefficient; tap_hi/tap_lo: its low 128 bits)
+void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,
+                double *vals, u64 *tap8, i64 *tap_hi, u64 *tap_lo, cudaStream_t s);
+// ... then FFTSpecial per 4096-slot tile (+ tail pass for more slots; zs = scratch of n_ct * slots complex)
+void launch_decode_fft(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const double *vals, cplx *zs,
+                       u32 n_ct, double *out, u64 n, cudaStream_t s);
 // debug/parity taps of the two halves above
 void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
                         cudaStream_t s);

@@ -24,7 +24,12 @@ bool is_prime(uint64_t n);
 uint64_t first_prime(uint32_t bits, uint32_t m);      // smallest prime >= 2^bits congruent 1 mod m
 uint64_t previous_prime(uint64_t q, uint32_t m);      // next smaller prime congruent 1 mod m
 uint64_t min_primitive_root(uint32_t m, uint64_t q);  // numerically smallest primitive m-th root of unity (m = 2^k)
-uint32_t select_ring_dim(uint32_t scale_bits);        // HEStd_128_classic table, multDepth 1, HYBRID dnum 2
+uint64_t next_prime(uint64_t q, uint32_t m);          // next larger prime congruent 1 mod m
+uint32_t num_large_digits(uint32_t mult_depth);       // PALISADE's default dnum for the HYBRID key switch
+// HEStd_128_classic table, HYBRID key switching; ckks.cpp:26 passes mult_depth = 1
+uint32_t select_ring_dim(uint32_t scale_bits, uint32_t mult_depth = 1);
+// q[0..mult_depth] of genCryptoContextCKKS(multDepth, scaleFactorBits) under EXACTRESCALE; returns the limb count
+int modulus_chain(uint32_t scale_bits, uint32_t mult_depth, uint32_t ring_dim, uint64_t *q);
 
 }  // namespace nt
 }  // namespace shelfi

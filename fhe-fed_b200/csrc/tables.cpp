@@ -32,27 +32,30 @@ void build_gauss_cdf(double sigma, uint64_t cdf[32]) {
     cdf[31] = UINT64_MAX;
 }
 
-std::string make_limb_const(uint64_t q, uint64_t psi, LimbConst *lc, std::vector<tw_t> *tw, std::vector<tw_t> *itw) {
+std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *lc, std::vector<tw_t> *tw,
+                            std::vector<tw_t> *itw) {
+    if (logn < (uint32_t)kLogN || logn > (uint32_t)(kLogN + kMaxLogBlocks)) return "ring dimension must be 8192, 16384 or 32768";
+    const uint32_t n = 1u << logn, d = logn - kLogN;
     if (q >= ((uint64_t)1 << 60) || q < 64 || !(q & 1)) return "limb modulus must be an odd value in [64, 2^60)";
-    if ((q - 1) % (2 * kN)) return "limb modulus is not 1 mod 2N";
-    if (nt::pow_mod(psi, kN, q) != q - 1) return "root of unity is not a primitive 2N-th root";
+    if ((q - 1) % (2 * (uint64_t)n)) return "limb modulus is not 1 mod 2N";
+    if (nt::pow_mod(psi, n, q) != q - 1) return "root of unity is not a primitive 2N-th root";
     std::memset(lc, 0, sizeof *lc);
     lc->q = q;
     lc->q2 = 2 * q;
     lc->nq = (uint64_t)0 - q;
     lc->mu = (uint64_t)((((u128)1) << 64) / q);
     uint64_t ipsi = nt::inv_mod(psi, q);
-    tw->assign(kN, tw_t{0, 0});
-    itw->assign(kN, tw_t{0, 0});
+    tw->assign(n, tw_t{0, 0});
+    itw->assign(n, tw_t{0, 0});
     uint64_t p = 1, ip = 1;
-    for (uint32_t i = 0; i < (uint32_t)kN; i++) {  // PALISADE's reverse tables: index bitrev(i) holds psi^i
-        uint32_t r = bit_reverse(i, kLogN);
+    for (uint32_t i = 0; i < n; i++) {  // PALISADE's reverse tables: index bitrev(i) holds psi^i
+        uint32_t r = bit_reverse(i, (int)logn);
         (*tw)[r] = tw_t{p, nt::shoup(p, q)};
         (*itw)[r] = tw_t{ip, nt::shoup(ip, q)};
         p = nt::mul_mod(p, psi, q);
         ip = nt::mul_mod(ip, ipsi, q);
     }
-    lc->ninv = nt::inv_mod(kN % q, q);
+    lc->ninv = nt::inv_mod(n % q, q);
     lc->ninv_s = nt::shoup(lc->ninv, q);
     lc->wninv = nt::mul_mod((*itw)[1].w, lc->ninv, q);
     lc->wninv_s = nt::shoup(lc->wninv, q);
@@ -69,10 +72,11 @@ std::string make_limb_const(uint64_t q, uint64_t psi, LimbConst *lc, std::vector
     } else {
         lc->rmode = 2; lc->rshift = 0;                    // anything else: Barrett quotient by mulhi
     }
-    // forward NTT: every Harvey stage adds 2q to the bound; reduce at the end of pass p-1 when pass p would overflow
+    // forward NTT: every Harvey stage adds 2q to the bound; reduce at the end of pass p-1 when pass p would overflow.
+    // The tile's loader has already applied d stages (HeadLoad): inputs are below (1 + 2d) q.
     const uint64_t H = UINT64_MAX / q;
     const int stages[5] = {3, 3, 3, 3, 1};
-    uint64_t B = 1;
+    uint64_t B = 1 + 2 * (uint64_t)d;
     lc->fwd_mask = 0;
     for (int pass = 0; pass < 5; pass++) {
         if (B + 2 * stages[pass] > H) {
@@ -106,6 +110,32 @@ void make_fft_tables(uint32_t M, uint32_t slots, std::vector<cplx> *inv, std::ve
             (*fwd)[lenh - 1 + j] = ksi[(rot[j] % lenq) * gap];
         }
     }
+}
+
+CrtNConst make_crtn(const uint64_t *q, uint32_t limbs) {
+    CrtNConst c;
+    std::memset(&c, 0, sizeof c);
+    c.limbs = limbs;
+    uint64_t Q[kMaxLimbs + 1] = {1};
+    for (uint32_t i = 0; i < limbs; i++) {
+        c.q[i] = q[i];
+        c.mu[i] = (uint64_t)((((u128)1) << 64) / q[i]);
+        for (uint32_t j = 0; j < i; j++) {
+            c.inv[i][j] = nt::inv_mod(q[j] % q[i], q[i]);
+            c.inv_s[i][j] = nt::shoup(c.inv[i][j], q[i]);
+        }
+        u128 carry = 0;
+        for (int k = 0; k <= kMaxLimbs; k++) {
+            u128 cur = (u128)Q[k] * q[i] + carry;
+            Q[k] = (uint64_t)cur;
+            carry = cur >> 64;
+        }
+    }
+    for (int k = 0; k < kMaxLimbs; k++) {
+        c.Q[k] = Q[k];
+        c.Qh[k] = (Q[k] >> 1) | (Q[k + 1] << 63);
+    }
+    return c;
 }
 
 Crt2Const make_crt2(uint64_t q0, uint64_t q1) {

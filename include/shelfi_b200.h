@@ -65,6 +65,12 @@ int shelfi_load_crypto_params_from_memory(shelfi_ckks *h, const uint8_t *cc, siz
 /* CKKS::genCryptoContextAndKeyGen (src/ckks.cpp:25-59): multDepth 1, writes the three files into
  * cryptodir, does not load them.  Returns 1 on success, 0 on failure — the reference's convention. */
 int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h);
+/* Extension: the same with PALISADE's multDepth and ring dimension free (the reference hard-codes multDepth = 1,
+ * src/ckks.cpp:26, and lets PALISADE pick the ring dimension).  mult_depth in [1, 7] gives mult_depth + 1 limbs
+ * (60-bit q_0, then the EXACTRESCALE chain around 2^scaleFactorBits); ring_dim 0 = PALISADE's choice from the
+ * HEStd_128_classic table, else 8192 / 16384 / 32768.  (mult_depth 3, 52 bits) -> N = 16384, L = 4 and
+ * (7, 52) -> N = 32768, L = 8 are BASELINE configs 3 and 4.  Returns 1 / 0 like the reference call. */
+int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth, uint32_t ring_dim);
 
 /* Encryption randomness comes from the OS by default.  A fixed seed makes the device sampler
  * reproducible (tests, parity against the CPU oracle); never use it for real data. */
@@ -137,6 +143,9 @@ int shelfi_encode_device(shelfi_ckks *h, const double *d_x, uint64_t n, int64_t 
 /* Decrypt up to the centred CRT integer of every coefficient (two's complement hi/lo words) */
 int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, int64_t *d_hi, uint64_t *d_lo,
                                   void *stream);
+/* the same tap for any limb count: d_words[n_ct][N][8], little-endian two's complement (512 bits) of the centred
+ * CRT integer of every coefficient */
+int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint64_t *d_words, void *stream);
 
 /* ---- per-kernel timing (benchmarks): CUDA events on the launching stream around every launch ----
  * kernel ids: 0 encode+sample, 1 encrypt, 2 weighted sum, 3 decrypt inverse NTT, 4 decode, 5 pack, 6 unpack,

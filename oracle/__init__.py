@@ -54,6 +54,12 @@ def lib():
         "orc_load_from_memory": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p,
                                            C.c_size_t]),
         "orc_gen_context_and_keys": (C.c_int, [C.c_uint32, C.c_uint32, C.c_char_p, C.c_uint64, C.c_int]),
+        "orc_gen_context_and_keys_ex": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_char_p,
+                                                  C.c_uint64, C.c_int]),
+        "orc_select_ring_dim_ex": (C.c_uint32, [C.c_uint32, C.c_uint32]),
+        "orc_num_large_digits": (C.c_uint32, [C.c_uint32]),
+        "orc_modulus_chain": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
+        "orc_decrypt_ct_words": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]),
         "orc_last_error": (C.c_char_p, [C.c_void_p]),
         "orc_ring_dim": (C.c_uint32, [C.c_void_p]),
         "orc_num_limbs": (C.c_uint32, [C.c_void_p]),
@@ -127,9 +133,11 @@ class Oracle:
     def loadCryptoParams(self) -> int:
         return lib().orc_load_crypto_params(self._h)
 
-    def genCryptoContextAndKeyGen(self, seed: int = 1, nine_int: bool = False) -> int:
-        return lib().orc_gen_context_and_keys(self.batchSize, self.scaleFactorBits, self.cryptodir.encode(), seed,
-                                              int(nine_int))
+    def genCryptoContextAndKeyGen(self, seed: int = 1, nine_int: bool = False, mult_depth: int = 1,
+                                  ring_dim: int = 0) -> int:
+        """mult_depth / ring_dim are extensions (ckks.cpp:26 hard-codes multDepth = 1, ring_dim automatic)."""
+        return lib().orc_gen_context_and_keys_ex(self.batchSize, self.scaleFactorBits, mult_depth, ring_dim,
+                                                 self.cryptodir.encode(), seed, int(nine_int))
 
     def encrypt(self, data, seed: int = 0) -> bytes:
         x = np.ascontiguousarray(data, dtype=np.float64).ravel()
@@ -248,6 +256,16 @@ class Oracle:
             raise RuntimeError(f"decrypt_ct failed ({rc})")
         return (out, hi, lo) if want_coeffs else out
 
+    def decrypt_ct_words(self, ct, sf):
+        """(doubles, centred CRT integers as Python ints) for any limb count."""
+        ct = _u64(ct)
+        out = np.empty(self.slots, np.float64)
+        words = np.empty((self.ring_dim, 8), np.uint64)
+        rc = lib().orc_decrypt_ct_words(self._h, ct.ctypes.data, sf, out.ctypes.data, words.ctypes.data)
+        if rc:
+            raise RuntimeError(f"decrypt_ct_words failed ({rc})")
+        return out, words
+
     def weight_constant(self, w: float) -> int:
         return lib().orc_weight_constant(self._h, w)
 
@@ -299,6 +317,24 @@ def first_prime(bits, m): return lib().orc_first_prime(bits, m)
 def previous_prime(q, m): return lib().orc_previous_prime(q, m)
 def min_root_of_unity(m, q): return lib().orc_min_root_of_unity(m, q)
 def select_ring_dim(bits, batch): return lib().orc_select_ring_dim(bits, batch)
+def select_ring_dim_ex(bits, mult_depth): return lib().orc_select_ring_dim_ex(bits, mult_depth)
+
+
+def modulus_chain(bits, mult_depth, ring_dim):
+    q = np.zeros(8, np.uint64)
+    n = lib().orc_modulus_chain(bits, mult_depth, ring_dim, q.ctypes.data)
+    if n < 0:
+        raise ValueError("unsupported chain")
+    return [int(v) for v in q[:n]]
+
+
+def words_to_int(words) -> list:
+    """rows of 8 little-endian u64 (two's complement, 512 bit) -> Python ints"""
+    out = []
+    for row in np.asarray(words, dtype=np.uint64):
+        v = sum(int(w) << (64 * i) for i, w in enumerate(row))
+        out.append(v - (1 << 512) if v >> 511 else v)
+    return out
 
 
 def philox(seed: int, ctr) -> np.ndarray:

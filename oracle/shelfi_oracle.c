@@ -105,23 +105,60 @@ uint64_t orc_min_root_of_unity(uint32_t m, uint64_t q) {
     }
     return best;
 }
-/* [PAL] LPAlgorithmParamsGenCKKS::ParamsGen ring-dimension choice for multDepth=1 (ckks.cpp:26),
- * HYBRID key switching with dnum=2, 60-bit first modulus and auxiliary moduli, HEStd_128_classic,
- * ternary secrets (StdLatticeParm table). */
-uint32_t orc_select_ring_dim(uint32_t scale_bits, uint32_t batch) {
+/* [PAL] LPAlgorithmParamsGenCKKS::ParamsGen ring-dimension choice (ckks.cpp:26 passes multDepth = 1),
+ * HYBRID key switching, 60-bit first modulus and 60-bit auxiliary moduli, HEStd_128_classic, ternary
+ * secrets (StdLatticeParm table).  numLargeDigits defaults to 3 above depth 3, 2 above depth 0, else 1. */
+uint32_t orc_num_large_digits(uint32_t mult_depth) { return mult_depth > 3 ? 3 : mult_depth > 0 ? 2 : 1; }
+uint32_t orc_select_ring_dim_ex(uint32_t scale_bits, uint32_t mult_depth) {
     static const uint32_t dims[] = {1024, 2048, 4096, 8192, 16384, 32768};
     static const uint32_t maxq[] = {27, 54, 109, 218, 438, 881};
-    uint32_t qb = 60 + scale_bits;
-    uint32_t part = (qb + 1) / 2; /* ceil(qBound / numPartQ), numPartQ = 2 */
+    uint32_t dnum = orc_num_large_digits(mult_depth);
+    uint32_t qb = 60 + mult_depth * scale_bits;
+    uint32_t part = (qb + dnum - 1) / dnum; /* ceil(qBound / numPartQ) */
     qb += ((part + 59) / 60) * 60;
     uint32_t n = 0, prev = 0;
     for (int i = 0; i < 6; i++) {
         if (qb <= maxq[i] && qb > prev) { n = dims[i]; break; }
         prev = maxq[i];
     }
-    if (!n) n = 65536;
-    (void)batch; /* [PAL] batch > n/2 throws; callers check */
+    if (!n) n = qb <= 27 ? 1024 : 65536;
     return n;
+}
+uint32_t orc_select_ring_dim(uint32_t scale_bits, uint32_t batch) {
+    (void)batch; /* [PAL] batch > n/2 throws; callers check */
+    return orc_select_ring_dim_ex(scale_bits, 1);
+}
+/* [PAL] ParamsGen modulus chain under EXACTRESCALE, firstModSize = 60: q_last = FirstPrime(bits, M); the inner
+ * moduli alternate just below / just above the running scaling factor sf_{i} = sf_{i+1}^2 / q_{i+1} so the
+ * scale stays close to 2^bits after every rescale; q_0 = PreviousPrime(FirstPrime(60, M), M).  For two limbs
+ * (all that ckks.cpp:26 produces) this is the rule verified on the fixtures; the alternation for deeper chains
+ * is restated from PALISADE v1.11 and has no fixture => parity unpinned. */
+static uint64_t next_prime_step(uint64_t q, uint32_t m) { do q += m; while (!is_prime64(q)); return q; }
+int orc_modulus_chain(uint32_t scale_bits, uint32_t mult_depth, uint32_t ring_dim, uint64_t *q) {
+    uint32_t M = 2 * ring_dim;
+    int L = (int)mult_depth + 1;
+    if (L < 1 || L > ORC_MAX_LIMBS) return -1;
+    q[L - 1] = orc_first_prime(scale_bits, M);
+    if (L > 1) {
+        double sf = (double)q[L - 1];
+        uint32_t cnt = 0;
+        for (int i = L - 2; i >= 1; i--) {
+            sf = pow(sf, 2) / (double)q[i + 1];
+            uint64_t sf_int = (uint64_t)llround(sf), rem = sf_int % M, cand;
+            int clash = 1;
+            if ((cnt % 2) == 0) {
+                cand = sf_int - M - rem + 1;
+                while (clash) { clash = 0; cand = orc_previous_prime(cand, M); for (int j = i + 1; j < L; j++) if (cand == q[j]) clash = 1; }
+            } else {
+                cand = sf_int + M - rem + 1;
+                while (clash) { clash = 0; cand = next_prime_step(cand, M); for (int j = i + 1; j < L; j++) if (cand == q[j]) clash = 1; }
+            }
+            q[i] = cand;
+            cnt++;
+        }
+        q[0] = orc_previous_prime(orc_first_prime(60, M), M);
+    }
+    return L;
 }
 
 /* ------------------------------------------------------------------------------------------- */
@@ -465,13 +502,86 @@ int orc_encrypt_ct(const orc_ctx *c, const double *x, uint32_t n, uint64_t seed,
     return rc;
 }
 
+/* ---- multi-limb CRT helpers (chains deeper than two limbs): little-endian 64-bit words ---- */
+#define ORC_CRT_WORDS 8 /* 8 limbs x 60 bits = 480 bits */
+typedef struct { uint64_t w[ORC_CRT_WORDS]; } big_t;
+static void big_mul_add(big_t *x, uint64_t m, uint64_t a) { /* x = x*m + a */
+    u128 carry = a;
+    for (int i = 0; i < ORC_CRT_WORDS; i++) {
+        u128 cur = (u128)x->w[i] * m + carry;
+        x->w[i] = (uint64_t)cur;
+        carry = cur >> 64;
+    }
+}
+static int big_cmp(const big_t *a, const big_t *b) {
+    for (int i = ORC_CRT_WORDS - 1; i >= 0; i--)
+        if (a->w[i] != b->w[i]) return a->w[i] > b->w[i] ? 1 : -1;
+    return 0;
+}
+static void big_sub(big_t *r, const big_t *a, const big_t *b) { /* r = a - b (mod 2^512) */
+    uint64_t borrow = 0;
+    for (int i = 0; i < ORC_CRT_WORDS; i++) {
+        uint64_t ai = a->w[i], bi = b->w[i], d = ai - bi - borrow;
+        borrow = (ai < bi) || (ai == bi && borrow);
+        r->w[i] = d;
+    }
+}
+/* magnitude -> double with ONE round-to-nearest-even (what a correctly rounded BigInteger conversion gives;
+ * PALISADE's own ConvertToDouble accumulates word by word and can differ in the last ulp: unpinned, ~1e-16) */
+static double big_to_double(const big_t *m) {
+    int top = ORC_CRT_WORDS - 1;
+    while (top > 0 && !m->w[top]) top--;
+    if (top == 0) return (double)m->w[0];
+    int s = __builtin_clzll(m->w[top]);
+    uint64_t hi = m->w[top], lo = m->w[top - 1];
+    uint64_t win = s ? (hi << s) | (lo >> (64 - s)) : hi;
+    int sticky = (s ? (lo << s) : lo) != 0; /* bits of the next word below the 64-bit window */
+    for (int i = top - 2; i >= 0 && !sticky; i--) sticky |= m->w[i] != 0;
+    if (sticky) win |= 1ull;
+    return ldexp((double)win, 64 * top - s);
+}
+typedef struct {
+    int L;
+    uint64_t q[ORC_MAX_LIMBS];
+    uint64_t inv[ORC_MAX_LIMBS][ORC_MAX_LIMBS]; /* inv[i][j] = q_j^-1 mod q_i, j < i */
+    big_t Q, Qh;
+} crt_plan;
+static void crt_plan_init(crt_plan *p, const uint64_t *q, int L) {
+    memset(p, 0, sizeof *p);
+    p->L = L;
+    p->Q.w[0] = 1;
+    for (int i = 0; i < L; i++) {
+        p->q[i] = q[i];
+        for (int j = 0; j < i; j++) p->inv[i][j] = invmod(q[j] % q[i], q[i]);
+        big_mul_add(&p->Q, q[i], 0);
+    }
+    for (int i = 0; i < ORC_CRT_WORDS; i++)
+        p->Qh.w[i] = (p->Q.w[i] >> 1) | (i + 1 < ORC_CRT_WORDS ? p->Q.w[i + 1] << 63 : 0);
+}
+/* [PAL] DCRTPoly::CRTInterpolate for one coefficient: the unique x in [0, Q) with x = a_i (mod q_i), here by
+ * Garner's mixed-radix digits + Horner; then the centred representative as sign + magnitude */
+static void crt_centered(const crt_plan *p, const uint64_t *a, int *neg, big_t *mag) {
+    uint64_t v[ORC_MAX_LIMBS] = {0};
+    for (int i = 0; i < p->L; i++) {
+        uint64_t qi = p->q[i], t = a[i];
+        for (int j = 0; j < i; j++) t = mulmod(submod(t, v[j] % qi, qi), p->inv[i][j], qi);
+        v[i] = t;
+    }
+    big_t x; memset(&x, 0, sizeof x);
+    x.w[0] = v[p->L - 1];
+    for (int i = p->L - 2; i >= 0; i--) big_mul_add(&x, p->q[i], v[i]);
+    if (big_cmp(&x, &p->Qh) > 0) { *neg = 1; big_sub(mag, &p->Q, &x); }
+    else { *neg = 0; *mag = x; }
+}
+
 /* [PAL] LPAlgorithmCKKS::Decrypt + DCRTPoly::CRTInterpolate + CKKSPackedEncoding::Decode (noise
- * flooding of PALISADE >= 1.10.6 left out: it is random, ~2^-40 relative, far below the 1e-6 tier) */
-int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out, int64_t *coeff_hi, uint64_t *coeff_lo) {
+ * flooding of PALISADE >= 1.10.6 left out: it is random, ~2^-40 relative, far below the 1e-6 tier).
+ * words (optional): N x 8 little-endian words, two's complement of the centred integer. */
+static int decrypt_ct_impl(const orc_ctx *c, const uint64_t *ct, double sf, double *out, int64_t *coeff_hi,
+                           uint64_t *coeff_lo, uint64_t *words) {
     if (!c->have_cc || !c->have_sk) return -1;
     uint32_t N = c->wp.N, Nh = N / 2, slots = c->wp.batch;
     int L = c->wp.L;
-    if (L > 2) return -2; /* 128-bit CRT only */
     uint32_t gap = Nh / slots;
     uint64_t *t = malloc((size_t)L * N * 8);
     for (int l = 0; l < L; l++) {
@@ -485,24 +595,24 @@ int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out,
     double p = (double)c->wp.ptm;
     double pre = pow(sf, -1) * pow(2, p), powP = pow(2, -p);
     double *z = malloc((size_t)slots * 2 * sizeof(double));
-    u128 Q = c->wp.q[0], Qh;
-    uint64_t q0inv = 0;
-    if (L == 2) { Q = (u128)c->wp.q[0] * c->wp.q[1]; q0inv = invmod(c->wp.q[0] % c->wp.q[1], c->wp.q[1]); }
-    Qh = Q >> 1;
+    crt_plan plan;
+    crt_plan_init(&plan, c->wp.q, L);
     for (uint32_t j = 0; j < N; j++) {
-        u128 xv;
-        if (L == 1) xv = t[j];
-        else {
-            uint64_t q1 = c->wp.q[1], a0 = t[j], a1 = t[N + j];
-            uint64_t d = mulmod(submod(a1, a0 % q1, q1), q0inv, q1);
-            xv = (u128)a0 + (u128)c->wp.q[0] * d;
+        uint64_t a[ORC_MAX_LIMBS];
+        for (int l = 0; l < L; l++) a[l] = t[(size_t)l * N + j];
+        int neg; big_t mag;
+        crt_centered(&plan, a, &neg, &mag);
+        if (coeff_hi || words) {
+            big_t zero, tc; memset(&zero, 0, sizeof zero);
+            if (neg) big_sub(&tc, &zero, &mag); else tc = mag;
+            if (coeff_hi) { coeff_hi[j] = (int64_t)tc.w[1]; coeff_lo[j] = tc.w[0]; }
+            if (words) memcpy(words + (size_t)j * ORC_CRT_WORDS, tc.w, sizeof tc.w);
         }
-        i128 sv = xv > Qh ? -(i128)(Q - xv) : (i128)xv;
-        if (coeff_hi) { coeff_hi[j] = (int64_t)(sv >> 64); coeff_lo[j] = (uint64_t)sv; }
         uint32_t idx = j < Nh ? j : j - Nh;
         if (idx % gap == 0) {
             uint32_t slot = idx / gap;
-            z[2 * slot + (j < Nh ? 0 : 1)] = (double)sv * pre;
+            double d = big_to_double(&mag);
+            z[2 * slot + (j < Nh ? 0 : 1)] = (neg ? -d : d) * pre;
         }
     }
     orc_fft_special(c, z, slots);
@@ -511,6 +621,12 @@ int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out,
     for (uint32_t i = 0; i < slots; i++) out[i] = z[2 * i] * powP;
     free(t); free(z);
     return 0;
+}
+int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out, int64_t *coeff_hi, uint64_t *coeff_lo) {
+    return decrypt_ct_impl(c, ct, sf, out, coeff_hi, coeff_lo, NULL);
+}
+int orc_decrypt_ct_words(const orc_ctx *c, const uint64_t *ct, double sf, double *out, uint64_t *words) {
+    return decrypt_ct_impl(c, ct, sf, out, NULL, NULL, words);
 }
 
 int64_t orc_weight_constant(const orc_ctx *c, float w) {
@@ -1141,20 +1257,26 @@ static int write_file(const char *dir, const char *name, const uint8_t *b, size_
 }
 
 int orc_gen_context_and_keys(uint32_t batch, uint32_t scale_bits, const char *cryptodir, uint64_t seed, int nine_int) {
+    return orc_gen_context_and_keys_ex(batch, scale_bits, 1, 0, cryptodir, seed, nine_int); /* ckks.cpp:26 */
+}
+/* the same with multDepth and ring dimension free (ring_dim 0: PALISADE's choice): contexts the reference's
+ * hard-coded multDepth = 1 cannot produce (BASELINE configs 3-4) */
+int orc_gen_context_and_keys_ex(uint32_t batch, uint32_t scale_bits, uint32_t mult_depth, uint32_t ring_dim,
+                                const char *cryptodir, uint64_t seed, int nine_int) {
     wire_params p; memset(&p, 0, sizeof p);
-    uint32_t N = orc_select_ring_dim(scale_bits, batch);
-    if (batch > N / 2 || batch == 0 || (batch & (batch - 1))) return 0;
-    p.N = N; p.M = 2 * N; p.L = 2; /* multDepth = 1 (ckks.cpp:26) => 2 limbs */
-    /* [PAL] ParamsGen: q_last = FirstPrime(bits, M); q0 = PreviousPrime(FirstPrime(60, M), M) */
-    p.q[1] = orc_first_prime(scale_bits, p.M);
-    p.q[0] = orc_previous_prime(orc_first_prime(60, p.M), p.M);
-    for (int l = 0; l < 2; l++) p.psi[l] = orc_min_root_of_unity(p.M, p.q[l]);
+    uint32_t N = ring_dim ? ring_dim : orc_select_ring_dim_ex(scale_bits, mult_depth);
+    if (batch > N / 2 || batch == 0 || (batch & (batch - 1)) || (N & (N - 1))) return 0;
+    p.N = N; p.M = 2 * N;
+    p.L = orc_modulus_chain(scale_bits, mult_depth, N, p.q); /* multDepth + 1 limbs */
+    if (p.L < 1) return 0;
+    for (int l = 0; l < p.L; l++) p.psi[l] = orc_min_root_of_unity(p.M, p.q[l]);
     bigint_from_product(p.q, p.L, p.bigQ, &p.bigQ_msb);
     p.ptm = scale_bits; p.batch = batch;
     p.sigma = 3.19f; p.alpha = 9.0f; p.hermite = 1.006f;
     /* relinWindow, depth, maxDepth, [extra 0], mode(OPTIMIZED), stdLevel, rsTech(EXACT), ksTech(HYBRID), dnum */
-    if (nine_int) { uint32_t v[9] = {0, 1, 2, 0, 1, 0, 2, 1, 2}; memcpy(p.ints, v, sizeof v); p.nints = 9; }
-    else { uint32_t v[8] = {0, 1, 2, 1, 0, 2, 1, 2}; memcpy(p.ints, v, sizeof v); p.nints = 8; }
+    uint32_t dnum = orc_num_large_digits(mult_depth);
+    if (nine_int) { uint32_t v[9] = {0, 1, 2, 0, 1, 0, 2, 1, dnum}; memcpy(p.ints, v, sizeof v); p.nints = 9; }
+    else { uint32_t v[8] = {0, 1, 2, 1, 0, 2, 1, dnum}; memcpy(p.ints, v, sizeof v); p.nints = 8; }
     p.enabled = 5; /* ENCRYPTION | SHE (ckks.cpp:32-33) */
 
     orc_ctx *c = orc_create(batch, scale_bits, cryptodir);

@@ -43,6 +43,10 @@ int orc_load_from_memory(orc_ctx *c, const uint8_t *cc, size_t cc_len, const uin
  * 9-int RLWE block wire variant. */
 int orc_gen_context_and_keys(uint32_t batch, uint32_t scale_bits, const char *cryptodir, uint64_t seed,
                              int nine_int);
+/* extension: multDepth and ring dimension free (ring_dim 0 = PALISADE's automatic choice); mult_depth = 1,
+ * ring_dim = 0 is orc_gen_context_and_keys */
+int orc_gen_context_and_keys_ex(uint32_t batch, uint32_t scale_bits, uint32_t mult_depth, uint32_t ring_dim,
+                                const char *cryptodir, uint64_t seed, int nine_int);
 const char *orc_last_error(const orc_ctx *c);
 
 /* ---- introspection ---- */
@@ -64,6 +68,10 @@ uint64_t orc_previous_prime(uint64_t q, uint32_t m);          /* next smaller pr
 uint64_t orc_min_root_of_unity(uint32_t m, uint64_t q);       /* smallest primitive m-th root mod q  */
 /* ring dimension PALISADE's genCryptoContextCKKS picks for (multDepth=1, bits, batch) */
 uint32_t orc_select_ring_dim(uint32_t scale_bits, uint32_t batch);
+uint32_t orc_select_ring_dim_ex(uint32_t scale_bits, uint32_t mult_depth);
+uint32_t orc_num_large_digits(uint32_t mult_depth);
+/* EXACTRESCALE modulus chain q[0..mult_depth]; returns the limb count or -1 */
+int orc_modulus_chain(uint32_t scale_bits, uint32_t mult_depth, uint32_t ring_dim, uint64_t *q);
 
 /* ---- primitives (PALISADE ChineseRemainderTransformFTT / DiscreteFourierTransform) ---- */
 void orc_ntt_forward(const orc_ctx *c, int limb, uint64_t *a); /* natural -> bit-reversed, in place */
@@ -86,6 +94,8 @@ int orc_encrypt_ct(const orc_ctx *c, const double *x, uint32_t n, uint64_t seed,
  * (two's-complement 128 bit) — the bit-exact integer stage. out gets `slots` doubles. */
 int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out, int64_t *coeff_hi,
                    uint64_t *coeff_lo);
+/* any limb count: words = N x 8 little-endian u64, two's complement of the centred CRT integer */
+int orc_decrypt_ct_words(const orc_ctx *c, const uint64_t *ct, double sf, double *out, uint64_t *words);
 /* EvalMult(ct,(float)w) constant: (int64)((double)w * sf0 + 0.5)   (ckks.cpp:287-288) */
 int64_t orc_weight_constant(const orc_ctx *c, float w);
 

@@ -64,7 +64,8 @@ class Emu:
             "emu_encode": (None, [vp, vp, u64, vp]),
             "emu_encode_sample": (None, [vp, vp, u64, u64, u64, vp, vp]),
             "emu_encrypt": (None, [vp, vp, vp, vp, vp, vp]),
-            "emu_decrypt": (None, [vp, vp, vp, f64, f64, vp, u64, vp, vp]),
+            "emu_decrypt": (None, [vp, vp, vp, f64, f64, vp, u64, vp, vp, vp]),
+            "emu_create_ex": (vp, [vp, vp, u32, u32, u32, u32, f64]),
             "emu_weighted_sum": (None, [vp, u32, C.POINTER(vp), vp, u32, vp, u32]),
             "emu_unpack": (None, [vp, vp, u64, u32, u64, vp, vp]),
             "emu_pack": (None, [vp, vp, u64, u32, u64, vp, vp]),
@@ -79,16 +80,18 @@ class Emu:
             "emu_previous_prime": (u64, [u64, u32]),
             "emu_min_primitive_root": (u64, [u32, u64]),
             "emu_select_ring_dim": (u32, [u32]),
+            "emu_select_ring_dim_ex": (u32, [u32, u32]),
+            "emu_modulus_chain": (C.c_int, [u32, u32, u32, vp]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
         self.L = L
 
-    def context(self, q, psi, slots=4096, batch=4096, sigma=float(np.float32(3.19))):
+    def context(self, q, psi, slots=4096, batch=4096, sigma=float(np.float32(3.19)), logn=13):
         q = np.ascontiguousarray(q, np.uint64)
         psi = np.ascontiguousarray(psi, np.uint64)
-        h = self.L.emu_create(q.ctypes.data, psi.ctypes.data, len(q), slots, batch, sigma)
+        h = self.L.emu_create_ex(q.ctypes.data, psi.ctypes.data, len(q), logn, slots, batch, sigma)
         err = self.L.emu_error(h).decode()
         if err:
             self.L.emu_destroy(h)
@@ -114,6 +117,39 @@ def emu_ctx(emu, oracles):
     for name, o in oracles.items():
         L = o.num_limbs
         out[name] = emu.context([o.modulus(l) for l in range(L)], [o.psi(l) for l in range(L)], o.slots, 4096)
+    return out
+
+
+# Contexts beyond what the reference's hard-coded multDepth = 1 produces (BASELINE configs 3 and 4, plus a deep chain
+# at ring dimension 8192 and sparse packing in a large ring): name -> (batch/slots, scale bits, multDepth, ring_dim)
+DEEP_CONTEXTS = {
+    "n16k_l4": (8192, 52, 3, 0),        # config 3: N = 16384, 4 limbs, full packing
+    "n32k_l8": (16384, 52, 7, 0),       # config 4: N = 32768, 8 limbs, full packing
+    "n8k_l3": (4096, 40, 2, 8192),      # 3 limbs in one tile: the general CRT without the tile split
+    "n16k_sparse": (1024, 45, 3, 16384),  # slots < 4096 in a two-tile ring: gap 8
+}
+
+
+@pytest.fixture(scope="session")
+def deep_oracles(oracle_mod, tmp_path_factory):
+    """Oracle-generated key material (fixed seeds) for DEEP_CONTEXTS, loaded."""
+    out = {}
+    for i, (name, (batch, bits, depth, ring)) in enumerate(DEEP_CONTEXTS.items()):
+        d = str(tmp_path_factory.mktemp(name)) + "/"
+        o = oracle_mod.Oracle("ckks", batch, bits, d)
+        assert o.genCryptoContextAndKeyGen(seed=100 + i, nine_int=True, mult_depth=depth, ring_dim=ring) == 1
+        assert o.loadCryptoParams() == 0
+        out[name] = o
+    return out
+
+
+@pytest.fixture(scope="session")
+def deep_emu_ctx(emu, deep_oracles):
+    out = {}
+    for name, o in deep_oracles.items():
+        L = o.num_limbs
+        out[name] = emu.context([o.modulus(l) for l in range(L)], [o.psi(l) for l in range(L)], o.slots, o.batchSize,
+                                logn=int(o.ring_dim).bit_length() - 1)
     return out
 
 

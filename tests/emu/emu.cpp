@@ -22,6 +22,7 @@ struct Emu {
     RingConst rc;
     EncodeConst ec;
     Crt2Const crt;
+    CrtNConst crtn;
     uint64_t cdf[32];
     std::vector<tw_t> tw[kMaxLimbs], itw[kMaxLimbs];
     std::vector<cplx> fft_inv, fft_fwd;
@@ -31,64 +32,99 @@ struct Emu {
 #define FOR_THREADS(n) for (int tid = 0; tid < (n); tid++)
 
 template <class Load, class Store>
-static void replay_forward(u64 *sm, const LimbConst &lc, Load ld, Store st) {
-    FOR_THREADS(kNttThreads) fwd_phase_a(tid, sm, lc, ld);
-    FOR_THREADS(kNttThreads) fwd_phase_mid<7>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) fwd_phase_mid<4>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) fwd_phase_mid<1>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) fwd_phase_e(tid, sm, lc, st);
+static void replay_forward(u64 *sm, const LimbConst &lc, u32 hb, Load ld, Store st) {
+    FOR_THREADS(kNttThreads) fwd_phase_a(tid, sm, lc, hb, ld);
+    FOR_THREADS(kNttThreads) fwd_phase_mid<7>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) fwd_phase_mid<4>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) fwd_phase_mid<1>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) fwd_phase_e(tid, sm, lc, hb, st);
 }
-template <class Load, class Store>
-static void replay_inverse(u64 *sm, const LimbConst &lc, Load ld, Store st) {
-    FOR_THREADS(kNttThreads) inv_phase_e(tid, sm, lc, ld);
-    FOR_THREADS(kNttThreads) inv_phase_mid<1>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) inv_phase_mid<4>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) inv_phase_mid<7>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) inv_phase_last(tid, sm, lc, st);
+// intt_tile<D>
+template <int D, class Load>
+static void replay_inverse(u64 *sm, const LimbConst &lc, u32 hb, Load ld, u64 *dst) {
+    FOR_THREADS(kNttThreads) inv_phase_e(tid, sm, lc, hb, ld);
+    FOR_THREADS(kNttThreads) inv_phase_mid<1>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) inv_phase_mid<4>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) inv_phase_mid<7>(tid, sm, lc, hb);
+    if (D == 0) { FOR_THREADS(kNttThreads) inv_phase_last(tid, sm, lc, StoreGlobal{dst}); }
+    else { FOR_THREADS(kNttThreads) inv_phase_last_lazy(tid, sm, lc, hb, StoreGlobal{dst}); }
 }
+// intt_tail_kernel<D> over one row
+template <int D>
+static void replay_tail(const LimbConst &lc, u64 *row) {
+    for (u32 i = 0; i < (u32)kN; i++) {
+        u64 a[1 << D];
+        for (int k = 0; k < (1 << D); k++) a[k] = row[i + (size_t)k * kN];
+        inv_tail<D>(a, lc);
+        for (int k = 0; k < (1 << D); k++) row[i + (size_t)k * kN] = a[k];
+    }
+}
+#define EMU_D(d, ...)                                         \
+    switch (d) {                                              \
+        case 0: { constexpr int D = 0; __VA_ARGS__; break; }  \
+        case 1: { constexpr int D = 1; __VA_ARGS__; break; }  \
+        default: { constexpr int D = 2; __VA_ARGS__; break; } \
+    }
 
 extern "C" {
 
-Emu *emu_create(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint32_t slots, uint32_t batch, double sigma) {
+Emu *emu_create_ex(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint32_t logn, uint32_t slots, uint32_t batch,
+                   double sigma) {
     Emu *e = new Emu();
     std::memset(&e->rc, 0, sizeof e->rc);
-    e->rc.n = kN; e->rc.logn = kLogN; e->rc.limbs = limbs; e->rc.slots = slots;
+    const uint32_t n = 1u << logn;
+    e->rc.n = n; e->rc.logn = logn; e->rc.log_blocks = logn - kLogN; e->rc.limbs = limbs; e->rc.slots = slots;
     for (uint32_t l = 0; l < limbs; l++) {
-        e->err = make_limb_const(q[l], psi[l], &e->rc.limb[l], &e->tw[l], &e->itw[l]);
+        e->err = make_limb_const(q[l], psi[l], logn, &e->rc.limb[l], &e->tw[l], &e->itw[l]);
         if (!e->err.empty()) return e;
         e->rc.limb[l].tw = e->tw[l].data();
         e->rc.limb[l].itw = e->itw[l].data();
     }
-    make_fft_tables(2 * kN, slots, &e->fft_inv, &e->fft_fwd);
+    make_fft_tables(2 * n, slots, &e->fft_inv, &e->fft_fwd);
     std::memset(&e->ec, 0, sizeof e->ec);
-    e->ec.slots = slots; e->ec.gap = (kN / 2) / slots; e->ec.batch = batch;
+    e->ec.slots = slots; e->ec.gap = (n / 2) / slots; e->ec.batch = batch;
     while ((1u << e->ec.log_slots) < slots) e->ec.log_slots++;
     e->ec.pow_p = (double)q[limbs - 1];
     e->ec.inv_size = 1.0 / (double)slots;
     e->ec.tw_inv = e->fft_inv.data();
     e->ec.tw_fwd = e->fft_fwd.data();
     e->crt = make_crt2(q[0], limbs >= 2 ? q[1] : 0);
+    e->crtn = make_crtn(q, limbs);
     build_gauss_cdf(sigma, e->cdf);
     return e;
+}
+Emu *emu_create(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint32_t slots, uint32_t batch, double sigma) {
+    return emu_create_ex(q, psi, limbs, kLogN, slots, batch, sigma);
 }
 void emu_destroy(Emu *e) { delete e; }
 const char *emu_error(const Emu *e) { return e->err.c_str(); }
 uint32_t emu_fwd_mask(const Emu *e, uint32_t l) { return e->rc.limb[l].fwd_mask; }
 uint32_t emu_rmode(const Emu *e, uint32_t l) { return e->rc.limb[l].rmode; }
 
-// ntt_forward_kernel / ntt_inverse_kernel, one row
+// ntt_forward_kernel<D> / ntt_inverse_kernel<D> (+ intt_tail_kernel<D>), one row of rc.n values
 void emu_ntt_forward(const Emu *e, uint32_t limb, uint64_t *row) {
-    std::vector<u64> sm(kN);
+    std::vector<u64> sm(kN), src(row, row + e->rc.n);
     const LimbConst lc = e->rc.limb[limb];
-    replay_forward(sm.data(), lc, LoadGlobal{row}, StoreFullReducePair{row, &lc});
+    const u32 d = e->rc.log_blocks;
+    for (u32 blk = 0; blk < (1u << d); blk++) {
+        u64 *dst = row + (size_t)blk * kN;
+        EMU_D(d, replay_forward(sm.data(), lc, head_bits(d, blk), HeadLoad<D, LoadGlobal>{LoadGlobal{src.data()}, &lc, blk},
+                                StoreFullReducePair{dst, &lc}))
+    }
 }
 void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
     std::vector<u64> sm(kN);
     const LimbConst lc = e->rc.limb[limb];
-    replay_inverse(sm.data(), lc, LoadPairGlobal{row}, StoreGlobal{row});
+    const u32 d = e->rc.log_blocks;
+    for (u32 blk = 0; blk < (1u << d); blk++) {
+        u64 *t = row + (size_t)blk * kN;
+        EMU_D(d, replay_inverse<D>(sm.data(), lc, head_bits(d, blk), LoadPairGlobal{t}, t))
+    }
+    if (d == 1) replay_tail<1>(lc, row);
+    if (d == 2) replay_tail<2>(lc, row);
 }
 
-// encode_kernel<SAMPLE>: one ciphertext
+// encode_kernel<SAMPLE> (ring dimension 8192) or encode_block_kernel<DF> (+ sample_add_kernel): one ciphertext
 static void replay_encode(const Emu *e, const double *x, uint64_t n_valid, std::vector<cplx> &z) {
     z.assign(e->ec.slots, cplx{0, 0});
     FOR_THREADS(kFftThreads) encode_load(tid, kFftThreads, z.data(), e->ec, x, n_valid);
@@ -103,70 +139,170 @@ static void replay_encode(const Emu *e, const double *x, uint64_t n_valid, std::
     }
     FOR_THREADS(kFftThreads) encode_finalize(tid, kFftThreads, z.data(), e->ec);
 }
+extern "C++" {
+template <int DF>
+static void replay_encode_block(const Emu *e, const double *x, uint64_t n_valid, u32 fb, int64_t *m) {
+    const EncodeConst &ec = e->ec;
+    std::vector<cplx> z(kFftFast, cplx{0, 0});
+    FOR_THREADS(kFftThreads) encode_load_block<DF>(tid, kFftThreads, z.data(), ec, x, n_valid, fb);
+    EncodeConst et = ec;
+    if (ec.slots >= kFftFast) {
+        et.slots = kFftFast; et.log_slots = 12;
+        FOR_THREADS(kFftThreads) fft_inv_pass8<9>(tid, z.data(), ec.tw_inv);
+        FOR_THREADS(kFftThreads) fft_inv_pass8<6>(tid, z.data(), ec.tw_inv);
+        FOR_THREADS(kFftThreads) fft_inv_pass8<3>(tid, z.data(), ec.tw_inv);
+        FOR_THREADS(kFftThreads) fft_inv_pass8<0>(tid, z.data(), ec.tw_inv);
+    } else {
+        for (u32 len = ec.slots; len >= 2; len >>= 1)
+            FOR_THREADS(kFftThreads) fft_inv_stage(tid, kFftThreads, z.data(), ec.slots, len, ec.tw_inv);
+    }
+    FOR_THREADS(kFftThreads) encode_finalize(tid, kFftThreads, z.data(), et);
+    FOR_THREADS(kFftThreads) encode_emit_block<DF>(tid, kFftThreads, z.data(), ec, fb, e->rc.n >> 1, (i64 *)m);
+}
+}  // extern "C++"
 void emu_encode(const Emu *e, const double *x, uint64_t n_valid, int64_t *m) {
-    std::vector<cplx> z;
-    replay_encode(e, x, n_valid, z);
-    FOR_THREADS(kFftThreads)
-        for (u32 j = tid; j < (u32)kN; j += kFftThreads) m[j] = encode_coeff(z.data(), e->ec, j);
+    if (e->rc.log_blocks == 0) {
+        std::vector<cplx> z;
+        replay_encode(e, x, n_valid, z);
+        FOR_THREADS(kFftThreads)
+            for (u32 j = tid; j < (u32)kN; j += kFftThreads) m[j] = encode_coeff(z.data(), e->ec, j);
+        return;
+    }
+    const u32 df = e->ec.log_slots > 12 ? e->ec.log_slots - 12 : 0;
+    for (u32 fb = 0; fb < (1u << df); fb++) { EMU_D(df, replay_encode_block<D>(e, x, n_valid, fb, m)) }
 }
 void emu_encode_sample(const Emu *e, const double *x, uint64_t n_valid, uint64_t seed, uint64_t ct_index, int64_t *m_e0,
                        uint16_t *ve) {
-    std::vector<cplx> z;
-    replay_encode(e, x, n_valid, z);
     SamplerConst sc;
     std::memset(&sc, 0, sizeof sc);
     sc.seed = seed;
-    FOR_THREADS(kFftThreads)
-        encode_sample_emit(tid, kFftThreads, z.data(), e->ec, sc, e->cdf, ct_index, (i64 *)m_e0, ve);
+    if (e->rc.log_blocks == 0) {
+        std::vector<cplx> z;
+        replay_encode(e, x, n_valid, z);
+        FOR_THREADS(kFftThreads)
+            encode_sample_emit(tid, kFftThreads, z.data(), e->ec, sc, e->cdf, ct_index, (i64 *)m_e0, ve);
+        return;
+    }
+    emu_encode(e, x, n_valid, m_e0);
+    for (u32 j4 = 0; j4 < e->rc.n / 4; j4++) sample_add_group(j4, ct_index, sc, e->cdf, (i64 *)m_e0, ve);
 }
 
-// encrypt_kernel: one ciphertext, all limbs; pk_b / pk_a: [L][N] {value, shoup}; out: [2][L][N]
+// encrypt_kernel<D>: one ciphertext, all limbs; pk_b / pk_a: [L][N] values; out: [2][L][N]
 void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const uint64_t *pk_b, const uint64_t *pk_a,
                  uint64_t *out) {
-    const u32 L = e->rc.limbs;
+    const u32 L = e->rc.limbs, d = e->rc.log_blocks;
+    const size_t n = e->rc.n;
     std::vector<u64> sm(kN);
     for (u32 l = 0; l < L; l++) {
         const LimbConst lc = e->rc.limb[l];
-        std::vector<tw_t> b(kN), a(kN);
-        for (int j = 0; j < kN; j++) {
-            b[j] = tw_t{pk_b[(size_t)l * kN + j], nt::shoup(pk_b[(size_t)l * kN + j], lc.q)};
-            a[j] = tw_t{pk_a[(size_t)l * kN + j], nt::shoup(pk_a[(size_t)l * kN + j], lc.q)};
+        std::vector<tw_t> b(n), a(n);
+        for (size_t j = 0; j < n; j++) {
+            b[j] = tw_t{pk_b[l * n + j], nt::shoup(pk_b[l * n + j], lc.q)};
+            a[j] = tw_t{pk_a[l * n + j], nt::shoup(pk_a[l * n + j], lc.q)};
         }
-        u64 *c0 = out + (size_t)(0 * L + l) * kN, *c1 = out + (size_t)(1 * L + l) * kN;
-        replay_forward(sm.data(), lc, LoadTernary{ve, lc.q}, StoreLazyPair{c1});
-        replay_forward(sm.data(), lc, LoadSigned{(const i64 *)m_e0, &lc}, StoreMulAdd{b.data(), c1, c0, &lc});
-        replay_forward(sm.data(), lc, LoadGaussHi{ve, lc.q}, StoreMulAdd{a.data(), c1, c1, &lc});
+        for (u32 blk = 0; blk < (1u << d); blk++) {
+            const size_t off = (size_t)blk * kN;
+            u64 *c0 = out + (0 * L + l) * n + off, *c1 = out + (1 * L + l) * n + off;
+            const u32 hb = head_bits(d, blk);
+            EMU_D(d, {
+                replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve, lc.q}, &lc, blk}, StoreLazyPair{c1});
+                replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadSigned>{LoadSigned{(const i64 *)m_e0, &lc}, &lc, blk},
+                               StoreMulAdd{b.data() + off, c1, c0, &lc});
+                replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadGaussHi>{LoadGaussHi{ve, lc.q}, &lc, blk},
+                               StoreMulAdd{a.data() + off, c1, c1, &lc});
+            })
+        }
     }
 }
 
-// decrypt_intt_kernel + decode_kernel: one ciphertext; sk: [L][N]; out: slots doubles (first `length` written)
+extern "C++" {
+template <int L>
+static void replay_crt(const Emu *e, const DecodeConst &dc, const u64 *coeff, double *vals, u64 *tap8) {
+    for (u32 j = 0; j < e->rc.n; j++) {
+        u64 t[8];
+        double v = decode_value<L>(coeff, e->rc.n, j, dc.crt, e->crtn, tap8 ? t : nullptr);
+        vals[j] = shelfi::fmul(v, dc.pre);
+        if (tap8) std::memcpy(tap8 + (size_t)j * 8, t, sizeof t);
+    }
+}
+template <int DF>
+static void replay_decode_fft(const Emu *e, const DecodeConst &dc, const double *vals, cplx *zs, double *out, u64 length) {
+    const EncodeConst &ec = e->ec;
+    for (u32 fb = 0; fb < (1u << DF); fb++) {
+        std::vector<cplx> z(kFftFast);
+        FOR_THREADS(kFftThreads) decode_load_block<DF>(tid, kFftThreads, z.data(), ec, fb, e->rc.n, vals);
+        if (ec.slots >= kFftFast) {
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<0>(tid, z.data(), ec.tw_fwd);
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<3>(tid, z.data(), ec.tw_fwd);
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<6>(tid, z.data(), ec.tw_fwd);
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<9>(tid, z.data(), ec.tw_fwd);
+        } else {
+            for (u32 len = 2; len <= ec.slots; len <<= 1)
+                FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), ec.slots, len, ec.tw_fwd);
+        }
+        if (DF == 0) { FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length); }
+        else for (u32 i = 0; i < kFftFast; i++) zs[(size_t)fb * kFftFast + i] = z[zsw(i)];
+    }
+    if (DF > 0) for (u32 i = 0; i < kFftFast; i++) decode_tail<DF>(i, zs, ec, dc, out, length);
+}
+
+}  // extern "C++"
+// decrypt_intt_kernel<D> (+ tail) then decode_kernel (8192, <= 2 limbs) or crt_kernel<L> + decode_fft_kernel<DF> (+ tail):
+// one ciphertext; sk: [L][N]; out: slots doubles (first `length` written); tap8: N x 8 words or NULL
 void emu_decrypt(const Emu *e, const uint64_t *ct, const uint64_t *sk, double pre, double pow_p, double *out,
-                 uint64_t length, int64_t *tap_hi, uint64_t *tap_lo) {
-    const u32 L = e->rc.limbs;
-    std::vector<u64> sm(kN), coeff((size_t)L * kN);
+                 uint64_t length, int64_t *tap_hi, uint64_t *tap_lo, uint64_t *tap8) {
+    const u32 L = e->rc.limbs, d = e->rc.log_blocks;
+    const size_t n = e->rc.n;
+    std::vector<u64> sm(kN), coeff(L * n);
     for (u32 l = 0; l < L; l++) {
         const LimbConst lc = e->rc.limb[l];
-        std::vector<tw_t> s(kN);
-        for (int j = 0; j < kN; j++) s[j] = tw_t{sk[(size_t)l * kN + j], nt::shoup(sk[(size_t)l * kN + j], lc.q)};
-        replay_inverse(sm.data(), lc,
-                       LoadDecryptPair{ct + (size_t)(0 * L + l) * kN, ct + (size_t)(1 * L + l) * kN, s.data(), lc.q},
-                       StoreGlobal{coeff.data() + (size_t)l * kN});
+        std::vector<tw_t> s(n);
+        for (size_t j = 0; j < n; j++) s[j] = tw_t{sk[l * n + j], nt::shoup(sk[l * n + j], lc.q)};
+        for (u32 blk = 0; blk < (1u << d); blk++) {
+            const size_t off = (size_t)blk * kN;
+            EMU_D(d, replay_inverse<D>(sm.data(), lc, head_bits(d, blk),
+                                       LoadDecryptPair{ct + (0 * L + l) * n + off, ct + (1 * L + l) * n + off, s.data() + off, lc.q},
+                                       coeff.data() + l * n + off))
+        }
+        if (d == 1) replay_tail<1>(lc, coeff.data() + l * n);
+        if (d == 2) replay_tail<2>(lc, coeff.data() + l * n);
     }
     DecodeConst dc;
     dc.crt = e->crt; dc.pre = pre; dc.pow_p = pow_p;
-    std::vector<cplx> z(e->ec.slots);
-    FOR_THREADS(kFftThreads)
-        decode_load(tid, kFftThreads, z.data(), e->ec, dc, L, coeff.data(), (i64 *)tap_hi, (u64 *)tap_lo);
-    if (e->ec.slots == kFftFast) {
-        FOR_THREADS(kFftThreads) fft_fwd_pass8<0>(tid, z.data(), e->ec.tw_fwd);
-        FOR_THREADS(kFftThreads) fft_fwd_pass8<3>(tid, z.data(), e->ec.tw_fwd);
-        FOR_THREADS(kFftThreads) fft_fwd_pass8<6>(tid, z.data(), e->ec.tw_fwd);
-        FOR_THREADS(kFftThreads) fft_fwd_pass8<9>(tid, z.data(), e->ec.tw_fwd);
-    } else {
-        for (u32 len = 2; len <= e->ec.slots; len <<= 1)
-            FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_fwd);
+    if (d == 0 && L <= 2 && !tap8) {
+        std::vector<cplx> z(e->ec.slots);
+        FOR_THREADS(kFftThreads)
+            decode_load(tid, kFftThreads, z.data(), e->ec, dc, L, coeff.data(), (i64 *)tap_hi, (u64 *)tap_lo);
+        if (e->ec.slots == kFftFast) {
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<0>(tid, z.data(), e->ec.tw_fwd);
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<3>(tid, z.data(), e->ec.tw_fwd);
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<6>(tid, z.data(), e->ec.tw_fwd);
+            FOR_THREADS(kFftThreads) fft_fwd_pass8<9>(tid, z.data(), e->ec.tw_fwd);
+        } else {
+            for (u32 len = 2; len <= e->ec.slots; len <<= 1)
+                FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_fwd);
+        }
+        FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length);
+        return;
     }
-    FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length);
+    std::vector<double> vals(n);
+    std::vector<u64> t8(tap8 || tap_hi ? n * 8 : 0);
+    u64 *tp = t8.empty() ? nullptr : t8.data();
+    switch (L) {
+        case 1: replay_crt<1>(e, dc, coeff.data(), vals.data(), tp); break;
+        case 2: replay_crt<2>(e, dc, coeff.data(), vals.data(), tp); break;
+        case 3: replay_crt<3>(e, dc, coeff.data(), vals.data(), tp); break;
+        case 4: replay_crt<4>(e, dc, coeff.data(), vals.data(), tp); break;
+        case 5: replay_crt<5>(e, dc, coeff.data(), vals.data(), tp); break;
+        case 6: replay_crt<6>(e, dc, coeff.data(), vals.data(), tp); break;
+        case 7: replay_crt<7>(e, dc, coeff.data(), vals.data(), tp); break;
+        default: replay_crt<8>(e, dc, coeff.data(), vals.data(), tp); break;
+    }
+    if (tap8) std::memcpy(tap8, t8.data(), n * 8 * sizeof(u64));
+    if (tap_hi) for (size_t j = 0; j < n; j++) { tap_hi[j] = (int64_t)t8[j * 8 + 1]; tap_lo[j] = t8[j * 8]; }
+    const u32 df = e->ec.log_slots > 12 ? e->ec.log_slots - 12 : 0;
+    std::vector<cplx> zs(e->ec.slots);
+    EMU_D(df, replay_decode_fft<D>(e, dc, vals.data(), zs.data(), out, length))
 }
 
 // weighted_sum_kernel arithmetic on one limb row: out[j] = sum_k c[k] * in[k][j] mod q
@@ -181,28 +317,36 @@ void emu_weighted_sum(const Emu *e, uint32_t limb, const uint64_t *const *in, co
 }
 
 // pack_kernel / unpack_kernel over a whole blob image
-static BlobRuns runs_of(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs) {
+static BlobRuns runs_of(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint32_t n) {
     BlobRuns br;
     std::memset(&br, 0, sizeof br);
-    br.runs = runs; br.stride = stride;
+    br.runs = runs; br.stride = stride; br.n = n;
     for (u32 r = 0; r < runs; r++) { br.off0[r] = run0[r]; br.off1[r] = run1[r]; }
     return br;
 }
-void emu_unpack(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint64_t n_ct,
-                const uint64_t *image, uint64_t *dense) {
-    BlobRuns br = runs_of(run0, run1, stride, runs);
+void emu_unpack_n(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint32_t n, uint64_t n_ct,
+                  const uint64_t *image, uint64_t *dense) {
+    BlobRuns br = runs_of(run0, run1, stride, runs, n);
     for (u64 run = 0; run < n_ct * runs; run++) {
         u64 a0 = run_offset(br, run / runs, (u32)(run % runs));
-        for (u32 i = 0; i < (u32)kN; i++) dense[run * kN + i] = load_unaligned(image, a0 + 8ull * i);
+        for (u32 i = 0; i < n; i++) dense[run * n + i] = load_unaligned(image, a0 + 8ull * i);
     }
+}
+void emu_pack_n(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint32_t n, uint64_t n_ct,
+                const uint64_t *dense, uint64_t *image) {
+    BlobRuns br = runs_of(run0, run1, stride, runs, n);
+    for (u64 run = 0; run < n_ct * runs; run++) {
+        u64 a0 = run_offset(br, run / runs, (u32)(run % runs));
+        for (u64 w = a0 >> 3; w <= (a0 + 8ull * n - 1) >> 3; w++) pack_word(image, a0, w, dense + run * n, n);
+    }
+}
+void emu_unpack(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint64_t n_ct,
+                const uint64_t *image, uint64_t *dense) {
+    emu_unpack_n(run0, run1, stride, runs, kN, n_ct, image, dense);
 }
 void emu_pack(const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t runs, uint64_t n_ct,
               const uint64_t *dense, uint64_t *image) {
-    BlobRuns br = runs_of(run0, run1, stride, runs);
-    for (u64 run = 0; run < n_ct * runs; run++) {
-        u64 a0 = run_offset(br, run / runs, (u32)(run % runs));
-        for (u64 w = a0 >> 3; w <= (a0 + 8ull * kN - 1) >> 3; w++) pack_word(image, a0, w, dense + run * kN);
-    }
+    emu_pack_n(run0, run1, stride, runs, kN, n_ct, dense, image);
 }
 
 // ---- wire format (wire.cpp is plain host code; exercised here without the CUDA library) ----
@@ -245,12 +389,13 @@ uint8_t *emu_wire_rebuild(const uint8_t *in, uint64_t len, uint64_t *out_len, ch
     std::string e = wire::map_ciphertext_blob(in, len, false, &m);
     if (!e.empty()) { std::snprintf(err, err_cap, "%s", e.c_str()); return nullptr; }
     const uint32_t runs = 2 * m.ctx.limbs;
-    std::vector<uint64_t> image((len + 7) / 8 + 1, 0), dense(m.n_ct * runs * (size_t)kN);
+    const uint32_t n = m.ctx.ring_dim;
+    std::vector<uint64_t> image((len + 7) / 8 + 1, 0), dense(m.n_ct * runs * (size_t)n);
     std::memcpy(image.data(), in, len);
-    emu_unpack(m.run0, m.run1, m.stride, runs, m.n_ct, image.data(), dense.data());
+    emu_unpack_n(m.run0, m.run1, m.stride, runs, n, m.n_ct, image.data(), dense.data());
     wire::BlobPlan plan = wire::plan_ciphertext_blob(m.ctx, m.n_ct, m.meta);
     std::vector<uint64_t> out_image((plan.size + 7) / 8 + 1, 0xA5A5A5A5A5A5A5A5ull);
-    emu_pack(plan.run0, plan.run1, plan.stride, runs, m.n_ct, dense.data(), out_image.data());
+    emu_pack_n(plan.run0, plan.run1, plan.stride, runs, n, m.n_ct, dense.data(), out_image.data());
     uint8_t *out = (uint8_t *)std::malloc(plan.size);
     std::memcpy(out, out_image.data(), plan.size);
     for (const auto &seg : plan.segments) std::memcpy(out + seg.offset, seg.bytes.data(), seg.bytes.size());
@@ -269,5 +414,9 @@ uint64_t emu_first_prime(uint32_t bits, uint32_t m) { return nt::first_prime(bit
 uint64_t emu_previous_prime(uint64_t q, uint32_t m) { return nt::previous_prime(q, m); }
 uint64_t emu_min_primitive_root(uint32_t m, uint64_t q) { return nt::min_primitive_root(m, q); }
 uint32_t emu_select_ring_dim(uint32_t bits) { return nt::select_ring_dim(bits); }
+uint32_t emu_select_ring_dim_ex(uint32_t bits, uint32_t mult_depth) { return nt::select_ring_dim(bits, mult_depth); }
+int emu_modulus_chain(uint32_t bits, uint32_t mult_depth, uint32_t ring_dim, uint64_t *q) {
+    return nt::modulus_chain(bits, mult_depth, ring_dim, q);
+}
 
 }  // extern "C"

@@ -94,7 +94,7 @@ def test_encrypt_decrypt_match_oracle(emu, emu_ctx, oracles, fixture_name):
     out_ref, hi_ref, lo_ref = o.decrypt_ct(ref, sf, want_coeffs=True)
     out, hi, lo = np.zeros(4096), np.empty(N, np.int64), np.empty(N, np.uint64)
     emu.L.emu_decrypt(h, vp(ct), vp(s), math.pow(sf, -1) * math.pow(2, 52), math.pow(2, -52), vp(out), 4096, vp(hi),
-                      vp(lo))
+                      vp(lo), None)
     assert np.array_equal(hi, hi_ref) and np.array_equal(lo, lo_ref)
     assert np.array_equal(out, out_ref)
     assert np.abs(out - x).max() < 1e-9
@@ -116,3 +116,70 @@ def test_weighted_sum_arithmetic_matches_oracle(emu, emu_ctx, oracles):
         emu.L.emu_weighted_sum(h, l, ptrs, vp(c), k, vp(out), 512)
         ref = [sum(int(ci) * int(a[j]) for ci, a in zip(c, ins)) % q for j in range(512)]
         assert out.tolist() == ref
+
+
+# ---- ring dimensions above one NTT tile, chains deeper than two limbs, slot counts above one FFT tile ----
+DEEP = ["n16k_l4", "n32k_l8", "n8k_l3", "n16k_sparse"]
+
+
+@pytest.mark.parametrize("name", DEEP)
+def test_deep_ntt_matches_oracle(emu, deep_emu_ctx, deep_oracles, name):
+    o, h = deep_oracles[name], deep_emu_ctx[name]
+    n = o.ring_dim
+    rng = np.random.default_rng(17)
+    for l in sorted({0, 1, o.num_limbs - 1}):
+        q = o.modulus(l)
+        for a in (rng.integers(0, q, n, dtype=np.uint64), np.full(n, q - 1, np.uint64)):
+            f = a.copy(); emu.L.emu_ntt_forward(h, l, vp(f))
+            assert np.array_equal(f, o.ntt_forward(l, a))
+            b = a.copy(); emu.L.emu_ntt_inverse(h, l, vp(b))
+            assert np.array_equal(b, o.ntt_inverse(l, a))
+
+
+@pytest.mark.parametrize("name", DEEP)
+def test_deep_encode_matches_oracle(emu, deep_emu_ctx, deep_oracles, name):
+    o, h = deep_oracles[name], deep_emu_ctx[name]
+    n, slots = o.ring_dim, o.slots
+    for n_valid, scale in ((slots, 1.0), (slots - 3, 50.0), (1, 0.01)):
+        x = (np.random.default_rng(n_valid).random(n_valid) - 0.5) * 2 * scale
+        m = np.full(n, -7, np.int64)
+        emu.L.emu_encode(h, vp(x), n_valid, vp(m))
+        assert np.array_equal(m, o.encode_coeffs(x))
+
+
+@pytest.mark.parametrize("name", DEEP)
+def test_deep_encrypt_decrypt_match_oracle(emu, deep_emu_ctx, deep_oracles, name, oracle_mod):
+    o, h = deep_oracles[name], deep_emu_ctx[name]
+    n, slots, L, bits = o.ring_dim, o.slots, o.num_limbs, o.scaleFactorBits
+    x = np.random.default_rng(5).normal(0, 0.05, slots)
+    m_e0, ve = np.empty(n, np.int64), np.empty(n, np.uint16)
+    emu.L.emu_encode_sample(h, vp(x), slots, 4321, 9, vp(m_e0), vp(ve))
+    v, e0, e1 = o.sample_noise(4321, 9)
+    assert np.array_equal(m_e0, o.encode_coeffs(x) + e0)
+    assert np.array_equal((ve & 0xFF).astype(np.int8), v.astype(np.int8))
+    b, a = o.public_key()
+    ct = np.empty((2, L, n), np.uint64)
+    emu.L.emu_encrypt(h, vp(m_e0), vp(ve), vp(b), vp(a), vp(ct))
+    ref = o.encrypt_ct(x, 4321, 9)
+    assert np.array_equal(ct, ref)
+    s = o.secret_key()
+    sf = o.scaling_factor
+    out_ref, words_ref = o.decrypt_ct_words(ref, sf)
+    out, words = np.zeros(slots), np.empty((n, 8), np.uint64)
+    emu.L.emu_decrypt(h, vp(ct), vp(s), math.pow(sf, -1) * math.pow(2, bits), math.pow(2, -bits), vp(out), slots, None,
+                      None, vp(words))
+    assert np.array_equal(words, words_ref)
+    assert np.array_equal(out, out_ref)
+    assert np.abs(out - x).max() < 2.0 ** (24 - bits)   # fresh-encryption noise scales with 1 / Delta
+
+
+def test_deep_parameter_rules_match_oracle(emu, oracle_mod):
+    for bits, depth in ((52, 1), (52, 3), (52, 7), (40, 2), (45, 3), (30, 5), (59, 1), (14, 1)):
+        n = emu.L.emu_select_ring_dim_ex(bits, depth)
+        assert n == oracle_mod.select_ring_dim_ex(bits, depth)
+        if n > 32768:
+            continue
+        q = np.zeros(8, np.uint64)
+        L = emu.L.emu_modulus_chain(bits, depth, n, vp(q))
+        assert [int(v) for v in q[:L]] == oracle_mod.modulus_chain(bits, depth, n)
+    assert (emu.L.emu_select_ring_dim_ex(52, 3), emu.L.emu_select_ring_dim_ex(52, 7)) == (16384, 32768)
