@@ -83,6 +83,7 @@ def lib() -> C.CDLL:
         "shelfi_encrypt_device": (C.c_int, [vp, vp, u64, u64, vp, vp]),
         "shelfi_encrypt_many_device": (C.c_int, [vp, C.POINTER(vp), u32, u64, u64, C.POINTER(vp), vp]),
         "shelfi_weighted_sum_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_float), u32, u64, vp, vp]),
+        "shelfi_weighted_sum_accumulate_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_float), u32, u64, vp, vp]),
         "shelfi_decrypt_device": (C.c_int, [vp, vp, u64, f64, vp, u64, vp]),
         "shelfi_pack_device": (C.c_int, [vp, vp, u64, vp, vp]),
         "shelfi_unpack_device": (C.c_int, [vp, vp, u64, vp, vp]),

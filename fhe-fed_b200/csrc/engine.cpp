@@ -842,10 +842,8 @@ int shelfi_encrypt_many_device(shelfi_ckks *h, const double *const *d_x, uint32_
     return encrypt_dense_many(h, d_x, k, n, ct_index0, d_ct, static_cast<cudaStream_t>(stream));
 }
 
-int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
-                               uint64_t n_ct, uint64_t *d_out, void *stream) {
-    if (!h) return SHELFI_ERR_ARG;
-    std::lock_guard<std::mutex> lock(h->mu);
+static int weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
+                               uint64_t n_ct, uint64_t *d_out, bool accumulate, cudaStream_t s) {
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
     if (!d_cts || !weights || !d_out || k == 0 || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
@@ -853,18 +851,30 @@ int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, con
     for (uint32_t base = 0; base < k; base += kMaxLearnersPerLaunch) {
         WavgArgs wa{};
         wa.k = std::min<uint32_t>(kMaxLearnersPerLaunch, k - base);
-        wa.accumulate = base ? 1u : 0u;
+        wa.accumulate = (base || accumulate) ? 1u : 0u;
         for (uint32_t i = 0; i < wa.k; i++) {
             wa.in[i] = reinterpret_cast<const u64 *>(d_cts[base + i]);
             int64_t sc = weight_constant(h, weights[base + i]);
             for (uint32_t l = 0; l < L; l++) wa.c[i][l] = nt::signed_mod(sc, h->ctx.modulus[l]);
         }
-        timed(h, kKWeightedSum, static_cast<cudaStream_t>(stream), [&] {
-            launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, static_cast<cudaStream_t>(stream));
-        });
+        timed(h, kKWeightedSum, s, [&] { launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, s); });
     }
     CU(cudaGetLastError());
     return 0;
+}
+
+int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
+                               uint64_t n_ct, uint64_t *d_out, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return weighted_sum_device(h, d_cts, weights, k, n_ct, d_out, false, static_cast<cudaStream_t>(stream));
+}
+
+int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
+                                          uint64_t n_ct, uint64_t *d_acc, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return weighted_sum_device(h, d_cts, weights, k, n_ct, d_acc, true, static_cast<cudaStream_t>(stream));
 }
 
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,

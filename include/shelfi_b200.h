@@ -126,6 +126,10 @@ int shelfi_encrypt_many_device(shelfi_ckks *h, const double *const *d_x, uint32_
                                uint64_t *const *d_ct, void *stream);
 int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
                                uint64_t n_ct, uint64_t *d_out, void *stream);
+/* the same folded into an accumulator that already holds a (reduced) partial sum: learners streamed through a resident
+ * accumulator in groups when K x ciphertext bytes exceed HBM (BASELINE config 4: 100 learners x 6.5 GB) */
+int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,
+                                          uint64_t n_ct, uint64_t *d_acc, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
                           uint64_t n, void *stream);
 /* dense <-> serialized image on the device (image buffers must be 8-byte aligned and hold
