@@ -53,7 +53,8 @@ struct LimbConst {
     u64 ninv, ninv_s;       // N^-1 mod q and Shoup companion
     u64 wninv, wninv_s;     // itw[1] * N^-1 mod q (last inverse stage with the scaling folded in)
     u64 r64, r64_s;         // 2^64 mod q and Shoup companion (128-bit accumulator reduction)
-    u32 rshift;     // quick-reduce shift
+    u64 radd;       // quick-reduce addend: 0 (mode 0) or q (mode 1)
+    u32 rshift;     // quick-reduce shift (>= 32 in modes 0 and 1)
     u32 rmode;      // 0: q just below 2^rshift; 1: q just above 2^rshift; 2: generic (mulhi by mu)
     u32 fwd_mask;   // bit p: quick-reduce to [0,2q) at the end of forward pass p (0..3)
     u32 pad;
@@ -118,12 +119,101 @@ HD u64 shoup_lazy_nq(u64 x, u64 w, u64 ws, u64 nq) {
     return x * w + mulhi(x, ws) * nq;
 #endif
 }
+// floor(x*ws / 2^64) or one less: the 2^0 partial product xl*sl is dropped (it contributes < 1), the two middle
+// products are summed exactly.  3 IMAD.WIDE instead of the 4 (+ carry chain) of __umul64hi.
+HD u64 mulhi_trunc(u64 x, u64 ws) {
+    u32 xl = (u32)x, xh = (u32)(x >> 32), sl = (u32)ws, sh = (u32)(ws >> 32);
+#ifdef __CUDA_ARCH__
+    u64 r;
+    asm("{\n\t"
+        ".reg .u64 t1, t2, a;\n\t"
+        ".reg .u32 t1l, t1h, t2l, t2h, c, ch;\n\t"
+        "mul.wide.u32 t1, %2, %3;\n\t"
+        "mov.b64 {t1l, t1h}, t1;\n\t"
+        "cvt.u64.u32 a, t1l;\n\t"
+        "mad.wide.u32 t2, %1, %4, a;\n\t"
+        "mov.b64 {t2l, t2h}, t2;\n\t"
+        "add.cc.u32 c, t1h, t2h;\n\t"
+        "addc.u32 ch, 0, 0;\n\t"
+        "mov.b64 a, {c, ch};\n\t"
+        "mad.wide.u32 %0, %2, %4, a;\n\t"
+        "}"
+        : "=l"(r)
+        : "r"(xl), "r"(xh), "r"(sl), "r"(sh));
+    return r;
+#else
+    u64 t1 = (u64)xh * sl;
+    u64 t2 = (u64)xl * sh + (u32)t1;
+    return (u64)xh * sh + (t1 >> 32) + (t2 >> 32);
+#endif
+}
+// Shoup product with the truncated quotient: x*w - Q'*q with Q' in {Q - 1, Q}, so the result lies in [0, 3q) for ANY
+// 64-bit x.  The butterflies use this one; their bounds grow by 3q per stage instead of 2q (tables.cpp schedules the
+// quick-reduces accordingly), which costs the 60-bit limb two more quick-reduces per transform and saves one
+// IMAD.WIDE plus the carry chain in each of the 53,248 butterflies.
+HD u64 shoup_lazy3_nq(u64 x, u64 w, u64 ws, u64 nq) {
+    u64 h = mulhi_trunc(x, ws);
+#ifdef __CUDA_ARCH__
+    u32 xl = (u32)x, xh = (u32)(x >> 32), wl = (u32)w, wh = (u32)(w >> 32);
+    u32 hl = (u32)h, hh = (u32)(h >> 32), nl = (u32)nq, nh = (u32)(nq >> 32);
+    u64 r;
+    asm("{\n\t"
+        ".reg .u64 t;\n\t"
+        ".reg .u32 lo, hi;\n\t"
+        "mul.wide.u32 t, %1, %3;\n\t"
+        "mad.wide.u32 t, %5, %7, t;\n\t"
+        "mov.b64 {lo, hi}, t;\n\t"
+        "mad.lo.u32 hi, %1, %4, hi;\n\t"
+        "mad.lo.u32 hi, %2, %3, hi;\n\t"
+        "mad.lo.u32 hi, %5, %8, hi;\n\t"
+        "mad.lo.u32 hi, %6, %7, hi;\n\t"
+        "mov.b64 %0, {lo, hi};\n\t"
+        "}"
+        : "=l"(r)
+        : "r"(xl), "r"(xh), "r"(wl), "r"(wh), "r"(hl), "r"(hh), "r"(nl), "r"(nh));
+    return r;
+#else
+    return x * w + h * nq;
+#endif
+}
 HD u64 csub(u64 x, u64 m) { return x >= m ? x - m : x; }
-// x (any value the caller's bound analysis allows) -> [0, 2q)
+// x (any 64-bit value) -> [0, 2q).  PALISADE's primes sit next to a power of two, so the quotient estimate is a shift:
+// modes 0 / 1 (q just below 2^rshift / just above it, rshift >= 32): x - (x >> rshift) q (+ q), written as
+// x + radd + hi * (2^64 - q) = one funnel shift, one IMAD.WIDE, one IMAD, no branch per value; mode 2 (anything
+// else): Barrett quotient by mulhi.  tables.cpp proves the range for every 64-bit x before choosing a mode.
+HD u64 quick_reduce_shift(u64 x, const LimbConst &lc) {
+    u32 hi = (u32)(x >> lc.rshift);
+#ifdef __CUDA_ARCH__
+    u32 nl = (u32)lc.nq, nh = (u32)(lc.nq >> 32);
+    u64 r, base = x + lc.radd;
+    asm("{\n\t"
+        ".reg .u64 t;\n\t"
+        ".reg .u32 lo, hi;\n\t"
+        "mad.wide.u32 t, %1, %2, %4;\n\t"
+        "mov.b64 {lo, hi}, t;\n\t"
+        "mad.lo.u32 hi, %1, %3, hi;\n\t"
+        "mov.b64 %0, {lo, hi};\n\t"
+        "}"
+        : "=l"(r)
+        : "r"(hi), "r"(nl), "r"(nh), "l"(base));
+    return r;
+#else
+    return x + lc.radd + (u64)hi * lc.nq;
+#endif
+}
 HD u64 quick_reduce(u64 x, const LimbConst &lc) {
-    if (lc.rmode == 0) return x - (x >> lc.rshift) * lc.q;
-    if (lc.rmode == 1) return x - (x >> lc.rshift) * lc.q + lc.q;
-    return x - mulhi(x, lc.mu) * lc.q;
+    if (lc.rmode == 2) return x - mulhi(x, lc.mu) * lc.q;
+    return quick_reduce_shift(x, lc);
+}
+// the same over the 8 values of a radix-8 pass with the mode test hoisted out
+HD void quick_reduce8(u64 (&a)[8], const LimbConst &lc) {
+    if (lc.rmode == 2) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = a[k] - mulhi(a[k], lc.mu) * lc.q;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = quick_reduce_shift(a[k], lc);
+    }
 }
 HD u64 full_reduce(u64 x, const LimbConst &lc) { return csub(quick_reduce(x, lc), lc.q); }
 // any 64-bit x -> [0, q)
@@ -166,23 +256,34 @@ template <int LO> HD u32 tile_off(u32 base, int k) {
 }
 HD u32 tile_pair(u32 vt) { return (vt << 4) ^ (((vt >> 3) & 7u) << 4); }
 
-// Cooley-Tukey butterfly, Harvey lazy form: no per-butterfly correction, bounds grow by 2q per stage
-// and are brought back by quick_reduce at the pass boundaries named in LimbConst::fwd_mask.
-HD void ct_bfly(u64 &x, u64 &y, const tw_t &w, u64 nq, u64 q2) {
-    u64 t = shoup_lazy_nq(y, w.w, w.ws, nq);
-    y = x + q2 - t;
+// Cooley-Tukey butterfly, Harvey lazy form: no per-butterfly correction, bounds grow by 3q per stage (truncated
+// Shoup quotient) and are brought back by quick_reduce at the pass boundaries named in LimbConst::fwd_mask.
+// q3 = 3q.
+// Measured on B200 (profiles/README.md): the truncated quotient is NOT faster — the 60-bit limb needs three
+// quick-reduces per transform instead of one and ptxas already schedules __umul64hi's carry chain well
+// (8140-row forward NTT 0.541 ms truncated vs 0.533 ms exact).  Kept behind a switch, off by default.
+#ifndef SHELFI_TRUNC_SHOUP
+#define SHELFI_TRUNC_SHOUP 0
+#endif
+constexpr int kBflyGrowth = SHELFI_TRUNC_SHOUP ? 3 : 2;   // bound growth per forward stage, in units of q
+HD u64 bfly_mul(u64 x, u64 w, u64 ws, u64 nq) {
+    return SHELFI_TRUNC_SHOUP ? shoup_lazy3_nq(x, w, ws, nq) : shoup_lazy_nq(x, w, ws, nq);
+}
+HD void ct_bfly(u64 &x, u64 &y, const tw_t &w, u64 nq, u64 q3) {
+    u64 t = bfly_mul(y, w.w, w.ws, nq);
+    y = x + q3 - t;
     x = x + t;
 }
 // radix-8 register pass: a[k], k = (b2 b1 b0) with b2 the address bit of the first stage.
-HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 nq, u64 q2) {
+HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 nq, u64 q3) {
     tw_t w = tw[t0];
 #pragma unroll
-    for (int k = 0; k < 4; k++) ct_bfly(a[k], a[k + 4], w, nq, q2);
+    for (int k = 0; k < 4; k++) ct_bfly(a[k], a[k + 4], w, nq, q3);
     tw_t w0 = tw[2 * t0], w1 = tw[2 * t0 + 1];
-    ct_bfly(a[0], a[2], w0, nq, q2); ct_bfly(a[1], a[3], w0, nq, q2);
-    ct_bfly(a[4], a[6], w1, nq, q2); ct_bfly(a[5], a[7], w1, nq, q2);
+    ct_bfly(a[0], a[2], w0, nq, q3); ct_bfly(a[1], a[3], w0, nq, q3);
+    ct_bfly(a[4], a[6], w1, nq, q3); ct_bfly(a[5], a[7], w1, nq, q3);
 #pragma unroll
-    for (int k = 0; k < 4; k++) ct_bfly(a[2 * k], a[2 * k + 1], tw[4 * t0 + k], nq, q2);
+    for (int k = 0; k < 4; k++) ct_bfly(a[2 * k], a[2 * k + 1], tw[4 * t0 + k], nq, q3);
 }
 
 // ---- forward NTT phases (natural order in, bit-reversed order out), 8192 points, 256 threads ----
@@ -190,18 +291,15 @@ HD void ct_radix8(u64 (&a)[8], const tw_t *__restrict__ tw, u32 t0, u64 nq, u64 
 template <class Load>
 HD void fwd_phase_a(int tid, u64 *smem, const LimbConst &lc, u32 hb, Load ld) {
     char *sm = reinterpret_cast<char *>(smem);
-    const u64 nq = lc.nq, q2 = lc.q2;
+    const u64 nq = lc.nq, q3 = kBflyGrowth * lc.q;
 #pragma unroll 1
     for (int r = 0; r < 4; r++) {
         u32 vt = tid + kNttThreads * r;
         u64 a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = ld((u32)(k << 10) | vt);
-        ct_radix8(a, lc.tw, hb, nq, q2);
-        if (lc.fwd_mask & 1u) {
-#pragma unroll
-            for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
-        }
+        ct_radix8(a, lc.tw, hb, nq, q3);
+        if (lc.fwd_mask & 1u) quick_reduce8(a, lc);
         u32 base = tile_base<10>(vt);
 #pragma unroll
         for (int k = 0; k < 8; k++) tile(sm, tile_off<10>(base, k)) = a[k];
@@ -213,7 +311,7 @@ HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
     constexpr int PASS = (10 - LO) / 3;               // 1, 2, 3
     constexpr u32 S0 = 12 - (LO + 2);                 // first stage of the pass: 3, 6, 9
     char *sm = reinterpret_cast<char *>(smem);
-    const u64 nq = lc.nq, q2 = lc.q2;
+    const u64 nq = lc.nq, q3 = kBflyGrowth * lc.q;
 #pragma unroll 1
     for (int r = 0; r < 4; r++) {
         u32 vt = tid + kNttThreads * r;
@@ -221,11 +319,8 @@ HD void fwd_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
         u64 a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<LO>(base, k));
-        ct_radix8(a, lc.tw, (hb << S0) + (vt >> LO), nq, q2);
-        if (lc.fwd_mask & (1u << PASS)) {
-#pragma unroll
-            for (int k = 0; k < 8; k++) a[k] = quick_reduce(a[k], lc);
-        }
+        ct_radix8(a, lc.tw, (hb << S0) + (vt >> LO), nq, q3);
+        if (lc.fwd_mask & (1u << PASS)) quick_reduce8(a, lc);
 #pragma unroll
         for (int k = 0; k < 8; k++) tile(sm, tile_off<LO>(base, k)) = a[k];
     }
@@ -239,7 +334,7 @@ template <class Store>
 HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store st) {
     constexpr int G = Store::kGroup;
     const char *sm = reinterpret_cast<const char *>(smem);
-    const u64 nq = lc.nq, q2 = lc.q2;
+    const u64 nq = lc.nq, q3 = kBflyGrowth * lc.q;
     const tw_t *__restrict__ tw = lc.tw + ((size_t)hb << (kLogN - 1));
 #pragma unroll 1
     for (int r0 = 0; r0 < 16; r0 += G) {  // G rounds in flight: every long-latency load is issued before any math
@@ -254,7 +349,7 @@ HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store
         for (int i = 0; i < G; i++) v[i] = *reinterpret_cast<const u64x2 *>(sm + tile_pair(tid + kNttThreads * (r0 + i)));
 #pragma unroll
         for (int i = 0; i < G; i++) {
-            ct_bfly(v[i].x, v[i].y, w[i], nq, q2);
+            ct_bfly(v[i].x, v[i].y, w[i], nq, q3);
             st((u32)(tid + kNttThreads * (r0 + i)), v[i].x, v[i].y, aux[i]);
         }
     }
@@ -263,7 +358,13 @@ HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store
 // ---- inverse NTT phases (bit-reversed in, natural out), Gentleman-Sande ----
 // Inputs to a pass are < 2q; X' = X + Y doubles the bound per stage, Y' = (X - Y + c)*w with
 // c = (bound of Y) so the difference stays non-negative.  Every pass ends with quick_reduce.
+// gs_bfly: truncated quotient, y' < 3q (every use below keeps c >= the bound of y); gs_bfly_exact: y' < 2q.
 HD void gs_bfly(u64 &x, u64 &y, const tw_t &w, u64 nq, u64 c) {
+    u64 t = x + c - y;
+    x = x + y;
+    y = bfly_mul(t, w.w, w.ws, nq);
+}
+HD void gs_bfly_exact(u64 &x, u64 &y, const tw_t &w, u64 nq, u64 c) {
     u64 t = x + c - y;
     x = x + y;
     y = shoup_lazy_nq(t, w.w, w.ws, nq);
@@ -295,7 +396,7 @@ HD void inv_phase_e(int tid, u64 *smem, const LimbConst &lc, u32 hb, Load ld) {
         u32 vt = tid + kNttThreads * r;
         u64 x, y;
         ld(vt, x, y);
-        gs_bfly(x, y, lc.itw[((size_t)hb << (kLogN - 1)) + vt], nq, 2 * q2);
+        gs_bfly_exact(x, y, lc.itw[((size_t)hb << (kLogN - 1)) + vt], nq, 2 * q2);   // y is stored unreduced: < 2q
         *reinterpret_cast<u64x2 *>(sm + tile_pair(vt)) = u64x2{quick_reduce(x, lc), y};
     }
 }
@@ -311,8 +412,9 @@ HD void inv_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<LO>(base, k));
         gs_radix8(a, lc.itw, (hb << (10 - LO)) + (vt >> LO), nq, q2);
+        quick_reduce8(a, lc);
 #pragma unroll
-        for (int k = 0; k < 8; k++) tile(sm, tile_off<LO>(base, k)) = quick_reduce(a[k], lc);
+        for (int k = 0; k < 8; k++) tile(sm, tile_off<LO>(base, k)) = a[k];
     }
 }
 // Last pass: address bits 10, 11, 12 with N^-1 folded into the final stage; st(index, value in [0,q)).
@@ -358,8 +460,9 @@ HD void inv_phase_last_lazy(int tid, const u64 *smem, const LimbConst &lc, u32 h
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<10>(base, k));
         gs_radix8(a, lc.itw, hb, nq, q2);
+        quick_reduce8(a, lc);
 #pragma unroll
-        for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, quick_reduce(a[k], lc));
+        for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, a[k]);
     }
 }
 // The d outermost Gentleman-Sande stages (address bits 13..13+d-1) with N^-1 folded into the last one, on the
@@ -372,8 +475,8 @@ HD void inv_tail(u64 (&a)[1 << D], const LimbConst &lc) {
         a[0] = csub(shoup_lazy_nq(s, lc.ninv, lc.ninv_s, nq), q);
         a[1] = csub(shoup_lazy_nq(d, lc.wninv, lc.wninv_s, nq), q);
     } else if (D == 2) {
-        gs_bfly(a[0], a[1], lc.itw[2], nq, q2);   // address bit 13: a[0], a[2] < 4q; a[1], a[3] < 2q
-        gs_bfly(a[2], a[3], lc.itw[3], nq, q2);
+        gs_bfly_exact(a[0], a[1], lc.itw[2], nq, q2);   // address bit 13: a[0], a[2] < 4q; a[1], a[3] < 2q
+        gs_bfly_exact(a[2], a[3], lc.itw[3], nq, q2);
         u64 s0 = a[0] + a[2], d0 = a[0] + 2 * q2 - a[2];   // address bit 14 with N^-1
         u64 s1 = a[1] + a[3], d1 = a[1] + q2 - a[3];
         a[0] = csub(shoup_lazy_nq(s0, lc.ninv, lc.ninv_s, nq), q);

@@ -65,26 +65,27 @@ std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *
     int b = bit_length(q);
     u128 two_b = (u128)1 << b, kmax0 = ((u128)1 << (64 - b)) - 1;
     u128 delta1 = (u128)q - ((u128)1 << (b - 1)), kmax1 = ((u128)1 << (65 - b)) - 1;
-    if (two_b + kmax0 * (two_b - q) <= (u128)2 * q) {
-        lc->rmode = 0; lc->rshift = (uint32_t)b;          // q just below 2^b:  x - (x >> b) q
-    } else if (kmax1 * delta1 <= (u128)q) {
-        lc->rmode = 1; lc->rshift = (uint32_t)(b - 1);    // q just above 2^(b-1): x - (x >> (b-1)) q + q
+    if (b >= 33 && two_b + kmax0 * (two_b - q) <= (u128)2 * q) {
+        lc->rmode = 0; lc->rshift = (uint32_t)b; lc->radd = 0;   // q just below 2^b:  x - (x >> b) q
+    } else if (b >= 34 && kmax1 * delta1 <= (u128)q) {
+        lc->rmode = 1; lc->rshift = (uint32_t)(b - 1); lc->radd = q;   // q just above 2^(b-1): x - (x >> (b-1)) q + q
     } else {
         lc->rmode = 2; lc->rshift = 0;                    // anything else: Barrett quotient by mulhi
     }
-    // forward NTT: every Harvey stage adds 2q to the bound; reduce at the end of pass p-1 when pass p would overflow.
+    // forward NTT: every stage adds 3q to the bound (truncated Shoup quotient: products < 3q); reduce at the end of
+    // pass p-1 when pass p would overflow.
     // The tile's loader has already applied d stages (HeadLoad): inputs are below (1 + 2d) q.
     const uint64_t H = UINT64_MAX / q;
     const int stages[5] = {3, 3, 3, 3, 1};
     uint64_t B = 1 + 2 * (uint64_t)d;
     lc->fwd_mask = 0;
     for (int pass = 0; pass < 5; pass++) {
-        if (B + 2 * stages[pass] > H) {
-            if (pass == 0 || 2 + 2 * (uint64_t)stages[pass] > H) return "modulus leaves no headroom for lazy butterflies";
+        if (B + kBflyGrowth * stages[pass] > H) {
+            if (pass == 0 || 2 + kBflyGrowth * (uint64_t)stages[pass] > H) return "modulus leaves no headroom for lazy butterflies";
             lc->fwd_mask |= 1u << (pass - 1);
             B = 2;
         }
-        B += 2 * stages[pass];
+        B += kBflyGrowth * stages[pass];
     }
     if (H < 16) return "modulus leaves no headroom for the inverse transform";
     return "";

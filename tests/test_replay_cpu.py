@@ -15,7 +15,8 @@ def vp(a):
 
 
 def test_reduction_schedule(emu, emu_ctx):
-    # 60-bit q0: one mid-transform reduction (end of pass 1), shift-type quick reduce;
+    # 60-bit q0 (bounds grow 2q per stage, 16q fit in 64 bits): one mid-transform reduction (end of pass 1),
+    # shift-type quick reduce;
     # 52-bit q1: no mid reduction, "just above a power of two" quick reduce
     h = emu_ctx["pybind"]
     assert (emu.L.emu_fwd_mask(h, 0), emu.L.emu_rmode(h, 0)) == (2, 0)
