@@ -77,6 +77,13 @@ def lib() -> C.CDLL:
         "shelfi_compute_weighted_average_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, vp, u64,
                                                             u64p]),
         "shelfi_decrypt": (C.c_int, [vp, vp, u64, u64, vp]),
+        "shelfi_encrypt_layers": (C.c_int, [vp, C.POINTER(vp), u64p, u32, C.POINTER(vp), u64p, u64p, u64p]),
+        "shelfi_compute_weighted_average_layers": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, u32,
+                                                             C.POINTER(vp), u64p, u64p, u64p]),
+        "shelfi_decrypt_layers": (C.c_int, [vp, C.POINTER(vp), u64p, u64p, u32, vp]),
+        "shelfi_encrypt_layers_into": (C.c_int, [vp, C.POINTER(vp), u64p, u32, vp, u64, u64p, u64p, u64p]),
+        "shelfi_compute_weighted_average_layers_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, u32,
+                                                                  vp, u64, u64p, u64p, u64p]),
         "shelfi_free": (None, [vp]),
         "shelfi_host_alloc": (vp, [C.c_size_t]),
         "shelfi_host_free": (None, [vp]),
@@ -104,13 +111,107 @@ def lib() -> C.CDLL:
     return L
 
 
-def _as_bytes(blob) -> bytes:
+def _as_bytes(blob):
     # pybind11 2.6.1's permissive std::string caster takes bytes or str (ckks.cpp:170,276)
+    if isinstance(blob, PinnedBlob):
+        return blob
     if isinstance(blob, (bytes, bytearray, memoryview)):
         return bytes(blob) if not isinstance(blob, bytes) else blob
     if isinstance(blob, str):
         return blob.encode("latin-1")
     raise TypeError("ciphertext blob must be bytes or str")
+
+
+def _new_bytes(n: int) -> bytes:
+    """An uninitialised bytes object of n bytes for the library to fill in place (what pybind's py::bytes(ptr, n)
+    does in one step): saves the malloc + copy + free of going through a library-owned buffer."""
+    f = C.pythonapi.PyBytes_FromStringAndSize
+    f.restype, f.argtypes = C.py_object, [C.c_char_p, C.c_ssize_t]
+    return f(None, n)
+
+
+def _addr(buf) -> int:
+    """Address of a bytes / PinnedBlob / buffer-protocol object's memory (borrowed for the duration of the call)."""
+    if isinstance(buf, PinnedBlob):
+        return buf.address
+    if isinstance(buf, bytes):
+        return C.cast(C.c_char_p(buf), C.c_void_p).value
+    return np.frombuffer(buf, dtype=np.uint8).ctypes.data
+
+
+class _PinnedPool:
+    """Page-locked host buffers are expensive to create (cudaHostAlloc pins at a few GB/s) and cheap to reuse:
+    freed blobs go back to a size-keyed free list."""
+
+    def __init__(self):
+        self.free = {}
+
+    def take(self, n: int):
+        cap = max(4096, 1 << (int(n) - 1).bit_length()) if n > (1 << 20) else max(4096, int(n))
+        lst = self.free.get(cap)
+        if lst:
+            return lst.pop(), cap
+        p = lib().shelfi_host_alloc(cap)
+        if not p:
+            raise MemoryError(f"cudaHostAlloc({cap}) failed")
+        return p, cap
+
+    def give(self, p, cap):
+        self.free.setdefault(cap, []).append(p)
+
+
+_pool = _PinnedPool()
+
+
+class PinnedBlob:
+    """A serialized ciphertext vector held in page-locked host memory (opt-in: ``CKKS(..., pinned=True)``).
+
+    Bytes-like: ``len``, ``bytes(b)``, ``memoryview(b)`` / the buffer protocol through ``b.array`` (numpy uint8 view),
+    equality with ``bytes``.  Passing it back to ``computeWeightedAverage`` / ``decrypt`` moves it over PCIe at the
+    link rate instead of through the driver's pageable staging path; ``bytes(b)`` gives the reference's exact type
+    when the payload has to leave the process."""
+
+    def __init__(self, n: int, _parent=None, _offset: int = 0):
+        if _parent is None:
+            self._p, self._cap = _pool.take(n)
+        else:   # a slice of another blob's buffer (the per-layer results of the *_layers calls); keeps it alive
+            self._p, self._cap = _parent._p + _offset, 0
+        self._parent = _parent
+        self._n = int(n)
+        self.array = np.ctypeslib.as_array((C.c_uint8 * self._n).from_address(self._p))
+
+    def view(self, offset: int, n: int) -> "PinnedBlob":
+        return PinnedBlob(n, self, offset)
+
+    @property
+    def address(self) -> int:
+        return self._p
+
+    def __len__(self):
+        return self._n
+
+    def __bytes__(self):
+        return C.string_at(self._p, self._n)
+
+    tobytes = __bytes__
+
+    def __eq__(self, other):
+        if isinstance(other, PinnedBlob):
+            return self._n == other._n and bool(np.array_equal(self.array, other.array))
+        if isinstance(other, (bytes, bytearray, memoryview)):
+            return self._n == len(other) and bytes(self) == bytes(other)
+        return NotImplemented
+
+    def __hash__(self):
+        return hash((self._p, self._n))
+
+    def __del__(self):
+        p = getattr(self, "_p", None)
+        if p and _lib is not None:
+            self.array = None
+            if self._parent is None:
+                _pool.give(p, self._cap)
+            self._p = self._parent = None
 
 
 class Scheme:
@@ -124,8 +225,9 @@ class CKKS(Scheme):
     """CKKS helper with the reference's constructor and methods (binding.cpp:18-31)."""
 
     def __init__(self, scheme: str = "ckks", batchSize: int = 4096, scaleFactorBits: int = 52,
-                 cryptodir: str = "../resources/cryptoparams/", device: int | None = None):
+                 cryptodir: str = "../resources/cryptoparams/", device: int | None = None, pinned: bool = False):
         super().__init__(scheme)
+        self.pinned = bool(pinned) or os.environ.get("SHELFI_PINNED", "0") == "1"   # return PinnedBlob objects instead of bytes (extension; see PinnedBlob)
         self.batchSize, self.scaleFactorBits, self.cryptodir = int(batchSize), int(scaleFactorBits), str(cryptodir)
         if device is None:
             device = int(os.environ.get("SHELFI_DEVICE", os.environ.get("LOCAL_RANK", "0")))
@@ -185,12 +287,16 @@ class CKKS(Scheme):
     def encrypt(self, data_array) -> bytes:
         """ckks.cpp:61-104: any array-like convertible to float64 (flattened) -> serialized ciphertext vector."""
         x = np.ascontiguousarray(data_array, dtype=np.float64).ravel()
-        out, n = C.c_void_p(), C.c_uint64()
-        self._check(lib().shelfi_encrypt(self._h, x.ctypes.data, x.size, C.byref(out), C.byref(n)))
-        try:
-            return C.string_at(out.value, n.value)
-        finally:
-            lib().shelfi_free(out)
+        cap = self.blob_size(self.num_ciphertexts(x.size)) if x.size else 0
+        if cap == 0:   # not loaded / empty input: let the library report it
+            out, n = C.c_void_p(), C.c_uint64()
+            self._check(lib().shelfi_encrypt(self._h, x.ctypes.data, x.size, C.byref(out), C.byref(n)))
+            raise ShelfiError(-1, "encrypt produced no ciphertext")
+        dst = PinnedBlob(cap) if self.pinned else _new_bytes(cap)
+        n = C.c_uint64()
+        self._check(lib().shelfi_encrypt_into(self._h, x.ctypes.data, x.size, _addr(dst), cap, C.byref(n)))
+        assert n.value == cap
+        return dst
 
     def computeWeightedAverage(self, learner_data, scaling_factors) -> bytes:
         """ckks.cpp:264-320: sum_i float32(w_i) * ct_i over learners; size mismatch prints and returns b""."""
@@ -200,10 +306,17 @@ class CKKS(Scheme):
             return b""
         blobs = [_as_bytes(b) for b in learner_data]
         k = len(blobs)
-        ptrs = (C.c_void_p * k)(*[C.cast(C.c_char_p(b), C.c_void_p) for b in blobs])
+        ptrs = (C.c_void_p * k)(*[_addr(b) for b in blobs])
         lens = (C.c_uint64 * k)(*[len(b) for b in blobs])
         w = (C.c_float * k)(*[float(v) for v in scaling_factors])
-        out, n = C.c_void_p(), C.c_uint64()
+        cap = len(blobs[0]) if k else 0   # the result has learner 0's layout (ckks.cpp:291-292)
+        if cap:
+            dst = PinnedBlob(cap) if self.pinned else _new_bytes(cap)
+            n = C.c_uint64()
+            rc = lib().shelfi_compute_weighted_average_into(self._h, ptrs, lens, w, k, _addr(dst), cap, C.byref(n))
+            if rc == 0 and n.value == cap:
+                return dst
+        out, n = C.c_void_p(), C.c_uint64()   # errors, or a result of another size: the allocating call reports / returns it
         self._check(lib().shelfi_compute_weighted_average(self._h, ptrs, lens, w, k, C.byref(out), C.byref(n)))
         try:
             return C.string_at(out.value, n.value)
@@ -215,8 +328,62 @@ class CKKS(Scheme):
         blob = _as_bytes(learner_data)
         n = int(data_dimensions)
         out = np.empty(n, dtype=np.float64)
-        self._check(lib().shelfi_decrypt(self._h, blob, len(blob), n, out.ctypes.data))
+        self._check(lib().shelfi_decrypt(self._h, _addr(blob), len(blob), n, out.ctypes.data))
         return out
+
+    # ---- layer-wise callers (benchmark.py:490-493, benchmark_selection.py:152-193) in one call each ----
+    def encrypt_layers(self, arrays) -> list:
+        """[encrypt(a) for a in arrays] with one host->device copy, one stream of launches, one copy back."""
+        flat = [np.ascontiguousarray(a, dtype=np.float64).ravel() for a in arrays]
+        n = len(flat)
+        xp = (C.c_void_p * n)(*[a.ctypes.data for a in flat])
+        ll = (C.c_uint64 * n)(*[a.size for a in flat])
+        offs, lens, total = (C.c_uint64 * n)(), (C.c_uint64 * n)(), C.c_uint64()
+        cap = sum((self.blob_size(self.num_ciphertexts(a.size)) + 7) // 8 * 8 for a in flat if a.size)
+        dst = PinnedBlob(max(cap, 8)) if self.pinned else _new_bytes(max(cap, 8))
+        self._check(lib().shelfi_encrypt_layers_into(self._h, xp, ll, n, _addr(dst), cap, offs, lens,
+                                                     C.byref(total)))
+        return self._split(dst, offs, lens, n)
+
+    def _split(self, dst, offs, lens, n) -> list:
+        if self.pinned:
+            return [dst.view(offs[i], lens[i]) for i in range(n)]
+        mv = memoryview(dst)
+        return [bytes(mv[offs[i]:offs[i] + lens[i]]) for i in range(n)]
+
+    def computeWeightedAverage_layers(self, learner_layers, scaling_factors) -> list:
+        """learner_layers[i][s] = blob of learner i, layer s -> [computeWeightedAverage over learners for each layer]."""
+        learner_layers, scaling_factors = [list(l) for l in learner_layers], list(scaling_factors)
+        if len(learner_layers) != len(scaling_factors):
+            print("Error: learner_data and scaling_factors size mismatch")  # ckks.cpp:266
+            return []
+        k, n = len(learner_layers), len(learner_layers[0]) if learner_layers else 0
+        if any(len(l) != n for l in learner_layers):
+            raise ValueError("every learner must supply the same number of layers")
+        blobs = [_as_bytes(b) for l in learner_layers for b in l]
+        ptrs = (C.c_void_p * (k * n))(*[_addr(b) for b in blobs])
+        blens = (C.c_uint64 * (k * n))(*[len(b) for b in blobs])
+        w = (C.c_float * k)(*[float(v) for v in scaling_factors])
+        offs, lens, total = (C.c_uint64 * n)(), (C.c_uint64 * n)(), C.c_uint64()
+        cap = sum((len(b) + 7) // 8 * 8 for b in blobs[:n])   # results have learner 0's layout (ckks.cpp:291-292)
+        dst = PinnedBlob(max(cap, 8)) if self.pinned else _new_bytes(max(cap, 8))
+        self._check(lib().shelfi_compute_weighted_average_layers_into(self._h, ptrs, blens, w, k, n, _addr(dst), cap, offs,
+                                                                      lens, C.byref(total)))
+        return self._split(dst, offs, lens, n)
+
+    def decrypt_layers(self, blobs, data_dimensions) -> list:
+        """[decrypt(b, n) for b, n in zip(blobs, data_dimensions)] in one pass; returns one float64 array per layer."""
+        blobs = [_as_bytes(b) for b in blobs]
+        dims = [int(d) for d in data_dimensions]
+        n = len(blobs)
+        if n != len(dims):
+            raise ValueError("one data_dimensions entry per blob")
+        ptrs = (C.c_void_p * n)(*[_addr(b) for b in blobs])
+        blens = (C.c_uint64 * n)(*[len(b) for b in blobs])
+        dd = (C.c_uint64 * n)(*dims)
+        out = np.empty(sum(dims), dtype=np.float64)
+        self._check(lib().shelfi_decrypt_layers(self._h, ptrs, blens, dd, n, out.ctypes.data))
+        return np.split(out, np.cumsum(dims)[:-1]) if n else []
 
     encrypt_cpp = encrypt
     decrypt_cpp = decrypt

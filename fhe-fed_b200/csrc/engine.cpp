@@ -366,23 +366,43 @@ void write_segments(const wire::BlobPlan &plan, uint8_t *dst) {
     for (const auto &seg : plan.segments) std::memcpy(dst + seg.offset, seg.bytes.data(), seg.bytes.size());
 }
 
-int encrypt_host(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint64_t cap, uint8_t **alloc_out,
-                 uint64_t *blob_len) {
+// Where layer s of a multi-layer call lives: its ciphertexts inside the dense batch, its blob inside the image.
+struct LayerSlot {
+    uint64_t n = 0, n_ct = 0, ct0 = 0;      // values, ciphertexts, first ciphertext in the concatenated dense batch
+    uint64_t x0 = 0;                        // first value in the concatenated plaintext vector
+    uint64_t off = 0;                       // byte offset of the blob in the image (8-byte aligned)
+    wire::BlobPlan plan;
+};
+uint64_t align8(uint64_t v) { return (v + 7) & ~(uint64_t)7; }
+
+// ckks.cpp:61-104 for n_layers independent vectors xs[s]: copies and encrypt kernels of all layers queued on one
+// stream, one D2H.  n_layers == 1 is CKKS::encrypt.  Blob s lands at dst + offsets[s], lens[s] bytes.
+int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_len, uint32_t n_layers, uint8_t *dst,
+                 uint64_t cap, uint8_t **alloc_out, uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
     int rcode = check_stage(h, true, false);
     if (rcode) return rcode;
-    if (!x || !blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
-    if (n == 0) return fail(h, SHELFI_ERR_ARG, "empty input (undefined behaviour in the reference, ckks.cpp:66,95)");
-    const uint64_t n_ct = (n + h->batch - 1) / h->batch;
+    if (!xs || !layer_len || !lens || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
+    for (uint32_t s = 0; s < n_layers; s++)
+        if (!xs[s]) return fail(h, SHELFI_ERR_ARG, "null argument");
     std::vector<wire::CiphertextMeta> meta(1);
     meta[0].depth = 1; meta[0].level = 0; meta[0].encoding_type = 4;
     meta[0].scaling_factor = (double)h->ctx.modulus[h->ctx.limbs - 1];
     std::memcpy(meta[0].tag, h->key_tag.c_str(), 32);
-    wire::BlobPlan plan = wire::plan_ciphertext_blob(h->ctx, n_ct, meta);
+    std::vector<LayerSlot> slot(n_layers);
+    uint64_t n = 0, n_ct = 0, image = 0;
+    for (uint32_t s = 0; s < n_layers; s++) {
+        if (layer_len[s] == 0) return fail(h, SHELFI_ERR_ARG, "empty input (undefined behaviour in the reference, ckks.cpp:66,95)");
+        slot[s].n = layer_len[s]; slot[s].n_ct = (layer_len[s] + h->batch - 1) / h->batch;
+        slot[s].x0 = n; slot[s].ct0 = n_ct; slot[s].off = image;
+        slot[s].plan = wire::plan_ciphertext_blob(h->ctx, slot[s].n_ct, meta);
+        n += slot[s].n; n_ct += slot[s].n_ct; image = align8(image + slot[s].plan.size);
+    }
+    const uint64_t total = n_layers == 1 ? slot[0].plan.size : image;
     if (alloc_out) {
-        dst = static_cast<uint8_t *>(std::malloc(plan.size));
+        dst = static_cast<uint8_t *>(std::malloc(total));
         if (!dst) return fail(h, SHELFI_ERR_ARG, "out of host memory");
-    } else if (!dst || cap < plan.size) {
-        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
+    } else if (!dst || cap < total) {
+        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(total) + " bytes");
     }
     cudaStream_t s = h->stream;
     const uint64_t ct_words = 2ull * h->ctx.limbs * h->ctx.ring_dim;
@@ -394,127 +414,185 @@ int encrypt_host(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint
     } while (0)
     CUB(h->s_x.reserve(n * sizeof(double)));
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
-    CUB(h->s_image.reserve(image_bytes(plan.size)));
-    CUB(cudaMemcpyAsync(h->s_x.p, x, n * sizeof(double), cudaMemcpyHostToDevice, s));
-    if ((rcode = encrypt_dense(h, h->s_x.as<double>(), n, 0, h->s_dense.as<u64>(), s))) return bail(rcode);
-    timed(h, kKPack, s, [&] {
-        launch_pack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride), h->s_dense.as<u64>(),
-                    h->s_image.as<u64>(), n_ct, s);
-    });
+    CUB(h->s_image.reserve(image_bytes(image)));
+    for (uint32_t i = 0; i < n_layers; i++)
+        CUB(cudaMemcpyAsync(h->s_x.as<double>() + slot[i].x0, xs[i], slot[i].n * sizeof(double), cudaMemcpyHostToDevice, s));
+    for (const LayerSlot &ls : slot) {   // every layer is its own ciphertext vector: sampler index restarts at 0
+        if ((rcode = encrypt_dense(h, h->s_x.as<double>() + ls.x0, ls.n, 0, h->s_dense.as<u64>() + ls.ct0 * ct_words, s)))
+            return bail(rcode);
+        timed(h, kKPack, s, [&] {
+            launch_pack(h->rc, to_runs(h, ls.plan.run0, ls.plan.run1, ls.plan.stride), h->s_dense.as<u64>() + ls.ct0 * ct_words,
+                        h->s_image.as<u64>() + ls.off / 8, ls.n_ct, s);
+        });
+    }
     CUB(cudaGetLastError());
-    CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
+    CUB(cudaMemcpyAsync(dst, h->s_image.p, total, cudaMemcpyDeviceToHost, s));
     CUB(cudaStreamSynchronize(s));
-    write_segments(plan, dst);
+    for (uint32_t i = 0; i < n_layers; i++) {
+        write_segments(slot[i].plan, dst + slot[i].off);
+        if (offsets) offsets[i] = slot[i].off;
+        lens[i] = slot[i].plan.size;
+    }
     if (alloc_out) *alloc_out = dst;
-    *blob_len = plan.size;
+    if (total_len) *total_len = total;
     return 0;
 }
 
-int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *lens, const float *w, uint32_t k,
-              uint8_t *dst, uint64_t cap, uint8_t **alloc_out, uint64_t *blob_len) {
+// ckks.cpp:264-320 for n_layers ciphertext vectors per learner (blobs[i * n_layers + s] = learner i, layer s).
+// n_layers == 1 is CKKS::computeWeightedAverage.  Learner i+1 streams in over PCIe while learner i is folded into the
+// resident accumulator; one D2H returns all result blobs (blob s at dst + offsets[s]).
+int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens, const float *w, uint32_t k,
+              uint32_t n_layers, uint8_t *dst, uint64_t cap, uint8_t **alloc_out, uint64_t *offsets, uint64_t *lens,
+              uint64_t *total_len) {
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
-    if (!blobs || !lens || !w || !blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    if (!blobs || !blob_lens || !w || !lens || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
     if (k == 0) return fail(h, SHELFI_ERR_ARG, "no learners");
     const uint32_t L = h->ctx.limbs;
     const double sf0 = (double)h->ctx.modulus[L - 1];
-    std::vector<wire::BlobMap> maps(k);
+    std::vector<wire::BlobMap> maps((size_t)k * n_layers);
+    std::vector<uint64_t> in_off((size_t)k * n_layers);   // where each input blob sits in its learner's image
+    size_t max_image = 0;
     for (uint32_t i = 0; i < k; i++) {  // ckks.cpp:278-281 Deserialize, minus the payload copy
-        if (!blobs[i]) return fail(h, SHELFI_ERR_ARG, "null blob");
-        std::string e = wire::map_ciphertext_blob(blobs[i], lens[i], false, &maps[i]);
-        if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, "learner " + std::to_string(i) + ": " + e);
-        if (!same_ring(maps[i].ctx, h->ctx))
-            return fail(h, SHELFI_ERR_PARAMS, "learner " + std::to_string(i) + ": ciphertext parameters differ from the loaded context");
-        if (maps[i].n_ct != maps[0].n_ct)
-            return fail(h, SHELFI_ERR_PARAMS, "learner " + std::to_string(i) + ": ciphertext count differs");
-        for (const auto &m : maps[i].meta)
-            if (m.depth != 1 || m.level != 0)
-                return fail(h, SHELFI_ERR_UNSUPPORTED, "learner " + std::to_string(i) + ": only fresh depth-1 level-0 ciphertexts are supported");
+        uint64_t img = 0;
+        for (uint32_t s = 0; s < n_layers; s++) {
+            const size_t id = (size_t)i * n_layers + s;
+            const std::string who = "learner " + std::to_string(i) + (n_layers > 1 ? " layer " + std::to_string(s) : "");
+            if (!blobs[id]) return fail(h, SHELFI_ERR_ARG, "null blob");
+            std::string e = wire::map_ciphertext_blob(blobs[id], blob_lens[id], false, &maps[id]);
+            if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, who + ": " + e);
+            if (!same_ring(maps[id].ctx, h->ctx))
+                return fail(h, SHELFI_ERR_PARAMS, who + ": ciphertext parameters differ from the loaded context");
+            if (maps[id].n_ct != maps[s].n_ct) return fail(h, SHELFI_ERR_PARAMS, who + ": ciphertext count differs");
+            for (const auto &m : maps[id].meta)
+                if (m.depth != 1 || m.level != 0)
+                    return fail(h, SHELFI_ERR_UNSUPPORTED, who + ": only fresh depth-1 level-0 ciphertexts are supported");
+            in_off[id] = img;
+            img = align8(img + blob_lens[id]);
+        }
+        max_image = std::max(max_image, image_bytes(img));
     }
-    const uint64_t n_ct = maps[0].n_ct;
-    std::vector<wire::CiphertextMeta> meta = maps[0].meta;  // ckks.cpp:291-292: result starts as learner 0's vector
-    for (auto &m : meta) { m.depth += 1; m.scaling_factor *= sf0; }  // [PAL] EvalMult(ct, double), no rescale
-    wire::BlobPlan plan = wire::plan_ciphertext_blob(maps[0].ctx, n_ct, meta);
+    std::vector<LayerSlot> slot(n_layers);
+    uint64_t n_ct = 0, image = 0;
+    for (uint32_t s = 0; s < n_layers; s++) {
+        std::vector<wire::CiphertextMeta> meta = maps[s].meta;  // ckks.cpp:291-292: result starts as learner 0's vector
+        for (auto &m : meta) { m.depth += 1; m.scaling_factor *= sf0; }  // [PAL] EvalMult(ct, double), no rescale
+        slot[s].n_ct = maps[s].n_ct; slot[s].ct0 = n_ct; slot[s].off = image;
+        slot[s].plan = wire::plan_ciphertext_blob(maps[s].ctx, slot[s].n_ct, meta);
+        n_ct += slot[s].n_ct; image = align8(image + slot[s].plan.size);
+    }
+    const uint64_t total = n_layers == 1 ? slot[0].plan.size : image;
     if (alloc_out) {
-        dst = static_cast<uint8_t *>(std::malloc(plan.size));
+        dst = static_cast<uint8_t *>(std::malloc(total));
         if (!dst) return fail(h, SHELFI_ERR_ARG, "out of host memory");
-    } else if (!dst || cap < plan.size) {
-        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
+    } else if (!dst || cap < total) {
+        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(total) + " bytes");
     }
     auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
-    cudaStream_t s = h->stream, cs = h->copy_stream;
+    cudaStream_t st = h->stream, cs = h->copy_stream;
     const uint64_t ct_words = 2ull * L * h->ctx.ring_dim;
-    size_t max_image = 0;
-    for (uint32_t i = 0; i < k; i++) max_image = std::max(max_image, image_bytes(lens[i]));
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
-    CUB(h->s_image.reserve(std::max(max_image, image_bytes(plan.size))));
+    CUB(h->s_image.reserve(std::max(max_image, image_bytes(image))));
     CUB(h->s_image2.reserve(max_image));
     DeviceBuffer *img[2] = {&h->s_image, &h->s_image2};
-    // learner i+1 streams in over PCIe while learner i is folded into the accumulator
     for (uint32_t i = 0; i < k; i++) {
         int b = i & 1;
         if (i >= 2) CUB(cudaStreamWaitEvent(cs, h->ev_done[b], 0));
-        CUB(cudaMemcpyAsync(img[b]->p, blobs[i], lens[i], cudaMemcpyHostToDevice, cs));
+        for (uint32_t s = 0; s < n_layers; s++) {
+            const size_t id = (size_t)i * n_layers + s;
+            CUB(cudaMemcpyAsync(img[b]->as<uint8_t>() + in_off[id], blobs[id], blob_lens[id], cudaMemcpyHostToDevice, cs));
+        }
         CUB(cudaEventRecord(h->ev_copy[b], cs));
-        CUB(cudaStreamWaitEvent(s, h->ev_copy[b], 0));
+        CUB(cudaStreamWaitEvent(st, h->ev_copy[b], 0));
         int64_t sc = weight_constant(h, w[i]);
         LimbScalars cs_l{};
         for (uint32_t l = 0; l < L; l++) cs_l.c[l] = nt::signed_mod(sc, h->ctx.modulus[l]);
-        timed(h, kKUnpackScaleAcc, s, [&] {
-            launch_unpack_scale_accumulate(h->rc, to_runs(h, maps[i].run0, maps[i].run1, maps[i].stride),
-                                           img[b]->as<u64>(), cs_l, i == 0 ? 1u : 0u, h->s_dense.as<u64>(), n_ct, s);
-        });
+        for (uint32_t s = 0; s < n_layers; s++) {
+            const size_t id = (size_t)i * n_layers + s;
+            timed(h, kKUnpackScaleAcc, st, [&] {
+                launch_unpack_scale_accumulate(h->rc, to_runs(h, maps[id].run0, maps[id].run1, maps[id].stride),
+                                               img[b]->as<u64>() + in_off[id] / 8, cs_l, i == 0 ? 1u : 0u,
+                                               h->s_dense.as<u64>() + slot[s].ct0 * ct_words, slot[s].n_ct, st);
+            });
+        }
         CUB(cudaGetLastError());
-        CUB(cudaEventRecord(h->ev_done[b], s));
+        CUB(cudaEventRecord(h->ev_done[b], st));
     }
-    timed(h, kKPack, s, [&] {
-        launch_pack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride), h->s_dense.as<u64>(), h->s_image.as<u64>(), n_ct, s);
-    });
+    for (const LayerSlot &ls : slot)
+        timed(h, kKPack, st, [&] {
+            launch_pack(h->rc, to_runs(h, ls.plan.run0, ls.plan.run1, ls.plan.stride), h->s_dense.as<u64>() + ls.ct0 * ct_words,
+                        h->s_image.as<u64>() + ls.off / 8, ls.n_ct, st);
+        });
     CUB(cudaGetLastError());
-    CUB(cudaMemcpyAsync(dst, h->s_image.p, plan.size, cudaMemcpyDeviceToHost, s));
-    CUB(cudaStreamSynchronize(s));
-    write_segments(plan, dst);
+    CUB(cudaMemcpyAsync(dst, h->s_image.p, total, cudaMemcpyDeviceToHost, st));
+    CUB(cudaStreamSynchronize(st));
+    for (uint32_t s = 0; s < n_layers; s++) {
+        write_segments(slot[s].plan, dst + slot[s].off);
+        if (offsets) offsets[s] = slot[s].off;
+        lens[s] = slot[s].plan.size;
+    }
     if (alloc_out) *alloc_out = dst;
-    *blob_len = plan.size;
+    if (total_len) *total_len = total;
     return 0;
 }
 
-int decrypt_host(shelfi_ckks *h, const uint8_t *blob, uint64_t len, uint64_t n, double *out) {
+// ckks.cpp:170-213 for n_layers ciphertext vectors: out = concatenation of the layers' data_dimensions[s] values.
+// n_layers == 1 is CKKS::decrypt.
+int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens, const uint64_t *dims,
+                 uint32_t n_layers, double *out) {
     int rcode = check_stage(h, false, true);
     if (rcode) return rcode;
-    if (!blob || !out) return fail(h, SHELFI_ERR_ARG, "null argument");
-    wire::BlobMap map;
-    std::string e = wire::map_ciphertext_blob(blob, len, false, &map);
-    if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, e);
-    if (!same_ring(map.ctx, h->ctx)) return fail(h, SHELFI_ERR_PARAMS, "ciphertext parameters differ from the loaded context");
-    const uint64_t n_ct = map.n_ct, batch = h->batch;
-    if (n == 0 || n > n_ct * batch || n + batch <= n_ct * batch)
-        return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
+    if (!blobs || !blob_lens || !dims || !out || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
+    const uint64_t batch = h->batch;
+    std::vector<wire::BlobMap> maps(n_layers);
+    std::vector<LayerSlot> slot(n_layers);
+    uint64_t n = 0, n_ct = 0, image = 0, max_ct = 0;
+    for (uint32_t s = 0; s < n_layers; s++) {
+        if (!blobs[s]) return fail(h, SHELFI_ERR_ARG, "null blob");
+        std::string e = wire::map_ciphertext_blob(blobs[s], blob_lens[s], false, &maps[s]);
+        if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, e);
+        if (!same_ring(maps[s].ctx, h->ctx)) return fail(h, SHELFI_ERR_PARAMS, "ciphertext parameters differ from the loaded context");
+        const uint64_t c = maps[s].n_ct;
+        if (dims[s] == 0 || dims[s] > c * batch || dims[s] + batch <= c * batch)
+            return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
+        slot[s].n = dims[s]; slot[s].n_ct = c; slot[s].x0 = n; slot[s].ct0 = n_ct; slot[s].off = image;
+        n += dims[s]; n_ct += c; image = align8(image + blob_lens[s]);
+        max_ct = std::max(max_ct, c);
+    }
     const uint32_t L = h->ctx.limbs;
-    const uint64_t ct_words = 2ull * L * h->ctx.ring_dim;
-    cudaStream_t s = h->stream;
-    CU(h->s_image.reserve(image_bytes(len)));
+    const uint64_t N = h->ctx.ring_dim, ct_words = 2ull * L * N;
+    cudaStream_t st = h->stream;
+    CU(h->s_image.reserve(image_bytes(image)));
     CU(h->s_dense.reserve(n_ct * ct_words * 8));
     CU(h->s_out.reserve(n * sizeof(double)));
-    CU(cudaMemcpyAsync(h->s_image.p, blob, len, cudaMemcpyHostToDevice, s));
-    timed(h, kKUnpack, s, [&] {
-        launch_unpack(h->rc, to_runs(h, map.run0, map.run1, map.stride), h->s_image.as<u64>(), h->s_dense.as<u64>(), n_ct, s);
-    });
-    CU(cudaGetLastError());
-    // ciphertexts usually share one scaling factor; split the launch where they do not
-    uint64_t j0 = 0;
-    while (j0 < n_ct) {
-        uint64_t j1 = j0 + 1;
-        while (j1 < n_ct && map.meta[j1].scaling_factor == map.meta[j0].scaling_factor) j1++;
-        uint64_t first = j0 * batch, last = std::min(n, j1 * batch);
-        if ((rcode = decrypt_dense(h, h->s_dense.as<u64>() + j0 * ct_words, j1 - j0, map.meta[j0].scaling_factor,
-                                   h->s_out.as<double>() + first, last - first, s)))
-            return rcode;
-        CU(cudaStreamSynchronize(s));  // decrypt_dense reuses one coefficient scratch
-        j0 = j1;
+    // decrypt_dense's scratch, sized once so that no launch of this call waits on a reallocation
+    CU(h->s_coeff.reserve(max_ct * L * N * sizeof(uint64_t)));
+    if (general_decode(h)) {
+        CU(h->s_vals.reserve(max_ct * N * sizeof(double)));
+        if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(max_ct * (size_t)h->ec.slots * sizeof(cplx)));
     }
-    CU(cudaMemcpyAsync(out, h->s_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
+    for (uint32_t s = 0; s < n_layers; s++) {
+        const LayerSlot &ls = slot[s];
+        CU(cudaMemcpyAsync(h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], cudaMemcpyHostToDevice, st));
+        u64 *dense = h->s_dense.as<u64>() + ls.ct0 * ct_words;
+        timed(h, kKUnpack, st, [&] {
+            launch_unpack(h->rc, to_runs(h, maps[s].run0, maps[s].run1, maps[s].stride), h->s_image.as<u64>() + ls.off / 8, dense,
+                          ls.n_ct, st);
+        });
+        CU(cudaGetLastError());
+        // ciphertexts usually share one scaling factor; split the launch where they do not
+        for (uint64_t j0 = 0; j0 < ls.n_ct;) {
+            uint64_t j1 = j0 + 1;
+            while (j1 < ls.n_ct && maps[s].meta[j1].scaling_factor == maps[s].meta[j0].scaling_factor) j1++;
+            uint64_t first = j0 * batch, last = std::min(ls.n, j1 * batch);
+            if ((rcode = decrypt_dense(h, dense + j0 * ct_words, j1 - j0, maps[s].meta[j0].scaling_factor,
+                                       h->s_out.as<double>() + ls.x0 + first, last - first, st)))
+                return rcode;
+            j0 = j1;
+        }
+    }
+    CU(cudaMemcpyAsync(out, h->s_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -787,30 +865,68 @@ int64_t shelfi_weight_constant(const shelfi_ckks *h, float w) { return h && h->h
 int shelfi_encrypt(shelfi_ckks *h, const double *x, uint64_t n, uint8_t **blob, uint64_t *blob_len) {
     if (!h || !blob) return SHELFI_ERR_ARG;
     std::lock_guard<std::mutex> lock(h->mu);
-    return encrypt_host(h, x, n, nullptr, 0, blob, blob_len);
+    return encrypt_host(h, &x, &n, 1, nullptr, 0, blob, nullptr, blob_len, nullptr);
 }
 int shelfi_encrypt_into(shelfi_ckks *h, const double *x, uint64_t n, uint8_t *dst, uint64_t cap, uint64_t *blob_len) {
     if (!h) return SHELFI_ERR_ARG;
     std::lock_guard<std::mutex> lock(h->mu);
-    return encrypt_host(h, x, n, dst, cap, nullptr, blob_len);
+    if (!blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    return encrypt_host(h, &x, &n, 1, dst, cap, nullptr, nullptr, blob_len, nullptr);
 }
 int shelfi_compute_weighted_average(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                                     const float *weights, uint32_t k, uint8_t **blob, uint64_t *blob_len) {
     if (!h || !blob) return SHELFI_ERR_ARG;
     std::lock_guard<std::mutex> lock(h->mu);
-    return wavg_host(h, blobs, blob_lens, weights, k, nullptr, 0, blob, blob_len);
+    if (!blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    return wavg_host(h, blobs, blob_lens, weights, k, 1, nullptr, 0, blob, nullptr, blob_len, nullptr);
 }
 int shelfi_compute_weighted_average_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                                          const float *weights, uint32_t k, uint8_t *dst, uint64_t cap,
                                          uint64_t *blob_len) {
     if (!h) return SHELFI_ERR_ARG;
     std::lock_guard<std::mutex> lock(h->mu);
-    return wavg_host(h, blobs, blob_lens, weights, k, dst, cap, nullptr, blob_len);
+    if (!blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    return wavg_host(h, blobs, blob_lens, weights, k, 1, dst, cap, nullptr, nullptr, blob_len, nullptr);
 }
 int shelfi_decrypt(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint64_t n, double *out) {
     if (!h) return SHELFI_ERR_ARG;
     std::lock_guard<std::mutex> lock(h->mu);
-    return decrypt_host(h, blob, blob_len, n, out);
+    return decrypt_host(h, &blob, &blob_len, &n, 1, out);
+}
+
+// ---- many independent vectors per call (the layers of a state_dict: code/benchmark.py:490-493,
+// code/benchmark_selection.py:152-193 call encrypt / computeWeightedAverage / decrypt once per layer) ----
+int shelfi_encrypt_layers(shelfi_ckks *h, const double *const *x, const uint64_t *layer_len, uint32_t n_layers, uint8_t **blobs,
+                          uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
+    if (!h || !blobs) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return encrypt_host(h, x, layer_len, n_layers, nullptr, 0, blobs, offsets, lens, total_len);
+}
+int shelfi_compute_weighted_average_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                           const float *weights, uint32_t k, uint32_t n_layers, uint8_t **out,
+                                           uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
+    if (!h || !out) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return wavg_host(h, blobs, blob_lens, weights, k, n_layers, nullptr, 0, out, offsets, lens, total_len);
+}
+int shelfi_encrypt_layers_into(shelfi_ckks *h, const double *const *x, const uint64_t *layer_len, uint32_t n_layers, uint8_t *dst,
+                               uint64_t cap, uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return encrypt_host(h, x, layer_len, n_layers, dst, cap, nullptr, offsets, lens, total_len);
+}
+int shelfi_compute_weighted_average_layers_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                                const float *weights, uint32_t k, uint32_t n_layers, uint8_t *dst,
+                                                uint64_t cap, uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return wavg_host(h, blobs, blob_lens, weights, k, n_layers, dst, cap, nullptr, offsets, lens, total_len);
+}
+int shelfi_decrypt_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                          const uint64_t *data_dimensions, uint32_t n_layers, double *out) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return decrypt_host(h, blobs, blob_lens, data_dimensions, n_layers, out);
 }
 
 void shelfi_free(void *p) { std::free(p); }

@@ -108,6 +108,31 @@ int shelfi_compute_weighted_average_into(shelfi_ckks *h, const uint8_t *const *b
 /* CKKS::decrypt (src/ckks.cpp:170-213): blob -> n doubles (n = data_dimensions). */
 int shelfi_decrypt(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint64_t n, double *out);
 
+/* ---- many independent vectors in one call ----
+ * The reference's callers encrypt, aggregate and decrypt a model layer by layer (code/benchmark.py:490-493,
+ * code/benchmark_selection.py:152-193: one CKKS::encrypt / computeWeightedAverage / decrypt per state_dict entry).
+ * These entry points do the same work for n_layers vectors with one host->device copy, the kernels of every layer on
+ * one stream and one device->host copy.  Every layer is its own serialized ciphertext vector, byte-identical to
+ * what the single-vector call returns for it (under a fixed sampler seed).
+ *   encrypt: x[s] = layer s, layer_len[s] values.  *blobs receives ONE buffer
+ *            (shelfi_free) holding blob s at offsets[s] (8-byte aligned), lens[s] bytes; *total_len its size.
+ *   weighted average: blobs[i * n_layers + s] / blob_lens[...] = learner i, layer s; result laid out as above.
+ *   decrypt: out = data_dimensions[0] values of layer 0, then layer 1, ... */
+int shelfi_encrypt_layers(shelfi_ckks *h, const double *const *x, const uint64_t *layer_len, uint32_t n_layers, uint8_t **blobs,
+                          uint64_t *offsets, uint64_t *lens, uint64_t *total_len);
+int shelfi_compute_weighted_average_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                           const float *weights, uint32_t k, uint32_t n_layers, uint8_t **out,
+                                           uint64_t *offsets, uint64_t *lens, uint64_t *total_len);
+/* the same into a caller buffer (e.g. page-locked memory from shelfi_host_alloc): layer s of n_ct_s ciphertexts needs
+ * shelfi_blob_size(h, n_ct_s) bytes rounded up to a multiple of 8; the blobs are laid out back to back in that order */
+int shelfi_encrypt_layers_into(shelfi_ckks *h, const double *const *x, const uint64_t *layer_len, uint32_t n_layers, uint8_t *dst,
+                               uint64_t cap, uint64_t *offsets, uint64_t *lens, uint64_t *total_len);
+int shelfi_compute_weighted_average_layers_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                                const float *weights, uint32_t k, uint32_t n_layers, uint8_t *dst,
+                                                uint64_t cap, uint64_t *offsets, uint64_t *lens, uint64_t *total_len);
+int shelfi_decrypt_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                          const uint64_t *data_dimensions, uint32_t n_layers, double *out);
+
 void shelfi_free(void *p);
 /* page-locked host memory for the *_into calls and for inputs */
 void *shelfi_host_alloc(size_t bytes);

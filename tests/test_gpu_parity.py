@@ -315,3 +315,88 @@ def test_full_size_properties(gpu_ckks):
     a1 = h.computeWeightedAverage(blobs[:3], [0.5, 0.25, 0.25])
     a2 = h.computeWeightedAverage([blobs[2], blobs[0], blobs[1]], [0.25, 0.5, 0.25])
     assert a1 == a2
+
+
+# ---- layer-wise callers: one call for all state_dict entries (benchmark.py:490-493, benchmark_selection.py:152-193) ----
+CNN_LAYERS = [800, 32, 51200, 64, 1605632, 512, 5120, 10]      # CNN_OriginalFedAvg (benchmark.py:152-219)
+
+
+def test_layers_api_equals_per_layer_calls(gpu_ckks, oracles):
+    """encrypt_layers / computeWeightedAverage_layers / decrypt_layers == the reference's per-layer loop, byte for byte."""
+    h, o = gpu_ckks["pybind"], oracles["pybind"]
+    sizes = [800, 32, 4096, 4097, 1, 9000]
+    rng = np.random.default_rng(8)
+    K, w = 3, [0.5, 0.2, 0.3]
+    models = [[rng.normal(0, 0.05, n) for n in sizes] for _ in range(K)]
+    enc = []
+    for i, layers in enumerate(models):
+        h.set_sampler_seed(40 + i)
+        blobs = h.encrypt_layers(layers)
+        single = [h.encrypt(a) for a in layers]
+        h.set_sampler_seed(None)
+        assert blobs == single
+        assert blobs == [o.encrypt(a, seed=40 + i) for a in layers]
+        enc.append(blobs)
+    avg = h.computeWeightedAverage_layers(enc, w)
+    assert avg == [h.computeWeightedAverage([enc[i][s] for i in range(K)], w) for s in range(len(sizes))]
+    assert avg == [o.computeWeightedAverage([enc[i][s] for i in range(K)], w) for s in range(len(sizes))]
+    dec = h.decrypt_layers(avg, sizes)
+    for s, n in enumerate(sizes):
+        assert np.array_equal(dec[s], h.decrypt(avg[s], n)) and np.array_equal(dec[s], o.decrypt(avg[s], n))
+        expect = sum(float(np.float32(wi)) * models[i][s] for i, wi in enumerate(w))
+        assert rel_err(dec[s], expect) < RTOL
+    assert h.computeWeightedAverage_layers(enc, w[:2]) == []        # ckks.cpp:265-268
+    with pytest.raises(Exception):
+        h.decrypt_layers(avg, [n + 5000 for n in sizes])
+
+
+def test_layers_api_full_cnn(gpu_ckks):
+    """The 8 state_dict entries of the config-2 CNN, 10 learners: 412 ciphertexts per learner instead of 407."""
+    h = gpu_ckks["code"]
+    rng = np.random.default_rng(6)
+    K = 10
+    models = [[rng.normal(0, 0.05, n).astype(np.float32) for n in CNN_LAYERS] for _ in range(K)]
+    enc = [h.encrypt_layers(m) for m in models]
+    assert sum(h.num_ciphertexts(n) for n in CNN_LAYERS) == 412
+    avg = h.computeWeightedAverage_layers(enc, [1.0 / K] * K)
+    dec = h.decrypt_layers(avg, CNN_LAYERS)
+    for s in range(len(CNN_LAYERS)):
+        expect = sum(np.float64(np.float32(1.0 / K)) * models[i][s].astype(np.float64) for i in range(K))
+        assert rel_err(dec[s], expect) < RTOL
+
+
+def test_pinned_blob_mode_equals_bytes_mode(shelfi, gpu_ckks):
+    """CKKS(..., pinned=True) returns bytes-like PinnedBlob objects (page-locked host memory, pooled): same bytes,
+    accepted wherever a blob is, and interchangeable with real bytes."""
+    h = gpu_ckks["pybind"]
+    d = str(FIXTURE_DIRS["pybind"]) + "/"
+    p = shelfi.CKKS("ckks", 4096, 52, d, device=0, pinned=True)
+    p.loadCryptoParams()
+    rng = np.random.default_rng(14)
+    xs = [rng.normal(0, 0.05, 9000) for _ in range(3)]
+    w = [0.5, 0.2, 0.3]
+    blobs_b, blobs_p = [], []
+    for i, x in enumerate(xs):
+        for hh, out in ((h, blobs_b), (p, blobs_p)):
+            hh.set_sampler_seed(70 + i)
+            out.append(hh.encrypt(x))
+            hh.set_sampler_seed(None)
+    assert all(isinstance(b, shelfi.PinnedBlob) for b in blobs_p) and all(isinstance(b, bytes) for b in blobs_b)
+    assert [bytes(b) for b in blobs_p] == blobs_b and blobs_p[0] == blobs_b[0] and len(blobs_p[0]) == len(blobs_b[0])
+    avg_b = h.computeWeightedAverage(blobs_b, w)
+    avg_p = p.computeWeightedAverage(blobs_p, w)
+    assert bytes(avg_p) == avg_b == bytes(p.computeWeightedAverage([blobs_p[0], blobs_b[1], memoryview(blobs_b[2])], w))
+    assert np.array_equal(p.decrypt(avg_p, 9000), h.decrypt(avg_b, 9000))
+    assert np.array_equal(h.decrypt(avg_p, 9000), h.decrypt(avg_b, 9000))
+    layers = [xs[0][:100], xs[1][:5000], xs[2]]
+    p.set_sampler_seed(3); h.set_sampler_seed(3)
+    lp, lb = p.encrypt_layers(layers), h.encrypt_layers(layers)
+    p.set_sampler_seed(None); h.set_sampler_seed(None)
+    assert [bytes(b) for b in lp] == lb
+    ap = p.computeWeightedAverage_layers([lp, lp], [0.5, 0.5])
+    assert [bytes(b) for b in ap] == h.computeWeightedAverage_layers([lb, lb], [0.5, 0.5])
+    for got, want in zip(p.decrypt_layers(ap, [100, 5000, 9000]), layers):
+        assert rel_err(got, want) < RTOL
+    del blobs_p, lp, ap, avg_p                                   # buffers go back to the pool and are reused
+    again = p.encrypt(xs[0])
+    assert rel_err(p.decrypt(again, 9000), xs[0]) < RTOL
