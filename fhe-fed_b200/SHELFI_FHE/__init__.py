@@ -334,22 +334,21 @@ class CKKS(Scheme):
     # ---- layer-wise callers (benchmark.py:490-493, benchmark_selection.py:152-193) in one call each ----
     def encrypt_layers(self, arrays) -> list:
         """[encrypt(a) for a in arrays] with one host->device copy, one stream of launches, one copy back."""
+        if not self.pinned:   # real bytes objects cannot share one buffer: filling each in place beats slicing copies
+            return [self.encrypt(a) for a in arrays]
         flat = [np.ascontiguousarray(a, dtype=np.float64).ravel() for a in arrays]
         n = len(flat)
         xp = (C.c_void_p * n)(*[a.ctypes.data for a in flat])
         ll = (C.c_uint64 * n)(*[a.size for a in flat])
         offs, lens, total = (C.c_uint64 * n)(), (C.c_uint64 * n)(), C.c_uint64()
         cap = sum((self.blob_size(self.num_ciphertexts(a.size)) + 7) // 8 * 8 for a in flat if a.size)
-        dst = PinnedBlob(max(cap, 8)) if self.pinned else _new_bytes(max(cap, 8))
+        dst = PinnedBlob(max(cap, 8))
         self._check(lib().shelfi_encrypt_layers_into(self._h, xp, ll, n, _addr(dst), cap, offs, lens,
                                                      C.byref(total)))
         return self._split(dst, offs, lens, n)
 
     def _split(self, dst, offs, lens, n) -> list:
-        if self.pinned:
-            return [dst.view(offs[i], lens[i]) for i in range(n)]
-        mv = memoryview(dst)
-        return [bytes(mv[offs[i]:offs[i] + lens[i]]) for i in range(n)]
+        return [dst.view(offs[i], lens[i]) for i in range(n)]
 
     def computeWeightedAverage_layers(self, learner_layers, scaling_factors) -> list:
         """learner_layers[i][s] = blob of learner i, layer s -> [computeWeightedAverage over learners for each layer]."""
@@ -360,13 +359,15 @@ class CKKS(Scheme):
         k, n = len(learner_layers), len(learner_layers[0]) if learner_layers else 0
         if any(len(l) != n for l in learner_layers):
             raise ValueError("every learner must supply the same number of layers")
+        if not self.pinned:
+            return [self.computeWeightedAverage([l[s] for l in learner_layers], scaling_factors) for s in range(n)]
         blobs = [_as_bytes(b) for l in learner_layers for b in l]
         ptrs = (C.c_void_p * (k * n))(*[_addr(b) for b in blobs])
         blens = (C.c_uint64 * (k * n))(*[len(b) for b in blobs])
         w = (C.c_float * k)(*[float(v) for v in scaling_factors])
         offs, lens, total = (C.c_uint64 * n)(), (C.c_uint64 * n)(), C.c_uint64()
         cap = sum((len(b) + 7) // 8 * 8 for b in blobs[:n])   # results have learner 0's layout (ckks.cpp:291-292)
-        dst = PinnedBlob(max(cap, 8)) if self.pinned else _new_bytes(max(cap, 8))
+        dst = PinnedBlob(max(cap, 8))
         self._check(lib().shelfi_compute_weighted_average_layers_into(self._h, ptrs, blens, w, k, n, _addr(dst), cap, offs,
                                                                       lens, C.byref(total)))
         return self._split(dst, offs, lens, n)

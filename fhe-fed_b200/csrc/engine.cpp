@@ -8,7 +8,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <functional>
 #include <mutex>
+#include <thread>
 #include <random>
 #include <string>
 #include <vector>
@@ -72,6 +75,68 @@ struct Profiler {
     }
 };
 
+// Host-side memcpy split over a few persistent threads.  Pageable caller buffers (Python bytes, numpy arrays) are moved
+// through page-locked staging chunks; a single thread copying into freshly allocated memory is bound by page faults
+// (~3 GB/s), several threads first-touching disjoint ranges are not.
+class ParallelCopier {
+  public:
+    explicit ParallelCopier(unsigned n) {
+        for (unsigned i = 1; i < n; i++) workers_.emplace_back([this, i] { loop(i); });
+        parts_ = n ? n : 1;
+    }
+    ~ParallelCopier() {
+        { std::lock_guard<std::mutex> l(mu_); stop_ = true; gen_++; }
+        cv_.notify_all();
+        for (auto &t : workers_) t.join();
+    }
+    void copy(void *dst, const void *src, size_t bytes) {
+        if (bytes < (1u << 20) || parts_ == 1) { std::memcpy(dst, src, bytes); return; }
+        {
+            std::lock_guard<std::mutex> l(mu_);
+            dst_ = static_cast<char *>(dst); src_ = static_cast<const char *>(src); bytes_ = bytes;
+            pending_ = parts_ - 1; gen_++;
+        }
+        cv_.notify_all();
+        piece(0);
+        std::unique_lock<std::mutex> l(mu_);
+        done_.wait(l, [this] { return pending_ == 0; });
+    }
+
+  private:
+    void piece(unsigned i) {
+        size_t per = ((bytes_ / parts_) + 4095) & ~(size_t)4095;
+        size_t a = std::min(bytes_, per * i), b = (i + 1 == parts_) ? bytes_ : std::min(bytes_, per * (i + 1));
+        if (b > a) std::memcpy(dst_ + a, src_ + a, b - a);
+    }
+    void loop(unsigned i) {
+        uint64_t seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> l(mu_);
+                cv_.wait(l, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+            }
+            piece(i);
+            {
+                std::lock_guard<std::mutex> l(mu_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    const char *src_ = nullptr;
+    char *dst_ = nullptr;
+    size_t bytes_ = 0;
+    unsigned parts_ = 1, pending_ = 0;
+    uint64_t gen_ = 0;
+    bool stop_ = false;
+};
+
+constexpr size_t kStageBytes = 16u << 20;   // two page-locked staging chunks of this size per handle
+
 }  // namespace
 
 struct shelfi_ckks {
@@ -98,6 +163,10 @@ struct shelfi_ckks {
     uint64_t seed = 0;
     Profiler prof;
     std::mutex mu;
+    // pageable host buffers: staging chunks + copy threads (created on first use)
+    void *stage[2] = {nullptr, nullptr};
+    cudaEvent_t ev_stage[2] = {nullptr, nullptr};
+    ParallelCopier *copier = nullptr;
 };
 
 namespace {
@@ -178,6 +247,70 @@ void free_params(shelfi_ckks *h) {
 int upload(shelfi_ckks *h, DeviceBuffer *buf, const void *src, size_t bytes) {
     CU(buf->reserve(bytes));
     CU(cudaMemcpy(buf->p, src, bytes, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+bool is_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+int ensure_staging(shelfi_ckks *h) {
+    if (h->copier) return 0;
+    for (int i = 0; i < 2; i++) {
+        CU(cudaHostAlloc(&h->stage[i], kStageBytes, cudaHostAllocDefault));
+        CU(cudaEventCreateWithFlags(&h->ev_stage[i], cudaEventDisableTiming));
+    }
+    unsigned n = std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
+    if (const char *e = std::getenv("SHELFI_COPY_THREADS")) n = (unsigned)std::max(1, std::atoi(e));
+    h->copier = new ParallelCopier(n);
+    return 0;
+}
+// Host -> device, queued on `s`.  Page-locked sources go straight to the copy engine (asynchronous); pageable ones are
+// copied chunk by chunk into page-locked staging by the copy threads (the call returns when the last chunk is queued).
+int h2d(shelfi_ckks *h, void *dev, const void *host, size_t bytes, cudaStream_t s) {
+    if (bytes < (4u << 20) || is_pinned(host)) {
+        CU(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, s));
+        return 0;
+    }
+    int rcode = ensure_staging(h);
+    if (rcode) return rcode;
+    size_t off = 0;
+    for (int c = 0; off < bytes; c++, off += kStageBytes) {
+        const int b = c & 1;
+        const size_t len = std::min(kStageBytes, bytes - off);
+        if (c >= 2) CU(cudaEventSynchronize(h->ev_stage[b]));
+        h->copier->copy(h->stage[b], static_cast<const char *>(host) + off, len);
+        CU(cudaMemcpyAsync(static_cast<char *>(dev) + off, h->stage[b], len, cudaMemcpyHostToDevice, s));
+        CU(cudaEventRecord(h->ev_stage[b], s));
+    }
+    CU(cudaEventSynchronize(h->ev_stage[0]));   // staging is reused by the next call
+    CU(cudaEventSynchronize(h->ev_stage[1]));
+    return 0;
+}
+// Device -> host after everything queued on `s`; returns when the bytes are in `host`.
+int d2h_sync(shelfi_ckks *h, void *host, const void *dev, size_t bytes, cudaStream_t s) {
+    if (bytes < (4u << 20) || is_pinned(host)) {
+        CU(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        return 0;
+    }
+    int rcode = ensure_staging(h);
+    if (rcode) return rcode;
+    const size_t chunks = (bytes + kStageBytes - 1) / kStageBytes;
+    auto issue = [&](size_t c) -> cudaError_t {
+        const size_t off = c * kStageBytes, len = std::min(kStageBytes, bytes - off);
+        cudaError_t e = cudaMemcpyAsync(h->stage[c & 1], static_cast<const char *>(dev) + off, len, cudaMemcpyDeviceToHost, s);
+        return e != cudaSuccess ? e : cudaEventRecord(h->ev_stage[c & 1], s);
+    };
+    CU(issue(0));
+    if (chunks > 1) CU(issue(1));
+    for (size_t c = 0; c < chunks; c++) {
+        const size_t off = c * kStageBytes, len = std::min(kStageBytes, bytes - off);
+        CU(cudaEventSynchronize(h->ev_stage[c & 1]));
+        h->copier->copy(static_cast<char *>(host) + off, h->stage[c & 1], len);
+        if (c + 2 < chunks) CU(issue(c + 2));
+    }
     return 0;
 }
 
@@ -416,7 +549,7 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
     CUB(h->s_image.reserve(image_bytes(image)));
     for (uint32_t i = 0; i < n_layers; i++)
-        CUB(cudaMemcpyAsync(h->s_x.as<double>() + slot[i].x0, xs[i], slot[i].n * sizeof(double), cudaMemcpyHostToDevice, s));
+        if ((rcode = h2d(h, h->s_x.as<double>() + slot[i].x0, xs[i], slot[i].n * sizeof(double), s))) return bail(rcode);
     for (const LayerSlot &ls : slot) {   // every layer is its own ciphertext vector: sampler index restarts at 0
         if ((rcode = encrypt_dense(h, h->s_x.as<double>() + ls.x0, ls.n, 0, h->s_dense.as<u64>() + ls.ct0 * ct_words, s)))
             return bail(rcode);
@@ -426,8 +559,7 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
         });
     }
     CUB(cudaGetLastError());
-    CUB(cudaMemcpyAsync(dst, h->s_image.p, total, cudaMemcpyDeviceToHost, s));
-    CUB(cudaStreamSynchronize(s));
+    if ((rcode = d2h_sync(h, dst, h->s_image.p, total, s))) return bail(rcode);
     for (uint32_t i = 0; i < n_layers; i++) {
         write_segments(slot[i].plan, dst + slot[i].off);
         if (offsets) offsets[i] = slot[i].off;
@@ -500,7 +632,7 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
         if (i >= 2) CUB(cudaStreamWaitEvent(cs, h->ev_done[b], 0));
         for (uint32_t s = 0; s < n_layers; s++) {
             const size_t id = (size_t)i * n_layers + s;
-            CUB(cudaMemcpyAsync(img[b]->as<uint8_t>() + in_off[id], blobs[id], blob_lens[id], cudaMemcpyHostToDevice, cs));
+            if ((rcode = h2d(h, img[b]->as<uint8_t>() + in_off[id], blobs[id], blob_lens[id], cs))) return bail(rcode);
         }
         CUB(cudaEventRecord(h->ev_copy[b], cs));
         CUB(cudaStreamWaitEvent(st, h->ev_copy[b], 0));
@@ -524,8 +656,7 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
                         h->s_image.as<u64>() + ls.off / 8, ls.n_ct, st);
         });
     CUB(cudaGetLastError());
-    CUB(cudaMemcpyAsync(dst, h->s_image.p, total, cudaMemcpyDeviceToHost, st));
-    CUB(cudaStreamSynchronize(st));
+    if ((rcode = d2h_sync(h, dst, h->s_image.p, total, st))) return bail(rcode);
     for (uint32_t s = 0; s < n_layers; s++) {
         write_segments(slot[s].plan, dst + slot[s].off);
         if (offsets) offsets[s] = slot[s].off;
@@ -573,7 +704,7 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
     }
     for (uint32_t s = 0; s < n_layers; s++) {
         const LayerSlot &ls = slot[s];
-        CU(cudaMemcpyAsync(h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], cudaMemcpyHostToDevice, st));
+        if ((rcode = h2d(h, h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], st))) return rcode;
         u64 *dense = h->s_dense.as<u64>() + ls.ct0 * ct_words;
         timed(h, kKUnpack, st, [&] {
             launch_unpack(h->rc, to_runs(h, maps[s].run0, maps[s].run1, maps[s].stride), h->s_image.as<u64>() + ls.off / 8, dense,
@@ -591,9 +722,7 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             j0 = j1;
         }
     }
-    CU(cudaMemcpyAsync(out, h->s_out.p, n * sizeof(double), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    return 0;
+    return d2h_sync(h, out, h->s_out.p, n * sizeof(double), st);
 }
 
 }  // namespace
@@ -629,6 +758,11 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
                                 &h->s_vals, &h->s_zs, &h->s_rows})
             b->release();
         for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_copy[i]); cudaEventDestroy(h->ev_done[i]); }
+        for (int i = 0; i < 2; i++) {
+            if (h->stage[i]) cudaFreeHost(h->stage[i]);
+            if (h->ev_stage[i]) cudaEventDestroy(h->ev_stage[i]);
+        }
+        delete h->copier;
         cudaStreamDestroy(h->stream);
         cudaStreamDestroy(h->copy_stream);
     }
