@@ -15,6 +15,7 @@
 #pragma once
 #include <stdint.h>
 #include <math.h>
+#include <string.h>
 
 #ifdef __CUDACC__
 #define HD __host__ __device__ __forceinline__
@@ -43,6 +44,9 @@ constexpr int kFftThreads = 256;
 
 struct __attribute__((aligned(16))) tw_t { u64 w, ws; };  // twiddle and its Shoup companion floor(w*2^64/q)
 struct __attribute__((aligned(16))) u64x2 { u64 x, y; };
+#ifndef __CUDACC__
+struct __attribute__((aligned(16))) double2 { double x, y; };
+#endif
 
 // Per-limb constants, passed to kernels by value inside RingConst.
 struct LimbConst {
@@ -57,9 +61,12 @@ struct LimbConst {
     u32 rshift;     // quick-reduce shift (>= 32 in modes 0 and 1)
     u32 rmode;      // 0: q just below 2^rshift; 1: q just above 2^rshift; 2: generic (mulhi by mu)
     u32 fwd_mask;   // bit p: quick-reduce to [0,2q) at the end of forward pass p (0..3)
-    u32 pad;
+    u32 dthr;       // FP64 path: high word of the double 0.49 q (renormalisation threshold)
     const tw_t *tw;   // forward table, index 1..N-1: psi^bitrev(i)      (PALISADE rootOfUnityReverseTable)
     const tw_t *itw;  // inverse table:                psi^-bitrev(i)
+    // FP64-pipe forward transform (limbs with q < 2^53, ring dimension 8192): centred twiddles as doubles, or null
+    const double *dtw;
+    double qd, qinv;  // q and 1/q as doubles
 };
 
 struct RingConst {
@@ -355,6 +362,193 @@ HD void fwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store
     }
 }
 
+// unfused IEEE double operations (nvcc would otherwise contract a*b+c; the reference does not)
+HD double fmul(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dmul_rn(a, b);
+#else
+    return a * b;
+#endif
+}
+HD double fadd(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dadd_rn(a, b);
+#else
+    return a + b;
+#endif
+}
+HD double fsub(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dsub_rn(a, b);
+#else
+    return a - b;
+#endif
+}
+// ------------------------------------------------------------------------------------------
+// The same forward transform on the FP64 pipe, for limbs with q < 2^53 (PALISADE's scaling primes at <= 52 bits).
+// B200 issues DFMA at full rate (64 lanes/clk/SM, measured: tools/ubench/pipes.cu) on a pipe the integer path
+// leaves idle, and a 53 x 53 -> 106-bit product is two instructions there (DMUL + DFMA) against four IMAD.WIDE.
+// Co-resident CTAs working on the 60-bit limb (integer pipe) and on a 52-bit limb (FP64 pipe) overlap.
+//
+// Values are integers held exactly in doubles, centred: |v| <= 0.51 q between stages.
+//   mulmod(y, w), |y| < q, |w| <= q/2:  h = RN(y w), l = y w - h (exact, FMA), c = rint(h / q) by the 1.5*2^52 magic
+//   constant (|h / q| < 2^51), d = h - c q (exact: an integer below 2^53), r = d + l.  |y w / q - c| <= 1/2 + |c| 2^-52
+//   so |r| <= 0.76 q for |y| <= 0.5 q.
+//   butterfly: x +- r is at most 1.26 q < 2^53 (exact); renormalise with v - q rint(v / q) back to |v| <= q/2.
+//   (q <= 1.25 * 2^52 keeps every bound above with room to spare: tables.cpp admits only such limbs.)
+// Every rounding that happens is of a value the derivation does not need exactly (h, c), so the residues — and after
+// the final conversion to [0, q) the stored words — equal the integer path's bit for bit.
+// ------------------------------------------------------------------------------------------
+HD double d_fma(double a, double b, double c) {
+#ifdef __CUDA_ARCH__
+    return __fma_rn(a, b, c);
+#else
+    return fma(a, b, c);
+#endif
+}
+HD u32 d_hi(double v) {
+#ifdef __CUDA_ARCH__
+    return (u32)__double2hiint(v);
+#else
+    u64 b; memcpy(&b, &v, 8); return (u32)(b >> 32);
+#endif
+}
+HD double d_copysign_q(double q, double v) {   // q > 0 with the sign of v
+#ifdef __CUDA_ARCH__
+    return __hiloint2double((int)((u32)__double2hiint(q) | ((u32)__double2hiint(v) & 0x80000000u)), __double2loint(q));
+#else
+    return copysign(q, v);
+#endif
+}
+HD double d_mulmod(double y, double w, double q, double qinv) {
+    const double M = 6755399441055744.0;   // 1.5 * 2^52
+    double h = fmul(y, w);
+    double l = d_fma(y, w, -h);
+    double c = fsub(d_fma(h, qinv, M), M);
+    double d = d_fma(-c, q, h);
+    return fadd(d, l);
+}
+// Renormalisation to |v| <= q/2 (+1): v - q rint(v / q), three FP64 operations and nothing on the ALU pipe.
+// Measured on B200 (8140-row forward NTT, 52-bit prime): this form 58.3 ns/row; compare-on-high-word + two FSEL
+// (1 FP64 + 5 ALU operations) 67.9; DSETP + predicated DADD (2 FP64 + 1 ALU) 64.8.  The others stay selectable.
+#ifndef SHELFI_DRENORM
+#define SHELFI_DRENORM 1
+#endif
+HD double d_renorm(double v, double q, double qinv, u32 thr) {
+#if SHELFI_DRENORM == 0
+    (void)qinv;
+    return (d_hi(v) & 0x7fffffffu) > thr ? fsub(v, d_copysign_q(q, v)) : v;
+#elif SHELFI_DRENORM == 1
+    (void)thr;
+    const double M = 6755399441055744.0;
+    double c = fsub(d_fma(v, qinv, M), M);
+    return d_fma(-c, q, v);
+#else
+    (void)qinv;
+#ifdef __CUDA_ARCH__
+    double t = __hiloint2double((int)thr, 0), s = d_copysign_q(q, v);
+    asm("{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .f64 a;\n\t"
+        "abs.f64 a, %0;\n\t"
+        "setp.gt.f64 p, a, %1;\n\t"
+        "@p sub.rn.f64 %0, %0, %2;\n\t"
+        "}"
+        : "+d"(v)
+        : "d"(t), "d"(s));
+    return v;
+#else
+    u64 tb = (u64)thr << 32;
+    double t;
+    memcpy(&t, &tb, 8);
+    return fabs(v) > t ? v - copysign(q, v) : v;
+#endif
+#endif
+}
+HD void d_bfly(double &x, double &y, double w, double q, double qinv, u32 thr) {
+    double t = d_mulmod(y, w, q, qinv);
+    y = d_renorm(fsub(x, t), q, qinv, thr);
+    x = d_renorm(fadd(x, t), q, qinv, thr);
+}
+HD void d_radix8(double (&a)[8], const double *__restrict__ tw, u32 t0, double q, double qinv, u32 thr) {
+    double w = tw[t0];
+#pragma unroll
+    for (int k = 0; k < 4; k++) d_bfly(a[k], a[k + 4], w, q, qinv, thr);
+    double w0 = tw[2 * t0], w1 = tw[2 * t0 + 1];
+    d_bfly(a[0], a[2], w0, q, qinv, thr); d_bfly(a[1], a[3], w0, q, qinv, thr);
+    d_bfly(a[4], a[6], w1, q, qinv, thr); d_bfly(a[5], a[7], w1, q, qinv, thr);
+#pragma unroll
+    for (int k = 0; k < 4; k++) d_bfly(a[2 * k], a[2 * k + 1], tw[4 * t0 + k], q, qinv, thr);
+}
+HD double &dtile(char *sm, u32 byte_off) { return *reinterpret_cast<double *>(sm + byte_off); }
+// residue in [0, q) -> centred double; centred integer double (|v| < q) -> residue in [0, q)
+HD double d_from_residue(u64 r, u64 q) { return (double)(r > (q >> 1) ? (i64)r - (i64)q : (i64)r); }
+HD u64 d_to_residue(double v, u64 q) {
+    i64 i = (i64)v;
+    return i < 0 ? (u64)(i + (i64)q) : (u64)i;
+}
+template <class Load>   // ld(index) -> centred double, |v| <= q/2
+HD void dfwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        double a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = ld((u32)(k << 10) | vt);
+        d_radix8(a, lc.dtw, 1u, q, qinv, thr);
+        u32 base = tile_base<10>(vt);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dtile(sm, tile_off<10>(base, k)) = a[k];
+    }
+}
+template <int LO>
+HD void dfwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
+    constexpr u32 S0 = 12 - (LO + 2);
+    char *sm = reinterpret_cast<char *>(smem);
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        u32 vt = tid + kNttThreads * r;
+        u32 base = tile_base<LO>(vt);
+        double a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = dtile(sm, tile_off<LO>(base, k));
+        d_radix8(a, lc.dtw, (1u << S0) + (vt >> LO), q, qinv, thr);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dtile(sm, tile_off<LO>(base, k)) = a[k];
+    }
+}
+// last stage + conversion back to residues: the storers of the integer path are used unchanged (they get x, y in [0, q))
+template <class Store>
+HD void dfwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+    constexpr int G = Store::kGroup;
+    const char *sm = reinterpret_cast<const char *>(smem);
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+    const double *__restrict__ tw = lc.dtw + (kN >> 1);
+#pragma unroll 1
+    for (int r0 = 0; r0 < 16; r0 += G) {
+        double w[G];
+        double2 v[G];
+        typename Store::Aux aux[G];
+#pragma unroll
+        for (int i = 0; i < G; i++) w[i] = tw[tid + kNttThreads * (r0 + i)];
+#pragma unroll
+        for (int i = 0; i < G; i++) aux[i] = st.fetch((u32)(tid + kNttThreads * (r0 + i)));
+#pragma unroll
+        for (int i = 0; i < G; i++) v[i] = *reinterpret_cast<const double2 *>(sm + tile_pair(tid + kNttThreads * (r0 + i)));
+#pragma unroll
+        for (int i = 0; i < G; i++) {
+            d_bfly(v[i].x, v[i].y, w[i], q, qinv, thr);
+            st((u32)(tid + kNttThreads * (r0 + i)), d_to_residue(v[i].x, lc.q), d_to_residue(v[i].y, lc.q), aux[i]);
+        }
+    }
+}
+
 // ---- inverse NTT phases (bit-reversed in, natural out), Gentleman-Sande ----
 // Inputs to a pass are < 2q; X' = X + Y doubles the bound per stage, Y' = (X - Y + c)*w with
 // c = (bound of Y) so the difference stays non-negative.  Every pass ends with quick_reduce.
@@ -544,27 +738,6 @@ HD int ternary_from_u32(u32 r) { return (int)mulhi32(r, 3u) - 1; }
 // results must match the reference's unfused butterflies bit for bit.
 // ------------------------------------------------------------------------------------------
 struct __attribute__((aligned(16))) cplx { double re, im; };
-HD double fmul(double a, double b) {
-#ifdef __CUDA_ARCH__
-    return __dmul_rn(a, b);
-#else
-    return a * b;
-#endif
-}
-HD double fadd(double a, double b) {
-#ifdef __CUDA_ARCH__
-    return __dadd_rn(a, b);
-#else
-    return a + b;
-#endif
-}
-HD double fsub(double a, double b) {
-#ifdef __CUDA_ARCH__
-    return __dsub_rn(a, b);
-#else
-    return a - b;
-#endif
-}
 HD u32 bitrev32(u32 x, int bits) {
 #ifdef __CUDA_ARCH__
     return bits ? __brev(x) >> (32 - bits) : 0u;
@@ -1138,6 +1311,23 @@ HD u64x2 ld_readonly(const u64x2 *p) {
 struct LoadGlobal {
     const u64 *p;
     HD u64 operator()(u32 i) const { return p[i]; }
+};
+// FP64-path loaders: centred doubles, |v| <= q/2
+struct DLoadGlobal {
+    const u64 *p; u64 q;
+    HD double operator()(u32 i) const { return d_from_residue(p[i], q); }
+};
+struct DLoadTernary {
+    const uint16_t *ve;
+    HD double operator()(u32 i) const { return (double)(int)(int8_t)(ve[i] & 0xFF); }
+};
+struct DLoadGaussHi {
+    const uint16_t *ve;
+    HD double operator()(u32 i) const { return (double)(int)(int8_t)(ve[i] >> 8); }
+};
+struct DLoadSigned {
+    const i64 *m; const LimbConst *lc;
+    HD double operator()(u32 i) const { return d_from_residue(signed_to_mod(m[i], *lc), lc->q); }
 };
 struct StoreFullReducePair {
     typedef NoAux Aux;

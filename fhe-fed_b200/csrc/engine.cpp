@@ -153,7 +153,7 @@ struct shelfi_ckks {
     CrtNConst crtn{};
     uint64_t gauss_cdf[32] = {0};
     // device-resident parameters
-    DeviceBuffer d_tw, d_itw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
+    DeviceBuffer d_tw, d_itw, d_dtw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
     // scratch
     DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_out, s_vals, s_zs, s_rows;
     cudaStream_t stream = nullptr;
@@ -240,7 +240,7 @@ bool write_file(const std::string &path, const std::vector<uint8_t> &data) {
 }
 
 void free_params(shelfi_ckks *h) {
-    h->d_tw.release(); h->d_itw.release(); h->d_pk_b.release(); h->d_pk_a.release(); h->d_sk.release();
+    h->d_tw.release(); h->d_itw.release(); h->d_dtw.release(); h->d_pk_b.release(); h->d_pk_a.release(); h->d_sk.release();
     h->d_fft_inv.release(); h->d_fft_fwd.release();
 }
 
@@ -328,18 +328,27 @@ int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
     RingConst rc{};
     rc.n = N; rc.logn = logn; rc.log_blocks = logn - kLogN; rc.limbs = p.limbs; rc.slots = p.batch_size;
     std::vector<tw_t> tw_all((size_t)p.limbs * N), itw_all((size_t)p.limbs * N), tw, itw;
+    std::vector<double> dtw_all((size_t)p.limbs * N, 0.0), dtw;
+    bool has_dtw[kMaxLimbs] = {false};
+    // SHELFI_FP64_NTT=0 keeps every limb on the integer pipe (A/B measurements; the results are the same bits)
+    const char *fp64_env = std::getenv("SHELFI_FP64_NTT");
+    const bool want_fp64 = !(fp64_env && std::atoi(fp64_env) == 0);
     for (uint32_t l = 0; l < p.limbs; l++) {
-        std::string e = make_limb_const(p.modulus[l], p.root[l], logn, &rc.limb[l], &tw, &itw);
+        std::string e = make_limb_const(p.modulus[l], p.root[l], logn, &rc.limb[l], &tw, &itw, &dtw);
         if (!e.empty()) return fail(h, SHELFI_ERR_UNSUPPORTED, "limb " + std::to_string(l) + ": " + e);
         std::memcpy(&tw_all[(size_t)l * N], tw.data(), sizeof(tw_t) * N);
         std::memcpy(&itw_all[(size_t)l * N], itw.data(), sizeof(tw_t) * N);
+        has_dtw[l] = want_fp64 && !dtw.empty();
+        if (has_dtw[l]) std::memcpy(&dtw_all[(size_t)l * N], dtw.data(), sizeof(double) * N);
     }
     int rcode;
+    if ((rcode = upload(h, &h->d_dtw, dtw_all.data(), dtw_all.size() * sizeof(double)))) return rcode;
     if ((rcode = upload(h, &h->d_tw, tw_all.data(), tw_all.size() * sizeof(tw_t)))) return rcode;
     if ((rcode = upload(h, &h->d_itw, itw_all.data(), itw_all.size() * sizeof(tw_t)))) return rcode;
     for (uint32_t l = 0; l < p.limbs; l++) {
         rc.limb[l].tw = h->d_tw.as<tw_t>() + (size_t)l * N;
         rc.limb[l].itw = h->d_itw.as<tw_t>() + (size_t)l * N;
+        rc.limb[l].dtw = has_dtw[l] ? h->d_dtw.as<double>() + (size_t)l * N : nullptr;
     }
     const uint32_t slots = p.batch_size;
     std::vector<cplx> t_inv, t_fwd;

@@ -33,7 +33,7 @@ void build_gauss_cdf(double sigma, uint64_t cdf[32]) {
 }
 
 std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *lc, std::vector<tw_t> *tw,
-                            std::vector<tw_t> *itw) {
+                            std::vector<tw_t> *itw, std::vector<double> *dtw) {
     if (logn < (uint32_t)kLogN || logn > (uint32_t)(kLogN + kMaxLogBlocks)) return "ring dimension must be 8192, 16384 or 32768";
     const uint32_t n = 1u << logn, d = logn - kLogN;
     if (q >= ((uint64_t)1 << 60) || q < 64 || !(q & 1)) return "limb modulus must be an odd value in [64, 2^60)";
@@ -88,6 +88,23 @@ std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *
         B += kBflyGrowth * stages[pass];
     }
     if (H < 16) return "modulus leaves no headroom for the inverse transform";
+    // FP64-pipe forward transform: exact for q <= 1.25 * 2^52 (ckks_core.cuh); one tile per polynomial only
+    if (dtw) {
+        dtw->clear();
+        if (logn == (uint32_t)kLogN && q <= (((uint64_t)5) << 50) && q >= 1024) {
+            dtw->assign(n, 0.0);
+            for (uint32_t i = 0; i < n; i++) {
+                uint64_t w = (*tw)[i].w;
+                (*dtw)[i] = w > (q >> 1) ? -(double)(q - w) : (double)w;
+            }
+            lc->qd = (double)q;
+            lc->qinv = 1.0 / lc->qd;
+            double thr = 0.49 * lc->qd;
+            uint64_t bits;
+            std::memcpy(&bits, &thr, 8);
+            lc->dthr = (uint32_t)(bits >> 32);
+        }
+    }
     return "";
 }
 

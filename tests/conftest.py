@@ -79,6 +79,8 @@ class Emu:
             "emu_first_prime": (u64, [u32, u32]),
             "emu_previous_prime": (u64, [u64, u32]),
             "emu_min_primitive_root": (u64, [u32, u64]),
+            "emu_limb_fp64": (C.c_int, [vp, u32]),
+            "emu_set_fp64": (None, [vp, C.c_int]),
             "emu_select_ring_dim": (u32, [u32]),
             "emu_select_ring_dim_ex": (u32, [u32, u32]),
             "emu_modulus_chain": (C.c_int, [u32, u32, u32, vp]),

@@ -25,6 +25,8 @@ struct Emu {
     CrtNConst crtn;
     uint64_t cdf[32];
     std::vector<tw_t> tw[kMaxLimbs], itw[kMaxLimbs];
+    std::vector<double> dtw[kMaxLimbs];
+    bool fp64 = true;
     std::vector<cplx> fft_inv, fft_fwd;
     std::string err;
 };
@@ -38,6 +40,15 @@ static void replay_forward(u64 *sm, const LimbConst &lc, u32 hb, Load ld, Store 
     FOR_THREADS(kNttThreads) fwd_phase_mid<4>(tid, sm, lc, hb);
     FOR_THREADS(kNttThreads) fwd_phase_mid<1>(tid, sm, lc, hb);
     FOR_THREADS(kNttThreads) fwd_phase_e(tid, sm, lc, hb, st);
+}
+// the FP64-pipe variant (ntt_forward_tile_d)
+template <class Load, class Store>
+static void replay_forward_d(u64 *sm, const LimbConst &lc, Load ld, Store st) {
+    FOR_THREADS(kNttThreads) dfwd_phase_a(tid, sm, lc, ld);
+    FOR_THREADS(kNttThreads) dfwd_phase_mid<7>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) dfwd_phase_mid<4>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) dfwd_phase_mid<1>(tid, sm, lc);
+    FOR_THREADS(kNttThreads) dfwd_phase_e(tid, sm, lc, st);
 }
 // intt_tile<D>
 template <int D, class Load>
@@ -75,10 +86,11 @@ Emu *emu_create_ex(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint3
     const uint32_t n = 1u << logn;
     e->rc.n = n; e->rc.logn = logn; e->rc.log_blocks = logn - kLogN; e->rc.limbs = limbs; e->rc.slots = slots;
     for (uint32_t l = 0; l < limbs; l++) {
-        e->err = make_limb_const(q[l], psi[l], logn, &e->rc.limb[l], &e->tw[l], &e->itw[l]);
+        e->err = make_limb_const(q[l], psi[l], logn, &e->rc.limb[l], &e->tw[l], &e->itw[l], &e->dtw[l]);
         if (!e->err.empty()) return e;
         e->rc.limb[l].tw = e->tw[l].data();
         e->rc.limb[l].itw = e->itw[l].data();
+        e->rc.limb[l].dtw = e->dtw[l].empty() ? nullptr : e->dtw[l].data();
     }
     make_fft_tables(2 * n, slots, &e->fft_inv, &e->fft_fwd);
     std::memset(&e->ec, 0, sizeof e->ec);
@@ -106,11 +118,22 @@ void emu_ntt_forward(const Emu *e, uint32_t limb, uint64_t *row) {
     std::vector<u64> sm(kN), src(row, row + e->rc.n);
     const LimbConst lc = e->rc.limb[limb];
     const u32 d = e->rc.log_blocks;
+    if (d == 0 && lc.dtw) {
+        replay_forward_d(sm.data(), lc, DLoadGlobal{src.data(), lc.q}, StoreFullReducePair{row, &lc});
+        return;
+    }
     for (u32 blk = 0; blk < (1u << d); blk++) {
         u64 *dst = row + (size_t)blk * kN;
         EMU_D(d, replay_forward(sm.data(), lc, head_bits(d, blk), HeadLoad<D, LoadGlobal>{LoadGlobal{src.data()}, &lc, blk},
                                 StoreFullReducePair{dst, &lc}))
     }
+}
+// 1 if limb l takes the FP64-pipe forward transform
+int emu_limb_fp64(const Emu *e, uint32_t l) { return e->rc.limb[l].dtw != nullptr; }
+// switch the FP64 path off / on for this context (the integer path must give the same bits)
+void emu_set_fp64(Emu *e, int on) {
+    for (u32 l = 0; l < e->rc.limbs; l++)
+        e->rc.limb[l].dtw = (on && !e->dtw[l].empty()) ? e->dtw[l].data() : nullptr;
 }
 void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
     std::vector<u64> sm(kN);
@@ -204,6 +227,12 @@ void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const ui
             const size_t off = (size_t)blk * kN;
             u64 *c0 = out + (0 * L + l) * n + off, *c1 = out + (1 * L + l) * n + off;
             const u32 hb = head_bits(d, blk);
+            if (d == 0 && lc.dtw) {
+                replay_forward_d(sm.data(), lc, DLoadTernary{ve}, StoreLazyPair{c1});
+                replay_forward_d(sm.data(), lc, DLoadSigned{(const i64 *)m_e0, &lc}, StoreMulAdd{b.data() + off, c1, c0, &lc});
+                replay_forward_d(sm.data(), lc, DLoadGaussHi{ve}, StoreMulAdd{a.data() + off, c1, c1, &lc});
+                continue;
+            }
             EMU_D(d, {
                 replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve, lc.q}, &lc, blk}, StoreLazyPair{c1});
                 replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadSigned>{LoadSigned{(const i64 *)m_e0, &lc}, &lc, blk},

@@ -184,3 +184,63 @@ def test_deep_parameter_rules_match_oracle(emu, oracle_mod):
         L = emu.L.emu_modulus_chain(bits, depth, n, vp(q))
         assert [int(v) for v in q[:L]] == oracle_mod.modulus_chain(bits, depth, n)
     assert (emu.L.emu_select_ring_dim_ex(52, 3), emu.L.emu_select_ring_dim_ex(52, 7)) == (16384, 32768)
+
+
+# ---- FP64-pipe forward transform (limbs with q <= 1.25 * 2^52): same bits as the integer path and the oracle ----
+def test_fp64_path_selected_for_the_scaling_limb(emu, emu_ctx, deep_emu_ctx):
+    h = emu_ctx["pybind"]
+    assert (emu.L.emu_limb_fp64(h, 0), emu.L.emu_limb_fp64(h, 1)) == (0, 1)      # 60-bit q0: integer pipe
+    assert emu.L.emu_limb_fp64(deep_emu_ctx["n16k_l4"], 1) == 0                    # more than one tile: integer path
+    assert [emu.L.emu_limb_fp64(deep_emu_ctx["n8k_l3"], l) for l in range(3)] == [0, 1, 1]
+
+
+@pytest.mark.parametrize("bits", [14, 20, 33, 40, 45, 50, 51, 52])
+def test_fp64_ntt_equals_integer_ntt_and_oracle(emu, oracle_mod, bits):
+    """Forward transform on doubles vs the integer path, for scaling primes of every size the reference sweeps
+    (code/benchmark_crypto.py:123-124) and adversarial inputs: all q-1, values around q/2, deltas, random."""
+    M = 2 * N
+    qs = [oracle_mod.first_prime(bits, M), oracle_mod.previous_prime(oracle_mod.first_prime(bits, M) + M * 64, M)]
+    rng = np.random.default_rng(bits)
+    for q in qs:
+        psi = oracle_mod.min_root_of_unity(M, q)
+        h = emu.context([q], [psi])
+        assert emu.L.emu_limb_fp64(h, 0) == 1
+        half = q // 2
+        rows = [np.full(N, q - 1, np.uint64), np.full(N, half, np.uint64), np.full(N, half + 1, np.uint64),
+                np.where(np.arange(N) % 2 == 0, half, half + 1).astype(np.uint64),
+                np.eye(1, N, N - 1, dtype=np.uint64)[0] * np.uint64(q - 1)]
+        rows += [rng.integers(0, q, N, dtype=np.uint64) for _ in range(6)]
+        rows += [(half + rng.integers(-3, 4, N)).astype(np.uint64)]
+        for a in rows:
+            f = a.copy(); emu.L.emu_ntt_forward(h, 0, vp(f))
+            emu.L.emu_set_fp64(h, 0)
+            g = a.copy(); emu.L.emu_ntt_forward(h, 0, vp(g))
+            emu.L.emu_set_fp64(h, 1)
+            assert np.array_equal(f, g)
+            assert f.max() < q
+        emu.L.emu_ntt_inverse(h, 0, vp(f))
+        assert np.array_equal(f, rows[-1])
+        emu.L.emu_destroy(h)
+
+
+def test_fp64_path_rejected_above_its_exactness_bound(emu, oracle_mod):
+    M = 2 * N
+    for bits, want in ((53, 0), (59, 0)):
+        q = oracle_mod.first_prime(bits, M)
+        h = emu.context([q], [oracle_mod.min_root_of_unity(M, q)])
+        assert emu.L.emu_limb_fp64(h, 0) == want
+        emu.L.emu_destroy(h)
+
+
+def test_fp64_encrypt_equals_integer_encrypt(emu, emu_ctx, oracles):
+    o, h = oracles["code"], emu_ctx["code"]
+    x = np.random.default_rng(31).normal(0, 30.0, 4096)          # large messages: m + e0 near 2^58
+    m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint16)
+    emu.L.emu_encode_sample(h, vp(x), 4096, 77, 3, vp(m_e0), vp(ve))
+    b, a = o.public_key()
+    ct1, ct2 = np.empty((2, 2, N), np.uint64), np.empty((2, 2, N), np.uint64)
+    emu.L.emu_encrypt(h, vp(m_e0), vp(ve), vp(b), vp(a), vp(ct1))
+    emu.L.emu_set_fp64(h, 0)
+    emu.L.emu_encrypt(h, vp(m_e0), vp(ve), vp(b), vp(a), vp(ct2))
+    emu.L.emu_set_fp64(h, 1)
+    assert np.array_equal(ct1, ct2) and np.array_equal(ct1, o.encrypt_ct(x, 77, 3))

@@ -1,0 +1,59 @@
+// Throughput of the instruction classes the modmul could be built from, per SM per clock (B200 microbenchmark).
+// nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o pipes pipes.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#define ITER 4096
+template <int OP> __global__ void k(uint64_t *out, uint64_t seed) {
+    uint64_t a = seed + threadIdx.x, b = seed * 3 + blockIdx.x, c = seed ^ 0x9E3779B97F4A7C15ull, d = a ^ b;
+    double x = (double)a, y = (double)b * 1e-9, z = 1.000001, w = 0.999999;
+    uint32_t p = (uint32_t)a, q = (uint32_t)b, r = (uint32_t)c, s = (uint32_t)d;
+#pragma unroll 1
+    for (int i = 0; i < ITER; i++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (OP == 0) {  // IMAD.WIDE.U32 x4 independent
+                a = (uint64_t)p * q + a; b = (uint64_t)q * r + b; c = (uint64_t)r * s + c; d = (uint64_t)s * p + d;
+                p += (uint32_t)a; q ^= (uint32_t)b;
+            } else if (OP == 1) {  // IMAD (32-bit) x4
+                p = p * q + r; q = q * r + s; r = r * s + p; s = s * p + q;
+            } else if (OP == 2) {  // DFMA x4
+                x = fma(x, z, y); y = fma(y, w, x); z = fma(z, w, 1e-30); w = fma(w, z, 1e-30);
+            } else if (OP == 3) {  // u64 -> f64 -> u64 conversions
+                x = (double)(long long)a; y = (double)(long long)b; a = (uint64_t)(long long)(y * 0.5) + c; b = (uint64_t)(long long)(x * 0.5) + d;
+            } else if (OP == 4) {  // __umul64hi
+                a = __umul64hi(a, c) + b; b = __umul64hi(b, d) + a;
+            } else if (OP == 5) {  // IADD3 / LOP3 (alu)
+                p = (p + q) ^ r; q = (q + r) ^ s; r = (r + s) ^ p; s = (s + p) ^ q;
+            } else if (OP == 6) {  // u32 -> f64 and f64 -> s32 conversions (I2F.F64.U32 / F2I.S32.F64)
+                x = (double)p; y = (double)q; p = (uint32_t)(int)(y * 0.5) + r; q = (uint32_t)(int)(x * 0.5) + s;
+            }
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a ^ b ^ c ^ d ^ (uint64_t)(x + y + z + w) ^ p ^ q ^ r ^ s;
+}
+template <int OP> void run(const char *name, double ops_per_iter) {
+    uint64_t *out; cudaMalloc(&out, 148 * 8 * 1024 * 8);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k<OP><<<148 * 8, 256>>>(out, 12345);
+    cudaDeviceSynchronize();
+    cudaEventRecord(e0);
+    k<OP><<<148 * 8, 256>>>(out, 12345);
+    cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    double total = 148.0 * 8 * 256 * ITER * 8 * ops_per_iter;
+    int clk; cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, 0);
+    printf("%-28s %8.3f ms  %7.1f Gop/s  %6.1f op/clk/SM (at %d MHz nominal)\n", name, ms, total / ms / 1e6,
+           total / (ms * 1e-3) / 148 / (clk * 1e3), clk / 1000);
+    cudaFree(out);
+}
+int main() {
+    run<0>("IMAD.WIDE.U32 (32x32+64)", 4);
+    run<1>("IMAD 32-bit", 4);
+    run<2>("DFMA", 4);
+    run<3>("I2F.F64.S64 + F2I.S64.F64", 4);   // 2 each
+    run<4>("__umul64hi (+add)", 2);
+    run<5>("IADD+LOP3 pair", 4);
+    run<6>("I2F.F64.U32 + F2I.S32.F64", 4);
+    return 0;
+}
