@@ -488,7 +488,7 @@ HD u64 d_to_residue(double v, u64 q) {
     return i < 0 ? (u64)(i + (i64)q) : (u64)i;
 }
 template <class Load>   // ld(index) -> centred double, |v| <= q/2
-HD void dfwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
+HD void dfwd_phase_a(int tid, u64 *smem, const LimbConst &lc, u32 hb, Load ld) {
     char *sm = reinterpret_cast<char *>(smem);
     const double q = lc.qd, qinv = lc.qinv;
     const u32 thr = lc.dthr;
@@ -498,14 +498,14 @@ HD void dfwd_phase_a(int tid, u64 *smem, const LimbConst &lc, Load ld) {
         double a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = ld((u32)(k << 10) | vt);
-        d_radix8(a, lc.dtw, 1u, q, qinv, thr);
+        d_radix8(a, lc.dtw, hb, q, qinv, thr);
         u32 base = tile_base<10>(vt);
 #pragma unroll
         for (int k = 0; k < 8; k++) dtile(sm, tile_off<10>(base, k)) = a[k];
     }
 }
 template <int LO>
-HD void dfwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
+HD void dfwd_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
     constexpr u32 S0 = 12 - (LO + 2);
     char *sm = reinterpret_cast<char *>(smem);
     const double q = lc.qd, qinv = lc.qinv;
@@ -517,19 +517,19 @@ HD void dfwd_phase_mid(int tid, u64 *smem, const LimbConst &lc) {
         double a[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) a[k] = dtile(sm, tile_off<LO>(base, k));
-        d_radix8(a, lc.dtw, (1u << S0) + (vt >> LO), q, qinv, thr);
+        d_radix8(a, lc.dtw, (hb << S0) + (vt >> LO), q, qinv, thr);
 #pragma unroll
         for (int k = 0; k < 8; k++) dtile(sm, tile_off<LO>(base, k)) = a[k];
     }
 }
 // last stage + conversion back to residues: the storers of the integer path are used unchanged (they get x, y in [0, q))
 template <class Store>
-HD void dfwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+HD void dfwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store st) {
     constexpr int G = Store::kGroup;
     const char *sm = reinterpret_cast<const char *>(smem);
     const double q = lc.qd, qinv = lc.qinv;
     const u32 thr = lc.dthr;
-    const double *__restrict__ tw = lc.dtw + (kN >> 1);
+    const double *__restrict__ tw = lc.dtw + ((size_t)hb << (kLogN - 1));
 #pragma unroll 1
     for (int r0 = 0; r0 < 16; r0 += G) {
         double w[G];
@@ -548,6 +548,27 @@ HD void dfwd_phase_e(int tid, const u64 *smem, const LimbConst &lc, Store st) {
         }
     }
 }
+
+// HeadLoad on doubles: the d outermost stages for tile blk, every intermediate renormalised (|result| <= q/2)
+template <int D, class Inner>
+struct DHeadLoad {
+    Inner in; const LimbConst *lc; u32 blk;
+    HD double operator()(u32 i) const {
+        if (D == 0) return in(i);
+        const double q = lc->qd, qinv = lc->qinv;
+        const double *__restrict__ tw = lc->dtw;
+        if (D == 1) {
+            double x = in(i), t = d_mulmod(in(i + kN), tw[1], q, qinv);
+            return d_renorm(blk ? fsub(x, t) : fadd(x, t), q, qinv, lc->dthr);
+        }
+        double x0 = in(i), x1 = in(i + kN);
+        double t0 = d_mulmod(in(i + 2 * kN), tw[1], q, qinv), t1 = d_mulmod(in(i + 3 * kN), tw[1], q, qinv);
+        double s0 = d_renorm(blk < 2 ? fadd(x0, t0) : fsub(x0, t0), q, qinv, lc->dthr);
+        double s1 = d_renorm(blk < 2 ? fadd(x1, t1) : fsub(x1, t1), q, qinv, lc->dthr);
+        double t = d_mulmod(s1, tw[2 + (blk >> 1)], q, qinv);
+        return d_renorm((blk & 1u) ? fsub(s0, t) : fadd(s0, t), q, qinv, lc->dthr);
+    }
+};
 
 // ---- inverse NTT phases (bit-reversed in, natural out), Gentleman-Sande ----
 // Inputs to a pass are < 2q; X' = X + Y doubles the bound per stage, Y' = (X - Y + c)*w with

@@ -14,16 +14,16 @@ namespace shelfi {
 // standalone forward / inverse NTT (parity taps, keygen, and the "NTT HBM GB/s" metric)
 // ------------------------------------------------------------------------------------------
 template <class Load, class Store>
-__device__ __forceinline__ void ntt_forward_tile_d(int tid, u64 *sm, const LimbConst &lc, Load ld, Store st) {
-    dfwd_phase_a(tid, sm, lc, ld);
+__device__ __forceinline__ void ntt_forward_tile_d(int tid, u64 *sm, const LimbConst &lc, u32 hb, Load ld, Store st) {
+    dfwd_phase_a(tid, sm, lc, hb, ld);
     __syncthreads();
-    dfwd_phase_mid<7>(tid, sm, lc);
+    dfwd_phase_mid<7>(tid, sm, lc, hb);
     __syncthreads();
-    dfwd_phase_mid<4>(tid, sm, lc);
+    dfwd_phase_mid<4>(tid, sm, lc, hb);
     __syncthreads();
-    dfwd_phase_mid<1>(tid, sm, lc);
+    dfwd_phase_mid<1>(tid, sm, lc, hb);
     __syncthreads();
-    dfwd_phase_e(tid, sm, lc, st);
+    dfwd_phase_e(tid, sm, lc, hb, st);
 }
 
 // One CTA per 8192-point tile: a polynomial of ring dimension 2^(13+D) is 2^D tiles (ckks_core.cuh).  For D > 0 the
@@ -39,8 +39,9 @@ __global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_kernel(const __gri
     const LimbConst lc = rc.limb[row % rc.limbs];
     const u64 *src = in + ((size_t)row << (kLogN + D));
     u64 *dst = out + ((size_t)row << (kLogN + D)) + (size_t)blk * kN;
-    if (D == 0 && lc.dtw) {   // q < 2^53: the same transform on the FP64 pipe
-        ntt_forward_tile_d(tid, sm, lc, DLoadGlobal{src, lc.q}, StoreFullReducePair{dst, &lc});
+    if (lc.dtw) {   // q < 2^53: the same transform on the FP64 pipe
+        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadGlobal>{DLoadGlobal{src, lc.q}, &lc, blk},
+                           StoreFullReducePair{dst, &lc});
         return;
     }
     fwd_phase_a(tid, sm, lc, hb, HeadLoad<D, LoadGlobal>{LoadGlobal{src}, &lc, blk});
@@ -213,12 +214,14 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * n + tile_off;
     u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * n + tile_off;
     const tw_t *kb = pk_b + (size_t)l * n + tile_off, *ka = pk_a + (size_t)l * n + tile_off;
-    if (D == 0 && lc.dtw) {
-        ntt_forward_tile_d(tid, sm, lc, DLoadTernary{ve_row}, StoreLazyPair{c1});
+    if (lc.dtw) {
+        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve_row}, &lc, blk}, StoreLazyPair{c1});
         __syncthreads();
-        ntt_forward_tile_d(tid, sm, lc, DLoadSigned{m_row, &lc}, StoreMulAdd{kb, c1, c0, &lc});
+        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadSigned>{DLoadSigned{m_row, &lc}, &lc, blk},
+                           StoreMulAdd{kb, c1, c0, &lc});
         __syncthreads();
-        ntt_forward_tile_d(tid, sm, lc, DLoadGaussHi{ve_row}, StoreMulAdd{ka, c1, c1, &lc});
+        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadGaussHi>{DLoadGaussHi{ve_row}, &lc, blk},
+                           StoreMulAdd{ka, c1, c1, &lc});
         return;
     }
     ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve_row, lc.q}, &lc, blk}, StoreLazyPair{c1});
@@ -279,11 +282,11 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
         u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
         u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
         if (lc.dtw) {
-            ntt_forward_tile_d(tid, sm, lc, DLoadTernary{ve_row}, StoreLazyPair{c1});
+            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadTernary{ve_row}, StoreLazyPair{c1});
             __syncthreads();
-            ntt_forward_tile_d(tid, sm, lc, DLoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
+            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
             __syncthreads();
-            ntt_forward_tile_d(tid, sm, lc, DLoadGaussHi{ve_row}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
+            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadGaussHi{ve_row}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
             __syncthreads();
             continue;
         }

@@ -88,10 +88,10 @@ std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *
         B += kBflyGrowth * stages[pass];
     }
     if (H < 16) return "modulus leaves no headroom for the inverse transform";
-    // FP64-pipe forward transform: exact for q <= 1.25 * 2^52 (ckks_core.cuh); one tile per polynomial only
+    // FP64-pipe forward transform: exact for q <= 1.25 * 2^52 (ckks_core.cuh)
     if (dtw) {
         dtw->clear();
-        if (logn == (uint32_t)kLogN && q <= (((uint64_t)5) << 50) && q >= 1024) {
+        if (q <= (((uint64_t)5) << 50) && q >= 1024) {
             dtw->assign(n, 0.0);
             for (uint32_t i = 0; i < n; i++) {
                 uint64_t w = (*tw)[i].w;

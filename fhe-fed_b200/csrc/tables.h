@@ -12,7 +12,7 @@ namespace shelfi {
 // Fills *lc (tw / itw pointers left null) and the two tables; returns "" or why the modulus is unusable.
 // logn = log2(ring dimension), 13..15; the tables hold 2^logn entries.
 // dtw (optional): centred forward twiddles as doubles for the FP64-pipe transform; left empty (and lc->dtw null) when
-// the limb does not qualify (q > 1.25 * 2^52 or more than one tile per polynomial).
+// the limb does not qualify (q > 1.25 * 2^52).
 std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *lc, std::vector<tw_t> *tw,
                             std::vector<tw_t> *itw, std::vector<double> *dtw = nullptr);
 // [PAL] DiscreteFourierTransform::PreComputeTable(M) flattened per stage: entry (len/2 - 1) + j

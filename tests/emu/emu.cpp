@@ -43,12 +43,12 @@ static void replay_forward(u64 *sm, const LimbConst &lc, u32 hb, Load ld, Store 
 }
 // the FP64-pipe variant (ntt_forward_tile_d)
 template <class Load, class Store>
-static void replay_forward_d(u64 *sm, const LimbConst &lc, Load ld, Store st) {
-    FOR_THREADS(kNttThreads) dfwd_phase_a(tid, sm, lc, ld);
-    FOR_THREADS(kNttThreads) dfwd_phase_mid<7>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) dfwd_phase_mid<4>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) dfwd_phase_mid<1>(tid, sm, lc);
-    FOR_THREADS(kNttThreads) dfwd_phase_e(tid, sm, lc, st);
+static void replay_forward_d(u64 *sm, const LimbConst &lc, u32 hb, Load ld, Store st) {
+    FOR_THREADS(kNttThreads) dfwd_phase_a(tid, sm, lc, hb, ld);
+    FOR_THREADS(kNttThreads) dfwd_phase_mid<7>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) dfwd_phase_mid<4>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) dfwd_phase_mid<1>(tid, sm, lc, hb);
+    FOR_THREADS(kNttThreads) dfwd_phase_e(tid, sm, lc, hb, st);
 }
 // intt_tile<D>
 template <int D, class Load>
@@ -118,12 +118,14 @@ void emu_ntt_forward(const Emu *e, uint32_t limb, uint64_t *row) {
     std::vector<u64> sm(kN), src(row, row + e->rc.n);
     const LimbConst lc = e->rc.limb[limb];
     const u32 d = e->rc.log_blocks;
-    if (d == 0 && lc.dtw) {
-        replay_forward_d(sm.data(), lc, DLoadGlobal{src.data(), lc.q}, StoreFullReducePair{row, &lc});
-        return;
-    }
     for (u32 blk = 0; blk < (1u << d); blk++) {
         u64 *dst = row + (size_t)blk * kN;
+        if (lc.dtw) {
+            EMU_D(d, replay_forward_d(sm.data(), lc, head_bits(d, blk),
+                                      DHeadLoad<D, DLoadGlobal>{DLoadGlobal{src.data(), lc.q}, &lc, blk},
+                                      StoreFullReducePair{dst, &lc}))
+            continue;
+        }
         EMU_D(d, replay_forward(sm.data(), lc, head_bits(d, blk), HeadLoad<D, LoadGlobal>{LoadGlobal{src.data()}, &lc, blk},
                                 StoreFullReducePair{dst, &lc}))
     }
@@ -227,10 +229,14 @@ void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const ui
             const size_t off = (size_t)blk * kN;
             u64 *c0 = out + (0 * L + l) * n + off, *c1 = out + (1 * L + l) * n + off;
             const u32 hb = head_bits(d, blk);
-            if (d == 0 && lc.dtw) {
-                replay_forward_d(sm.data(), lc, DLoadTernary{ve}, StoreLazyPair{c1});
-                replay_forward_d(sm.data(), lc, DLoadSigned{(const i64 *)m_e0, &lc}, StoreMulAdd{b.data() + off, c1, c0, &lc});
-                replay_forward_d(sm.data(), lc, DLoadGaussHi{ve}, StoreMulAdd{a.data() + off, c1, c1, &lc});
+            if (lc.dtw) {
+                EMU_D(d, {
+                    replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve}, &lc, blk}, StoreLazyPair{c1});
+                    replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadSigned>{DLoadSigned{(const i64 *)m_e0, &lc}, &lc, blk},
+                                     StoreMulAdd{b.data() + off, c1, c0, &lc});
+                    replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadGaussHi>{DLoadGaussHi{ve}, &lc, blk},
+                                     StoreMulAdd{a.data() + off, c1, c1, &lc});
+                })
                 continue;
             }
             EMU_D(d, {

@@ -190,7 +190,8 @@ def test_deep_parameter_rules_match_oracle(emu, oracle_mod):
 def test_fp64_path_selected_for_the_scaling_limb(emu, emu_ctx, deep_emu_ctx):
     h = emu_ctx["pybind"]
     assert (emu.L.emu_limb_fp64(h, 0), emu.L.emu_limb_fp64(h, 1)) == (0, 1)      # 60-bit q0: integer pipe
-    assert emu.L.emu_limb_fp64(deep_emu_ctx["n16k_l4"], 1) == 0                    # more than one tile: integer path
+    assert [emu.L.emu_limb_fp64(deep_emu_ctx["n16k_l4"], l) for l in range(4)] == [0, 1, 1, 1]
+    assert [emu.L.emu_limb_fp64(deep_emu_ctx["n32k_l8"], l) for l in range(8)] == [0] + [1] * 7
     assert [emu.L.emu_limb_fp64(deep_emu_ctx["n8k_l3"], l) for l in range(3)] == [0, 1, 1]
 
 
