@@ -166,7 +166,7 @@ _pool = _PinnedPool()
 class PinnedBlob:
     """A serialized ciphertext vector held in page-locked host memory (opt-in: ``CKKS(..., pinned=True)``).
 
-    Bytes-like: ``len``, ``bytes(b)``, ``memoryview(b)`` / the buffer protocol through ``b.array`` (numpy uint8 view),
+    Bytes-like: ``len``, ``bytes(b)``, ``memoryview(b)`` (buffer protocol), ``b.array`` (numpy uint8 view),
     equality with ``bytes``.  Passing it back to ``computeWeightedAverage`` / ``decrypt`` moves it over PCIe at the
     link rate instead of through the driver's pageable staging path; ``bytes(b)`` gives the reference's exact type
     when the payload has to leave the process."""
@@ -194,6 +194,9 @@ class PinnedBlob:
         return C.string_at(self._p, self._n)
 
     tobytes = __bytes__
+
+    def __buffer__(self, flags):   # PEP 688: memoryview(b), sock.sendall(b), f.write(b) read the pinned pages directly
+        return memoryview(self.array)
 
     def __eq__(self, other):
         if isinstance(other, PinnedBlob):

@@ -277,7 +277,11 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     encode_sample_emit(tid, kNttThreads, z, ec, sl, cdf, sl.ct_index0 + ct, m_row, ve_row);
     __syncthreads();  // scratch rows written by this block are visible to all of its threads; tile is free
     const u32 L = rc.limbs;
-    for (u32 l = 0; l < L; l++) {
+    // odd CTAs walk the limbs backwards: co-resident CTAs then tend to sit on different pipes (the 60-bit limb on the
+    // integer pipe, the scaling limbs on the FP64 pipe) instead of marching through the same limb together
+    const u32 flip = (blockIdx.x & 1u) ? L - 1 : 0u;
+    for (u32 li = 0; li < L; li++) {
+        const u32 l = flip ? flip - li : li;
         const LimbConst lc = rc.limb[l];
         u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
         u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;

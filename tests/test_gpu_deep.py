@@ -198,3 +198,18 @@ def test_config3_size_properties(shelfi, tmp_path):
     a1 = h.computeWeightedAverage(blobs, w)
     a2 = h.computeWeightedAverage([blobs[2], blobs[0], blobs[1]], [0.25, 0.5, 0.25])
     assert a1 == a2
+
+
+def test_fp64_pipe_equals_integer_pipe_on_deep_contexts(shelfi, gpu_deep, deep_oracles, monkeypatch):
+    """Multi-tile rings: head loader and tile passes on doubles vs the integer path (SHELFI_FP64_NTT=0), bit for bit."""
+    for name in ("n16k_l4", "n32k_l8"):
+        o, hf = deep_oracles[name], gpu_deep[name]
+        monkeypatch.setenv("SHELFI_FP64_NTT", "0")
+        hi = shelfi.CKKS("ckks", o.batchSize, o.scaleFactorBits, o.cryptodir, device=0)
+        hi.loadCryptoParams()
+        monkeypatch.delenv("SHELFI_FP64_NTT")
+        x = np.random.default_rng(2).normal(0, 10.0, 5 * o.batchSize + 3)
+        hf.set_sampler_seed(8); hi.set_sampler_seed(8)
+        b1, b2 = hf.encrypt(x), hi.encrypt(x)
+        hf.set_sampler_seed(None)
+        assert hashlib.sha256(b1).digest() == hashlib.sha256(b2).digest(), name

@@ -383,6 +383,7 @@ def test_pinned_blob_mode_equals_bytes_mode(shelfi, gpu_ckks):
             hh.set_sampler_seed(None)
     assert all(isinstance(b, shelfi.PinnedBlob) for b in blobs_p) and all(isinstance(b, bytes) for b in blobs_b)
     assert [bytes(b) for b in blobs_p] == blobs_b and blobs_p[0] == blobs_b[0] and len(blobs_p[0]) == len(blobs_b[0])
+    assert bytes(memoryview(blobs_p[1])) == blobs_b[1]           # buffer protocol (what sock.sendall / f.write use)
     avg_b = h.computeWeightedAverage(blobs_b, w)
     avg_p = p.computeWeightedAverage(blobs_p, w)
     assert bytes(avg_p) == avg_b == bytes(p.computeWeightedAverage([blobs_p[0], blobs_b[1], memoryview(blobs_b[2])], w))
@@ -400,3 +401,33 @@ def test_pinned_blob_mode_equals_bytes_mode(shelfi, gpu_ckks):
     del blobs_p, lp, ap, avg_p                                   # buffers go back to the pool and are reused
     again = p.encrypt(xs[0])
     assert rel_err(p.decrypt(again, 9000), xs[0]) < RTOL
+
+
+def test_fp64_pipe_ntt_equals_integer_pipe(shelfi, gpu_ckks, monkeypatch):
+    """The scaling limb's forward transform runs on the FP64 pipe (exact double arithmetic); a handle loaded with
+    SHELFI_FP64_NTT=0 keeps it on the integer pipe.  Same bits on 4000 rows and on whole encryptions."""
+    d = str(FIXTURE_DIRS["pybind"]) + "/"
+    monkeypatch.setenv("SHELFI_FP64_NTT", "0")
+    hi = shelfi.CKKS("ckks", 4096, 52, d, device=0)
+    hi.loadCryptoParams()
+    monkeypatch.delenv("SHELFI_FP64_NTT")
+    hf = gpu_ckks["pybind"]
+    rows = 4000
+    rng = np.random.default_rng(77)
+    q = [hf.modulus(0), hf.modulus(1)]
+    a = np.empty((rows, N), np.uint64)
+    for r in range(rows):
+        a[r] = rng.integers(0, q[r % 2], N, dtype=np.uint64)
+    a[1] = q[1] - 1
+    a[3] = q[1] // 2
+    a[5] = q[1] // 2 + 1
+    a[7, ::2] = q[1] - 1
+    d1, d2 = dev_u64(a), dev_u64(a)
+    check(hf, shelfi.lib().shelfi_ntt_forward_device(hf.handle, ptr(d1), rows, stream()))
+    check(hi, shelfi.lib().shelfi_ntt_forward_device(hi.handle, ptr(d2), rows, stream()))
+    assert torch.equal(d1, d2)
+    x = rng.normal(0, 20.0, 300000)
+    hf.set_sampler_seed(5); hi.set_sampler_seed(5)
+    b1, b2 = hf.encrypt(x), hi.encrypt(x)
+    hf.set_sampler_seed(None)
+    assert hashlib.sha256(b1).digest() == hashlib.sha256(b2).digest()
