@@ -1047,9 +1047,18 @@ struct WavgArgs {
 
 struct LimbScalars { u64 c[kMaxLimbs]; };
 
+// plaintext remainder of a selectively encrypted model: out[i] = sum_k w_k * x_k[i] (unfused, in learner order)
+struct PlainWavgArgs {
+    const double *in[kMaxLearnersPerLaunch];
+    double w[kMaxLearnersPerLaunch];
+    u32 k;
+    u32 accumulate;
+};
+
 // one launch may encrypt several learners' vectors (same length n): block b -> learner b / n_ct, ciphertext b % n_ct
 constexpr int kMaxEncryptBatch = 16;
 struct EncryptBatch {
+    const u32 *sel;   // optional selection shared by the learners: learner l's vector is x[l][sel[i]]
     const double *x[kMaxEncryptBatch];
     u64 *ct[kMaxEncryptBatch];
     u64 seed[kMaxEncryptBatch];
@@ -1068,9 +1077,12 @@ HD u64 run_offset(const BlobRuns &br, u64 ct, u32 r) { return ct == 0 ? br.off0[
 
 // ---- encode: MakeCKKSPackedPlaintext up to the integer coefficients (ckks.cpp:80) ----
 // phase 0: chunk of x -> z (zero padded)
-HD void encode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid) {
+// Selective encryption (benchmark_selection*.py encrypt a chosen subset of the parameters): with `sel` the chunk is
+// x[sel[i]] instead of x[i], i.e. the gather is part of the load (and the scatter part of decode_store).
+HD void encode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid,
+                    const u32 *sel = nullptr) {
     for (u32 i = tid; i < ec.slots; i += nthreads) {
-        z[zsw(i)].re = i < n_valid ? x[i] : 0.0;
+        z[zsw(i)].re = i < n_valid ? x[sel ? sel[i] : i] : 0.0;
         z[zsw(i)].im = 0.0;
     }
 }
@@ -1152,8 +1164,9 @@ HD void decode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const
     }
 }
 // phases 1..log_slots: fft_fwd_stage(len = 2 << (p-1)); last phase: real parts * 2^-p
-HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc, double *out, u64 length) {
-    for (u32 i = tid; i < length; i += nthreads) out[i] = fmul(z[zsw(i)].re, dc.pow_p);
+HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc, double *out, u64 length,
+                     const u32 *sel = nullptr) {
+    for (u32 i = tid; i < length; i += nthreads) out[sel ? sel[i] : i] = fmul(z[zsw(i)].re, dc.pow_p);
 }
 
 // ---- slot counts above one FFT tile (4096 complex values, 64 KiB) and ring dimensions above one NTT tile ----
@@ -1161,9 +1174,14 @@ HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc
 // apart into 2^df independent 4096-point blocks.  Block fb's loader applies those stages to the 2^df inputs
 // that share its tile-local index (same butterflies, same order as the reference => same doubles), the tile
 // runs the 12 inner stages, and the bit reversal sends tile position r to slot (r << df) | bitrev(fb).
-HD cplx encode_input(const double *x, u64 n_valid, u32 j) { return cplx{j < n_valid ? x[j] : 0.0, 0.0}; }
+struct EncSrc {             // one chunk of encode input: x[j] or x[sel[j]], j < n_valid
+    const double *x;
+    u64 n_valid;
+    const u32 *sel;
+};
+HD cplx encode_input(const EncSrc &x, u64, u32 j) { return cplx{j < x.n_valid ? x.x[x.sel ? x.sel[j] : j] : 0.0, 0.0}; }
 template <int DF>
-HD cplx encode_head(const EncodeConst &ec, const double *x, u64 n_valid, u32 fb, u32 i) {
+HD cplx encode_head(const EncodeConst &ec, const EncSrc &x, u64 n_valid, u32 fb, u32 i) {
     if (DF == 0) return encode_input(x, n_valid, i);
     const cplx *__restrict__ twi = ec.tw_inv;
     if (DF == 1) {
@@ -1180,9 +1198,11 @@ HD cplx encode_head(const EncodeConst &ec, const double *x, u64 n_valid, u32 fb,
     return (fb & 1u) ? a3 : a2;
 }
 template <int DF>
-HD void encode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid, u32 fb) {
+HD void encode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid, u32 fb,
+                          const u32 *sel = nullptr) {
     const u32 tile_slots = ec.slots < kFftFast ? ec.slots : kFftFast;
-    for (u32 i = tid; i < tile_slots; i += nthreads) z[zsw(i)] = encode_head<DF>(ec, x, n_valid, fb, i);
+    const EncSrc src{x, n_valid, sel};
+    for (u32 i = tid; i < tile_slots; i += nthreads) z[zsw(i)] = encode_head<DF>(ec, src, n_valid, fb, i);
 }
 // tile (finalized: bit-reversed within the tile, scaled, rounded) -> coefficients m[gap*slot], m[gap*slot + nh]
 template <int DF>
@@ -1261,7 +1281,8 @@ HD void decode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec,
 }
 // the df outermost FFTSpecial stages on the 2^df values sharing tile-local index i, then real parts * 2^-p
 template <int DF>
-HD void decode_tail(u32 i, const cplx *zs, const EncodeConst &ec, const DecodeConst &dc, double *out, u64 length) {
+HD void decode_tail(u32 i, const cplx *zs, const EncodeConst &ec, const DecodeConst &dc, double *out, u64 length,
+                    const u32 *sel = nullptr) {
     const cplx *__restrict__ twf = ec.tw_fwd;
     cplx a[1 << DF];
 #pragma unroll
@@ -1277,7 +1298,7 @@ HD void decode_tail(u32 i, const cplx *zs, const EncodeConst &ec, const DecodeCo
 #pragma unroll
     for (int k = 0; k < (1 << DF); k++) {
         u64 slot = i + (u64)k * kFftFast;
-        if (slot < length) out[slot] = fmul(a[k].re, dc.pow_p);
+        if (slot < length) out[sel ? sel[slot] : slot] = fmul(a[k].re, dc.pow_p);
     }
 }
 

@@ -155,8 +155,10 @@ struct shelfi_ckks {
     // device-resident parameters
     DeviceBuffer d_tw, d_itw, d_dtw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
     // scratch
-    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_out, s_vals, s_zs, s_rows;
+    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_image3, s_out, s_vals, s_zs, s_rows;
     cudaStream_t stream = nullptr;
+    cudaEvent_t ev_stage_out = nullptr;
+    cudaStream_t d2h_stream = nullptr;   // created on first use: results leave while the next inputs arrive (full duplex)
     cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
     cudaStream_t copy_stream = nullptr;
     bool seeded = false;
@@ -415,7 +417,7 @@ uint64_t fresh_seed() {
 // k learners' vectors (all of length n) in one launch: the grid covers k * n_ct ciphertexts, so small models still
 // fill the machine and co-resident CTAs are out of phase with one another.
 int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uint64_t n, uint64_t ct_index0,
-                       uint64_t *const *d_ct, cudaStream_t s) {
+                       uint64_t *const *d_ct, cudaStream_t s, const uint32_t *d_sel = nullptr) {
     uint64_t n_ct = (n + h->batch - 1) / h->batch;
     const uint64_t N = h->ctx.ring_dim;
     if (n_ct * k > (0x7fffffffull / (2 * kMaxLimbs)) >> h->rc.log_blocks)
@@ -431,7 +433,8 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
         for (uint32_t i = 0; i < k; i++) {
             sc.seed = h->seeded ? h->seed : fresh_seed();
             timed(h, kKEncodeSample, s, [&] {
-                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s);
+                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s,
+                                     d_sel);
             });
             timed(h, kKEncrypt, s, [&] {
                 launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(),
@@ -445,6 +448,7 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
         EncryptBatch eb{};
         eb.k = std::min<uint32_t>(kMaxEncryptBatch, k - base);
         eb.n_ct = (u32)n_ct;
+        eb.sel = d_sel;
         CU(h->s_m.reserve((size_t)eb.k * n_ct * N * sizeof(int64_t)));
         CU(h->s_ve.reserve((size_t)eb.k * n_ct * N * sizeof(uint16_t)));
         for (uint32_t i = 0; i < eb.k; i++) {
@@ -467,7 +471,7 @@ int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_ind
 bool general_decode(const shelfi_ckks *h) { return h->rc.log_blocks > 0 || h->ctx.limbs > 2; }
 
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
-                  cudaStream_t s) {
+                  cudaStream_t s, const uint32_t *d_sel = nullptr) {
     const uint64_t N = h->ctx.ring_dim;
     CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * N * sizeof(uint64_t)));
     timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(h->rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
@@ -477,14 +481,15 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
     dc.pre = std::pow(sf, -1) * std::pow(2, p);   // [PAL] Decode: scale to 2^p before the FFT, back after it
     dc.pow_p = std::pow(2, -p);
     if (!general_decode(h)) {
-        timed(h, kKDecode, s, [&] { launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s); });
+        timed(h, kKDecode, s, [&] { launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s, d_sel); });
     } else {
         CU(h->s_vals.reserve(n_ct * N * sizeof(double)));
         if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(n_ct * (size_t)h->ec.slots * sizeof(cplx)));
         timed(h, kKDecode, s, [&] {
             launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, h->s_vals.as<double>(), nullptr, nullptr,
                        nullptr, s);
-            launch_decode_fft(h->rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s);
+            launch_decode_fft(h->rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s,
+                              d_sel);
         });
     }
     CU(cudaGetLastError());
@@ -516,6 +521,7 @@ struct LayerSlot {
     wire::BlobPlan plan;
 };
 uint64_t align8(uint64_t v) { return (v + 7) & ~(uint64_t)7; }
+constexpr uint64_t kPipelineMinCts = 128;   // below this a call is launch latency, not copy time
 
 // ckks.cpp:61-104 for n_layers independent vectors xs[s]: copies and encrypt kernels of all layers queued on one
 // stream, one D2H.  n_layers == 1 is CKKS::encrypt.  Blob s lands at dst + offsets[s], lens[s] bytes.
@@ -557,6 +563,45 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
     CUB(h->s_x.reserve(n * sizeof(double)));
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
     CUB(h->s_image.reserve(image_bytes(image)));
+    if (n_layers == 1 && n_ct >= kPipelineMinCts && is_pinned(dst)) {
+        // One large vector into a page-locked destination: the blob is 8x the input, so the call is the D2H copy plus
+        // whatever is not hidden under it.  Ciphertext groups go through copy-in / encrypt / pack on the compute stream
+        // while the previous group's bytes are already crossing PCIe on the copy stream.
+        const LayerSlot &ls = slot[0];
+        const wire::BlobPlan &pl = ls.plan;
+        const uint32_t groups = n_ct >= 4 * kPipelineMinCts ? 4 : 2;
+        cudaStream_t cs = h->copy_stream;
+        auto run_start = [&](uint64_t j) { return j == 0 ? pl.run0[0] : pl.run1[0] + (j - 1) * pl.stride; };
+        uint64_t sent = 0;
+        for (uint32_t g = 0; g < groups; g++) {
+            const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
+            const uint64_t first = c0 * h->batch, count = std::min(ls.n, c1 * h->batch) - first;
+            if ((rcode = h2d(h, h->s_x.as<double>() + first, xs[0] + first, count * sizeof(double), s))) return bail(rcode);
+            if ((rcode = encrypt_dense(h, h->s_x.as<double>() + first, count, c0, h->s_dense.as<u64>() + c0 * ct_words, s)))
+                return bail(rcode);
+            uint64_t r0[2 * kMaxLimbs], r1[2 * kMaxLimbs];   // run offsets of ciphertexts c0 and c0 + 1
+            for (uint32_t r = 0; r < 2 * h->ctx.limbs; r++) {
+                r0[r] = c0 == 0 ? pl.run0[r] : pl.run1[r] + (c0 - 1) * pl.stride;
+                r1[r] = pl.run1[r] + c0 * pl.stride;
+            }
+            timed(h, kKPack, s, [&] {
+                launch_pack(h->rc, to_runs(h, r0, r1, pl.stride), h->s_dense.as<u64>() + c0 * ct_words, h->s_image.as<u64>(),
+                            c1 - c0, s);
+            });
+            CUB(cudaGetLastError());
+            CUB(cudaEventRecord(h->ev_done[g & 1], s));
+            CUB(cudaStreamWaitEvent(cs, h->ev_done[g & 1], 0));
+            const uint64_t upto = g + 1 == groups ? total : run_start(c1);   // header bytes are written by the host below
+            CUB(cudaMemcpyAsync(dst + sent, h->s_image.as<uint8_t>() + sent, upto - sent, cudaMemcpyDeviceToHost, cs));
+            sent = upto;
+        }
+        CUB(cudaStreamSynchronize(cs));
+        write_segments(pl, dst);
+        if (offsets) offsets[0] = 0;
+        lens[0] = pl.size;
+        if (total_len) *total_len = total;
+        return 0;
+    }
     for (uint32_t i = 0; i < n_layers; i++)
         if ((rcode = h2d(h, h->s_x.as<double>() + slot[i].x0, xs[i], slot[i].n * sizeof(double), s))) return bail(rcode);
     for (const LayerSlot &ls : slot) {   // every layer is its own ciphertext vector: sampler index restarts at 0
@@ -636,36 +681,86 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
     CUB(h->s_image.reserve(std::max(max_image, image_bytes(image))));
     CUB(h->s_image2.reserve(max_image));
     DeviceBuffer *img[2] = {&h->s_image, &h->s_image2};
-    for (uint32_t i = 0; i < k; i++) {
-        int b = i & 1;
-        if (i >= 2) CUB(cudaStreamWaitEvent(cs, h->ev_done[b], 0));
-        for (uint32_t s = 0; s < n_layers; s++) {
-            const size_t id = (size_t)i * n_layers + s;
-            if ((rcode = h2d(h, img[b]->as<uint8_t>() + in_off[id], blobs[id], blob_lens[id], cs))) return bail(rcode);
+    // One large vector into a page-locked destination: the ciphertext range is cut in two so that the first part's
+    // result crosses PCIe device->host while the second part's inputs are still arriving host->device.
+    const bool split = n_layers == 1 && n_ct >= 2 * kPipelineMinCts && is_pinned(dst);
+    if (split) {
+        if (!h->d2h_stream) {
+            CUB(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+            CUB(cudaEventCreateWithFlags(&h->ev_stage_out, cudaEventDisableTiming));
         }
-        CUB(cudaEventRecord(h->ev_copy[b], cs));
-        CUB(cudaStreamWaitEvent(st, h->ev_copy[b], 0));
-        int64_t sc = weight_constant(h, w[i]);
-        LimbScalars cs_l{};
-        for (uint32_t l = 0; l < L; l++) cs_l.c[l] = nt::signed_mod(sc, h->ctx.modulus[l]);
-        for (uint32_t s = 0; s < n_layers; s++) {
-            const size_t id = (size_t)i * n_layers + s;
-            timed(h, kKUnpackScaleAcc, st, [&] {
-                launch_unpack_scale_accumulate(h->rc, to_runs(h, maps[id].run0, maps[id].run1, maps[id].stride),
-                                               img[b]->as<u64>() + in_off[id] / 8, cs_l, i == 0 ? 1u : 0u,
-                                               h->s_dense.as<u64>() + slot[s].ct0 * ct_words, slot[s].n_ct, st);
+        CUB(h->s_image3.reserve(image_bytes(image)));
+    }
+    const uint32_t groups = split ? 2 : 1;
+    u64 *out_image = split ? h->s_image3.as<u64>() : h->s_image.as<u64>();
+    auto run_start = [](const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint64_t j) {
+        return j == 0 ? run0[0] : run1[0] + (j - 1) * stride;
+    };
+    auto sub_runs = [&](const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint64_t c0) {
+        uint64_t r0[2 * kMaxLimbs], r1[2 * kMaxLimbs];   // run offsets of ciphertexts c0 and c0 + 1
+        for (uint32_t r = 0; r < 2 * L; r++) {
+            r0[r] = c0 == 0 ? run0[r] : run1[r] + (c0 - 1) * stride;
+            r1[r] = run1[r] + c0 * stride;
+        }
+        return to_runs(h, r0, r1, stride);
+    };
+    uint64_t sent = 0;
+    for (uint32_t g = 0, seq = 0; g < groups; g++) {
+        // ciphertexts [c0, c1) of every layer's vector (split == false: everything; split: 3/4 then 1/4, so the second
+        // part's inputs take about as long as the first part's result)
+        const uint64_t cut = n_ct - n_ct / 4;
+        const uint64_t c0 = split && g == 1 ? cut : 0, c1 = split && g == 0 ? cut : 0;   // c1 == 0: to the end
+        for (uint32_t i = 0; i < k; i++, seq++) {
+            int b = seq & 1;
+            if (seq >= 2) CUB(cudaStreamWaitEvent(cs, h->ev_done[b], 0));
+            for (uint32_t s = 0; s < n_layers; s++) {
+                const size_t id = (size_t)i * n_layers + s;
+                const wire::BlobMap &m = maps[id];
+                const uint64_t lo = c0 ? run_start(m.run0, m.run1, m.stride, c0) : 0;
+                const uint64_t hi = c1 ? run_start(m.run0, m.run1, m.stride, c1) : blob_lens[id];
+                if ((rcode = h2d(h, img[b]->as<uint8_t>() + in_off[id] + lo, blobs[id] + lo, hi - lo, cs))) return bail(rcode);
+            }
+            CUB(cudaEventRecord(h->ev_copy[b], cs));
+            CUB(cudaStreamWaitEvent(st, h->ev_copy[b], 0));
+            int64_t sc = weight_constant(h, w[i]);
+            LimbScalars cs_l{};
+            for (uint32_t l = 0; l < L; l++) cs_l.c[l] = nt::signed_mod(sc, h->ctx.modulus[l]);
+            for (uint32_t s = 0; s < n_layers; s++) {
+                const size_t id = (size_t)i * n_layers + s;
+                const uint64_t cnt = (c1 ? c1 : slot[s].n_ct) - c0;
+                timed(h, kKUnpackScaleAcc, st, [&] {
+                    launch_unpack_scale_accumulate(h->rc, sub_runs(maps[id].run0, maps[id].run1, maps[id].stride, c0),
+                                                   img[b]->as<u64>() + in_off[id] / 8, cs_l, i == 0 ? 1u : 0u,
+                                                   h->s_dense.as<u64>() + (slot[s].ct0 + c0) * ct_words, cnt, st);
+                });
+            }
+            CUB(cudaGetLastError());
+            CUB(cudaEventRecord(h->ev_done[b], st));
+        }
+        for (const LayerSlot &ls : slot) {
+            const uint64_t cnt = (c1 ? c1 : ls.n_ct) - c0;
+            timed(h, kKPack, st, [&] {
+                launch_pack(h->rc, sub_runs(ls.plan.run0, ls.plan.run1, ls.plan.stride, c0),
+                            h->s_dense.as<u64>() + (ls.ct0 + c0) * ct_words, out_image + ls.off / 8, cnt, st);
             });
         }
         CUB(cudaGetLastError());
-        CUB(cudaEventRecord(h->ev_done[b], st));
+        if (split) {   // this part's bytes start their way back while the next part's inputs are still coming in
+            const wire::BlobPlan &pl = slot[0].plan;
+            const uint64_t upto = c1 ? run_start(pl.run0, pl.run1, pl.stride, c1) : total;
+            CUB(cudaEventRecord(h->ev_stage_out, st));
+            CUB(cudaStreamWaitEvent(h->d2h_stream, h->ev_stage_out, 0));
+            CUB(cudaMemcpyAsync(dst + sent, reinterpret_cast<const uint8_t *>(out_image) + sent, upto - sent,
+                                cudaMemcpyDeviceToHost, h->d2h_stream));
+            sent = upto;
+        }
     }
-    for (const LayerSlot &ls : slot)
-        timed(h, kKPack, st, [&] {
-            launch_pack(h->rc, to_runs(h, ls.plan.run0, ls.plan.run1, ls.plan.stride), h->s_dense.as<u64>() + ls.ct0 * ct_words,
-                        h->s_image.as<u64>() + ls.off / 8, ls.n_ct, st);
-        });
-    CUB(cudaGetLastError());
-    if ((rcode = d2h_sync(h, dst, h->s_image.p, total, st))) return bail(rcode);
+    if (split) {
+        CUB(cudaStreamSynchronize(h->d2h_stream));
+        CUB(cudaStreamSynchronize(st));
+    } else if ((rcode = d2h_sync(h, dst, h->s_image.p, total, st))) {
+        return bail(rcode);
+    }
     for (uint32_t s = 0; s < n_layers; s++) {
         write_segments(slot[s].plan, dst + slot[s].off);
         if (offsets) offsets[s] = slot[s].off;
@@ -763,8 +858,8 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         cudaDeviceSynchronize();
         h->prof.release();
         free_params(h);
-        for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_out,
-                                &h->s_vals, &h->s_zs, &h->s_rows})
+        for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_image3,
+                                &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows})
             b->release();
         for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_copy[i]); cudaEventDestroy(h->ev_done[i]); }
         for (int i = 0; i < 2; i++) {
@@ -774,6 +869,7 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         delete h->copier;
         cudaStreamDestroy(h->stream);
         cudaStreamDestroy(h->copy_stream);
+        if (h->d2h_stream) { cudaStreamDestroy(h->d2h_stream); cudaEventDestroy(h->ev_stage_out); }
     }
     delete h;
 }
@@ -1147,6 +1243,56 @@ int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, d
         return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
     return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n,
                          static_cast<cudaStream_t>(stream));
+}
+
+// ---- selective encryption (benchmark_selection.py:152-193, benchmark_selection_rate.py:133-141): only the chosen
+// parameters go through CKKS, the rest is averaged in plaintext on the same device ----
+int shelfi_encrypt_selected_many_device(shelfi_ckks *h, const double *const *d_x, uint32_t k, const uint32_t *d_sel,
+                                        uint64_t n_sel, uint64_t ct_index0, uint64_t *const *d_ct, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, true, false);
+    if (rcode) return rcode;
+    if (!d_x || !d_ct || !d_sel || n_sel == 0 || k == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    for (uint32_t i = 0; i < k; i++)
+        if (!d_x[i] || !d_ct[i]) return fail(h, SHELFI_ERR_ARG, "null learner buffer");
+    return encrypt_dense_many(h, d_x, k, n_sel, ct_index0, d_ct, static_cast<cudaStream_t>(stream), d_sel);
+}
+
+int shelfi_decrypt_scatter_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor,
+                                  double *d_out, const uint32_t *d_sel, uint64_t n_sel, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!d_ct || !d_out || !d_sel || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    if (n_sel == 0 || n_sel > n_ct * h->batch || n_sel + h->batch <= n_ct * h->batch)
+        return fail(h, SHELFI_ERR_ARG, "n_sel inconsistent with the number of ciphertexts");
+    return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n_sel,
+                         static_cast<cudaStream_t>(stream), d_sel);
+}
+
+int shelfi_plain_weighted_sum_device(shelfi_ckks *h, const double *const *d_x, const float *weights, uint32_t k,
+                                     uint64_t n, double *d_out, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (!d_x || !weights || !d_out || k == 0 || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    for (uint32_t base = 0; base < k; base += kMaxLearnersPerLaunch) {
+        PlainWavgArgs pa{};
+        pa.k = std::min<uint32_t>(kMaxLearnersPerLaunch, k - base);
+        pa.accumulate = base ? 1u : 0u;
+        for (uint32_t i = 0; i < pa.k; i++) {
+            if (!d_x[base + i]) return fail(h, SHELFI_ERR_ARG, "null learner buffer");
+            pa.in[i] = d_x[base + i];
+            pa.w[i] = (double)weights[base + i];   // the same float32 -> double widening as the encrypted part
+        }
+        launch_plain_weighted_sum(pa, n, d_out, s);
+    }
+    CU(cudaGetLastError());
+    return 0;
 }
 
 int shelfi_pack_device(shelfi_ckks *h, const uint64_t *d_dense, uint64_t n_ct, uint8_t *d_image, void *stream) {

@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(kTailThreads) intt_tail_kernel(const __grid_co
 template <bool SAMPLE>
 __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_constant__ EncodeConst ec,
                                                              const __grid_constant__ SamplerConst sc, const double *x,
-                                                             u64 n, i64 *m_e0, uint16_t *ve) {
+                                                             u64 n, i64 *m_e0, uint16_t *ve, const u32 *sel) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
     __shared__ u64 cdf[32];
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
     if (SAMPLE && tid < 32) cdf[tid] = sc.gauss_cdf[tid];
     u64 first = ct * ec.batch;
     u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
-    encode_load(tid, kFftThreads, z, ec, x + first, n_valid);
+    encode_load(tid, kFftThreads, z, ec, sel ? x : x + first, n_valid, sel ? sel + first : nullptr);
     __syncthreads();
     if (ec.slots == kFftFast) {
         fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
 // consecutive coefficients, the FFT blocks own strided ones).
 template <int DF>
 __global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_constant__ EncodeConst ec, u32 n_ring,
-                                                                   const double *x, u64 n, i64 *m) {
+                                                                   const double *x, u64 n, i64 *m, const u32 *sel) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
     const int tid = threadIdx.x;
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_
     const u64 ct = blockIdx.x >> DF;
     const u64 first = ct * ec.batch;
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
-    encode_load_block<DF>(tid, kFftThreads, z, ec, x + first, n_valid, fb);
+    encode_load_block<DF>(tid, kFftThreads, z, ec, sel ? x : x + first, n_valid, fb, sel ? sel + first : nullptr);
     __syncthreads();
     EncodeConst et = ec;                       // the tile's own geometry for the bit reversal
     if (ec.slots >= kFftFast) {
@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
     i64 *m_row = m_e0 + (u64)blockIdx.x * (u64)kN;
     uint16_t *ve_row = ve + (u64)blockIdx.x * (u64)kN;
-    encode_load(tid, kNttThreads, z, ec, x + first, n_valid);
+    encode_load(tid, kNttThreads, z, ec, eb.sel ? x : x + first, n_valid, eb.sel ? eb.sel + first : nullptr);
     __syncthreads();
     if (ec.slots == kFftFast) {
         fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
@@ -331,7 +331,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) decrypt_intt_kernel(const __gr
 __global__ void __launch_bounds__(kFftThreads) decode_kernel(const __grid_constant__ EncodeConst ec,
                                                              const __grid_constant__ DecodeConst dc, u32 limbs,
                                                              const u64 *coeff, double *out, u64 n, i64 *tap_hi,
-                                                             u64 *tap_lo) {
+                                                             u64 *tap_lo, const u32 *sel) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
     const int tid = threadIdx.x;
@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(kFftThreads) decode_kernel(const __grid_consta
     u64 first = ct * ec.batch;
     if (first >= n) return;
     u64 length = n - first < ec.batch ? n - first : ec.batch;
-    decode_store(tid, kFftThreads, z, dc, out + first, length);
+    decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr);
 }
 
 // General decode (any ring dimension, limb count, slot count): crt_kernel turns the L residues of every coefficient
@@ -382,7 +382,8 @@ __global__ void __launch_bounds__(kCrtThreads) crt_kernel(const __grid_constant_
 template <int DF>
 __global__ void __launch_bounds__(kFftThreads) decode_fft_kernel(const __grid_constant__ EncodeConst ec,
                                                                  const __grid_constant__ DecodeConst dc, u32 n_ring,
-                                                                 const double *vals, cplx *zs, double *out, u64 n) {
+                                                                 const double *vals, cplx *zs, double *out, u64 n,
+                                                                 const u32 *sel) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
     const int tid = threadIdx.x;
@@ -405,7 +406,7 @@ __global__ void __launch_bounds__(kFftThreads) decode_fft_kernel(const __grid_co
         u64 first = ct * ec.batch;
         if (first >= n) return;
         u64 length = n - first < ec.batch ? n - first : ec.batch;
-        decode_store(tid, kFftThreads, z, dc, out + first, length);
+        decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr);
     } else {
         cplx *dst = zs + ct * (u64)ec.slots + (u64)fb * kFftFast;
         for (u32 i = tid; i < kFftFast; i += kFftThreads) dst[i] = z[zsw(i)];
@@ -414,13 +415,13 @@ __global__ void __launch_bounds__(kFftThreads) decode_fft_kernel(const __grid_co
 template <int DF>
 __global__ void __launch_bounds__(kTailThreads) decode_tail_kernel(const __grid_constant__ EncodeConst ec,
                                                                    const __grid_constant__ DecodeConst dc,
-                                                                   const cplx *zs, double *out, u64 n) {
+                                                                   const cplx *zs, double *out, u64 n, const u32 *sel) {
     const u64 ct = blockIdx.y;
     const u32 i = blockIdx.x * kTailThreads + threadIdx.x;
     u64 first = ct * ec.batch;
     if (first >= n) return;
     u64 length = n - first < ec.batch ? n - first : ec.batch;
-    decode_tail<DF>(i, zs + ct * (u64)ec.slots, ec, dc, out + first, length);
+    decode_tail<DF>(i, zs + ct * (u64)ec.slots, ec, dc, sel ? out : out + first, length, sel ? sel + first : nullptr);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -471,6 +472,37 @@ __global__ void __launch_bounds__(kWavgThreads) weighted_sum_kernel(const __grid
     for (int p = 0; p < kWavgPairsPerThread; p++) {
         ulonglong2 r = make_ulonglong2(reduce128(acc[p][0], lc), reduce128(acc[p][1], lc));
         reinterpret_cast<ulonglong2 *>(out)[pair0 + (u64)p * kWavgThreads] = r;
+    }
+}
+
+// plaintext weighted sum (selective encryption: the parameters that are not encrypted); streaming, 8 B per lane
+constexpr int kPlainThreads = 256;
+constexpr int kPlainPerThread = 4;
+__global__ void __launch_bounds__(kPlainThreads) plain_weighted_sum_kernel(const __grid_constant__ PlainWavgArgs pa, u64 n,
+                                                                           double *out) {
+    const u64 base = (u64)blockIdx.x * (kPlainThreads * kPlainPerThread) + threadIdx.x;
+    double acc[kPlainPerThread];
+#pragma unroll
+    for (int p = 0; p < kPlainPerThread; p++) {
+        const u64 i = base + (u64)p * kPlainThreads;
+        acc[p] = (pa.accumulate && i < n) ? out[i] : 0.0;
+    }
+    for (u32 k = 0; k < pa.k; k++) {
+        const double *__restrict__ x = pa.in[k];
+        const double w = pa.w[k];
+        double v[kPlainPerThread];
+#pragma unroll
+        for (int p = 0; p < kPlainPerThread; p++) {
+            const u64 i = base + (u64)p * kPlainThreads;
+            v[p] = i < n ? x[i] : 0.0;
+        }
+#pragma unroll
+        for (int p = 0; p < kPlainPerThread; p++) acc[p] = fadd(acc[p], fmul(w, v[p]));
+    }
+#pragma unroll
+    for (int p = 0; p < kPlainPerThread; p++) {
+        const u64 i = base + (u64)p * kPlainThreads;
+        if (i < n) out[i] = acc[p];
     }
 }
 
@@ -579,25 +611,25 @@ void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s
     if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, data);
 }
 void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s) {
+                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s, const u32 *sel) {
     if (!n_ct) return;
     if (rc.log_blocks == 0) {
-        encode_kernel<true><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m_e0, ve);
+        encode_kernel<true><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m_e0, ve, sel);
         return;
     }
-    launch_encode_only(rc, ec, x, n, n_ct, m_e0, s);
+    launch_encode_only(rc, ec, x, n, n_ct, m_e0, s, sel);
     sample_add_kernel<<<dim3((rc.n / 4 + kSampleThreads - 1) / kSampleThreads, n_ct), kSampleThreads, 0, s>>>(sc, rc.n,
                                                                                                            m_e0, ve);
 }
 void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
-                        cudaStream_t s) {
+                        cudaStream_t s, const u32 *sel) {
     if (!n_ct) return;
     if (rc.log_blocks == 0) {
         SamplerConst sc{};
-        encode_kernel<false><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m, nullptr);
+        encode_kernel<false><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m, nullptr, sel);
         return;
     }
-    DISPATCH_D(fft_log_blocks(ec), encode_block_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, rc.n, x, n, m))
+    DISPATCH_D(fft_log_blocks(ec), encode_block_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, rc.n, x, n, m, sel))
 }
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s) {
@@ -618,10 +650,10 @@ void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64
     if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, coeff);
 }
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
-                   double *out, u64 n, cudaStream_t s) {
+                   double *out, u64 n, cudaStream_t s, const u32 *sel) {
     if (n_ct)   // ring dimension 8192, at most two limbs: CRT and FFT in one kernel
         decode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, dc, rc.limbs, coeff, out, n, nullptr,
-                                                                        nullptr);
+                                                                        nullptr, sel);
 }
 void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,
                 double *vals, u64 *tap8, i64 *tap_hi, u64 *tap_lo, cudaStream_t s) {
@@ -630,25 +662,29 @@ void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn,
     DISPATCH_L(rc.limbs, crt_kernel<L><<<grid, kCrtThreads, 0, s>>>(dc, cn, rc.n, coeff, vals, tap8, tap_hi, tap_lo))
 }
 void launch_decode_fft(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const double *vals, cplx *zs,
-                       u32 n_ct, double *out, u64 n, cudaStream_t s) {
+                       u32 n_ct, double *out, u64 n, cudaStream_t s, const u32 *sel) {
     if (!n_ct) return;
     const u32 df = fft_log_blocks(ec);
-    DISPATCH_D(df, decode_fft_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, dc, rc.n, vals, zs, out, n))
-    if (df == 1) decode_tail_kernel<1><<<dim3(kFftFast / kTailThreads, n_ct), kTailThreads, 0, s>>>(ec, dc, zs, out, n);
-    if (df == 2) decode_tail_kernel<2><<<dim3(kFftFast / kTailThreads, n_ct), kTailThreads, 0, s>>>(ec, dc, zs, out, n);
+    DISPATCH_D(df, decode_fft_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, dc, rc.n, vals, zs, out, n, sel))
+    if (df == 1) decode_tail_kernel<1><<<dim3(kFftFast / kTailThreads, n_ct), kTailThreads, 0, s>>>(ec, dc, zs, out, n, sel);
+    if (df == 2) decode_tail_kernel<2><<<dim3(kFftFast / kTailThreads, n_ct), kTailThreads, 0, s>>>(ec, dc, zs, out, n, sel);
 }
 void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coeff, u32 n_ct, i64 *hi, u64 *lo,
                      cudaStream_t s) {
     EncodeConst ec{};
     ec.slots = kN / 2; ec.gap = 1; ec.log_slots = kLogN - 1; ec.batch = kN / 2;
     if (n_ct)
-        decode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, dc, rc.limbs, coeff, nullptr, 0, hi, lo);
+        decode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, dc, rc.limbs, coeff, nullptr, 0, hi, lo, nullptr);
 }
 void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 n_ct, cudaStream_t s) {
     u64 elems = n_ct * 2 * rc.limbs * (u64)rc.n;
     if (elems) weighted_sum_kernel<<<(unsigned)(elems / kWavgElemsPerCta), kWavgThreads, 0, s>>>(rc, wa, out);
 }
 static dim3 run_grid(const BlobRuns &br, u64 n_ct) { return dim3((unsigned)(n_ct * br.runs), br.n / 2048); }
+void launch_plain_weighted_sum(const PlainWavgArgs &pa, u64 n, double *out, cudaStream_t s) {
+    const u64 per = (u64)kPlainThreads * kPlainPerThread;
+    if (n) plain_weighted_sum_kernel<<<(unsigned)((n + per - 1) / per), kPlainThreads, 0, s>>>(pa, n, out);
+}
 void launch_unpack(const RingConst &, const BlobRuns &br, const u64 *image, u64 *dense, u64 n_ct, cudaStream_t s) {
     if (n_ct) unpack_kernel<<<run_grid(br, n_ct), kPackThreads, 0, s>>>(br, image, dense);
 }

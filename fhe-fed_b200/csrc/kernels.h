@@ -14,8 +14,10 @@ void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, 
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
 
 // encode + sample: x[n] -> m_e0[n_ct][N] (m + e0, signed) and ve[n_ct][N] (v in the low byte, e1 in the high byte)
+// `sel` (optional, here and below): selective encryption — chunk element i is x[sel[i]] on the way in and
+// out[sel[i]] on the way out, so gather and scatter cost no pass of their own
 void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s);
+                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s, const u32 *sel = nullptr);
 // encrypt: three forward NTTs per (ciphertext, limb) + public-key combine -> ct[n_ct][2][L][N]
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s);
@@ -26,22 +28,25 @@ void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const Samp
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s);
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
-                   double *out, u64 n, cudaStream_t s);
+                   double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);
 // general decode: CRT of any limb count -> vals[n_ct][N] doubles (x dc.pre), optional taps of the centred integer
 // (tap8: 8 two's-complement words per coefficient; tap_hi/tap_lo: its low 128 bits)
 void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,
                 double *vals, u64 *tap8, i64 *tap_hi, u64 *tap_lo, cudaStream_t s);
 // ... then FFTSpecial per 4096-slot tile (+ tail pass for more slots; zs = scratch of n_ct * slots complex)
 void launch_decode_fft(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const double *vals, cplx *zs,
-                       u32 n_ct, double *out, u64 n, cudaStream_t s);
+                       u32 n_ct, double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);
 // debug/parity taps of the two halves above
 void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
-                        cudaStream_t s);
+                        cudaStream_t s, const u32 *sel = nullptr);
 void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coeff, u32 n_ct, i64 *hi, u64 *lo,
                      cudaStream_t s);
 
 // out = sum_k c_k * in_k mod q over dense payloads of n_ct ciphertexts
 void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 n_ct, cudaStream_t s);
+
+// out[i] (+)= sum_k w_k * x_k[i] in plaintext (the unencrypted part of a selectively encrypted model)
+void launch_plain_weighted_sum(const PlainWavgArgs &pa, u64 n, double *out, cudaStream_t s);
 
 // serialized blob image <-> dense payload
 void launch_unpack(const RingConst &rc, const BlobRuns &br, const u64 *image, u64 *dense, u64 n_ct, cudaStream_t s);

@@ -157,6 +157,22 @@ int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const 
                                           uint64_t n_ct, uint64_t *d_acc, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
                           uint64_t n, void *stream);
+/* ---- selective encryption: only a chosen subset of the parameters goes through CKKS, the rest is averaged in
+ * plaintext (the callers code/benchmark_selection.py:152-193 pick whole layers, benchmark_selection_rate.py:133-141 a
+ * leading fraction of every layer; a sensitivity mask is the general case).  d_sel[n_sel] holds the indices of the
+ * encrypted parameters (u32, any order, each < the length of the learners' vectors); it is shared by all learners.
+ *   encrypt_selected_many : ciphertexts of the gathered vectors y_l[i] = d_x[l][d_sel[i]] — bit-identical to
+ *                           shelfi_encrypt_many_device on the gathered copies; the gather is fused into the encode load
+ *   decrypt_scatter       : d_out[d_sel[i]] = decoded[i]; entries of d_out not named by d_sel are left untouched
+ *   plain_weighted_sum    : d_out[i] = sum_l (double)weights[l] * d_x[l][i] for all i < n, evaluated in learner order
+ *                           with separate multiply and add (== numpy's sum of w_l * x_l); run it first, then scatter the
+ *                           decrypted part over it.  Needs no keys. */
+int shelfi_encrypt_selected_many_device(shelfi_ckks *h, const double *const *d_x, uint32_t k, const uint32_t *d_sel,
+                                        uint64_t n_sel, uint64_t ct_index0, uint64_t *const *d_ct, void *stream);
+int shelfi_decrypt_scatter_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor,
+                                  double *d_out, const uint32_t *d_sel, uint64_t n_sel, void *stream);
+int shelfi_plain_weighted_sum_device(shelfi_ckks *h, const double *const *d_x, const float *weights, uint32_t k,
+                                     uint64_t n, double *d_out, void *stream);
 /* dense <-> serialized image on the device (image buffers must be 8-byte aligned and hold
  * shelfi_blob_size bytes rounded up to 8, plus 8) */
 int shelfi_pack_device(shelfi_ckks *h, const uint64_t *d_dense, uint64_t n_ct, uint8_t *d_image, void *stream);

@@ -62,6 +62,7 @@ class Emu:
             "emu_ntt_forward": (None, [vp, u32, vp]),
             "emu_ntt_inverse": (None, [vp, u32, vp]),
             "emu_encode": (None, [vp, vp, u64, vp]),
+            "emu_set_selection": (None, [vp]),
             "emu_encode_sample": (None, [vp, vp, u64, u64, u64, vp, vp]),
             "emu_encrypt": (None, [vp, vp, vp, vp, vp, vp]),
             "emu_decrypt": (None, [vp, vp, vp, f64, f64, vp, u64, vp, vp, vp]),

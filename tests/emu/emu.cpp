@@ -149,10 +149,14 @@ void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
     if (d == 2) replay_tail<2>(lc, row);
 }
 
+// selective encryption: when set, chunk element i is x[sel[i]] on encode and out[sel[i]] on decode
+static const u32 *g_sel = nullptr;
+void emu_set_selection(const uint32_t *sel) { g_sel = sel; }
+
 // encode_kernel<SAMPLE> (ring dimension 8192) or encode_block_kernel<DF> (+ sample_add_kernel): one ciphertext
 static void replay_encode(const Emu *e, const double *x, uint64_t n_valid, std::vector<cplx> &z) {
     z.assign(e->ec.slots, cplx{0, 0});
-    FOR_THREADS(kFftThreads) encode_load(tid, kFftThreads, z.data(), e->ec, x, n_valid);
+    FOR_THREADS(kFftThreads) encode_load(tid, kFftThreads, z.data(), e->ec, x, n_valid, g_sel);
     if (e->ec.slots == kFftFast) {
         FOR_THREADS(kFftThreads) fft_inv_pass8<9>(tid, z.data(), e->ec.tw_inv);
         FOR_THREADS(kFftThreads) fft_inv_pass8<6>(tid, z.data(), e->ec.tw_inv);
@@ -169,7 +173,7 @@ template <int DF>
 static void replay_encode_block(const Emu *e, const double *x, uint64_t n_valid, u32 fb, int64_t *m) {
     const EncodeConst &ec = e->ec;
     std::vector<cplx> z(kFftFast, cplx{0, 0});
-    FOR_THREADS(kFftThreads) encode_load_block<DF>(tid, kFftThreads, z.data(), ec, x, n_valid, fb);
+    FOR_THREADS(kFftThreads) encode_load_block<DF>(tid, kFftThreads, z.data(), ec, x, n_valid, fb, g_sel);
     EncodeConst et = ec;
     if (ec.slots >= kFftFast) {
         et.slots = kFftFast; et.log_slots = 12;
@@ -275,10 +279,10 @@ static void replay_decode_fft(const Emu *e, const DecodeConst &dc, const double 
             for (u32 len = 2; len <= ec.slots; len <<= 1)
                 FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), ec.slots, len, ec.tw_fwd);
         }
-        if (DF == 0) { FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length); }
+        if (DF == 0) { FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length, g_sel); }
         else for (u32 i = 0; i < kFftFast; i++) zs[(size_t)fb * kFftFast + i] = z[zsw(i)];
     }
-    if (DF > 0) for (u32 i = 0; i < kFftFast; i++) decode_tail<DF>(i, zs, ec, dc, out, length);
+    if (DF > 0) for (u32 i = 0; i < kFftFast; i++) decode_tail<DF>(i, zs, ec, dc, out, length, g_sel);
 }
 
 }  // extern "C++"
@@ -317,7 +321,7 @@ void emu_decrypt(const Emu *e, const uint64_t *ct, const uint64_t *sk, double pr
             for (u32 len = 2; len <= e->ec.slots; len <<= 1)
                 FOR_THREADS(kFftThreads) fft_fwd_stage(tid, kFftThreads, z.data(), e->ec.slots, len, e->ec.tw_fwd);
         }
-        FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length);
+        FOR_THREADS(kFftThreads) decode_store(tid, kFftThreads, z.data(), dc, out, length, g_sel);
         return;
     }
     std::vector<double> vals(n);

@@ -431,3 +431,29 @@ def test_fp64_pipe_ntt_equals_integer_pipe(shelfi, gpu_ckks, monkeypatch):
     b1, b2 = hf.encrypt(x), hi.encrypt(x)
     hf.set_sampler_seed(None)
     assert hashlib.sha256(b1).digest() == hashlib.sha256(b2).digest()
+
+
+def test_pipelined_host_paths_equal_the_plain_ones(shelfi, gpu_ckks):
+    """Vectors of >= 128 / 256 ciphertexts into page-locked results take the group-pipelined encrypt and the split
+    weighted average (copy back while the next part computes / arrives): same bytes as the unsplit pageable path."""
+    h = gpu_ckks["pybind"]
+    d = str(FIXTURE_DIRS["pybind"]) + "/"
+    p = shelfi.CKKS("ckks", 4096, 52, d, device=0, pinned=True)
+    p.loadCryptoParams()
+    rng = np.random.default_rng(15)
+    for n in (260 * 4096 - 7, 515 * 4096 + 1, 130 * 4096):
+        xs = [rng.normal(0, 0.05, n) for _ in range(3)]
+        w = [0.5, 0.2, 0.3]
+        bb, bp = [], []
+        for i, x in enumerate(xs):
+            for hh, out in ((h, bb), (p, bp)):
+                hh.set_sampler_seed(80 + i)
+                out.append(hh.encrypt(x))
+                hh.set_sampler_seed(None)
+        for a, b in zip(bb, bp):
+            assert len(a) == len(b) and np.array_equal(np.frombuffer(a, np.uint8), b.array)
+        avg_b, avg_p = h.computeWeightedAverage(bb, w), p.computeWeightedAverage(bp, w)
+        assert np.array_equal(np.frombuffer(avg_b, np.uint8), avg_p.array)
+        got = p.decrypt(avg_p, n)
+        assert rel_err(got, sum(np.float64(np.float32(wi)) * x for wi, x in zip(w, xs))) < RTOL
+        del bb, bp, avg_b, avg_p

@@ -245,3 +245,33 @@ def test_fp64_encrypt_equals_integer_encrypt(emu, emu_ctx, oracles):
     emu.L.emu_encrypt(h, vp(m_e0), vp(ve), vp(b), vp(a), vp(ct2))
     emu.L.emu_set_fp64(h, 1)
     assert np.array_equal(ct1, ct2) and np.array_equal(ct1, o.encrypt_ct(x, 77, 3))
+
+
+@pytest.mark.parametrize("which", ["code", "n16k_l4"])
+def test_selection_gather_on_encode_and_scatter_on_decode(emu, emu_ctx, deep_emu_ctx, oracles, deep_oracles, which):
+    """Selective encryption: with an index list the encode load reads x[sel[i]] and the decode store writes
+    out[sel[i]]; everything in between is the dense path, so the result equals the oracle's on the gathered copy."""
+    o = oracles[which] if which in oracles else deep_oracles[which]
+    h = emu_ctx[which] if which in emu_ctx else deep_emu_ctx[which]
+    n, slots, L, bits = o.ring_dim, o.slots, o.num_limbs, o.scaleFactorBits
+    rng = np.random.default_rng(21)
+    x = rng.normal(0, 0.05, 3 * slots)
+    n_valid = slots - 5
+    sel = rng.permutation(x.size)[:n_valid].astype(np.uint32)
+    m = np.empty(n, np.int64)
+    emu.L.emu_set_selection(vp(sel))
+    try:
+        emu.L.emu_encode(h, vp(x), n_valid, vp(m))
+        assert np.array_equal(m, o.encode_coeffs(x[sel]))
+        ct = o.encrypt_ct(x[sel], 5, 0)
+        s, sf = o.secret_key(), o.scaling_factor
+        out = np.full(x.size, 7.0)
+        emu.L.emu_decrypt(h, vp(ct), vp(s), math.pow(sf, -1) * math.pow(2, bits), math.pow(2, -bits), vp(out), n_valid,
+                          None, None, None)
+    finally:
+        emu.L.emu_set_selection(None)
+    ref = o.decrypt_ct(ct, sf)[:n_valid] if L <= 2 else o.decrypt_ct_words(ct, sf)[0][:n_valid]
+    assert np.array_equal(out[sel], ref)
+    untouched = np.ones(x.size, bool)
+    untouched[sel] = False
+    assert np.all(out[untouched] == 7.0)

@@ -26,7 +26,9 @@ def run(name, sizes, K, h, tag=""):
     res = {}
     for mode in ("per_layer", "layers"):
         best = None
+        enc = avg = dec = None
         for _ in range(3):
+            del enc, avg, dec                      # hand the previous pass's buffers back before timing the next
             t0 = time.perf_counter()
             if mode == "per_layer":
                 enc = [[h.encrypt(a) for a in m] for m in models]
