@@ -208,6 +208,8 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     h = SHELFI_FHE.CKKS("ckks", BATCH, 52, CRYPTODIR, device=local)
     h.loadCryptoParams()
