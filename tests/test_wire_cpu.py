@@ -103,3 +103,60 @@ def test_parameter_rules(emu):
     assert emu.L.emu_first_prime(50, M) == 0x4000000024001
     for bits in (14, 20, 33, 40, 52):  # code/benchmark_crypto.py:123-124 sweep
         assert emu.L.emu_select_ring_dim(bits) == 8192
+
+
+def test_mutated_blobs_never_map_out_of_bounds(emu, oracles):
+    """Ciphertext blobs arrive from other parties: a corrupted or truncated one must be rejected or map to runs that
+    lie inside the buffer (the device copies whole runs from those offsets) — and must never crash the parser."""
+    o = oracles["pybind"]
+    blob = o.encrypt(np.random.default_rng(0).random(3 * 4096 + 5), seed=1)
+    rng = np.random.default_rng(1)
+    hdr, accepted = 3000, 0
+    for it in range(1200):
+        b = bytearray(blob)
+        mode = it % 4
+        if mode == 0:      # one header byte
+            b[int(rng.integers(0, hdr))] = int(rng.integers(0, 256))
+        elif mode == 1:    # a 64-bit field (counts, lengths, moduli)
+            pos = int(rng.integers(0, hdr - 8))
+            b[pos:pos + 8] = int(rng.integers(0, 2**63)).to_bytes(8, "little")
+        elif mode == 2:    # truncation
+            b = b[:int(rng.integers(0, len(b)))]
+        else:              # later ciphertexts' headers / payload
+            b[int(rng.integers(len(b) - 700000, len(b)))] ^= 0xFF
+        data = bytes(b)
+        n_ct, limbs, stride, depth, level = C.c_uint64(), C.c_uint32(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+        sf = C.c_double()
+        run0, run1 = np.zeros(16, np.uint64), np.zeros(16, np.uint64)
+        tag, err = C.create_string_buffer(33), C.create_string_buffer(256)
+        rc = emu.L.emu_wire_map(data, len(data), 0, C.byref(n_ct), C.byref(limbs), run0.ctypes.data, run1.ctypes.data,
+                                C.byref(stride), C.byref(depth), C.byref(level), C.byref(sf), tag, err, 256)
+        if rc != 0:
+            assert err.value
+            continue
+        accepted += 1
+        runs = 2 * limbs.value
+        last = int(run0[runs - 1]) if n_ct.value == 1 else int(run1[runs - 1]) + (n_ct.value - 2) * stride.value
+        assert last + 8192 * 8 <= len(data), (it, mode)
+    assert accepted > 100      # payload flips are legitimate blobs; header damage is what gets rejected
+
+
+def test_mutated_key_files_are_rejected_or_reemitted(emu):
+    rng = np.random.default_rng(2)
+    for kind, name in enumerate(["cryptocontext.txt", "key-public.txt", "key-private.txt"]):
+        data = (FIXTURE_DIRS["code"] / name).read_bytes()
+        for it in range(300):
+            b = bytearray(data)
+            if it % 3 == 0:
+                b = b[:int(rng.integers(0, len(b)))]
+            elif it % 3 == 1:
+                b[int(rng.integers(0, min(len(b), 2700)))] = int(rng.integers(0, 256))
+            else:
+                pos = int(rng.integers(0, min(len(b), 2700) - 8))
+                b[pos:pos + 8] = int(rng.integers(0, 2**63)).to_bytes(8, "little")
+            n, err = C.c_uint64(), C.create_string_buffer(256)
+            p = emu.L.emu_wire_reemit(kind, bytes(b), len(b), C.byref(n), err, 256)
+            if p:
+                emu.take(p, n.value)
+            else:
+                assert err.value
