@@ -158,6 +158,9 @@ struct shelfi_ckks {
     DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_image3, s_out, s_vals, s_zs, s_rows;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_stage_out = nullptr;
+    // rings above one tile: learner i+1 is encoded and sampled on this stream while learner i's transforms run
+    cudaStream_t enc_stream = nullptr;
+    cudaEvent_t ev_enc_fork = nullptr, ev_enc_ready[2] = {nullptr, nullptr}, ev_enc_free[2] = {nullptr, nullptr};
     cudaStream_t d2h_stream = nullptr;   // created on first use: results leave while the next inputs arrive (full duplex)
     cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
     cudaStream_t copy_stream = nullptr;
@@ -428,18 +431,44 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
     if (h->rc.log_blocks > 0) {
         // ring dimension above one tile: encode per FFT block, sampler pass, then one CTA per (ciphertext, limb, tile);
         // a single learner already gives thousands of CTAs, so learners go one after another
-        CU(h->s_m.reserve((size_t)n_ct * N * sizeof(int64_t)));
-        CU(h->s_ve.reserve((size_t)n_ct * N * sizeof(uint16_t)));
+        // The encode/sample kernels are latency-bound and light on the arithmetic pipes; on a second stream they run
+        // under the previous learner's transforms (two scratch slots, events both ways).
+        const bool overlap = k > 1;
+        const size_t m_words = (size_t)n_ct * N;
+        CU(h->s_m.reserve((overlap ? 2 : 1) * m_words * sizeof(int64_t)));
+        CU(h->s_ve.reserve((overlap ? 2 : 1) * m_words * sizeof(uint16_t)));
+        cudaStream_t es = s;
+        if (overlap) {
+            if (!h->enc_stream) {
+                CU(cudaStreamCreateWithFlags(&h->enc_stream, cudaStreamNonBlocking));
+                CU(cudaEventCreateWithFlags(&h->ev_enc_fork, cudaEventDisableTiming));
+                for (int i = 0; i < 2; i++) {
+                    CU(cudaEventCreateWithFlags(&h->ev_enc_ready[i], cudaEventDisableTiming));
+                    CU(cudaEventCreateWithFlags(&h->ev_enc_free[i], cudaEventDisableTiming));
+                }
+            }
+            es = h->enc_stream;
+            CU(cudaEventRecord(h->ev_enc_fork, s));          // inputs and scratch are ordered after the caller's work
+            CU(cudaStreamWaitEvent(es, h->ev_enc_fork, 0));
+        }
         for (uint32_t i = 0; i < k; i++) {
+            const int b = overlap ? (int)(i & 1) : 0;
+            i64 *m_slot = h->s_m.as<i64>() + (size_t)b * m_words;
+            uint16_t *ve_slot = h->s_ve.as<uint16_t>() + (size_t)b * m_words;
             sc.seed = h->seeded ? h->seed : fresh_seed();
-            timed(h, kKEncodeSample, s, [&] {
-                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), s,
-                                     d_sel);
+            if (overlap && i >= 2) CU(cudaStreamWaitEvent(es, h->ev_enc_free[b], 0));   // slot b was read by learner i-2
+            timed(h, kKEncodeSample, es, [&] {
+                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, m_slot, ve_slot, es, d_sel);
             });
+            if (overlap) {
+                CU(cudaEventRecord(h->ev_enc_ready[b], es));
+                CU(cudaStreamWaitEvent(s, h->ev_enc_ready[b], 0));
+            }
             timed(h, kKEncrypt, s, [&] {
-                launch_encrypt(h->rc, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(),
+                launch_encrypt(h->rc, m_slot, ve_slot, h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(),
                                reinterpret_cast<u64 *>(d_ct[i]), (u32)n_ct, s);
             });
+            if (overlap) CU(cudaEventRecord(h->ev_enc_free[b], s));
         }
         CU(cudaGetLastError());
         return 0;
@@ -870,6 +899,11 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         cudaStreamDestroy(h->stream);
         cudaStreamDestroy(h->copy_stream);
         if (h->d2h_stream) { cudaStreamDestroy(h->d2h_stream); cudaEventDestroy(h->ev_stage_out); }
+        if (h->enc_stream) {
+            cudaStreamDestroy(h->enc_stream);
+            cudaEventDestroy(h->ev_enc_fork);
+            for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_enc_ready[i]); cudaEventDestroy(h->ev_enc_free[i]); }
+        }
     }
     delete h;
 }
