@@ -6,9 +6,111 @@
 // three CTAs per SM; butterflies are Shoup/Harvey lazy 64-bit modmuls on the IMAD/ALU pipes.
 #include "kernels.h"
 
+#include <cooperative_groups.h>
+
 namespace shelfi {
+namespace cg = cooperative_groups;
 
 #define NTT_SMEM_BYTES (kN * 8)
+
+// ------------------------------------------------------------------------------------------
+// Rings above one tile, N = 2^(13+D): the 2^D CTAs that hold the tiles of one polynomial form a thread-block
+// cluster.  The D outermost Cooley-Tukey stages pair element i of every tile; CTA r does them for its share
+// i in [r, r+1) * 8192 / 2^D of the index range — reading the 2^D strided inputs, one butterfly per output —
+// and writes output b straight into tile b, i.e. into the shared memory of CTA b (distributed shared memory).
+// Same arithmetic, operand for operand, as HeadLoad / DHeadLoad (which recompute the head per tile: 3 butterflies per
+// output at D = 2 instead of 1, and which the CPU replay harness keeps using), so results are bit-identical.
+// Protocol per transform: cluster barrier (every tile is free), scatter, cluster barrier (every tile is full).
+// Measured (profiles/README.md): at D = 2 the cluster form wins (config 4 encrypt 208 -> 172 ms); at D = 1 the
+// recomputed head costs only +7 % multiplications and the two cluster barriers cost as much (standalone NTT
+// 0.216 vs 0.240 ms), so D = 1 keeps HeadLoad.
+// ------------------------------------------------------------------------------------------
+__host__ __device__ constexpr bool cluster_head_for(int d) { return d >= 2; }
+struct LoadTile {
+    const u64 *sm;
+    __device__ __forceinline__ u64 operator()(u32 i) const { return sm[swz(i)]; }
+};
+struct DLoadTile {
+    const u64 *sm;
+    __device__ __forceinline__ double operator()(u32 i) const { return reinterpret_cast<const double *>(sm)[swz(i)]; }
+};
+template <int D, class Inner>
+__device__ __forceinline__ void head_scatter(int tid, u64 *sm, const LimbConst &lc, Inner in) {
+    cg::cluster_group cl = cg::this_cluster();
+    const u32 rank = cl.block_rank();
+    u64 *peer[1 << D];
+#pragma unroll
+    for (int b = 0; b < (1 << D); b++) peer[b] = cl.map_shared_rank(sm, b);
+    const u64 nq = lc.nq, q2 = lc.q2;
+    const tw_t *__restrict__ tw = lc.tw;
+    constexpr u32 span = (u32)kN >> D;
+    const tw_t w1 = tw[1];
+    for (u32 i = rank * span + tid; i < (rank + 1) * span; i += kNttThreads) {
+        const u32 pos = swz(i);
+        if (D == 1) {
+            u64 x = in(i), y = in(i + kN);
+            u64 t = shoup_lazy_nq(y, w1.w, w1.ws, nq);
+            peer[0][pos] = x + t;
+            peer[1][pos] = x + q2 - t;
+        } else {
+            u64 x0 = in(i), x1 = in(i + kN), x2 = in(i + 2 * kN), x3 = in(i + 3 * kN);
+            u64 t0 = shoup_lazy_nq(x2, w1.w, w1.ws, nq), t1 = shoup_lazy_nq(x3, w1.w, w1.ws, nq);
+            u64 a0 = x0 + t0, a1 = x1 + t1, b0 = x0 + q2 - t0, b1 = x1 + q2 - t1;
+            const tw_t w2 = tw[2], w3 = tw[3];
+            u64 ta = shoup_lazy_nq(a1, w2.w, w2.ws, nq), tb = shoup_lazy_nq(b1, w3.w, w3.ws, nq);
+            peer[0][pos] = a0 + ta;
+            peer[1][pos] = a0 + q2 - ta;
+            peer[2 % (1 << D)][pos] = b0 + tb;
+            peer[3 % (1 << D)][pos] = b0 + q2 - tb;
+        }
+    }
+}
+template <int D, class Inner>
+__device__ __forceinline__ void dhead_scatter(int tid, u64 *sm, const LimbConst &lc, Inner in) {
+    cg::cluster_group cl = cg::this_cluster();
+    const u32 rank = cl.block_rank();
+    double *peer[1 << D];
+#pragma unroll
+    for (int b = 0; b < (1 << D); b++) peer[b] = reinterpret_cast<double *>(cl.map_shared_rank(sm, b));
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+    const double *__restrict__ tw = lc.dtw;
+    constexpr u32 span = (u32)kN >> D;
+    const double w1 = tw[1];
+    for (u32 i = rank * span + tid; i < (rank + 1) * span; i += kNttThreads) {
+        const u32 pos = swz(i);
+        if (D == 1) {
+            double x = in(i), t = d_mulmod(in(i + kN), w1, q, qinv);
+            peer[0][pos] = d_renorm(fadd(x, t), q, qinv, thr);
+            peer[1][pos] = d_renorm(fsub(x, t), q, qinv, thr);
+        } else {
+            double x0 = in(i), x1 = in(i + kN);
+            double t0 = d_mulmod(in(i + 2 * kN), w1, q, qinv), t1 = d_mulmod(in(i + 3 * kN), w1, q, qinv);
+            double a0 = d_renorm(fadd(x0, t0), q, qinv, thr), a1 = d_renorm(fadd(x1, t1), q, qinv, thr);
+            double b0 = d_renorm(fsub(x0, t0), q, qinv, thr), b1 = d_renorm(fsub(x1, t1), q, qinv, thr);
+            double ta = d_mulmod(a1, tw[2], q, qinv), tb = d_mulmod(b1, tw[3], q, qinv);
+            peer[0][pos] = d_renorm(fadd(a0, ta), q, qinv, thr);
+            peer[1][pos] = d_renorm(fsub(a0, ta), q, qinv, thr);
+            peer[2 % (1 << D)][pos] = d_renorm(fadd(b0, tb), q, qinv, thr);
+            peer[3 % (1 << D)][pos] = d_renorm(fsub(b0, tb), q, qinv, thr);
+        }
+    }
+}
+// cluster barrier, scatter, cluster barrier: afterwards this CTA's tile holds its head-stage outputs
+template <int D, class Inner>
+__device__ __forceinline__ void cluster_head(int tid, u64 *sm, const LimbConst &lc, Inner in) {
+    cg::cluster_group cl = cg::this_cluster();
+    cl.sync();
+    head_scatter<D>(tid, sm, lc, in);
+    cl.sync();
+}
+template <int D, class Inner>
+__device__ __forceinline__ void cluster_head_d(int tid, u64 *sm, const LimbConst &lc, Inner in) {
+    cg::cluster_group cl = cg::this_cluster();
+    cl.sync();
+    dhead_scatter<D>(tid, sm, lc, in);
+    cl.sync();
+}
 
 // ------------------------------------------------------------------------------------------
 // standalone forward / inverse NTT (parity taps, keygen, and the "NTT HBM GB/s" metric)
@@ -40,11 +142,21 @@ __global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_kernel(const __gri
     const u64 *src = in + ((size_t)row << (kLogN + D));
     u64 *dst = out + ((size_t)row << (kLogN + D)) + (size_t)blk * kN;
     if (lc.dtw) {   // q < 2^53: the same transform on the FP64 pipe
-        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadGlobal>{DLoadGlobal{src, lc.q}, &lc, blk},
-                           StoreFullReducePair{dst, &lc});
+        if (!cluster_head_for(D)) {
+            ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadGlobal>{DLoadGlobal{src, lc.q}, &lc, blk},
+                               StoreFullReducePair{dst, &lc});
+        } else {
+            cluster_head_d<D>(tid, sm, lc, DLoadGlobal{src, lc.q});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreFullReducePair{dst, &lc});
+        }
         return;
     }
-    fwd_phase_a(tid, sm, lc, hb, HeadLoad<D, LoadGlobal>{LoadGlobal{src}, &lc, blk});
+    if (!cluster_head_for(D)) {
+        fwd_phase_a(tid, sm, lc, hb, HeadLoad<D, LoadGlobal>{LoadGlobal{src}, &lc, blk});
+    } else {
+        cluster_head<D>(tid, sm, lc, LoadGlobal{src});
+        fwd_phase_a(tid, sm, lc, hb, LoadTile{sm});
+    }
     __syncthreads();
     fwd_phase_mid<7>(tid, sm, lc, hb);
     __syncthreads();
@@ -214,6 +326,24 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * n + tile_off;
     u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * n + tile_off;
     const tw_t *kb = pk_b + (size_t)l * n + tile_off, *ka = pk_a + (size_t)l * n + tile_off;
+    if (cluster_head_for(D)) {   // the 2^D tiles of this (ciphertext, limb) are one cluster: head stages through DSMEM
+        if (lc.dtw) {
+            cluster_head_d<D>(tid, sm, lc, DLoadTernary{ve_row});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreLazyPair{c1});
+            cluster_head_d<D>(tid, sm, lc, DLoadSigned{m_row, &lc});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreMulAdd{kb, c1, c0, &lc});
+            cluster_head_d<D>(tid, sm, lc, DLoadGaussHi{ve_row});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreMulAdd{ka, c1, c1, &lc});
+            return;
+        }
+        cluster_head<D>(tid, sm, lc, LoadTernary{ve_row, lc.q});
+        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreLazyPair{c1});
+        cluster_head<D>(tid, sm, lc, LoadSigned{m_row, &lc});
+        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreMulAdd{kb, c1, c0, &lc});
+        cluster_head<D>(tid, sm, lc, LoadGaussHi{ve_row, lc.q});
+        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreMulAdd{ka, c1, c1, &lc});
+        return;
+    }
     if (lc.dtw) {
         ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve_row}, &lc, blk}, StoreLazyPair{c1});
         __syncthreads();
@@ -600,9 +730,26 @@ cudaError_t kernels_init() {
     return cudaSuccess;
 }
 
+// launch with the 2^D tiles of a polynomial as one thread-block cluster (consecutive blockIdx.x)
+template <class... KArgs, class... Args>
+static void launch_tiles(void (*kernel)(KArgs...), unsigned polys, unsigned log_blocks, cudaStream_t s, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(polys << log_blocks);
+    cfg.blockDim = dim3(kNttThreads);
+    cfg.dynamicSmemBytes = NTT_SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 1u << log_blocks;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = cluster_head_for((int)log_blocks) ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s) {
     if (!rows) return;
-    DISPATCH_D(rc.log_blocks, ntt_forward_kernel<D><<<rows << D, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, in, out))
+    DISPATCH_D(rc.log_blocks, launch_tiles(ntt_forward_kernel<D>, rows, D, s, rc, in, out))
 }
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s) {
     if (!rows) return;
@@ -634,7 +781,7 @@ void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s) {
     if (!n_ct) return;
-    DISPATCH_D(rc.log_blocks, encrypt_kernel<D><<<(n_ct * rc.limbs) << D, kNttThreads, NTT_SMEM_BYTES, s>>>(
+    DISPATCH_D(rc.log_blocks, launch_tiles(encrypt_kernel<D>, n_ct * rc.limbs, D, s,
                                   rc, m_e0, ve, pk_b, pk_a, ct))
 }
 void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const EncryptBatch &eb,
