@@ -213,3 +213,15 @@ def test_fp64_pipe_equals_integer_pipe_on_deep_contexts(shelfi, gpu_deep, deep_o
         b1, b2 = hf.encrypt(x), hi.encrypt(x)
         hf.set_sampler_seed(None)
         assert hashlib.sha256(b1).digest() == hashlib.sha256(b2).digest(), name
+
+
+def test_random_soak_against_oracle():
+    """tools/soak_gpu.py: random (context, learners, length, amplitude, weights) cases through the public API,
+    blobs bit-exact and decoded doubles identical to the oracle; 12 contexts incl. sparse packing and 3 ring sizes."""
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "tools" / "soak_gpu.py"), "36", "3"], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0 and "soak ok: 36 cases" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
