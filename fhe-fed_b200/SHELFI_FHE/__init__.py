@@ -198,6 +198,9 @@ class PinnedBlob:
 
     tobytes = __bytes__
 
+    def __reduce__(self):          # pickle / copy.deepcopy (benchmark_selection.py:171) hand back plain bytes
+        return (bytes, (bytes(self),))
+
     def __buffer__(self, flags):   # PEP 688: memoryview(b), sock.sendall(b), f.write(b) read the pinned pages directly
         return memoryview(self.array)
 

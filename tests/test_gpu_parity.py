@@ -384,6 +384,9 @@ def test_pinned_blob_mode_equals_bytes_mode(shelfi, gpu_ckks):
     assert all(isinstance(b, shelfi.PinnedBlob) for b in blobs_p) and all(isinstance(b, bytes) for b in blobs_b)
     assert [bytes(b) for b in blobs_p] == blobs_b and blobs_p[0] == blobs_b[0] and len(blobs_p[0]) == len(blobs_b[0])
     assert bytes(memoryview(blobs_p[1])) == blobs_b[1]           # buffer protocol (what sock.sendall / f.write use)
+    import copy
+    import pickle
+    assert pickle.loads(pickle.dumps(blobs_p[2])) == blobs_b[2] and copy.deepcopy({"k": blobs_p[0]})["k"] == blobs_b[0]
     avg_b = h.computeWeightedAverage(blobs_b, w)
     avg_p = p.computeWeightedAverage(blobs_p, w)
     assert bytes(avg_p) == avg_b == bytes(p.computeWeightedAverage([blobs_p[0], blobs_b[1], memoryview(blobs_b[2])], w))
