@@ -387,6 +387,30 @@ def run_ours(args):
             py_api[mode] = {"value": P_MODEL / best, "unit": UNIT, "seconds_per_step": best}
         h.pinned = False
 
+    # ---------------- BASELINE configs[0]: the pythonApi example (3 learners, weights .5/.2/.3), both arms ----------------
+    config1 = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle
+        o = oracle.Oracle("ckks", BATCH, 52, CRYPTODIR)
+        assert o.loadCryptoParams() == 0
+        config1 = {}
+        for n1 in (10_000, 100_000):                       # BASELINE's size and the script's own (ckks_example.py:8)
+            data = [np.random.default_rng(1 + i).random(n1) for i in range(3)]
+            w1 = [0.5, 0.2, 0.3]
+            row = {}
+            for arm, eng in (("gpu_python_api", h), ("cpu_oracle", o)):
+                best = None
+                for _ in range(3):
+                    t0 = time.perf_counter()
+                    blobs = [eng.encrypt(x) for x in data]
+                    res = eng.decrypt(eng.computeWeightedAverage(blobs, w1), n1)
+                    dt = time.perf_counter() - t0
+                    best = dt if best is None else min(best, dt)
+                ref1 = sum(np.float64(np.float32(wi)) * x for wi, x in zip(w1, data))
+                assert float(np.abs(res - ref1).max() / np.abs(ref1).max()) < 1e-6
+                row[arm] = {"seconds": best, "params_per_s": n1 / best}
+            config1[str(n1)] = row
+
     # optional reassembly of the decoded model: ONE all-gather over NVLink, outside the timed step
     gather_ms = None
     if world > 1:
@@ -417,7 +441,8 @@ def run_ours(args):
                              "frac_of_peak": path_gbs / peak},
                 "ntt": {"GBps": ntt_gbs, "frac_of_peak": ntt_gbs / peak, "rows": rows, "ms": ntt_ms,
                         "bytes_per_row": 16 * N_RING},
-                "value_reference_convention": ref_conv, "kernels": prof, "gather_ms": gather_ms,
+                "value_reference_convention": ref_conv, "config1_pythonapi_example": config1, "kernels": prof,
+                "gather_ms": gather_ms,
                 "parity": {"max_rel_err_vs_plaintext": rel, "host_path": rel_h}}
         print(json.dumps(line), flush=True)
     if world > 1:
