@@ -27,6 +27,23 @@ template <int OP> __global__ void k(uint64_t *out, uint64_t seed) {
                 p = (p + q) ^ r; q = (q + r) ^ s; r = (r + s) ^ p; s = (s + p) ^ q;
             } else if (OP == 6) {  // u32 -> f64 and f64 -> s32 conversions (I2F.F64.U32 / F2I.S32.F64)
                 x = (double)p; y = (double)q; p = (uint32_t)(int)(y * 0.5) + r; q = (uint32_t)(int)(x * 0.5) + s;
+            } else if (OP == 7) {  // IMAD.WIDE x4 and DFMA x4 interleaved in every warp: do the two pipes overlap?
+                a = (uint64_t)p * q + a; x = fma(x, z, y); b = (uint64_t)q * r + b; y = fma(y, w, x);
+                c = (uint64_t)r * s + c; z = fma(z, w, 1e-30); d = (uint64_t)s * p + d; w = fma(w, z, 1e-30);
+                p += (uint32_t)a; q ^= (uint32_t)b;
+            } else if (OP == 8) {  // even warps IMAD.WIDE x4, odd warps DFMA x4 (two CTAs' phases side by side)
+                if ((threadIdx.x >> 5) & 1) {
+                    x = fma(x, z, y); y = fma(y, w, x); z = fma(z, w, 1e-30); w = fma(w, z, 1e-30);
+                } else {
+                    a = (uint64_t)p * q + a; b = (uint64_t)q * r + b; c = (uint64_t)r * s + c; d = (uint64_t)s * p + d;
+                    p += (uint32_t)a; q ^= (uint32_t)b;
+                }
+            } else if (OP == 9) {  // IMAD.WIDE x4 + IADD/LOP3 x4 interleaved
+                a = (uint64_t)p * q + a; r = (r + s) ^ p; b = (uint64_t)q * r + b; s = (s + p) ^ q;
+                c = (uint64_t)r * s + c; p = (p + q) ^ r; d = (uint64_t)s * p + d; q = (q + r) ^ s;
+            } else if (OP == 10) {  // DFMA x4 + IADD/LOP3 x4 interleaved
+                x = fma(x, z, y); p = (p + q) ^ r; y = fma(y, w, x); q = (q + r) ^ s;
+                z = fma(z, w, 1e-30); r = (r + s) ^ p; w = fma(w, z, 1e-30); s = (s + p) ^ q;
             }
         }
     }
@@ -55,5 +72,10 @@ int main() {
     run<4>("__umul64hi (+add)", 2);
     run<5>("IADD+LOP3 pair", 4);
     run<6>("I2F.F64.U32 + F2I.S32.F64", 4);
+    // mixes: ops counted per class (4 + 4 per inner step); compare the ms with the single-class runs above
+    run<7>("IMAD.WIDE x4 + DFMA x4, interleaved", 8);
+    run<8>("IMAD.WIDE | DFMA by warp parity", 4);
+    run<9>("IMAD.WIDE x4 + ALU x4, interleaved", 8);
+    run<10>("DFMA x4 + ALU x4, interleaved", 8);
     return 0;
 }
