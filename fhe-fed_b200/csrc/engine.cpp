@@ -155,7 +155,7 @@ struct shelfi_ckks {
     // device-resident parameters
     DeviceBuffer d_tw, d_itw, d_dtw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
     // scratch
-    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_image3, s_out, s_vals, s_zs, s_rows;
+    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_image3, s_out, s_vals, s_zs, s_rows, s_pt;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_stage_out = nullptr;
     // rings above one tile: learner i+1 is encoded and sampled on this stream while learner i's transforms run
@@ -888,7 +888,7 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         h->prof.release();
         free_params(h);
         for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_image3,
-                                &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows})
+                                &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows, &h->s_pt})
             b->release();
         for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_copy[i]); cudaEventDestroy(h->ev_done[i]); }
         for (int i = 0; i < 2; i++) {
@@ -1277,6 +1277,41 @@ int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, d
         return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
     return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n,
                          static_cast<cudaStream_t>(stream));
+}
+
+// ---- per-slot plaintext weights: out = sum_l ct_l (*) Encode(w_l)  ([PAL] EvalMult(ct, plaintext) + EvalAdd; the
+// TenSEAL/FLARE-style aggregation of code/benchmark_nvidia.py:439,461-465) ----
+int shelfi_weighted_sum_vector_device(shelfi_ckks *h, const uint64_t *const *d_cts, const double *const *d_w, uint32_t k,
+                                      uint64_t n, uint64_t *d_out, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!d_cts || !d_w || !d_out || k == 0 || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    for (uint32_t i = 0; i < k; i++)
+        if (!d_cts[i] || !d_w[i]) return fail(h, SHELFI_ERR_ARG, "null learner buffer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const uint64_t n_ct = (n + h->batch - 1) / h->batch, N = h->ctx.ring_dim;
+    if (n_ct > (0x7fffffffull / (2 * kMaxLimbs)) >> h->rc.log_blocks)
+        return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
+    CU(h->s_m.reserve(n_ct * N * sizeof(int64_t)));
+    CU(h->s_pt.reserve(n_ct * h->ctx.limbs * N * sizeof(uint64_t)));
+    const double *encoded = nullptr;   // learners that share one weight vector share its encoding
+    for (uint32_t i = 0; i < k; i++) {
+        if (d_w[i] != encoded) {
+            timed(h, kKEncodeSample, s, [&] {
+                launch_encode_only(h->rc, h->ec, d_w[i], n, (u32)n_ct, h->s_m.as<i64>(), s);
+                launch_plain_ntt(h->rc, h->s_m.as<i64>(), h->s_pt.as<u64>(), (u32)n_ct, s);
+            });
+            encoded = d_w[i];
+        }
+        timed(h, kKWeightedSum, s, [&] {
+            launch_ct_pt_mac(h->rc, reinterpret_cast<const u64 *>(d_cts[i]), h->s_pt.as<u64>(),
+                             reinterpret_cast<u64 *>(d_out), n_ct, i > 0, s);
+        });
+    }
+    CU(cudaGetLastError());
+    return 0;
 }
 
 // ---- selective encryption (benchmark_selection.py:152-193, benchmark_selection_rate.py:133-141): only the chosen

@@ -167,6 +167,49 @@ __global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_kernel(const __gri
     fwd_phase_e(tid, sm, lc, hb, StoreFullReducePair{dst, &lc});
 }
 
+// Plaintext polynomial of an encoded weight vector -> evaluation form in every limb (EvalMult(ct, plaintext)): the
+// signed coefficients m[ct][N] are shared by the limbs, one CTA per (ciphertext, limb, tile).
+template <int D>
+__global__ void __launch_bounds__(kNttThreads, 3) plain_ntt_kernel(const __grid_constant__ RingConst rc, const i64 *m,
+                                                                   u64 *pt_hat) {
+    extern __shared__ __align__(16) u64 sm[];
+    const int tid = threadIdx.x;
+    const u32 L = rc.limbs;
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u32 hb = D ? head_bits(D, blk) : 1u;
+    const u32 poly = blockIdx.x >> D;          // ct * L + l
+    const u32 l = poly % L;
+    const u64 ct = poly / L;
+    const u64 n = (u64)kN << D;
+    const LimbConst lc = rc.limb[l];
+    const i64 *m_row = m + ct * n;
+    u64 *dst = pt_hat + (size_t)poly * n + (size_t)blk * kN;
+    if (lc.dtw) {
+        if (!cluster_head_for(D)) {
+            ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadSigned>{DLoadSigned{m_row, &lc}, &lc, blk},
+                               StoreFullReducePair{dst, &lc});
+        } else {
+            cluster_head_d<D>(tid, sm, lc, DLoadSigned{m_row, &lc});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreFullReducePair{dst, &lc});
+        }
+        return;
+    }
+    if (!cluster_head_for(D)) {
+        fwd_phase_a(tid, sm, lc, hb, HeadLoad<D, LoadSigned>{LoadSigned{m_row, &lc}, &lc, blk});
+    } else {
+        cluster_head<D>(tid, sm, lc, LoadSigned{m_row, &lc});
+        fwd_phase_a(tid, sm, lc, hb, LoadTile{sm});
+    }
+    __syncthreads();
+    fwd_phase_mid<7>(tid, sm, lc, hb);
+    __syncthreads();
+    fwd_phase_mid<4>(tid, sm, lc, hb);
+    __syncthreads();
+    fwd_phase_mid<1>(tid, sm, lc, hb);
+    __syncthreads();
+    fwd_phase_e(tid, sm, lc, hb, StoreFullReducePair{dst, &lc});
+}
+
 // inverse: the 13 inner stages per tile in place; for D > 0 the results stay lazy (< 2q) and intt_tail_kernel
 // applies the D outermost stages and N^-1 as a streaming pass
 template <int D, class Load>
@@ -605,6 +648,30 @@ __global__ void __launch_bounds__(kWavgThreads) weighted_sum_kernel(const __grid
     }
 }
 
+// out (+)= ct (*) pt_hat: EvalMult(ct, plaintext) + EvalAdd.  pt_hat[ct][L][N] multiplies both polynomials of the
+// ciphertext; the 128-bit product (plus the running value) is reduced once, so `out` always holds canonical residues.
+constexpr int kMacThreads = 256;
+__global__ void __launch_bounds__(kMacThreads) ct_pt_mac_kernel(const __grid_constant__ RingConst rc, const u64 *ct,
+                                                                const u64 *pt_hat, u64 *out, u32 accumulate) {
+    const u64 e = ((u64)blockIdx.x * kMacThreads + threadIdx.x) * 2;        // two adjacent coefficients per thread
+    const u32 L = rc.limbs;
+    const u64 row = e >> rc.logn;                                           // (ct * 2 + poly) * L + l
+    const u32 l = (u32)(row % L);
+    const u64 ctp = row / L;                                                // ct * 2 + poly
+    const u64 pt_off = (((ctp >> 1) * L + l) << rc.logn) + (e & ((u64)rc.n - 1));
+    const LimbConst &lc = rc.limb[l];
+    const ulonglong2 a = *reinterpret_cast<const ulonglong2 *>(ct + e);
+    const ulonglong2 b = *reinterpret_cast<const ulonglong2 *>(pt_hat + pt_off);
+    acc128 s0{0, 0}, s1{0, 0};
+    if (accumulate) {
+        const ulonglong2 o = *reinterpret_cast<const ulonglong2 *>(out + e);
+        s0.lo = o.x; s1.lo = o.y;
+    }
+    mac128(s0, a.x, b.x);
+    mac128(s1, a.y, b.y);
+    *reinterpret_cast<ulonglong2 *>(out + e) = make_ulonglong2(reduce128(s0, lc), reduce128(s1, lc));
+}
+
 // plaintext weighted sum (selective encryption: the parameters that are not encrypted); streaming, 8 B per lane
 constexpr int kPlainThreads = 256;
 constexpr int kPlainPerThread = 4;
@@ -718,6 +785,7 @@ cudaError_t kernels_init() {
     OPT_IN_D(ntt_forward_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(ntt_inverse_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(encrypt_kernel, NTT_SMEM_BYTES)
+    OPT_IN_D(plain_ntt_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(decrypt_intt_kernel, NTT_SMEM_BYTES)
     OPT_IN(encrypt_fused_kernel, NTT_SMEM_BYTES)
     OPT_IN(encode_kernel<true>, kFftFast * sizeof(cplx))
@@ -828,6 +896,16 @@ void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 
     if (elems) weighted_sum_kernel<<<(unsigned)(elems / kWavgElemsPerCta), kWavgThreads, 0, s>>>(rc, wa, out);
 }
 static dim3 run_grid(const BlobRuns &br, u64 n_ct) { return dim3((unsigned)(n_ct * br.runs), br.n / 2048); }
+void launch_plain_ntt(const RingConst &rc, const i64 *m, u64 *pt_hat, u32 n_ct, cudaStream_t s) {
+    if (!n_ct) return;
+    DISPATCH_D(rc.log_blocks, launch_tiles(plain_ntt_kernel<D>, n_ct * rc.limbs, D, s, rc, m, pt_hat))
+}
+void launch_ct_pt_mac(const RingConst &rc, const u64 *ct, const u64 *pt_hat, u64 *out, u64 n_ct, bool accumulate,
+                      cudaStream_t s) {
+    const u64 elems = n_ct * 2 * rc.limbs * (u64)rc.n;
+    if (elems) ct_pt_mac_kernel<<<(unsigned)(elems / (2 * kMacThreads)), kMacThreads, 0, s>>>(rc, ct, pt_hat, out,
+                                                                                              accumulate ? 1u : 0u);
+}
 void launch_plain_weighted_sum(const PlainWavgArgs &pa, u64 n, double *out, cudaStream_t s) {
     const u64 per = (u64)kPlainThreads * kPlainPerThread;
     if (n) plain_weighted_sum_kernel<<<(unsigned)((n + per - 1) / per), kPlainThreads, 0, s>>>(pa, n, out);

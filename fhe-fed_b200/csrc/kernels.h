@@ -45,6 +45,11 @@ void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coef
 // out = sum_k c_k * in_k mod q over dense payloads of n_ct ciphertexts
 void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 n_ct, cudaStream_t s);
 
+// EvalMult(ct, plaintext vector): encoded weights m[n_ct][N] -> evaluation form pt_hat[n_ct][L][N], then
+// out (+)= ct (*) pt_hat on both polynomials
+void launch_plain_ntt(const RingConst &rc, const i64 *m, u64 *pt_hat, u32 n_ct, cudaStream_t s);
+void launch_ct_pt_mac(const RingConst &rc, const u64 *ct, const u64 *pt_hat, u64 *out, u64 n_ct, bool accumulate,
+                      cudaStream_t s);
 // out[i] (+)= sum_k w_k * x_k[i] in plaintext (the unencrypted part of a selectively encrypted model)
 void launch_plain_weighted_sum(const PlainWavgArgs &pa, u64 n, double *out, cudaStream_t s);
 

@@ -157,6 +157,13 @@ int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const 
                                           uint64_t n_ct, uint64_t *d_acc, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
                           uint64_t n, void *stream);
+/* Per-slot plaintext weights: d_out = sum_l d_cts[l] (*) Encode(d_w[l]) — PALISADE EvalMult(ct, plaintext) + EvalAdd,
+ * the ct x plaintext-vector aggregation of the TenSEAL/FLARE-style workload (code/benchmark_nvidia.py:439,461-465);
+ * the reference's own computeWeightedAverage (ckks.cpp:287-288) only takes one scalar per learner.  d_w[l] holds n
+ * doubles (one per model parameter, chunked like encrypt); learners may share one vector (equal pointers are encoded
+ * once).  Result: depth 2, scale Delta^2, no rescale — decrypt with scaling_factor^2 like the scalar form. */
+int shelfi_weighted_sum_vector_device(shelfi_ckks *h, const uint64_t *const *d_cts, const double *const *d_w, uint32_t k,
+                                      uint64_t n, uint64_t *d_out, void *stream);
 /* ---- selective encryption: only a chosen subset of the parameters goes through CKKS, the rest is averaged in
  * plaintext (the callers code/benchmark_selection.py:152-193 pick whole layers, benchmark_selection_rate.py:133-141 a
  * leading fraction of every layer; a sensitivity mask is the general case).  d_sel[n_sel] holds the indices of the

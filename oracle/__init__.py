@@ -60,6 +60,7 @@ def lib():
         "orc_num_large_digits": (C.c_uint32, [C.c_uint32]),
         "orc_modulus_chain": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
         "orc_decrypt_ct_words": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]),
+        "orc_ct_mul_plain_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
         "orc_last_error": (C.c_char_p, [C.c_void_p]),
         "orc_ring_dim": (C.c_uint32, [C.c_void_p]),
         "orc_num_limbs": (C.c_uint32, [C.c_void_p]),
@@ -265,6 +266,18 @@ class Oracle:
         if rc:
             raise RuntimeError(f"decrypt_ct_words failed ({rc})")
         return out, words
+
+    def ct_mul_plain_accumulate(self, ct, w, acc=None):
+        """acc (+)= ct (*) Encode(w): EvalMult(ct, plaintext vector) + EvalAdd on one ciphertext [2][L][N]."""
+        ct = _u64(ct)
+        w = np.ascontiguousarray(w, dtype=np.float64)
+        first = acc is None
+        if first:
+            acc = np.empty((2, self.num_limbs, self.ring_dim), np.uint64)
+        rc = lib().orc_ct_mul_plain_accumulate(self._h, ct.ctypes.data, w.ctypes.data, w.size, int(first), acc.ctypes.data)
+        if rc:
+            raise RuntimeError(f"ct_mul_plain_accumulate failed ({rc})")
+        return acc
 
     def weight_constant(self, w: float) -> int:
         return lib().orc_weight_constant(self._h, w)

@@ -629,6 +629,34 @@ int orc_decrypt_ct_words(const orc_ctx *c, const uint64_t *ct, double sf, double
     return decrypt_ct_impl(c, ct, sf, out, NULL, NULL, words);
 }
 
+/* [PAL] EvalMult(ct, pt) with pt = MakeCKKSPackedPlaintext(w) (fresh: depth 1, level 0, scale Delta), then EvalAdd:
+ * acc (+)= ct (*) NTT(Encode(w)) on both polynomials of every limb.  This is the per-slot plaintext weighting of the
+ * TenSEAL/FLARE-style aggregation (code/benchmark_nvidia.py:439,461-465 multiply each ciphertext by a plaintext
+ * vector); the result has depth 2 and scale Delta^2 like EvalMult(ct, double), and is not rescaled (EXACTRESCALE). */
+int orc_ct_mul_plain_accumulate(const orc_ctx *c, const uint64_t *ct, const double *w, uint32_t n, int first, uint64_t *acc) {
+    if (!c->have_cc) return -1;
+    uint32_t N = c->wp.N;
+    int L = c->wp.L;
+    int64_t *m = malloc((size_t)N * 8);
+    uint64_t *pt = malloc((size_t)N * 8);
+    int rc = orc_encode_coeffs(c, w, n, m);
+    for (int l = 0; rc == 0 && l < L; l++) {
+        uint64_t q = c->wp.q[l];
+        for (uint32_t j = 0; j < N; j++) pt[j] = signed_mod(m[j], q);
+        orc_ntt_forward(c, l, pt);
+        for (int p = 0; p < 2; p++) {
+            const uint64_t *src = ct + ((size_t)p * L + l) * N;
+            uint64_t *dst = acc + ((size_t)p * L + l) * N;
+            for (uint32_t j = 0; j < N; j++) {
+                uint64_t v = mulmod(src[j], pt[j], q);
+                dst[j] = first ? v : addmod(dst[j], v, q);
+            }
+        }
+    }
+    free(m); free(pt);
+    return rc;
+}
+
 int64_t orc_weight_constant(const orc_ctx *c, float w) {
     double sc = (double)w; /* ckks.cpp:287 narrows the Python float to float32, [PAL] widens it back */
     return (int64_t)(sc * orc_scaling_factor(c) + 0.5);

@@ -96,6 +96,8 @@ int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out,
                    uint64_t *coeff_lo);
 /* any limb count: words = N x 8 little-endian u64, two's complement of the centred CRT integer */
 int orc_decrypt_ct_words(const orc_ctx *c, const uint64_t *ct, double sf, double *out, uint64_t *words);
+/* acc (+)= ct (*) NTT(Encode(w)): EvalMult(ct, plaintext vector) + EvalAdd, one ciphertext [2][L][N] */
+int orc_ct_mul_plain_accumulate(const orc_ctx *c, const uint64_t *ct, const double *w, uint32_t n, int first, uint64_t *acc);
 /* EvalMult(ct,(float)w) constant: (int64)((double)w * sf0 + 0.5)   (ckks.cpp:287-288) */
 int64_t orc_weight_constant(const orc_ctx *c, float w);
 
