@@ -1296,19 +1296,36 @@ int shelfi_weighted_sum_vector_device(shelfi_ckks *h, const uint64_t *const *d_c
         return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
     CU(h->s_m.reserve(n_ct * N * sizeof(int64_t)));
     CU(h->s_pt.reserve(n_ct * h->ctx.limbs * N * sizeof(uint64_t)));
-    const double *encoded = nullptr;   // learners that share one weight vector share its encoding
-    for (uint32_t i = 0; i < k; i++) {
-        if (d_w[i] != encoded) {
-            timed(h, kKEncodeSample, s, [&] {
-                launch_encode_only(h->rc, h->ec, d_w[i], n, (u32)n_ct, h->s_m.as<i64>(), s);
-                launch_plain_ntt(h->rc, h->s_m.as<i64>(), h->s_pt.as<u64>(), (u32)n_ct, s);
-            });
-            encoded = d_w[i];
+    // Consecutive learners that share one weight vector (the TenSEAL script's constant vector) are summed first:
+    // sum_l (ct_l (*) pt) == (sum_l ct_l) (*) pt as canonical residues, one encoding and one multiply per run.
+    const uint32_t L = h->ctx.limbs;
+    const uint64_t ct_words = 2ull * L * N;
+    for (uint32_t i0 = 0; i0 < k;) {
+        uint32_t i1 = i0 + 1;
+        while (i1 < k && d_w[i1] == d_w[i0]) i1++;
+        timed(h, kKEncodeSample, s, [&] {
+            launch_encode_only(h->rc, h->ec, d_w[i0], n, (u32)n_ct, h->s_m.as<i64>(), s);
+            launch_plain_ntt(h->rc, h->s_m.as<i64>(), h->s_pt.as<u64>(), (u32)n_ct, s);
+        });
+        const u64 *src = reinterpret_cast<const u64 *>(d_cts[i0]);
+        if (i1 - i0 > 1) {
+            CU(h->s_dense.reserve(n_ct * ct_words * 8));
+            for (uint32_t base = i0; base < i1; base += kMaxLearnersPerLaunch) {
+                WavgArgs wa{};
+                wa.k = std::min<uint32_t>(kMaxLearnersPerLaunch, i1 - base);
+                wa.accumulate = base > i0 ? 1u : 0u;
+                for (uint32_t j = 0; j < wa.k; j++) {
+                    wa.in[j] = reinterpret_cast<const u64 *>(d_cts[base + j]);
+                    for (uint32_t l = 0; l < L; l++) wa.c[j][l] = 1;
+                }
+                timed(h, kKWeightedSum, s, [&] { launch_weighted_sum(h->rc, wa, h->s_dense.as<u64>(), n_ct, s); });
+            }
+            src = h->s_dense.as<u64>();
         }
         timed(h, kKWeightedSum, s, [&] {
-            launch_ct_pt_mac(h->rc, reinterpret_cast<const u64 *>(d_cts[i]), h->s_pt.as<u64>(),
-                             reinterpret_cast<u64 *>(d_out), n_ct, i > 0, s);
+            launch_ct_pt_mac(h->rc, src, h->s_pt.as<u64>(), reinterpret_cast<u64 *>(d_out), n_ct, i0 > 0, s);
         });
+        i0 = i1;
     }
     CU(cudaGetLastError());
     return 0;

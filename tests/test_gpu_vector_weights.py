@@ -81,6 +81,11 @@ def test_shared_weight_vector_and_scalar_equivalence(shelfi, ctxs):
     check(h, lib.shelfi_weighted_sum_vector_device(h.handle, _ptrs(dct), _ptrs([dw] * k), k, n, ptr(out_v), stream()))
     wf = (C.c_float * k)(*[0.3] * k)
     check(h, lib.shelfi_weighted_sum_device(h.handle, _ptrs(dct), wf, k, n_ct, ptr(out_s), stream()))
+    got, cts = host_u64(out_v), [host_u64(t) for t in dct]
+    acc = None
+    for i in range(k):                                          # learner by learner, as PALISADE would
+        acc = o.ct_mul_plain_accumulate(cts[i][1], w[4096:8192], acc)
+    assert np.array_equal(got[1], acc)
     sf2 = h.scaling_factor ** 2
     dv, ds = torch.empty(n, dtype=torch.float64, device="cuda"), torch.empty(n, dtype=torch.float64, device="cuda")
     check(h, lib.shelfi_decrypt_device(h.handle, ptr(out_v), n_ct, sf2, ptr(dv), n, stream()))
