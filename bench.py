@@ -157,10 +157,17 @@ def cpu_arm_bounded(target_seconds: float):
                       f"{total:.1f} s of CPU work; last pass: " + runs[-1]["sample"].split("; ", 1)[1]}
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm is meant to use every host thread."""
+    if os.environ.get("OMP_NUM_THREADS", "") in ("", "1"):
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count())
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    use_all_host_threads()
     sample_cts = -(-P_MODEL // BATCH)   # the whole workload: ~1 s per step on 16 host threads
     cpu_arm(4)  # warm caches / OpenMP pool
     for _ in range(min(args.warmup, 1)):
@@ -181,7 +188,7 @@ def run_reference(args):
             "gpu_launches": 0,
             "note": "PALISADE is not vendored in the reference and cannot be built offline; this arm is the C oracle "
                     "(oracle/shelfi_oracle.c), a port of ckks.cpp:61-104,170-213,264-320 with OpenMP over ciphertexts"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config():
@@ -208,8 +215,6 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     h = SHELFI_FHE.CKKS("ckks", BATCH, 52, CRYPTODIR, device=local)
     h.loadCryptoParams()
@@ -444,12 +449,31 @@ def run_ours(args):
                 "value_reference_convention": ref_conv, "config1_pythonapi_example": config1, "kernels": prof,
                 "gather_ms": gather_ms,
                 "parity": {"max_rel_err_vs_plaintext": rel, "host_path": rel_h}}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The one JSON line, written to the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
+    use_all_host_threads()      # before anything loads libgomp
+    # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner under torchrun) is
+    # sent to stderr for the duration of the run
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
