@@ -470,10 +470,24 @@ HD void d_bfly(double &x, double &y, double w, double q, double qinv, u32 thr) {
     y = d_renorm(fsub(x, t), q, qinv, thr);
     x = d_renorm(fadd(x, t), q, qinv, thr);
 }
+// Both outputs left un-renormalised, |.| <= q + 2^49: allowed for a value that the NEXT stage uses only as the additive
+// operand x of a full d_bfly (x +- t then stays below 1.5 q + 2^50 < 2^53 for q <= 1.125 * 2^52, still an exact
+// integer, and the rint-style d_renorm folds any such value back).  Saves 6 of the 14 FP64 operations.
+HD void d_bfly_lazy(double &x, double &y, double w, double q, double qinv) {
+    double t = d_mulmod(y, w, q, qinv);
+    y = fsub(x, t);
+    x = fadd(x, t);
+}
 HD void d_radix8(double (&a)[8], const double *__restrict__ tw, u32 t0, double q, double qinv, u32 thr) {
     double w = tw[t0];
+#if SHELFI_DRENORM == 1
+    // stage 2 pairs (0,2) (1,3) (4,6) (5,7): a[0], a[1], a[4], a[5] are additive operands there
+    d_bfly_lazy(a[0], a[4], w, q, qinv); d_bfly_lazy(a[1], a[5], w, q, qinv);
+    d_bfly(a[2], a[6], w, q, qinv, thr); d_bfly(a[3], a[7], w, q, qinv, thr);
+#else
 #pragma unroll
     for (int k = 0; k < 4; k++) d_bfly(a[k], a[k + 4], w, q, qinv, thr);
+#endif
     double w0 = tw[2 * t0], w1 = tw[2 * t0 + 1];
     d_bfly(a[0], a[2], w0, q, qinv, thr); d_bfly(a[1], a[3], w0, q, qinv, thr);
     d_bfly(a[4], a[6], w1, q, qinv, thr); d_bfly(a[5], a[7], w1, q, qinv, thr);

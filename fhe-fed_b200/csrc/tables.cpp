@@ -88,10 +88,11 @@ std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *
         B += kBflyGrowth * stages[pass];
     }
     if (H < 16) return "modulus leaves no headroom for the inverse transform";
-    // FP64-pipe forward transform: exact for q <= 1.25 * 2^52 (ckks_core.cuh)
+    // FP64-pipe forward transform: exact for q <= 1.125 * 2^52 (ckks_core.cuh: the lazy first stage of a radix-8 pass
+    // needs 1.5 q + 2^50 < 2^53)
     if (dtw) {
         dtw->clear();
-        if (q <= (((uint64_t)5) << 50) && q >= 1024) {
+        if (q <= (((uint64_t)9) << 49) && q >= 1024) {
             dtw->assign(n, 0.0);
             for (uint32_t i = 0; i < n; i++) {
                 uint64_t w = (*tw)[i].w;
