@@ -386,16 +386,17 @@ HD double fsub(double a, double b) {
 }
 // ------------------------------------------------------------------------------------------
 // The same forward transform on the FP64 pipe, for limbs with q < 2^53 (PALISADE's scaling primes at <= 52 bits).
-// B200 issues DFMA at full rate (64 lanes/clk/SM, measured: tools/ubench/pipes.cu) on a pipe the integer path
-// leaves idle, and a 53 x 53 -> 106-bit product is two instructions there (DMUL + DFMA) against four IMAD.WIDE.
-// Co-resident CTAs working on the 60-bit limb (integer pipe) and on a 52-bit limb (FP64 pipe) overlap.
+// B200 issues DFMA at 50 /clk/SM against 29 for IMAD.WIDE (measured: tools/ubench/pipes.cu), and a 53 x 53 ->
+// 106-bit product is two instructions there (DMUL + DFMA) against four IMAD.WIDE: 56 ns per row against 70.
 //
 // Values are integers held exactly in doubles, centred: |v| <= 0.51 q between stages.
 //   mulmod(y, w), |y| < q, |w| <= q/2:  h = RN(y w), l = y w - h (exact, FMA), c = rint(h / q) by the 1.5*2^52 magic
 //   constant (|h / q| < 2^51), d = h - c q (exact: an integer below 2^53), r = d + l.  |y w / q - c| <= 1/2 + |c| 2^-52
 //   so |r| <= 0.76 q for |y| <= 0.5 q.
 //   butterfly: x +- r is at most 1.26 q < 2^53 (exact); renormalise with v - q rint(v / q) back to |v| <= q/2.
-//   (q <= 1.25 * 2^52 keeps every bound above with room to spare: tables.cpp admits only such limbs.)
+//   First-stage outputs of a radix-8 pass that the second stage only adds to skip that renormalisation
+//   (d_bfly_lazy): they are at most q + 2^49, the sums that follow at most 1.5 q + 2^50.
+//   (q <= 1.125 * 2^52 keeps every bound above below 2^53: tables.cpp admits only such limbs.)
 // Every rounding that happens is of a value the derivation does not need exactly (h, c), so the residues — and after
 // the final conversion to [0, q) the stored words — equal the integer path's bit for bit.
 // ------------------------------------------------------------------------------------------

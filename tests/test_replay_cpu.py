@@ -186,7 +186,7 @@ def test_deep_parameter_rules_match_oracle(emu, oracle_mod):
     assert (emu.L.emu_select_ring_dim_ex(52, 3), emu.L.emu_select_ring_dim_ex(52, 7)) == (16384, 32768)
 
 
-# ---- FP64-pipe forward transform (limbs with q <= 1.25 * 2^52): same bits as the integer path and the oracle ----
+# ---- FP64-pipe forward transform (limbs with q <= 1.125 * 2^52): same bits as the integer path and the oracle ----
 def test_fp64_path_selected_for_the_scaling_limb(emu, emu_ctx, deep_emu_ctx):
     h = emu_ctx["pybind"]
     assert (emu.L.emu_limb_fp64(h, 0), emu.L.emu_limb_fp64(h, 1)) == (0, 1)      # 60-bit q0: integer pipe
