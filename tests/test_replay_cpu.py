@@ -201,6 +201,9 @@ def test_fp64_ntt_equals_integer_ntt_and_oracle(emu, oracle_mod, bits):
     (code/benchmark_crypto.py:123-124) and adversarial inputs: all q-1, values around q/2, deltas, random."""
     M = 2 * N
     qs = [oracle_mod.first_prime(bits, M), oracle_mod.previous_prime(oracle_mod.first_prime(bits, M) + M * 64, M)]
+    if bits == 52:   # the largest modulus the FP64 path admits (1.125 * 2^52): the lazy-stage bounds are tightest here
+        qs.append(oracle_mod.previous_prime((9 << 49) + 1, M))
+        assert (9 << 49) - M * 4096 < qs[-1] <= 9 << 49
     rng = np.random.default_rng(bits)
     for q in qs:
         psi = oracle_mod.min_root_of_unity(M, q)
