@@ -76,6 +76,16 @@ def lib() -> C.CDLL:
                                                        C.POINTER(vp), u64p]),
         "shelfi_compute_weighted_average_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, vp, u64,
                                                             u64p]),
+        "shelfi_compute_weighted_average_rescaled": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32,
+                                                                C.POINTER(vp), u64p]),
+        "shelfi_compute_weighted_average_rescaled_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32,
+                                                                     vp, u64, u64p]),
+        "shelfi_rescale": (C.c_int, [vp, vp, u64, C.POINTER(vp), u64p]),
+        "shelfi_rescale_into": (C.c_int, [vp, vp, u64, vp, u64, u64p]),
+        "shelfi_blob_size_level": (u64, [vp, u64, u32]),
+        "shelfi_rescale_device": (C.c_int, [vp, vp, u64, u32, vp, vp]),
+        "shelfi_decrypt_level_device": (C.c_int, [vp, vp, u64, u32, f64, vp, u64, vp]),
+        "shelfi_decrypt_words_level_device": (C.c_int, [vp, vp, u64, u32, vp, vp]),
         "shelfi_decrypt": (C.c_int, [vp, vp, u64, u64, vp]),
         "shelfi_encrypt_layers": (C.c_int, [vp, C.POINTER(vp), u64p, u32, C.POINTER(vp), u64p, u64p, u64p]),
         "shelfi_compute_weighted_average_layers": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, u32,
@@ -252,8 +262,12 @@ class CKKS(Scheme):
     """CKKS helper with the reference's constructor and methods (binding.cpp:18-31)."""
 
     def __init__(self, scheme: str = "ckks", batchSize: int = 4096, scaleFactorBits: int = 52,
-                 cryptodir: str = "../resources/cryptoparams/", device: int | None = None, pinned: bool = False):
+                 cryptodir: str = "../resources/cryptoparams/", device: int | None = None, pinned: bool = False,
+                 rescale: bool = False):
         super().__init__(scheme)
+        # rescale-before-transport (extension, off by default like the reference): computeWeightedAverage returns the
+        # average one tower shorter (PALISADE ModReduce), i.e. half the bytes at the shipped two-tower context
+        self.rescale = bool(rescale) or os.environ.get("SHELFI_RESCALE", "0") == "1"
         self.pinned = bool(pinned) or os.environ.get("SHELFI_PINNED", "0") == "1"   # return PinnedBlob objects instead of bytes (extension; see PinnedBlob)
         self.batchSize, self.scaleFactorBits, self.cryptodir = int(batchSize), int(scaleFactorBits), str(cryptodir)
         if device is None:
@@ -325,8 +339,12 @@ class CKKS(Scheme):
         assert n.value == cap
         return dst
 
-    def computeWeightedAverage(self, learner_data, scaling_factors) -> bytes:
-        """ckks.cpp:264-320: sum_i float32(w_i) * ct_i over learners; size mismatch prints and returns b""."""
+    def computeWeightedAverage(self, learner_data, scaling_factors, rescale: bool | None = None) -> bytes:
+        """ckks.cpp:264-320: sum_i float32(w_i) * ct_i over learners; size mismatch prints and returns b"".
+
+        ``rescale`` (extension; default: the handle's setting, normally off) appends PALISADE's ModReduce to every
+        ciphertext of the result."""
+        rescale = self.rescale if rescale is None else bool(rescale)
         learner_data, scaling_factors = list(learner_data), list(scaling_factors)
         if len(learner_data) != len(scaling_factors):
             print("Error: learner_data and scaling_factors size mismatch")  # ckks.cpp:266
@@ -337,21 +355,37 @@ class CKKS(Scheme):
         lens = (C.c_uint64 * k)(*[len(b) for b in blobs])
         w = (C.c_float * k)(*[float(v) for v in scaling_factors])
         cap = len(blobs[0]) if k else 0   # the result has learner 0's layout (ckks.cpp:291-292)
+        into = lib().shelfi_compute_weighted_average_into
+        alloc = lib().shelfi_compute_weighted_average
+        if rescale:
+            into, alloc = lib().shelfi_compute_weighted_average_rescaled_into, lib().shelfi_compute_weighted_average_rescaled
+            n_ct = (cap - self.blob_size(1)) // (self.blob_size(2) - self.blob_size(1)) + 1 if cap else 0
+            cap = lib().shelfi_blob_size_level(self._h, n_ct, self.num_limbs - 1) if n_ct > 0 and self.num_limbs > 1 else 0
         if cap:
             dst = PinnedBlob(cap) if self.pinned else _new_bytes(cap)
             n = C.c_uint64()
-            rc = lib().shelfi_compute_weighted_average_into(self._h, ptrs, lens, w, k, _addr(dst), cap, C.byref(n))
+            rc = into(self._h, ptrs, lens, w, k, _addr(dst), cap, C.byref(n))
             if rc == 0 and n.value == cap:
                 return dst
         out, n = C.c_void_p(), C.c_uint64()   # errors, or a result of another size: the allocating call reports / returns it
-        self._check(lib().shelfi_compute_weighted_average(self._h, ptrs, lens, w, k, C.byref(out), C.byref(n)))
+        self._check(alloc(self._h, ptrs, lens, w, k, C.byref(out), C.byref(n)))
+        try:
+            return C.string_at(out.value, n.value)
+        finally:
+            lib().shelfi_free(out)
+
+    def rescaleCiphertexts(self, learner_data) -> bytes:
+        """Extension: PALISADE ModReduce on every ciphertext of an aggregated (depth-2) blob — one tower fewer."""
+        blob = _as_bytes(learner_data)
+        out, n = C.c_void_p(), C.c_uint64()
+        self._check(lib().shelfi_rescale(self._h, _addr(blob), len(blob), C.byref(out), C.byref(n)))
         try:
             return C.string_at(out.value, n.value)
         finally:
             lib().shelfi_free(out)
 
     def decrypt(self, learner_data, data_dimensions: int) -> np.ndarray:
-        """ckks.cpp:170-213: serialized ciphertext vector -> float64[data_dimensions]."""
+        """ckks.cpp:170-213: serialized ciphertext vector -> float64[data_dimensions] (level-0 or rescaled)."""
         blob = _as_bytes(learner_data)
         n = int(data_dimensions)
         out = np.empty(n, dtype=np.float64)

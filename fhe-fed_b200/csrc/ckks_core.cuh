@@ -1445,6 +1445,31 @@ struct StoreMulAdd {
         reinterpret_cast<u64x2 *>(out)[vt] = u64x2{csub(csub(r0, q2), q), csub(csub(r1, q2), q)};
     }
 };
+// rescale (PALISADE DCRTPoly::DropLastElementAndScale): the dropped tower's coefficients t (canonical, mod q_last) enter
+// the forward transform of every remaining tower as their centred representative reduced mod q_i (NativeVector::
+// SwitchModulus), and the epilogue forms (c_i - NTT_i(t)) * q_last^-1 mod q_i.
+struct RescaleConst { u64 q_last, inv[kMaxLimbs], inv_s[kMaxLimbs]; };   // inv[i] = q_last^-1 mod q_i + Shoup companion
+HD i64 centre_mod(u64 t, u64 q) { return t > (q >> 1) ? (i64)t - (i64)q : (i64)t; }
+struct LoadSwitch {
+    const u64 *t; u64 q_last; const LimbConst *lc;
+    HD u64 operator()(u32 i) const { return signed_to_mod(centre_mod(t[i], q_last), *lc); }
+};
+struct DLoadSwitch {
+    const u64 *t; u64 q_last; const LimbConst *lc;
+    HD double operator()(u32 i) const { return d_from_residue(signed_to_mod(centre_mod(t[i], q_last), *lc), lc->q); }
+};
+struct StoreRescale {
+    typedef u64x2 Aux;
+    static constexpr int kGroup = 4;
+    const u64 *c; u64 *out; const LimbConst *lc; u64 inv, inv_s;
+    HD Aux fetch(u32 vt) const { return ld_readonly(reinterpret_cast<const u64x2 *>(c) + vt); }
+    HD void operator()(u32 vt, u64 x, u64 y, const Aux &a) const {
+        const u64 q = lc->q, nq = lc->nq;
+        u64 d0 = a.x + q - full_reduce(x, *lc), d1 = a.y + q - full_reduce(y, *lc);       // (0, 2q)
+        reinterpret_cast<u64x2 *>(out)[vt] = u64x2{csub(shoup_lazy_nq(d0, inv, inv_s, nq), q),
+                                                   csub(shoup_lazy_nq(d1, inv, inv_s, nq), q)};
+    }
+};
 // decrypt: t = c0 + c1*s on the way into the inverse transform (< 3q for reduced input)
 struct LoadDecryptPair {
     const u64 *c0, *c1; const tw_t *s; u64 q;

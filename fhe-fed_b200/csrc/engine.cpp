@@ -43,7 +43,7 @@ struct DeviceBuffer {  // grow-only device scratch
 
 // Optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
 enum KernelId { kKEncodeSample, kKEncrypt, kKWeightedSum, kKDecryptIntt, kKDecode, kKPack, kKUnpack,
-                kKUnpackScaleAcc, kKNttForward, kKNttInverse, kKernelCount };
+                kKUnpackScaleAcc, kKNttForward, kKNttInverse, kKRescale, kKernelCount };
 struct Profiler {
     bool on = false;
     struct Rec { int id; cudaEvent_t a, b; };
@@ -155,7 +155,7 @@ struct shelfi_ckks {
     // device-resident parameters
     DeviceBuffer d_tw, d_itw, d_dtw, d_pk_b, d_pk_a, d_sk, d_fft_inv, d_fft_fwd;
     // scratch
-    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_image3, s_out, s_vals, s_zs, s_rows, s_pt;
+    DeviceBuffer s_x, s_m, s_ve, s_coeff, s_dense, s_image, s_image2, s_image3, s_out, s_vals, s_zs, s_rows, s_pt, s_resc, s_dense2;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_stage_out = nullptr;
     // rings above one tile: learner i+1 is encoded and sampled on this stream while learner i's transforms run
@@ -395,8 +395,8 @@ bool same_ring(const wire::ContextParams &a, const wire::ContextParams &b) {
            !std::memcmp(a.root, b.root, sizeof(uint64_t) * a.limbs);
 }
 
-BlobRuns to_runs(const shelfi_ckks *h, const uint64_t *run0, const uint64_t *run1, uint64_t stride) {
-    const uint32_t L = h->ctx.limbs;
+BlobRuns to_runs(const shelfi_ckks *h, const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint32_t limbs = 0) {
+    const uint32_t L = limbs ? limbs : h->ctx.limbs;
     BlobRuns br{};
     br.runs = 2 * L;
     br.n = h->ctx.ring_dim;
@@ -497,30 +497,70 @@ int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_ind
     return encrypt_dense_many(h, &d_x, 1, n, ct_index0, &d_ct, s);
 }
 
-bool general_decode(const shelfi_ckks *h) { return h->rc.log_blocks > 0 || h->ctx.limbs > 2; }
+bool general_decode(const shelfi_ckks *h, uint32_t limbs = 0) {
+    return h->rc.log_blocks > 0 || (limbs ? limbs : h->ctx.limbs) > 2;
+}
 
+// A rescaled ciphertext keeps the first `limbs` towers of the chain: the same ring and tables, a shorter CRT.
+// ([PAL] Decrypt drops the secret key's extra towers to match; here the kernels simply stop at rc.limbs.)
+struct LevelView {
+    RingConst rc;
+    Crt2Const crt;
+    CrtNConst crtn;
+};
+LevelView level_view(const shelfi_ckks *h, uint32_t limbs) {
+    LevelView v{h->rc, h->crt, h->crtn};
+    if (limbs && limbs != h->ctx.limbs) {
+        v.rc.limbs = limbs;
+        v.crt = make_crt2(h->ctx.modulus[0], limbs >= 2 ? h->ctx.modulus[1] : 0);
+        v.crtn = make_crtn(h->ctx.modulus, limbs);
+    }
+    return v;
+}
+
+// limbs = towers per polynomial of d_ct (0 = the context's chain, i.e. level 0)
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
-                  cudaStream_t s, const uint32_t *d_sel = nullptr) {
+                  cudaStream_t s, const uint32_t *d_sel = nullptr, uint32_t limbs = 0) {
     const uint64_t N = h->ctx.ring_dim;
-    CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * N * sizeof(uint64_t)));
-    timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(h->rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
+    const LevelView lv = level_view(h, limbs);
+    CU(h->s_coeff.reserve(n_ct * lv.rc.limbs * N * sizeof(uint64_t)));
+    timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(lv.rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
     DecodeConst dc{};
-    dc.crt = h->crt;
+    dc.crt = lv.crt;
     double p = (double)h->ctx.plaintext_modulus;
     dc.pre = std::pow(sf, -1) * std::pow(2, p);   // [PAL] Decode: scale to 2^p before the FFT, back after it
     dc.pow_p = std::pow(2, -p);
-    if (!general_decode(h)) {
-        timed(h, kKDecode, s, [&] { launch_decode(h->rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s, d_sel); });
+    if (!general_decode(h, lv.rc.limbs)) {
+        timed(h, kKDecode, s, [&] { launch_decode(lv.rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s, d_sel); });
     } else {
         CU(h->s_vals.reserve(n_ct * N * sizeof(double)));
         if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(n_ct * (size_t)h->ec.slots * sizeof(cplx)));
         timed(h, kKDecode, s, [&] {
-            launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, h->s_vals.as<double>(), nullptr, nullptr,
+            launch_crt(lv.rc, dc, lv.crtn, h->s_coeff.as<u64>(), (u32)n_ct, h->s_vals.as<double>(), nullptr, nullptr,
                        nullptr, s);
-            launch_decode_fft(h->rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s,
+            launch_decode_fft(lv.rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s,
                               d_sel);
         });
     }
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// [PAL] ModReduce under EXACTRESCALE (DCRTPoly::DropLastElementAndScale) on a dense batch:
+// d_ct[n_ct][2][limbs_in][N] -> d_out[n_ct][2][limbs_in - 1][N].  (c - [c]_{q_l}) / q_l with the centred remainder.
+int rescale_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs_in, uint64_t *d_out, cudaStream_t s) {
+    if (limbs_in < 2 || limbs_in > h->ctx.limbs) return fail(h, SHELFI_ERR_ARG, "no tower left to drop");
+    if (n_ct > (0x7fffffffull / (2 * kMaxLimbs)) >> h->rc.log_blocks) return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
+    const LevelView lv = level_view(h, limbs_in);
+    RescaleConst rs{};
+    rs.q_last = h->ctx.modulus[limbs_in - 1];
+    for (uint32_t i = 0; i + 1 < limbs_in; i++) {
+        const uint64_t q = h->ctx.modulus[i];
+        rs.inv[i] = nt::inv_mod(rs.q_last % q, q);
+        rs.inv_s[i] = nt::shoup(rs.inv[i], q);
+    }
+    CU(h->s_resc.reserve(n_ct * 2 * h->ctx.ring_dim * sizeof(uint64_t)));
+    timed(h, kKRescale, s, [&] { launch_rescale(lv.rc, rs, d_ct, h->s_resc.as<u64>(), d_out, (u32)n_ct, s); });
     CU(cudaGetLastError());
     return 0;
 }
@@ -656,15 +696,19 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
 // ckks.cpp:264-320 for n_layers ciphertext vectors per learner (blobs[i * n_layers + s] = learner i, layer s).
 // n_layers == 1 is CKKS::computeWeightedAverage.  Learner i+1 streams in over PCIe while learner i is folded into the
 // resident accumulator; one D2H returns all result blobs (blob s at dst + offsets[s]).
+// rescale: the average is brought back to depth 1 / one tower fewer before it is serialized (opt-in,
+// the reference leaves it at depth 2), which halves the bytes the server sends at two towers.
 int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens, const float *w, uint32_t k,
               uint32_t n_layers, uint8_t *dst, uint64_t cap, uint8_t **alloc_out, uint64_t *offsets, uint64_t *lens,
-              uint64_t *total_len) {
+              uint64_t *total_len, bool rescale = false) {
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
     if (!blobs || !blob_lens || !w || !lens || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
     if (k == 0) return fail(h, SHELFI_ERR_ARG, "no learners");
     const uint32_t L = h->ctx.limbs;
     const double sf0 = (double)h->ctx.modulus[L - 1];
+    if (rescale && L < 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "rescale needs a chain of at least two towers");
+    const uint32_t Lo = rescale ? L - 1 : L;   // towers of the result
     std::vector<wire::BlobMap> maps((size_t)k * n_layers);
     std::vector<uint64_t> in_off((size_t)k * n_layers);   // where each input blob sits in its learner's image
     size_t max_image = 0;
@@ -679,6 +723,8 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
             if (!same_ring(maps[id].ctx, h->ctx))
                 return fail(h, SHELFI_ERR_PARAMS, who + ": ciphertext parameters differ from the loaded context");
             if (maps[id].n_ct != maps[s].n_ct) return fail(h, SHELFI_ERR_PARAMS, who + ": ciphertext count differs");
+            if (maps[id].ct_limbs != L)
+                return fail(h, SHELFI_ERR_UNSUPPORTED, who + ": only fresh depth-1 level-0 ciphertexts are supported");
             for (const auto &m : maps[id].meta)
                 if (m.depth != 1 || m.level != 0)
                     return fail(h, SHELFI_ERR_UNSUPPORTED, who + ": only fresh depth-1 level-0 ciphertexts are supported");
@@ -692,6 +738,8 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
     for (uint32_t s = 0; s < n_layers; s++) {
         std::vector<wire::CiphertextMeta> meta = maps[s].meta;  // ckks.cpp:291-292: result starts as learner 0's vector
         for (auto &m : meta) { m.depth += 1; m.scaling_factor *= sf0; }  // [PAL] EvalMult(ct, double), no rescale
+        if (rescale)   // [PAL] ModReduce: depth - 1, level + 1, scalingFactor / q_l (double), last tower dropped
+            for (auto &m : meta) { m.depth -= 1; m.level += 1; m.scaling_factor /= sf0; m.limbs = Lo; }
         slot[s].n_ct = maps[s].n_ct; slot[s].ct0 = n_ct; slot[s].off = image;
         slot[s].plan = wire::plan_ciphertext_blob(maps[s].ctx, slot[s].n_ct, meta);
         n_ct += slot[s].n_ct; image = align8(image + slot[s].plan.size);
@@ -705,8 +753,9 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
     }
     auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
     cudaStream_t st = h->stream, cs = h->copy_stream;
-    const uint64_t ct_words = 2ull * L * h->ctx.ring_dim;
+    const uint64_t ct_words = 2ull * L * h->ctx.ring_dim, out_words = 2ull * Lo * h->ctx.ring_dim;
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
+    if (rescale) CUB(h->s_dense2.reserve(n_ct * out_words * 8));
     CUB(h->s_image.reserve(std::max(max_image, image_bytes(image))));
     CUB(h->s_image2.reserve(max_image));
     DeviceBuffer *img[2] = {&h->s_image, &h->s_image2};
@@ -725,13 +774,13 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
     auto run_start = [](const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint64_t j) {
         return j == 0 ? run0[0] : run1[0] + (j - 1) * stride;
     };
-    auto sub_runs = [&](const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint64_t c0) {
+    auto sub_runs = [&](const uint64_t *run0, const uint64_t *run1, uint64_t stride, uint64_t c0, uint32_t limbs) {
         uint64_t r0[2 * kMaxLimbs], r1[2 * kMaxLimbs];   // run offsets of ciphertexts c0 and c0 + 1
-        for (uint32_t r = 0; r < 2 * L; r++) {
+        for (uint32_t r = 0; r < 2 * limbs; r++) {
             r0[r] = c0 == 0 ? run0[r] : run1[r] + (c0 - 1) * stride;
             r1[r] = run1[r] + c0 * stride;
         }
-        return to_runs(h, r0, r1, stride);
+        return to_runs(h, r0, r1, stride, limbs);
     };
     uint64_t sent = 0;
     for (uint32_t g = 0, seq = 0; g < groups; g++) {
@@ -758,7 +807,7 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
                 const size_t id = (size_t)i * n_layers + s;
                 const uint64_t cnt = (c1 ? c1 : slot[s].n_ct) - c0;
                 timed(h, kKUnpackScaleAcc, st, [&] {
-                    launch_unpack_scale_accumulate(h->rc, sub_runs(maps[id].run0, maps[id].run1, maps[id].stride, c0),
+                    launch_unpack_scale_accumulate(h->rc, sub_runs(maps[id].run0, maps[id].run1, maps[id].stride, c0, L),
                                                    img[b]->as<u64>() + in_off[id] / 8, cs_l, i == 0 ? 1u : 0u,
                                                    h->s_dense.as<u64>() + (slot[s].ct0 + c0) * ct_words, cnt, st);
                 });
@@ -768,9 +817,15 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
         }
         for (const LayerSlot &ls : slot) {
             const uint64_t cnt = (c1 ? c1 : ls.n_ct) - c0;
+            const u64 *result = h->s_dense.as<u64>() + (ls.ct0 + c0) * ct_words;
+            if (rescale) {
+                u64 *reduced = h->s_dense2.as<u64>() + (ls.ct0 + c0) * out_words;
+                if ((rcode = rescale_dense(h, result, cnt, L, reduced, st))) return bail(rcode);
+                result = reduced;
+            }
             timed(h, kKPack, st, [&] {
-                launch_pack(h->rc, sub_runs(ls.plan.run0, ls.plan.run1, ls.plan.stride, c0),
-                            h->s_dense.as<u64>() + (ls.ct0 + c0) * ct_words, out_image + ls.off / 8, cnt, st);
+                launch_pack(h->rc, sub_runs(ls.plan.run0, ls.plan.run1, ls.plan.stride, c0, Lo), result,
+                            out_image + ls.off / 8, cnt, st);
             });
         }
         CUB(cudaGetLastError());
@@ -817,6 +872,7 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
         if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, e);
         if (!same_ring(maps[s].ctx, h->ctx)) return fail(h, SHELFI_ERR_PARAMS, "ciphertext parameters differ from the loaded context");
         const uint64_t c = maps[s].n_ct;
+        if (maps[s].ct_limbs < 1 || maps[s].ct_limbs > h->ctx.limbs) return fail(h, SHELFI_ERR_FORMAT, "unexpected tower count");
         if (dims[s] == 0 || dims[s] > c * batch || dims[s] + batch <= c * batch)
             return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
         slot[s].n = dims[s]; slot[s].n_ct = c; slot[s].x0 = n; slot[s].ct0 = n_ct; slot[s].off = image;
@@ -840,8 +896,8 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
         if ((rcode = h2d(h, h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], st))) return rcode;
         u64 *dense = h->s_dense.as<u64>() + ls.ct0 * ct_words;
         timed(h, kKUnpack, st, [&] {
-            launch_unpack(h->rc, to_runs(h, maps[s].run0, maps[s].run1, maps[s].stride), h->s_image.as<u64>() + ls.off / 8, dense,
-                          ls.n_ct, st);
+            launch_unpack(h->rc, to_runs(h, maps[s].run0, maps[s].run1, maps[s].stride, maps[s].ct_limbs),
+                          h->s_image.as<u64>() + ls.off / 8, dense, ls.n_ct, st);
         });
         CU(cudaGetLastError());
         // ciphertexts usually share one scaling factor; split the launch where they do not
@@ -849,13 +905,65 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             uint64_t j1 = j0 + 1;
             while (j1 < ls.n_ct && maps[s].meta[j1].scaling_factor == maps[s].meta[j0].scaling_factor) j1++;
             uint64_t first = j0 * batch, last = std::min(ls.n, j1 * batch);
-            if ((rcode = decrypt_dense(h, dense + j0 * ct_words, j1 - j0, maps[s].meta[j0].scaling_factor,
-                                       h->s_out.as<double>() + ls.x0 + first, last - first, st)))
+            const uint64_t layer_words = 2ull * maps[s].ct_limbs * N;   // a rescaled layer is packed tighter
+            if ((rcode = decrypt_dense(h, dense + j0 * layer_words, j1 - j0, maps[s].meta[j0].scaling_factor,
+                                       h->s_out.as<double>() + ls.x0 + first, last - first, st, nullptr, maps[s].ct_limbs)))
                 return rcode;
             j0 = j1;
         }
     }
     return d2h_sync(h, out, h->s_out.p, n * sizeof(double), st);
+}
+
+// [PAL] cc->ModReduce on every ciphertext of a serialized vector (rescale-before-transport): the blob
+// comes back one tower shorter, depth - 1, level + 1, scalingFactor / q_l.
+int rescale_host(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t *dst, uint64_t cap, uint8_t **alloc_out,
+                 uint64_t *out_len) {
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!blob || !out_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    wire::BlobMap map;
+    std::string e = wire::map_ciphertext_blob(blob, blob_len, false, &map);
+    if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, e);
+    if (!same_ring(map.ctx, h->ctx)) return fail(h, SHELFI_ERR_PARAMS, "ciphertext parameters differ from the loaded context");
+    const uint32_t Lin = map.ct_limbs;
+    if (Lin < 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "no tower left to drop");
+    std::vector<wire::CiphertextMeta> meta = map.meta;
+    const double ql = (double)h->ctx.modulus[Lin - 1];
+    for (auto &m : meta) {
+        if (m.depth < 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "ciphertext is already at depth 1");
+        m.depth -= 1; m.level += 1; m.scaling_factor /= ql; m.limbs = Lin - 1;
+    }
+    wire::BlobPlan plan = wire::plan_ciphertext_blob(map.ctx, map.n_ct, meta);
+    if (alloc_out) {
+        dst = static_cast<uint8_t *>(std::malloc(plan.size));
+        if (!dst) return fail(h, SHELFI_ERR_ARG, "out of host memory");
+    } else if (!dst || cap < plan.size) {
+        return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
+    }
+    auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
+    const uint64_t N = h->ctx.ring_dim;
+    cudaStream_t st = h->stream;
+    CUB(h->s_image.reserve(image_bytes(blob_len)));
+    CUB(h->s_image2.reserve(image_bytes(plan.size)));
+    CUB(h->s_dense.reserve(map.n_ct * 2 * Lin * N * 8));
+    CUB(h->s_dense2.reserve(map.n_ct * 2 * (Lin - 1) * N * 8));
+    if ((rcode = h2d(h, h->s_image.p, blob, blob_len, st))) return bail(rcode);
+    timed(h, kKUnpack, st, [&] {
+        launch_unpack(h->rc, to_runs(h, map.run0, map.run1, map.stride, Lin), h->s_image.as<u64>(), h->s_dense.as<u64>(),
+                      map.n_ct, st);
+    });
+    if ((rcode = rescale_dense(h, h->s_dense.as<u64>(), map.n_ct, Lin, h->s_dense2.as<u64>(), st))) return bail(rcode);
+    timed(h, kKPack, st, [&] {
+        launch_pack(h->rc, to_runs(h, plan.run0, plan.run1, plan.stride, Lin - 1), h->s_dense2.as<u64>(),
+                    h->s_image2.as<u64>(), map.n_ct, st);
+    });
+    CUB(cudaGetLastError());
+    if ((rcode = d2h_sync(h, dst, h->s_image2.p, plan.size, st))) return bail(rcode);
+    write_segments(plan, dst);
+    if (alloc_out) *alloc_out = dst;
+    *out_len = plan.size;
+    return 0;
 }
 
 }  // namespace
@@ -888,7 +996,7 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         h->prof.release();
         free_params(h);
         for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_image3,
-                                &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows, &h->s_pt})
+                                &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows, &h->s_pt, &h->s_resc, &h->s_dense2})
             b->release();
         for (int i = 0; i < 2; i++) { cudaEventDestroy(h->ev_copy[i]); cudaEventDestroy(h->ev_done[i]); }
         for (int i = 0; i < 2; i++) {
@@ -1130,6 +1238,9 @@ int shelfi_key_tag(const shelfi_ckks *h, char out[33]) {
 }
 uint64_t shelfi_num_ciphertexts(const shelfi_ckks *h, uint64_t n) { return h && h->batch ? (n + h->batch - 1) / h->batch : 0; }
 uint64_t shelfi_ciphertext_words(const shelfi_ckks *h) { return h && h->have_cc ? 2ull * h->ctx.limbs * h->ctx.ring_dim : 0; }
+uint64_t shelfi_blob_size_level(const shelfi_ckks *h, uint64_t n_ct, uint32_t limbs) {
+    return h && h->have_cc && n_ct && limbs >= 1 && limbs <= h->ctx.limbs ? wire::ciphertext_blob_size(h->ctx, n_ct, limbs) : 0;
+}
 uint64_t shelfi_blob_size(const shelfi_ckks *h, uint64_t n_ct) {
     return h && h->have_cc && n_ct ? wire::ciphertext_blob_size(h->ctx, n_ct) : 0;
 }
@@ -1160,6 +1271,31 @@ int shelfi_compute_weighted_average_into(shelfi_ckks *h, const uint8_t *const *b
     std::lock_guard<std::mutex> lock(h->mu);
     if (!blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
     return wavg_host(h, blobs, blob_lens, weights, k, 1, dst, cap, nullptr, nullptr, blob_len, nullptr);
+}
+int shelfi_compute_weighted_average_rescaled(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                             const float *weights, uint32_t k, uint8_t **blob, uint64_t *blob_len) {
+    if (!h || !blob) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    return wavg_host(h, blobs, blob_lens, weights, k, 1, nullptr, 0, blob, nullptr, blob_len, nullptr, true);
+}
+int shelfi_compute_weighted_average_rescaled_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                                  const float *weights, uint32_t k, uint8_t *dst, uint64_t cap,
+                                                  uint64_t *blob_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!blob_len) return fail(h, SHELFI_ERR_ARG, "null argument");
+    return wavg_host(h, blobs, blob_lens, weights, k, 1, dst, cap, nullptr, nullptr, blob_len, nullptr, true);
+}
+int shelfi_rescale(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t **out, uint64_t *out_len) {
+    if (!h || !out) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return rescale_host(h, blob, blob_len, nullptr, 0, out, out_len);
+}
+int shelfi_rescale_into(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t *dst, uint64_t cap, uint64_t *out_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return rescale_host(h, blob, blob_len, dst, cap, nullptr, out_len);
 }
 int shelfi_decrypt(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint64_t n, double *out) {
     if (!h) return SHELFI_ERR_ARG;
@@ -1277,6 +1413,48 @@ int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, d
         return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
     return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n,
                          static_cast<cudaStream_t>(stream));
+}
+
+int shelfi_rescale_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs_in, uint64_t *d_out, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!d_ct || !d_out || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    return rescale_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, limbs_in ? limbs_in : h->ctx.limbs,
+                         reinterpret_cast<u64 *>(d_out), static_cast<cudaStream_t>(stream));
+}
+int shelfi_decrypt_level_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs, double scaling_factor,
+                                double *d_out, uint64_t n, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!d_ct || !d_out || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    if (limbs < 1 || limbs > h->ctx.limbs) return fail(h, SHELFI_ERR_ARG, "tower count outside the chain");
+    if (n == 0 || n > n_ct * h->batch || n + h->batch <= n_ct * h->batch)
+        return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
+    return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n,
+                         static_cast<cudaStream_t>(stream), nullptr, limbs);
+}
+int shelfi_decrypt_words_level_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs, uint64_t *d_words,
+                                      void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!d_ct || !d_words || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    if (limbs < 1 || limbs > h->ctx.limbs) return fail(h, SHELFI_ERR_ARG, "tower count outside the chain");
+    const LevelView lv = level_view(h, limbs);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CU(h->s_coeff.reserve(n_ct * limbs * h->ctx.ring_dim * sizeof(uint64_t)));
+    launch_decrypt_intt(lv.rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
+    DecodeConst dc{};
+    dc.crt = lv.crt;
+    launch_crt(lv.rc, dc, lv.crtn, h->s_coeff.as<u64>(), (u32)n_ct, nullptr, reinterpret_cast<u64 *>(d_words), nullptr,
+               nullptr, s);
+    CU(cudaGetLastError());
+    return 0;
 }
 
 // ---- per-slot plaintext weights: out = sum_l ct_l (*) Encode(w_l)  ([PAL] EvalMult(ct, plaintext) + EvalAdd; the

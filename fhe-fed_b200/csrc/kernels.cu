@@ -234,6 +234,66 @@ __global__ void __launch_bounds__(kNttThreads, 3) ntt_inverse_kernel(const __gri
     u64 *tile_ptr = data + (size_t)blockIdx.x * kN;   // tiles of a row are contiguous
     intt_tile<D>(threadIdx.x, sm, lc, D ? head_bits(D, blk) : 1u, LoadPairGlobal{tile_ptr}, tile_ptr);
 }
+// ------------------------------------------------------------------------------------------
+// rescale: drop the last tower of every polynomial (PALISADE ModReduce under EXACTRESCALE)
+//   pass 1: inverse transform of the last tower of each polynomial, read in place from the ciphertext batch,
+//           coefficients to t[n_ct * 2][N]   (rings above one tile: + intt_tail_kernel on t)
+//   pass 2: one CTA per (polynomial, remaining tower i, tile): forward transform of t switched into q_i, with
+//           (c_i - .) * q_last^-1 folded into the store -> out[n_ct][2][L-1][N]
+// ------------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(kNttThreads, 3) rescale_intt_kernel(const __grid_constant__ RingConst rc, const u64 *ct,
+                                                                      u64 *t) {
+    extern __shared__ __align__(16) u64 sm[];
+    const u32 L = rc.limbs;                       // towers of the input
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u64 ctp = blockIdx.x >> D;              // ct * 2 + poly
+    const u64 n = (u64)kN << D;
+    const LimbConst lc = rc.limb[L - 1];
+    const u64 *src = ct + (ctp * L + (L - 1)) * n + (size_t)blk * kN;
+    intt_tile<D>(threadIdx.x, sm, lc, D ? head_bits(D, blk) : 1u, LoadPairGlobal{src}, t + ctp * n + (size_t)blk * kN);
+}
+template <int D>
+__global__ void __launch_bounds__(kNttThreads, 3) rescale_ntt_kernel(const __grid_constant__ RingConst rc,
+                                                                     const __grid_constant__ RescaleConst rs,
+                                                                     const u64 *ct, const u64 *t, u64 *out) {
+    extern __shared__ __align__(16) u64 sm[];
+    const int tid = threadIdx.x;
+    const u32 L = rc.limbs, Lo = L - 1;
+    const u32 blk = D ? blockIdx.x & ((1u << D) - 1u) : 0u;
+    const u32 hb = D ? head_bits(D, blk) : 1u;
+    const u32 row = blockIdx.x >> D;              // ctp * (L - 1) + i
+    const u32 i = row % Lo;
+    const u64 ctp = row / Lo;
+    const u64 n = (u64)kN << D;
+    const LimbConst lc = rc.limb[i];
+    const u64 *t_row = t + ctp * n;
+    const StoreRescale st{ct + (ctp * L + i) * n + (size_t)blk * kN, out + (size_t)row * n + (size_t)blk * kN, &lc,
+                          rs.inv[i], rs.inv_s[i]};
+    if (lc.dtw) {
+        if (!cluster_head_for(D)) {
+            ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadSwitch>{DLoadSwitch{t_row, rs.q_last, &lc}, &lc, blk}, st);
+        } else {
+            cluster_head_d<D>(tid, sm, lc, DLoadSwitch{t_row, rs.q_last, &lc});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, st);
+        }
+        return;
+    }
+    if (!cluster_head_for(D)) {
+        fwd_phase_a(tid, sm, lc, hb, HeadLoad<D, LoadSwitch>{LoadSwitch{t_row, rs.q_last, &lc}, &lc, blk});
+    } else {
+        cluster_head<D>(tid, sm, lc, LoadSwitch{t_row, rs.q_last, &lc});
+        fwd_phase_a(tid, sm, lc, hb, LoadTile{sm});
+    }
+    __syncthreads();
+    fwd_phase_mid<7>(tid, sm, lc, hb);
+    __syncthreads();
+    fwd_phase_mid<4>(tid, sm, lc, hb);
+    __syncthreads();
+    fwd_phase_mid<1>(tid, sm, lc, hb);
+    __syncthreads();
+    fwd_phase_e(tid, sm, lc, hb, st);
+}
 constexpr int kTailThreads = 256;
 template <int D>
 __global__ void __launch_bounds__(kTailThreads) intt_tail_kernel(const __grid_constant__ RingConst rc, u64 *data) {
@@ -787,6 +847,8 @@ cudaError_t kernels_init() {
     OPT_IN_D(encrypt_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(plain_ntt_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(decrypt_intt_kernel, NTT_SMEM_BYTES)
+    OPT_IN_D(rescale_intt_kernel, NTT_SMEM_BYTES)
+    OPT_IN_D(rescale_ntt_kernel, NTT_SMEM_BYTES)
     OPT_IN(encrypt_fused_kernel, NTT_SMEM_BYTES)
     OPT_IN(encode_kernel<true>, kFftFast * sizeof(cplx))
     OPT_IN(encode_kernel<false>, kFftFast * sizeof(cplx))
@@ -863,6 +925,20 @@ void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64
     DISPATCH_D(rc.log_blocks, decrypt_intt_kernel<D><<<rows << D, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ct, sk, coeff))
     if (rc.log_blocks == 1) intt_tail_kernel<1><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, coeff);
     if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, coeff);
+}
+void launch_rescale(const RingConst &rc, const RescaleConst &rs, const u64 *ct, u64 *t, u64 *out, u32 n_ct,
+                    cudaStream_t s) {
+    if (!n_ct || rc.limbs < 2) return;
+    const u32 polys = n_ct * 2;
+    DISPATCH_D(rc.log_blocks, rescale_intt_kernel<D><<<polys << D, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ct, t))
+    if (rc.log_blocks) {   // outer inverse stages + N^-1 over t, whose rows all belong to the dropped tower
+        RingConst last = rc;
+        last.limbs = 1;
+        last.limb[0] = rc.limb[rc.limbs - 1];
+        if (rc.log_blocks == 1) intt_tail_kernel<1><<<dim3(kN / kTailThreads, polys), kTailThreads, 0, s>>>(last, t);
+        if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, polys), kTailThreads, 0, s>>>(last, t);
+    }
+    DISPATCH_D(rc.log_blocks, launch_tiles(rescale_ntt_kernel<D>, polys * (rc.limbs - 1), D, s, rc, rs, ct, t, out))
 }
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
                    double *out, u64 n, cudaStream_t s, const u32 *sel) {

@@ -26,6 +26,10 @@ void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const Samp
                           u64 n, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s);
 // decrypt stage 1: c0 + c1*s, inverse NTT -> coeff[n_ct][L][N]
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s);
+// rescale by one level: ct[n_ct][2][L][N] -> out[n_ct][2][L-1][N] (rc.limbs = L = towers of the input);
+// t = scratch of n_ct * 2 * N words (the dropped tower in coefficient form)
+void launch_rescale(const RingConst &rc, const RescaleConst &rs, const u64 *ct, u64 *t, u64 *out, u32 n_ct,
+                    cudaStream_t s);
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
                    double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);

@@ -205,11 +205,21 @@ void context(Archive &ar, ContextParams &p) {
     }
 }
 
-// DCRTPoly in EVALUATION format; offsets[l] receives where tower l's coefficients are
-void dcrt_poly(Archive &ar, const ContextParams &p, uint64_t *dst, const uint64_t *src, uint64_t *offsets) {
+// DCRTPoly in EVALUATION format; offsets[l] receives where tower l's coefficients are.
+// *limbs = towers of this polynomial: the context's count at level 0, fewer after a rescale (0 on input when reading =
+// accept what the blob says).  A rescaled polynomial no longer shares the context's parameter object: PALISADE's
+// DCRTPolyImpl::DropLastElement gives it a copy with the last tower popped and the modulus divided, and cereal writes
+// that object in line — a new pointer id, the ElemParams fields, and back references to the ILNativeParams the context
+// carried.  No fixture pins this form.
+void dcrt_poly(Archive &ar, const ContextParams &p, uint32_t *limbs, uint64_t *dst, const uint64_t *src,
+               uint64_t *offsets) {
     ar.version(kVDcrtPoly, 1);
-    ar.literal<uint64_t>(p.limbs, "tower count");
-    for (uint32_t l = 0; l < p.limbs && ar.ok(); l++) {
+    uint64_t count = *limbs;
+    ar.value(count);
+    if (count < 1 || count > p.limbs || (*limbs && count != *limbs)) { ar.fail("unexpected tower count"); return; }
+    *limbs = (uint32_t)count;
+    const uint32_t lc = *limbs;
+    for (uint32_t l = 0; l < lc && ar.ok(); l++) {
         ar.version(kVNativePoly, 1);
         ar.same();
         ar.literal<uint8_t>(1, "values present flag");
@@ -225,7 +235,25 @@ void dcrt_poly(Archive &ar, const ContextParams &p, uint64_t *dst, const uint64_
     }
     ar.literal<uint32_t>(0, "polynomial format (EVALUATION)");
     ar.same();
-    ar.literal<uint32_t>(ar.ids.dcrt, "element parameter reference");
+    if (lc == p.limbs) { ar.literal<uint32_t>(ar.ids.dcrt, "element parameter reference"); return; }
+    ar.new_pointer();
+    ar.version(kVDcrtParams, 1); ar.version(kVElemParamsBig, 1);
+    ar.literal<uint32_t>(p.cyclotomic_order, "reduced parameters: cyclotomic order");
+    ar.literal<uint32_t>(p.ring_dim, "reduced parameters: ring dimension");
+    ar.literal<uint8_t>(1, "isPowerOfTwo");
+    ar.version(kVBigInteger, 1);
+    ContextParams reduced = p;
+    reduced.limbs = lc;
+    set_big_modulus(&reduced);
+    for (uint32_t w : reduced.big_modulus) ar.literal<uint32_t>(w, "reduced modulus word");
+    ar.literal<uint16_t>(reduced.big_modulus_msb, "reduced modulus msb");
+    big_zero(ar); big_zero(ar); big_zero(ar);
+    ar.literal<uint64_t>(lc, "reduced tower count");
+    for (uint32_t l = 0; l < lc; l++) {
+        ar.same();
+        ar.literal<uint32_t>(ar.ids.native[l], "reduced tower parameter reference");
+    }
+    big_zero(ar);  // originalModulus
 }
 
 void key_tag(Archive &ar, char (&tag)[33]) {
@@ -253,8 +281,10 @@ void key_file(Archive &ar, KeyFile &k, int n_polys) {
     size_t words = (size_t)k.ctx.limbs * k.ctx.ring_dim;
     if (ar.reading()) k.polys.assign(words * n_polys, 0);
     else if (k.polys.size() != words * n_polys) { ar.fail("key polynomial size mismatch"); return; }
-    for (int i = 0; i < n_polys && ar.ok(); i++)
-        dcrt_poly(ar, k.ctx, k.polys.data() + i * words, k.polys.data() + i * words, nullptr);
+    for (int i = 0; i < n_polys && ar.ok(); i++) {
+        uint32_t limbs = k.ctx.limbs;  // keys always carry the full chain
+        dcrt_poly(ar, k.ctx, &limbs, k.polys.data() + i * words, k.polys.data() + i * words, nullptr);
+    }
 }
 
 void ciphertext(Archive &ar, ContextParams &p, CiphertextMeta &m, uint64_t *runs) {
@@ -265,8 +295,10 @@ void ciphertext(Archive &ar, ContextParams &p, CiphertextMeta &m, uint64_t *runs
     if (!ar.ok()) return;
     key_tag(ar, m.tag);
     ar.literal<uint64_t>(2, "ciphertext element count");
-    dcrt_poly(ar, p, nullptr, nullptr, runs);
-    if (ar.ok()) dcrt_poly(ar, p, nullptr, nullptr, runs + p.limbs);
+    if (!ar.reading() && !m.limbs) m.limbs = p.limbs;
+    if (ar.reading()) m.limbs = 0;
+    dcrt_poly(ar, p, &m.limbs, nullptr, nullptr, runs);
+    if (ar.ok()) dcrt_poly(ar, p, &m.limbs, nullptr, nullptr, runs + m.limbs);
     ar.value(m.depth); ar.value(m.level); ar.value(m.scaling_factor); ar.value(m.encoding_type);
     ar.new_pointer();                                   // shared_ptr<map<string, Metadata>>, always empty here
     ar.literal<uint64_t>(0, "metadata map size");
@@ -313,6 +345,8 @@ std::string map_ciphertext_blob(const uint8_t *data, size_t len, bool single, Bl
         size_t start = ar.position();
         ciphertext(ar, out->ctx, out->meta[j], runs);
         if (!ar.ok()) break;
+        if (j == 0) out->ct_limbs = out->meta[0].limbs;
+        else if (out->meta[j].limbs != out->ct_limbs) { ar.fail("ciphertexts of one blob at different levels"); break; }
         if (j == 0) std::memcpy(out->run0, runs, sizeof runs);
         if (j == 1) { std::memcpy(out->run1, runs, sizeof runs); start1 = start; }
         if (j == 2) out->stride = start - start1;
@@ -364,8 +398,9 @@ BlobPlan plan_ciphertext_blob(const ContextParams &p, uint64_t n_ct, const std::
     return plan;
 }
 
-uint64_t ciphertext_blob_size(const ContextParams &p, uint64_t n_ct) {
+uint64_t ciphertext_blob_size(const ContextParams &p, uint64_t n_ct, uint32_t ct_limbs) {
     std::vector<CiphertextMeta> m(1);
+    m[0].limbs = ct_limbs;
     if (n_ct <= 2) return plan_ciphertext_blob(p, n_ct, m).size;
     uint64_t s1 = plan_ciphertext_blob(p, 1, m).size, s2 = plan_ciphertext_blob(p, 2, m).size;
     return s1 + (n_ct - 1) * (s2 - s1);

@@ -41,12 +41,14 @@ struct CiphertextMeta {
     double scaling_factor = 0;
     uint32_t encoding_type = 4;           // CKKSPacked
     char tag[33] = {0};
+    uint32_t limbs = 0;                   // towers per polynomial; 0 when writing = the context's count (level 0)
 };
 
 // Where things are inside a serialized vector<Ciphertext>.
 struct BlobMap {
     ContextParams ctx;
     uint64_t n_ct = 0;
+    uint32_t ct_limbs = 0;                // towers per polynomial (< ctx.limbs after a rescale)
     uint64_t size = 0;
     uint64_t run0[2 * kMaxLimbs] = {0};   // byte offsets of ciphertext 0's coefficient runs
     uint64_t run1[2 * kMaxLimbs] = {0};   // ... of ciphertext 1 (absolute)
@@ -73,9 +75,9 @@ struct BlobPlan {
     uint64_t run0[2 * kMaxLimbs] = {0}, run1[2 * kMaxLimbs] = {0}, stride = 0;
     std::vector<Segment> segments;
 };
-// meta: one entry (applied to every ciphertext) or n_ct entries
+// meta: one entry (applied to every ciphertext) or n_ct entries; meta[].limbs < p.limbs writes rescaled ciphertexts
 BlobPlan plan_ciphertext_blob(const ContextParams &p, uint64_t n_ct, const std::vector<CiphertextMeta> &meta);
-uint64_t ciphertext_blob_size(const ContextParams &p, uint64_t n_ct);
+uint64_t ciphertext_blob_size(const ContextParams &p, uint64_t n_ct, uint32_t ct_limbs = 0);
 
 void set_big_modulus(ContextParams *p);  // fills big_modulus / msb from the limb moduli
 

@@ -89,6 +89,7 @@ int shelfi_key_tag(const shelfi_ckks *h, char out[33]);
 uint64_t shelfi_num_ciphertexts(const shelfi_ckks *h, uint64_t n); /* ceil(n / batchSize), src/ckks.cpp:65 */
 uint64_t shelfi_ciphertext_words(const shelfi_ckks *h);            /* 2 * L * N u64 per ciphertext (dense form) */
 uint64_t shelfi_blob_size(const shelfi_ckks *h, uint64_t n_ct);    /* bytes of a serialized vector of n_ct ciphertexts */
+uint64_t shelfi_blob_size_level(const shelfi_ckks *h, uint64_t n_ct, uint32_t limbs); /* ... that kept `limbs` towers */
 /* EvalMult constant for a learner weight: (int64)((double)(float)w * scalingFactor + 0.5)  (src/ckks.cpp:287-288) */
 int64_t shelfi_weight_constant(const shelfi_ckks *h, float w);
 
@@ -105,7 +106,19 @@ int shelfi_compute_weighted_average(shelfi_ckks *h, const uint8_t *const *blobs,
 int shelfi_compute_weighted_average_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                                          const float *weights, uint32_t k, uint8_t *dst, uint64_t cap,
                                          uint64_t *blob_len);
-/* CKKS::decrypt (src/ckks.cpp:170-213): blob -> n doubles (n = data_dimensions). */
+/* Rescale-before-transport (opt-in extension; the reference leaves the average at depth 2, src/ckks.cpp:287-303):
+ * the same weighted average followed by PALISADE's ModReduce (EXACTRESCALE: DCRTPoly::DropLastElementAndScale) on
+ * every ciphertext.  The result blob has one tower fewer (half the bytes at two towers), depth 1, level 1,
+ * scalingFactor / q_last; shelfi_decrypt and a PALISADE Decrypt read it like any other ciphertext vector.
+ * shelfi_rescale does the ModReduce alone on an already aggregated (depth >= 2) blob. */
+int shelfi_compute_weighted_average_rescaled(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                             const float *weights, uint32_t k, uint8_t **blob, uint64_t *blob_len);
+int shelfi_compute_weighted_average_rescaled_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                                  const float *weights, uint32_t k, uint8_t *dst, uint64_t cap,
+                                                  uint64_t *blob_len);
+int shelfi_rescale(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t **out, uint64_t *out_len);
+int shelfi_rescale_into(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t *dst, uint64_t cap, uint64_t *out_len);
+/* CKKS::decrypt (src/ckks.cpp:170-213): blob -> n doubles (n = data_dimensions).  Accepts level-0 and rescaled blobs. */
 int shelfi_decrypt(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint64_t n, double *out);
 
 /* ---- many independent vectors in one call ----
@@ -157,6 +170,14 @@ int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const 
                                           uint64_t n_ct, uint64_t *d_acc, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
                           uint64_t n, void *stream);
+/* ModReduce on a dense batch: d_ct[n_ct][2][limbs_in][N] -> d_out[n_ct][2][limbs_in - 1][N] (limbs_in 0 = the context's
+ * chain); the decrypt calls below take the towers the ciphertexts kept.  After one rescale of a depth-2 average the
+ * scaling factor to pass is scalingFactor^2 / q_last. */
+int shelfi_rescale_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs_in, uint64_t *d_out, void *stream);
+int shelfi_decrypt_level_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs, double scaling_factor,
+                                double *d_out, uint64_t n, void *stream);
+int shelfi_decrypt_words_level_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs, uint64_t *d_words,
+                                      void *stream);
 /* Per-slot plaintext weights: d_out = sum_l d_cts[l] (*) Encode(d_w[l]) — PALISADE EvalMult(ct, plaintext) + EvalAdd,
  * the ct x plaintext-vector aggregation of the TenSEAL/FLARE-style workload (code/benchmark_nvidia.py:439,461-465);
  * the reference's own computeWeightedAverage (ckks.cpp:287-288) only takes one scalar per learner.  d_w[l] holds n
@@ -201,7 +222,7 @@ int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n
 
 /* ---- per-kernel timing (benchmarks): CUDA events on the launching stream around every launch ----
  * kernel ids: 0 encode+sample, 1 encrypt, 2 weighted sum, 3 decrypt inverse NTT, 4 decode, 5 pack, 6 unpack,
- * 7 unpack-scale-accumulate, 8 forward NTT, 9 inverse NTT.  shelfi_profile_get waits for recorded launches. */
+ * 7 unpack-scale-accumulate, 8 forward NTT, 9 inverse NTT, 10 rescale.  shelfi_profile_get waits for recorded launches. */
 int shelfi_profile_enable(shelfi_ckks *h, int on);
 int shelfi_profile_reset(shelfi_ckks *h);
 int shelfi_profile_get(shelfi_ckks *h, int kernel, double *ms_total, uint64_t *launches);

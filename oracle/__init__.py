@@ -61,6 +61,10 @@ def lib():
         "orc_modulus_chain": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
         "orc_decrypt_ct_words": (C.c_int, [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]),
         "orc_ct_mul_plain_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]),
+        "orc_rescale_constants": (None, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+        "orc_rescale_ct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
+        "orc_decrypt_ct_level": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_double, C.c_void_p, C.c_void_p]),
+        "orc_rescale_blob": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), u64p]),
         "orc_last_error": (C.c_char_p, [C.c_void_p]),
         "orc_ring_dim": (C.c_uint32, [C.c_void_p]),
         "orc_num_limbs": (C.c_uint32, [C.c_void_p]),
@@ -279,6 +283,41 @@ class Oracle:
             raise RuntimeError(f"ct_mul_plain_accumulate failed ({rc})")
         return acc
 
+    # --- rescale-before-transport: PALISADE ModReduce under EXACTRESCALE ---
+    def rescale_constants(self, limbs_in=None):
+        """(QlQlInvModqlDivqlModq[i], qlInvModq[i]) for i < limbs_in - 1."""
+        lin = self.num_limbs if limbs_in is None else limbs_in
+        t, qi = np.zeros(8, np.uint64), np.zeros(8, np.uint64)
+        lib().orc_rescale_constants(self._h, lin, t.ctypes.data, qi.ctypes.data)
+        return [int(v) for v in t[:lin - 1]], [int(v) for v in qi[:lin - 1]]
+
+    def rescale_ct(self, ct):
+        """[2][Lin][N] -> [2][Lin-1][N]"""
+        ct = _u64(ct)
+        lin = ct.shape[-2]
+        out = np.empty((2, lin - 1, self.ring_dim), np.uint64)
+        rc = lib().orc_rescale_ct(self._h, ct.ctypes.data, lin, out.ctypes.data)
+        if rc:
+            raise RuntimeError(f"rescale_ct failed ({rc})")
+        return out
+
+    def decrypt_ct_level(self, ct, sf):
+        """Decrypt+Decode of a ciphertext [2][limbs][N] with limbs <= L: (doubles, centred CRT words)."""
+        ct = _u64(ct)
+        out = np.empty(self.slots, np.float64)
+        words = np.empty((self.ring_dim, 8), np.uint64)
+        rc = lib().orc_decrypt_ct_level(self._h, ct.ctypes.data, ct.shape[-2], sf, out.ctypes.data, words.ctypes.data)
+        if rc:
+            raise RuntimeError(f"decrypt_ct_level failed ({rc})")
+        return out, words
+
+    def rescale(self, blob: bytes) -> bytes:
+        out, n = C.c_void_p(), C.c_uint64()
+        rc = lib().orc_rescale_blob(self._h, blob, len(blob), C.byref(out), C.byref(n))
+        if rc:
+            raise RuntimeError(f"oracle rescale failed ({rc}): {self.last_error()}")
+        return _take(out, n.value)
+
     def weight_constant(self, w: float) -> int:
         return lib().orc_weight_constant(self._h, w)
 
@@ -287,7 +326,7 @@ class Oracle:
 
     def blob_build(self, payload, depth=1, level=0, sf=None) -> bytes:
         payload = _u64(payload)
-        words = 2 * self.num_limbs * self.ring_dim
+        words = 2 * (self.num_limbs - level) * self.ring_dim
         n_ct = payload.size // words
         out, n = C.c_void_p(), C.c_uint64()
         lib().orc_blob_build(self._h, n_ct, payload.ctypes.data, depth, level,

@@ -577,11 +577,12 @@ static void crt_centered(const crt_plan *p, const uint64_t *a, int *neg, big_t *
 /* [PAL] LPAlgorithmCKKS::Decrypt + DCRTPoly::CRTInterpolate + CKKSPackedEncoding::Decode (noise
  * flooding of PALISADE >= 1.10.6 left out: it is random, ~2^-40 relative, far below the 1e-6 tier).
  * words (optional): N x 8 little-endian words, two's complement of the centred integer. */
-static int decrypt_ct_impl(const orc_ctx *c, const uint64_t *ct, double sf, double *out, int64_t *coeff_hi,
+static int decrypt_ct_impl(const orc_ctx *c, const uint64_t *ct, int L, double sf, double *out, int64_t *coeff_hi,
                            uint64_t *coeff_lo, uint64_t *words) {
-    if (!c->have_cc || !c->have_sk) return -1;
+    if (!c->have_cc || !c->have_sk || L < 1 || L > c->wp.L) return -1;
     uint32_t N = c->wp.N, Nh = N / 2, slots = c->wp.batch;
-    int L = c->wp.L;
+    /* L = towers of this ciphertext: the first L towers of the secret key and of the chain ([PAL] Decrypt drops the
+     * key's extra towers to match a rescaled ciphertext) */
     uint32_t gap = Nh / slots;
     uint64_t *t = malloc((size_t)L * N * 8);
     for (int l = 0; l < L; l++) {
@@ -623,10 +624,77 @@ static int decrypt_ct_impl(const orc_ctx *c, const uint64_t *ct, double sf, doub
     return 0;
 }
 int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out, int64_t *coeff_hi, uint64_t *coeff_lo) {
-    return decrypt_ct_impl(c, ct, sf, out, coeff_hi, coeff_lo, NULL);
+    return decrypt_ct_impl(c, ct, c->wp.L, sf, out, coeff_hi, coeff_lo, NULL);
 }
 int orc_decrypt_ct_words(const orc_ctx *c, const uint64_t *ct, double sf, double *out, uint64_t *words) {
-    return decrypt_ct_impl(c, ct, sf, out, NULL, NULL, words);
+    return decrypt_ct_impl(c, ct, c->wp.L, sf, out, NULL, NULL, words);
+}
+int orc_decrypt_ct_level(const orc_ctx *c, const uint64_t *ct, uint32_t limbs, double sf, double *out, uint64_t *words) {
+    return decrypt_ct_impl(c, ct, (int)limbs, sf, out, NULL, NULL, words);
+}
+
+/* [PAL] NativeVector::SwitchModulus for one value: the centred representative of n (mod q_old) reduced mod q_new.
+ * Written with PALISADE's two branches (larger / smaller new modulus). */
+static inline uint64_t switch_modulus(uint64_t n, uint64_t q_old, uint64_t q_new) {
+    uint64_t half = q_old >> 1;
+    if (q_new > q_old) return n > half ? n + (q_new - q_old) : n;
+    uint64_t diff = (q_old - q_new) % q_new, a = n % q_new;
+    return n > half ? submod(a, diff, q_new) : a;
+}
+/* big = big / d, returns the remainder */
+static uint64_t big_divmod_u64(big_t *x, uint64_t d) {
+    u128 rem = 0;
+    for (int i = ORC_CRT_WORDS - 1; i >= 0; i--) {
+        u128 cur = (rem << 64) | x->w[i];
+        x->w[i] = (uint64_t)(cur / d);
+        rem = cur % d;
+    }
+    return (uint64_t)rem;
+}
+/* [PAL] the two per-tower constants of DropLastElementAndScale for a polynomial of Lin towers (l = Lin - 1):
+ *   QlQlInvModqlDivqlModq[i] = ((Q_l/q_l) * ((Q_l/q_l)^-1 mod q_l)) / q_l  mod q_i,   qlInvModq[i] = q_l^-1 mod q_i */
+void orc_rescale_constants(const orc_ctx *c, uint32_t Lin, uint64_t *t, uint64_t *ql_inv) {
+    const uint64_t *q = c->wp.q;
+    int l = (int)Lin - 1;
+    uint64_t p_mod_ql = 1;
+    for (int j = 0; j < l; j++) p_mod_ql = mulmod(p_mod_ql, q[j] % q[l], q[l]);
+    uint64_t p_inv = invmod(p_mod_ql, q[l]);
+    big_t x; memset(&x, 0, sizeof x);
+    x.w[0] = 1;
+    for (int j = 0; j < l; j++) big_mul_add(&x, q[j], 0);
+    big_mul_add(&x, p_inv, 0);
+    big_divmod_u64(&x, q[l]); /* floor */
+    for (int i = 0; i < l; i++) {
+        big_t y = x;
+        t[i] = big_divmod_u64(&y, q[i]);
+        ql_inv[i] = invmod(q[l] % q[i], q[i]);
+    }
+}
+/* [PAL] ModReduce under EXACTRESCALE = DCRTPoly::DropLastElementAndScale on both polynomials:
+ * in [2][Lin][N] -> out [2][Lin-1][N], EVALUATION form throughout.  The last tower goes to coefficient form, is
+ * switched into every remaining modulus, multiplied by its constant, transformed back, and added to the tower scaled
+ * by q_l^-1 — i.e. (c - [c]_{q_l}) / q_l with the centred remainder. */
+int orc_rescale_ct(const orc_ctx *c, const uint64_t *in, uint32_t Lin, uint64_t *out) {
+    if (!c->have_cc || Lin < 2 || (int)Lin > c->wp.L) return -1;
+    uint32_t N = c->wp.N;
+    int l = (int)Lin - 1;
+    uint64_t t[ORC_MAX_LIMBS], qi[ORC_MAX_LIMBS];
+    orc_rescale_constants(c, Lin, t, qi);
+    uint64_t *last = malloc((size_t)N * 8), *tmp = malloc((size_t)N * 8);
+    for (int p = 0; p < 2; p++) {
+        memcpy(last, in + ((size_t)p * Lin + l) * N, (size_t)N * 8);
+        orc_ntt_inverse(c, l, last);
+        for (int i = 0; i < l; i++) {
+            uint64_t q = c->wp.q[i];
+            for (uint32_t j = 0; j < N; j++) tmp[j] = mulmod(switch_modulus(last[j], c->wp.q[l], q), t[i], q);
+            orc_ntt_forward(c, i, tmp);
+            const uint64_t *src = in + ((size_t)p * Lin + i) * N;
+            uint64_t *dst = out + ((size_t)p * l + i) * N;
+            for (uint32_t j = 0; j < N; j++) dst[j] = addmod(mulmod(src[j], qi[i], q), tmp[j], q);
+        }
+    }
+    free(last); free(tmp);
+    return 0;
 }
 
 /* [PAL] EvalMult(ct, pt) with pt = MakeCKKSPackedPlaintext(w) (fresh: depth 1, level 0, scale Delta), then EvalAdd:
@@ -853,11 +921,20 @@ static void wr_context(wr_t *w, const wire_params *p, wire_ids *ids, int full) {
     wr_u64(w, 4); wr_raw(w, "CKKS", 4);
 }
 
-/* DCRTPoly := [VER] u64 L Tower*L u32 format SAME REF(dcrt) ; data goes to dst[l*N..] */
-static void rd_dcrtpoly(rd_t *r, const wire_params *p, const wire_ids *ids, uint64_t *dst, uint32_t *format) {
+static void bigint_from_product(const uint64_t *q, int L, uint32_t words[110], uint16_t *msb);
+
+/* DCRTPoly := [VER] u64 Lc Tower*Lc u32 format SAME (REF(dcrt) | reduced parameters) ; data goes to dst[l*N..]
+ * Lc = the context's tower count for a level-0 ciphertext.  After a rescale, [PAL] DCRTPolyImpl::DropLastElement gives
+ * the polynomial a parameter object of its own (a copy of the context's ILDCRTParams with the last tower popped and the
+ * modulus divided by it); cereal then writes that object in line — NEW(id), the ElemParams fields, and the towers as
+ * back references to the ILNativeParams the context already carried.  No fixture pins this form ("parity unpinned"). */
+static void rd_dcrtpoly(rd_t *r, const wire_params *p, const wire_ids *ids, uint32_t *next_id, int *ct_limbs,
+                        uint64_t *dst, uint32_t *format) {
     rd_ver(r, V_DCRTPOLY);
-    if (rd_u64(r) != (uint64_t)p->L) { r->err = 20; return; }
-    for (int l = 0; l < p->L && !r->err; l++) {
+    uint64_t Lc = rd_u64(r);
+    if (Lc < 1 || Lc > (uint64_t)p->L || (*ct_limbs && Lc != (uint64_t)*ct_limbs)) { r->err = 20; return; }
+    *ct_limbs = (int)Lc;
+    for (int l = 0; l < (int)Lc && !r->err; l++) {
         rd_ver(r, V_NATPOLY);
         rd_expect32(r, W_SAME);
         if (rd_u8(r) != 1) r->err = 21;
@@ -875,12 +952,29 @@ static void rd_dcrtpoly(rd_t *r, const wire_params *p, const wire_ids *ids, uint
     uint32_t f = rd_u32(r);
     if (format) *format = f;
     rd_expect32(r, W_SAME);
-    if (rd_u32(r) != ids->dcrt) r->err = 25;
+    uint32_t id = rd_u32(r);
+    if ((int)Lc == p->L) { if (id != ids->dcrt) r->err = 25; return; }
+    if (id != (W_NEW | *next_id)) { r->err = 26; return; }
+    (*next_id)++;
+    rd_ver(r, V_DCRTP); rd_ver(r, V_EPBIG);
+    if (rd_u32(r) != p->M || rd_u32(r) != p->N || rd_u8(r) != 1) r->err = 27;
+    rd_ver(r, V_BIGINT);
+    uint32_t want[110], got[110]; uint16_t want_msb, got_msb;
+    bigint_from_product(p->q, (int)Lc, want, &want_msb);
+    rd_bigint(r, got, &got_msb);
+    if (memcmp(want, got, sizeof want) || want_msb != got_msb) r->err = 28;
+    rd_bigint_zero(r); rd_bigint_zero(r); rd_bigint_zero(r);
+    if (rd_u64(r) != Lc) r->err = 29;
+    for (int l = 0; l < (int)Lc && !r->err; l++) {
+        rd_expect32(r, W_SAME);
+        if (rd_u32(r) != ids->native[l]) r->err = 29;
+    }
+    rd_bigint_zero(r);
 }
-static void wr_dcrtpoly(wr_t *w, const wire_params *p, const wire_ids *ids, const uint64_t *src, uint32_t format) {
+static void wr_dcrtpoly(wr_t *w, const wire_params *p, const wire_ids *ids, int Lc, const uint64_t *src, uint32_t format) {
     wr_ver(w, V_DCRTPOLY);
-    wr_u64(w, (uint64_t)p->L);
-    for (int l = 0; l < p->L; l++) {
+    wr_u64(w, (uint64_t)Lc);
+    for (int l = 0; l < Lc; l++) {
         wr_ver(w, V_NATPOLY);
         wr_u32(w, W_SAME); wr_u8(w, 1);
         wr_ver(w, V_NATVEC);
@@ -890,10 +984,22 @@ static void wr_dcrtpoly(wr_t *w, const wire_params *p, const wire_ids *ids, cons
         wr_u32(w, W_SAME); wr_u32(w, ids->native[l]);
     }
     wr_u32(w, format);
-    wr_u32(w, W_SAME); wr_u32(w, ids->dcrt);
+    wr_u32(w, W_SAME);
+    if (Lc == p->L) { wr_u32(w, ids->dcrt); return; }
+    wr_new(w);
+    wr_ver(w, V_DCRTP); wr_ver(w, V_EPBIG);
+    wr_u32(w, p->M); wr_u32(w, p->N); wr_u8(w, 1);
+    wr_ver(w, V_BIGINT);
+    uint32_t big[110]; uint16_t msb;
+    bigint_from_product(p->q, Lc, big, &msb);
+    wr_bigint(w, big, msb);
+    wr_bigint_zero(w); wr_bigint_zero(w); wr_bigint_zero(w);
+    wr_u64(w, (uint64_t)Lc);
+    for (int l = 0; l < Lc; l++) { wr_u32(w, W_SAME); wr_u32(w, ids->native[l]); }
+    wr_bigint_zero(w);
 }
 
-typedef struct { uint64_t depth, level; double sf; uint32_t enc; char tag[33]; } ct_meta;
+typedef struct { uint64_t depth, level; double sf; uint32_t enc; char tag[33]; int limbs; } ct_meta;
 
 /* Ciphertext := SAME NEW(id) [VER VER] CryptoContext u64 32 tag u64 2 DCRTPoly DCRTPoly depth level sf enc NEW(id) u64 0 */
 static void rd_ciphertext(rd_t *r, wire_params *p, wire_ids *ids, uint32_t *next_id, uint64_t *dst, ct_meta *m,
@@ -916,7 +1022,8 @@ static void rd_ciphertext(rd_t *r, wire_params *p, wire_ids *ids, uint32_t *next
             *first_data_off = probe.p;
         }
         uint32_t fmt = 0;
-        rd_dcrtpoly(r, p, ids, dst ? dst + (size_t)k * p->L * p->N : NULL, &fmt);
+        if (k == 0) m->limbs = 0;
+        rd_dcrtpoly(r, p, ids, next_id, &m->limbs, dst ? dst + (size_t)k * m->limbs * p->N : NULL, &fmt);
         if (fmt != 0) r->err = 33; /* EVALUATION */
     }
     m->depth = rd_u64(r); m->level = rd_u64(r); m->sf = rd_f64(r); m->enc = rd_u32(r);
@@ -931,14 +1038,16 @@ static void wr_ciphertext(wr_t *w, const wire_params *p, wire_ids *ids, int full
     wr_context(w, p, ids, full_ctx);
     wr_u64(w, 32); wr_raw(w, m->tag, 32);
     wr_u64(w, 2);
-    wr_dcrtpoly(w, p, ids, src, 0);
-    wr_dcrtpoly(w, p, ids, src + (size_t)p->L * p->N, 0);
+    int Lc = m->limbs ? m->limbs : p->L;
+    wr_dcrtpoly(w, p, ids, Lc, src, 0);
+    wr_dcrtpoly(w, p, ids, Lc, src + (size_t)Lc * p->N, 0);
     wr_u64(w, m->depth); wr_u64(w, m->level); wr_f64(w, m->sf); wr_u32(w, m->enc);
     wr_new(w); wr_u64(w, 0);
 }
 
 /* parsed vector<Ciphertext> */
-typedef struct { wire_params p; uint64_t n_ct; uint64_t *data; ct_meta *meta; uint64_t first_off, stride; } ct_vec;
+/* cL = towers per ciphertext polynomial: p.L at level 0, fewer after a rescale */
+typedef struct { wire_params p; uint64_t n_ct; uint64_t *data; ct_meta *meta; uint64_t first_off, stride; int cL; } ct_vec;
 static void ct_vec_free(ct_vec *v) { free(v->data); free(v->meta); v->data = NULL; v->meta = NULL; }
 
 static int parse_ct_blob(const uint8_t *blob, uint64_t len, int single, ct_vec *out, int want_data) {
@@ -960,11 +1069,12 @@ static int parse_ct_blob(const uint8_t *blob, uint64_t len, int single, ct_vec *
             rd_t probe = r; wire_ids pid = ids; uint32_t pn = next_id; ct_meta pm;
             rd_ciphertext(&probe, &out->p, &pid, &pn, NULL, &pm, &out->first_off);
             if (probe.err) { ct_vec_free(out); return -3; }
-            ct_words = (size_t)2 * out->p.L * out->p.N;
+            out->cL = pm.limbs;
+            ct_words = (size_t)2 * out->cL * out->p.N;
             if (want_data) out->data = malloc(n_ct * ct_words * 8);
         }
         rd_ciphertext(&r, &out->p, &ids, &next_id, want_data ? out->data + j * ct_words : NULL, &out->meta[j], NULL);
-        if (r.err) { ct_vec_free(out); return -4; }
+        if (r.err || out->meta[j].limbs != out->cL) { ct_vec_free(out); return -4; }
         if (j == 1) start1 = start;
         if (j == 2) out->stride = start - start1;
     }
@@ -979,7 +1089,7 @@ static void emit_ct_blob(wr_t *w, const wire_params *p, uint64_t n_ct, const uin
     wr_u8(w, 1);
     if (!single) wr_u64(w, n_ct);
     wire_ids ids; memset(&ids, 0, sizeof ids);
-    size_t ct_words = (size_t)2 * p->L * p->N;
+    size_t ct_words = (size_t)2 * (meta[0].limbs ? meta[0].limbs : p->L) * p->N;
     for (uint64_t j = 0; j < n_ct; j++) wr_ciphertext(w, p, &ids, j == 0, data + j * ct_words, &meta[same_meta ? 0 : j]);
 }
 
@@ -987,13 +1097,13 @@ int orc_blob_parse(const uint8_t *blob, uint64_t len, int single, orc_blob_info 
     ct_vec v;
     int rc = parse_ct_blob(blob, len, single, &v, payload != NULL);
     if (rc) return rc;
-    size_t words = (size_t)v.n_ct * 2 * v.p.L * v.p.N;
+    size_t words = (size_t)v.n_ct * 2 * v.cL * v.p.N;
     if (payload) {
         if (cap < words) { ct_vec_free(&v); return -6; }
         memcpy(payload, v.data, words * 8);
     }
     if (info) {
-        info->n_ct = v.n_ct; info->n_polys = 2; info->n_limbs = (uint32_t)v.p.L; info->ring_dim = v.p.N;
+        info->n_ct = v.n_ct; info->n_polys = 2; info->n_limbs = (uint32_t)v.cL; info->ring_dim = v.p.N;
         info->depth = v.meta[0].depth; info->level = v.meta[0].level; info->scaling_factor = v.meta[0].sf;
         info->encoding_type = v.meta[0].enc;
         memcpy(info->key_tag, v.meta[0].tag, 33);
@@ -1037,7 +1147,8 @@ static int parse_key_file(const uint8_t *in, uint64_t len, int kind, wire_params
     *polys = malloc(np * words * 8);
     for (int k = 0; k < np; k++) {
         uint32_t fmt = 0;
-        rd_dcrtpoly(&r, p, &ids, *polys + k * words, &fmt);
+        int key_limbs = p->L; /* keys always carry the full chain */
+        rd_dcrtpoly(&r, p, &ids, &next_id, &key_limbs, *polys + k * words, &fmt);
         if (fmt != 0) r.err = 40;
     }
     if (r.err || r.p != len) { free(*polys); *polys = NULL; return -7; }
@@ -1054,8 +1165,8 @@ static void emit_key_file(wr_t *w, int kind, const wire_params *p, const char ta
     wr_context(w, p, &ids, 1);
     wr_u64(w, 32); wr_raw(w, tag, 32);
     size_t words = (size_t)p->L * p->N;
-    if (kind == 1) { wr_u64(w, 2); wr_dcrtpoly(w, p, &ids, polys, 0); wr_dcrtpoly(w, p, &ids, polys + words, 0); }
-    else wr_dcrtpoly(w, p, &ids, polys, 0);
+    if (kind == 1) { wr_u64(w, 2); wr_dcrtpoly(w, p, &ids, p->L, polys, 0); wr_dcrtpoly(w, p, &ids, p->L, polys + words, 0); }
+    else wr_dcrtpoly(w, p, &ids, p->L, polys, 0);
 }
 int orc_file_reemit(const uint8_t *in, uint64_t len, int kind, uint8_t **out, uint64_t *out_len) {
     wire_params p; char tag[33] = {0}; uint64_t *polys = NULL;
@@ -1136,6 +1247,7 @@ uint64_t orc_num_ciphertexts(const orc_ctx *c, uint64_t n) { return (n + c->batc
 
 static void default_meta(const orc_ctx *c, ct_meta *m, uint64_t depth, uint64_t level, double sf) {
     m->depth = depth; m->level = level; m->sf = sf; m->enc = 4; /* CKKSPacked */
+    m->limbs = c->wp.L - (int)level; /* EXACTRESCALE: one tower dropped per level */
     memcpy(m->tag, c->key_tag, 33);
 }
 int orc_blob_build(const orc_ctx *c, uint64_t n_ct, const uint64_t *payload, uint64_t depth, uint64_t level, double sf,
@@ -1189,7 +1301,7 @@ int orc_weighted_average(orc_ctx *c, const uint8_t *const *blobs, const uint64_t
             ct_vec_free(&acc); return -3;
         }
         if (v.p.N != c->wp.N || v.p.L != c->wp.L || memcmp(v.p.q, c->wp.q, sizeof(uint64_t) * v.p.L) ||
-            (i > 0 && v.n_ct != acc.n_ct)) {
+            v.cL != v.p.L || (i > 0 && v.n_ct != acc.n_ct)) {
             snprintf(c->err, sizeof c->err, "learner %u: ciphertext parameters differ", i);
             ct_vec_free(&v); ct_vec_free(&acc); return -4;
         }
@@ -1238,17 +1350,46 @@ int orc_decrypt(orc_ctx *c, const uint8_t *blob, uint64_t len, uint64_t n, doubl
     if (n > v.n_ct * batch || n + batch <= v.n_ct * batch || batch > slots) {
         ct_vec_free(&v); snprintf(c->err, sizeof c->err, "data_dimensions inconsistent with blob"); return -5;
     }
-    size_t words = (size_t)2 * v.p.L * v.p.N;
+    size_t words = (size_t)2 * v.cL * v.p.N;
     int bad = 0;
 #pragma omp parallel for schedule(dynamic) /* ckks.cpp:186 */
     for (uint64_t i = 0; i < v.n_ct; i++) {
         double *tmp = malloc(slots * sizeof(double));
-        if (orc_decrypt_ct(c, v.data + i * words, v.meta[i].sf, tmp, NULL, NULL)) bad = 1;
+        if (decrypt_ct_impl(c, v.data + i * words, v.cL, v.meta[i].sf, tmp, NULL, NULL, NULL)) bad = 1;
         uint64_t length = (i == v.n_ct - 1) ? n - i * batch : batch; /* ckks.cpp:192-196 */
         memcpy(out + i * batch, tmp, length * sizeof(double));        /* ckks.cpp:200-204 (64-bit index) */
         free(tmp);
     }
     ct_vec_free(&v);
+    return bad ? -6 : 0;
+}
+
+/* Rescale-before-transport (not something ckks.cpp does — it leaves the average at depth 2):
+ * [PAL] cc->ModReduce on every ciphertext of a blob.  depth - 1, level + 1, scalingFactor / q_l (in double). */
+int orc_rescale_blob(orc_ctx *c, const uint8_t *blob, uint64_t len, uint8_t **out, uint64_t *out_len) {
+    if (!c->have_cc) { snprintf(c->err, sizeof c->err, "crypto params not loaded"); return -1; }
+    ct_vec v;
+    if (parse_ct_blob(blob, len, 0, &v, 1)) { snprintf(c->err, sizeof c->err, "malformed ciphertext blob"); return -3; }
+    if (v.p.N != c->wp.N || v.p.L != c->wp.L || memcmp(v.p.q, c->wp.q, sizeof(uint64_t) * v.p.L) || v.cL < 2) {
+        ct_vec_free(&v); snprintf(c->err, sizeof c->err, "ciphertext parameters differ or no tower left to drop"); return -4;
+    }
+    int Lin = v.cL;
+    size_t win = (size_t)2 * Lin * v.p.N, wout = (size_t)2 * (Lin - 1) * v.p.N;
+    uint64_t *data = malloc(v.n_ct * wout * 8);
+    int bad = 0;
+#pragma omp parallel for schedule(dynamic)
+    for (uint64_t j = 0; j < v.n_ct; j++) {
+        if (orc_rescale_ct(c, v.data + j * win, (uint32_t)Lin, data + j * wout)) bad = 1;
+        v.meta[j].depth -= 1; v.meta[j].level += 1;
+        v.meta[j].sf /= (double)c->wp.q[Lin - 1];
+        v.meta[j].limbs = Lin - 1;
+    }
+    if (!bad) {
+        wr_t wr;
+        emit_ct_blob(&wr, &v.p, v.n_ct, data, v.meta, 0, 0);
+        *out = wr.b; *out_len = wr.n;
+    }
+    free(data); ct_vec_free(&v);
     return bad ? -6 : 0;
 }
 

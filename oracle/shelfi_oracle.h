@@ -98,6 +98,15 @@ int orc_decrypt_ct(const orc_ctx *c, const uint64_t *ct, double sf, double *out,
 int orc_decrypt_ct_words(const orc_ctx *c, const uint64_t *ct, double sf, double *out, uint64_t *words);
 /* acc (+)= ct (*) NTT(Encode(w)): EvalMult(ct, plaintext vector) + EvalAdd, one ciphertext [2][L][N] */
 int orc_ct_mul_plain_accumulate(const orc_ctx *c, const uint64_t *ct, const double *w, uint32_t n, int first, uint64_t *acc);
+/* ---- rescale-before-transport: PALISADE ModReduce under EXACTRESCALE ---- */
+/* the per-tower constants of DCRTPoly::DropLastElementAndScale for a polynomial of Lin towers */
+void orc_rescale_constants(const orc_ctx *c, uint32_t Lin, uint64_t *t, uint64_t *ql_inv);
+/* one ciphertext [2][Lin][N] -> [2][Lin-1][N] */
+int orc_rescale_ct(const orc_ctx *c, const uint64_t *in, uint32_t Lin, uint64_t *out);
+/* Decrypt+Decode of a ciphertext that kept only its first `limbs` towers ([2][limbs][N]); words as above */
+int orc_decrypt_ct_level(const orc_ctx *c, const uint64_t *ct, uint32_t limbs, double sf, double *out, uint64_t *words);
+/* every ciphertext of a blob rescaled by one level; metadata: depth - 1, level + 1, scalingFactor / q_l */
+int orc_rescale_blob(orc_ctx *c, const uint8_t *blob, uint64_t len, uint8_t **out, uint64_t *out_len);
 /* EvalMult(ct,(float)w) constant: (int64)((double)w * sf0 + 0.5)   (ckks.cpp:287-288) */
 int64_t orc_weight_constant(const orc_ctx *c, float w);
 

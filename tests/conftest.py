@@ -76,6 +76,8 @@ class Emu:
                                        C.c_size_t]),
             "emu_wire_rebuild": (vp, [C.c_char_p, u64, C.POINTER(u64), C.c_char_p, C.c_size_t]),
             "emu_wire_blob_size": (u64, [C.c_char_p, u64, u64]),
+            "emu_wire_blob_size_level": (u64, [C.c_char_p, u64, u64, u32]),
+            "emu_rescale": (None, [vp, vp, vp]),
             "emu_free": (None, [vp]),
             "emu_first_prime": (u64, [u32, u32]),
             "emu_previous_prime": (u64, [u64, u32]),

@@ -149,6 +149,44 @@ void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
     if (d == 2) replay_tail<2>(lc, row);
 }
 
+// rescale_intt_kernel<D> (+ intt_tail_kernel<D>) then rescale_ntt_kernel<D>: one ciphertext [2][L][N] -> [2][L-1][N]
+void emu_rescale(const Emu *e, const uint64_t *ct, uint64_t *out) {
+    const u32 L = e->rc.limbs, d = e->rc.log_blocks;
+    const size_t n = e->rc.n;
+    RescaleConst rs{};
+    rs.q_last = e->rc.limb[L - 1].q;
+    for (u32 i = 0; i + 1 < L; i++) {
+        const u64 q = e->rc.limb[i].q;
+        rs.inv[i] = nt::inv_mod(rs.q_last % q, q);
+        rs.inv_s[i] = nt::shoup(rs.inv[i], q);
+    }
+    std::vector<u64> sm(kN), t(n);
+    for (u32 p = 0; p < 2; p++) {
+        const LimbConst last = e->rc.limb[L - 1];
+        for (u32 blk = 0; blk < (1u << d); blk++) {
+            const size_t off = (size_t)blk * kN;
+            EMU_D(d, replay_inverse<D>(sm.data(), last, head_bits(d, blk), LoadPairGlobal{ct + (p * L + (L - 1)) * n + off},
+                                       t.data() + off))
+        }
+        if (d == 1) replay_tail<1>(last, t.data());
+        if (d == 2) replay_tail<2>(last, t.data());
+        for (u32 i = 0; i + 1 < L; i++) {
+            const LimbConst lc = e->rc.limb[i];
+            for (u32 blk = 0; blk < (1u << d); blk++) {
+                const size_t off = (size_t)blk * kN;
+                const StoreRescale st{ct + (p * L + i) * n + off, out + (p * (L - 1) + i) * n + off, &lc, rs.inv[i], rs.inv_s[i]};
+                if (lc.dtw) {
+                    EMU_D(d, replay_forward_d(sm.data(), lc, head_bits(d, blk),
+                                              DHeadLoad<D, DLoadSwitch>{DLoadSwitch{t.data(), rs.q_last, &lc}, &lc, blk}, st))
+                } else {
+                    EMU_D(d, replay_forward(sm.data(), lc, head_bits(d, blk),
+                                            HeadLoad<D, LoadSwitch>{LoadSwitch{t.data(), rs.q_last, &lc}, &lc, blk}, st))
+                }
+            }
+        }
+    }
+}
+
 // selective encryption: when set, chunk element i is x[sel[i]] on encode and out[sel[i]] on decode
 static const u32 *g_sel = nullptr;
 void emu_set_selection(const uint32_t *sel) { g_sel = sel; }
@@ -415,7 +453,7 @@ int emu_wire_map(const uint8_t *in, uint64_t len, int single, uint64_t *n_ct, ui
     wire::BlobMap m;
     std::string e = wire::map_ciphertext_blob(in, len, single != 0, &m);
     if (!e.empty()) { std::snprintf(err, err_cap, "%s", e.c_str()); return -1; }
-    *n_ct = m.n_ct; *limbs = m.ctx.limbs; *stride = m.stride;
+    *n_ct = m.n_ct; *limbs = m.ct_limbs; *stride = m.stride;
     std::memcpy(run0, m.run0, sizeof m.run0);
     std::memcpy(run1, m.run1, sizeof m.run1);
     *depth = m.meta[0].depth; *level = m.meta[0].level; *sf = m.meta[0].scaling_factor;
@@ -427,7 +465,7 @@ uint8_t *emu_wire_rebuild(const uint8_t *in, uint64_t len, uint64_t *out_len, ch
     wire::BlobMap m;
     std::string e = wire::map_ciphertext_blob(in, len, false, &m);
     if (!e.empty()) { std::snprintf(err, err_cap, "%s", e.c_str()); return nullptr; }
-    const uint32_t runs = 2 * m.ctx.limbs;
+    const uint32_t runs = 2 * m.ct_limbs;   // fewer than the context's towers after a rescale
     const uint32_t n = m.ctx.ring_dim;
     std::vector<uint64_t> image((len + 7) / 8 + 1, 0), dense(m.n_ct * runs * (size_t)n);
     std::memcpy(image.data(), in, len);
@@ -445,6 +483,11 @@ uint64_t emu_wire_blob_size(const uint8_t *ctx_file, uint64_t len, uint64_t n_ct
     wire::ContextParams p;
     if (!wire::parse_context(ctx_file, len, &p).empty()) return 0;
     return wire::ciphertext_blob_size(p, n_ct);
+}
+uint64_t emu_wire_blob_size_level(const uint8_t *ctx_file, uint64_t len, uint64_t n_ct, uint32_t limbs) {
+    wire::ContextParams p;
+    if (!wire::parse_context(ctx_file, len, &p).empty()) return 0;
+    return wire::ciphertext_blob_size(p, n_ct, limbs);
 }
 void emu_free(void *p) { std::free(p); }
 
