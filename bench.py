@@ -452,6 +452,7 @@ def run_ours(args):
 
     # optional reassembly of the decoded model: ONE all-gather over NVLink, outside the timed step
     gather_ms = None
+    peer_gather = None
     if world > 1:
         full = torch.empty(world * P_MODEL, dtype=torch.float64, device="cuda")
         dist.all_gather_into_tensor(full, d_out)
@@ -462,6 +463,41 @@ def run_ours(args):
         g1.record(stream)
         barrier()
         gather_ms = g0.elapsed_time(g1)
+        # the same reassembly folded into the decode kernel (stores to peer-mapped buffers over NVLink + one barrier),
+        # against decrypt followed by the NCCL all-gather; both timed on the launching stream, max over ranks below
+        try:
+            from SHELFI_FHE.sharding import PeerGather
+            pg = PeerGather(h, world * n_ct * BATCH, BATCH)
+
+            def via_nccl():
+                ck(L.shelfi_decrypt_device(h.handle, C.c_void_p(d_avg.data_ptr()), n_ct, sf2, C.c_void_p(d_out.data_ptr()), P_MODEL, sp))
+                dist.all_gather_into_tensor(full, d_out)
+
+            def via_peers():
+                pg.decrypt(d_avg.data_ptr(), n_ct, sf2, stream.cuda_stream)
+                pg.barrier()
+
+            pair = []
+            for fn in (via_nccl, via_peers):
+                for _ in range(3):
+                    fn()
+                barrier()
+                g0.record(stream)
+                for _ in range(10):
+                    fn()
+                g1.record(stream)
+                barrier()
+                t = torch.tensor([g0.elapsed_time(g1) / 10], device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                pair.append(float(t.item()))
+            mine = pg.tensor()[rank * n_ct * BATCH: rank * n_ct * BATCH + P_MODEL]
+            peer = pg.tensor()[((rank + 1) % world) * n_ct * BATCH: ((rank + 1) % world) * n_ct * BATCH + P_MODEL]
+            ok = bool(torch.equal(mine, d_out)) and bool(torch.isfinite(peer).all()) and float(peer.abs().max()) > 0
+            peer_gather = {"decrypt_plus_nccl_all_gather_ms": pair[0], "decrypt_gather_plus_barrier_ms": pair[1],
+                           "own_slice_identical": ok}
+            pg.close()
+        except Exception as e:  # the IPC path must never cost the bench line
+            peer_gather = {"error": repr(e)[:200]}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -481,7 +517,7 @@ def run_ours(args):
                 "ntt": {"GBps": ntt_gbs, "frac_of_peak": ntt_gbs / peak, "rows": rows, "ms": ntt_ms,
                         "bytes_per_row": 16 * N_RING},
                 "value_reference_convention": ref_conv, "config1_pythonapi_example": config1, "kernels": prof,
-                "gather_ms": gather_ms,
+                "gather_ms": gather_ms, "peer_gather": peer_gather,
                 "rescale": rescale,
                 "parity": {"max_rel_err_vs_plaintext": rel, "host_path": rel_h}}
         emit(line)

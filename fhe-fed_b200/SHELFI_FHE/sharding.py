@@ -55,3 +55,79 @@ def gather_decoded(local, n_params: int, batch: int, group=None):
     out = torch.empty(world * block, dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(out, padded, group=group)
     return out[:n_params]
+
+
+class PeerGather:
+    """Decoded-model reassembly with no collective: every rank owns one device buffer of `world * block` float64 that
+    its peers map (CUDA IPC through the C ABI), and `decrypt` makes the decode kernel store this rank's slice into all
+    of them at the slice's offset (shelfi_decrypt_gather_device).  The stores ride NVLink while the kernel computes;
+    what remains of the all-gather is one barrier.  `torch.distributed` only carries the 64-byte handles and the barrier.
+
+        pg = PeerGather(ckks, n_params, batch)             # collective: every rank of `group` calls it
+        pg.decrypt(d_ct_ptr, n_ct, scaling_factor, stream)  # this rank's ciphertexts -> everybody's buffer
+        pg.barrier(); full = pg.tensor()[:n_params]         # contiguous decoded model on this GPU
+    """
+
+    def __init__(self, ckks, n_params: int, batch: int, group=None):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        from . import lib
+
+        self._C, self._lib, self._ckks, self._dist, self._group = C, lib(), ckks, dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.shard = shard_range(n_params, batch, self.rank, self.world)
+        self.n_params, self.block = n_params, self.shard.ct_per_rank * batch
+        self.values = self.world * self.block
+        own, handle = C.c_void_p(), C.create_string_buffer(64)
+        ckks._check(self._lib.shelfi_peer_buffer_create(ckks.handle, self.values * 8, C.byref(own), handle))
+        self._own = own.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        self._ptrs = []
+        for r, hb in enumerate(handles):
+            if r == self.rank:
+                self._ptrs.append(self._own)
+                continue
+            p = C.c_void_p()
+            ckks._check(self._lib.shelfi_peer_buffer_open(ckks.handle, hb, C.byref(p)))
+            self._ptrs.append(p.value)
+        # own copy first (shelfi_decrypt_gather_device's d_outs[0]), then the peers in rank order
+        order = [self.rank] + [r for r in range(self.world) if r != self.rank]
+        self._outs = (C.c_void_p * self.world)(*[self._ptrs[r] for r in order])
+
+    def decrypt(self, d_ct_ptr: int, n_ct: int, scaling_factor: float, stream: int = 0) -> None:
+        """Queue decrypt + scatter of this rank's `n_ct` ciphertexts on `stream`; returns at once."""
+        C, sh = self._C, self.shard
+        if n_ct != sh.ct_count:
+            raise ValueError(f"rank {self.rank}: {n_ct} ciphertexts, shard owns {sh.ct_count}")
+        if n_ct == 0:
+            return
+        self._ckks._check(self._lib.shelfi_decrypt_gather_device(
+            self._ckks.handle, C.c_void_p(d_ct_ptr), n_ct, scaling_factor, self._outs, self.world, sh.param_first,
+            sh.param_count, C.c_void_p(stream)))
+
+    def barrier(self) -> None:
+        """After this every rank's buffer holds every slice (the caller has synchronised its own stream)."""
+        self._dist.barrier(group=self._group)
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": (self.values,), "typestr": "<f8", "data": (self._own, False), "version": 3, "strides": None}
+
+    def tensor(self):
+        """This rank's buffer as a torch tensor (no copy); [:n_params] is the decoded model."""
+        import torch
+
+        return torch.as_tensor(self, device=f"cuda:{self._ckks.device}")
+
+    def close(self) -> None:
+        if self._own is None:
+            return
+        for r, p in enumerate(self._ptrs):
+            if r != self.rank:
+                self._lib.shelfi_peer_buffer_close(self._ckks.handle, self._C.c_void_p(p))
+        self._dist.barrier(group=self._group)      # nobody has the buffer mapped any more
+        self._lib.shelfi_peer_buffer_destroy(self._ckks.handle, self._C.c_void_p(self._own))
+        self._own = None

@@ -1047,10 +1047,16 @@ struct EncodeConst {
     const cplx *tw_fwd;                // ... of FFTSpecial
 };
 
+constexpr int kMaxPeerOuts = 7;   // further destinations of a decoded value: the other GPUs of one box
 struct DecodeConst {
     Crt2Const crt;
     double pre;     // scalingFactor^-1 * 2^p
     double pow_p;   // 2^-p
+    // decrypt-gather: every decoded value is also stored to peer[p][index] (peer-mapped memory of the other GPUs,
+    // already offset to this rank's slice), so the decoded slices are assembled on every GPU by the decode kernel's
+    // own stores over NVLink instead of by a collective that re-reads them.  Not combined with a selection list.
+    double *peer[kMaxPeerOuts];
+    u32 n_peer;
 };
 
 struct WavgArgs {
@@ -1179,9 +1185,18 @@ HD void decode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const
     }
 }
 // phases 1..log_slots: fft_fwd_stage(len = 2 << (p-1)); last phase: real parts * 2^-p
+// `first` = index of out[0] in the whole decoded vector (what the peer destinations are indexed by)
 HD void decode_store(int tid, int nthreads, const cplx *z, const DecodeConst &dc, double *out, u64 length,
-                     const u32 *sel = nullptr) {
-    for (u32 i = tid; i < length; i += nthreads) out[sel ? sel[i] : i] = fmul(z[zsw(i)].re, dc.pow_p);
+                     const u32 *sel = nullptr, u64 first = 0) {
+    if (dc.n_peer == 0) {
+        for (u32 i = tid; i < length; i += nthreads) out[sel ? sel[i] : i] = fmul(z[zsw(i)].re, dc.pow_p);
+        return;
+    }
+    for (u32 i = tid; i < length; i += nthreads) {
+        const double v = fmul(z[zsw(i)].re, dc.pow_p);
+        out[i] = v;
+        for (u32 p = 0; p < dc.n_peer; p++) dc.peer[p][first + i] = v;
+    }
 }
 
 // ---- slot counts above one FFT tile (4096 complex values, 64 KiB) and ring dimensions above one NTT tile ----
@@ -1297,7 +1312,7 @@ HD void decode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec,
 // the df outermost FFTSpecial stages on the 2^df values sharing tile-local index i, then real parts * 2^-p
 template <int DF>
 HD void decode_tail(u32 i, const cplx *zs, const EncodeConst &ec, const DecodeConst &dc, double *out, u64 length,
-                    const u32 *sel = nullptr) {
+                    const u32 *sel = nullptr, u64 first = 0) {
     const cplx *__restrict__ twf = ec.tw_fwd;
     cplx a[1 << DF];
 #pragma unroll
@@ -1313,7 +1328,11 @@ HD void decode_tail(u32 i, const cplx *zs, const EncodeConst &ec, const DecodeCo
 #pragma unroll
     for (int k = 0; k < (1 << DF); k++) {
         u64 slot = i + (u64)k * kFftFast;
-        if (slot < length) out[sel ? sel[slot] : slot] = fmul(a[k].re, dc.pow_p);
+        if (slot < length) {
+            const double v = fmul(a[k].re, dc.pow_p);
+            out[sel ? sel[slot] : slot] = v;
+            for (u32 p = 0; p < dc.n_peer; p++) dc.peer[p][first + slot] = v;
+        }
     }
 }
 

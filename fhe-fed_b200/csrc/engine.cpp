@@ -519,8 +519,10 @@ LevelView level_view(const shelfi_ckks *h, uint32_t limbs) {
 }
 
 // limbs = towers per polynomial of d_ct (0 = the context's chain, i.e. level 0)
+// peers[0..n_peer): further destinations of every decoded value (decrypt-gather), already offset to this rank's slice
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
-                  cudaStream_t s, const uint32_t *d_sel = nullptr, uint32_t limbs = 0) {
+                  cudaStream_t s, const uint32_t *d_sel = nullptr, uint32_t limbs = 0, double *const *peers = nullptr,
+                  uint32_t n_peer = 0) {
     const uint64_t N = h->ctx.ring_dim;
     const LevelView lv = level_view(h, limbs);
     CU(h->s_coeff.reserve(n_ct * lv.rc.limbs * N * sizeof(uint64_t)));
@@ -530,6 +532,8 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
     double p = (double)h->ctx.plaintext_modulus;
     dc.pre = std::pow(sf, -1) * std::pow(2, p);   // [PAL] Decode: scale to 2^p before the FFT, back after it
     dc.pow_p = std::pow(2, -p);
+    for (uint32_t i = 0; i < n_peer; i++) dc.peer[i] = peers[i];
+    dc.n_peer = n_peer;
     if (!general_decode(h, lv.rc.limbs)) {
         timed(h, kKDecode, s, [&] { launch_decode(lv.rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s, d_sel); });
     } else {
@@ -1413,6 +1417,71 @@ int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, d
         return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
     return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_out, n,
                          static_cast<cudaStream_t>(stream));
+}
+
+// Decrypt with the all-gather folded into the decode kernel's stores: value i goes to d_outs[p][offset + i] for every p.
+int shelfi_decrypt_gather_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor,
+                                 double *const *d_outs, uint32_t n_outs, uint64_t offset, uint64_t n, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!d_ct || !d_outs || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    if (n_outs == 0 || n_outs > (uint32_t)kMaxPeerOuts + 1)
+        return fail(h, SHELFI_ERR_ARG, "between 1 and " + std::to_string(kMaxPeerOuts + 1) + " destinations");
+    for (uint32_t i = 0; i < n_outs; i++)
+        if (!d_outs[i]) return fail(h, SHELFI_ERR_ARG, "null destination");
+    if (n == 0 || n > n_ct * h->batch || n + h->batch <= n_ct * h->batch)
+        return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
+    double *peers[kMaxPeerOuts] = {nullptr};
+    for (uint32_t i = 1; i < n_outs; i++) peers[i - 1] = d_outs[i] + offset;
+    return decrypt_dense(h, reinterpret_cast<const u64 *>(d_ct), n_ct, scaling_factor, d_outs[0] + offset, n,
+                         static_cast<cudaStream_t>(stream), nullptr, 0, peers, n_outs - 1);
+}
+
+// Buffers other processes of the box can map (CUDA IPC): the destinations of shelfi_decrypt_gather_device.
+int shelfi_peer_buffer_create(shelfi_ckks *h, uint64_t bytes, void **d_ptr, uint8_t handle[SHELFI_PEER_HANDLE_BYTES]) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (!d_ptr || !handle || bytes == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == SHELFI_PEER_HANDLE_BYTES, "handle size");
+    void *p = nullptr;
+    CU(cudaMalloc(&p, bytes));   // a whole allocation of its own: the handle maps from its first byte
+    cudaIpcMemHandle_t ipc;
+    cudaError_t e = cudaIpcGetMemHandle(&ipc, p);
+    if (e != cudaSuccess) { cudaFree(p); return cuda_fail(h, e, "cudaIpcGetMemHandle"); }
+    std::memcpy(handle, &ipc, sizeof ipc);
+    *d_ptr = p;
+    return 0;
+}
+int shelfi_peer_buffer_open(shelfi_ckks *h, const uint8_t handle[SHELFI_PEER_HANDLE_BYTES], void **d_ptr) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (!d_ptr || !handle) return fail(h, SHELFI_ERR_ARG, "null argument");
+    cudaIpcMemHandle_t ipc;
+    std::memcpy(&ipc, handle, sizeof ipc);
+    CU(cudaIpcOpenMemHandle(d_ptr, ipc, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+int shelfi_peer_buffer_close(shelfi_ckks *h, void *d_ptr) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (d_ptr) CU(cudaIpcCloseMemHandle(d_ptr));
+    return 0;
+}
+int shelfi_peer_buffer_destroy(shelfi_ckks *h, void *d_ptr) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (d_ptr) CU(cudaFree(d_ptr));
+    return 0;
 }
 
 int shelfi_rescale_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t limbs_in, uint64_t *d_out, void *stream) {

@@ -587,7 +587,7 @@ __global__ void __launch_bounds__(kFftThreads) decode_kernel(const __grid_consta
     u64 first = ct * ec.batch;
     if (first >= n) return;
     u64 length = n - first < ec.batch ? n - first : ec.batch;
-    decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr);
+    decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr, first);
 }
 
 // General decode (any ring dimension, limb count, slot count): crt_kernel turns the L residues of every coefficient
@@ -639,7 +639,7 @@ __global__ void __launch_bounds__(kFftThreads) decode_fft_kernel(const __grid_co
         u64 first = ct * ec.batch;
         if (first >= n) return;
         u64 length = n - first < ec.batch ? n - first : ec.batch;
-        decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr);
+        decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr, first);
     } else {
         cplx *dst = zs + ct * (u64)ec.slots + (u64)fb * kFftFast;
         for (u32 i = tid; i < kFftFast; i += kFftThreads) dst[i] = z[zsw(i)];
@@ -654,7 +654,7 @@ __global__ void __launch_bounds__(kTailThreads) decode_tail_kernel(const __grid_
     u64 first = ct * ec.batch;
     if (first >= n) return;
     u64 length = n - first < ec.batch ? n - first : ec.batch;
-    decode_tail<DF>(i, zs + ct * (u64)ec.slots, ec, dc, sel ? out : out + first, length, sel ? sel + first : nullptr);
+    decode_tail<DF>(i, zs + ct * (u64)ec.slots, ec, dc, sel ? out : out + first, length, sel ? sel + first : nullptr, first);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -170,6 +170,23 @@ int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const 
                                           uint64_t n_ct, uint64_t *d_acc, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
                           uint64_t n, void *stream);
+/* Decrypt-gather: the optional reassembly of the decoded model across the GPUs of one box (the reference decrypts every
+ * ciphertext into one float64 array, ckks.cpp:181-205; sharded by ciphertext index that array is the concatenation of
+ * the ranks' slices) folded into the decode kernel: decoded value i, i < n, is stored to d_outs[p][offset + i] for every
+ * p < n_outs <= 8.  d_outs[0] is normally this GPU's copy of the full vector and the others are the peers' copies,
+ * mapped with shelfi_peer_buffer_open (or any other peer-accessible device pointers); offset = first parameter index
+ * of this rank's slice.  The stores cross NVLink while the kernel computes; no collective re-reads the slices.  The
+ * caller orders the ranks afterwards (stream synchronise + a process-group barrier) before anyone reads its copy. */
+int shelfi_decrypt_gather_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor,
+                                 double *const *d_outs, uint32_t n_outs, uint64_t offset, uint64_t n, void *stream);
+/* Device buffers that the other processes of the box can map (CUDA IPC, one process per GPU): create on the owning
+ * handle's device and pass the 64-byte handle to the peers by any byte transport; each peer opens it once and closes it
+ * before the owner destroys the buffer. */
+#define SHELFI_PEER_HANDLE_BYTES 64
+int shelfi_peer_buffer_create(shelfi_ckks *h, uint64_t bytes, void **d_ptr, uint8_t handle[SHELFI_PEER_HANDLE_BYTES]);
+int shelfi_peer_buffer_open(shelfi_ckks *h, const uint8_t handle[SHELFI_PEER_HANDLE_BYTES], void **d_ptr);
+int shelfi_peer_buffer_close(shelfi_ckks *h, void *d_ptr);
+int shelfi_peer_buffer_destroy(shelfi_ckks *h, void *d_ptr);
 /* ModReduce on a dense batch: d_ct[n_ct][2][limbs_in][N] -> d_out[n_ct][2][limbs_in - 1][N] (limbs_in 0 = the context's
  * chain); the decrypt calls below take the towers the ciphertexts kept.  After one rescale of a depth-2 average the
  * scaling factor to pass is scalingFactor^2 / q_last. */

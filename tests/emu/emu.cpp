@@ -344,7 +344,7 @@ void emu_decrypt(const Emu *e, const uint64_t *ct, const uint64_t *sk, double pr
         if (d == 1) replay_tail<1>(lc, coeff.data() + l * n);
         if (d == 2) replay_tail<2>(lc, coeff.data() + l * n);
     }
-    DecodeConst dc;
+    DecodeConst dc{};
     dc.crt = e->crt; dc.pre = pre; dc.pow_p = pow_p;
     if (d == 0 && L <= 2 && !tap8) {
         std::vector<cplx> z(e->ec.slots);
