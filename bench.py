@@ -474,8 +474,7 @@ def run_ours(args):
                 dist.all_gather_into_tensor(full, d_out)
 
             def via_peers():
-                pg.decrypt(d_avg.data_ptr(), n_ct, sf2, stream.cuda_stream)
-                pg.barrier()
+                pg.decrypt(d_avg.data_ptr(), n_ct, sf2, stream.cuda_stream)   # barrier, decode + peer stores, barrier
 
             pair = []
             for fn in (via_nccl, via_peers):
@@ -493,8 +492,8 @@ def run_ours(args):
             mine = pg.tensor()[rank * n_ct * BATCH: rank * n_ct * BATCH + P_MODEL]
             peer = pg.tensor()[((rank + 1) % world) * n_ct * BATCH: ((rank + 1) % world) * n_ct * BATCH + P_MODEL]
             ok = bool(torch.equal(mine, d_out)) and bool(torch.isfinite(peer).all()) and float(peer.abs().max()) > 0
-            peer_gather = {"decrypt_plus_nccl_all_gather_ms": pair[0], "decrypt_gather_plus_barrier_ms": pair[1],
-                           "own_slice_identical": ok}
+            peer_gather = {"decrypt_plus_nccl_all_gather_ms": pair[0], "decrypt_gather_device_barriers_ms": pair[1],
+                           "own_slice_identical": ok, "barrier_timeouts": pg.timed_out()}
             pg.close()
         except Exception as e:  # the IPC path must never cost the bench line
             peer_gather = {"error": repr(e)[:200]}

@@ -61,12 +61,16 @@ class PeerGather:
     """Decoded-model reassembly with no collective: every rank owns one device buffer of `world * block` float64 that
     its peers map (CUDA IPC through the C ABI), and `decrypt` makes the decode kernel store this rank's slice into all
     of them at the slice's offset (shelfi_decrypt_gather_device).  The stores ride NVLink while the kernel computes;
-    what remains of the all-gather is one barrier.  `torch.distributed` only carries the 64-byte handles and the barrier.
+    what remains of the all-gather is a flag exchange between the GPUs, queued on the same stream before and after the
+    decode (shelfi_peer_barrier_device) — no host synchronisation, no NCCL launch.  `torch.distributed` only carries
+    the 64-byte handles at construction.
 
-        pg = PeerGather(ckks, n_params, batch)             # collective: every rank of `group` calls it
+        pg = PeerGather(ckks, n_params, batch)              # collective: every rank of `group` calls it
         pg.decrypt(d_ct_ptr, n_ct, scaling_factor, stream)  # this rank's ciphertexts -> everybody's buffer
-        pg.barrier(); full = pg.tensor()[:n_params]         # contiguous decoded model on this GPU
+        full = pg.tensor()[:n_params]                       # valid for work queued on `stream` after decrypt()
     """
+
+    FLAG_WORDS = 16    # 8 rank slots + status slot, padded to 128 bytes
 
     def __init__(self, ckks, n_params: int, batch: int, group=None):
         import ctypes as C
@@ -77,11 +81,16 @@ class PeerGather:
 
         self._C, self._lib, self._ckks, self._dist, self._group = C, lib(), ckks, dist, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > 8:
+            raise ValueError("PeerGather covers the GPUs of one box (at most 8 ranks)")
         self.shard = shard_range(n_params, batch, self.rank, self.world)
         self.n_params, self.block = n_params, self.shard.ct_per_rank * batch
         self.values = self.world * self.block
+        self._flag_off = (self.values * 8 + 255) // 256 * 256
+        self._epoch = 0
         own, handle = C.c_void_p(), C.create_string_buffer(64)
-        ckks._check(self._lib.shelfi_peer_buffer_create(ckks.handle, self.values * 8, C.byref(own), handle))
+        ckks._check(self._lib.shelfi_peer_buffer_create(ckks.handle, self._flag_off + 8 * self.FLAG_WORDS, C.byref(own),
+                                                        handle))
         self._own = own.value
         handles = [None] * self.world
         dist.all_gather_object(handles, bytes(handle.raw), group=group)
@@ -96,38 +105,66 @@ class PeerGather:
         # own copy first (shelfi_decrypt_gather_device's d_outs[0]), then the peers in rank order
         order = [self.rank] + [r for r in range(self.world) if r != self.rank]
         self._outs = (C.c_void_p * self.world)(*[self._ptrs[r] for r in order])
+        self._flags = (C.c_void_p * self.world)(*[p + self._flag_off for p in self._ptrs])
 
-    def decrypt(self, d_ct_ptr: int, n_ct: int, scaling_factor: float, stream: int = 0) -> None:
-        """Queue decrypt + scatter of this rank's `n_ct` ciphertexts on `stream`; returns at once."""
+    def device_barrier(self, stream: int = 0) -> None:
+        """Queue a barrier between the ranks' streams (every rank calls it the same number of times)."""
+        self._epoch += 1
+        self._ckks._check(self._lib.shelfi_peer_barrier_device(self._ckks.handle, self._flags, self.world, self.rank,
+                                                               self._epoch, self._C.c_void_p(stream)))
+
+    def decrypt(self, d_ct_ptr: int, n_ct: int, scaling_factor: float, stream: int = 0, device_barriers: bool = True) -> None:
+        """Queue on `stream`: barrier (the peers have consumed the previous result), decrypt + scatter of this rank's
+        `n_ct` ciphertexts, barrier (every slice has landed here).  Returns at once; with device_barriers=False the
+        caller orders the ranks itself (synchronise the stream, then `barrier()`)."""
         C, sh = self._C, self.shard
         if n_ct != sh.ct_count:
             raise ValueError(f"rank {self.rank}: {n_ct} ciphertexts, shard owns {sh.ct_count}")
-        if n_ct == 0:
-            return
-        self._ckks._check(self._lib.shelfi_decrypt_gather_device(
-            self._ckks.handle, C.c_void_p(d_ct_ptr), n_ct, scaling_factor, self._outs, self.world, sh.param_first,
-            sh.param_count, C.c_void_p(stream)))
+        if device_barriers:
+            self.device_barrier(stream)
+        if n_ct:
+            self._ckks._check(self._lib.shelfi_decrypt_gather_device(
+                self._ckks.handle, C.c_void_p(d_ct_ptr), n_ct, scaling_factor, self._outs, self.world, sh.param_first,
+                sh.param_count, C.c_void_p(stream)))
+        if device_barriers:
+            self.device_barrier(stream)
+
+    def timed_out(self) -> int:
+        """Epoch of the last barrier this rank gave up on (0 = never); synchronises the device."""
+        import torch
+
+        torch.cuda.synchronize(self._ckks.device)
+        flags = torch.as_tensor(_RawDevice(self._own + self._flag_off, (self.FLAG_WORDS,), "<i8"),
+                                device=f"cuda:{self._ckks.device}")
+        return int(flags[8].item())
 
     def barrier(self) -> None:
-        """After this every rank's buffer holds every slice (the caller has synchronised its own stream)."""
+        """Host-side barrier of the process group (the caller has synchronised its own stream)."""
         self._dist.barrier(group=self._group)
-
-    @property
-    def __cuda_array_interface__(self):
-        return {"shape": (self.values,), "typestr": "<f8", "data": (self._own, False), "version": 3, "strides": None}
 
     def tensor(self):
         """This rank's buffer as a torch tensor (no copy); [:n_params] is the decoded model."""
         import torch
 
-        return torch.as_tensor(self, device=f"cuda:{self._ckks.device}")
+        return torch.as_tensor(_RawDevice(self._own, (self.values,), "<f8"), device=f"cuda:{self._ckks.device}")
 
     def close(self) -> None:
         if self._own is None:
             return
+        import torch
+
+        torch.cuda.synchronize(self._ckks.device)
         for r, p in enumerate(self._ptrs):
             if r != self.rank:
                 self._lib.shelfi_peer_buffer_close(self._ckks.handle, self._C.c_void_p(p))
         self._dist.barrier(group=self._group)      # nobody has the buffer mapped any more
         self._lib.shelfi_peer_buffer_destroy(self._ckks.handle, self._C.c_void_p(self._own))
         self._own = None
+
+
+class _RawDevice:
+    """__cuda_array_interface__ view of library-owned device memory (torch wraps it without copying)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False), "version": 3,
+                                         "strides": None}

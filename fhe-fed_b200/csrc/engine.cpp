@@ -1439,6 +1439,28 @@ int shelfi_decrypt_gather_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t 
                          static_cast<cudaStream_t>(stream), nullptr, 0, peers, n_outs - 1);
 }
 
+// Stream-ordered barrier between the ranks of one box; d_flags[r] = rank r's flag array (9 zero-initialised u64 in a peer
+// buffer).  Every rank calls it with the same, growing epoch.
+int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,
+                               void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (!d_flags || n_ranks == 0 || n_ranks > 8 || my_rank >= n_ranks || epoch == 0)
+        return fail(h, SHELFI_ERR_ARG, "1..8 ranks, my_rank below that, epoch from 1");
+    PeerFlags pf{};
+    for (uint32_t i = 0; i < n_ranks; i++) {
+        if (!d_flags[i]) return fail(h, SHELFI_ERR_ARG, "null flag array");
+        pf.flags[i] = reinterpret_cast<unsigned long long *>(d_flags[i]);
+    }
+    uint64_t timeout_ns = 20ull * 1000000000ull;
+    if (const char *e = std::getenv("SHELFI_PEER_TIMEOUT_MS")) timeout_ns = (uint64_t)std::max(1, std::atoi(e)) * 1000000ull;
+    launch_peer_barrier(pf, n_ranks, my_rank, epoch, timeout_ns, static_cast<cudaStream_t>(stream));
+    CU(cudaGetLastError());
+    return 0;
+}
+
 // Buffers other processes of the box can map (CUDA IPC): the destinations of shelfi_decrypt_gather_device.
 int shelfi_peer_buffer_create(shelfi_ckks *h, uint64_t bytes, void **d_ptr, uint8_t handle[SHELFI_PEER_HANDLE_BYTES]) {
     if (!h) return SHELFI_ERR_ARG;
@@ -1449,8 +1471,11 @@ int shelfi_peer_buffer_create(shelfi_ckks *h, uint64_t bytes, void **d_ptr, uint
     static_assert(sizeof(cudaIpcMemHandle_t) == SHELFI_PEER_HANDLE_BYTES, "handle size");
     void *p = nullptr;
     CU(cudaMalloc(&p, bytes));   // a whole allocation of its own: the handle maps from its first byte
+    cudaError_t e = cudaMemset(p, 0, bytes);   // barrier flags start at epoch 0
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { cudaFree(p); return cuda_fail(h, e, "cudaMemset"); }
     cudaIpcMemHandle_t ipc;
-    cudaError_t e = cudaIpcGetMemHandle(&ipc, p);
+    e = cudaIpcGetMemHandle(&ipc, p);
     if (e != cudaSuccess) { cudaFree(p); return cuda_fail(h, e, "cudaIpcGetMemHandle"); }
     std::memcpy(handle, &ipc, sizeof ipc);
     *d_ptr = p;

@@ -971,6 +971,38 @@ void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 
     u64 elems = n_ct * 2 * rc.limbs * (u64)rc.n;
     if (elems) weighted_sum_kernel<<<(unsigned)(elems / kWavgElemsPerCta), kWavgThreads, 0, s>>>(rc, wa, out);
 }
+// ------------------------------------------------------------------------------------------
+// decrypt-gather: stream-ordered barrier between the GPUs of one box (flags in peer-mapped memory)
+// ------------------------------------------------------------------------------------------
+// Lane r publishes this rank's epoch to rank r and waits for rank r's epoch in the local array.  The fence orders the
+// decode kernel's peer stores (earlier in the stream) before the flag; release/acquire at system scope pair the flag
+// with the reader's later loads.  Epochs only grow, so a flag never has to be reset.
+__global__ void __launch_bounds__(32) peer_barrier_kernel(const __grid_constant__ PeerFlags pf, u32 n_ranks, u32 me,
+                                                          u64 epoch, u64 timeout_ns) {
+    const u32 r = threadIdx.x;
+    if (r >= n_ranks) return;
+    __threadfence_system();
+    unsigned long long *theirs = pf.flags[r] + me;
+    const unsigned long long *mine = pf.flags[me] + r;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(theirs), "l"(epoch) : "memory");
+    unsigned long long t0, t1, seen;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(mine) : "memory");
+        if (seen >= epoch) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > timeout_ns) {   // a peer never arrived: record it and let the stream go on
+            pf.flags[me][8] = epoch;
+            break;
+        }
+        __nanosleep(100);
+    }
+    __threadfence_system();
+}
+void launch_peer_barrier(const PeerFlags &pf, u32 n_ranks, u32 me, u64 epoch, u64 timeout_ns, cudaStream_t s) {
+    peer_barrier_kernel<<<1, 32, 0, s>>>(pf, n_ranks, me, epoch, timeout_ns);
+}
+
 static dim3 run_grid(const BlobRuns &br, u64 n_ct) { return dim3((unsigned)(n_ct * br.runs), br.n / 2048); }
 void launch_plain_ntt(const RingConst &rc, const i64 *m, u64 *pt_hat, u32 n_ct, cudaStream_t s) {
     if (!n_ct) return;

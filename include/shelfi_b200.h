@@ -187,6 +187,14 @@ int shelfi_peer_buffer_create(shelfi_ckks *h, uint64_t bytes, void **d_ptr, uint
 int shelfi_peer_buffer_open(shelfi_ckks *h, const uint8_t handle[SHELFI_PEER_HANDLE_BYTES], void **d_ptr);
 int shelfi_peer_buffer_close(shelfi_ckks *h, void *d_ptr);
 int shelfi_peer_buffer_destroy(shelfi_ckks *h, void *d_ptr);
+/* Barrier between the ranks of one box, queued on `stream` (no host synchronisation): rank my_rank stores `epoch` into
+ * slot my_rank of every d_flags[r] and waits until all n_ranks slots of d_flags[my_rank] show it.  d_flags[r] points
+ * at 9 u64 inside rank r's peer buffer (zero after shelfi_peer_buffer_create); every rank passes the same epoch,
+ * larger on every call.  One before shelfi_decrypt_gather_device (the peers are done reading the previous result) and
+ * one after it (every slice has landed) replace the collective's synchronisation.  A rank that waits longer than
+ * SHELFI_PEER_TIMEOUT_MS (default 20000) writes the epoch to slot 8 of its own array and lets the stream continue. */
+int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,
+                               void *stream);
 /* ModReduce on a dense batch: d_ct[n_ct][2][limbs_in][N] -> d_out[n_ct][2][limbs_in - 1][N] (limbs_in 0 = the context's
  * chain); the decrypt calls below take the towers the ciphertexts kept.  After one rescale of a depth-2 average the
  * scaling factor to pass is scalingFactor^2 / q_last. */

@@ -63,6 +63,14 @@ def test_no_cpu_fallback(shelfi):
     with pytest.raises(shelfi.ShelfiError):
         h.decrypt(b"\x01", 1)
     assert h.genCryptoContextAndKeyGen() == 0
+    # the peer-buffer / decrypt-gather entry points too: no device, no work
+    import ctypes as C
+    lib = shelfi.lib()
+    p, handle = C.c_void_p(), C.create_string_buffer(64)
+    assert lib.shelfi_peer_buffer_create(h.handle, 4096, C.byref(p), handle) == -5 and not p.value
+    assert lib.shelfi_peer_buffer_open(h.handle, handle, C.byref(p)) == -5
+    outs = (C.c_void_p * 2)(8, 16)
+    assert lib.shelfi_decrypt_gather_device(h.handle, C.c_void_p(8), 1, 1.0, outs, 2, 0, 1, None) == -5
 
 
 def test_product_never_imports_the_oracle():

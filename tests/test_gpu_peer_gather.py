@@ -82,6 +82,43 @@ def test_peer_buffer_lifecycle(shelfi, handles):
     assert lib.shelfi_peer_buffer_create(h.handle, 0, C.byref(p), handle) != 0
 
 
+def test_stream_barrier_between_two_ranks_on_one_gpu(shelfi, handles):
+    """Two 'ranks' = two streams of one process: each barrier kernel must wait for the other's flag."""
+    h, _ = handles["pybind"]
+    lib = shelfi.lib()
+    flags = [torch.zeros(16, dtype=torch.int64, device="cuda") for _ in range(2)]
+    arr = (C.c_void_p * 2)(*[f.data_ptr() for f in flags])
+    s = [torch.cuda.Stream() for _ in range(2)]
+    marks = torch.zeros(2, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    for epoch in (1, 2, 3):
+        with torch.cuda.stream(s[0]):
+            torch.cuda._sleep(20_000_000)                      # rank 0 arrives ~10 ms late
+            marks[0] = epoch                                   # ... having written this before its barrier
+            check(h, lib.shelfi_peer_barrier_device(h.handle, arr, 2, 0, epoch, C.c_void_p(s[0].cuda_stream)))
+        with torch.cuda.stream(s[1]):
+            check(h, lib.shelfi_peer_barrier_device(h.handle, arr, 2, 1, epoch, C.c_void_p(s[1].cuda_stream)))
+            seen = marks[0].clone()                            # after the barrier rank 1 must see rank 0's write
+        torch.cuda.synchronize()
+        assert int(seen.item()) == epoch
+        assert flags[0][:2].tolist() == [epoch, epoch] and flags[1][:2].tolist() == [epoch, epoch]
+        assert int(flags[0][8].item()) == 0 and int(flags[1][8].item()) == 0
+    assert lib.shelfi_peer_barrier_device(h.handle, arr, 9, 0, 4, None) != 0
+    assert lib.shelfi_peer_barrier_device(h.handle, arr, 2, 2, 4, None) != 0
+    assert lib.shelfi_peer_barrier_device(h.handle, arr, 2, 0, 0, None) != 0
+
+
+def test_barrier_gives_up_after_the_timeout(shelfi, handles, monkeypatch):
+    h, _ = handles["pybind"]
+    lib = shelfi.lib()
+    monkeypatch.setenv("SHELFI_PEER_TIMEOUT_MS", "50")
+    flags = [torch.zeros(16, dtype=torch.int64, device="cuda") for _ in range(2)]
+    arr = (C.c_void_p * 2)(*[f.data_ptr() for f in flags])
+    check(h, lib.shelfi_peer_barrier_device(h.handle, arr, 2, 0, 5, stream()))   # rank 1 never comes
+    torch.cuda.synchronize()
+    assert int(flags[0][8].item()) == 5 and int(flags[1][0].item()) == 5
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on the box")
 def test_two_ranks_equal_nccl_all_gather():
     env = dict(os.environ, MASTER_ADDR="127.0.0.1")

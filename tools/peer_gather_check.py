@@ -5,7 +5,7 @@
 
 Every rank encrypts and aggregates its ciphertext-index shard of a P-parameter model (BASELINE config 2 shape by
 default), then reassembles the decoded model twice: (a) shelfi_decrypt_device + dist.all_gather_into_tensor (NCCL),
-(b) shelfi_decrypt_gather_device into peer-mapped buffers + one barrier.  The two results must be identical on every
+(b) shelfi_decrypt_gather_device into peer-mapped buffers between two stream-ordered flag barriers.  The two results must be identical on every
 rank; rank 0 prints one JSON line with both times (CUDA events on the launching stream, max over ranks)."""
 import argparse
 import ctypes as C
@@ -65,8 +65,12 @@ def main():
 
     pg = PeerGather(h, P, batch)
 
-    def peer_path():
+    def peer_path():          # barrier, decode with peer stores, barrier: three launches on the stream, nothing else
         pg.decrypt(d_avg.data_ptr(), sh.ct_count, sf2, torch.cuda.current_stream().cuda_stream)
+        return pg.tensor()[:P]
+
+    def peer_path_host_barrier():
+        pg.decrypt(d_avg.data_ptr(), sh.ct_count, sf2, torch.cuda.current_stream().cuda_stream, device_barriers=False)
         pg.barrier()
         return pg.tensor()[:P]
 
@@ -95,14 +99,20 @@ def main():
     rel = float(np.abs(got.cpu().numpy() - expect).max() / np.abs(expect).max())
     flag = torch.tensor([int(same and rel < 1e-6)], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    ms_nccl, ms_peer = timed(nccl_path), timed(peer_path)
+    ms_nccl, ms_peer, ms_peer_host = timed(nccl_path), timed(peer_path), timed(peer_path_host_barrier)
+    again = peer_path()
+    torch.cuda.synchronize()
+    flag2 = torch.tensor([int(torch.equal(ref, again) and pg.timed_out() == 0)], device="cuda")
+    dist.all_reduce(flag2, op=dist.ReduceOp.MIN)
+    flag = torch.minimum(flag, flag2)
     # decode alone, for scale
     ms_dec = timed(lambda: sh.ct_count and ck(L.shelfi_decrypt_device(
         h.handle, C.c_void_p(d_avg.data_ptr()), sh.ct_count, sf2, C.c_void_p(d_out.data_ptr()), sh.param_count, sp)))
     if rank == 0:
         print(json.dumps({"tool": "peer_gather_check", "n_gpus": world, "params": P, "learners": K,
                           "identical_on_every_rank": bool(flag.item()), "max_rel_err_vs_plaintext": rel,
-                          "ms_decrypt_plus_nccl_all_gather": ms_nccl, "ms_decrypt_gather_plus_barrier": ms_peer,
+                          "ms_decrypt_plus_nccl_all_gather": ms_nccl, "ms_decrypt_gather_device_barriers": ms_peer,
+                          "ms_decrypt_gather_plus_nccl_barrier": ms_peer_host,
                           "ms_decrypt_alone": ms_dec, "bytes_gathered_per_gpu": 8 * pg.values}))
     pg.close()
     dist.destroy_process_group()
