@@ -94,6 +94,10 @@ def lib() -> C.CDLL:
         "shelfi_encrypt_layers_into": (C.c_int, [vp, C.POINTER(vp), u64p, u32, vp, u64, u64p, u64p, u64p]),
         "shelfi_compute_weighted_average_layers_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32, u32,
                                                                   vp, u64, u64p, u64p, u64p]),
+        "shelfi_compute_weighted_average_layers_rescaled": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float), u32,
+                                                                      u32, C.POINTER(vp), u64p, u64p, u64p]),
+        "shelfi_compute_weighted_average_layers_rescaled_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float),
+                                                                           u32, u32, vp, u64, u64p, u64p, u64p]),
         "shelfi_free": (None, [vp]),
         "shelfi_host_alloc": (vp, [C.c_size_t]),
         "shelfi_host_free": (None, [vp]),
@@ -417,8 +421,10 @@ class CKKS(Scheme):
     def _split(self, dst, offs, lens, n) -> list:
         return [dst.view(offs[i], lens[i]) for i in range(n)]
 
-    def computeWeightedAverage_layers(self, learner_layers, scaling_factors) -> list:
-        """learner_layers[i][s] = blob of learner i, layer s -> [computeWeightedAverage over learners for each layer]."""
+    def computeWeightedAverage_layers(self, learner_layers, scaling_factors, rescale: bool | None = None) -> list:
+        """learner_layers[i][s] = blob of learner i, layer s -> [computeWeightedAverage over learners for each layer];
+        ``rescale`` as in computeWeightedAverage."""
+        rescale = self.rescale if rescale is None else bool(rescale)
         learner_layers, scaling_factors = [list(l) for l in learner_layers], list(scaling_factors)
         if len(learner_layers) != len(scaling_factors):
             print("Error: learner_data and scaling_factors size mismatch")  # ckks.cpp:266
@@ -427,16 +433,16 @@ class CKKS(Scheme):
         if any(len(l) != n for l in learner_layers):
             raise ValueError("every learner must supply the same number of layers")
         if not self.pinned:
-            return [self.computeWeightedAverage([l[s] for l in learner_layers], scaling_factors) for s in range(n)]
+            return [self.computeWeightedAverage([l[s] for l in learner_layers], scaling_factors, rescale) for s in range(n)]
         blobs = [_as_bytes(b) for l in learner_layers for b in l]
         ptrs = (C.c_void_p * (k * n))(*[_addr(b) for b in blobs])
         blens = (C.c_uint64 * (k * n))(*[len(b) for b in blobs])
         w = (C.c_float * k)(*[float(v) for v in scaling_factors])
         offs, lens, total = (C.c_uint64 * n)(), (C.c_uint64 * n)(), C.c_uint64()
         cap = sum((len(b) + 7) // 8 * 8 for b in blobs[:n])   # results have learner 0's layout (ckks.cpp:291-292)
-        dst = PinnedBlob(max(cap, 8))
-        self._check(lib().shelfi_compute_weighted_average_layers_into(self._h, ptrs, blens, w, k, n, _addr(dst), cap, offs,
-                                                                      lens, C.byref(total)))
+        dst = PinnedBlob(max(cap, 8))   # a rescaled result is shorter than learner 0's blobs, never longer
+        into = lib().shelfi_compute_weighted_average_layers_rescaled_into if rescale else lib().shelfi_compute_weighted_average_layers_into
+        self._check(into(self._h, ptrs, blens, w, k, n, _addr(dst), cap, offs, lens, C.byref(total)))
         return self._split(dst, offs, lens, n)
 
     def decrypt_layers(self, blobs, data_dimensions) -> list:

@@ -1335,6 +1335,22 @@ int shelfi_compute_weighted_average_layers_into(shelfi_ckks *h, const uint8_t *c
     std::lock_guard<std::mutex> lock(h->mu);
     return wavg_host(h, blobs, blob_lens, weights, k, n_layers, dst, cap, nullptr, offsets, lens, total_len);
 }
+// the layer-wise average followed by ModReduce on every ciphertext of every layer (rescale-before-transport, opt-in)
+int shelfi_compute_weighted_average_layers_rescaled(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                                    const float *weights, uint32_t k, uint32_t n_layers, uint8_t **out,
+                                                    uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
+    if (!h || !out) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return wavg_host(h, blobs, blob_lens, weights, k, n_layers, nullptr, 0, out, offsets, lens, total_len, true);
+}
+int shelfi_compute_weighted_average_layers_rescaled_into(shelfi_ckks *h, const uint8_t *const *blobs,
+                                                         const uint64_t *blob_lens, const float *weights, uint32_t k,
+                                                         uint32_t n_layers, uint8_t *dst, uint64_t cap, uint64_t *offsets,
+                                                         uint64_t *lens, uint64_t *total_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return wavg_host(h, blobs, blob_lens, weights, k, n_layers, dst, cap, nullptr, offsets, lens, total_len, true);
+}
 int shelfi_decrypt_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                           const uint64_t *data_dimensions, uint32_t n_layers, double *out) {
     if (!h) return SHELFI_ERR_ARG;

@@ -143,6 +143,15 @@ int shelfi_encrypt_layers_into(shelfi_ckks *h, const double *const *x, const uin
 int shelfi_compute_weighted_average_layers_into(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                                                 const float *weights, uint32_t k, uint32_t n_layers, uint8_t *dst,
                                                 uint64_t cap, uint64_t *offsets, uint64_t *lens, uint64_t *total_len);
+/* the same followed by ModReduce on every ciphertext of every layer (rescale-before-transport, opt-in; see
+ * shelfi_compute_weighted_average_rescaled): blob s is byte-identical to that call on layer s alone */
+int shelfi_compute_weighted_average_layers_rescaled(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
+                                                    const float *weights, uint32_t k, uint32_t n_layers, uint8_t **out,
+                                                    uint64_t *offsets, uint64_t *lens, uint64_t *total_len);
+int shelfi_compute_weighted_average_layers_rescaled_into(shelfi_ckks *h, const uint8_t *const *blobs,
+                                                         const uint64_t *blob_lens, const float *weights, uint32_t k,
+                                                         uint32_t n_layers, uint8_t *dst, uint64_t cap, uint64_t *offsets,
+                                                         uint64_t *lens, uint64_t *total_len);
 int shelfi_decrypt_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                           const uint64_t *data_dimensions, uint32_t n_layers, double *out);
 

@@ -185,3 +185,48 @@ def test_config2_size_property(shelfi, gpu_ckks):
     ref = sum(float(np.float32(1.0 / K)) * x for x in xs)
     assert float((a - b).abs().max()) < 1e-9
     assert float((b - ref).abs().max()) / max(float(ref.abs().max()), 1e-3) < RTOL
+
+
+def test_layerwise_rescaled_average_equals_per_layer_calls(shelfi, gpu_ckks, oracles):
+    """shelfi_compute_weighted_average_layers_rescaled[_into]: blob s == the single-vector rescaled call on layer s ==
+    the oracle's ModReduce of the oracle's average; decrypt_layers reads the shorter blobs."""
+    o = oracles["pybind"]
+    d = str(o.cryptodir)
+    sizes = [800, 32, 4096, 4097, 1, 9000]
+    rng = np.random.default_rng(18)
+    K, w = 3, [0.5, 0.2, 0.3]
+    models = [[rng.normal(0, 0.05, n) for n in sizes] for _ in range(K)]
+    enc = [[o.encrypt(a, seed=300 + 10 * i + s) for s, a in enumerate(layers)] for i, layers in enumerate(models)]
+    want = [o.rescale(o.computeWeightedAverage([enc[i][s] for i in range(K)], w)) for s in range(len(sizes))]
+    for pinned in (False, True):   # False: the shim loops over layers; True: one C call for all layers
+        h = shelfi.CKKS("ckks", 4096, 52, d, device=0, pinned=pinned)
+        h.loadCryptoParams()
+        assert h.load_status == 0
+        got = h.computeWeightedAverage_layers(enc, w, rescale=True)
+        assert [bytes(b) for b in got] == want
+        assert [bytes(b) for b in got] == [bytes(h.computeWeightedAverage([enc[i][s] for i in range(K)], w, rescale=True))
+                                           for s in range(len(sizes))]
+        dec = h.decrypt_layers(got, sizes)
+        for s, n in enumerate(sizes):
+            assert np.array_equal(dec[s], o.decrypt(want[s], n))
+            expect = sum(float(np.float32(wi)) * models[i][s] for i, wi in enumerate(w))
+            assert rel_err(dec[s], expect) < RTOL
+        # default stays the reference's depth-2 result
+        plain = h.computeWeightedAverage_layers(enc, w)
+        assert [bytes(b) for b in plain] == [o.computeWeightedAverage([enc[i][s] for i in range(K)], w) for s in range(len(sizes))]
+    # the allocating C entry point
+    lib = shelfi.lib()
+    h = gpu_ckks["pybind"]
+    flat = [enc[i][s] for i in range(K) for s in range(len(sizes))]
+    n = len(sizes)
+    ptrs = (C.c_void_p * (K * n))(*[C.cast(C.c_char_p(b), C.c_void_p).value for b in flat])
+    lens_in = (C.c_uint64 * (K * n))(*[len(b) for b in flat])
+    ww = (C.c_float * K)(*w)
+    out, offs, lens, total = C.c_void_p(), (C.c_uint64 * n)(), (C.c_uint64 * n)(), C.c_uint64()
+    check(h, lib.shelfi_compute_weighted_average_layers_rescaled(h.handle, ptrs, lens_in, ww, K, n, C.byref(out), offs, lens,
+                                                                 C.byref(total)))
+    try:
+        for s in range(n):
+            assert C.string_at(out.value + offs[s], lens[s]) == want[s]
+    finally:
+        lib.shelfi_free(out)
