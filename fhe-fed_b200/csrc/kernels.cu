@@ -971,6 +971,20 @@ void launch_weighted_sum(const RingConst &rc, const WavgArgs &wa, u64 *out, u64 
     u64 elems = n_ct * 2 * rc.limbs * (u64)rc.n;
     if (elems) weighted_sum_kernel<<<(unsigned)(elems / kWavgElemsPerCta), kWavgThreads, 0, s>>>(rc, wa, out);
 }
+// One warp per segment: cereal's bookkeeping between the coefficient runs (8 to ~150 bytes per segment, one of 2.7 KB
+// holding the crypto context).  Byte stores only: the neighbouring run bytes belong to pack_kernel.
+__global__ void __launch_bounds__(256) write_segments_kernel(const SegDesc *__restrict__ desc,
+                                                             const unsigned char *__restrict__ bytes,
+                                                             unsigned char *image, u32 n_seg) {
+    const u32 seg = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (seg >= n_seg) return;
+    const SegDesc d = desc[seg];
+    for (u32 i = threadIdx.x & 31; i < d.len; i += 32) image[d.dst + i] = bytes[d.src + i];
+}
+void launch_write_segments(const SegDesc *desc, const unsigned char *bytes, unsigned char *image, u32 n_seg, cudaStream_t s) {
+    if (n_seg) write_segments_kernel<<<(n_seg + 7) / 8, 256, 0, s>>>(desc, bytes, image, n_seg);
+}
+
 // ------------------------------------------------------------------------------------------
 // decrypt-gather: stream-ordered barrier between the GPUs of one box (flags in peer-mapped memory)
 // ------------------------------------------------------------------------------------------

@@ -64,6 +64,10 @@ void launch_pack(const RingConst &rc, const BlobRuns &br, const u64 *dense, u64 
 void launch_unpack_scale_accumulate(const RingConst &rc, const BlobRuns &br, const u64 *image, const LimbScalars &cs,
                                     u32 first, u64 *acc, u64 n_ct, cudaStream_t s);
 
+// serialized image: bookkeeping bytes (everything between the coefficient runs) copied in from a packed table
+struct SegDesc { unsigned long long dst; unsigned src, len; };   // image byte offset, offset into `bytes`, length
+void launch_write_segments(const SegDesc *desc, const unsigned char *bytes, unsigned char *image, u32 n_seg, cudaStream_t s);
+
 // Barrier between the GPUs of one box, on the stream: rank `me` publishes `epoch` in slot `me` of every rank's flag
 // array (peer-mapped) and waits until its own array shows `epoch` in every slot.  flags[r] -> rank r's array of >= 9
 // u64 (slot 8 = status: set to `epoch` if the wait gave up after `timeout_ns`).
