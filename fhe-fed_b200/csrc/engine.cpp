@@ -977,6 +977,55 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
         CU(h->s_vals.reserve(max_ct * N * sizeof(double)));
         if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(max_ct * (size_t)h->ec.slots * sizeof(cplx)));
     }
+    bool one_scale = true;
+    for (const auto &m : maps[0].meta) one_scale = one_scale && m.scaling_factor == maps[0].meta[0].scaling_factor;
+    if (n_layers == 1 && n_ct >= kPipelineMinCts && one_scale && is_pinned(blobs[0]) && is_pinned(out)) {
+        // One large vector between page-locked buffers: the call is the H2D copy of the blob plus whatever is not hidden
+        // under it.  Ciphertext groups arrive on the copy stream; each is unpacked and decrypted while the next one is
+        // still crossing PCIe, and its values leave on a third stream (the link is full duplex).
+        const wire::BlobMap &m = maps[0];
+        const uint32_t groups = 4;
+        cudaStream_t cs = h->copy_stream;
+        if (!h->d2h_stream) {
+            CU(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&h->ev_stage_out, cudaEventDisableTiming));
+        }
+        CU(cudaEventRecord(h->ev_done[0], st));          // the image and scratch are free once earlier work on st is done
+        CU(cudaStreamWaitEvent(cs, h->ev_done[0], 0));
+        const uint64_t layer_words = 2ull * m.ct_limbs * N;
+        auto run_start = [&](uint64_t j) { return j == 0 ? m.run0[0] : m.run1[0] + (j - 1) * m.stride; };
+        uint64_t got = 0;
+        for (uint32_t g = 0; g < groups; g++) {
+            const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
+            // bytes up to the first run of ciphertext c1, cut on a 4 KiB boundary at or after it (aligned copies are faster)
+            const uint64_t upto = g + 1 == groups ? blob_lens[0] : std::min<uint64_t>(blob_lens[0], (run_start(c1) + 4095) & ~(uint64_t)4095);
+            if (upto > got) CU(cudaMemcpyAsync(h->s_image.as<uint8_t>() + got, blobs[0] + got, upto - got, cudaMemcpyHostToDevice, cs));
+            got = std::max(got, upto);
+            CU(cudaEventRecord(h->ev_copy[g & 1], cs));
+            CU(cudaStreamWaitEvent(st, h->ev_copy[g & 1], 0));
+            uint64_t r0[2 * kMaxLimbs], r1[2 * kMaxLimbs];   // run offsets of ciphertexts c0 and c0 + 1
+            for (uint32_t r = 0; r < 2 * m.ct_limbs; r++) {
+                r0[r] = c0 == 0 ? m.run0[r] : m.run1[r] + (c0 - 1) * m.stride;
+                r1[r] = m.run1[r] + c0 * m.stride;
+            }
+            u64 *dense = h->s_dense.as<u64>() + c0 * layer_words;
+            timed(h, kKUnpack, st, [&] {
+                launch_unpack(h->rc, to_runs(h, r0, r1, m.stride, m.ct_limbs), h->s_image.as<u64>(), dense, c1 - c0, st);
+            });
+            CU(cudaGetLastError());
+            const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
+            if ((rcode = decrypt_dense(h, dense, c1 - c0, m.meta[0].scaling_factor, h->s_out.as<double>() + first, last - first,
+                                       st, nullptr, m.ct_limbs)))
+                return rcode;
+            CU(cudaEventRecord(h->ev_stage_out, st));
+            CU(cudaStreamWaitEvent(h->d2h_stream, h->ev_stage_out, 0));
+            CU(cudaMemcpyAsync(out + first, h->s_out.as<double>() + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost,
+                               h->d2h_stream));
+        }
+        CU(cudaStreamSynchronize(h->d2h_stream));
+        CU(cudaStreamSynchronize(st));
+        return 0;
+    }
     for (uint32_t s = 0; s < n_layers; s++) {
         const LayerSlot &ls = slot[s];
         if ((rcode = h2d(h, h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], st))) return rcode;

@@ -459,4 +459,10 @@ def test_pipelined_host_paths_equal_the_plain_ones(shelfi, gpu_ckks):
         assert np.array_equal(np.frombuffer(avg_b, np.uint8), avg_p.array)
         got = p.decrypt(avg_p, n)
         assert rel_err(got, sum(np.float64(np.float32(wi)) * x for wi, x in zip(w, xs))) < RTOL
+        # page-locked blob AND page-locked result: the group-pipelined decrypt (upload / decrypt / copy back overlapped)
+        pin_out = torch.full((n,), np.nan, dtype=torch.float64).pin_memory()
+        lib = shelfi.lib()
+        assert lib.shelfi_decrypt(p.handle, C.c_void_p(avg_p.array.ctypes.data), len(avg_p), n, C.c_void_p(pin_out.data_ptr())) == 0
+        assert np.array_equal(pin_out.numpy(), h.decrypt(avg_b, n))
+        assert np.array_equal(pin_out.numpy(), got)
         del bb, bp, avg_b, avg_p
