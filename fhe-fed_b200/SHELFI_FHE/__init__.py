@@ -403,11 +403,23 @@ class CKKS(Scheme):
         return out
 
     # ---- layer-wise callers (benchmark.py:490-493, benchmark_selection.py:152-193) in one call each ----
+    _PIPELINE_MIN_CTS = 128    # engine.cpp kPipelineMinCts: from here a single vector is pipelined against its own copies
     def encrypt_layers(self, arrays) -> list:
         """[encrypt(a) for a in arrays] with one host->device copy, one stream of launches, one copy back."""
         if not self.pinned:   # real bytes objects cannot share one buffer: filling each in place beats slicing copies
             return [self.encrypt(a) for a in arrays]
         flat = [np.ascontiguousarray(a, dtype=np.float64).ravel() for a in arrays]
+        # a layer of >= 128 ciphertexts goes through the single-vector call, whose copy back overlaps its own
+        # compute group by group; the small layers of the model share one call (one launch sequence, one copy back)
+        big = [i for i, a in enumerate(flat) if self.num_ciphertexts(a.size) >= self._PIPELINE_MIN_CTS]
+        if big and len(flat) > 1:
+            out = [None] * len(flat)
+            for i in big:
+                out[i] = self.encrypt(flat[i])
+            rest = [i for i in range(len(flat)) if out[i] is None]
+            for i, b in zip(rest, self.encrypt_layers([flat[i] for i in rest]) if rest else []):
+                out[i] = b
+            return out
         n = len(flat)
         xp = (C.c_void_p * n)(*[a.ctypes.data for a in flat])
         ll = (C.c_uint64 * n)(*[a.size for a in flat])
@@ -434,6 +446,18 @@ class CKKS(Scheme):
             raise ValueError("every learner must supply the same number of layers")
         if not self.pinned:
             return [self.computeWeightedAverage([l[s] for l in learner_layers], scaling_factors, rescale) for s in range(n)]
+        big_len = self.blob_size(self._PIPELINE_MIN_CTS)
+        big = [s for s in range(n) if k and len(learner_layers[0][s]) >= big_len]
+        if big and n > 1:    # as in encrypt_layers: large layers take the pipelined single-vector call
+            out = [None] * n
+            for s in big:
+                out[s] = self.computeWeightedAverage([l[s] for l in learner_layers], scaling_factors, rescale)
+            rest = [s for s in range(n) if out[s] is None]
+            if rest:
+                for s, b in zip(rest, self.computeWeightedAverage_layers([[l[s] for s in rest] for l in learner_layers],
+                                                                       scaling_factors, rescale)):
+                    out[s] = b
+            return out
         blobs = [_as_bytes(b) for l in learner_layers for b in l]
         ptrs = (C.c_void_p * (k * n))(*[_addr(b) for b in blobs])
         blens = (C.c_uint64 * (k * n))(*[len(b) for b in blobs])

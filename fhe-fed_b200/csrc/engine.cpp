@@ -91,7 +91,9 @@ class ParallelCopier {
         for (auto &t : workers_) t.join();
     }
     void copy(void *dst, const void *src, size_t bytes) {
-        if (bytes < (1u << 20) || parts_ == 1) { std::memcpy(dst, src, bytes); return; }
+        // waking the workers costs a few hundred microseconds on a virtualised host (measured: 2.2 MB takes 0.5 ms with
+        // eight threads), so only copies that take longer than that alone are split
+        if (bytes < (4u << 20) || parts_ == 1) { std::memcpy(dst, src, bytes); return; }
         {
             std::lock_guard<std::mutex> l(mu_);
             dst_ = static_cast<char *>(dst); src_ = static_cast<const char *>(src); bytes_ = bytes;
@@ -170,6 +172,8 @@ struct shelfi_ckks {
     Profiler prof;
     std::mutex mu;
     // pageable host buffers: staging chunks + copy threads (created on first use)
+    void *pin_x = nullptr;       // page-locked copy of a pageable encrypt input (grow-only)
+    size_t pin_x_cap = 0;
     void *stage[2] = {nullptr, nullptr};
     cudaEvent_t ev_stage[2] = {nullptr, nullptr};
     ParallelCopier *copier = nullptr;
@@ -290,7 +294,9 @@ int ensure_staging(shelfi_ckks *h) {
 // Host -> device, queued on `s`.  Page-locked sources go straight to the copy engine (asynchronous); pageable ones are
 // copied chunk by chunk into page-locked staging by the copy threads (the call returns when the last chunk is queued).
 int h2d(shelfi_ckks *h, void *dev, const void *host, size_t bytes, cudaStream_t s) {
-    if (bytes < (4u << 20) || is_pinned(host)) {
+    // (from 1 MiB: the per-group inputs of a pipelined encrypt are 2 MB of pageable numpy memory, which the driver's
+    // own pageable path moves at a few GB/s and synchronously)
+    if (bytes < (1u << 20) || is_pinned(host)) {
         CU(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, s));
         return 0;
     }
@@ -615,6 +621,10 @@ const wire::BlobPlan &plan_of(const LayerSlot &l) { return l.ep ? l.ep->plan : l
 uint64_t align8(uint64_t v) { return (v + 7) & ~(uint64_t)7; }
 constexpr uint64_t kPipelineMinCts = 128;   // below this a call is launch latency, not copy time
 
+// Called where a reference-facing call starts (everything queued by earlier calls has completed by then).
+void trim_enc_plans(shelfi_ckks *h) {
+    if (h->enc_plans.size() > 256) drop_enc_plans(h);
+}
 // The serialization plan of a vector of n_ct ciphertexts that all carry metadata m under context ctx (what encrypt
 // and, with every learner-0 ciphertext alike, the weighted average write), cached with its segments on the device.
 bool same_meta(const wire::CiphertextMeta &a, const wire::CiphertextMeta &b) {
@@ -630,8 +640,7 @@ int enc_plan(shelfi_ckks *h, const wire::ContextParams &ctx, uint64_t n_ct, cons
     key.append(reinterpret_cast<const char *>(&m.encoding_type), 4).append(reinterpret_cast<const char *>(&m.limbs), 4);
     key.append(m.tag, 32);
     auto it = h->enc_plans.find(key);
-    if (it == h->enc_plans.end()) {
-        if (h->enc_plans.size() >= 16) drop_enc_plans(h);
+    if (it == h->enc_plans.end()) {   // (eviction happens between calls, trim_enc_plans: a call keeps pointers into the map)
         shelfi_ckks::EncPlan ep;
         ep.plan = wire::plan_ciphertext_blob(ctx, n_ct, std::vector<wire::CiphertextMeta>(1, m));
         std::vector<SegDesc> desc;
@@ -641,9 +650,11 @@ int enc_plan(shelfi_ckks *h, const wire::ContextParams &ctx, uint64_t n_ct, cons
             bytes.insert(bytes.end(), seg.bytes.begin(), seg.bytes.end());
         }
         ep.n_seg = (uint32_t)desc.size();
-        int rcode;
-        if ((rcode = upload(h, &ep.d_desc, desc.data(), desc.size() * sizeof(SegDesc)))) return rcode;
-        if ((rcode = upload(h, &ep.d_bytes, bytes.data(), bytes.size()))) { ep.d_desc.release(); return rcode; }
+        if (n_ct >= kDeviceHeaderMinCts) {   // smaller vectors get their few segments from the host
+            int rcode;
+            if ((rcode = upload(h, &ep.d_desc, desc.data(), desc.size() * sizeof(SegDesc)))) return rcode;
+            if ((rcode = upload(h, &ep.d_bytes, bytes.data(), bytes.size()))) { ep.d_desc.release(); return rcode; }
+        }
         it = h->enc_plans.emplace(std::move(key), std::move(ep)).first;
     }
     *out = &it->second;
@@ -656,6 +667,7 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
                  uint64_t cap, uint8_t **alloc_out, uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
     int rcode = check_stage(h, true, false);
     if (rcode) return rcode;
+    trim_enc_plans(h);
     if (!xs || !layer_len || !lens || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
     for (uint32_t s = 0; s < n_layers; s++)
         if (!xs[s]) return fail(h, SHELFI_ERR_ARG, "null argument");
@@ -711,12 +723,33 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
         if (const char *e = std::getenv("SHELFI_ENC_GROUPS")) groups = (uint32_t)std::min<uint64_t>(n_ct, std::max(1, std::atoi(e)));
         cudaStream_t cs = h->copy_stream;
         queue_headers(ls);
+        // A pageable input (a numpy array) is moved into a page-locked copy by the copy threads, group by group, each
+        // while the GPU works on the group before; nothing waits on anything.  (Group-sized cudaMemcpyAsync calls on
+        // pageable memory are synchronous and slow: 4.0 ms per call on the config-2 vector.)
+        const double *src = xs[0];
+        const bool stage_x = !is_pinned(src) && ls.n * sizeof(double) <= ((size_t)512 << 20);
+        if (stage_x) {
+            if ((rcode = ensure_staging(h))) return bail(rcode);
+            if (h->pin_x_cap < ls.n * sizeof(double)) {
+                if (h->pin_x) cudaFreeHost(h->pin_x);
+                h->pin_x = nullptr; h->pin_x_cap = 0;
+                const size_t want = ls.n * sizeof(double) + (ls.n * sizeof(double)) / 8;
+                CUB(cudaHostAlloc(&h->pin_x, want, cudaHostAllocDefault));
+                h->pin_x_cap = want;
+            }
+        }
         auto run_start = [&](uint64_t j) { return j == 0 ? pl.run0[0] : pl.run1[0] + (j - 1) * pl.stride; };
         uint64_t sent = 0;
         for (uint32_t g = 0; g < groups; g++) {
             const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
             const uint64_t first = c0 * h->batch, count = std::min(ls.n, c1 * h->batch) - first;
-            if ((rcode = h2d(h, h->s_x.as<double>() + first, xs[0] + first, count * sizeof(double), s))) return bail(rcode);
+            if (stage_x) {
+                h->copier->copy(static_cast<double *>(h->pin_x) + first, src + first, count * sizeof(double));
+                CUB(cudaMemcpyAsync(h->s_x.as<double>() + first, static_cast<const double *>(h->pin_x) + first,
+                                    count * sizeof(double), cudaMemcpyHostToDevice, s));
+            } else if ((rcode = h2d(h, h->s_x.as<double>() + first, src + first, count * sizeof(double), s))) {
+                return bail(rcode);
+            }
             if ((rcode = encrypt_dense(h, h->s_x.as<double>() + first, count, c0, h->s_dense.as<u64>() + c0 * ct_words, s)))
                 return bail(rcode);
             uint64_t r0[2 * kMaxLimbs], r1[2 * kMaxLimbs];   // run offsets of ciphertexts c0 and c0 + 1
@@ -779,6 +812,7 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
               uint64_t *total_len, bool rescale = false) {
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
+    trim_enc_plans(h);
     if (!blobs || !blob_lens || !w || !lens || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
     if (k == 0) return fail(h, SHELFI_ERR_ARG, "no learners");
     const uint32_t L = h->ctx.limbs;
@@ -1138,6 +1172,7 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
             if (h->stage[i]) cudaFreeHost(h->stage[i]);
             if (h->ev_stage[i]) cudaEventDestroy(h->ev_stage[i]);
         }
+        if (h->pin_x) cudaFreeHost(h->pin_x);
         delete h->copier;
         cudaStreamDestroy(h->stream);
         cudaStreamDestroy(h->copy_stream);

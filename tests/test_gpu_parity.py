@@ -466,3 +466,35 @@ def test_pipelined_host_paths_equal_the_plain_ones(shelfi, gpu_ckks):
         assert np.array_equal(pin_out.numpy(), h.decrypt(avg_b, n))
         assert np.array_equal(pin_out.numpy(), got)
         del bb, bp, avg_b, avg_p
+
+
+def test_layers_with_many_distinct_sizes(shelfi, gpu_ckks, oracles):
+    """More distinct layer sizes in one call than any plan cache holds, large ones (headers written by the device
+    kernel) next to small ones (written by the host): every blob equals the per-layer call and the oracle's."""
+    o = oracles["pybind"]
+    d = str(FIXTURE_DIRS["pybind"]) + "/"
+    p = shelfi.CKKS("ckks", 4096, 52, d, device=0, pinned=True)
+    p.loadCryptoParams()
+    h = gpu_ckks["pybind"]
+    sizes = [4096 * j + 5 for j in range(1, 41)] + [7, 4096, 300]
+    rng = np.random.default_rng(23)
+    models = [[rng.normal(0, 0.05, n) for n in sizes] for _ in range(2)]
+    enc = []
+    for i, layers in enumerate(models):
+        p.set_sampler_seed(500 + i)
+        blobs = p.encrypt_layers(layers)
+        p.set_sampler_seed(None)
+        for s in (0, 17, 39, 40, 42):
+            assert bytes(blobs[s]) == o.encrypt(layers[s], seed=500 + i), s
+        h.set_sampler_seed(500 + i)
+        assert [bytes(b) for b in blobs] == [h.encrypt(a) for a in layers]
+        h.set_sampler_seed(None)
+        enc.append(blobs)
+    w = [0.25, 0.75]
+    avg = p.computeWeightedAverage_layers(enc, w)
+    for s in (0, 31, 39, 41):
+        assert bytes(avg[s]) == o.computeWeightedAverage([bytes(enc[i][s]) for i in range(2)], w), s
+    assert [bytes(b) for b in avg] == [h.computeWeightedAverage([bytes(enc[i][s]) for i in range(2)], w) for s in range(len(sizes))]
+    dec = p.decrypt_layers(avg, sizes)
+    for s, n in enumerate(sizes):
+        assert rel_err(dec[s], sum(float(np.float32(wi)) * models[i][s] for i, wi in enumerate(w))) < RTOL
