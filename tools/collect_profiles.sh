@@ -9,6 +9,8 @@ python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/r01_bench_ref
 python tools/bench_configs.py --configs 3,4,5,6 > gpurun_out/r01_bench_configs.jsonl 2>> gpurun_out/bench.err
 python tools/bench_selective.py > gpurun_out/r01_bench_selective.jsonl 2>> gpurun_out/bench.err
 python tools/bench_layers.py > gpurun_out/r01_bench_layers.jsonl 2>> gpurun_out/bench.err
+python tools/e2e_phases.py > gpurun_out/r01_e2e_phases.json 2>> gpurun_out/bench.err
+# (two or more GPUs: torchrun ... tools/peer_gather_check.py and bench.py --gpus N feed r01_peer_gather.jsonl / r01_scaling.jsonl)
 B="python bench.py --steps 2 --warmup 3 --no-cpu"
 $B > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r01_launches.csv $B > gpurun_out/ncu_l.log 2>&1
 echo "# ncu --set full, one launch per kernel of \`$B\` (tools/collect_profiles.sh), current build" > gpurun_out/r01_ncu_step.md
