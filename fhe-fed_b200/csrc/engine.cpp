@@ -623,7 +623,7 @@ constexpr uint64_t kPipelineMinCts = 128;   // below this a call is launch laten
 
 // Called where a reference-facing call starts (everything queued by earlier calls has completed by then).
 void trim_enc_plans(shelfi_ckks *h) {
-    if (h->enc_plans.size() > 256) drop_enc_plans(h);
+    if (h->enc_plans.size() > 64) drop_enc_plans(h);
 }
 // The serialization plan of a vector of n_ct ciphertexts that all carry metadata m under context ctx (what encrypt
 // and, with every learner-0 ciphertext alike, the weighted average write), cached with its segments on the device.
