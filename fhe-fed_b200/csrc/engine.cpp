@@ -4,6 +4,8 @@
 #include "../../include/shelfi_b200.h"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -82,30 +84,47 @@ struct Profiler {
 class ParallelCopier {
   public:
     explicit ParallelCopier(unsigned n) {
-        for (unsigned i = 1; i < n; i++) workers_.emplace_back([this, i] { loop(i); });
         parts_ = n ? n : 1;
+        for (unsigned i = 1; i < parts_; i++) workers_.emplace_back([this, i] { loop(i); });
     }
     ~ParallelCopier() {
-        { std::lock_guard<std::mutex> l(mu_); stop_ = true; gen_++; }
+        { std::lock_guard<std::mutex> l(mu_); stop_.store(true); gen_.fetch_add(1, std::memory_order_release); }
         cv_.notify_all();
         for (auto &t : workers_) t.join();
     }
     void copy(void *dst, const void *src, size_t bytes) {
-        // waking the workers costs a few hundred microseconds on a virtualised host (measured: 2.2 MB takes 0.5 ms with
-        // eight threads), so only copies that take longer than that alone are split
+        // waking sleeping workers costs a few hundred microseconds on a virtualised host (measured: 2.2 MB takes 0.5 ms
+        // with eight threads), so only copies that take longer than that alone are split
         if (bytes < (4u << 20) || parts_ == 1) { std::memcpy(dst, src, bytes); return; }
-        {
-            std::lock_guard<std::mutex> l(mu_);
-            dst_ = static_cast<char *>(dst); src_ = static_cast<const char *>(src); bytes_ = bytes;
-            pending_ = parts_ - 1; gen_++;
-        }
+        dst_ = static_cast<char *>(dst); src_ = static_cast<const char *>(src); bytes_ = bytes;
+        pending_.store(parts_ - 1, std::memory_order_relaxed);
+        { std::lock_guard<std::mutex> l(mu_); gen_.fetch_add(1, std::memory_order_release); }
         cv_.notify_all();
         piece(0);
-        std::unique_lock<std::mutex> l(mu_);
-        done_.wait(l, [this] { return pending_ == 0; });
+        if (!spin_until([this] { return pending_.load(std::memory_order_acquire) == 0; }, 5000)) {
+            std::unique_lock<std::mutex> l(mu_);
+            done_.wait(l, [this] { return pending_.load(std::memory_order_acquire) == 0; });
+        }
     }
 
   private:
+    static void relax() {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();
+#else
+        std::this_thread::yield();
+#endif
+    }
+    // poll `ready` for at most `us` microseconds; chunked copies follow each other within that time, so the workers
+    // of a multi-chunk transfer never go back to sleep between chunks
+    template <class F> static bool spin_until(F ready, unsigned us) {
+        const auto t0 = std::chrono::steady_clock::now();
+        for (unsigned it = 0;; it++) {
+            if (ready()) return true;
+            if ((it & 63) == 63 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(us)) return false;
+            relax();
+        }
+    }
     void piece(unsigned i) {
         size_t per = ((bytes_ / parts_) + 4095) & ~(size_t)4095;
         size_t a = std::min(bytes_, per * i), b = (i + 1 == parts_) ? bytes_ : std::min(bytes_, per * (i + 1));
@@ -114,16 +133,16 @@ class ParallelCopier {
     void loop(unsigned i) {
         uint64_t seen = 0;
         for (;;) {
-            {
+            if (!spin_until([&] { return gen_.load(std::memory_order_acquire) != seen; }, 500)) {
                 std::unique_lock<std::mutex> l(mu_);
-                cv_.wait(l, [&] { return gen_ != seen; });
-                seen = gen_;
-                if (stop_) return;
+                cv_.wait(l, [&] { return gen_.load(std::memory_order_acquire) != seen; });
             }
+            seen = gen_.load(std::memory_order_acquire);
+            if (stop_.load()) return;
             piece(i);
-            {
+            if (pending_.fetch_sub(1, std::memory_order_acq_rel) == 1) {
                 std::lock_guard<std::mutex> l(mu_);
-                if (--pending_ == 0) done_.notify_one();
+                done_.notify_one();
             }
         }
     }
@@ -133,9 +152,10 @@ class ParallelCopier {
     const char *src_ = nullptr;
     char *dst_ = nullptr;
     size_t bytes_ = 0;
-    unsigned parts_ = 1, pending_ = 0;
-    uint64_t gen_ = 0;
-    bool stop_ = false;
+    unsigned parts_ = 1;
+    std::atomic<unsigned> pending_{0};
+    std::atomic<uint64_t> gen_{0};
+    std::atomic<bool> stop_{false};
 };
 
 constexpr size_t kStageBytes = 16u << 20;   // two page-locked staging chunks of this size per handle
