@@ -126,6 +126,7 @@ def lib() -> C.CDLL:
         "shelfi_profile_enable": (C.c_int, [vp, C.c_int]),
         "shelfi_profile_reset": (C.c_int, [vp]),
         "shelfi_profile_get": (C.c_int, [vp, C.c_int, C.POINTER(C.c_double), u64p]),
+        "shelfi_selftest_parallel_copy": (C.c_int, [u64, u32, u32]),
         "shelfi_version": (C.c_char_p, []),
     }
     for name, (res, args) in sig.items():

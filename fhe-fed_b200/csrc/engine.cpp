@@ -1642,6 +1642,22 @@ int shelfi_decrypt_gather_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t 
                          static_cast<cudaStream_t>(stream), nullptr, 0, peers, n_outs - 1);
 }
 
+// Host-only self-test of the copy threads (no device needed): `rounds` copies of `bytes` patterned bytes with `threads`
+// workers, each verified; returns 0, or the 1-based round that came back wrong.
+int shelfi_selftest_parallel_copy(uint64_t bytes, uint32_t threads, uint32_t rounds) {
+    if (bytes == 0 || threads == 0 || threads > 64) return SHELFI_ERR_ARG;
+    std::vector<uint8_t> src(bytes), dst(bytes);
+    ParallelCopier pc(threads);
+    for (uint32_t r = 0; r < rounds; r++) {
+        for (uint64_t i = 0; i < bytes; i += 4096) src[i] = (uint8_t)(i / 4096 + r);
+        src[bytes - 1] = (uint8_t)(r * 7 + 1);
+        std::fill(dst.begin(), dst.end(), (uint8_t)0xEE);
+        pc.copy(dst.data(), src.data(), bytes);
+        if (std::memcmp(dst.data(), src.data(), bytes) != 0) return (int)r + 1;
+    }
+    return 0;
+}
+
 // Stream-ordered barrier between the ranks of one box; d_flags[r] = rank r's flag array (9 zero-initialised u64 in a peer
 // buffer).  Every rank calls it with the same, growing epoch.
 int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,

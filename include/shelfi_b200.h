@@ -240,6 +240,10 @@ int shelfi_plain_weighted_sum_device(shelfi_ckks *h, const double *const *d_x, c
 int shelfi_pack_device(shelfi_ckks *h, const uint64_t *d_dense, uint64_t n_ct, uint8_t *d_image, void *stream);
 int shelfi_unpack_device(shelfi_ckks *h, const uint8_t *d_image, uint64_t n_ct, uint64_t *d_dense, void *stream);
 
+/* Host-only self-test of the staging copy threads (runs without a device): `rounds` verified copies of `bytes` bytes
+ * split over `threads` workers; 0 = all correct. */
+int shelfi_selftest_parallel_copy(uint64_t bytes, uint32_t threads, uint32_t rounds);
+
 /* ---- primitives, exposed for parity tests and the NTT bandwidth metric ---- */
 /* rows limb polynomials [rows][N], limb = row % L; PALISADE ForwardTransformToBitReverse /
  * InverseTransformFromBitReverse semantics, in place */

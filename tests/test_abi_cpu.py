@@ -73,6 +73,20 @@ def test_no_cpu_fallback(shelfi):
     assert lib.shelfi_decrypt_gather_device(h.handle, C.c_void_p(8), 1, 1.0, outs, 2, 0, 1, None) == -5
 
 
+def test_copy_threads_selftest(shelfi):
+    """The staging copy threads (spin-then-sleep hand-off) on host memory only: many back-to-back copies, odd sizes,
+    1 to 8 workers, and copies far enough apart that the workers have gone back to sleep."""
+    import time
+    lib = shelfi.lib()
+    for threads in (1, 2, 3, 8):
+        assert lib.shelfi_selftest_parallel_copy((5 << 20) + 12345, threads, 40) == 0
+        assert lib.shelfi_selftest_parallel_copy((1 << 20) + 1, threads, 5) == 0      # below the split threshold
+    for _ in range(3):
+        time.sleep(0.01)
+        assert lib.shelfi_selftest_parallel_copy(16 << 20, 8, 3) == 0
+    assert lib.shelfi_selftest_parallel_copy(0, 8, 1) != 0
+
+
 def test_product_never_imports_the_oracle():
     for path in list((ROOT / "fhe-fed_b200").rglob("*.py")) + list((ROOT / "fhe-fed_b200" / "csrc").iterdir()):
         if path.is_file():
