@@ -465,7 +465,10 @@ def run_ours(args):
         gather_ms = g0.elapsed_time(g1)
         # the same reassembly folded into the decode kernel (stores to peer-mapped buffers over NVLink + one barrier),
         # against decrypt followed by the NCCL all-gather; both timed on the launching stream, max over ranks below
+        # (PeerGather's constructor fails on all ranks or on none; SHELFI_BENCH_NO_PEER_GATHER=1 skips the comparison)
         try:
+            if os.environ.get("SHELFI_BENCH_NO_PEER_GATHER") == "1":
+                raise RuntimeError("skipped by SHELFI_BENCH_NO_PEER_GATHER")
             from SHELFI_FHE.sharding import PeerGather
             pg = PeerGather(h, world * n_ct * BATCH, BATCH)
 

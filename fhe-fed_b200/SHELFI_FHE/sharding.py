@@ -88,20 +88,37 @@ class PeerGather:
         self.values = self.world * self.block
         self._flag_off = (self.values * 8 + 255) // 256 * 256
         self._epoch = 0
+        # Every rank goes through the same collectives whatever fails locally, and all of them raise together: a rank
+        # that dropped out alone would leave the others waiting in the next collective.
         own, handle = C.c_void_p(), C.create_string_buffer(64)
-        ckks._check(self._lib.shelfi_peer_buffer_create(ckks.handle, self._flag_off + 8 * self.FLAG_WORDS, C.byref(own),
-                                                        handle))
-        self._own = own.value
+        rc = self._lib.shelfi_peer_buffer_create(ckks.handle, self._flag_off + 8 * self.FLAG_WORDS, C.byref(own), handle)
+        self._own = own.value if rc == 0 else None
         handles = [None] * self.world
-        dist.all_gather_object(handles, bytes(handle.raw), group=group)
-        self._ptrs = []
-        for r, hb in enumerate(handles):
-            if r == self.rank:
-                self._ptrs.append(self._own)
-                continue
-            p = C.c_void_p()
-            ckks._check(self._lib.shelfi_peer_buffer_open(ckks.handle, hb, C.byref(p)))
-            self._ptrs.append(p.value)
+        dist.all_gather_object(handles, bytes(handle.raw) if rc == 0 else None, group=group)
+        self._ptrs, failed = [], None
+        if all(hb is not None for hb in handles):
+            for r, hb in enumerate(handles):
+                if r == self.rank:
+                    self._ptrs.append(self._own)
+                    continue
+                p = C.c_void_p()
+                if self._lib.shelfi_peer_buffer_open(ckks.handle, hb, C.byref(p)) != 0:
+                    failed = f"rank {self.rank}: cannot map rank {r}'s buffer: {ckks._err()}"
+                    break
+                self._ptrs.append(p.value)
+        else:
+            failed = f"rank {self.rank}: peer buffer allocation failed on rank(s) {[r for r, hb in enumerate(handles) if hb is None]}"
+        verdicts = [None] * self.world
+        dist.all_gather_object(verdicts, failed, group=group)
+        if any(v is not None for v in verdicts):
+            for r, p in enumerate(self._ptrs):
+                if r != self.rank:
+                    self._lib.shelfi_peer_buffer_close(ckks.handle, C.c_void_p(p))
+            dist.barrier(group=group)
+            if self._own is not None:
+                self._lib.shelfi_peer_buffer_destroy(ckks.handle, C.c_void_p(self._own))
+            self._own = None
+            raise RuntimeError("; ".join(v for v in verdicts if v is not None))
         # own copy first (shelfi_decrypt_gather_device's d_outs[0]), then the peers in rank order
         order = [self.rank] + [r for r in range(self.world) if r != self.rank]
         self._outs = (C.c_void_p * self.world)(*[self._ptrs[r] for r in order])

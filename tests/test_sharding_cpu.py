@@ -66,3 +66,34 @@ def _worker(rank, world, port, n, batch, out_dir):
 def test_gather_decoded_gloo(world, n, tmp_path):
     mp.spawn(_worker, args=(world, _free_port(), n, 4096, str(tmp_path)), nprocs=world, join=True)
     assert [(tmp_path / f"rank{r}.txt").read_text() for r in range(world)] == ["ok"] * world
+
+
+def _peer_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import SHELFI_FHE
+        from SHELFI_FHE.sharding import PeerGather
+        h = SHELFI_FHE.CKKS(device=0)
+        try:
+            PeerGather(h, 100000, 4096)
+            verdict = "constructed"
+        except RuntimeError as e:            # no device here: the allocation fails on every rank, and all learn of it
+            verdict = "raised:" + str(e)
+        t = torch.tensor([1.0])
+        dist.all_reduce(t)                   # the process group is still usable and nobody is stuck in a collective
+        with open(os.path.join(out_dir, f"rank{rank}.txt"), "w") as f:
+            f.write(verdict + f"|{int(t.item())}")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-device failure mode")
+def test_peer_gather_fails_on_every_rank_together(tmp_path):
+    """PeerGather's constructor is collective: a local failure is shared before anyone raises, so no rank is left
+    waiting in all_gather_object (here every rank fails: there is no device)."""
+    world = 2
+    mp.spawn(_peer_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        text = (tmp_path / f"rank{r}.txt").read_text()
+        assert text.startswith("raised:") and "allocation failed on rank(s) [0, 1]" in text and text.endswith("|2"), text
