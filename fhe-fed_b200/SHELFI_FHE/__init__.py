@@ -262,6 +262,20 @@ class PinnedBlob:
             self._p = self._parent = None
 
 
+class _PinnedArray(np.ndarray):
+    """float64 result of decrypt in pinned mode: a view of a PinnedBlob's page-locked buffer that holds on to it (views
+    and slices keep this array as their base, so the buffer returns to the pool only when nothing refers to it)."""
+
+    _keep = None
+
+    def __array_finalize__(self, obj):
+        if obj is not None and getattr(self, "_keep", None) is None:
+            self._keep = getattr(obj, "_keep", None)
+
+    def __reduce__(self):          # pickle / deepcopy hand back a plain array
+        return np.asarray(self).copy().__reduce__()
+
+
 class Scheme:
     """Opaque base class, as bound at binding.cpp:16 (include/scheme.h:15-32)."""
 
@@ -399,7 +413,14 @@ class CKKS(Scheme):
         """ckks.cpp:170-213: serialized ciphertext vector -> float64[data_dimensions] (level-0 or rescaled)."""
         blob = _as_bytes(learner_data)
         n = int(data_dimensions)
-        out = np.empty(n, dtype=np.float64)
+        if self.pinned and n * 8 >= (1 << 20):
+            # pinned mode: the result lives in pooled page-locked memory too (an ndarray that keeps its buffer alive),
+            # so a page-locked blob takes the engine's pipelined decrypt (upload / decrypt / copy back overlapped)
+            keep = PinnedBlob(n * 8)
+            out = keep.array.view(np.float64).view(_PinnedArray)
+            out._keep = keep
+        else:
+            out = np.empty(n, dtype=np.float64)
         self._check(lib().shelfi_decrypt(self._h, _addr(blob), len(blob), n, out.ctypes.data))
         return out
 

@@ -6,6 +6,7 @@ exactly against the oracle (same unfused FFT order) and within RTOL = 1e-6 relat
 weighted average — the tolerance BASELINE.json's north_star states for PALISADE's own decrypt.
 """
 import ctypes as C
+import gc
 import hashlib
 import math
 
@@ -459,6 +460,15 @@ def test_pipelined_host_paths_equal_the_plain_ones(shelfi, gpu_ckks):
         assert np.array_equal(np.frombuffer(avg_b, np.uint8), avg_p.array)
         got = p.decrypt(avg_p, n)
         assert rel_err(got, sum(np.float64(np.float32(wi)) * x for wi, x in zip(w, xs))) < RTOL
+        # pinned mode hands back an ndarray over pooled page-locked memory: a view must keep that memory out of the pool
+        assert isinstance(got, np.ndarray) and got.dtype == np.float64 and got.shape == (n,)
+        view, want_view = got[5:15], got[5:15].copy()
+        del got
+        gc.collect()
+        other = p.decrypt(bp[0], n)                      # different values; would land in the same buffer if it were free
+        assert np.array_equal(view, want_view) and not np.array_equal(other[5:15], want_view)
+        got = p.decrypt(avg_p, n)
+        del view, other
         # page-locked blob AND page-locked result: the group-pipelined decrypt (upload / decrypt / copy back overlapped)
         pin_out = torch.full((n,), np.nan, dtype=torch.float64).pin_memory()
         lib = shelfi.lib()
