@@ -714,7 +714,14 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
     }
     cudaStream_t s = h->stream;
     const uint64_t ct_words = 2ull * h->ctx.limbs * h->ctx.ring_dim;
-    auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
+    // an error return must not leave copies in flight to or from the caller's buffers (they are only borrowed for the call)
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        if (h->d2h_stream) cudaStreamSynchronize(h->d2h_stream);
+        if (alloc_out) std::free(dst);
+        return code;
+    };
     // bookkeeping bytes of a large vector: dropped into the image by a kernel (disjoint from the runs the pack kernel
     // writes, byte stores on both sides), so the blob arrives complete and the host touches none of it
     auto device_headers = [&](const LayerSlot &l) { return l.n_ct >= kDeviceHeaderMinCts; };
@@ -887,7 +894,14 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
     } else if (!dst || cap < total) {
         return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(total) + " bytes");
     }
-    auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
+    // an error return must not leave copies in flight to or from the caller's buffers (they are only borrowed for the call)
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        if (h->d2h_stream) cudaStreamSynchronize(h->d2h_stream);
+        if (alloc_out) std::free(dst);
+        return code;
+    };
     cudaStream_t st = h->stream, cs = h->copy_stream;
     const uint64_t ct_words = 2ull * L * h->ctx.ring_dim, out_words = 2ull * Lo * h->ctx.ring_dim;
     CUB(h->s_dense.reserve(n_ct * ct_words * 8));
@@ -1069,8 +1083,11 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             CU(cudaGetLastError());
             const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
             if ((rcode = decrypt_dense(h, dense, c1 - c0, m.meta[0].scaling_factor, h->s_out.as<double>() + first, last - first,
-                                       st, nullptr, m.ct_limbs)))
+                                       st, nullptr, m.ct_limbs))) {
+                cudaStreamSynchronize(cs);            // nothing stays in flight on the caller's buffers
+                cudaStreamSynchronize(h->d2h_stream);
                 return rcode;
+            }
             CU(cudaEventRecord(h->ev_stage_out, st));
             CU(cudaStreamWaitEvent(h->d2h_stream, h->ev_stage_out, 0));
             CU(cudaMemcpyAsync(out + first, h->s_out.as<double>() + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost,
@@ -1130,7 +1147,14 @@ int rescale_host(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t
     } else if (!dst || cap < plan.size) {
         return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(plan.size) + " bytes");
     }
-    auto bail = [&](int code) { if (alloc_out) std::free(dst); return code; };
+    // an error return must not leave copies in flight to or from the caller's buffers (they are only borrowed for the call)
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        if (h->d2h_stream) cudaStreamSynchronize(h->d2h_stream);
+        if (alloc_out) std::free(dst);
+        return code;
+    };
     const uint64_t N = h->ctx.ring_dim;
     cudaStream_t st = h->stream;
     CUB(h->s_image.reserve(image_bytes(blob_len)));
