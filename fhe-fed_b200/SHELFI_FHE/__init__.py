@@ -58,6 +58,7 @@ def lib() -> C.CDLL:
         "shelfi_gen_crypto_context_and_keygen_ex": (C.c_int, [vp, u32, u32]),
         "shelfi_set_sampler_seed": (C.c_int, [vp, u64]),
         "shelfi_clear_sampler_seed": (C.c_int, [vp]),
+        "shelfi_chacha20_block_device": (C.c_int, [vp, vp, u32, vp, vp]),
         "shelfi_ring_dim": (u32, [vp]),
         "shelfi_num_limbs": (u32, [vp]),
         "shelfi_slots": (u32, [vp]),

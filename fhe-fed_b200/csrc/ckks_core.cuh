@@ -48,6 +48,34 @@ struct __attribute__((aligned(16))) u64x2 { u64 x, y; };
 struct __attribute__((aligned(16))) double2 { double x, y; };
 #endif
 
+// L2 residency hints (fused encrypt).  A CTA parks values in global memory for its own later passes (m + e0 in a
+// not-yet-written output row, v^ in the c1 row) while it streams finished rows that nobody reads again; without hints
+// the streamed rows push the parked ones out of L2 before they are re-read or overwritten (round 1: 1.46x the
+// algorithmic DRAM bytes).  keep = a createpolicy evict_last descriptor (0: plain store), stream = st.global.cs.
+HD u64 make_keep_policy() {
+#ifdef __CUDA_ARCH__
+    u64 pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+#else
+    return 0;
+#endif
+}
+HD void st_pair(u64x2 *p, u64x2 v, u64 keep, bool stream) {
+#ifdef __CUDA_ARCH__
+    if (keep) {
+        asm volatile("st.global.L2::cache_hint.v2.u64 [%0], {%1, %2}, %3;" ::"l"(p), "l"(v.x), "l"(v.y), "l"(keep) : "memory");
+        return;
+    }
+    if (stream) {
+        asm volatile("st.global.cs.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v.x), "l"(v.y) : "memory");
+        return;
+    }
+#else
+    (void)keep; (void)stream;
+#endif
+    *p = v;
+}
 // Per-limb constants, passed to kernels by value inside RingConst.
 struct LimbConst {
     u64 q;          // modulus (<= 60 bits)
@@ -742,21 +770,61 @@ struct HeadLoad {
 };
 
 // ------------------------------------------------------------------------------------------
-// sampler: Philox4x32-10, counter layout shared with the CPU oracle
+// sampler: ChaCha20 in counter mode (the RFC 8439 block function, 20 rounds, 256-bit key).  Every draw of the
+// path — ternary v and Gaussian e0, e1 of Encrypt, ternary s, Gaussian e and uniform a of KeyGen — is a fixed
+// function of (key, nonce, block counter), so any thread can produce any coefficient's randomness on its own
+// and the CPU oracle reproduces the stream word for word under a test key (DESIGN.md §4.2 has the layout).
+// The reference draws the same quantities from PALISADE's Blake2-based PRNG seeded from OS entropy
+// (ckks.cpp:46,81,95); keys here come from getrandom(2), one per call, secret and public material under
+// independent keys (engine.cpp fresh_key).
 // ------------------------------------------------------------------------------------------
-HD void philox4x32_10(u64 seed, u32 c0, u32 c1, u32 c2, u32 c3, u32 (&out)[4]) {
-    u32 k0 = (u32)seed, k1 = (u32)(seed >> 32);
+HD u32 rotl32(u32 x, int n) {
+#ifdef __CUDA_ARCH__
+    return __funnelshift_l(x, x, n);
+#else
+    return (x << n) | (x >> (32 - n));
+#endif
+}
+#define SHELFI_CHACHA_QR(a, b, c, d)                  \
+    a += b; d ^= a; d = rotl32(d, 16);                \
+    c += d; b ^= c; b = rotl32(b, 12);                \
+    a += b; d ^= a; d = rotl32(d, 8);                 \
+    c += d; b ^= c; b = rotl32(b, 7);
+struct SamplerKey { u32 k[8]; };
+// state = "expand 32-byte k" | key | counter | nonce[3]; out = state + 20 rounds(state)
+HD void chacha20_block(const SamplerKey &key, u32 counter, u32 n0, u32 n1, u32 n2, u32 (&out)[16]) {
+    const u32 in[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u, key.k[0], key.k[1], key.k[2], key.k[3],
+                        key.k[4], key.k[5], key.k[6], key.k[7], counter, n0, n1, n2};
+    u32 x[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) x[i] = in[i];
 #pragma unroll
     for (int r = 0; r < 10; r++) {
-        u32 h0 = mulhi32(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
-        u32 h1 = mulhi32(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
-        u32 n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
-        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        SHELFI_CHACHA_QR(x[0], x[4], x[8], x[12])
+        SHELFI_CHACHA_QR(x[1], x[5], x[9], x[13])
+        SHELFI_CHACHA_QR(x[2], x[6], x[10], x[14])
+        SHELFI_CHACHA_QR(x[3], x[7], x[11], x[15])
+        SHELFI_CHACHA_QR(x[0], x[5], x[10], x[15])
+        SHELFI_CHACHA_QR(x[1], x[6], x[11], x[12])
+        SHELFI_CHACHA_QR(x[2], x[7], x[8], x[13])
+        SHELFI_CHACHA_QR(x[3], x[4], x[9], x[14])
     }
-    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+#pragma unroll
+    for (int i = 0; i < 16; i++) out[i] = x[i] + in[i];
 }
-enum { kStreamGauss = 0, kStreamTernary = 1, kStreamKeyS = 2, kStreamKeyE = 3, kStreamKeyA = 4 };
+// Test keys: shelfi_set_sampler_seed(seed) makes the engine deterministic; the 64-bit seed is laid into a key per
+// domain so that the CPU checker under oracle/ draws the same stream.  Never used for real data.
+enum { kKeyDomainEncrypt = 0, kKeyDomainKeySecret = 1, kKeyDomainKeyPublic = 2 };
+HD SamplerKey seed_key(u64 seed, u32 domain) {
+    SamplerKey k;
+    k.k[0] = (u32)seed; k.k[1] = (u32)(seed >> 32);
+    k.k[2] = 0x4c454853u; k.k[3] = 0x422d4946u; k.k[4] = 0x20303032u; k.k[5] = 0x64656573u;   // "SHELFI-B200 seed"
+    k.k[6] = domain; k.k[7] = 0;
+    return k;
+}
+// nonce word 2 names the stream; nonce words 0, 1 hold the ciphertext index (Encrypt) or (limb, attempt) (KeyGen a)
+enum { kStreamGauss = 0, kStreamTernary = 1, kStreamKeyS = 2, kStreamKeyE = 3, kStreamKeyA = 4, kStreamKeyTag = 5,
+       kStreamDecodeNoise = 6 };
 // magnitude = #{k : u >= cdf[k]} over a 32-entry table of floor(2^64 * P(|X| <= k)); bit 63 of r is the sign
 HD int gauss_from_u64(const u64 *cdf, u64 r) {
     u64 u = r << 1;
@@ -1034,7 +1102,7 @@ namespace shelfi {
 constexpr int kMaxLearnersPerLaunch = 16;
 
 struct SamplerConst {
-    u64 seed;
+    SamplerKey key;      // ChaCha20 key of this call (one learner's vector)
     u64 ct_index0;       // global index of the first ciphertext of this launch (shards draw the oracle's stream)
     u64 gauss_cdf[32];   // floor(2^64 * P(|X| <= k)), k = 0..31
 };
@@ -1082,7 +1150,7 @@ struct EncryptBatch {
     const u32 *sel;   // optional selection shared by the learners: learner l's vector is x[l][sel[i]]
     const double *x[kMaxEncryptBatch];
     u64 *ct[kMaxEncryptBatch];
-    u64 seed[kMaxEncryptBatch];
+    SamplerKey key[kMaxEncryptBatch];   // every learner's vector is encrypted under its own key
     u32 k, n_ct;
 };
 
@@ -1130,31 +1198,89 @@ HD i64 encode_coeff(const cplx *z, const EncodeConst &ec, u32 j) {
     if (idx & (ec.gap - 1)) return 0;
     return zi[2 * zsw(idx / ec.gap) + half];
 }
-// sampling + output of one group of four coefficients (ternary v, Gaussian e0, e1): [PAL] Encrypt's draws
-HD void sample_group(u32 j4, u64 ct_index, const SamplerConst &sc, const u64 *cdf, int (&v)[4], int (&e0)[4],
-                     int (&e1)[4]) {
-    u32 o[4];
-    philox4x32_10(sc.seed, j4, (u32)ct_index, (u32)(ct_index >> 32), kStreamTernary, o);
+// [PAL] Encrypt's draws for ciphertext `ct` (ckks.cpp:81,95), as counter-mode blocks:
+//   ternary block b, nonce (ct_lo, ct_hi, kStreamTernary): v[16 b + i] = floor(3 word_i / 2^32) - 1, i < 16
+//   Gaussian block b, nonce (ct_lo, ct_hi, kStreamGauss):  e0[4 b + i] from words (4i, 4i+1), e1[4 b + i] from words
+//                     (4i+2, 4i+3) as (low, high) halves of a 64-bit draw inverted through the CDF table
+// The small draws of one coefficient travel as one byte: bits 1..0 = v + 1, bits 7..2 = e1 + 32 (|e1| <= 31).
+HD uint8_t pack_ve(int v, int e1) { return (uint8_t)((u32)(v + 1) | ((u32)(e1 + 32) << 2)); }
+HD int ve_ternary(uint8_t b) { return (int)(b & 3u) - 1; }
+HD int ve_gauss(uint8_t b) { return (int)(b >> 2) - 32; }
+HD void sample_ternary_block(const SamplerKey &key, u64 ct, u32 b, u32 stream, int (&v)[16]) {
+    u32 o[16];
+    chacha20_block(key, b, (u32)ct, (u32)(ct >> 32), stream, o);
 #pragma unroll
-    for (int i = 0; i < 4; i++) v[i] = ternary_from_u32(o[i]);
+    for (int i = 0; i < 16; i++) v[i] = ternary_from_u32(o[i]);
+}
+HD void sample_gauss_block(const SamplerKey &key, const u64 *cdf, u64 ct, u32 b, int (&e0)[4], int (&e1)[4]) {
+    u32 o[16];
+    chacha20_block(key, b, (u32)ct, (u32)(ct >> 32), kStreamGauss, o);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        philox4x32_10(sc.seed, 4 * j4 + i, (u32)ct_index, (u32)(ct_index >> 32), kStreamGauss, o);
-        e0[i] = gauss_from_u64(cdf, ((u64)o[1] << 32) | o[0]);
-        e1[i] = gauss_from_u64(cdf, ((u64)o[3] << 32) | o[2]);
+        e0[i] = gauss_from_u64(cdf, ((u64)o[4 * i + 1] << 32) | o[4 * i]);
+        e1[i] = gauss_from_u64(cdf, ((u64)o[4 * i + 3] << 32) | o[4 * i + 2]);
     }
 }
-HD void encode_sample_emit(int tid, int nthreads, const cplx *z, const EncodeConst &ec, const SamplerConst &sc,
-                           const u64 *cdf, u64 ct_index, i64 *m_e0, uint16_t *ve) {
-    for (u32 j4 = tid; j4 < (u32)(kN >> 2); j4 += nthreads) {
-        int v[4], e0[4], e1[4];
-        sample_group(j4, ct_index, sc, cdf, v, e0, e1);
+// [PAL] KeyGen's draws (ckks.cpp:46): s <- ternary and e <- Gaussian under the SECRET key-generation key, a <- uniform
+// mod q_l per limb (EVALUATION form) and the key tag under the PUBLIC one.
+//   s[16 b + i]: ternary block b, nonce (0, 0, kStreamKeyS)
+//   e[8 b + i] : words (2i, 2i+1) of block b, nonce (0, 0, kStreamKeyE), through the CDF table
+//   a_l[j]     : attempt t = 0, 1, ...: words (2 (j & 7), 2 (j & 7) + 1) of block j >> 3, nonce (l, t, kStreamKeyA),
+//                top bits(q_l) bits of the 64-bit draw, accepted when below q_l
+HD void keygen_error_block(const SamplerKey &key, const u64 *cdf, u32 b, int (&e)[8]) {
+    u32 o[16];
+    chacha20_block(key, b, 0, 0, kStreamKeyE, o);
+#pragma unroll
+    for (int i = 0; i < 8; i++) e[i] = gauss_from_u64(cdf, ((u64)o[2 * i + 1] << 32) | o[2 * i]);
+}
+HD u64 keygen_uniform(const SamplerKey &key, u32 l, u32 j, u64 q) {
+    int qbits = 0;
+    while (qbits < 64 && (q >> qbits)) qbits++;
+    for (u32 t = 0;; t++) {
+        u32 o[16];
+        chacha20_block(key, j >> 3, l, t, kStreamKeyA, o);
+        u64 r = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            if ((u32)i == (j & 7u)) r = ((u64)o[2 * i + 1] << 32) | o[2 * i];
+        const u64 a = r >> (64 - qbits);
+        if (a < q) return a;
+    }
+}
+// phase 1 of the sampler: ve[j] = v[j] + 1 for the n coefficients of one ciphertext (16 bytes per thread and block)
+HD void sample_ternary_phase(int tid, int nthreads, const SamplerKey &key, u64 ct, u32 n, uint8_t *ve) {
+    for (u32 b = tid; b < (n >> 4); b += nthreads) {
+        int v[16];
+        sample_ternary_block(key, ct, b, kStreamTernary, v);
+        u32 w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            w[i] = (u32)(v[4 * i] + 1) | ((u32)(v[4 * i + 1] + 1) << 8) | ((u32)(v[4 * i + 2] + 1) << 16) |
+                   ((u32)(v[4 * i + 3] + 1) << 24);
+        u32 *dst = reinterpret_cast<u32 *>(ve + 16 * (size_t)b);
+        dst[0] = w[0]; dst[1] = w[1]; dst[2] = w[2]; dst[3] = w[3];
+    }
+}
+// phase 2 (after a barrier): m_e0[j] = coefficient j of the encoded message + e0[j]; e1[j] joins v[j] in ve[j].
+// `z` = the finalized FFT tile (ring dimension 8192), or null when m_e0 already holds the message (larger rings).
+HD void sample_gauss_phase(int tid, int nthreads, const cplx *z, const EncodeConst &ec, const SamplerKey &key,
+                           const u64 *cdf, u64 ct, u32 n, i64 *m_e0, uint8_t *ve, u64 keep = 0) {
+    for (u32 b = tid; b < (n >> 2); b += nthreads) {
+        int e0[4], e1[4];
+        sample_gauss_block(key, cdf, ct, b, e0, e1);
+        u32 *vw = reinterpret_cast<u32 *>(ve + 4 * (size_t)b);
+        u32 w = *vw;
+        u64 m[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            u32 j = 4 * j4 + i;
-            m_e0[j] = encode_coeff(z, ec, j) + (i64)e0[i];
-            ve[j] = (uint16_t)(((u32)v[i] & 0xFFu) | (((u32)e1[i] & 0xFFu) << 8));
+            const u32 j = 4 * b + i;
+            m[i] = (u64)((z ? encode_coeff(z, ec, j) : m_e0[j]) + (i64)e0[i]);
+            w |= (u32)(e1[i] + 32) << (8 * i + 2);
         }
+        *vw = w;
+        u64x2 *dst = reinterpret_cast<u64x2 *>(m_e0 + 4 * (size_t)b);
+        st_pair(dst, u64x2{m[0], m[1]}, keep, false);
+        st_pair(dst + 1, u64x2{m[2], m[3]}, keep, false);
     }
 }
 HD u64 small_to_mod(int x, u64 q) { return x >= 0 ? (u64)x : q - (u64)(-x); }
@@ -1247,18 +1373,6 @@ HD void encode_emit_block(int tid, int nthreads, const cplx *z, const EncodeCons
         for (u32 g = 1; g < ec.gap; g++) { m[idx + g] = 0; m[idx + nh + g] = 0; }
     }
 }
-// m += e0 ; ve = (v, e1): the sampler as a streaming pass over one ciphertext's N coefficients
-HD void sample_add_group(u32 j4, u64 ct_index, const SamplerConst &sc, const u64 *cdf, i64 *m_e0, uint16_t *ve) {
-    int v[4], e0[4], e1[4];
-    sample_group(j4, ct_index, sc, cdf, v, e0, e1);
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        u32 j = 4 * j4 + i;
-        m_e0[j] += (i64)e0[i];
-        ve[j] = (uint16_t)(((u32)v[i] & 0xFFu) | (((u32)e1[i] & 0xFFu) << 8));
-    }
-}
-
 // centred CRT value of coefficient j of a polynomial stored [L][n] -> double (and optionally its words)
 template <int L>
 HD double decode_value(const u64 *coeff, u32 n, u32 j, const Crt2Const &c2, const CrtNConst &cn, u64 *tap8) {
@@ -1394,12 +1508,12 @@ struct DLoadGlobal {
     HD double operator()(u32 i) const { return d_from_residue(p[i], q); }
 };
 struct DLoadTernary {
-    const uint16_t *ve;
-    HD double operator()(u32 i) const { return (double)(int)(int8_t)(ve[i] & 0xFF); }
+    const uint8_t *ve;
+    HD double operator()(u32 i) const { return (double)ve_ternary(ve[i]); }
 };
 struct DLoadGaussHi {
-    const uint16_t *ve;
-    HD double operator()(u32 i) const { return (double)(int)(int8_t)(ve[i] >> 8); }
+    const uint8_t *ve;
+    HD double operator()(u32 i) const { return (double)ve_gauss(ve[i]); }
 };
 struct DLoadSigned {
     const i64 *m; const LimbConst *lc;
@@ -1425,14 +1539,14 @@ struct StoreGlobal {
     u64 *p;
     HD void operator()(u32 i, u64 v) const { p[i] = v; }
 };
-// encrypt: ve[j] = v (low byte, int8) | e1 (high byte, int8); m[j] = m + e0 (signed)
+// encrypt: ve[j] = packed (v, e1) of coefficient j (pack_ve); m[j] = m + e0 (signed)
 struct LoadTernary {
-    const uint16_t *ve; u64 q;
-    HD u64 operator()(u32 i) const { return small_to_mod((int)(int8_t)(ve[i] & 0xFF), q); }
+    const uint8_t *ve; u64 q;
+    HD u64 operator()(u32 i) const { return small_to_mod(ve_ternary(ve[i]), q); }
 };
 struct LoadGaussHi {
-    const uint16_t *ve; u64 q;
-    HD u64 operator()(u32 i) const { return small_to_mod((int)(int8_t)(ve[i] >> 8), q); }
+    const uint8_t *ve; u64 q;
+    HD u64 operator()(u32 i) const { return small_to_mod(ve_gauss(ve[i]), q); }
 };
 struct LoadSigned {
     const i64 *m; const LimbConst *lc;
@@ -1444,15 +1558,17 @@ struct LoadSigned {
 struct StoreLazyPair {
     typedef NoAux Aux;
     static constexpr int kGroup = 4;
-    u64 *park;
+    u64 *park; u64 keep;
     HD Aux fetch(u32) const { return Aux{}; }
-    HD void operator()(u32 vt, u64 x, u64 y, const Aux &) const { reinterpret_cast<u64x2 *>(park)[vt] = u64x2{x, y}; }
+    HD void operator()(u32 vt, u64 x, u64 y, const Aux &) const {
+        st_pair(reinterpret_cast<u64x2 *>(park) + vt, u64x2{x, y}, keep, false);
+    }
 };
 struct PkAux { u64x2 v, k0, k1; };
 struct StoreMulAdd {
     typedef PkAux Aux;
     static constexpr int kGroup = 2;
-    const tw_t *key; const u64 *park; u64 *out; const LimbConst *lc;
+    const tw_t *key; const u64 *park; u64 *out; const LimbConst *lc; bool stream;
     HD Aux fetch(u32 vt) const {
         const u64x2 *kp = reinterpret_cast<const u64x2 *>(key) + 2 * vt;
         return Aux{reinterpret_cast<const u64x2 *>(park)[vt], ld_readonly(kp), ld_readonly(kp + 1)};
@@ -1461,7 +1577,7 @@ struct StoreMulAdd {
         const u64 q = lc->q, q2 = lc->q2, nq = lc->nq;
         u64 r0 = shoup_lazy_nq(a.v.x, a.k0.x, a.k0.y, nq) + quick_reduce(x, *lc);   // < 4q
         u64 r1 = shoup_lazy_nq(a.v.y, a.k1.x, a.k1.y, nq) + quick_reduce(y, *lc);
-        reinterpret_cast<u64x2 *>(out)[vt] = u64x2{csub(csub(r0, q2), q), csub(csub(r1, q2), q)};
+        st_pair(reinterpret_cast<u64x2 *>(out) + vt, u64x2{csub(csub(r0, q2), q), csub(csub(r1, q2), q)}, 0, stream);
     }
 };
 // rescale (PALISADE DCRTPoly::DropLastElementAndScale): the dropped tower's coefficients t (canonical, mod q_last) enter

@@ -9,15 +9,17 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cerrno>
 #include <cstring>
 #include <condition_variable>
 #include <functional>
 #include <map>
 #include <mutex>
 #include <thread>
-#include <random>
 #include <string>
 #include <vector>
+
+#include <sys/random.h>
 
 #include "kernels.h"
 #include "numtheory.h"
@@ -453,9 +455,27 @@ int64_t weight_constant(const shelfi_ckks *h, float w) {
     return (int64_t)(sc * (double)h->ctx.modulus[h->ctx.limbs - 1] + 0.5);
 }
 
-uint64_t fresh_seed() {
-    std::random_device rd;
-    return ((uint64_t)rd() << 32) ^ (uint64_t)rd() ^ ((uint64_t)rd() << 16);
+// 256 bits from the kernel's CSPRNG (getrandom(2), blocking until the pool is initialised): one ChaCha20 key per
+// encrypt call and learner, two independent ones per key generation (secret material / public material).  The
+// reference gets the same from PALISADE's PRNG, which seeds itself from OS entropy.
+bool fresh_key(SamplerKey *k) {
+    unsigned char *p = reinterpret_cast<unsigned char *>(k->k);
+    size_t got = 0;
+    while (got < sizeof k->k) {
+        ssize_t r = getrandom(p + got, sizeof k->k - got, 0);
+        if (r < 0) {
+            if (errno == EINTR) continue;
+            return false;
+        }
+        got += (size_t)r;
+    }
+    return true;
+}
+// the key of one call: from the OS, or (tests) laid out from the fixed seed for the given domain
+int call_key(shelfi_ckks *h, uint32_t domain, SamplerKey *k) {
+    if (h->seeded) { *k = seed_key(h->seed, domain); return 0; }
+    if (!fresh_key(k)) return fail(h, SHELFI_ERR_IO, std::string("getrandom failed: ") + std::strerror(errno));
+    return 0;
 }
 
 // --- stage drivers (all asynchronous on `s`) ---
@@ -478,7 +498,7 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
         const bool overlap = k > 1;
         const size_t m_words = (size_t)n_ct * N;
         CU(h->s_m.reserve((overlap ? 2 : 1) * m_words * sizeof(int64_t)));
-        CU(h->s_ve.reserve((overlap ? 2 : 1) * m_words * sizeof(uint16_t)));
+        CU(h->s_ve.reserve((overlap ? 2 : 1) * m_words * sizeof(uint8_t)));
         cudaStream_t es = s;
         if (overlap) {
             if (!h->enc_stream) {
@@ -496,8 +516,9 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
         for (uint32_t i = 0; i < k; i++) {
             const int b = overlap ? (int)(i & 1) : 0;
             i64 *m_slot = h->s_m.as<i64>() + (size_t)b * m_words;
-            uint16_t *ve_slot = h->s_ve.as<uint16_t>() + (size_t)b * m_words;
-            sc.seed = h->seeded ? h->seed : fresh_seed();
+            uint8_t *ve_slot = h->s_ve.as<uint8_t>() + (size_t)b * m_words;
+            int krc = call_key(h, kKeyDomainEncrypt, &sc.key);
+            if (krc) return krc;
             if (overlap && i >= 2) CU(cudaStreamWaitEvent(es, h->ev_enc_free[b], 0));   // slot b was read by learner i-2
             timed(h, kKEncodeSample, es, [&] {
                 launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, m_slot, ve_slot, es, d_sel);
@@ -520,16 +541,14 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
         eb.k = std::min<uint32_t>(kMaxEncryptBatch, k - base);
         eb.n_ct = (u32)n_ct;
         eb.sel = d_sel;
-        CU(h->s_m.reserve((size_t)eb.k * n_ct * N * sizeof(int64_t)));
-        CU(h->s_ve.reserve((size_t)eb.k * n_ct * N * sizeof(uint16_t)));
         for (uint32_t i = 0; i < eb.k; i++) {
             eb.x[i] = d_x[base + i];
             eb.ct[i] = reinterpret_cast<u64 *>(d_ct[base + i]);
-            eb.seed[i] = h->seeded ? h->seed : fresh_seed();
+            int krc = call_key(h, kKeyDomainEncrypt, &eb.key[i]);
+            if (krc) return krc;
         }
         timed(h, kKEncrypt, s, [&] {
-            launch_encrypt_fused(h->rc, h->ec, sc, eb, n, h->s_m.as<i64>(), h->s_ve.as<uint16_t>(), h->d_pk_b.as<tw_t>(),
-                                 h->d_pk_a.as<tw_t>(), s);
+            launch_encrypt_fused(h->rc, h->ec, sc, eb, n, h->d_pk_b.as<tw_t>(), h->d_pk_a.as<tw_t>(), s);
         });
     }
     CU(cudaGetLastError());
@@ -1346,52 +1365,42 @@ int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth,
                            for (int i = 0; i < 2; i++) { if (tmp.ev_copy[i]) cudaEventDestroy(tmp.ev_copy[i]);
                                                          if (tmp.ev_done[i]) cudaEventDestroy(tmp.ev_done[i]); } };
     if (ensure_cuda(&tmp) || install_context(&tmp, p)) { h->err = tmp.err; cleanup(); return 0; }
-    const uint64_t seed = h->seeded ? h->seed : fresh_seed();
+    // Secret material (s, e) and public material (a, the key tag) are drawn under independent keys, so nothing that
+    // is published carries information about the stream that produced the secret key.
+    SamplerConst secret{};
+    SamplerKey pubkey;
+    if (call_key(h, kKeyDomainKeySecret, &secret.key) || call_key(h, kKeyDomainKeyPublic, &pubkey)) { cleanup(); return 0; }
+    std::memcpy(secret.gauss_cdf, tmp.gauss_cdf, sizeof secret.gauss_cdf);
     const size_t LN = (size_t)L * N;
-    std::vector<uint64_t> rows(2 * LN);  // s limbs 0..L-1, then e limbs 0..L-1
-    u32 o[4];
-    for (uint32_t j = 0; j < N; j++) {
-        philox4x32_10(seed, j >> 2, 0, 0, kStreamKeyS, o);
-        int sv = ternary_from_u32(o[j & 3]);
-        philox4x32_10(seed, j, 0, 0, kStreamKeyE, o);
-        int ev = gauss_from_u64(tmp.gauss_cdf, ((uint64_t)o[1] << 32) | o[0]);
-        for (int l = 0; l < L; l++) {
-            rows[(size_t)l * N + j] = nt::signed_mod(sv, p.modulus[l]);
-            rows[LN + (size_t)l * N + j] = nt::signed_mod(ev, p.modulus[l]);
-        }
-    }
-    bool ok = tmp.s_rows.reserve(rows.size() * 8) == cudaSuccess && tmp.s_dense.reserve(rows.size() * 8) == cudaSuccess &&
-              cudaMemcpy(tmp.s_rows.p, rows.data(), rows.size() * 8, cudaMemcpyHostToDevice) == cudaSuccess;
+    std::vector<uint64_t> s_hat(LN), a_rows(LN), b_rows(LN);
+    DeviceBuffer d_a, d_b, d_tag;
+    bool ok = tmp.s_rows.reserve(2 * LN * 8) == cudaSuccess && tmp.s_dense.reserve(2 * LN * 8) == cudaSuccess &&
+              d_a.reserve(LN * 8) == cudaSuccess && d_b.reserve(LN * 8) == cudaSuccess && d_tag.reserve(64) == cudaSuccess;
+    uint32_t tag_words[16] = {0};
     if (ok) {
+        launch_keygen_sample(tmp.rc, secret, pubkey, tmp.s_rows.as<u64>(), d_a.as<u64>(), tmp.stream);
         launch_ntt_forward(tmp.rc, tmp.s_rows.as<u64>(), tmp.s_dense.as<u64>(), 2 * (u32)L, tmp.stream);
+        launch_keygen_combine(tmp.rc, tmp.s_dense.as<u64>(), d_a.as<u64>(), d_b.as<u64>(), tmp.stream);
+        launch_chacha20_block(pubkey, 0, 0, 0, kStreamKeyTag, d_tag.as<u32>(), tmp.stream);
         ok = cudaStreamSynchronize(tmp.stream) == cudaSuccess &&
-             cudaMemcpy(rows.data(), tmp.s_dense.p, rows.size() * 8, cudaMemcpyDeviceToHost) == cudaSuccess;
+             cudaMemcpy(s_hat.data(), tmp.s_dense.p, LN * 8, cudaMemcpyDeviceToHost) == cudaSuccess &&
+             cudaMemcpy(a_rows.data(), d_a.p, LN * 8, cudaMemcpyDeviceToHost) == cudaSuccess &&
+             cudaMemcpy(b_rows.data(), d_b.p, LN * 8, cudaMemcpyDeviceToHost) == cudaSuccess &&
+             cudaMemcpy(tag_words, d_tag.p, 64, cudaMemcpyDeviceToHost) == cudaSuccess;
+        // the secret key and its error never stay behind in device memory
+        cudaMemsetAsync(tmp.s_rows.p, 0, 2 * LN * 8, tmp.stream);
+        cudaMemsetAsync(tmp.s_dense.p, 0, 2 * LN * 8, tmp.stream);
+        cudaStreamSynchronize(tmp.stream);
     }
-    if (!ok) { fail(h, SHELFI_ERR_CUDA, "key generation transforms failed"); cleanup(); return 0; }
+    d_a.release(); d_b.release(); d_tag.release();
+    if (!ok) { fail(h, SHELFI_ERR_CUDA, "key generation kernels failed"); cleanup(); return 0; }
     wire::KeyFile pub, priv;
     pub.ctx = p; priv.ctx = p;
-    pub.polys.assign(2 * LN, 0);
-    priv.polys.assign(rows.begin(), rows.begin() + LN);
-    for (int l = 0; l < L; l++) {
-        const uint64_t q = p.modulus[l];
-        const int qbits = 64 - __builtin_clzll(q);
-        for (uint32_t j = 0; j < N; j++) {
-            uint64_t a;
-            uint32_t tries = 0;
-            do {  // uniform below q by rejection on the top bits of a 64-bit draw
-                philox4x32_10(seed, j, (u32)l, tries++, kStreamKeyA, o);
-                a = (((uint64_t)o[1] << 32) | o[0]) >> (64 - qbits);
-            } while (a >= q);
-            uint64_t sv = rows[(size_t)l * N + j], ev = rows[LN + (size_t)l * N + j];
-            pub.polys[LN + (size_t)l * N + j] = a;
-            pub.polys[(size_t)l * N + j] = nt::sub_mod(ev, nt::mul_mod(a, sv, q), q);
-        }
-    }
-    char tag[33];
-    for (int i = 0; i < 8; i++) {  // [PAL] GenerateUniqueKeyID: 32 hex characters
-        philox4x32_10(seed, (u32)i, 0, 0, 99, o);
-        std::snprintf(tag + 4 * i, 5, "%04x", o[0] & 0xffff);
-    }
+    pub.polys.assign(b_rows.begin(), b_rows.end());
+    pub.polys.insert(pub.polys.end(), a_rows.begin(), a_rows.end());
+    priv.polys.assign(s_hat.begin(), s_hat.end());
+    char tag[33];   // [PAL] GenerateUniqueKeyID: 32 hex characters
+    std::snprintf(tag, sizeof tag, "%08x%08x%08x%08x", tag_words[0], tag_words[1], tag_words[2], tag_words[3]);
     pub.tag = tag; priv.tag = tag;
     cleanup();
     if (!write_file(h->cryptodir + "key-public.txt", wire::emit_public_key(pub))) {  // ckks.cpp:48
@@ -1407,12 +1416,33 @@ int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth,
 
 int shelfi_set_sampler_seed(shelfi_ckks *h, uint64_t seed) {
     if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
     h->seeded = true; h->seed = seed;
     return 0;
 }
 int shelfi_clear_sampler_seed(shelfi_ckks *h) {
     if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
     h->seeded = false;
+    return 0;
+}
+// known-answer tap of the device sampler: one ChaCha20 block (key 8 words, counter, nonce 3 words -> 16 words)
+int shelfi_chacha20_block_device(shelfi_ckks *h, const uint32_t key[8], uint32_t counter, const uint32_t nonce[3],
+                                 uint32_t out[16]) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    if (!key || !nonce || !out) return fail(h, SHELFI_ERR_ARG, "null argument");
+    SamplerKey k;
+    std::memcpy(k.k, key, sizeof k.k);
+    DeviceBuffer d;
+    CU(d.reserve(64));
+    launch_chacha20_block(k, counter, nonce[0], nonce[1], nonce[2], d.as<u32>(), h->stream);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    if (e == cudaSuccess) e = cudaMemcpy(out, d.p, 64, cudaMemcpyDeviceToHost);
+    d.release();
+    if (e != cudaSuccess) return cuda_fail(h, e, "chacha20 block");
     return 0;
 }
 

@@ -312,16 +312,12 @@ __global__ void __launch_bounds__(kTailThreads) intt_tail_kernel(const __grid_co
 // ------------------------------------------------------------------------------------------
 // encode (+ sampler): one CTA per ciphertext, FFT tile in shared memory
 // ------------------------------------------------------------------------------------------
-template <bool SAMPLE>
-__global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_constant__ EncodeConst ec,
-                                                             const __grid_constant__ SamplerConst sc, const double *x,
-                                                             u64 n, i64 *m_e0, uint16_t *ve, const u32 *sel) {
+__global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_constant__ EncodeConst ec, const double *x,
+                                                             u64 n, i64 *m, const u32 *sel) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
-    __shared__ u64 cdf[32];
     const int tid = threadIdx.x;
     const u64 ct = blockIdx.x;
-    if (SAMPLE && tid < 32) cdf[tid] = sc.gauss_cdf[tid];
     u64 first = ct * ec.batch;
     u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
     encode_load(tid, kFftThreads, z, ec, sel ? x : x + first, n_valid, sel ? sel + first : nullptr);
@@ -339,17 +335,13 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
     }
     encode_finalize(tid, kFftThreads, z, ec);
     __syncthreads();
-    i64 *mrow = m_e0 + ct * (u64)kN;
-    if (SAMPLE) {
-        encode_sample_emit(tid, kFftThreads, z, ec, sc, cdf, sc.ct_index0 + ct, mrow, ve + ct * (u64)kN);
-    } else {
-        for (u32 j = tid; j < (u32)kN; j += kFftThreads) mrow[j] = encode_coeff(z, ec, j);
-    }
+    i64 *mrow = m + ct * (u64)kN;
+    for (u32 j = tid; j < (u32)kN; j += kFftThreads) mrow[j] = encode_coeff(z, ec, j);
 }
 
 // Ring dimensions / slot counts above one tile: one CTA per (ciphertext, FFT block), message coefficients only;
-// sample_add_kernel then adds e0 and writes (v, e1) as a streaming pass (the sampler draws per group of four
-// consecutive coefficients, the FFT blocks own strided ones).
+// sample_add_kernel then adds e0 and writes (v, e1) as a pass of its own (the sampler draws blocks of consecutive
+// coefficients, the FFT blocks own strided ones).
 template <int DF>
 __global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_constant__ EncodeConst ec, u32 n_ring,
                                                                    const double *x, u64 n, i64 *m, const u32 *sel) {
@@ -381,14 +373,15 @@ __global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_
 }
 constexpr int kSampleThreads = 256;
 __global__ void __launch_bounds__(kSampleThreads) sample_add_kernel(const __grid_constant__ SamplerConst sc, u32 n_ring,
-                                                                    i64 *m_e0, uint16_t *ve) {
+                                                                    i64 *m_e0, uint8_t *ve) {
     __shared__ u64 cdf[32];
     if (threadIdx.x < 32) cdf[threadIdx.x] = sc.gauss_cdf[threadIdx.x];
-    __syncthreads();
-    const u64 ct = blockIdx.y;
-    const u32 j4 = blockIdx.x * kSampleThreads + threadIdx.x;
-    if (j4 < (n_ring >> 2))
-        sample_add_group(j4, sc.ct_index0 + ct, sc, cdf, m_e0 + ct * (u64)n_ring, ve + ct * (u64)n_ring);
+    const u64 ct = blockIdx.x;
+    uint8_t *ve_row = ve + ct * (u64)n_ring;
+    sample_ternary_phase(threadIdx.x, kSampleThreads, sc.key, sc.ct_index0 + ct, n_ring, ve_row);
+    __syncthreads();   // the bytes written above are completed by other threads of this block below
+    sample_gauss_phase(threadIdx.x, kSampleThreads, nullptr, EncodeConst{}, sc.key, cdf, sc.ct_index0 + ct, n_ring,
+                       m_e0 + ct * (u64)n_ring, ve_row);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -411,7 +404,7 @@ __device__ __forceinline__ void ntt_forward_tile(int tid, u64 *sm, const LimbCon
 
 template <int D>
 __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_constant__ RingConst rc, const i64 *m_e0,
-                                                                 const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
+                                                                 const uint8_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                                                                  u64 *ct_out) {
     extern __shared__ __align__(16) u64 sm[];
     const int tid = threadIdx.x;
@@ -423,7 +416,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     const u64 ct = poly / L;
     const u64 n = (u64)kN << D;
     const LimbConst lc = rc.limb[l];
-    const uint16_t *ve_row = ve + ct * n;
+    const uint8_t *ve_row = ve + ct * n;
     const i64 *m_row = m_e0 + ct * n;
     const size_t tile_off = (size_t)blk * kN;
     u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * n + tile_off;
@@ -432,66 +425,74 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
     if (cluster_head_for(D)) {   // the 2^D tiles of this (ciphertext, limb) are one cluster: head stages through DSMEM
         if (lc.dtw) {
             cluster_head_d<D>(tid, sm, lc, DLoadTernary{ve_row});
-            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreLazyPair{c1});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreLazyPair{c1, 0});
             cluster_head_d<D>(tid, sm, lc, DLoadSigned{m_row, &lc});
-            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreMulAdd{kb, c1, c0, &lc});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreMulAdd{kb, c1, c0, &lc, false});
             cluster_head_d<D>(tid, sm, lc, DLoadGaussHi{ve_row});
-            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreMulAdd{ka, c1, c1, &lc});
+            ntt_forward_tile_d(tid, sm, lc, hb, DLoadTile{sm}, StoreMulAdd{ka, c1, c1, &lc, false});
             return;
         }
         cluster_head<D>(tid, sm, lc, LoadTernary{ve_row, lc.q});
-        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreLazyPair{c1});
+        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreLazyPair{c1, 0});
         cluster_head<D>(tid, sm, lc, LoadSigned{m_row, &lc});
-        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreMulAdd{kb, c1, c0, &lc});
+        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreMulAdd{kb, c1, c0, &lc, false});
         cluster_head<D>(tid, sm, lc, LoadGaussHi{ve_row, lc.q});
-        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreMulAdd{ka, c1, c1, &lc});
+        ntt_forward_tile(tid, sm, lc, hb, LoadTile{sm}, StoreMulAdd{ka, c1, c1, &lc, false});
         return;
     }
     if (lc.dtw) {
-        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve_row}, &lc, blk}, StoreLazyPair{c1});
+        ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve_row}, &lc, blk}, StoreLazyPair{c1, 0});
         __syncthreads();
         ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadSigned>{DLoadSigned{m_row, &lc}, &lc, blk},
-                           StoreMulAdd{kb, c1, c0, &lc});
+                           StoreMulAdd{kb, c1, c0, &lc, false});
         __syncthreads();
         ntt_forward_tile_d(tid, sm, lc, hb, DHeadLoad<D, DLoadGaussHi>{DLoadGaussHi{ve_row}, &lc, blk},
-                           StoreMulAdd{ka, c1, c1, &lc});
+                           StoreMulAdd{ka, c1, c1, &lc, false});
         return;
     }
-    ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve_row, lc.q}, &lc, blk}, StoreLazyPair{c1});
+    ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve_row, lc.q}, &lc, blk}, StoreLazyPair{c1, 0});
     __syncthreads();
     ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadSigned>{LoadSigned{m_row, &lc}, &lc, blk},
-                     StoreMulAdd{kb, c1, c0, &lc});
+                     StoreMulAdd{kb, c1, c0, &lc, false});
     __syncthreads();
     ntt_forward_tile(tid, sm, lc, hb, HeadLoad<D, LoadGaussHi>{LoadGaussHi{ve_row, lc.q}, &lc, blk},
-                     StoreMulAdd{ka, c1, c1, &lc});
+                     StoreMulAdd{ka, c1, c1, &lc, false});
 }
 
-// Fused encrypt: one CTA per ciphertext does encode + sampling (FFT tile), parks m+e0 / (v,e1) in global scratch
-// (L2-resident, 80 KiB per ciphertext), then reuses the same 64 KiB tile for the 3 NTTs of every limb.  Compared
-// with encode_kernel + encrypt_kernel this samples once per ciphertext, removes one launch and its partial
-// wave, and lets the latency-bound FFT/sampler phases of one CTA hide under the integer work of its two
-// co-resident CTAs.
+// Fused encrypt (ring dimension 8192): one CTA per ciphertext does encode + sampling in the FFT tile, then reuses the
+// same 64 KiB tile for the 3 NTTs of every limb.  Nothing of a ciphertext's intermediate state has a buffer of its
+// own: the packed (v, e1) draws (1 byte per coefficient) stay in 8 KiB of shared memory, and m + e0 (int64) is parked
+// in the c0 row of the limb this CTA transforms LAST — an output row that is not written until that limb's own
+// NTT(m + e0), which reads all of it (pass A) before any thread stores to it (pass E).  Compared with
+// encode_kernel + sample_add_kernel + encrypt_kernel this samples once per ciphertext, is one launch, lets the
+// latency-bound FFT / sampler phases of one CTA hide under the transforms of its two co-resident CTAs, and (round 2)
+// moves no scratch bytes to DRAM.
 __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __grid_constant__ RingConst rc,
                                                                        const __grid_constant__ EncodeConst ec,
                                                                        const __grid_constant__ SamplerConst sc,
                                                                        const __grid_constant__ EncryptBatch eb,
-                                                                       u64 n, i64 *m_e0, uint16_t *ve,
-                                                                       const tw_t *pk_b, const tw_t *pk_a) {
+                                                                       u64 n, const tw_t *pk_b, const tw_t *pk_a) {
     extern __shared__ __align__(16) u64 sm[];
     cplx *z = reinterpret_cast<cplx *>(sm);
     __shared__ u64 cdf[32];
+    __shared__ __align__(16) uint8_t ve[kN];
     const int tid = threadIdx.x;
     const u32 learner = blockIdx.x / eb.n_ct;
     const u64 ct = blockIdx.x % eb.n_ct;
     const double *x = eb.x[learner];
     u64 *ct_out = eb.ct[learner];
-    SamplerConst sl;   // per-learner seed; the CDF lives in shared memory
-    sl.seed = eb.seed[learner]; sl.ct_index0 = sc.ct_index0;
+    const u64 ct_index = sc.ct_index0 + ct;
     if (tid < 32) cdf[tid] = sc.gauss_cdf[tid];
     const u64 first = ct * ec.batch;
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
-    i64 *m_row = m_e0 + (u64)blockIdx.x * (u64)kN;
-    uint16_t *ve_row = ve + (u64)blockIdx.x * (u64)kN;
+    const u32 L = rc.limbs;
+    // odd CTAs walk the limbs backwards: co-resident CTAs then tend to sit on different pipes (the 60-bit limb on the
+    // integer pipe, the scaling limbs on the FP64 pipe) instead of marching through the same limb together
+    const u32 flip = (blockIdx.x & 1u) ? L - 1 : 0u;
+    const u32 l_last = flip ? 0u : L - 1;
+    i64 *m_row = reinterpret_cast<i64 *>(ct_out + ((ct * 2 + 0) * L + l_last) * (u64)kN);
+    const u64 keep = make_keep_policy();
+    sample_ternary_phase(tid, kNttThreads, eb.key[learner], ct_index, kN, ve);   // touches only `ve`
     encode_load(tid, kNttThreads, z, ec, eb.sel ? x : x + first, n_valid, eb.sel ? eb.sel + first : nullptr);
     __syncthreads();
     if (ec.slots == kFftFast) {
@@ -507,34 +508,92 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     }
     encode_finalize(tid, kNttThreads, z, ec);
     __syncthreads();
-    encode_sample_emit(tid, kNttThreads, z, ec, sl, cdf, sl.ct_index0 + ct, m_row, ve_row);
-    __syncthreads();  // scratch rows written by this block are visible to all of its threads; tile is free
-    const u32 L = rc.limbs;
-    // odd CTAs walk the limbs backwards: co-resident CTAs then tend to sit on different pipes (the 60-bit limb on the
-    // integer pipe, the scaling limbs on the FP64 pipe) instead of marching through the same limb together
-    const u32 flip = (blockIdx.x & 1u) ? L - 1 : 0u;
+    sample_gauss_phase(tid, kNttThreads, z, ec, eb.key[learner], cdf, ct_index, kN, m_row, ve, keep);
+    __syncthreads();  // the parked row and `ve` are visible to all threads of the block; the tile is free
     for (u32 li = 0; li < L; li++) {
         const u32 l = flip ? flip - li : li;
         const LimbConst lc = rc.limb[l];
         u64 *c0 = ct_out + ((ct * 2 + 0) * L + l) * (u64)kN;
         u64 *c1 = ct_out + ((ct * 2 + 1) * L + l) * (u64)kN;
+        const StoreMulAdd st0{pk_b + (size_t)l * kN, c1, c0, &lc, true}, st1{pk_a + (size_t)l * kN, c1, c1, &lc, true};
         if (lc.dtw) {
-            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadTernary{ve_row}, StoreLazyPair{c1});
+            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadTernary{ve}, StoreLazyPair{c1, keep});
             __syncthreads();
-            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
+            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadSigned{m_row, &lc}, st0);
             __syncthreads();
-            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadGaussHi{ve_row}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
+            ntt_forward_tile_d(tid, sm, lc, 1u, DLoadGaussHi{ve}, st1);
             __syncthreads();
             continue;
         }
-        ntt_forward_tile(tid, sm, lc, 1u, LoadTernary{ve_row, lc.q},
-                         StoreLazyPair{c1});
+        ntt_forward_tile(tid, sm, lc, 1u, LoadTernary{ve, lc.q}, StoreLazyPair{c1, keep});
         __syncthreads();
-        ntt_forward_tile(tid, sm, lc, 1u, LoadSigned{m_row, &lc}, StoreMulAdd{pk_b + (size_t)l * kN, c1, c0, &lc});
+        ntt_forward_tile(tid, sm, lc, 1u, LoadSigned{m_row, &lc}, st0);
         __syncthreads();
-        ntt_forward_tile(tid, sm, lc, 1u, LoadGaussHi{ve_row, lc.q}, StoreMulAdd{pk_a + (size_t)l * kN, c1, c1, &lc});
+        ntt_forward_tile(tid, sm, lc, 1u, LoadGaussHi{ve, lc.q}, st1);
         __syncthreads();
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// key generation ([PAL] LPAlgorithmCKKS::KeyGen, ckks.cpp:46) on the device:
+//   keygen_sample_kernel : rows[0..L) = s, rows[L..2L) = e reduced into every limb (coefficient form), a[L][N] uniform
+//   (ntt_forward_kernel over the 2L rows)
+//   keygen_combine_kernel: b = e^ - a * s^ per limb
+// ------------------------------------------------------------------------------------------
+constexpr int kKeygenThreads = 256;
+__global__ void __launch_bounds__(kKeygenThreads) keygen_sample_kernel(const __grid_constant__ RingConst rc,
+                                                                       const __grid_constant__ SamplerConst secret,
+                                                                       const __grid_constant__ SamplerKey pub, u64 *rows,
+                                                                       u64 *a) {
+    const u32 n = rc.n, L = rc.limbs;
+    const u32 t = blockIdx.x * kKeygenThreads + threadIdx.x, stride = gridDim.x * kKeygenThreads;
+    for (u32 b = t; b < (n >> 4); b += stride) {
+        int sv[16];
+        sample_ternary_block(secret.key, 0, b, kStreamKeyS, sv);
+        for (u32 l = 0; l < L; l++)
+#pragma unroll
+            for (int i = 0; i < 16; i++) rows[(size_t)l * n + 16 * b + i] = small_to_mod(sv[i], rc.limb[l].q);
+    }
+    for (u32 b = t; b < (n >> 3); b += stride) {
+        int ev[8];
+        keygen_error_block(secret.key, secret.gauss_cdf, b, ev);
+        for (u32 l = 0; l < L; l++)
+#pragma unroll
+            for (int i = 0; i < 8; i++) rows[(size_t)(L + l) * n + 8 * b + i] = small_to_mod(ev[i], rc.limb[l].q);
+    }
+    for (u32 i = t; i < L * n; i += stride) {
+        const u32 l = i / n, j = i - l * n;
+        a[i] = keygen_uniform(pub, l, j, rc.limb[l].q);
+    }
+}
+__global__ void __launch_bounds__(kKeygenThreads) keygen_combine_kernel(const __grid_constant__ RingConst rc,
+                                                                        const u64 *rows_hat, const u64 *a, u64 *b) {
+    const u32 n = rc.n, L = rc.limbs;
+    const u32 i = blockIdx.x * kKeygenThreads + threadIdx.x;
+    if (i >= L * n) return;
+    const LimbConst &lc = rc.limb[i / n];
+    acc128 p{0, 0};
+    mac128(p, a[i], rows_hat[i]);                       // a * s^ as a 128-bit integer
+    const u64 as = reduce128(p, lc), e = rows_hat[(size_t)L * n + i];
+    b[i] = csub(e + lc.q - as, lc.q);
+}
+void launch_keygen_sample(const RingConst &rc, const SamplerConst &secret, const SamplerKey &pub, u64 *rows, u64 *a,
+                          cudaStream_t s) {
+    keygen_sample_kernel<<<(rc.limbs * rc.n + kKeygenThreads - 1) / kKeygenThreads, kKeygenThreads, 0, s>>>(rc, secret, pub,
+                                                                                                         rows, a);
+}
+void launch_keygen_combine(const RingConst &rc, const u64 *rows_hat, const u64 *a, u64 *b, cudaStream_t s) {
+    keygen_combine_kernel<<<(rc.limbs * rc.n + kKeygenThreads - 1) / kKeygenThreads, kKeygenThreads, 0, s>>>(rc, rows_hat,
+                                                                                                          a, b);
+}
+// known-answer tap of the device sampler: one ChaCha20 block (RFC 8439 2.3.2 test vector in tests/)
+__global__ void chacha20_block_kernel(const __grid_constant__ SamplerKey key, u32 counter, u32 n0, u32 n1, u32 n2, u32 *out) {
+    u32 o[16];
+    chacha20_block(key, counter, n0, n1, n2, o);
+    for (int i = 0; i < 16; i++) out[i] = o[i];
+}
+void launch_chacha20_block(const SamplerKey &key, u32 counter, u32 n0, u32 n1, u32 n2, u32 *out, cudaStream_t s) {
+    chacha20_block_kernel<<<1, 1, 0, s>>>(key, counter, n0, n1, n2, out);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -850,8 +909,7 @@ cudaError_t kernels_init() {
     OPT_IN_D(rescale_intt_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(rescale_ntt_kernel, NTT_SMEM_BYTES)
     OPT_IN(encrypt_fused_kernel, NTT_SMEM_BYTES)
-    OPT_IN(encode_kernel<true>, kFftFast * sizeof(cplx))
-    OPT_IN(encode_kernel<false>, kFftFast * sizeof(cplx))
+    OPT_IN(encode_kernel, kFftFast * sizeof(cplx))
     OPT_IN(decode_kernel, kFftFast * sizeof(cplx))
     OPT_IN_D(encode_block_kernel, kFftFast * sizeof(cplx))
     OPT_IN_D(decode_fft_kernel, kFftFast * sizeof(cplx))
@@ -887,37 +945,32 @@ void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s
     if (rc.log_blocks == 1) intt_tail_kernel<1><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, data);
     if (rc.log_blocks == 2) intt_tail_kernel<2><<<dim3(kN / kTailThreads, rows), kTailThreads, 0, s>>>(rc, data);
 }
+// rings above one tile: message coefficients, then the sampler pass (the fused kernel covers ring dimension 8192)
 void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s, const u32 *sel) {
+                          u32 n_ct, i64 *m_e0, uint8_t *ve, cudaStream_t s, const u32 *sel) {
     if (!n_ct) return;
-    if (rc.log_blocks == 0) {
-        encode_kernel<true><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m_e0, ve, sel);
-        return;
-    }
     launch_encode_only(rc, ec, x, n, n_ct, m_e0, s, sel);
-    sample_add_kernel<<<dim3((rc.n / 4 + kSampleThreads - 1) / kSampleThreads, n_ct), kSampleThreads, 0, s>>>(sc, rc.n,
-                                                                                                           m_e0, ve);
+    sample_add_kernel<<<n_ct, kSampleThreads, 0, s>>>(sc, rc.n, m_e0, ve);
 }
 void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
                         cudaStream_t s, const u32 *sel) {
     if (!n_ct) return;
     if (rc.log_blocks == 0) {
-        SamplerConst sc{};
-        encode_kernel<false><<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, sc, x, n, m, nullptr, sel);
+        encode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, x, n, m, sel);
         return;
     }
     DISPATCH_D(fft_log_blocks(ec), encode_block_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, rc.n, x, n, m, sel))
 }
-void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
+void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint8_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s) {
     if (!n_ct) return;
     DISPATCH_D(rc.log_blocks, launch_tiles(encrypt_kernel<D>, n_ct * rc.limbs, D, s,
                                   rc, m_e0, ve, pk_b, pk_a, ct))
 }
 void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const EncryptBatch &eb,
-                          u64 n, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s) {
+                          u64 n, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s) {
     if (eb.n_ct && eb.k)   // ring dimension 8192 only (one tile per polynomial); callers check rc.log_blocks == 0
-        encrypt_fused_kernel<<<eb.n_ct * eb.k, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, sc, eb, n, m_e0, ve, pk_b, pk_a);
+        encrypt_fused_kernel<<<eb.n_ct * eb.k, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, sc, eb, n, pk_b, pk_a);
 }
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s) {
     if (!n_ct) return;

@@ -13,17 +13,24 @@ cudaError_t kernels_init();  // opt-in shared-memory sizes; call once per device
 void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s);
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
 
-// encode + sample: x[n] -> m_e0[n_ct][N] (m + e0, signed) and ve[n_ct][N] (v in the low byte, e1 in the high byte)
+// encode + sample (rings above one tile): x[n] -> m_e0[n_ct][N] (m + e0, signed) and ve[n_ct][N] (pack_ve bytes)
 // `sel` (optional, here and below): selective encryption — chunk element i is x[sel[i]] on the way in and
 // out[sel[i]] on the way out, so gather and scatter cost no pass of their own
 void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint16_t *ve, cudaStream_t s, const u32 *sel = nullptr);
+                          u32 n_ct, i64 *m_e0, uint8_t *ve, cudaStream_t s, const u32 *sel = nullptr);
 // encrypt: three forward NTTs per (ciphertext, limb) + public-key combine -> ct[n_ct][2][L][N]
-void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a,
+void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint8_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s);
-// encode + sample + encrypt in one kernel, one CTA per ciphertext (m_e0 / ve are scratch)
+// encode + sample + encrypt in one kernel, one CTA per ciphertext, ring dimension 8192 (no scratch: the draws stay in
+// shared memory and m + e0 is parked in an output row of the ciphertext itself)
 void launch_encrypt_fused(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const EncryptBatch &eb,
-                          u64 n, i64 *m_e0, uint16_t *ve, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s);
+                          u64 n, const tw_t *pk_b, const tw_t *pk_a, cudaStream_t s);
+// key generation: s, e (coefficient form, rows[2L][N]) and uniform a[L][N]; after launch_ntt_forward over the 2L rows,
+// b = e^ - a s^
+void launch_keygen_sample(const RingConst &rc, const SamplerConst &secret, const SamplerKey &pub, u64 *rows, u64 *a,
+                          cudaStream_t s);
+void launch_keygen_combine(const RingConst &rc, const u64 *rows_hat, const u64 *a, u64 *b, cudaStream_t s);
+void launch_chacha20_block(const SamplerKey &key, u32 counter, u32 n0, u32 n1, u32 n2, u32 *out, cudaStream_t s);
 // decrypt stage 1: c0 + c1*s, inverse NTT -> coeff[n_ct][L][N]
 void launch_decrypt_intt(const RingConst &rc, const u64 *ct, const tw_t *sk, u64 *coeff, u32 n_ct, cudaStream_t s);
 // rescale by one level: ct[n_ct][2][L][N] -> out[n_ct][2][L-1][N] (rc.limbs = L = towers of the input);

@@ -72,10 +72,18 @@ int shelfi_gen_crypto_context_and_keygen(shelfi_ckks *h);
  * (7, 52) -> N = 32768, L = 8 are BASELINE configs 3 and 4.  Returns 1 / 0 like the reference call. */
 int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth, uint32_t ring_dim);
 
-/* Encryption randomness comes from the OS by default.  A fixed seed makes the device sampler
+/* Randomness.  The reference draws v, e0, e1 (Encrypt, src/ckks.cpp:81,95) and s, e, a (KeyGen, src/ckks.cpp:46) from
+ * PALISADE's Blake2-based PRNG, seeded from OS entropy.  Here every draw is ChaCha20 in counter mode (the RFC 8439
+ * block function, 20 rounds) under a 256-bit key taken from getrandom(2): one fresh key per encrypt call and learner;
+ * key generation uses two independent keys, one for the secret material (s, e) and one for what is published (a, the
+ * key tag).  A fixed seed replaces those keys by ones laid out from the seed so that the device sampler is
  * reproducible (tests, parity against the CPU oracle); never use it for real data. */
 int shelfi_set_sampler_seed(shelfi_ckks *h, uint64_t seed);
 int shelfi_clear_sampler_seed(shelfi_ckks *h);
+/* known-answer tap: one ChaCha20 block computed by the device sampler code (key 8 words, block counter, nonce 3
+ * words -> 16 words); tests hold the RFC 8439 vectors */
+int shelfi_chacha20_block_device(shelfi_ckks *h, const uint32_t key[8], uint32_t counter, const uint32_t nonce[3],
+                                 uint32_t out[16]);
 
 /* ---- introspection ---- */
 uint32_t shelfi_ring_dim(const shelfi_ckks *h);

@@ -18,15 +18,31 @@ _HERE = Path(__file__).resolve().parent
 _LIB_PATH = _HERE / "_build" / "libshelfi_oracle.so"
 
 
+def _cpu_stamp() -> str:
+    """The oracle is compiled -march=native (it is the timed CPU baseline): a library built on another machine
+    (it travels with the repo snapshot) may hold instructions this CPU lacks, so it is rebuilt when the flags differ."""
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("flags"):
+                import hashlib
+                return hashlib.sha256(line.encode()).hexdigest()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def build(force: bool = False) -> Path:
     """Compile the oracle with gcc (oracle/Makefile)."""
-    src = [_HERE / "shelfi_oracle.c", _HERE / "shelfi_oracle.h"]
+    src = [_HERE / "shelfi_oracle.c", _HERE / "shelfi_oracle.h", _HERE / "Makefile"]
+    stamp = _HERE / "_build" / "cpu.stamp"
     stale = (not _LIB_PATH.exists()) or any(s.stat().st_mtime > _LIB_PATH.stat().st_mtime for s in src)
-    if force or stale:
+    foreign = not stamp.exists() or stamp.read_text() != _cpu_stamp()
+    if force or stale or foreign:
         env = dict(os.environ)
         env.pop("CC", None)
-        subprocess.run(["make", "-C", str(_HERE), "-B" if force else "-s"], check=True, env=env,
+        subprocess.run(["make", "-C", str(_HERE), "-B" if (force or foreign) else "-s"], check=True, env=env,
                        stdout=subprocess.DEVNULL)
+        stamp.write_text(_cpu_stamp())
     return _LIB_PATH
 
 
@@ -84,7 +100,8 @@ def lib():
         "orc_ntt_inverse": (None, [C.c_void_p, C.c_int, C.c_void_p]),
         "orc_fft_special": (None, [C.c_void_p, C.c_void_p, C.c_uint32]),
         "orc_fft_special_inv": (None, [C.c_void_p, C.c_void_p, C.c_uint32]),
-        "orc_philox": (None, [C.c_uint64, C.c_void_p, C.c_void_p]),
+        "orc_chacha20_block": (None, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+        "orc_seed_key": (None, [C.c_uint64, C.c_uint32, C.c_void_p]),
         "orc_sample_encrypt_noise": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
         "orc_encode_coeffs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
         "orc_encrypt_ct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p]),
@@ -389,8 +406,16 @@ def words_to_int(words) -> list:
     return out
 
 
-def philox(seed: int, ctr) -> np.ndarray:
-    c = np.asarray(ctr, dtype=np.uint32)
-    out = np.empty(4, np.uint32)
-    lib().orc_philox(seed, c.ctypes.data, out.ctypes.data)
+def chacha20_block(key, counter: int, nonce) -> np.ndarray:
+    """RFC 8439 2.3: key 8 words, block counter, nonce 3 words -> 16 words."""
+    k = np.ascontiguousarray(key, dtype=np.uint32)
+    n = np.ascontiguousarray(nonce, dtype=np.uint32)
+    out = np.empty(16, np.uint32)
+    lib().orc_chacha20_block(k.ctypes.data, counter, n.ctypes.data, out.ctypes.data)
     return out
+
+
+def seed_key(seed: int, domain: int) -> np.ndarray:
+    key = np.empty(8, np.uint32)
+    lib().orc_seed_key(seed, domain, key.ctypes.data)
+    return key

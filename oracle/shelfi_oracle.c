@@ -401,22 +401,40 @@ void orc_fft_special(const orc_ctx *c, double *v, uint32_t size) {
 }
 
 /* ------------------------------------------------------------------------------------------- */
-/* sampler: Philox4x32-10 counter RNG (spec shared with the device)               */
+/* sampler: ChaCha20 in counter mode (RFC 8439 block function), spec shared with the device      */
+/* (fhe-fed_b200/csrc/ckks_core.cuh).  Written from the RFC, independently of the */
+/* device code; tests/test_sampler_cpu.py checks both against the RFC's test vector.             */
 /* ------------------------------------------------------------------------------------------- */
-void orc_philox(uint64_t seed, const uint32_t ctr[4], uint32_t out[4]) {
-    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
-    uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3];
-    for (int r = 0; r < 10; r++) {
-        uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
-        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1;
-        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
-        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-    }
-    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+static inline uint32_t rotl(uint32_t x, int n) { return (x << n) | (x >> (32 - n)); }
+static void quarter(uint32_t *s, int a, int b, int c, int d) {
+    s[a] += s[b]; s[d] ^= s[a]; s[d] = rotl(s[d], 16);
+    s[c] += s[d]; s[b] ^= s[c]; s[b] = rotl(s[b], 12);
+    s[a] += s[b]; s[d] ^= s[a]; s[d] = rotl(s[d], 8);
+    s[c] += s[d]; s[b] ^= s[c]; s[b] = rotl(s[b], 7);
 }
-/* stream ids: counter word 3 */
-enum { STREAM_GAUSS = 0, STREAM_TERNARY = 1, STREAM_KEY_S = 2, STREAM_KEY_E = 3, STREAM_KEY_A = 4 };
+void orc_chacha20_block(const uint32_t key[8], uint32_t counter, const uint32_t nonce[3], uint32_t out[16]) {
+    uint32_t st[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u};
+    memcpy(st + 4, key, 32);
+    st[12] = counter;
+    memcpy(st + 13, nonce, 12);
+    uint32_t w[16];
+    memcpy(w, st, sizeof w);
+    for (int r = 0; r < 10; r++) {
+        quarter(w, 0, 4, 8, 12); quarter(w, 1, 5, 9, 13); quarter(w, 2, 6, 10, 14); quarter(w, 3, 7, 11, 15);
+        quarter(w, 0, 5, 10, 15); quarter(w, 1, 6, 11, 12); quarter(w, 2, 7, 8, 13); quarter(w, 3, 4, 9, 14);
+    }
+    for (int i = 0; i < 16; i++) out[i] = w[i] + st[i];
+}
+/* test keys: the 64-bit seed of the tests laid into a 256-bit key per domain ("SHELFI-B200 seed") */
+enum { KEY_ENCRYPT = 0, KEY_KEYGEN_SECRET = 1, KEY_KEYGEN_PUBLIC = 2 };
+void orc_seed_key(uint64_t seed, uint32_t domain, uint32_t key[8]) {
+    key[0] = (uint32_t)seed; key[1] = (uint32_t)(seed >> 32);
+    key[2] = 0x4c454853u; key[3] = 0x422d4946u; key[4] = 0x20303032u; key[5] = 0x64656573u;
+    key[6] = domain; key[7] = 0;
+}
+/* stream ids: nonce word 2 */
+enum { STREAM_GAUSS = 0, STREAM_TERNARY = 1, STREAM_KEY_S = 2, STREAM_KEY_E = 3, STREAM_KEY_A = 4, STREAM_KEY_TAG = 5,
+       STREAM_DECODE_NOISE = 6 };
 
 static inline int64_t gauss_from_u64(const uint64_t cdf[32], uint64_t r) {
     /* bit 63 = sign, the other 63 bits (shifted up) are compared against the magnitude CDF */
@@ -432,21 +450,24 @@ static inline int64_t ternary_from_u32(uint32_t r) { return (int64_t)(((uint64_t
 
 /* [PAL] LPAlgorithmCKKS::Encrypt draws v <- TernaryUniform (mode OPTIMIZED), e0,e1 <- DiscreteGaussian(sigma).
  * PALISADE's own PRNG is seeded from OS entropy, so only the distribution is pinned; this spec makes
- * oracle and device draw the same values for a given (seed, ct_index):
- *   gauss  call: ctr = (j, ct_lo, ct_hi, 0)      -> e0[j] from words (0,1), e1[j] from words (2,3)
- *   ternary call: ctr = (j>>2, ct_lo, ct_hi, 1)  -> v[4*(j>>2)+i] from word i                     */
+ * oracle and device draw the same values for a given (key, ct_index):
+ *   ternary block b, nonce (ct_lo, ct_hi, 1): v[16b + i] from word i
+ *   gauss   block b, nonce (ct_lo, ct_hi, 0): e0[4b + i] from words (4i, 4i+1), e1[4b + i] from words (4i+2, 4i+3) */
 void orc_sample_encrypt_noise(const orc_ctx *c, uint64_t seed, uint64_t ct, int64_t *v, int64_t *e0, int64_t *e1) {
-    uint32_t N = c->wp.N, out[4];
-    for (uint32_t j = 0; j < N; j++) {
-        uint32_t ctr[4] = {j, (uint32_t)ct, (uint32_t)(ct >> 32), STREAM_GAUSS};
-        orc_philox(seed, ctr, out);
-        e0[j] = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[1] << 32) | out[0]);
-        e1[j] = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[3] << 32) | out[2]);
+    uint32_t N = c->wp.N, out[16], key[8];
+    orc_seed_key(seed, KEY_ENCRYPT, key);
+    uint32_t ng[3] = {(uint32_t)ct, (uint32_t)(ct >> 32), STREAM_GAUSS};
+    uint32_t nt[3] = {(uint32_t)ct, (uint32_t)(ct >> 32), STREAM_TERNARY};
+    for (uint32_t b = 0; b < N / 4; b++) {
+        orc_chacha20_block(key, b, ng, out);
+        for (int i = 0; i < 4; i++) {
+            e0[4 * b + i] = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[4 * i + 1] << 32) | out[4 * i]);
+            e1[4 * b + i] = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[4 * i + 3] << 32) | out[4 * i + 2]);
+        }
     }
-    for (uint32_t j4 = 0; j4 < N / 4; j4++) {
-        uint32_t ctr[4] = {j4, (uint32_t)ct, (uint32_t)(ct >> 32), STREAM_TERNARY};
-        orc_philox(seed, ctr, out);
-        for (int i = 0; i < 4; i++) v[4 * j4 + i] = ternary_from_u32(out[i]);
+    for (uint32_t b = 0; b < N / 16; b++) {
+        orc_chacha20_block(key, b, nt, out);
+        for (int i = 0; i < 16; i++) v[16 * b + i] = ternary_from_u32(out[i]);
     }
 }
 
@@ -1457,40 +1478,48 @@ int orc_gen_context_and_keys_ex(uint32_t batch, uint32_t scale_bits, uint32_t mu
     free(w.b);
     if (!ok) { orc_destroy(c); return 0; }
 
-    /* [PAL] LPAlgorithmCKKS::KeyGen: a <- uniform (EVALUATION), s <- ternary, e <- Gaussian, b = e - a*s */
+    /* [PAL] LPAlgorithmCKKS::KeyGen: a <- uniform (EVALUATION), s <- ternary, e <- Gaussian, b = e - a*s.
+     * s and e are drawn under the secret test key, a and the key tag under the public one:
+     *   s[16b + i]: word i of block b, nonce (0, 0, STREAM_KEY_S);  e[8b + i]: words (2i, 2i+1) of block b, nonce (0, 0, STREAM_KEY_E)
+     *   a_l[j]: attempt t: words (2(j&7), 2(j&7)+1) of block j >> 3, nonce (l, t, STREAM_KEY_A), top bits(q_l) bits, accepted below q_l */
     size_t words = (size_t)p.L * N;
     uint64_t *pk = malloc(2 * words * 8), *sk = malloc(words * 8), *e = malloc(words * 8);
-    uint32_t out[4];
-    for (uint32_t j = 0; j < N; j++) {
-        uint32_t c1[4] = {j >> 2, 0, 0, STREAM_KEY_S}, c2[4] = {j, 0, 0, STREAM_KEY_E};
-        orc_philox(seed, c1, out);
-        int64_t sv = ternary_from_u32(out[j & 3]);
-        orc_philox(seed, c2, out);
-        int64_t ev = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[1] << 32) | out[0]);
-        for (int l = 0; l < p.L; l++) { sk[(size_t)l * N + j] = signed_mod(sv, p.q[l]); e[(size_t)l * N + j] = signed_mod(ev, p.q[l]); }
+    uint32_t out[16], ksec[8], kpub[8];
+    orc_seed_key(seed, KEY_KEYGEN_SECRET, ksec);
+    orc_seed_key(seed, KEY_KEYGEN_PUBLIC, kpub);
+    uint32_t n_s[3] = {0, 0, STREAM_KEY_S}, n_e[3] = {0, 0, STREAM_KEY_E};
+    for (uint32_t b = 0; b < N / 16; b++) {
+        orc_chacha20_block(ksec, b, n_s, out);
+        for (int i = 0; i < 16; i++)
+            for (int l = 0; l < p.L; l++) sk[(size_t)l * N + 16 * b + i] = signed_mod(ternary_from_u32(out[i]), p.q[l]);
+    }
+    for (uint32_t b = 0; b < N / 8; b++) {
+        orc_chacha20_block(ksec, b, n_e, out);
+        for (int i = 0; i < 8; i++) {
+            int64_t ev = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[2 * i + 1] << 32) | out[2 * i]);
+            for (int l = 0; l < p.L; l++) e[(size_t)l * N + 8 * b + i] = signed_mod(ev, p.q[l]);
+        }
     }
     for (int l = 0; l < p.L; l++) {
         orc_ntt_forward(c, l, sk + (size_t)l * N);
         orc_ntt_forward(c, l, e + (size_t)l * N);
+        int bits = 64 - __builtin_clzll(p.q[l]);
         for (uint32_t j = 0; j < N; j++) {
             uint64_t a;
             uint32_t tries = 0;
             do { /* rejection sampling of a 64-bit word below q */
-                uint32_t c3[4] = {j, (uint32_t)l, tries++, STREAM_KEY_A};
-                orc_philox(seed, c3, out);
-                int bits = 64 - __builtin_clzll(p.q[l]);
-                a = (((uint64_t)out[1] << 32) | out[0]) >> (64 - bits);
+                uint32_t n_a[3] = {(uint32_t)l, tries++, STREAM_KEY_A};
+                orc_chacha20_block(kpub, j >> 3, n_a, out);
+                a = (((uint64_t)out[2 * (j & 7) + 1] << 32) | out[2 * (j & 7)]) >> (64 - bits);
             } while (a >= p.q[l]);
             pk[words + (size_t)l * N + j] = a;
             pk[(size_t)l * N + j] = submod(e[(size_t)l * N + j], mulmod(a, sk[(size_t)l * N + j], p.q[l]), p.q[l]);
         }
     }
-    char tag[33];
-    for (int i = 0; i < 8; i++) { /* [PAL] GenerateUniqueKeyID: 32 hex chars */
-        uint32_t c4[4] = {(uint32_t)i, 0, 0, 99};
-        orc_philox(seed, c4, out);
-        snprintf(tag + 4 * i, 5, "%04x", out[0] & 0xffff);
-    }
+    char tag[33]; /* [PAL] GenerateUniqueKeyID: 32 hex chars */
+    uint32_t n_t[3] = {0, 0, STREAM_KEY_TAG};
+    orc_chacha20_block(kpub, 0, n_t, out);
+    snprintf(tag, sizeof tag, "%08x%08x%08x%08x", out[0], out[1], out[2], out[3]);
     emit_key_file(&w, 1, &p, tag, pk);
     ok = write_file(cryptodir, "key-public.txt", w.b, w.n); /* ckks.cpp:48 */
     free(w.b);

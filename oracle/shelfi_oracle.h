@@ -78,8 +78,9 @@ void orc_ntt_forward(const orc_ctx *c, int limb, uint64_t *a); /* natural -> bit
 void orc_ntt_inverse(const orc_ctx *c, int limb, uint64_t *a); /* bit-reversed -> natural          */
 void orc_fft_special(const orc_ctx *c, double *re_im, uint32_t size);     /* interleaved re,im */
 void orc_fft_special_inv(const orc_ctx *c, double *re_im, uint32_t size);
-/* Philox4x32-10; the sampler spec shared with the device */
-void orc_philox(uint64_t seed, const uint32_t ctr[4], uint32_t out[4]);
+/* RFC 8439 ChaCha20 block function and the test-key layout shared with the device sampler */
+void orc_chacha20_block(const uint32_t key[8], uint32_t counter, const uint32_t nonce[3], uint32_t out[16]);
+void orc_seed_key(uint64_t seed, uint32_t domain, uint32_t key[8]);
 /* fills v (ternary), e0, e1 (discrete Gaussian) for ciphertext index ct_index: N values each */
 void orc_sample_encrypt_noise(const orc_ctx *c, uint64_t seed, uint64_t ct_index, int64_t *v, int64_t *e0,
                               int64_t *e1);

@@ -65,6 +65,8 @@ class Emu:
             "emu_set_selection": (None, [vp]),
             "emu_encode_sample": (None, [vp, vp, u64, u64, u64, vp, vp]),
             "emu_encrypt": (None, [vp, vp, vp, vp, vp, vp]),
+            "emu_chacha20_block": (None, [vp, u32, vp, vp]),
+            "emu_keygen_draws": (None, [vp, u64, vp, vp, vp]),
             "emu_decrypt": (None, [vp, vp, vp, f64, f64, vp, u64, vp, vp, vp]),
             "emu_create_ex": (vp, [vp, vp, u32, u32, u32, u32, f64]),
             "emu_weighted_sum": (None, [vp, u32, C.POINTER(vp), vp, u32, vp, u32]),

@@ -238,24 +238,50 @@ void emu_encode(const Emu *e, const double *x, uint64_t n_valid, int64_t *m) {
     const u32 df = e->ec.log_slots > 12 ? e->ec.log_slots - 12 : 0;
     for (u32 fb = 0; fb < (1u << df); fb++) { EMU_D(df, replay_encode_block<D>(e, x, n_valid, fb, m)) }
 }
+// the sampler phases of encrypt_fused_kernel (ring dimension 8192) / sample_add_kernel (larger rings) under the test
+// key of `seed`: m_e0[N] = m + e0, ve[N] = pack_ve(v, e1)
 void emu_encode_sample(const Emu *e, const double *x, uint64_t n_valid, uint64_t seed, uint64_t ct_index, int64_t *m_e0,
-                       uint16_t *ve) {
-    SamplerConst sc;
-    std::memset(&sc, 0, sizeof sc);
-    sc.seed = seed;
+                       uint8_t *ve) {
+    const SamplerKey key = seed_key(seed, kKeyDomainEncrypt);
+    FOR_THREADS(kNttThreads) sample_ternary_phase(tid, kNttThreads, key, ct_index, e->rc.n, ve);
     if (e->rc.log_blocks == 0) {
         std::vector<cplx> z;
         replay_encode(e, x, n_valid, z);
-        FOR_THREADS(kFftThreads)
-            encode_sample_emit(tid, kFftThreads, z.data(), e->ec, sc, e->cdf, ct_index, (i64 *)m_e0, ve);
+        FOR_THREADS(kNttThreads)
+            sample_gauss_phase(tid, kNttThreads, z.data(), e->ec, key, e->cdf, ct_index, e->rc.n, (i64 *)m_e0, ve);
         return;
     }
     emu_encode(e, x, n_valid, m_e0);
-    for (u32 j4 = 0; j4 < e->rc.n / 4; j4++) sample_add_group(j4, ct_index, sc, e->cdf, (i64 *)m_e0, ve);
+    FOR_THREADS(kNttThreads)
+        sample_gauss_phase(tid, kNttThreads, nullptr, e->ec, key, e->cdf, ct_index, e->rc.n, (i64 *)m_e0, ve);
+}
+// one ChaCha20 block through the device code's implementation (RFC 8439 known-answer test)
+void emu_chacha20_block(const uint32_t *key, uint32_t counter, const uint32_t *nonce, uint32_t *out) {
+    SamplerKey k;
+    std::memcpy(k.k, key, sizeof k.k);
+    u32 o[16];
+    chacha20_block(k, counter, nonce[0], nonce[1], nonce[2], o);
+    std::memcpy(out, o, sizeof o);
+}
+// the device keygen draws under the test keys of `seed`: s[N], e[N] (signed), a[L][N]
+void emu_keygen_draws(const Emu *e, uint64_t seed, int64_t *s, int64_t *err, uint64_t *a) {
+    const SamplerKey ks = seed_key(seed, kKeyDomainKeySecret), kp = seed_key(seed, kKeyDomainKeyPublic);
+    for (u32 b = 0; b < e->rc.n / 16; b++) {
+        int v[16];
+        sample_ternary_block(ks, 0, b, kStreamKeyS, v);
+        for (int i = 0; i < 16; i++) s[16 * b + i] = v[i];
+    }
+    for (u32 b = 0; b < e->rc.n / 8; b++) {
+        int v[8];
+        keygen_error_block(ks, e->cdf, b, v);
+        for (int i = 0; i < 8; i++) err[8 * b + i] = v[i];
+    }
+    for (u32 l = 0; l < e->rc.limbs; l++)
+        for (u32 j = 0; j < e->rc.n; j++) a[(size_t)l * e->rc.n + j] = keygen_uniform(kp, l, j, e->rc.limb[l].q);
 }
 
 // encrypt_kernel<D>: one ciphertext, all limbs; pk_b / pk_a: [L][N] values; out: [2][L][N]
-void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const uint64_t *pk_b, const uint64_t *pk_a,
+void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint8_t *ve, const uint64_t *pk_b, const uint64_t *pk_a,
                  uint64_t *out) {
     const u32 L = e->rc.limbs, d = e->rc.log_blocks;
     const size_t n = e->rc.n;
@@ -273,20 +299,20 @@ void emu_encrypt(const Emu *e, const int64_t *m_e0, const uint16_t *ve, const ui
             const u32 hb = head_bits(d, blk);
             if (lc.dtw) {
                 EMU_D(d, {
-                    replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve}, &lc, blk}, StoreLazyPair{c1});
+                    replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadTernary>{DLoadTernary{ve}, &lc, blk}, StoreLazyPair{c1, 0});
                     replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadSigned>{DLoadSigned{(const i64 *)m_e0, &lc}, &lc, blk},
-                                     StoreMulAdd{b.data() + off, c1, c0, &lc});
+                                     StoreMulAdd{b.data() + off, c1, c0, &lc, false});
                     replay_forward_d(sm.data(), lc, hb, DHeadLoad<D, DLoadGaussHi>{DLoadGaussHi{ve}, &lc, blk},
-                                     StoreMulAdd{a.data() + off, c1, c1, &lc});
+                                     StoreMulAdd{a.data() + off, c1, c1, &lc, false});
                 })
                 continue;
             }
             EMU_D(d, {
-                replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve, lc.q}, &lc, blk}, StoreLazyPair{c1});
+                replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadTernary>{LoadTernary{ve, lc.q}, &lc, blk}, StoreLazyPair{c1, 0});
                 replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadSigned>{LoadSigned{(const i64 *)m_e0, &lc}, &lc, blk},
-                               StoreMulAdd{b.data() + off, c1, c0, &lc});
+                               StoreMulAdd{b.data() + off, c1, c0, &lc, false});
                 replay_forward(sm.data(), lc, hb, HeadLoad<D, LoadGaussHi>{LoadGaussHi{ve, lc.q}, &lc, blk},
-                               StoreMulAdd{a.data() + off, c1, c1, &lc});
+                               StoreMulAdd{a.data() + off, c1, c1, &lc, false});
             })
         }
     }

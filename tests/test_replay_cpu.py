@@ -67,12 +67,12 @@ def test_sampler_matches_oracle_and_distribution(emu, emu_ctx, oracles):
     x = np.zeros(4096)
     vs, es = [], []
     for ct in (0, 1, 2**32 + 5):
-        m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint16)
+        m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint8)
         emu.L.emu_encode_sample(h, vp(x), 4096, 99, ct, vp(m_e0), vp(ve))
         v, e0, e1 = o.sample_noise(99, ct)
         assert np.array_equal(m_e0, e0)                      # x = 0 -> m = 0
-        assert np.array_equal((ve & 0xFF).astype(np.int8), v.astype(np.int8))
-        assert np.array_equal((ve >> 8).astype(np.int8), e1.astype(np.int8))
+        assert np.array_equal((ve & 3).astype(np.int64) - 1, v)          # pack_ve: bits 1..0 = v + 1, bits 7..2 = e1 + 32
+        assert np.array_equal((ve >> 2).astype(np.int64) - 32, e1)
         vs.append(v); es += [e0, e1]
     v, e = np.concatenate(vs), np.concatenate(es)
     assert set(np.unique(v)) == {-1, 0, 1}
@@ -83,7 +83,7 @@ def test_sampler_matches_oracle_and_distribution(emu, emu_ctx, oracles):
 def test_encrypt_decrypt_match_oracle(emu, emu_ctx, oracles, fixture_name):
     o, h = oracles[fixture_name], emu_ctx[fixture_name]
     x = np.random.default_rng(3).normal(0, 0.05, 4096)
-    m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint16)
+    m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint8)
     emu.L.emu_encode_sample(h, vp(x), 4096, 1234, 7, vp(m_e0), vp(ve))
     b, a = o.public_key()
     ct = np.empty((2, 2, N), np.uint64)
@@ -153,11 +153,11 @@ def test_deep_encrypt_decrypt_match_oracle(emu, deep_emu_ctx, deep_oracles, name
     o, h = deep_oracles[name], deep_emu_ctx[name]
     n, slots, L, bits = o.ring_dim, o.slots, o.num_limbs, o.scaleFactorBits
     x = np.random.default_rng(5).normal(0, 0.05, slots)
-    m_e0, ve = np.empty(n, np.int64), np.empty(n, np.uint16)
+    m_e0, ve = np.empty(n, np.int64), np.empty(n, np.uint8)
     emu.L.emu_encode_sample(h, vp(x), slots, 4321, 9, vp(m_e0), vp(ve))
     v, e0, e1 = o.sample_noise(4321, 9)
     assert np.array_equal(m_e0, o.encode_coeffs(x) + e0)
-    assert np.array_equal((ve & 0xFF).astype(np.int8), v.astype(np.int8))
+    assert np.array_equal((ve & 3).astype(np.int64) - 1, v) and np.array_equal((ve >> 2).astype(np.int64) - 32, e1)
     b, a = o.public_key()
     ct = np.empty((2, L, n), np.uint64)
     emu.L.emu_encrypt(h, vp(m_e0), vp(ve), vp(b), vp(a), vp(ct))
@@ -239,7 +239,7 @@ def test_fp64_path_rejected_above_its_exactness_bound(emu, oracle_mod):
 def test_fp64_encrypt_equals_integer_encrypt(emu, emu_ctx, oracles):
     o, h = oracles["code"], emu_ctx["code"]
     x = np.random.default_rng(31).normal(0, 30.0, 4096)          # large messages: m + e0 near 2^58
-    m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint16)
+    m_e0, ve = np.empty(N, np.int64), np.empty(N, np.uint8)
     emu.L.emu_encode_sample(h, vp(x), 4096, 77, 3, vp(m_e0), vp(ve))
     b, a = o.public_key()
     ct1, ct2 = np.empty((2, 2, N), np.uint64), np.empty((2, 2, N), np.uint64)
