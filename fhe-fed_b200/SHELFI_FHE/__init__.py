@@ -24,7 +24,8 @@ __version__ = "0.1.0-b200"
 _PKG = Path(__file__).resolve().parent.parent
 _LIB_PATH = Path(os.environ.get("SHELFI_B200_LIB", _PKG / "lib" / "libshelfi_b200.so"))
 
-ERR_NAMES = {0: "OK", -1: "ARG", -2: "NOT_LOADED", -3: "FORMAT", -4: "PARAMS", -5: "CUDA", -6: "IO", -7: "UNSUPPORTED"}
+ERR_NAMES = {0: "OK", -1: "ARG", -2: "NOT_LOADED", -3: "FORMAT", -4: "PARAMS", -5: "CUDA", -6: "IO", -7: "UNSUPPORTED",
+             -8: "MEMORY"}
 
 
 class ShelfiError(RuntimeError):
@@ -99,6 +100,18 @@ def lib() -> C.CDLL:
                                                                       u32, C.POINTER(vp), u64p, u64p, u64p]),
         "shelfi_compute_weighted_average_layers_rescaled_into": (C.c_int, [vp, C.POINTER(vp), u64p, C.POINTER(C.c_float),
                                                                            u32, u32, vp, u64, u64p, u64p, u64p]),
+        "shelfi_ct_encrypt": (C.c_int, [vp, vp, u64, C.c_int, C.POINTER(vp)]),
+        "shelfi_ct_from_blob": (C.c_int, [vp, vp, u64, C.POINTER(vp)]),
+        "shelfi_ct_weighted_average": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_float), u32, C.c_int, C.POINTER(vp)]),
+        "shelfi_ct_decrypt": (C.c_int, [vp, vp, u64, vp]),
+        "shelfi_ct_blob_size": (u64, [vp]),
+        "shelfi_ct_to_blob": (C.c_int, [vp, vp, vp, u64, u64p]),
+        "shelfi_ct_info": (C.c_int, [vp, u64p, C.POINTER(u32), u64p, u64p, C.POINTER(f64)]),
+        "shelfi_ct_device_ptr": (vp, [vp]),
+        "shelfi_ct_free": (None, [vp, vp]),
+        "shelfi_resident_stats": (C.c_int, [vp, u64p, u64p, u64p]),
+        "shelfi_resident_set_limit": (C.c_int, [vp, u64]),
+        "shelfi_synchronize": (C.c_int, [vp]),
         "shelfi_free": (None, [vp]),
         "shelfi_host_alloc": (vp, [C.c_size_t]),
         "shelfi_host_free": (None, [vp]),
@@ -139,7 +152,7 @@ def lib() -> C.CDLL:
 
 def _as_bytes(blob):
     # pybind11 2.6.1's permissive std::string caster takes bytes or str (ckks.cpp:170,276)
-    if isinstance(blob, PinnedBlob):
+    if isinstance(blob, (PinnedBlob, ResidentBlob)):
         return blob
     if isinstance(blob, (bytes, bytearray, memoryview)):
         return bytes(blob) if not isinstance(blob, bytes) else blob
@@ -177,6 +190,8 @@ def _addr(buf) -> int:
     """Address of a bytes / PinnedBlob / buffer-protocol object's memory (borrowed for the duration of the call)."""
     if isinstance(buf, PinnedBlob):
         return buf.address
+    if isinstance(buf, ResidentBlob):
+        buf = bytes(buf)     # cached on the blob, which the caller keeps alive for the call
     if isinstance(buf, bytes):
         return C.cast(C.c_char_p(buf), C.c_void_p).value
     return np.frombuffer(buf, dtype=np.uint8).ctypes.data
@@ -184,57 +199,127 @@ def _addr(buf) -> int:
 
 class _PinnedPool:
     """Page-locked host buffers are expensive to create (cudaHostAlloc pins at a few GB/s) and cheap to reuse:
-    freed blobs go back to a size-keyed free list."""
+    freed blobs go back to a size-keyed free list, up to SHELFI_PINNED_POOL_MB (default 2048) of parked memory;
+    beyond that they are returned to the driver."""
 
     def __init__(self):
         self.free = {}
+        self.parked = 0
+        self.cap_bytes = int(os.environ.get("SHELFI_PINNED_POOL_MB", "2048")) << 20
 
     def take(self, n: int):
         cap = max(4096, 1 << (int(n) - 1).bit_length()) if n > (1 << 20) else max(4096, int(n))
         lst = self.free.get(cap)
         if lst:
+            self.parked -= cap
             return lst.pop(), cap
         p = lib().shelfi_host_alloc(cap)
         if not p:
-            raise MemoryError(f"cudaHostAlloc({cap}) failed")
+            self.trim()
+            p = lib().shelfi_host_alloc(cap)
+            if not p:
+                raise MemoryError(f"cudaHostAlloc({cap}) failed")
         return p, cap
 
     def give(self, p, cap):
+        if self.parked + cap > self.cap_bytes:
+            lib().shelfi_host_free(p)
+            return
+        self.parked += cap
         self.free.setdefault(cap, []).append(p)
+
+    def trim(self):
+        for lst in self.free.values():
+            for p in lst:
+                lib().shelfi_host_free(p)
+        self.free.clear()
+        self.parked = 0
 
 
 _pool = _PinnedPool()
 
 
+class _KeepArray(np.ndarray):
+    """A numpy view of memory owned by another object (`_keep`): views and slices keep this array as their base, so
+    the owner — and with it the page-locked buffer — stays alive as long as anything refers to the memory."""
+
+    _keep = None
+
+    def __array_finalize__(self, obj):
+        if obj is not None and getattr(self, "_keep", None) is None:
+            self._keep = getattr(obj, "_keep", None)
+
+    def __reduce__(self):          # pickle / deepcopy hand back a plain array
+        return np.asarray(self).copy().__reduce__()
+
+
+class _PinnedBuffer:
+    """One page-locked allocation from the pool; returns to it when the last array / blob over it is gone."""
+
+    __slots__ = ("p", "cap")
+
+    def __init__(self, n: int):
+        self.p, self.cap = _pool.take(n)
+
+    def __del__(self):
+        if getattr(self, "p", None) and _lib is not None:
+            _pool.give(self.p, self.cap)
+            self.p = None
+
+    def array(self, offset: int, n: int, dtype=np.uint8) -> np.ndarray:
+        count = int(n) // np.dtype(dtype).itemsize
+        a = np.ctypeslib.as_array((C.c_uint8 * int(n)).from_address(self.p + offset)).view(dtype)[:count].view(_KeepArray)
+        a._keep = self
+        return a
+
+
+def pinned_empty(shape, dtype=np.float64) -> np.ndarray:
+    """An uninitialised numpy array in page-locked host memory (pooled): inputs placed here are read by the GPU's copy
+    engine straight from the caller's pages, at the PCIe rate, instead of through the pageable staging path."""
+    shape = (int(shape),) if np.isscalar(shape) else tuple(int(v) for v in shape)
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    return _PinnedBuffer(max(n, 1)).array(0, n, dtype).reshape(shape)
+
+
+def pinned_array(a, dtype=None) -> np.ndarray:
+    """A page-locked copy of `a` (see pinned_empty)."""
+    a = np.asarray(a, dtype=dtype)
+    out = pinned_empty(a.shape, a.dtype)
+    np.copyto(out, a)
+    return out
+
+
 class PinnedBlob:
     """A serialized ciphertext vector held in page-locked host memory (opt-in: ``CKKS(..., pinned=True)``).
 
-    Bytes-like: ``len``, ``bytes(b)``, ``memoryview(b)`` (buffer protocol), ``b.array`` (numpy uint8 view),
-    equality with ``bytes``.  Passing it back to ``computeWeightedAverage`` / ``decrypt`` moves it over PCIe at the
-    link rate instead of through the driver's pageable staging path; ``bytes(b)`` gives the reference's exact type
-    when the payload has to leave the process."""
+    Bytes-like: ``len``, ``bytes(b)``, ``memoryview(b)`` (buffer protocol), ``b.array`` (numpy uint8 view that keeps
+    the buffer alive), equality and hash like the ``bytes`` it stands for.  Passing it back to
+    ``computeWeightedAverage`` / ``decrypt`` moves it over PCIe at the link rate instead of through the driver's
+    pageable staging path; ``bytes(b)`` gives the reference's exact type when the payload has to leave the process."""
 
     def __init__(self, n: int, _parent=None, _offset: int = 0):
         if _parent is None:
-            self._p, self._cap = _pool.take(n)
-        else:   # a slice of another blob's buffer (the per-layer results of the *_layers calls); keeps it alive
-            self._p, self._cap = _parent._p + _offset, 0
-        self._parent = _parent
+            self._buf, self._off = _PinnedBuffer(n), 0
+        else:   # a slice of another blob's buffer (the per-layer results of the *_layers calls)
+            self._buf, self._off = _parent._buf, _parent._off + _offset
         self._n = int(n)
-        self.array = np.ctypeslib.as_array((C.c_uint8 * self._n).from_address(self._p))
 
     def view(self, offset: int, n: int) -> "PinnedBlob":
         return PinnedBlob(n, self, offset)
 
     @property
+    def array(self) -> np.ndarray:
+        return self._buf.array(self._off, self._n)
+
+    @property
     def address(self) -> int:
-        return self._p
+        return self._buf.p + self._off
 
     def __len__(self):
         return self._n
 
     def __bytes__(self):
-        return C.string_at(self._p, self._n)
+        return C.string_at(self.address, self._n)
 
     tobytes = __bytes__
 
@@ -247,34 +332,83 @@ class PinnedBlob:
     def __eq__(self, other):
         if isinstance(other, PinnedBlob):
             return self._n == other._n and bool(np.array_equal(self.array, other.array))
-        if isinstance(other, (bytes, bytearray, memoryview)):
+        if isinstance(other, (bytes, bytearray, memoryview, ResidentBlob)):
             return self._n == len(other) and bytes(self) == bytes(other)
         return NotImplemented
 
-    def __hash__(self):
-        return hash((self._p, self._n))
+    def __hash__(self):            # equal to the bytes it compares equal to
+        return hash(bytes(self))
+
+
+class ResidentBlob:
+    """A serialized ciphertext vector that lives in GPU memory (opt-in: ``CKKS(..., resident=True)``).
+
+    What ``encrypt`` and ``computeWeightedAverage`` return in resident mode.  The reference's callers never look inside
+    these objects: they collect them in lists and dicts and pass them to the next call (benchmark.py:490-528), which is
+    all a handle has to support to cost nothing.  Whenever the bytes themselves are needed — ``bytes(b)``,
+    ``memoryview(b)``, pickling, ``==``, writing to a socket or file — the exact wire bytes of the bytes-mode call are
+    produced on demand (and cached); ``len(b)`` is known without producing them."""
+
+    __slots__ = ("_ck", "_p", "_len", "_cache", "__weakref__")
+
+    def __init__(self, ckks: "CKKS", ptr):
+        self._ck, self._p, self._cache = ckks, ptr, None
+        self._len = int(lib().shelfi_ct_blob_size(ptr))
 
     def __del__(self):
-        p = getattr(self, "_p", None)
-        if p and _lib is not None:
-            self.array = None
-            if self._parent is None:
-                _pool.give(p, self._cap)
-            self._p = self._parent = None
+        p, ck = getattr(self, "_p", None), getattr(self, "_ck", None)
+        if p and ck is not None and _lib is not None and getattr(ck, "_h", None):
+            _lib.shelfi_ct_free(ck._h, p)
+        self._p = None
+
+    def __len__(self):
+        return self._len
+
+    def __bytes__(self):
+        if self._cache is None:
+            dst = _new_bytes(self._len)
+            n = C.c_uint64()
+            self._ck._check(lib().shelfi_ct_to_blob(self._ck._h, self._p, _addr(dst), self._len, C.byref(n)))
+            assert n.value == self._len
+            self._cache = dst
+        return self._cache
+
+    tobytes = __bytes__
+
+    def to_pinned(self) -> PinnedBlob:
+        dst = PinnedBlob(self._len)
+        n = C.c_uint64()
+        self._ck._check(lib().shelfi_ct_to_blob(self._ck._h, self._p, dst.address, self._len, C.byref(n)))
+        return dst
+
+    def __reduce__(self):
+        return (bytes, (bytes(self),))
+
+    def __buffer__(self, flags):
+        return memoryview(bytes(self))
+
+    def __eq__(self, other):
+        if isinstance(other, (bytes, bytearray, memoryview, PinnedBlob, ResidentBlob)):
+            return self._len == len(other) and bytes(self) == bytes(other)
+        return NotImplemented
+
+    def __hash__(self):
+        return hash(bytes(self))
+
+    def _info(self):
+        n_ct, limbs, depth, level, sf = C.c_uint64(), C.c_uint32(), C.c_uint64(), C.c_uint64(), C.c_double()
+        lib().shelfi_ct_info(self._p, C.byref(n_ct), C.byref(limbs), C.byref(depth), C.byref(level), C.byref(sf))
+        return n_ct.value, limbs.value, depth.value, level.value, sf.value
+
+    n_ct = property(lambda self: self._info()[0])
+    limbs = property(lambda self: self._info()[1])
+    depth = property(lambda self: self._info()[2])
+    level = property(lambda self: self._info()[3])
+    scaling_factor = property(lambda self: self._info()[4])
+    device_ptr = property(lambda self: lib().shelfi_ct_device_ptr(self._p))
 
 
-class _PinnedArray(np.ndarray):
-    """float64 result of decrypt in pinned mode: a view of a PinnedBlob's page-locked buffer that holds on to it (views
-    and slices keep this array as their base, so the buffer returns to the pool only when nothing refers to it)."""
-
-    _keep = None
-
-    def __array_finalize__(self, obj):
-        if obj is not None and getattr(self, "_keep", None) is None:
-            self._keep = getattr(obj, "_keep", None)
-
-    def __reduce__(self):          # pickle / deepcopy hand back a plain array
-        return np.asarray(self).copy().__reduce__()
+_PinnedArray = _KeepArray   # decrypt results in pinned / resident mode
 
 
 class Scheme:
@@ -289,8 +423,12 @@ class CKKS(Scheme):
 
     def __init__(self, scheme: str = "ckks", batchSize: int = 4096, scaleFactorBits: int = 52,
                  cryptodir: str = "../resources/cryptoparams/", device: int | None = None, pinned: bool = False,
-                 rescale: bool = False):
+                 rescale: bool = False, resident: bool = False):
         super().__init__(scheme)
+        # resident mode (extension, off by default): encrypt / computeWeightedAverage return ResidentBlob objects whose
+        # payload stays in GPU memory; decrypt and computeWeightedAverage accept them (and bytes, and PinnedBlob) in any
+        # mix.  The wire bytes are produced only when something asks for them.
+        self.resident = bool(resident) or os.environ.get("SHELFI_RESIDENT", "0") == "1"
         # rescale-before-transport (extension, off by default like the reference): computeWeightedAverage returns the
         # average one tower shorter (PALISADE ModReduce), i.e. half the bytes at the shipped two-tower context
         self.rescale = bool(rescale) or os.environ.get("SHELFI_RESCALE", "0") == "1"
@@ -353,6 +491,8 @@ class CKKS(Scheme):
 
     def encrypt(self, data_array) -> bytes:
         """ckks.cpp:61-104: any array-like convertible to float64 (flattened) -> serialized ciphertext vector."""
+        if self.resident:
+            return self._encrypt_resident(data_array)
         x = np.ascontiguousarray(data_array, dtype=np.float64).ravel()
         cap = self.blob_size(self.num_ciphertexts(x.size)) if x.size else 0
         if cap == 0:   # not loaded / empty input: let the library report it
@@ -365,6 +505,50 @@ class CKKS(Scheme):
         assert n.value == cap
         return dst
 
+    def _encrypt_resident(self, data_array) -> ResidentBlob:
+        """encrypt with the ciphertexts left in GPU memory.  float32 arrays (what the reference's callers pass: the
+        state_dict entries as numpy, benchmark.py:490-493) are uploaded as they are, 4 bytes per parameter, and widened
+        on the device — the values pybind's array_t<double> conversion would produce; everything else goes as float64.
+        Objects with ``__cuda_array_interface__`` (a torch.cuda tensor, a cupy array; float32 or float64, contiguous,
+        already computed: synchronise their stream first) are read where they are."""
+        cai = getattr(data_array, "__cuda_array_interface__", None)
+        out = C.c_void_p()
+        if cai is not None:
+            if cai.get("strides") is not None or cai["typestr"] not in ("<f8", "<f4"):
+                raise TypeError("device input must be contiguous float64 or float32")
+            n = int(np.prod(cai["shape"])) if cai["shape"] else 1
+            self._check(lib().shelfi_ct_encrypt(self._h, cai["data"][0], n, int(cai["typestr"] == "<f4"), C.byref(out)))
+            return ResidentBlob(self, out)
+        a = data_array if isinstance(data_array, np.ndarray) else np.asarray(data_array)
+        f32 = a.dtype == np.float32
+        x = np.ascontiguousarray(a, dtype=np.float32 if f32 else np.float64).ravel()
+        self._check(lib().shelfi_ct_encrypt(self._h, x.ctypes.data, x.size, int(f32), C.byref(out)))
+        return ResidentBlob(self, out)
+
+    def _as_resident(self, blob):
+        """(handle pointer, owner to keep alive) for any accepted blob type; bytes are uploaded and unpacked."""
+        if isinstance(blob, ResidentBlob) and blob._ck is self:
+            return blob._p, blob
+        raw = _as_bytes(blob)
+        out = C.c_void_p()
+        self._check(lib().shelfi_ct_from_blob(self._h, _addr(raw), len(raw), C.byref(out)))
+        return out, ResidentBlob(self, out)
+
+    def to_resident(self, blob) -> ResidentBlob:
+        """bytes / PinnedBlob (from this engine or a PALISADE peer) -> ResidentBlob on this handle's GPU."""
+        return self._as_resident(blob)[1]
+
+    def _wavg_resident(self, learner_data, scaling_factors, rescale: bool):
+        k = len(learner_data)
+        if k == 0:
+            raise ShelfiError(-1, "no learners")
+        held = [self._as_resident(b) for b in learner_data]
+        ptrs = (C.c_void_p * k)(*[p if isinstance(p, int) else p.value for p, _ in held])
+        w = (C.c_float * k)(*[float(v) for v in scaling_factors])
+        out = C.c_void_p()
+        self._check(lib().shelfi_ct_weighted_average(self._h, ptrs, w, k, int(rescale), C.byref(out)))
+        return ResidentBlob(self, out)
+
     def computeWeightedAverage(self, learner_data, scaling_factors, rescale: bool | None = None) -> bytes:
         """ckks.cpp:264-320: sum_i float32(w_i) * ct_i over learners; size mismatch prints and returns b"".
 
@@ -375,6 +559,9 @@ class CKKS(Scheme):
         if len(learner_data) != len(scaling_factors):
             print("Error: learner_data and scaling_factors size mismatch")  # ckks.cpp:266
             return b""
+        if self.resident or any(isinstance(b, ResidentBlob) for b in learner_data):
+            res = self._wavg_resident(learner_data, scaling_factors, rescale)
+            return res if self.resident else (res.to_pinned() if self.pinned else bytes(res))
         blobs = [_as_bytes(b) for b in learner_data]
         k = len(blobs)
         ptrs = (C.c_void_p * k)(*[_addr(b) for b in blobs])
@@ -414,23 +601,24 @@ class CKKS(Scheme):
         """ckks.cpp:170-213: serialized ciphertext vector -> float64[data_dimensions] (level-0 or rescaled)."""
         blob = _as_bytes(learner_data)
         n = int(data_dimensions)
-        if self.pinned and n * 8 >= (1 << 20):
-            # pinned mode: the result lives in pooled page-locked memory too (an ndarray that keeps its buffer alive),
-            # so a page-locked blob takes the engine's pipelined decrypt (upload / decrypt / copy back overlapped)
-            keep = PinnedBlob(n * 8)
-            out = keep.array.view(np.float64).view(_PinnedArray)
-            out._keep = keep
+        if (self.pinned or self.resident) and n * 8 >= (1 << 20):
+            # pinned / resident mode: the result lives in pooled page-locked memory (an ndarray that keeps its buffer
+            # alive), so the values cross PCIe at the link rate and the engine's pipelined decrypt applies
+            out = pinned_empty(n, np.float64)
         else:
             out = np.empty(n, dtype=np.float64)
-        self._check(lib().shelfi_decrypt(self._h, _addr(blob), len(blob), n, out.ctypes.data))
+        if isinstance(blob, ResidentBlob) and blob._ck is self:
+            self._check(lib().shelfi_ct_decrypt(self._h, blob._p, n, out.ctypes.data))
+        else:
+            self._check(lib().shelfi_decrypt(self._h, _addr(blob), len(blob), n, out.ctypes.data))
         return out
 
     # ---- layer-wise callers (benchmark.py:490-493, benchmark_selection.py:152-193) in one call each ----
     _PIPELINE_MIN_CTS = 128    # engine.cpp kPipelineMinCts: from here a single vector is pipelined against its own copies
     def encrypt_layers(self, arrays) -> list:
         """[encrypt(a) for a in arrays] with one host->device copy, one stream of launches, one copy back."""
-        if not self.pinned:   # real bytes objects cannot share one buffer: filling each in place beats slicing copies
-            return [self.encrypt(a) for a in arrays]
+        if self.resident or not self.pinned:   # resident: nothing crosses PCIe but the inputs; bytes objects cannot
+            return [self.encrypt(a) for a in arrays]   # share one buffer: filling each in place beats slicing copies
         flat = [np.ascontiguousarray(a, dtype=np.float64).ravel() for a in arrays]
         # a layer of >= 128 ciphertexts goes through the single-vector call, whose copy back overlaps its own
         # compute group by group; the small layers of the model share one call (one launch sequence, one copy back)
@@ -467,7 +655,7 @@ class CKKS(Scheme):
         k, n = len(learner_layers), len(learner_layers[0]) if learner_layers else 0
         if any(len(l) != n for l in learner_layers):
             raise ValueError("every learner must supply the same number of layers")
-        if not self.pinned:
+        if self.resident or not self.pinned or any(isinstance(b, ResidentBlob) for l in learner_layers for b in l):
             return [self.computeWeightedAverage([l[s] for l in learner_layers], scaling_factors, rescale) for s in range(n)]
         big_len = self.blob_size(self._PIPELINE_MIN_CTS)
         big = [s for s in range(n) if k and len(learner_layers[0][s]) >= big_len]
@@ -499,6 +687,8 @@ class CKKS(Scheme):
         n = len(blobs)
         if n != len(dims):
             raise ValueError("one data_dimensions entry per blob")
+        if any(isinstance(b, ResidentBlob) for b in blobs):
+            return [self.decrypt(b, d) for b, d in zip(blobs, dims)]
         ptrs = (C.c_void_p * n)(*[_addr(b) for b in blobs])
         blens = (C.c_uint64 * n)(*[len(b) for b in blobs])
         dd = (C.c_uint64 * n)(*dims)
@@ -516,6 +706,19 @@ class CKKS(Scheme):
             lib().shelfi_clear_sampler_seed(self._h)
         else:
             lib().shelfi_set_sampler_seed(self._h, int(seed) & (2**64 - 1))
+
+    def synchronize(self) -> None:
+        """Wait for everything this handle has queued on the GPU (resident calls return before their kernels end)."""
+        self._check(lib().shelfi_synchronize(self._h))
+
+    def resident_stats(self) -> dict:
+        """Bytes of GPU memory held by live ResidentBlobs, parked on the pool's free list, and the pool's limit."""
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(lib().shelfi_resident_stats(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"in_use": a.value, "pooled": b.value, "limit": c.value}
+
+    def set_resident_limit(self, nbytes: int) -> None:
+        self._check(lib().shelfi_resident_set_limit(self._h, int(nbytes)))
 
     def load_from_memory(self, cc: bytes | None, pk: bytes | None, sk: bytes | None) -> int:
         rc = lib().shelfi_load_crypto_params_from_memory(self._h, cc, len(cc or b""), pk, len(pk or b""), sk,

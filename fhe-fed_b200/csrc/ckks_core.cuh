@@ -1152,6 +1152,7 @@ struct EncryptBatch {
     u64 *ct[kMaxEncryptBatch];
     SamplerKey key[kMaxEncryptBatch];   // every learner's vector is encrypted under its own key
     u32 k, n_ct;
+    u32 f32, pad;     // the x[] hold float32 values
 };
 
 // byte offsets of the 2L coefficient runs of a serialized vector<Ciphertext> (wire.h)
@@ -1168,10 +1169,16 @@ HD u64 run_offset(const BlobRuns &br, u64 ct, u32 r) { return ct == 0 ? br.off0[
 // phase 0: chunk of x -> z (zero padded)
 // Selective encryption (benchmark_selection*.py encrypt a chosen subset of the parameters): with `sel` the chunk is
 // x[sel[i]] instead of x[i], i.e. the gather is part of the load (and the scatter part of decode_store).
+// `f32`: x holds float32 values (the reference's callers pass float32 state_dict arrays, code/benchmark.py:490-493,
+// which pybind's array_t<double> caster widens on the host; here the widening — exact — is part of the load, so such
+// an input crosses PCIe at 4 bytes per parameter).
+HD double encode_value(const double *x, u64 idx, bool f32) {
+    return f32 ? (double)reinterpret_cast<const float *>(x)[idx] : x[idx];
+}
 HD void encode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid,
-                    const u32 *sel = nullptr) {
+                    const u32 *sel = nullptr, bool f32 = false) {
     for (u32 i = tid; i < ec.slots; i += nthreads) {
-        z[zsw(i)].re = i < n_valid ? x[sel ? sel[i] : i] : 0.0;
+        z[zsw(i)].re = i < n_valid ? encode_value(x, sel ? sel[i] : i, f32) : 0.0;
         z[zsw(i)].im = 0.0;
     }
 }
@@ -1334,8 +1341,11 @@ struct EncSrc {             // one chunk of encode input: x[j] or x[sel[j]], j <
     const double *x;
     u64 n_valid;
     const u32 *sel;
+    bool f32;
 };
-HD cplx encode_input(const EncSrc &x, u64, u32 j) { return cplx{j < x.n_valid ? x.x[x.sel ? x.sel[j] : j] : 0.0, 0.0}; }
+HD cplx encode_input(const EncSrc &x, u64, u32 j) {
+    return cplx{j < x.n_valid ? encode_value(x.x, x.sel ? x.sel[j] : j, x.f32) : 0.0, 0.0};
+}
 template <int DF>
 HD cplx encode_head(const EncodeConst &ec, const EncSrc &x, u64 n_valid, u32 fb, u32 i) {
     if (DF == 0) return encode_input(x, n_valid, i);
@@ -1355,9 +1365,9 @@ HD cplx encode_head(const EncodeConst &ec, const EncSrc &x, u64 n_valid, u32 fb,
 }
 template <int DF>
 HD void encode_load_block(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid, u32 fb,
-                          const u32 *sel = nullptr) {
+                          const u32 *sel = nullptr, bool f32 = false) {
     const u32 tile_slots = ec.slots < kFftFast ? ec.slots : kFftFast;
-    const EncSrc src{x, n_valid, sel};
+    const EncSrc src{x, n_valid, sel, f32};
     for (u32 i = tid; i < tile_slots; i += nthreads) z[zsw(i)] = encode_head<DF>(ec, src, n_valid, fb, i);
 }
 // tile (finalized: bit-reversed within the tile, scaled, rounded) -> coefficients m[gap*slot], m[gap*slot + nh]

@@ -162,7 +162,61 @@ class ParallelCopier {
 
 constexpr size_t kStageBytes = 16u << 20;   // two page-locked staging chunks of this size per handle
 
+// Device memory of the resident ciphertext vectors (shelfi_ct): freed buffers are kept on a size-keyed free list,
+// because cudaFree synchronises the whole device and a federation round makes and drops K + 1 vectors of the same size.
+// Every kernel that touches such a buffer runs on the handle's compute stream, so handing a freed buffer to the next
+// vector is ordered by that stream and needs no event.
+struct DevicePool {
+    static constexpr size_t kGrain = 2u << 20;
+    std::multimap<size_t, void *> free_list;
+    size_t in_use = 0, pooled = 0, limit = 0;   // bytes; limit 0 = not yet sized
+    static size_t round_up(size_t b) { return (b + kGrain - 1) / kGrain * kGrain; }
+    void trim() {
+        for (auto &kv : free_list) cudaFree(kv.second);
+        free_list.clear();
+        pooled = 0;
+    }
+    // returns nullptr when the limit or the device is exhausted (after giving the pooled buffers back)
+    void *take(size_t bytes, size_t *cap) {
+        const size_t want = round_up(bytes);
+        auto it = free_list.lower_bound(want);
+        if (it != free_list.end() && it->first <= want + want / 4) {
+            void *p = it->second;
+            *cap = it->first;
+            pooled -= it->first; in_use += it->first;
+            free_list.erase(it);
+            return p;
+        }
+        if (limit && in_use + pooled + want > limit) trim();
+        if (limit && in_use + want > limit) return nullptr;
+        void *p = nullptr;
+        if (cudaMalloc(&p, want) != cudaSuccess) {
+            cudaGetLastError();
+            trim();
+            if (cudaMalloc(&p, want) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        }
+        *cap = want; in_use += want;
+        return p;
+    }
+    void give(void *p, size_t cap) {
+        in_use -= cap; pooled += cap;
+        free_list.emplace(cap, p);
+    }
+};
+
 }  // namespace
+
+// A vector<Ciphertext<DCRTPoly>> that lives in HBM: the dense payload [n_ct][2][limbs][N] plus what the wire format
+// needs to write it out again byte for byte (context variant, per-ciphertext metadata).
+struct shelfi_ct {
+    shelfi_ckks *owner = nullptr;
+    u64 *d = nullptr;
+    size_t cap = 0;
+    uint64_t n_ct = 0;
+    uint32_t limbs = 0;
+    wire::ContextParams ctx;
+    std::vector<wire::CiphertextMeta> meta;   // one entry (every ciphertext alike) or n_ct entries
+};
 
 struct shelfi_ckks {
     std::string scheme, cryptodir, err;
@@ -209,6 +263,14 @@ struct shelfi_ckks {
         uint32_t n_seg = 0;
     };
     std::map<std::string, EncPlan> enc_plans;   // key: context bytes + n_ct + the (uniform) ciphertext metadata
+    // resident ciphertext vectors (shelfi_ct_*): pool, two input slots so that the upload of one vector overlaps the
+    // encryption of the one before, and the events that order the copy streams against the compute stream
+    DevicePool pool;
+    std::vector<shelfi_ct *> live;
+    DeviceBuffer r_x[2], r_out;
+    cudaEvent_t ev_x_in[2] = {nullptr, nullptr}, ev_x_free[2] = {nullptr, nullptr}, ev_r_out = nullptr;
+    bool x_busy[2] = {false, false};
+    unsigned r_turn = 0;
 };
 
 namespace {
@@ -481,8 +543,9 @@ int call_key(shelfi_ckks *h, uint32_t domain, SamplerKey *k) {
 // --- stage drivers (all asynchronous on `s`) ---
 // k learners' vectors (all of length n) in one launch: the grid covers k * n_ct ciphertexts, so small models still
 // fill the machine and co-resident CTAs are out of phase with one another.
+// dtype 1: the d_x[i] hold float32 values (widened on load)
 int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uint64_t n, uint64_t ct_index0,
-                       uint64_t *const *d_ct, cudaStream_t s, const uint32_t *d_sel = nullptr) {
+                       uint64_t *const *d_ct, cudaStream_t s, const uint32_t *d_sel = nullptr, int dtype = 0) {
     uint64_t n_ct = (n + h->batch - 1) / h->batch;
     const uint64_t N = h->ctx.ring_dim;
     if (n_ct * k > (0x7fffffffull / (2 * kMaxLimbs)) >> h->rc.log_blocks)
@@ -521,7 +584,7 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
             if (krc) return krc;
             if (overlap && i >= 2) CU(cudaStreamWaitEvent(es, h->ev_enc_free[b], 0));   // slot b was read by learner i-2
             timed(h, kKEncodeSample, es, [&] {
-                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, m_slot, ve_slot, es, d_sel);
+                launch_encode_sample(h->rc, h->ec, sc, d_x[i], n, (u32)n_ct, m_slot, ve_slot, es, d_sel, dtype == 1);
             });
             if (overlap) {
                 CU(cudaEventRecord(h->ev_enc_ready[b], es));
@@ -541,6 +604,7 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
         eb.k = std::min<uint32_t>(kMaxEncryptBatch, k - base);
         eb.n_ct = (u32)n_ct;
         eb.sel = d_sel;
+        eb.f32 = dtype == 1 ? 1u : 0u;
         for (uint32_t i = 0; i < eb.k; i++) {
             eb.x[i] = d_x[base + i];
             eb.ct[i] = reinterpret_cast<u64 *>(d_ct[base + i]);
@@ -556,6 +620,25 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
 }
 int encrypt_dense(shelfi_ckks *h, const double *d_x, uint64_t n, uint64_t ct_index0, uint64_t *d_ct, cudaStream_t s) {
     return encrypt_dense_many(h, &d_x, 1, n, ct_index0, &d_ct, s);
+}
+
+// EvalMult(ct, (float)w) + EvalAdd over k dense batches (ckks.cpp:286-297), 16 learners per launch
+int weighted_sum_dense(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k, uint64_t n_ct,
+                       uint64_t *d_out, bool accumulate, cudaStream_t s) {
+    const uint32_t L = h->ctx.limbs;
+    for (uint32_t base = 0; base < k; base += kMaxLearnersPerLaunch) {
+        WavgArgs wa{};
+        wa.k = std::min<uint32_t>(kMaxLearnersPerLaunch, k - base);
+        wa.accumulate = (base || accumulate) ? 1u : 0u;
+        for (uint32_t i = 0; i < wa.k; i++) {
+            wa.in[i] = reinterpret_cast<const u64 *>(d_cts[base + i]);
+            int64_t sc = weight_constant(h, weights[base + i]);
+            for (uint32_t l = 0; l < L; l++) wa.c[i][l] = nt::signed_mod(sc, h->ctx.modulus[l]);
+        }
+        timed(h, kKWeightedSum, s, [&] { launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, s); });
+    }
+    CU(cudaGetLastError());
+    return 0;
 }
 
 bool general_decode(const shelfi_ckks *h, uint32_t limbs = 0) {
@@ -1198,6 +1281,284 @@ int rescale_host(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t
     return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Resident ciphertext vectors (shelfi_ct_*): the three reference calls with the ciphertexts left in HBM.
+// The reference's callers keep every blob inside one process and only hand it to the next call
+// (code/benchmark.py:459-460,490-493,507-513,527-528), so nothing forces 64 bytes per parameter and learner across
+// PCIe twice; what must cross it is the plaintext in (8 or 4 bytes per parameter) and the average out (8 bytes).
+// ---------------------------------------------------------------------------------------------
+int ensure_resident(shelfi_ckks *h) {
+    if (h->ev_r_out) return 0;
+    for (int i = 0; i < 2; i++) {
+        CU(cudaEventCreateWithFlags(&h->ev_x_in[i], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_x_free[i], cudaEventDisableTiming));
+    }
+    if (!h->d2h_stream) {
+        CU(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&h->ev_stage_out, cudaEventDisableTiming));
+    }
+    if (!h->pool.limit) {
+        size_t free_b = 0, total_b = 0;
+        CU(cudaMemGetInfo(&free_b, &total_b));
+        h->pool.limit = free_b - free_b / 5;   // 80 % of what is free now; shelfi_resident_set_limit changes it
+        if (const char *e = std::getenv("SHELFI_RESIDENT_LIMIT_MB")) h->pool.limit = (size_t)std::max(1, std::atoi(e)) << 20;
+    }
+    CU(cudaEventCreateWithFlags(&h->ev_r_out, cudaEventDisableTiming));
+    return 0;
+}
+int new_ct(shelfi_ckks *h, uint64_t n_ct, uint32_t limbs, shelfi_ct **out) {
+    const size_t bytes = (size_t)n_ct * 2 * limbs * h->ctx.ring_dim * sizeof(uint64_t);
+    shelfi_ct *c = new shelfi_ct();
+    c->d = static_cast<u64 *>(h->pool.take(bytes, &c->cap));
+    if (!c->d) {
+        delete c;
+        return fail(h, SHELFI_ERR_MEMORY, "device pool exhausted: " + std::to_string(bytes >> 20) + " MiB requested, " +
+                                              std::to_string(h->pool.in_use >> 20) + " MiB in resident ciphertexts, limit " +
+                                              std::to_string(h->pool.limit >> 20) + " MiB (free vectors you no longer need, or raise SHELFI_RESIDENT_LIMIT_MB)");
+    }
+    c->owner = h; c->n_ct = n_ct; c->limbs = limbs; c->ctx = h->ctx;
+    h->live.push_back(c);
+    *out = c;
+    return 0;
+}
+void drop_ct(shelfi_ckks *h, shelfi_ct *c) {
+    auto it = std::find(h->live.begin(), h->live.end(), c);
+    if (it == h->live.end()) return;
+    h->live.erase(it);
+    if (c->d) h->pool.give(c->d, c->cap);
+    delete c;
+}
+bool is_device_ptr(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice;
+}
+// the serialization plan of a resident vector (cached for vectors of like ciphertexts)
+int ct_plan(shelfi_ckks *h, const shelfi_ct *c, shelfi_ckks::EncPlan **ep, wire::BlobPlan *own) {
+    *ep = nullptr;
+    if (c->meta.size() == 1) return enc_plan(h, c->ctx, c->n_ct, c->meta[0], ep);
+    *own = wire::plan_ciphertext_blob(c->ctx, c->n_ct, c->meta);
+    return 0;
+}
+
+// ckks.cpp:61-104 with the result left on the device.  x: n values, float64 (dtype 0) or float32 (dtype 1), in host
+// memory (page-locked: copied by the DMA engine straight from the caller's pages; pageable: staged through the copy
+// threads) or in device memory.  Returns once x has been read; the encryption itself continues on the compute stream.
+int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct **out) {
+    int rcode = check_stage(h, true, false);
+    if (rcode) return rcode;
+    if (!x || !out || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument (an empty input is undefined behaviour in the reference, ckks.cpp:66,95)");
+    if (dtype != 0 && dtype != 1) return fail(h, SHELFI_ERR_ARG, "dtype: 0 = float64, 1 = float32");
+    if ((rcode = ensure_resident(h))) return rcode;
+    trim_enc_plans(h);
+    const uint64_t n_ct = (n + h->batch - 1) / h->batch;
+    const size_t in_bytes = n * (dtype ? 4 : 8);
+    shelfi_ct *c = nullptr;
+    if ((rcode = new_ct(h, n_ct, h->ctx.limbs, &c))) return rcode;
+    wire::CiphertextMeta m;
+    m.depth = 1; m.level = 0; m.encoding_type = 4;
+    m.scaling_factor = (double)h->ctx.modulus[h->ctx.limbs - 1];
+    std::memcpy(m.tag, h->key_tag.c_str(), 32);
+    c->meta.assign(1, m);
+    cudaStream_t st = h->stream, cs = h->copy_stream;
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(cs);
+        cudaStreamSynchronize(st);
+        drop_ct(h, c);
+        return code;
+    };
+    const void *d_x = x;
+    const bool on_device = is_device_ptr(x);
+    const unsigned b = h->r_turn++ & 1u;
+    if (!on_device) {
+        // slot b was last read by the encryption two calls ago
+        if (h->x_busy[b]) CUB(cudaStreamWaitEvent(cs, h->ev_x_free[b], 0));
+        if (h->r_x[b].cap < in_bytes) {   // growing reallocates: wait until nothing reads the old buffer
+            CUB(cudaStreamSynchronize(st));
+            CUB(h->r_x[b].reserve(in_bytes));
+        }
+        if ((rcode = h2d(h, h->r_x[b].p, x, in_bytes, cs))) return bail(rcode);
+        CUB(cudaEventRecord(h->ev_x_in[b], cs));
+        CUB(cudaStreamWaitEvent(st, h->ev_x_in[b], 0));
+        d_x = h->r_x[b].p;
+    }
+    const double *dx64 = static_cast<const double *>(d_x);
+    u64 *ct_ptr = c->d;
+    if ((rcode = encrypt_dense_many(h, &dx64, 1, n, 0, reinterpret_cast<uint64_t *const *>(&ct_ptr), st, nullptr, dtype)))
+        return bail(rcode);
+    if (!on_device) {
+        CUB(cudaEventRecord(h->ev_x_free[b], st));
+        h->x_busy[b] = true;
+        CUB(cudaEventSynchronize(h->ev_x_in[b]));   // the caller's buffer is only borrowed for the call
+    } else {
+        CUB(cudaStreamSynchronize(st));             // likewise: the kernel read the caller's device buffer
+    }
+    *out = c;
+    return 0;
+}
+
+// a serialized vector (bytes from encrypt / computeWeightedAverage, here or in a PALISADE peer) -> resident
+int ct_from_blob(shelfi_ckks *h, const uint8_t *blob, uint64_t len, shelfi_ct **out) {
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!blob || !out) return fail(h, SHELFI_ERR_ARG, "null argument");
+    if ((rcode = ensure_resident(h))) return rcode;
+    wire::BlobMap map;
+    std::string e = wire::map_ciphertext_blob(blob, len, false, &map);
+    if (!e.empty()) return fail(h, SHELFI_ERR_FORMAT, e);
+    if (!same_ring(map.ctx, h->ctx)) return fail(h, SHELFI_ERR_PARAMS, "ciphertext parameters differ from the loaded context");
+    if (map.ct_limbs < 1 || map.ct_limbs > h->ctx.limbs) return fail(h, SHELFI_ERR_FORMAT, "unexpected tower count");
+    shelfi_ct *c = nullptr;
+    if ((rcode = new_ct(h, map.n_ct, map.ct_limbs, &c))) return rcode;
+    c->ctx = map.ctx;
+    bool uniform = true;
+    for (size_t j = 1; uniform && j < map.meta.size(); j++) uniform = same_meta(map.meta[j], map.meta[0]);
+    for (auto &m : map.meta) m.limbs = map.ct_limbs == h->ctx.limbs ? 0 : map.ct_limbs;
+    if (uniform) c->meta.assign(1, map.meta[0]); else c->meta = map.meta;
+    cudaStream_t st = h->stream;
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(st);
+        drop_ct(h, c);
+        return code;
+    };
+    CUB(h->s_image.reserve(image_bytes(len)));
+    if ((rcode = h2d(h, h->s_image.p, blob, len, st))) return bail(rcode);
+    timed(h, kKUnpack, st, [&] {
+        launch_unpack(h->rc, to_runs(h, map.run0, map.run1, map.stride, map.ct_limbs), h->s_image.as<u64>(), c->d, map.n_ct, st);
+    });
+    CUB(cudaGetLastError());
+    CUB(cudaStreamSynchronize(st));   // the blob is only borrowed for the call (and s_image is shared scratch)
+    *out = c;
+    return 0;
+}
+
+// ckks.cpp:264-320 over resident vectors; the result is a new resident vector
+int ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *w, uint32_t k, int rescale, shelfi_ct **out) {
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!cts || !w || !out) return fail(h, SHELFI_ERR_ARG, "null argument");
+    if (k == 0) return fail(h, SHELFI_ERR_ARG, "no learners");
+    const uint32_t L = h->ctx.limbs;
+    const double sf0 = (double)h->ctx.modulus[L - 1];
+    if (rescale && L < 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "rescale needs a chain of at least two towers");
+    for (uint32_t i = 0; i < k; i++) {
+        const std::string who = "learner " + std::to_string(i);
+        if (!cts[i] || cts[i]->owner != h) return fail(h, SHELFI_ERR_ARG, who + ": not a resident vector of this handle");
+        if (cts[i]->n_ct != cts[0]->n_ct) return fail(h, SHELFI_ERR_PARAMS, who + ": ciphertext count differs");
+        if (cts[i]->limbs != L) return fail(h, SHELFI_ERR_UNSUPPORTED, who + ": only fresh depth-1 level-0 ciphertexts are supported");
+        for (const auto &m : cts[i]->meta)
+            if (m.depth != 1 || m.level != 0)
+                return fail(h, SHELFI_ERR_UNSUPPORTED, who + ": only fresh depth-1 level-0 ciphertexts are supported");
+    }
+    const uint64_t n_ct = cts[0]->n_ct;
+    shelfi_ct *acc = nullptr;
+    if ((rcode = new_ct(h, n_ct, L, &acc))) return rcode;
+    acc->ctx = cts[0]->ctx;
+    acc->meta = cts[0]->meta;                     // ckks.cpp:291-292: the result starts as learner 0's vector
+    for (auto &m : acc->meta) { m.depth += 1; m.scaling_factor *= sf0; }   // [PAL] EvalMult(ct, double), no rescale
+    cudaStream_t st = h->stream;
+    std::vector<const uint64_t *> ptrs(k);
+    for (uint32_t i = 0; i < k; i++) ptrs[i] = cts[i]->d;
+    if ((rcode = weighted_sum_dense(h, ptrs.data(), w, k, n_ct, acc->d, false, st))) { drop_ct(h, acc); return rcode; }
+    if (rescale) {
+        shelfi_ct *red = nullptr;
+        if ((rcode = new_ct(h, n_ct, L - 1, &red))) { drop_ct(h, acc); return rcode; }
+        red->ctx = acc->ctx; red->meta = acc->meta;
+        for (auto &m : red->meta) { m.depth -= 1; m.level += 1; m.scaling_factor /= sf0; m.limbs = L - 1; }
+        if ((rcode = rescale_dense(h, acc->d, n_ct, L, red->d, st))) { drop_ct(h, red); drop_ct(h, acc); return rcode; }
+        drop_ct(h, acc);   // stream order: whoever gets this buffer next writes it after the rescale has read it
+        acc = red;
+    }
+    *out = acc;
+    return 0;
+}
+
+// ckks.cpp:170-213 from a resident vector into host memory (any kind); returns when `out` holds the values
+int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
+    int rcode = check_stage(h, false, true);
+    if (rcode) return rcode;
+    if (!c || c->owner != h || !out) return fail(h, SHELFI_ERR_ARG, "null argument or foreign vector");
+    if ((rcode = ensure_resident(h))) return rcode;
+    const uint64_t batch = h->batch, n_ct = c->n_ct;
+    if (n == 0 || n > n_ct * batch || n + batch <= n_ct * batch)
+        return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
+    cudaStream_t st = h->stream, ds = h->d2h_stream;
+    const uint64_t words = 2ull * c->limbs * h->ctx.ring_dim;
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(st);
+        cudaStreamSynchronize(ds);
+        return code;
+    };
+    CUB(cudaStreamWaitEvent(st, h->ev_r_out, 0));   // an earlier call's copy out of r_out (already finished: calls return after it)
+    if (h->r_out.cap < n * sizeof(double)) {
+        CUB(cudaStreamSynchronize(st));
+        CUB(h->r_out.reserve(n * sizeof(double)));
+    }
+    double *d_out = h->r_out.as<double>();
+    auto sf_of = [&](uint64_t j) { return c->meta[c->meta.size() == 1 ? 0 : j].scaling_factor; };
+    const bool one_scale = c->meta.size() == 1;
+    const bool pinned = is_pinned(out);
+    // a large vector into page-locked memory: groups are decrypted while the group before crosses PCIe
+    const uint32_t groups = (one_scale && pinned && n_ct >= kPipelineMinCts) ? 4 : 1;
+    if (groups > 1) {
+        for (uint32_t g = 0; g < groups; g++) {
+            const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
+            const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
+            if ((rcode = decrypt_dense(h, c->d + c0 * words, c1 - c0, sf_of(0), d_out + first, last - first, st, nullptr, c->limbs)))
+                return bail(rcode);
+            CUB(cudaEventRecord(h->ev_stage_out, st));
+            CUB(cudaStreamWaitEvent(ds, h->ev_stage_out, 0));
+            CUB(cudaMemcpyAsync(out + first, d_out + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost, ds));
+        }
+        CUB(cudaEventRecord(h->ev_r_out, ds));
+        CUB(cudaStreamSynchronize(ds));
+        return 0;
+    }
+    for (uint64_t j0 = 0; j0 < n_ct;) {   // ciphertexts usually share one scaling factor; split the launch where they do not
+        uint64_t j1 = one_scale ? n_ct : j0 + 1;
+        while (j1 < n_ct && sf_of(j1) == sf_of(j0)) j1++;
+        const uint64_t first = j0 * batch, last = std::min(n, j1 * batch);
+        if ((rcode = decrypt_dense(h, c->d + j0 * words, j1 - j0, sf_of(j0), d_out + first, last - first, st, nullptr, c->limbs)))
+            return bail(rcode);
+        j0 = j1;
+    }
+    if ((rcode = d2h_sync(h, out, d_out, n * sizeof(double), st))) return bail(rcode);
+    return 0;
+}
+
+uint64_t ct_blob_size(const shelfi_ct *c) {
+    return wire::ciphertext_blob_size(c->ctx, c->n_ct, c->limbs == c->ctx.limbs ? 0 : c->limbs);
+}
+// Serial::Serialize of a resident vector (ckks.cpp:98-101,308-310): the exact bytes the host-buffer calls return
+int ct_to_blob(shelfi_ckks *h, const shelfi_ct *c, uint8_t *dst, uint64_t cap, uint64_t *len) {
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (!c || c->owner != h || !dst || !len) return fail(h, SHELFI_ERR_ARG, "null argument or foreign vector");
+    trim_enc_plans(h);
+    shelfi_ckks::EncPlan *ep = nullptr;
+    wire::BlobPlan own;
+    if ((rcode = ct_plan(h, c, &ep, &own))) return rcode;
+    const wire::BlobPlan &pl = ep ? ep->plan : own;
+    if (cap < pl.size) return fail(h, SHELFI_ERR_ARG, "destination buffer too small: need " + std::to_string(pl.size) + " bytes");
+    cudaStream_t st = h->stream;
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(st);
+        return code;
+    };
+    CUB(h->s_image.reserve(image_bytes(pl.size)));
+    timed(h, kKPack, st, [&] {
+        launch_pack(h->rc, to_runs(h, pl.run0, pl.run1, pl.stride, c->limbs), c->d, h->s_image.as<u64>(), c->n_ct, st);
+    });
+    const bool dev_hdr = ep && c->n_ct >= kDeviceHeaderMinCts;
+    if (dev_hdr) launch_write_segments(ep->d_desc.as<SegDesc>(), ep->d_bytes.as<uint8_t>(), h->s_image.as<uint8_t>(), ep->n_seg, st);
+    CUB(cudaGetLastError());
+    if ((rcode = d2h_sync(h, dst, h->s_image.p, pl.size, st))) return bail(rcode);
+    if (!dev_hdr) write_segments(pl, dst);
+    *len = pl.size;
+    return 0;
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -1227,6 +1588,16 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         cudaDeviceSynchronize();
         h->prof.release();
         free_params(h);
+        for (shelfi_ct *c : h->live) { if (c->d) cudaFree(c->d); delete c; }   // vectors die with their handle
+        h->live.clear();
+        h->pool.trim();
+        for (int i = 0; i < 2; i++) {
+            h->r_x[i].release();
+            if (h->ev_x_in[i]) cudaEventDestroy(h->ev_x_in[i]);
+            if (h->ev_x_free[i]) cudaEventDestroy(h->ev_x_free[i]);
+        }
+        h->r_out.release();
+        if (h->ev_r_out) cudaEventDestroy(h->ev_r_out);
         for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_image3,
                                 &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows, &h->s_pt, &h->s_resc, &h->s_dense2})
             b->release();
@@ -1599,6 +1970,79 @@ int shelfi_decrypt_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uin
     return decrypt_host(h, blobs, blob_lens, data_dimensions, n_layers, out);
 }
 
+// ---- resident ciphertext vectors ----
+int shelfi_ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct **out) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return ct_encrypt(h, x, n, dtype, out);
+}
+int shelfi_ct_from_blob(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, shelfi_ct **out) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return ct_from_blob(h, blob, blob_len, out);
+}
+int shelfi_ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *weights, uint32_t k, int rescale,
+                               shelfi_ct **out) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return ct_weighted_average(h, cts, weights, k, rescale, out);
+}
+int shelfi_ct_decrypt(shelfi_ckks *h, const shelfi_ct *ct, uint64_t n, double *out) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return ct_decrypt(h, ct, n, out);
+}
+uint64_t shelfi_ct_blob_size(const shelfi_ct *ct) { return ct ? ct_blob_size(ct) : 0; }
+int shelfi_ct_to_blob(shelfi_ckks *h, const shelfi_ct *ct, uint8_t *dst, uint64_t cap, uint64_t *blob_len) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return ct_to_blob(h, ct, dst, cap, blob_len);
+}
+int shelfi_ct_info(const shelfi_ct *ct, uint64_t *n_ct, uint32_t *limbs, uint64_t *depth, uint64_t *level,
+                   double *scaling_factor) {
+    if (!ct || ct->meta.empty()) return SHELFI_ERR_ARG;
+    if (n_ct) *n_ct = ct->n_ct;
+    if (limbs) *limbs = ct->limbs;
+    if (depth) *depth = ct->meta[0].depth;
+    if (level) *level = ct->meta[0].level;
+    if (scaling_factor) *scaling_factor = ct->meta[0].scaling_factor;
+    return 0;
+}
+const uint64_t *shelfi_ct_device_ptr(const shelfi_ct *ct) { return ct ? ct->d : nullptr; }
+void shelfi_ct_free(shelfi_ckks *h, shelfi_ct *ct) {
+    if (!h || !ct) return;
+    std::lock_guard<std::mutex> lock(h->mu);
+    drop_ct(h, ct);
+}
+int shelfi_resident_stats(shelfi_ckks *h, uint64_t *in_use, uint64_t *pooled, uint64_t *limit) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (in_use) *in_use = h->pool.in_use;
+    if (pooled) *pooled = h->pool.pooled;
+    if (limit) *limit = h->pool.limit;
+    return 0;
+}
+int shelfi_resident_set_limit(shelfi_ckks *h, uint64_t bytes) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = ensure_cuda(h);
+    if (rcode) return rcode;
+    CU(cudaDeviceSynchronize());   // parked buffers may still be read by queued kernels
+    h->pool.trim();
+    h->pool.limit = bytes;
+    return 0;
+}
+int shelfi_synchronize(shelfi_ckks *h) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!h->cuda_ready) return 0;
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->copy_stream));
+    if (h->d2h_stream) CU(cudaStreamSynchronize(h->d2h_stream));
+    return 0;
+}
+
 void shelfi_free(void *p) { std::free(p); }
 void *shelfi_host_alloc(size_t bytes) {
     void *p = nullptr;
@@ -1633,20 +2077,7 @@ static int weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, con
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
     if (!d_cts || !weights || !d_out || k == 0 || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
-    const uint32_t L = h->ctx.limbs;
-    for (uint32_t base = 0; base < k; base += kMaxLearnersPerLaunch) {
-        WavgArgs wa{};
-        wa.k = std::min<uint32_t>(kMaxLearnersPerLaunch, k - base);
-        wa.accumulate = (base || accumulate) ? 1u : 0u;
-        for (uint32_t i = 0; i < wa.k; i++) {
-            wa.in[i] = reinterpret_cast<const u64 *>(d_cts[base + i]);
-            int64_t sc = weight_constant(h, weights[base + i]);
-            for (uint32_t l = 0; l < L; l++) wa.c[i][l] = nt::signed_mod(sc, h->ctx.modulus[l]);
-        }
-        timed(h, kKWeightedSum, s, [&] { launch_weighted_sum(h->rc, wa, reinterpret_cast<u64 *>(d_out), n_ct, s); });
-    }
-    CU(cudaGetLastError());
-    return 0;
+    return weighted_sum_dense(h, d_cts, weights, k, n_ct, d_out, accumulate, s);
 }
 
 int shelfi_weighted_sum_device(shelfi_ckks *h, const uint64_t *const *d_cts, const float *weights, uint32_t k,

@@ -312,15 +312,18 @@ __global__ void __launch_bounds__(kTailThreads) intt_tail_kernel(const __grid_co
 // ------------------------------------------------------------------------------------------
 // encode (+ sampler): one CTA per ciphertext, FFT tile in shared memory
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ const double *chunk_ptr(const double *x, u64 first, bool f32) {
+    return f32 ? reinterpret_cast<const double *>(reinterpret_cast<const float *>(x) + first) : x + first;
+}
 __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_constant__ EncodeConst ec, const double *x,
-                                                             u64 n, i64 *m, const u32 *sel) {
+                                                             u64 n, i64 *m, const u32 *sel, u32 f32) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
     const int tid = threadIdx.x;
     const u64 ct = blockIdx.x;
     u64 first = ct * ec.batch;
     u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
-    encode_load(tid, kFftThreads, z, ec, sel ? x : x + first, n_valid, sel ? sel + first : nullptr);
+    encode_load(tid, kFftThreads, z, ec, sel ? x : chunk_ptr(x, first, f32), n_valid, sel ? sel + first : nullptr, f32);
     __syncthreads();
     if (ec.slots == kFftFast) {
         fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
@@ -344,7 +347,7 @@ __global__ void __launch_bounds__(kFftThreads) encode_kernel(const __grid_consta
 // coefficients, the FFT blocks own strided ones).
 template <int DF>
 __global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_constant__ EncodeConst ec, u32 n_ring,
-                                                                   const double *x, u64 n, i64 *m, const u32 *sel) {
+                                                                   const double *x, u64 n, i64 *m, const u32 *sel, u32 f32) {
     extern __shared__ __align__(16) unsigned char smraw[];
     cplx *z = reinterpret_cast<cplx *>(smraw);
     const int tid = threadIdx.x;
@@ -352,7 +355,7 @@ __global__ void __launch_bounds__(kFftThreads) encode_block_kernel(const __grid_
     const u64 ct = blockIdx.x >> DF;
     const u64 first = ct * ec.batch;
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
-    encode_load_block<DF>(tid, kFftThreads, z, ec, sel ? x : x + first, n_valid, fb, sel ? sel + first : nullptr);
+    encode_load_block<DF>(tid, kFftThreads, z, ec, sel ? x : chunk_ptr(x, first, f32), n_valid, fb, sel ? sel + first : nullptr, f32);
     __syncthreads();
     EncodeConst et = ec;                       // the tile's own geometry for the bit reversal
     if (ec.slots >= kFftFast) {
@@ -493,7 +496,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     i64 *m_row = reinterpret_cast<i64 *>(ct_out + ((ct * 2 + 0) * L + l_last) * (u64)kN);
     const u64 keep = make_keep_policy();
     sample_ternary_phase(tid, kNttThreads, eb.key[learner], ct_index, kN, ve);   // touches only `ve`
-    encode_load(tid, kNttThreads, z, ec, eb.sel ? x : x + first, n_valid, eb.sel ? eb.sel + first : nullptr);
+    encode_load(tid, kNttThreads, z, ec, eb.sel ? x : chunk_ptr(x, first, eb.f32), n_valid, eb.sel ? eb.sel + first : nullptr, eb.f32);
     __syncthreads();
     if (ec.slots == kFftFast) {
         fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
@@ -947,19 +950,19 @@ void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s
 }
 // rings above one tile: message coefficients, then the sampler pass (the fused kernel covers ring dimension 8192)
 void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint8_t *ve, cudaStream_t s, const u32 *sel) {
+                          u32 n_ct, i64 *m_e0, uint8_t *ve, cudaStream_t s, const u32 *sel, bool f32) {
     if (!n_ct) return;
-    launch_encode_only(rc, ec, x, n, n_ct, m_e0, s, sel);
+    launch_encode_only(rc, ec, x, n, n_ct, m_e0, s, sel, f32);
     sample_add_kernel<<<n_ct, kSampleThreads, 0, s>>>(sc, rc.n, m_e0, ve);
 }
 void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
-                        cudaStream_t s, const u32 *sel) {
+                        cudaStream_t s, const u32 *sel, bool f32) {
     if (!n_ct) return;
     if (rc.log_blocks == 0) {
-        encode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, x, n, m, sel);
+        encode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, x, n, m, sel, f32 ? 1u : 0u);
         return;
     }
-    DISPATCH_D(fft_log_blocks(ec), encode_block_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, rc.n, x, n, m, sel))
+    DISPATCH_D(fft_log_blocks(ec), encode_block_kernel<D><<<n_ct << D, kFftThreads, fft_smem(ec), s>>>(ec, rc.n, x, n, m, sel, f32 ? 1u : 0u))
 }
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint8_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s) {

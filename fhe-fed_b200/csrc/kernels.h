@@ -17,7 +17,7 @@ void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s
 // `sel` (optional, here and below): selective encryption — chunk element i is x[sel[i]] on the way in and
 // out[sel[i]] on the way out, so gather and scatter cost no pass of their own
 void launch_encode_sample(const RingConst &rc, const EncodeConst &ec, const SamplerConst &sc, const double *x, u64 n,
-                          u32 n_ct, i64 *m_e0, uint8_t *ve, cudaStream_t s, const u32 *sel = nullptr);
+                          u32 n_ct, i64 *m_e0, uint8_t *ve, cudaStream_t s, const u32 *sel = nullptr, bool f32 = false);
 // encrypt: three forward NTTs per (ciphertext, limb) + public-key combine -> ct[n_ct][2][L][N]
 void launch_encrypt(const RingConst &rc, const i64 *m_e0, const uint8_t *ve, const tw_t *pk_b, const tw_t *pk_a,
                     u64 *ct, u32 n_ct, cudaStream_t s);
@@ -49,7 +49,7 @@ void launch_decode_fft(const RingConst &rc, const EncodeConst &ec, const DecodeC
                        u32 n_ct, double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);
 // debug/parity taps of the two halves above
 void launch_encode_only(const RingConst &rc, const EncodeConst &ec, const double *x, u64 n, u32 n_ct, i64 *m,
-                        cudaStream_t s, const u32 *sel = nullptr);
+                        cudaStream_t s, const u32 *sel = nullptr, bool f32 = false);
 void launch_crt_only(const RingConst &rc, const DecodeConst &dc, const u64 *coeff, u32 n_ct, i64 *hi, u64 *lo,
                      cudaStream_t s);
 

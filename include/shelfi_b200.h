@@ -44,7 +44,8 @@ enum {
     SHELFI_ERR_PARAMS = -4,     /* object belongs to different crypto parameters */
     SHELFI_ERR_CUDA = -5,       /* CUDA runtime failure (including: no device) */
     SHELFI_ERR_IO = -6,         /* file could not be read / written */
-    SHELFI_ERR_UNSUPPORTED = -7 /* outside what the engine implements (e.g. ring dimension != 8192) */
+    SHELFI_ERR_UNSUPPORTED = -7, /* outside what the engine implements (e.g. ring dimension != 8192) */
+    SHELFI_ERR_MEMORY = -8       /* device memory for resident ciphertexts exhausted (limit or the device itself) */
 };
 
 /* ---- lifecycle: CKKS::CKKS (src/ckks.cpp:5-9, defaults src/binding.cpp:19-23) ---- */
@@ -162,6 +163,47 @@ int shelfi_compute_weighted_average_layers_rescaled_into(shelfi_ckks *h, const u
                                                          uint64_t *lens, uint64_t *total_len);
 int shelfi_decrypt_layers(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens,
                           const uint64_t *data_dimensions, uint32_t n_layers, double *out);
+
+/* ---- resident ciphertext vectors: the same three calls with the ciphertexts left in HBM ----
+ * The reference's callers keep every serialized vector inside one process and only hand it to the next call
+ * (code/benchmark.py:459-460 encrypt, :490-493 the per-layer loop, :507-513 computeWeightedAverage, :527-528 decrypt), so
+ * nothing forces 64 bytes per parameter and learner across PCIe twice.  A shelfi_ct is a vector<Ciphertext<DCRTPoly>>
+ * held in device memory by the handle that made it: the dense payload plus what the wire format needs to write it
+ * out again.  shelfi_ct_to_blob yields exactly the bytes shelfi_encrypt / shelfi_compute_weighted_average would have
+ * returned (Serial::Serialize, src/ckks.cpp:98-101,308-310); shelfi_ct_from_blob is the inverse (Deserialize,
+ * src/ckks.cpp:172-176,278-281), so vectors enter and leave the device only when a caller needs the bytes.
+ *   shelfi_ct_encrypt          CKKS::encrypt (src/ckks.cpp:61-104).  x: n values, dtype 0 = float64, 1 = float32 (widened
+ *                              exactly on the device — what pybind's array_t<double> caster does on the host for the
+ *                              float32 state_dict arrays the reference's callers pass), in pageable or page-locked host
+ *                              memory or in device memory.  Returns when x has been read (the caller may reuse it); the
+ *                              encryption itself continues on the device, so the upload of the next learner's vector
+ *                              overlaps it.
+ *   shelfi_ct_weighted_average CKKS::computeWeightedAverage (src/ckks.cpp:264-320) over k resident vectors -> a new one;
+ *                              rescale != 0 appends PALISADE's ModReduce (see shelfi_compute_weighted_average_rescaled).
+ *   shelfi_ct_decrypt          CKKS::decrypt (src/ckks.cpp:170-213) -> n doubles in host memory; returns when they are there.
+ * Device memory comes from a per-handle pool (freed vectors are reused, cudaFree never runs on the hot path) with a
+ * byte limit: 80 % of the free device memory at first use, SHELFI_RESIDENT_LIMIT_MB, or shelfi_resident_set_limit.
+ * A call that would exceed it fails with SHELFI_ERR_MEMORY and says how much is held.  Free every vector before
+ * destroying its handle (shelfi_ckks_destroy releases the device memory of those still alive). */
+typedef struct shelfi_ct shelfi_ct;
+int shelfi_ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct **out);
+int shelfi_ct_from_blob(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, shelfi_ct **out);
+int shelfi_ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *weights, uint32_t k, int rescale,
+                               shelfi_ct **out);
+int shelfi_ct_decrypt(shelfi_ckks *h, const shelfi_ct *ct, uint64_t n, double *out);
+uint64_t shelfi_ct_blob_size(const shelfi_ct *ct);   /* bytes shelfi_ct_to_blob writes */
+int shelfi_ct_to_blob(shelfi_ckks *h, const shelfi_ct *ct, uint8_t *dst, uint64_t cap, uint64_t *blob_len);
+/* number of ciphertexts, towers per polynomial, depth / level / scaling factor of ciphertext 0; any pointer may be NULL */
+int shelfi_ct_info(const shelfi_ct *ct, uint64_t *n_ct, uint32_t *limbs, uint64_t *depth, uint64_t *level,
+                   double *scaling_factor);
+/* the dense payload u64 [n_ct][2][limbs][N] in device memory (for the shelfi_*_device calls); valid until the free */
+const uint64_t *shelfi_ct_device_ptr(const shelfi_ct *ct);
+void shelfi_ct_free(shelfi_ckks *h, shelfi_ct *ct);
+/* bytes held by live vectors, bytes parked on the free list, the limit */
+int shelfi_resident_stats(shelfi_ckks *h, uint64_t *in_use, uint64_t *pooled, uint64_t *limit);
+int shelfi_resident_set_limit(shelfi_ckks *h, uint64_t bytes);   /* also returns the parked buffers to the driver */
+/* waits for everything the handle has queued on the device (resident calls return before their kernels finish) */
+int shelfi_synchronize(shelfi_ckks *h);
 
 void shelfi_free(void *p);
 /* page-locked host memory for the *_into calls and for inputs */
