@@ -824,18 +824,83 @@ HD SamplerKey seed_key(u64 seed, u32 domain) {
 }
 // nonce word 2 names the stream; nonce words 0, 1 hold the ciphertext index (Encrypt) or (limb, attempt) (KeyGen a)
 enum { kStreamGauss = 0, kStreamTernary = 1, kStreamKeyS = 2, kStreamKeyE = 3, kStreamKeyA = 4, kStreamKeyTag = 5,
-       kStreamDecodeNoise = 6 };
-// magnitude = #{k : u >= cdf[k]} over a 32-entry table of floor(2^64 * P(|X| <= k)); bit 63 of r is the sign
-HD int gauss_from_u64(const u64 *cdf, u64 r) {
-    u64 u = r << 1;
+       kStreamDecodeNoise = 6, kStreamGaussRetry = 7, kStreamTernaryRetry = 8, kStreamKeySRetry = 9, kStreamKeyERetry = 10 };
+// Both small distributions are sampled EXACTLY (to the precision of the CDF table) from as few random bits as that
+// allows; the rare draws that need more take them from a retry stream of their own, so the common path stays
+// branch-free and a ciphertext costs 1280 ChaCha20 blocks instead of the 2560 of one 64-bit word per Gaussian and one
+// 32-bit word per ternary value.
+//   Gaussian(sigma): CDF inversion.  cdf63[k] = floor(2^63 P(|X| <= k)), k < 32.  A draw is the 63-bit number
+//     U = (h >> 1) * 2^32 + l with h, l uniform 32-bit words; magnitude = #{k : U >= cdf63[k]} (at most 31), sign = h & 1.
+//     The top 31 bits decide unless they equal the top 31 bits of a table entry (probability < 2^-26 per draw); only
+//     then is l drawn.  The result is the same as if l had always been drawn.
+//   ternary: eight 2-bit attempts from a 16-bit half word, low bits first: 0, 1, 2 -> -1, 0, +1, 3 -> next attempt;
+//     all eight rejected (probability 2^-16): the attempts continue in the retry stream.  Uniform on {-1, 0, 1}.
+struct GaussTable {
+    const u32 *hi31;   // cdf63[k] >> 32
+    const u64 *cdf63;
+};
+HD int cdf_rank32(const u32 *t, u32 m) {      // #{k < 31 : m >= t[k]} for a sorted table
     int lo = 0;
 #pragma unroll
     for (int step = 16; step >= 1; step >>= 1)
-        if (u >= cdf[lo + step - 1]) lo += step;
-    if (lo > 31) lo = 31;
-    return (r >> 63) ? -lo : lo;
+        if (m >= t[lo + step - 1]) lo += step;
+    return lo;
 }
-HD int ternary_from_u32(u32 r) { return (int)mulhi32(r, 3u) - 1; }
+HD int cdf_rank64(const u64 *t, u64 u) {
+    int lo = 0;
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1)
+        if (u >= t[lo + step - 1]) lo += step;
+    return lo;
+}
+template <class Retry>   // retry() -> the 32-bit word l of this draw
+HD int gauss_lazy(const GaussTable &g, u32 h, Retry retry) {
+    const u32 m = h >> 1;
+    int lo = cdf_rank32(g.hi31, m);
+    if (lo > 0 && g.hi31[lo - 1] == m) lo = cdf_rank64(g.cdf63, ((u64)m << 32) | retry());
+    return (h & 1u) ? -lo : lo;
+}
+HD int first_set(u32 x) {   // index of the lowest set bit, x != 0
+#ifdef __CUDA_ARCH__
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+template <class Retry>   // retry() -> a value in {-1, 0, 1} from the retry stream
+HD int ternary16(u32 h16, Retry retry) {
+    const u32 ok = ~(h16 & (h16 >> 1)) & 0x5555u;   // bit 2a set iff attempt a is not 3
+    if (ok == 0) return retry();
+    return (int)((h16 >> first_set(ok)) & 3u) - 1;
+}
+// the retry streams: one block per coefficient, counter = coefficient index
+HD u32 retry_word(const SamplerKey &key, u64 ct, u32 stream, u32 j, u32 which) {
+    u32 o[16];
+    chacha20_block(key, j, (u32)ct, (u32)(ct >> 32), stream, o);
+    u32 r = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++)
+        if ((u32)i == which) r = o[i];
+    return r;
+}
+HD int retry_ternary(const SamplerKey &key, u64 ct, u32 stream, u32 j) {
+    u32 o[16];
+    chacha20_block(key, j, (u32)ct, (u32)(ct >> 32), stream, o);
+    for (int i = 0; i < 16; i++)
+        for (int a = 0; a < 16; a++) {
+            const u32 c = (o[i] >> (2 * a)) & 3u;
+            if (c != 3u) return (int)c - 1;
+        }
+    return 0;   // 256 rejections in a row: probability 2^-512
+}
+struct GaussRetry {
+    const SamplerKey *key; u64 ct; u32 stream, j, which;
+    HD u32 operator()() const { return retry_word(*key, ct, stream, j, which); }
+};
+struct TernaryRetry {
+    const SamplerKey *key; u64 ct; u32 stream, j;
+    HD int operator()() const { return retry_ternary(*key, ct, stream, j); }
+};
 
 // ------------------------------------------------------------------------------------------
 // canonical-embedding FFT (FFTSpecial / FFTSpecialInv), FP64, no fused multiply-add: llround()
@@ -1104,7 +1169,7 @@ constexpr int kMaxLearnersPerLaunch = 16;
 struct SamplerConst {
     SamplerKey key;      // ChaCha20 key of this call (one learner's vector)
     u64 ct_index0;       // global index of the first ciphertext of this launch (shards draw the oracle's stream)
-    u64 gauss_cdf[32];   // floor(2^64 * P(|X| <= k)), k = 0..31
+    u64 gauss_cdf[32];   // cdf63: floor(2^63 * P(|X| <= k)), k = 0..31
 };
 
 struct EncodeConst {
@@ -1206,39 +1271,54 @@ HD i64 encode_coeff(const cplx *z, const EncodeConst &ec, u32 j) {
     return zi[2 * zsw(idx / ec.gap) + half];
 }
 // [PAL] Encrypt's draws for ciphertext `ct` (ckks.cpp:81,95), as counter-mode blocks:
-//   ternary block b, nonce (ct_lo, ct_hi, kStreamTernary): v[16 b + i] = floor(3 word_i / 2^32) - 1, i < 16
-//   Gaussian block b, nonce (ct_lo, ct_hi, kStreamGauss):  e0[4 b + i] from words (4i, 4i+1), e1[4 b + i] from words
-//                     (4i+2, 4i+3) as (low, high) halves of a 64-bit draw inverted through the CDF table
+//   ternary block b, nonce (ct_lo, ct_hi, kStreamTernary): v[32 b + 2 i] from the low half of word i, v[32 b + 2 i + 1]
+//                     from its high half (ternary16), i < 16
+//   Gaussian block b, nonce (ct_lo, ct_hi, kStreamGauss):  e0[8 b + i] from word 2 i, e1[8 b + i] from word 2 i + 1
+//                     (gauss_lazy), i < 8
+//   retries: block j (the coefficient), nonce (ct_lo, ct_hi, kStreamTernaryRetry / kStreamGaussRetry; the latter's
+//            word 0 serves e0[j], word 1 e1[j])
 // The small draws of one coefficient travel as one byte: bits 1..0 = v + 1, bits 7..2 = e1 + 32 (|e1| <= 31).
 HD uint8_t pack_ve(int v, int e1) { return (uint8_t)((u32)(v + 1) | ((u32)(e1 + 32) << 2)); }
 HD int ve_ternary(uint8_t b) { return (int)(b & 3u) - 1; }
 HD int ve_gauss(uint8_t b) { return (int)(b >> 2) - 32; }
-HD void sample_ternary_block(const SamplerKey &key, u64 ct, u32 b, u32 stream, int (&v)[16]) {
+// 32 ternary values of block b, as v + 1 in eight words of four bytes each
+HD void sample_ternary_block(const SamplerKey &key, u64 ct, u32 b, u32 stream, u32 retry_stream, u32 (&packed)[8]) {
     u32 o[16];
     chacha20_block(key, b, (u32)ct, (u32)(ct >> 32), stream, o);
 #pragma unroll
-    for (int i = 0; i < 16; i++) v[i] = ternary_from_u32(o[i]);
+    for (int w = 0; w < 8; w++) {
+        u32 acc = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const u32 idx = 4 * w + i;                       // coefficient 32 b + idx
+            const u32 h16 = (o[idx >> 1] >> (16 * (idx & 1u))) & 0xFFFFu;
+            const int v = ternary16(h16, TernaryRetry{&key, ct, retry_stream, 32 * b + idx});
+            acc |= (u32)(v + 1) << (8 * i);
+        }
+        packed[w] = acc;
+    }
 }
-HD void sample_gauss_block(const SamplerKey &key, const u64 *cdf, u64 ct, u32 b, int (&e0)[4], int (&e1)[4]) {
+HD void sample_gauss_block(const SamplerKey &key, const GaussTable &g, u64 ct, u32 b, int (&e0)[8], int (&e1)[8]) {
     u32 o[16];
     chacha20_block(key, b, (u32)ct, (u32)(ct >> 32), kStreamGauss, o);
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        e0[i] = gauss_from_u64(cdf, ((u64)o[4 * i + 1] << 32) | o[4 * i]);
-        e1[i] = gauss_from_u64(cdf, ((u64)o[4 * i + 3] << 32) | o[4 * i + 2]);
+    for (int i = 0; i < 8; i++) {
+        e0[i] = gauss_lazy(g, o[2 * i], GaussRetry{&key, ct, kStreamGaussRetry, 8 * b + (u32)i, 0});
+        e1[i] = gauss_lazy(g, o[2 * i + 1], GaussRetry{&key, ct, kStreamGaussRetry, 8 * b + (u32)i, 1});
     }
 }
 // [PAL] KeyGen's draws (ckks.cpp:46): s <- ternary and e <- Gaussian under the SECRET key-generation key, a <- uniform
 // mod q_l per limb (EVALUATION form) and the key tag under the PUBLIC one.
-//   s[16 b + i]: ternary block b, nonce (0, 0, kStreamKeyS)
-//   e[8 b + i] : words (2i, 2i+1) of block b, nonce (0, 0, kStreamKeyE), through the CDF table
+//   s          : ternary blocks as above with nonce (0, 0, kStreamKeyS), retries (0, 0, kStreamKeySRetry)
+//   e[16 b + i]: word i of block b, nonce (0, 0, kStreamKeyE), gauss_lazy with retries from word 0 of block 16 b + i,
+//                nonce (0, 0, kStreamKeyERetry)
 //   a_l[j]     : attempt t = 0, 1, ...: words (2 (j & 7), 2 (j & 7) + 1) of block j >> 3, nonce (l, t, kStreamKeyA),
 //                top bits(q_l) bits of the 64-bit draw, accepted when below q_l
-HD void keygen_error_block(const SamplerKey &key, const u64 *cdf, u32 b, int (&e)[8]) {
+HD void keygen_error_block(const SamplerKey &key, const GaussTable &g, u32 b, int (&e)[16]) {
     u32 o[16];
     chacha20_block(key, b, 0, 0, kStreamKeyE, o);
 #pragma unroll
-    for (int i = 0; i < 8; i++) e[i] = gauss_from_u64(cdf, ((u64)o[2 * i + 1] << 32) | o[2 * i]);
+    for (int i = 0; i < 16; i++) e[i] = gauss_lazy(g, o[i], GaussRetry{&key, 0, kStreamKeyERetry, 16 * b + (u32)i, 0});
 }
 HD u64 keygen_uniform(const SamplerKey &key, u32 l, u32 j, u64 q) {
     int qbits = 0;
@@ -1254,40 +1334,37 @@ HD u64 keygen_uniform(const SamplerKey &key, u32 l, u32 j, u64 q) {
         if (a < q) return a;
     }
 }
-// phase 1 of the sampler: ve[j] = v[j] + 1 for the n coefficients of one ciphertext (16 bytes per thread and block)
+// phase 1 of the sampler: ve[j] = v[j] + 1 for the n coefficients of one ciphertext (32 bytes per thread and block)
 HD void sample_ternary_phase(int tid, int nthreads, const SamplerKey &key, u64 ct, u32 n, uint8_t *ve) {
-    for (u32 b = tid; b < (n >> 4); b += nthreads) {
-        int v[16];
-        sample_ternary_block(key, ct, b, kStreamTernary, v);
-        u32 w[4];
+    for (u32 b = tid; b < (n >> 5); b += nthreads) {
+        u32 w[8];
+        sample_ternary_block(key, ct, b, kStreamTernary, kStreamTernaryRetry, w);
+        u32 *dst = reinterpret_cast<u32 *>(ve + 32 * (size_t)b);
 #pragma unroll
-        for (int i = 0; i < 4; i++)
-            w[i] = (u32)(v[4 * i] + 1) | ((u32)(v[4 * i + 1] + 1) << 8) | ((u32)(v[4 * i + 2] + 1) << 16) |
-                   ((u32)(v[4 * i + 3] + 1) << 24);
-        u32 *dst = reinterpret_cast<u32 *>(ve + 16 * (size_t)b);
-        dst[0] = w[0]; dst[1] = w[1]; dst[2] = w[2]; dst[3] = w[3];
+        for (int i = 0; i < 8; i++) dst[i] = w[i];
     }
 }
 // phase 2 (after a barrier): m_e0[j] = coefficient j of the encoded message + e0[j]; e1[j] joins v[j] in ve[j].
 // `z` = the finalized FFT tile (ring dimension 8192), or null when m_e0 already holds the message (larger rings).
 HD void sample_gauss_phase(int tid, int nthreads, const cplx *z, const EncodeConst &ec, const SamplerKey &key,
-                           const u64 *cdf, u64 ct, u32 n, i64 *m_e0, uint8_t *ve, u64 keep = 0) {
-    for (u32 b = tid; b < (n >> 2); b += nthreads) {
-        int e0[4], e1[4];
-        sample_gauss_block(key, cdf, ct, b, e0, e1);
-        u32 *vw = reinterpret_cast<u32 *>(ve + 4 * (size_t)b);
-        u32 w = *vw;
-        u64 m[4];
+                           const GaussTable &g, u64 ct, u32 n, i64 *m_e0, uint8_t *ve, u64 keep = 0) {
+    for (u32 b = tid; b < (n >> 3); b += nthreads) {
+        int e0[8], e1[8];
+        sample_gauss_block(key, g, ct, b, e0, e1);
+        u32 *vw = reinterpret_cast<u32 *>(ve + 8 * (size_t)b);
+        u32 w0 = vw[0], w1 = vw[1];
+        u64 m[8];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const u32 j = 4 * b + i;
+        for (int i = 0; i < 8; i++) {
+            const u32 j = 8 * b + i;
             m[i] = (u64)((z ? encode_coeff(z, ec, j) : m_e0[j]) + (i64)e0[i]);
-            w |= (u32)(e1[i] + 32) << (8 * i + 2);
+            if (i < 4) w0 |= (u32)(e1[i] + 32) << (8 * i + 2);
+            else w1 |= (u32)(e1[i] + 32) << (8 * (i - 4) + 2);
         }
-        *vw = w;
-        u64x2 *dst = reinterpret_cast<u64x2 *>(m_e0 + 4 * (size_t)b);
-        st_pair(dst, u64x2{m[0], m[1]}, keep, false);
-        st_pair(dst + 1, u64x2{m[2], m[3]}, keep, false);
+        vw[0] = w0; vw[1] = w1;
+        u64x2 *dst = reinterpret_cast<u64x2 *>(m_e0 + 8 * (size_t)b);
+#pragma unroll
+        for (int i = 0; i < 4; i++) st_pair(dst + i, u64x2{m[2 * i], m[2 * i + 1]}, keep, false);
     }
 }
 HD u64 small_to_mod(int x, u64 q) { return x >= 0 ? (u64)x : q - (u64)(-x); }

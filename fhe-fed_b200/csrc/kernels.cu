@@ -378,12 +378,16 @@ constexpr int kSampleThreads = 256;
 __global__ void __launch_bounds__(kSampleThreads) sample_add_kernel(const __grid_constant__ SamplerConst sc, u32 n_ring,
                                                                     i64 *m_e0, uint8_t *ve) {
     __shared__ u64 cdf[32];
-    if (threadIdx.x < 32) cdf[threadIdx.x] = sc.gauss_cdf[threadIdx.x];
+    __shared__ u32 cdf_hi[32];
+    if (threadIdx.x < 32) {
+        cdf[threadIdx.x] = sc.gauss_cdf[threadIdx.x];
+        cdf_hi[threadIdx.x] = (u32)(sc.gauss_cdf[threadIdx.x] >> 32);
+    }
     const u64 ct = blockIdx.x;
     uint8_t *ve_row = ve + ct * (u64)n_ring;
     sample_ternary_phase(threadIdx.x, kSampleThreads, sc.key, sc.ct_index0 + ct, n_ring, ve_row);
     __syncthreads();   // the bytes written above are completed by other threads of this block below
-    sample_gauss_phase(threadIdx.x, kSampleThreads, nullptr, EncodeConst{}, sc.key, cdf, sc.ct_index0 + ct, n_ring,
+    sample_gauss_phase(threadIdx.x, kSampleThreads, nullptr, EncodeConst{}, sc.key, GaussTable{cdf_hi, cdf}, sc.ct_index0 + ct, n_ring,
                        m_e0 + ct * (u64)n_ring, ve_row);
 }
 
@@ -478,6 +482,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     extern __shared__ __align__(16) u64 sm[];
     cplx *z = reinterpret_cast<cplx *>(sm);
     __shared__ u64 cdf[32];
+    __shared__ u32 cdf_hi[32];
     __shared__ __align__(16) uint8_t ve[kN];
     const int tid = threadIdx.x;
     const u32 learner = blockIdx.x / eb.n_ct;
@@ -485,7 +490,10 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     const double *x = eb.x[learner];
     u64 *ct_out = eb.ct[learner];
     const u64 ct_index = sc.ct_index0 + ct;
-    if (tid < 32) cdf[tid] = sc.gauss_cdf[tid];
+    if (tid < 32) {
+        cdf[tid] = sc.gauss_cdf[tid];
+        cdf_hi[tid] = (u32)(sc.gauss_cdf[tid] >> 32);
+    }
     const u64 first = ct * ec.batch;
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
     const u32 L = rc.limbs;
@@ -511,7 +519,7 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __g
     }
     encode_finalize(tid, kNttThreads, z, ec);
     __syncthreads();
-    sample_gauss_phase(tid, kNttThreads, z, ec, eb.key[learner], cdf, ct_index, kN, m_row, ve, keep);
+    sample_gauss_phase(tid, kNttThreads, z, ec, eb.key[learner], GaussTable{cdf_hi, cdf}, ct_index, kN, m_row, ve, keep);
     __syncthreads();  // the parked row and `ve` are visible to all threads of the block; the tile is free
     for (u32 li = 0; li < L; li++) {
         const u32 l = flip ? flip - li : li;
@@ -550,19 +558,27 @@ __global__ void __launch_bounds__(kKeygenThreads) keygen_sample_kernel(const __g
                                                                        u64 *a) {
     const u32 n = rc.n, L = rc.limbs;
     const u32 t = blockIdx.x * kKeygenThreads + threadIdx.x, stride = gridDim.x * kKeygenThreads;
-    for (u32 b = t; b < (n >> 4); b += stride) {
-        int sv[16];
-        sample_ternary_block(secret.key, 0, b, kStreamKeyS, sv);
-        for (u32 l = 0; l < L; l++)
-#pragma unroll
-            for (int i = 0; i < 16; i++) rows[(size_t)l * n + 16 * b + i] = small_to_mod(sv[i], rc.limb[l].q);
+    __shared__ u64 cdf[32];
+    __shared__ u32 cdf_hi[32];
+    if (threadIdx.x < 32) {
+        cdf[threadIdx.x] = secret.gauss_cdf[threadIdx.x];
+        cdf_hi[threadIdx.x] = (u32)(secret.gauss_cdf[threadIdx.x] >> 32);
     }
-    for (u32 b = t; b < (n >> 3); b += stride) {
-        int ev[8];
-        keygen_error_block(secret.key, secret.gauss_cdf, b, ev);
+    __syncthreads();
+    for (u32 b = t; b < (n >> 5); b += stride) {
+        u32 packed[8];
+        sample_ternary_block(secret.key, 0, b, kStreamKeyS, kStreamKeySRetry, packed);
         for (u32 l = 0; l < L; l++)
 #pragma unroll
-            for (int i = 0; i < 8; i++) rows[(size_t)(L + l) * n + 8 * b + i] = small_to_mod(ev[i], rc.limb[l].q);
+            for (int i = 0; i < 32; i++)
+                rows[(size_t)l * n + 32 * b + i] = small_to_mod((int)((packed[i >> 2] >> (8 * (i & 3))) & 3u) - 1, rc.limb[l].q);
+    }
+    for (u32 b = t; b < (n >> 4); b += stride) {
+        int ev[16];
+        keygen_error_block(secret.key, GaussTable{cdf_hi, cdf}, b, ev);
+        for (u32 l = 0; l < L; l++)
+#pragma unroll
+            for (int i = 0; i < 16; i++) rows[(size_t)(L + l) * n + 16 * b + i] = small_to_mod(ev[i], rc.limb[l].q);
     }
     for (u32 i = t; i < L * n; i += stride) {
         const u32 l = i / n, j = i - l * n;

@@ -26,10 +26,10 @@ void build_gauss_cdf(double sigma, uint64_t cdf[32]) {
     double acc = 0.0;
     for (int k = 0; k < 32; k++) {
         acc += (k == 0 ? rho[0] : 2.0 * rho[k]) / total;
-        double v = std::ldexp(acc, 64);
-        cdf[k] = (v >= 18446744073709551615.0) ? UINT64_MAX : (uint64_t)v;
+        double v = std::ldexp(acc, 63);
+        cdf[k] = (v >= 9223372036854775807.0) ? (UINT64_MAX >> 1) : (uint64_t)v;
     }
-    cdf[31] = UINT64_MAX;
+    cdf[31] = UINT64_MAX >> 1;
 }
 
 std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *lc, std::vector<tw_t> *tw,

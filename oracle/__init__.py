@@ -102,6 +102,8 @@ def lib():
         "orc_fft_special_inv": (None, [C.c_void_p, C.c_void_p, C.c_uint32]),
         "orc_chacha20_block": (None, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
         "orc_seed_key": (None, [C.c_uint64, C.c_uint32, C.c_void_p]),
+        "orc_gauss_from_words": (C.c_int64, [C.c_void_p, C.c_uint32, C.c_uint32]),
+        "orc_ternary_from_half": (C.c_int64, [C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]),
         "orc_sample_encrypt_noise": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
         "orc_encode_coeffs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
         "orc_encrypt_ct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p]),
@@ -244,6 +246,9 @@ class Oracle:
         v = np.ascontiguousarray(z, dtype=np.complex128).copy()
         lib().orc_fft_special_inv(self._h, v.ctypes.data, v.size)
         return v
+
+    def gauss_from_words(self, h: int, l: int) -> int:
+        return lib().orc_gauss_from_words(self._h, h, l)
 
     def sample_noise(self, seed, ct_index):
         n = self.ring_dim

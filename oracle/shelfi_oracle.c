@@ -215,8 +215,8 @@ static void free_tables(orc_ctx *c) {
     c->rot_group = NULL; c->ksi = NULL;
 }
 
-/* Discrete Gaussian CDF table shared with the device sampler (DESIGN.md §5):
- * cdf[k] = floor(2^64 * P(|X| <= k)), P(X = x) ~ exp(-x^2 / (2 sigma^2)), k = 0..31. */
+/* Discrete Gaussian CDF table shared with the device sampler (DESIGN.md 4.2):
+ * cdf[k] = floor(2^63 * P(|X| <= k)), P(X = x) ~ exp(-x^2 / (2 sigma^2)), k = 0..31. */
 static void build_gauss_cdf(double sigma, uint64_t cdf[32]) {
     double rho[64], total = 0.0;
     for (int k = 0; k < 64; k++) rho[k] = exp(-(double)k * (double)k / (2.0 * sigma * sigma));
@@ -225,10 +225,10 @@ static void build_gauss_cdf(double sigma, uint64_t cdf[32]) {
     double acc = 0.0;
     for (int k = 0; k < 32; k++) {
         acc += (k == 0 ? rho[0] : 2.0 * rho[k]) / total;
-        double v = ldexp(acc, 64);
-        cdf[k] = (v >= 18446744073709551615.0) ? UINT64_MAX : (uint64_t)v;
+        double v = ldexp(acc, 63);
+        cdf[k] = (v >= 9223372036854775807.0) ? (UINT64_MAX >> 1) : (uint64_t)v;
     }
-    cdf[31] = UINT64_MAX;
+    cdf[31] = UINT64_MAX >> 1;
 }
 
 static void build_tables(orc_ctx *c) {
@@ -434,41 +434,85 @@ void orc_seed_key(uint64_t seed, uint32_t domain, uint32_t key[8]) {
 }
 /* stream ids: nonce word 2 */
 enum { STREAM_GAUSS = 0, STREAM_TERNARY = 1, STREAM_KEY_S = 2, STREAM_KEY_E = 3, STREAM_KEY_A = 4, STREAM_KEY_TAG = 5,
-       STREAM_DECODE_NOISE = 6 };
+       STREAM_DECODE_NOISE = 6, STREAM_GAUSS_RETRY = 7, STREAM_TERNARY_RETRY = 8, STREAM_KEY_S_RETRY = 9,
+       STREAM_KEY_E_RETRY = 10 };
 
-static inline int64_t gauss_from_u64(const uint64_t cdf[32], uint64_t r) {
-    /* bit 63 = sign, the other 63 bits (shifted up) are compared against the magnitude CDF */
-    uint64_t u = r << 1;
-    int neg = (int)(r >> 63);
-    int lo = 0; /* magnitude = number of k with u >= cdf[k]; binary search over 32 entries */
-    for (int step = 16; step >= 1; step >>= 1)
-        if (u >= cdf[lo + step - 1]) lo += step;
-    if (lo > 31) lo = 31;
-    return neg ? -(int64_t)lo : (int64_t)lo;
+/* Discrete Gaussian by CDF inversion on a 63-bit uniform U = (h >> 1) * 2^32 + l: magnitude = #{k < 31 : U >= cdf[k]},
+ * sign = h & 1.  Written the plain way: l is always passed in.  The device decides from the top 31 bits and draws l only
+ * when they tie with a table entry; the value is the same (tests/test_sampler_cpu.py checks the two against each other
+ * on ties and non-ties), so here the caller simply fetches l from the retry stream whenever a tie is possible. */
+static inline int64_t gauss_from_u63(const uint64_t cdf[32], uint32_t h, uint32_t l) {
+    uint64_t u = ((uint64_t)(h >> 1) << 32) | l;
+    int mag = 0;
+    for (int k = 0; k < 31; k++)
+        if (u >= cdf[k]) mag++;
+    return (h & 1) ? -(int64_t)mag : (int64_t)mag;
 }
-static inline int64_t ternary_from_u32(uint32_t r) { return (int64_t)(((uint64_t)r * 3) >> 32) - 1; }
+static inline int gauss_needs_low_word(const uint64_t cdf[32], uint32_t h) {
+    for (int k = 0; k < 31; k++)
+        if ((uint32_t)(cdf[k] >> 32) == (h >> 1)) return 1;
+    return 0;
+}
+int64_t orc_gauss_from_words(const orc_ctx *c, uint32_t h, uint32_t l) { return gauss_from_u63(c->gauss_cdf, h, l); }
+/* one Gaussian draw: h from the main stream, l (if a tie makes it matter) word `which` of retry block j */
+static int64_t gauss_draw(const uint64_t cdf[32], uint32_t h, const uint32_t key[8], const uint32_t nonce_retry[3], uint32_t j,
+                          int which) {
+    uint32_t l = 0;
+    if (gauss_needs_low_word(cdf, h)) {
+        uint32_t out[16];
+        orc_chacha20_block(key, j, nonce_retry, out);
+        l = out[which];
+    }
+    return gauss_from_u63(cdf, h, l);
+}
+/* uniform on {-1, 0, 1}: 2-bit attempts, low bits first, 3 = rejected; eight attempts in the 16-bit half word, then
+ * the 256 attempts of retry block j */
+static int64_t ternary_draw(uint32_t h16, const uint32_t key[8], const uint32_t nonce_retry[3], uint32_t j) {
+    for (int a = 0; a < 8; a++) {
+        uint32_t c = (h16 >> (2 * a)) & 3;
+        if (c != 3) return (int64_t)c - 1;
+    }
+    uint32_t out[16];
+    orc_chacha20_block(key, j, nonce_retry, out);
+    for (int i = 0; i < 16; i++)
+        for (int a = 0; a < 16; a++) {
+            uint32_t c = (out[i] >> (2 * a)) & 3;
+            if (c != 3) return (int64_t)c - 1;
+        }
+    return 0;
+}
+int64_t orc_ternary_from_half(uint32_t h16, const uint32_t key[8], const uint32_t nonce_retry[3], uint32_t j) {
+    return ternary_draw(h16, key, nonce_retry, j);
+}
+static void ternary_stream(const uint32_t key[8], uint32_t n0, uint32_t n1, uint32_t stream, uint32_t retry_stream, uint32_t N,
+                           int64_t *v) {
+    uint32_t out[16], nonce[3] = {n0, n1, stream}, nr[3] = {n0, n1, retry_stream};
+    for (uint32_t b = 0; b < N / 32; b++) {
+        orc_chacha20_block(key, b, nonce, out);
+        for (uint32_t i = 0; i < 32; i++)
+            v[32 * b + i] = ternary_draw((out[i >> 1] >> (16 * (i & 1))) & 0xFFFF, key, nr, 32 * b + i);
+    }
+}
 
 /* [PAL] LPAlgorithmCKKS::Encrypt draws v <- TernaryUniform (mode OPTIMIZED), e0,e1 <- DiscreteGaussian(sigma).
  * PALISADE's own PRNG is seeded from OS entropy, so only the distribution is pinned; this spec makes
  * oracle and device draw the same values for a given (key, ct_index):
- *   ternary block b, nonce (ct_lo, ct_hi, 1): v[16b + i] from word i
- *   gauss   block b, nonce (ct_lo, ct_hi, 0): e0[4b + i] from words (4i, 4i+1), e1[4b + i] from words (4i+2, 4i+3) */
+ *   ternary block b, nonce (ct_lo, ct_hi, 1): v[32b + 2i], v[32b + 2i + 1] from the low / high half of word i
+ *   gauss   block b, nonce (ct_lo, ct_hi, 0): e0[8b + i] from word 2i, e1[8b + i] from word 2i + 1
+ *   retries: block j = coefficient, nonce (ct_lo, ct_hi, 8) for ternary, (ct_lo, ct_hi, 7) words 0 / 1 for e0 / e1 */
 void orc_sample_encrypt_noise(const orc_ctx *c, uint64_t seed, uint64_t ct, int64_t *v, int64_t *e0, int64_t *e1) {
     uint32_t N = c->wp.N, out[16], key[8];
     orc_seed_key(seed, KEY_ENCRYPT, key);
     uint32_t ng[3] = {(uint32_t)ct, (uint32_t)(ct >> 32), STREAM_GAUSS};
-    uint32_t nt[3] = {(uint32_t)ct, (uint32_t)(ct >> 32), STREAM_TERNARY};
-    for (uint32_t b = 0; b < N / 4; b++) {
+    uint32_t ngr[3] = {(uint32_t)ct, (uint32_t)(ct >> 32), STREAM_GAUSS_RETRY};
+    for (uint32_t b = 0; b < N / 8; b++) {
         orc_chacha20_block(key, b, ng, out);
-        for (int i = 0; i < 4; i++) {
-            e0[4 * b + i] = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[4 * i + 1] << 32) | out[4 * i]);
-            e1[4 * b + i] = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[4 * i + 3] << 32) | out[4 * i + 2]);
+        for (uint32_t i = 0; i < 8; i++) {
+            e0[8 * b + i] = gauss_draw(c->gauss_cdf, out[2 * i], key, ngr, 8 * b + i, 0);
+            e1[8 * b + i] = gauss_draw(c->gauss_cdf, out[2 * i + 1], key, ngr, 8 * b + i, 1);
         }
     }
-    for (uint32_t b = 0; b < N / 16; b++) {
-        orc_chacha20_block(key, b, nt, out);
-        for (int i = 0; i < 16; i++) v[16 * b + i] = ternary_from_u32(out[i]);
-    }
+    ternary_stream(key, (uint32_t)ct, (uint32_t)(ct >> 32), STREAM_TERNARY, STREAM_TERNARY_RETRY, N, v);
 }
 
 /* ------------------------------------------------------------------------------------------- */
@@ -1480,24 +1524,26 @@ int orc_gen_context_and_keys_ex(uint32_t batch, uint32_t scale_bits, uint32_t mu
 
     /* [PAL] LPAlgorithmCKKS::KeyGen: a <- uniform (EVALUATION), s <- ternary, e <- Gaussian, b = e - a*s.
      * s and e are drawn under the secret test key, a and the key tag under the public one:
-     *   s[16b + i]: word i of block b, nonce (0, 0, STREAM_KEY_S);  e[8b + i]: words (2i, 2i+1) of block b, nonce (0, 0, STREAM_KEY_E)
+     *   s: the ternary stream of nonce (0, 0, STREAM_KEY_S);  e[16b + i]: word i of block b, nonce (0, 0, STREAM_KEY_E)
      *   a_l[j]: attempt t: words (2(j&7), 2(j&7)+1) of block j >> 3, nonce (l, t, STREAM_KEY_A), top bits(q_l) bits, accepted below q_l */
     size_t words = (size_t)p.L * N;
     uint64_t *pk = malloc(2 * words * 8), *sk = malloc(words * 8), *e = malloc(words * 8);
     uint32_t out[16], ksec[8], kpub[8];
     orc_seed_key(seed, KEY_KEYGEN_SECRET, ksec);
     orc_seed_key(seed, KEY_KEYGEN_PUBLIC, kpub);
-    uint32_t n_s[3] = {0, 0, STREAM_KEY_S}, n_e[3] = {0, 0, STREAM_KEY_E};
-    for (uint32_t b = 0; b < N / 16; b++) {
-        orc_chacha20_block(ksec, b, n_s, out);
-        for (int i = 0; i < 16; i++)
-            for (int l = 0; l < p.L; l++) sk[(size_t)l * N + 16 * b + i] = signed_mod(ternary_from_u32(out[i]), p.q[l]);
+    {
+        int64_t *sv = malloc((size_t)N * 8);
+        ternary_stream(ksec, 0, 0, STREAM_KEY_S, STREAM_KEY_S_RETRY, N, sv);
+        for (uint32_t j = 0; j < N; j++)
+            for (int l = 0; l < p.L; l++) sk[(size_t)l * N + j] = signed_mod(sv[j], p.q[l]);
+        free(sv);
     }
-    for (uint32_t b = 0; b < N / 8; b++) {
+    uint32_t n_e[3] = {0, 0, STREAM_KEY_E}, n_er[3] = {0, 0, STREAM_KEY_E_RETRY};
+    for (uint32_t b = 0; b < N / 16; b++) {
         orc_chacha20_block(ksec, b, n_e, out);
-        for (int i = 0; i < 8; i++) {
-            int64_t ev = gauss_from_u64(c->gauss_cdf, ((uint64_t)out[2 * i + 1] << 32) | out[2 * i]);
-            for (int l = 0; l < p.L; l++) e[(size_t)l * N + 8 * b + i] = signed_mod(ev, p.q[l]);
+        for (uint32_t i = 0; i < 16; i++) {
+            int64_t ev = gauss_draw(c->gauss_cdf, out[i], ksec, n_er, 16 * b + i, 0);
+            for (int l = 0; l < p.L; l++) e[(size_t)l * N + 16 * b + i] = signed_mod(ev, p.q[l]);
         }
     }
     for (int l = 0; l < p.L; l++) {

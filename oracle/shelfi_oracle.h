@@ -81,6 +81,9 @@ void orc_fft_special_inv(const orc_ctx *c, double *re_im, uint32_t size);
 /* RFC 8439 ChaCha20 block function and the test-key layout shared with the device sampler */
 void orc_chacha20_block(const uint32_t key[8], uint32_t counter, const uint32_t nonce[3], uint32_t out[16]);
 void orc_seed_key(uint64_t seed, uint32_t domain, uint32_t key[8]);
+/* the two primitive samplers on caller-chosen random words (unit tests of the rare paths) */
+int64_t orc_gauss_from_words(const orc_ctx *c, uint32_t h, uint32_t l);
+int64_t orc_ternary_from_half(uint32_t h16, const uint32_t key[8], const uint32_t nonce_retry[3], uint32_t j);
 /* fills v (ternary), e0, e1 (discrete Gaussian) for ciphertext index ct_index: N values each */
 void orc_sample_encrypt_noise(const orc_ctx *c, uint64_t seed, uint64_t ct_index, int64_t *v, int64_t *e0,
                               int64_t *e1);

@@ -67,6 +67,10 @@ class Emu:
             "emu_encrypt": (None, [vp, vp, vp, vp, vp, vp]),
             "emu_chacha20_block": (None, [vp, u32, vp, vp]),
             "emu_keygen_draws": (None, [vp, u64, vp, vp, vp]),
+            "emu_gauss_lazy": (C.c_int, [vp, u32, u32, C.POINTER(C.c_int)]),
+            "emu_ternary16": (C.c_int, [u32, C.c_int, C.POINTER(C.c_int)]),
+            "emu_retry_ternary": (C.c_int, [vp, u64, u32, u32]),
+            "emu_gauss_table": (None, [vp, vp]),
             "emu_decrypt": (None, [vp, vp, vp, f64, f64, vp, u64, vp, vp, vp]),
             "emu_create_ex": (vp, [vp, vp, u32, u32, u32, u32, f64]),
             "emu_weighted_sum": (None, [vp, u32, C.POINTER(vp), vp, u32, vp, u32]),

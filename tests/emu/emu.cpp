@@ -24,6 +24,8 @@ struct Emu {
     Crt2Const crt;
     CrtNConst crtn;
     uint64_t cdf[32];
+    uint32_t cdf_hi[32];
+    GaussTable gauss() const { return GaussTable{cdf_hi, cdf}; }
     std::vector<tw_t> tw[kMaxLimbs], itw[kMaxLimbs];
     std::vector<double> dtw[kMaxLimbs];
     bool fp64 = true;
@@ -103,6 +105,7 @@ Emu *emu_create_ex(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint3
     e->crt = make_crt2(q[0], limbs >= 2 ? q[1] : 0);
     e->crtn = make_crtn(q, limbs);
     build_gauss_cdf(sigma, e->cdf);
+    for (int k = 0; k < 32; k++) e->cdf_hi[k] = (uint32_t)(e->cdf[k] >> 32);
     return e;
 }
 Emu *emu_create(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint32_t slots, uint32_t batch, double sigma) {
@@ -248,12 +251,12 @@ void emu_encode_sample(const Emu *e, const double *x, uint64_t n_valid, uint64_t
         std::vector<cplx> z;
         replay_encode(e, x, n_valid, z);
         FOR_THREADS(kNttThreads)
-            sample_gauss_phase(tid, kNttThreads, z.data(), e->ec, key, e->cdf, ct_index, e->rc.n, (i64 *)m_e0, ve);
+            sample_gauss_phase(tid, kNttThreads, z.data(), e->ec, key, e->gauss(), ct_index, e->rc.n, (i64 *)m_e0, ve);
         return;
     }
     emu_encode(e, x, n_valid, m_e0);
     FOR_THREADS(kNttThreads)
-        sample_gauss_phase(tid, kNttThreads, nullptr, e->ec, key, e->cdf, ct_index, e->rc.n, (i64 *)m_e0, ve);
+        sample_gauss_phase(tid, kNttThreads, nullptr, e->ec, key, e->gauss(), ct_index, e->rc.n, (i64 *)m_e0, ve);
 }
 // one ChaCha20 block through the device code's implementation (RFC 8439 known-answer test)
 void emu_chacha20_block(const uint32_t *key, uint32_t counter, const uint32_t *nonce, uint32_t *out) {
@@ -263,18 +266,38 @@ void emu_chacha20_block(const uint32_t *key, uint32_t counter, const uint32_t *n
     chacha20_block(k, counter, nonce[0], nonce[1], nonce[2], o);
     std::memcpy(out, o, sizeof o);
 }
+// the primitive samplers on caller-chosen random words: gauss_lazy with l supplied (used only on a tie of the top 31
+// bits; *used_retry reports it), ternary16 with the retry value supplied
+int emu_gauss_lazy(const Emu *e, uint32_t h, uint32_t l, int *used_retry) {
+    int used = 0;
+    int r = gauss_lazy(e->gauss(), h, [&] { used = 1; return l; });
+    if (used_retry) *used_retry = used;
+    return r;
+}
+int emu_ternary16(uint32_t h16, int retry_value, int *used_retry) {
+    int used = 0;
+    int r = ternary16(h16, [&] { used = 1; return retry_value; });
+    if (used_retry) *used_retry = used;
+    return r;
+}
+int emu_retry_ternary(const uint32_t *key, uint64_t ct, uint32_t stream, uint32_t j) {
+    SamplerKey k;
+    std::memcpy(k.k, key, sizeof k.k);
+    return retry_ternary(k, ct, stream, j);
+}
+void emu_gauss_table(const Emu *e, uint64_t *cdf63) { std::memcpy(cdf63, e->cdf, sizeof e->cdf); }
 // the device keygen draws under the test keys of `seed`: s[N], e[N] (signed), a[L][N]
 void emu_keygen_draws(const Emu *e, uint64_t seed, int64_t *s, int64_t *err, uint64_t *a) {
     const SamplerKey ks = seed_key(seed, kKeyDomainKeySecret), kp = seed_key(seed, kKeyDomainKeyPublic);
+    for (u32 b = 0; b < e->rc.n / 32; b++) {
+        u32 w[8];
+        sample_ternary_block(ks, 0, b, kStreamKeyS, kStreamKeySRetry, w);
+        for (int i = 0; i < 32; i++) s[32 * b + i] = (int)((w[i >> 2] >> (8 * (i & 3))) & 3u) - 1;
+    }
     for (u32 b = 0; b < e->rc.n / 16; b++) {
         int v[16];
-        sample_ternary_block(ks, 0, b, kStreamKeyS, v);
-        for (int i = 0; i < 16; i++) s[16 * b + i] = v[i];
-    }
-    for (u32 b = 0; b < e->rc.n / 8; b++) {
-        int v[8];
-        keygen_error_block(ks, e->cdf, b, v);
-        for (int i = 0; i < 8; i++) err[8 * b + i] = v[i];
+        keygen_error_block(ks, e->gauss(), b, v);
+        for (int i = 0; i < 16; i++) err[16 * b + i] = v[i];
     }
     for (u32 l = 0; l < e->rc.limbs; l++)
         for (u32 j = 0; j < e->rc.n; j++) a[(size_t)l * e->rc.n + j] = keygen_uniform(kp, l, j, e->rc.limb[l].q);
