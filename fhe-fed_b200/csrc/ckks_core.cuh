@@ -19,8 +19,10 @@
 
 #ifdef __CUDACC__
 #define HD __host__ __device__ __forceinline__
+#define HD_COLD static __host__ __device__ __noinline__    // rare paths: one out-of-line copy, not one per call site
 #else
 #define HD inline
+#define HD_COLD inline
 #endif
 
 namespace shelfi {
@@ -874,7 +876,7 @@ HD int ternary16(u32 h16, Retry retry) {
     return (int)((h16 >> first_set(ok)) & 3u) - 1;
 }
 // the retry streams: one block per coefficient, counter = coefficient index
-HD u32 retry_word(const SamplerKey &key, u64 ct, u32 stream, u32 j, u32 which) {
+HD_COLD u32 retry_word(const SamplerKey &key, u64 ct, u32 stream, u32 j, u32 which) {
     u32 o[16];
     chacha20_block(key, j, (u32)ct, (u32)(ct >> 32), stream, o);
     u32 r = 0;
@@ -883,7 +885,7 @@ HD u32 retry_word(const SamplerKey &key, u64 ct, u32 stream, u32 j, u32 which) {
         if ((u32)i == which) r = o[i];
     return r;
 }
-HD int retry_ternary(const SamplerKey &key, u64 ct, u32 stream, u32 j) {
+HD_COLD int retry_ternary(const SamplerKey &key, u64 ct, u32 stream, u32 j) {
     u32 o[16];
     chacha20_block(key, j, (u32)ct, (u32)(ct >> 32), stream, o);
     for (int i = 0; i < 16; i++)
@@ -1281,10 +1283,12 @@ HD i64 encode_coeff(const cplx *z, const EncodeConst &ec, u32 j) {
 HD uint8_t pack_ve(int v, int e1) { return (uint8_t)((u32)(v + 1) | ((u32)(e1 + 32) << 2)); }
 HD int ve_ternary(uint8_t b) { return (int)(b & 3u) - 1; }
 HD int ve_gauss(uint8_t b) { return (int)(b >> 2) - 32; }
-// 32 ternary values of block b, as v + 1 in eight words of four bytes each
+// 32 ternary values of block b, as v + 1 in eight words of four bytes each.  Draws whose eight attempts were all
+// rejected are noted in a mask and settled afterwards, so the common path holds no call.
 HD void sample_ternary_block(const SamplerKey &key, u64 ct, u32 b, u32 stream, u32 retry_stream, u32 (&packed)[8]) {
     u32 o[16];
     chacha20_block(key, b, (u32)ct, (u32)(ct >> 32), stream, o);
+    u32 pending = 0;
 #pragma unroll
     for (int w = 0; w < 8; w++) {
         u32 acc = 0;
@@ -1292,19 +1296,56 @@ HD void sample_ternary_block(const SamplerKey &key, u64 ct, u32 b, u32 stream, u
         for (int i = 0; i < 4; i++) {
             const u32 idx = 4 * w + i;                       // coefficient 32 b + idx
             const u32 h16 = (o[idx >> 1] >> (16 * (idx & 1u))) & 0xFFFFu;
-            const int v = ternary16(h16, TernaryRetry{&key, ct, retry_stream, 32 * b + idx});
-            acc |= (u32)(v + 1) << (8 * i);
+            const u32 ok = ~(h16 & (h16 >> 1)) & 0x5555u;    // ternary16 with the retry deferred
+            if (ok == 0) pending |= 1u << idx;
+            acc |= (ok ? ((h16 >> first_set(ok)) & 3u) : 1u) << (8 * i);
         }
         packed[w] = acc;
     }
+    while (pending) {
+        const u32 idx = (u32)first_set(pending);
+        pending &= pending - 1;
+        const u32 v1 = (u32)(retry_ternary(key, ct, retry_stream, 32 * b + idx) + 1);
+#pragma unroll
+        for (int w = 0; w < 8; w++)
+            if ((u32)w == (idx >> 2)) packed[w] = (packed[w] & ~(0xFFu << (8 * (idx & 3u)))) | (v1 << (8 * (idx & 3u)));
+    }
+}
+// one Gaussian draw from its first word; a tie of the top 31 bits with a table entry is reported, not settled
+HD int gauss_fast(const GaussTable &g, u32 h, bool &tie) {
+    const u32 m = h >> 1;
+    const int lo = cdf_rank32(g.hi31, m);
+    tie = lo > 0 && g.hi31[lo - 1] == m;
+    return (h & 1u) ? -lo : lo;
+}
+HD_COLD int gauss_settle(const GaussTable &g, u32 h, const SamplerKey &key, u64 ct, u32 stream, u32 j, u32 which) {
+    const int lo = cdf_rank64(g.cdf63, ((u64)(h >> 1) << 32) | retry_word(key, ct, stream, j, which));
+    return (h & 1u) ? -lo : lo;
 }
 HD void sample_gauss_block(const SamplerKey &key, const GaussTable &g, u64 ct, u32 b, int (&e0)[8], int (&e1)[8]) {
     u32 o[16];
     chacha20_block(key, b, (u32)ct, (u32)(ct >> 32), kStreamGauss, o);
+    u32 pending = 0;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-        e0[i] = gauss_lazy(g, o[2 * i], GaussRetry{&key, ct, kStreamGaussRetry, 8 * b + (u32)i, 0});
-        e1[i] = gauss_lazy(g, o[2 * i + 1], GaussRetry{&key, ct, kStreamGaussRetry, 8 * b + (u32)i, 1});
+        bool t0, t1;
+        e0[i] = gauss_fast(g, o[2 * i], t0);
+        e1[i] = gauss_fast(g, o[2 * i + 1], t1);
+        pending |= (t0 ? 1u : 0u) << (2 * i) | (t1 ? 1u : 0u) << (2 * i + 1);
+    }
+    while (pending) {
+        const u32 w = (u32)first_set(pending);
+        pending &= pending - 1;
+        u32 h = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++)
+            if ((u32)i == w) h = o[i];
+        const int v = gauss_settle(g, h, key, ct, kStreamGaussRetry, 8 * b + (w >> 1), w & 1u);
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if ((u32)(2 * i) == w) e0[i] = v;
+            if ((u32)(2 * i + 1) == w) e1[i] = v;
+        }
     }
 }
 // [PAL] KeyGen's draws (ckks.cpp:46): s <- ternary and e <- Gaussian under the SECRET key-generation key, a <- uniform
@@ -1317,8 +1358,11 @@ HD void sample_gauss_block(const SamplerKey &key, const GaussTable &g, u64 ct, u
 HD void keygen_error_block(const SamplerKey &key, const GaussTable &g, u32 b, int (&e)[16]) {
     u32 o[16];
     chacha20_block(key, b, 0, 0, kStreamKeyE, o);
-#pragma unroll
-    for (int i = 0; i < 16; i++) e[i] = gauss_lazy(g, o[i], GaussRetry{&key, 0, kStreamKeyERetry, 16 * b + (u32)i, 0});
+    for (int i = 0; i < 16; i++) {
+        bool tie;
+        e[i] = gauss_fast(g, o[i], tie);
+        if (tie) e[i] = gauss_settle(g, o[i], key, 0, kStreamKeyERetry, 16 * b + (u32)i, 0);
+    }
 }
 HD u64 keygen_uniform(const SamplerKey &key, u32 l, u32 j, u64 q) {
     int qbits = 0;
