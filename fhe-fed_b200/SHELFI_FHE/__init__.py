@@ -126,6 +126,7 @@ def lib() -> C.CDLL:
         "shelfi_peer_buffer_close": (C.c_int, [vp, vp]),
         "shelfi_peer_buffer_destroy": (C.c_int, [vp, vp]),
         "shelfi_peer_barrier_device": (C.c_int, [vp, C.POINTER(vp), u32, u32, u64, vp]),
+        "shelfi_peer_barrier_guard_device": (C.c_int, [vp, C.POINTER(vp), u32, u32, u64, vp, u64, vp]),
         "shelfi_weighted_sum_vector_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), u32, u64, vp, vp]),
         "shelfi_encrypt_selected_many_device": (C.c_int, [vp, C.POINTER(vp), u32, vp, u64, u64, C.POINTER(vp), vp]),
         "shelfi_decrypt_scatter_device": (C.c_int, [vp, vp, u64, f64, vp, vp, u64, vp]),

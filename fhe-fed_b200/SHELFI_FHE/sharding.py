@@ -124,9 +124,16 @@ class PeerGather:
         self._outs = (C.c_void_p * self.world)(*[self._ptrs[r] for r in order])
         self._flags = (C.c_void_p * self.world)(*[p + self._flag_off for p in self._ptrs])
 
-    def device_barrier(self, stream: int = 0) -> None:
-        """Queue a barrier between the ranks' streams (every rank calls it the same number of times)."""
+    def device_barrier(self, stream: int = 0, guard: bool = False) -> None:
+        """Queue a barrier between the ranks' streams (every rank calls it the same number of times).  guard=True (the
+        barrier after a decrypt): should the wait for a rank time out, the first value of that rank's slice in this
+        GPU's copy becomes NaN, so a partial gather cannot pass for a whole one (`timed_out()` tells which epoch)."""
         self._epoch += 1
+        if guard:
+            self._ckks._check(self._lib.shelfi_peer_barrier_guard_device(
+                self._ckks.handle, self._flags, self.world, self.rank, self._epoch, self._C.c_void_p(self._own),
+                self.block, self._C.c_void_p(stream)))
+            return
         self._ckks._check(self._lib.shelfi_peer_barrier_device(self._ckks.handle, self._flags, self.world, self.rank,
                                                                self._epoch, self._C.c_void_p(stream)))
 
@@ -144,7 +151,7 @@ class PeerGather:
                 self._ckks.handle, C.c_void_p(d_ct_ptr), n_ct, scaling_factor, self._outs, self.world, sh.param_first,
                 sh.param_count, C.c_void_p(stream)))
         if device_barriers:
-            self.device_barrier(stream)
+            self.device_barrier(stream, guard=True)
 
     def timed_out(self) -> int:
         """Epoch of the last barrier this rank gave up on (0 = never); synchronises the device."""

@@ -271,6 +271,13 @@ struct shelfi_ckks {
     cudaEvent_t ev_x_in[2] = {nullptr, nullptr}, ev_x_free[2] = {nullptr, nullptr}, ev_r_out = nullptr;
     bool x_busy[2] = {false, false};
     unsigned r_turn = 0;
+    // The device-resident calls run on the CALLER's stream but share this handle's scratch (encode / sample output,
+    // decrypt coefficients, CRT doubles, rescale tower).  Two calls on different streams would otherwise be free to
+    // overlap on the GPU and corrupt each other's intermediates: every such call first makes its stream wait for the
+    // event the previous one recorded after its last use of the scratch.
+    cudaEvent_t ev_scratch = nullptr;
+    cudaStream_t scratch_stream = nullptr;
+    bool scratch_used = false;
 };
 
 namespace {
@@ -540,6 +547,19 @@ int call_key(shelfi_ckks *h, uint32_t domain, SamplerKey *k) {
     return 0;
 }
 
+// scratch hand-over between caller streams (see shelfi_ckks::ev_scratch)
+int scratch_begin(shelfi_ckks *h, cudaStream_t s) {
+    if (!h->ev_scratch) CU(cudaEventCreateWithFlags(&h->ev_scratch, cudaEventDisableTiming));
+    if (h->scratch_used && s != h->scratch_stream) CU(cudaStreamWaitEvent(s, h->ev_scratch, 0));
+    return 0;
+}
+int scratch_end(shelfi_ckks *h, cudaStream_t s) {
+    CU(cudaEventRecord(h->ev_scratch, s));
+    h->scratch_stream = s;
+    h->scratch_used = true;
+    return 0;
+}
+
 // --- stage drivers (all asynchronous on `s`) ---
 // k learners' vectors (all of length n) in one launch: the grid covers k * n_ct ciphertexts, so small models still
 // fill the machine and co-resident CTAs are out of phase with one another.
@@ -554,6 +574,8 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
     sc.ct_index0 = ct_index0;
     std::memcpy(sc.gauss_cdf, h->gauss_cdf, sizeof sc.gauss_cdf);
     if (h->rc.log_blocks > 0) {
+        int src = scratch_begin(h, s);
+        if (src) return src;
         // ring dimension above one tile: encode per FFT block, sampler pass, then one CTA per (ciphertext, limb, tile);
         // a single learner already gives thousands of CTAs, so learners go one after another
         // The encode/sample kernels are latency-bound and light on the arithmetic pipes; on a second stream they run
@@ -597,7 +619,7 @@ int encrypt_dense_many(shelfi_ckks *h, const double *const *d_x, uint32_t k, uin
             if (overlap) CU(cudaEventRecord(h->ev_enc_free[b], s));
         }
         CU(cudaGetLastError());
-        return 0;
+        return scratch_end(h, s);
     }
     for (uint32_t base = 0; base < k; base += kMaxEncryptBatch) {
         EncryptBatch eb{};
@@ -669,6 +691,8 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
                   uint32_t n_peer = 0) {
     const uint64_t N = h->ctx.ring_dim;
     const LevelView lv = level_view(h, limbs);
+    int src = scratch_begin(h, s);
+    if (src) return src;
     CU(h->s_coeff.reserve(n_ct * lv.rc.limbs * N * sizeof(uint64_t)));
     timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(lv.rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
     DecodeConst dc{};
@@ -691,7 +715,7 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
         });
     }
     CU(cudaGetLastError());
-    return 0;
+    return scratch_end(h, s);
 }
 
 // [PAL] ModReduce under EXACTRESCALE (DCRTPoly::DropLastElementAndScale) on a dense batch:
@@ -707,10 +731,12 @@ int rescale_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint32_t 
         rs.inv[i] = nt::inv_mod(rs.q_last % q, q);
         rs.inv_s[i] = nt::shoup(rs.inv[i], q);
     }
+    int src = scratch_begin(h, s);
+    if (src) return src;
     CU(h->s_resc.reserve(n_ct * 2 * h->ctx.ring_dim * sizeof(uint64_t)));
     timed(h, kKRescale, s, [&] { launch_rescale(lv.rc, rs, d_ct, h->s_resc.as<u64>(), d_out, (u32)n_ct, s); });
     CU(cudaGetLastError());
-    return 0;
+    return scratch_end(h, s);
 }
 
 int check_stage(shelfi_ckks *h, bool need_pk, bool need_sk) {
@@ -1138,14 +1164,21 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
     const uint32_t L = h->ctx.limbs;
     const uint64_t N = h->ctx.ring_dim, ct_words = 2ull * L * N;
     cudaStream_t st = h->stream;
-    CU(h->s_image.reserve(image_bytes(image)));
-    CU(h->s_dense.reserve(n_ct * ct_words * 8));
-    CU(h->s_out.reserve(n * sizeof(double)));
+    // an error return must not leave copies in flight to or from the caller's buffers (they are only borrowed for the call)
+    auto bail = [&](int code) {
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        if (h->d2h_stream) cudaStreamSynchronize(h->d2h_stream);
+        return code;
+    };
+    CUB(h->s_image.reserve(image_bytes(image)));
+    CUB(h->s_dense.reserve(n_ct * ct_words * 8));
+    CUB(h->s_out.reserve(n * sizeof(double)));
     // decrypt_dense's scratch, sized once so that no launch of this call waits on a reallocation
-    CU(h->s_coeff.reserve(max_ct * L * N * sizeof(uint64_t)));
+    CUB(h->s_coeff.reserve(max_ct * L * N * sizeof(uint64_t)));
     if (general_decode(h)) {
-        CU(h->s_vals.reserve(max_ct * N * sizeof(double)));
-        if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(max_ct * (size_t)h->ec.slots * sizeof(cplx)));
+        CUB(h->s_vals.reserve(max_ct * N * sizeof(double)));
+        if (h->ec.slots > kFftFast) CUB(h->s_zs.reserve(max_ct * (size_t)h->ec.slots * sizeof(cplx)));
     }
     bool one_scale = true;
     for (const auto &m : maps[0].meta) one_scale = one_scale && m.scaling_factor == maps[0].meta[0].scaling_factor;
@@ -1157,11 +1190,11 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
         const uint32_t groups = 4;
         cudaStream_t cs = h->copy_stream;
         if (!h->d2h_stream) {
-            CU(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
-            CU(cudaEventCreateWithFlags(&h->ev_stage_out, cudaEventDisableTiming));
+            CUB(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+            CUB(cudaEventCreateWithFlags(&h->ev_stage_out, cudaEventDisableTiming));
         }
-        CU(cudaEventRecord(h->ev_done[0], st));          // the image and scratch are free once earlier work on st is done
-        CU(cudaStreamWaitEvent(cs, h->ev_done[0], 0));
+        CUB(cudaEventRecord(h->ev_done[0], st));          // the image and scratch are free once earlier work on st is done
+        CUB(cudaStreamWaitEvent(cs, h->ev_done[0], 0));
         const uint64_t layer_words = 2ull * m.ct_limbs * N;
         auto run_start = [&](uint64_t j) { return j == 0 ? m.run0[0] : m.run1[0] + (j - 1) * m.stride; };
         uint64_t got = 0;
@@ -1169,10 +1202,10 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
             // bytes up to the first run of ciphertext c1, cut on a 4 KiB boundary at or after it (aligned copies are faster)
             const uint64_t upto = g + 1 == groups ? blob_lens[0] : std::min<uint64_t>(blob_lens[0], (run_start(c1) + 4095) & ~(uint64_t)4095);
-            if (upto > got) CU(cudaMemcpyAsync(h->s_image.as<uint8_t>() + got, blobs[0] + got, upto - got, cudaMemcpyHostToDevice, cs));
+            if (upto > got) CUB(cudaMemcpyAsync(h->s_image.as<uint8_t>() + got, blobs[0] + got, upto - got, cudaMemcpyHostToDevice, cs));
             got = std::max(got, upto);
-            CU(cudaEventRecord(h->ev_copy[g & 1], cs));
-            CU(cudaStreamWaitEvent(st, h->ev_copy[g & 1], 0));
+            CUB(cudaEventRecord(h->ev_copy[g & 1], cs));
+            CUB(cudaStreamWaitEvent(st, h->ev_copy[g & 1], 0));
             uint64_t r0[2 * kMaxLimbs], r1[2 * kMaxLimbs];   // run offsets of ciphertexts c0 and c0 + 1
             for (uint32_t r = 0; r < 2 * m.ct_limbs; r++) {
                 r0[r] = c0 == 0 ? m.run0[r] : m.run1[r] + (c0 - 1) * m.stride;
@@ -1182,32 +1215,30 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             timed(h, kKUnpack, st, [&] {
                 launch_unpack(h->rc, to_runs(h, r0, r1, m.stride, m.ct_limbs), h->s_image.as<u64>(), dense, c1 - c0, st);
             });
-            CU(cudaGetLastError());
+            CUB(cudaGetLastError());
             const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
             if ((rcode = decrypt_dense(h, dense, c1 - c0, m.meta[0].scaling_factor, h->s_out.as<double>() + first, last - first,
                                        st, nullptr, m.ct_limbs))) {
-                cudaStreamSynchronize(cs);            // nothing stays in flight on the caller's buffers
-                cudaStreamSynchronize(h->d2h_stream);
-                return rcode;
+                return bail(rcode);
             }
-            CU(cudaEventRecord(h->ev_stage_out, st));
-            CU(cudaStreamWaitEvent(h->d2h_stream, h->ev_stage_out, 0));
-            CU(cudaMemcpyAsync(out + first, h->s_out.as<double>() + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost,
+            CUB(cudaEventRecord(h->ev_stage_out, st));
+            CUB(cudaStreamWaitEvent(h->d2h_stream, h->ev_stage_out, 0));
+            CUB(cudaMemcpyAsync(out + first, h->s_out.as<double>() + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost,
                                h->d2h_stream));
         }
-        CU(cudaStreamSynchronize(h->d2h_stream));
-        CU(cudaStreamSynchronize(st));
+        CUB(cudaStreamSynchronize(h->d2h_stream));
+        CUB(cudaStreamSynchronize(st));
         return 0;
     }
     for (uint32_t s = 0; s < n_layers; s++) {
         const LayerSlot &ls = slot[s];
-        if ((rcode = h2d(h, h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], st))) return rcode;
+        if ((rcode = h2d(h, h->s_image.as<uint8_t>() + ls.off, blobs[s], blob_lens[s], st))) return bail(rcode);
         u64 *dense = h->s_dense.as<u64>() + ls.ct0 * ct_words;
         timed(h, kKUnpack, st, [&] {
             launch_unpack(h->rc, to_runs(h, maps[s].run0, maps[s].run1, maps[s].stride, maps[s].ct_limbs),
                           h->s_image.as<u64>() + ls.off / 8, dense, ls.n_ct, st);
         });
-        CU(cudaGetLastError());
+        CUB(cudaGetLastError());
         // ciphertexts usually share one scaling factor; split the launch where they do not
         for (uint64_t j0 = 0; j0 < ls.n_ct;) {
             uint64_t j1 = j0 + 1;
@@ -1216,11 +1247,12 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             const uint64_t layer_words = 2ull * maps[s].ct_limbs * N;   // a rescaled layer is packed tighter
             if ((rcode = decrypt_dense(h, dense + j0 * layer_words, j1 - j0, maps[s].meta[j0].scaling_factor,
                                        h->s_out.as<double>() + ls.x0 + first, last - first, st, nullptr, maps[s].ct_limbs)))
-                return rcode;
+                return bail(rcode);
             j0 = j1;
         }
     }
-    return d2h_sync(h, out, h->s_out.p, n * sizeof(double), st);
+    if ((rcode = d2h_sync(h, out, h->s_out.p, n * sizeof(double), st))) return bail(rcode);
+    return 0;
 }
 
 // [PAL] cc->ModReduce on every ciphertext of a serialized vector (rescale-before-transport): the blob
@@ -1598,6 +1630,7 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         }
         h->r_out.release();
         if (h->ev_r_out) cudaEventDestroy(h->ev_r_out);
+        if (h->ev_scratch) cudaEventDestroy(h->ev_scratch);
         for (DeviceBuffer *b : {&h->s_x, &h->s_m, &h->s_ve, &h->s_coeff, &h->s_dense, &h->s_image, &h->s_image2, &h->s_image3,
                                 &h->s_out, &h->s_vals, &h->s_zs, &h->s_rows, &h->s_pt, &h->s_resc, &h->s_dense2})
             b->release();
@@ -2145,10 +2178,8 @@ int shelfi_selftest_parallel_copy(uint64_t bytes, uint32_t threads, uint32_t rou
 
 // Stream-ordered barrier between the ranks of one box; d_flags[r] = rank r's flag array (9 zero-initialised u64 in a peer
 // buffer).  Every rank calls it with the same, growing epoch.
-int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,
-                               void *stream) {
-    if (!h) return SHELFI_ERR_ARG;
-    std::lock_guard<std::mutex> lock(h->mu);
+static int peer_barrier(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,
+                        double *poison, uint64_t poison_stride, void *stream) {
     int rcode = ensure_cuda(h);
     if (rcode) return rcode;
     if (!d_flags || n_ranks == 0 || n_ranks > 8 || my_rank >= n_ranks || epoch == 0)
@@ -2160,9 +2191,24 @@ int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_
     }
     uint64_t timeout_ns = 20ull * 1000000000ull;
     if (const char *e = std::getenv("SHELFI_PEER_TIMEOUT_MS")) timeout_ns = (uint64_t)std::max(1, std::atoi(e)) * 1000000ull;
-    launch_peer_barrier(pf, n_ranks, my_rank, epoch, timeout_ns, static_cast<cudaStream_t>(stream));
+    launch_peer_barrier(pf, n_ranks, my_rank, epoch, timeout_ns, poison, poison_stride, static_cast<cudaStream_t>(stream));
     CU(cudaGetLastError());
     return 0;
+}
+int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,
+                               void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return peer_barrier(h, d_flags, n_ranks, my_rank, epoch, nullptr, 0, stream);
+}
+// the same, guarding a gathered result: if the wait for rank r times out, d_values[r * block] (the first value of the
+// slice rank r owed this GPU) is set to NaN
+int shelfi_peer_barrier_guard_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank,
+                                     uint64_t epoch, double *d_values, uint64_t block, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!d_values || block == 0) return fail(h, SHELFI_ERR_ARG, "null result buffer or zero block");
+    return peer_barrier(h, d_flags, n_ranks, my_rank, epoch, d_values, block, stream);
 }
 
 // Buffers other processes of the box can map (CUDA IPC): the destinations of shelfi_decrypt_gather_device.
@@ -2245,6 +2291,7 @@ int shelfi_decrypt_words_level_device(shelfi_ckks *h, const uint64_t *d_ct, uint
     if (limbs < 1 || limbs > h->ctx.limbs) return fail(h, SHELFI_ERR_ARG, "tower count outside the chain");
     const LevelView lv = level_view(h, limbs);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if ((rcode = scratch_begin(h, s))) return rcode;
     CU(h->s_coeff.reserve(n_ct * limbs * h->ctx.ring_dim * sizeof(uint64_t)));
     launch_decrypt_intt(lv.rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
     DecodeConst dc{};
@@ -2252,7 +2299,7 @@ int shelfi_decrypt_words_level_device(shelfi_ckks *h, const uint64_t *d_ct, uint
     launch_crt(lv.rc, dc, lv.crtn, h->s_coeff.as<u64>(), (u32)n_ct, nullptr, reinterpret_cast<u64 *>(d_words), nullptr,
                nullptr, s);
     CU(cudaGetLastError());
-    return 0;
+    return scratch_end(h, s);
 }
 
 // ---- per-slot plaintext weights: out = sum_l ct_l (*) Encode(w_l)  ([PAL] EvalMult(ct, plaintext) + EvalAdd; the
@@ -2270,6 +2317,7 @@ int shelfi_weighted_sum_vector_device(shelfi_ckks *h, const uint64_t *const *d_c
     const uint64_t n_ct = (n + h->batch - 1) / h->batch, N = h->ctx.ring_dim;
     if (n_ct > (0x7fffffffull / (2 * kMaxLimbs)) >> h->rc.log_blocks)
         return fail(h, SHELFI_ERR_ARG, "too many ciphertexts for one call");
+    if ((rcode = scratch_begin(h, s))) return rcode;
     CU(h->s_m.reserve(n_ct * N * sizeof(int64_t)));
     CU(h->s_pt.reserve(n_ct * h->ctx.limbs * N * sizeof(uint64_t)));
     // Consecutive learners that share one weight vector (the TenSEAL script's constant vector) are summed first:
@@ -2304,7 +2352,7 @@ int shelfi_weighted_sum_vector_device(shelfi_ckks *h, const uint64_t *const *d_c
         i0 = i1;
     }
     CU(cudaGetLastError());
-    return 0;
+    return scratch_end(h, s);
 }
 
 // ---- selective encryption (benchmark_selection.py:152-193, benchmark_selection_rate.py:133-141): only the chosen
@@ -2390,6 +2438,7 @@ int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, v
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const u64 *src = reinterpret_cast<const u64 *>(d_rows);
     if (h->rc.log_blocks > 0) {   // a tile's loader reads its whole row: transform from a copy
+        if ((rcode = scratch_begin(h, s))) return rcode;
         size_t bytes = (size_t)rows * h->ctx.ring_dim * sizeof(uint64_t);
         CU(h->s_rows.reserve(bytes));
         CU(cudaMemcpyAsync(h->s_rows.p, d_rows, bytes, cudaMemcpyDeviceToDevice, s));
@@ -2397,6 +2446,7 @@ int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, v
     }
     timed(h, kKNttForward, s, [&] { launch_ntt_forward(h->rc, src, reinterpret_cast<u64 *>(d_rows), rows, s); });
     CU(cudaGetLastError());
+    if (h->rc.log_blocks > 0) return scratch_end(h, s);
     return 0;
 }
 int shelfi_ntt_inverse_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream) {
@@ -2429,6 +2479,7 @@ int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t
     if (rcode) return rcode;
     if (h->ctx.limbs > 2) return fail(h, SHELFI_ERR_UNSUPPORTED, "128-bit tap covers 1 and 2 limbs; use shelfi_decrypt_words_device");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if ((rcode = scratch_begin(h, s))) return rcode;
     CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * h->ctx.ring_dim * sizeof(uint64_t)));
     launch_decrypt_intt(h->rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
     DecodeConst dc{};
@@ -2439,7 +2490,7 @@ int shelfi_decrypt_integer_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t
         launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, nullptr, nullptr, reinterpret_cast<i64 *>(d_hi),
                    reinterpret_cast<u64 *>(d_lo), s);
     CU(cudaGetLastError());
-    return 0;
+    return scratch_end(h, s);
 }
 
 int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, uint64_t *d_words, void *stream) {
@@ -2449,6 +2500,7 @@ int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n
     if (rcode) return rcode;
     if (!d_ct || !d_words || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if ((rcode = scratch_begin(h, s))) return rcode;
     CU(h->s_coeff.reserve(n_ct * h->ctx.limbs * h->ctx.ring_dim * sizeof(uint64_t)));
     launch_decrypt_intt(h->rc, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s);
     DecodeConst dc{};
@@ -2456,7 +2508,7 @@ int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n
     launch_crt(h->rc, dc, h->crtn, h->s_coeff.as<u64>(), (u32)n_ct, nullptr, reinterpret_cast<u64 *>(d_words), nullptr,
                nullptr, s);
     CU(cudaGetLastError());
-    return 0;
+    return scratch_end(h, s);
 }
 
 }  // extern "C"

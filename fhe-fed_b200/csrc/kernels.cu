@@ -1064,7 +1064,7 @@ void launch_write_segments(const SegDesc *desc, const unsigned char *bytes, unsi
 // decode kernel's peer stores (earlier in the stream) before the flag; release/acquire at system scope pair the flag
 // with the reader's later loads.  Epochs only grow, so a flag never has to be reset.
 __global__ void __launch_bounds__(32) peer_barrier_kernel(const __grid_constant__ PeerFlags pf, u32 n_ranks, u32 me,
-                                                          u64 epoch, u64 timeout_ns) {
+                                                          u64 epoch, u64 timeout_ns, double *poison, u64 poison_stride) {
     const u32 r = threadIdx.x;
     if (r >= n_ranks) return;
     __threadfence_system();
@@ -1077,16 +1077,19 @@ __global__ void __launch_bounds__(32) peer_barrier_kernel(const __grid_constant_
         asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(mine) : "memory");
         if (seen >= epoch) break;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (t1 - t0 > timeout_ns) {   // a peer never arrived: record it and let the stream go on
+        if (t1 - t0 > timeout_ns) {   // a peer never arrived: record it and let the stream go on ...
             pf.flags[me][8] = epoch;
+            // ... but not with a half-gathered model that looks whole: the slice rank r owed us starts with a NaN
+            if (poison) poison[(u64)r * poison_stride] = __longlong_as_double(0x7ff8000000000000ll);
             break;
         }
         __nanosleep(100);
     }
     __threadfence_system();
 }
-void launch_peer_barrier(const PeerFlags &pf, u32 n_ranks, u32 me, u64 epoch, u64 timeout_ns, cudaStream_t s) {
-    peer_barrier_kernel<<<1, 32, 0, s>>>(pf, n_ranks, me, epoch, timeout_ns);
+void launch_peer_barrier(const PeerFlags &pf, u32 n_ranks, u32 me, u64 epoch, u64 timeout_ns, double *poison,
+                         u64 poison_stride, cudaStream_t s) {
+    peer_barrier_kernel<<<1, 32, 0, s>>>(pf, n_ranks, me, epoch, timeout_ns, poison, poison_stride);
 }
 
 static dim3 run_grid(const BlobRuns &br, u64 n_ct) { return dim3((unsigned)(n_ct * br.runs), br.n / 2048); }

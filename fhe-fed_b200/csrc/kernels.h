@@ -79,6 +79,9 @@ void launch_write_segments(const SegDesc *desc, const unsigned char *bytes, unsi
 // array (peer-mapped) and waits until its own array shows `epoch` in every slot.  flags[r] -> rank r's array of >= 9
 // u64 (slot 8 = status: set to `epoch` if the wait gave up after `timeout_ns`).
 struct PeerFlags { unsigned long long *flags[8]; };
-void launch_peer_barrier(const PeerFlags &pf, u32 n_ranks, u32 me, u64 epoch, u64 timeout_ns, cudaStream_t s);
+// poison (optional): on a timeout waiting for rank r, poison[r * poison_stride] is set to NaN (the first value of the
+// slice that rank owed this GPU), so a consumer that never looks at the status word still cannot mistake the result
+void launch_peer_barrier(const PeerFlags &pf, u32 n_ranks, u32 me, u64 epoch, u64 timeout_ns, double *poison,
+                         u64 poison_stride, cudaStream_t s);
 
 }  // namespace shelfi

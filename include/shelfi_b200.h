@@ -254,6 +254,11 @@ int shelfi_peer_buffer_destroy(shelfi_ckks *h, void *d_ptr);
  * SHELFI_PEER_TIMEOUT_MS (default 20000) writes the epoch to slot 8 of its own array and lets the stream continue. */
 int shelfi_peer_barrier_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank, uint64_t epoch,
                                void *stream);
+/* The barrier AFTER a decrypt-gather, guarding its result: if the wait for rank r times out, d_values[r * block] — the
+ * first value of the slice rank r owed this GPU, in this GPU's copy of the model — is set to NaN besides the status
+ * word, so that a consumer which never reads the status cannot take a half-gathered model for a whole one. */
+int shelfi_peer_barrier_guard_device(shelfi_ckks *h, uint64_t *const *d_flags, uint32_t n_ranks, uint32_t my_rank,
+                                     uint64_t epoch, double *d_values, uint64_t block, void *stream);
 /* ModReduce on a dense batch: d_ct[n_ct][2][limbs_in][N] -> d_out[n_ct][2][limbs_in - 1][N] (limbs_in 0 = the context's
  * chain); the decrypt calls below take the towers the ciphertexts kept.  After one rescale of a depth-2 average the
  * scaling factor to pass is scalingFactor^2 / q_last. */

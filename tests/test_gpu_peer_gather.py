@@ -119,6 +119,32 @@ def test_barrier_gives_up_after_the_timeout(shelfi, handles, monkeypatch):
     assert int(flags[0][8].item()) == 5 and int(flags[1][0].item()) == 5
 
 
+def test_guarded_barrier_poisons_the_missing_slice(shelfi, handles, monkeypatch):
+    """The barrier after a decrypt-gather: a peer that never arrives leaves a NaN at the start of ITS slice in this
+    GPU's copy (and the status word), nothing else is touched; a barrier that completes leaves the values alone."""
+    h, _ = handles["pybind"]
+    lib = shelfi.lib()
+    monkeypatch.setenv("SHELFI_PEER_TIMEOUT_MS", "50")
+    flags = [torch.zeros(16, dtype=torch.int64, device="cuda") for _ in range(2)]
+    arr = (C.c_void_p * 2)(*[f.data_ptr() for f in flags])
+    block = 1000
+    values = torch.ones(2 * block, dtype=torch.float64, device="cuda")
+    check(h, lib.shelfi_peer_barrier_guard_device(h.handle, arr, 2, 0, 7, C.c_void_p(values.data_ptr()), block, stream()))
+    torch.cuda.synchronize()
+    got = values.cpu().numpy()
+    assert int(flags[0][8].item()) == 7
+    assert np.isnan(got[block]) and not np.isnan(got[0])          # rank 1 owed the second slice
+    assert np.all(np.delete(got, block) == 1.0)
+    # a one-rank barrier always completes: no poison
+    solo = torch.zeros(16, dtype=torch.int64, device="cuda")
+    arr1 = (C.c_void_p * 1)(solo.data_ptr())
+    v1 = torch.ones(block, dtype=torch.float64, device="cuda")
+    check(h, lib.shelfi_peer_barrier_guard_device(h.handle, arr1, 1, 0, 1, C.c_void_p(v1.data_ptr()), block, stream()))
+    torch.cuda.synchronize()
+    assert bool((v1 == 1.0).all()) and int(solo[8].item()) == 0
+    assert lib.shelfi_peer_barrier_guard_device(h.handle, arr1, 1, 0, 2, None, block, stream()) != 0
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on the box")
 def test_two_ranks_equal_nccl_all_gather():
     env = dict(os.environ, MASTER_ADDR="127.0.0.1")
