@@ -60,6 +60,8 @@ def lib() -> C.CDLL:
         "shelfi_set_sampler_seed": (C.c_int, [vp, u64]),
         "shelfi_clear_sampler_seed": (C.c_int, [vp]),
         "shelfi_chacha20_block_device": (C.c_int, [vp, vp, u32, vp, vp]),
+        "shelfi_set_option": (C.c_int, [vp, C.c_int, i64]),
+        "shelfi_get_option": (i64, [vp, C.c_int]),
         "shelfi_ring_dim": (u32, [vp]),
         "shelfi_num_limbs": (u32, [vp]),
         "shelfi_slots": (u32, [vp]),
@@ -707,6 +709,16 @@ class CKKS(Scheme):
             lib().shelfi_clear_sampler_seed(self._h)
         else:
             lib().shelfi_set_sampler_seed(self._h, int(seed) & (2**64 - 1))
+
+    OPT_EVALMULT_ROUND, OPT_DECODE_NOISE, OPT_WIRE_VARIANT = 1, 2, 3
+
+    def set_option(self, option: int, value: int) -> None:
+        """The PALISADE semantics no fixture pins (include/shelfi_b200.h: SHELFI_OPT_*): EvalMult rounding, decode
+        noise, wire variant of generated contexts."""
+        self._check(lib().shelfi_set_option(self._h, int(option), int(value)))
+
+    def get_option(self, option: int) -> int:
+        return int(lib().shelfi_get_option(self._h, int(option)))
 
     def synchronize(self) -> None:
         """Wait for everything this handle has queued on the GPU (resident calls return before their kernels end)."""

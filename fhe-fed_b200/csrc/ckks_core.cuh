@@ -816,7 +816,7 @@ HD void chacha20_block(const SamplerKey &key, u32 counter, u32 n0, u32 n1, u32 n
 }
 // Test keys: shelfi_set_sampler_seed(seed) makes the engine deterministic; the 64-bit seed is laid into a key per
 // domain so that the CPU checker under oracle/ draws the same stream.  Never used for real data.
-enum { kKeyDomainEncrypt = 0, kKeyDomainKeySecret = 1, kKeyDomainKeyPublic = 2 };
+enum { kKeyDomainEncrypt = 0, kKeyDomainKeySecret = 1, kKeyDomainKeyPublic = 2, kKeyDomainDecode = 3 };
 HD SamplerKey seed_key(u64 seed, u32 domain) {
     SamplerKey k;
     k.k[0] = (u32)seed; k.k[1] = (u32)(seed >> 32);
@@ -1271,6 +1271,13 @@ HD i64 encode_coeff(const cplx *z, const EncodeConst &ec, u32 j) {
     u32 half = j >= nh ? 1u : 0u, idx = j - half * nh;
     if (idx & (ec.gap - 1)) return 0;
     return zi[2 * zsw(idx / ec.gap) + half];
+}
+// two standard normals from four random words (Box-Muller on two 53-bit uniforms): the decode noise of [PAL] Decode
+HD void normal_pair(u32 w0, u32 w1, u32 w2, u32 w3, double &z0, double &z1) {
+    const double u1 = (double)(((((u64)w1 << 32) | w0) >> 11) + 1) * 1.1102230246251565e-16;   // (0, 1]
+    const double u2 = (double)((((u64)w3 << 32) | w2) >> 11) * 1.1102230246251565e-16;          // [0, 1)
+    const double r = sqrt(-2.0 * log(u1)), a = 6.283185307179586476925286766559 * u2;
+    z0 = r * cos(a); z1 = r * sin(a);
 }
 // [PAL] Encrypt's draws for ciphertext `ct` (ckks.cpp:81,95), as counter-mode blocks:
 //   ternary block b, nonce (ct_lo, ct_hi, kStreamTernary): v[32 b + 2 i] from the low half of word i, v[32 b + 2 i + 1]

@@ -278,6 +278,11 @@ struct shelfi_ckks {
     cudaEvent_t ev_scratch = nullptr;
     cudaStream_t scratch_stream = nullptr;
     bool scratch_used = false;
+    // the semantics the reference's fixtures do not pin, switchable (shelfi_set_option; same ids in the oracle)
+    int opt_evalmult_round = 0;   // 0: (int64)(c * Delta + 0.5);  1: llround(c * Delta)
+    int opt_decode_noise = 0;     // 1: PALISADE >= 1.10.6 Decode noise flooding
+    int opt_wire_variant = 0;     // generated contexts: 0 = default (9 RLWE words), 8 or 9
+    SamplerKey noise_key{};       // key of the decode noise of the current reference-facing call
 };
 
 namespace {
@@ -521,6 +526,7 @@ size_t image_bytes(uint64_t blob_size) { return ((size_t)blob_size + 7) / 8 * 8 
 
 int64_t weight_constant(const shelfi_ckks *h, float w) {
     double sc = (double)w;  // ckks.cpp:287 narrows to float32; PALISADE's EvalMult(ct, double) widens it back
+    if (h->opt_evalmult_round == 1) return (int64_t)std::llround(sc * (double)h->ctx.modulus[h->ctx.limbs - 1]);
     return (int64_t)(sc * (double)h->ctx.modulus[h->ctx.limbs - 1] + 0.5);
 }
 
@@ -686,9 +692,10 @@ LevelView level_view(const shelfi_ckks *h, uint32_t limbs) {
 
 // limbs = towers per polynomial of d_ct (0 = the context's chain, i.e. level 0)
 // peers[0..n_peer): further destinations of every decoded value (decrypt-gather), already offset to this rank's slice
+// ct_index0: index of d_ct[0] within the vector the caller decrypts (names the decode-noise stream of each ciphertext)
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
                   cudaStream_t s, const uint32_t *d_sel = nullptr, uint32_t limbs = 0, double *const *peers = nullptr,
-                  uint32_t n_peer = 0) {
+                  uint32_t n_peer = 0, uint64_t ct_index0 = 0) {
     const uint64_t N = h->ctx.ring_dim;
     const LevelView lv = level_view(h, limbs);
     int src = scratch_begin(h, s);
@@ -702,7 +709,7 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
     dc.pow_p = std::pow(2, -p);
     for (uint32_t i = 0; i < n_peer; i++) dc.peer[i] = peers[i];
     dc.n_peer = n_peer;
-    if (!general_decode(h, lv.rc.limbs)) {
+    if (!general_decode(h, lv.rc.limbs) && !h->opt_decode_noise) {
         timed(h, kKDecode, s, [&] { launch_decode(lv.rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s, d_sel); });
     } else {
         CU(h->s_vals.reserve(n_ct * N * sizeof(double)));
@@ -710,6 +717,8 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
         timed(h, kKDecode, s, [&] {
             launch_crt(lv.rc, dc, lv.crtn, h->s_coeff.as<u64>(), (u32)n_ct, h->s_vals.as<double>(), nullptr, nullptr,
                        nullptr, s);
+            if (h->opt_decode_noise)   // [PAL] Decode adds its noise at scale 2^p, before FFTSpecial
+                launch_decode_noise(lv.rc, h->ec, h->noise_key, ct_index0, h->s_vals.as<double>(), (u32)n_ct, s);
             launch_decode_fft(lv.rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s,
                               d_sel);
         });
@@ -746,6 +755,7 @@ int check_stage(shelfi_ckks *h, bool need_pk, bool need_sk) {
     if (!h->have_cc) return fail(h, SHELFI_ERR_NOT_LOADED, "crypto context not loaded (call loadCryptoParams)");
     if (need_pk && !h->have_pk) return fail(h, SHELFI_ERR_NOT_LOADED, "public key not loaded");
     if (need_sk && !h->have_sk) return fail(h, SHELFI_ERR_NOT_LOADED, "private key not loaded");
+    if (need_sk && h->opt_decode_noise && (rcode = call_key(h, kKeyDomainDecode, &h->noise_key))) return rcode;   // one key per decrypt call
     if (h->batch == 0 || h->batch > h->ctx.batch_size)
         return fail(h, SHELFI_ERR_PARAMS, "batchSize exceeds the slots of the loaded context");
     return 0;
@@ -1218,7 +1228,7 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             CUB(cudaGetLastError());
             const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
             if ((rcode = decrypt_dense(h, dense, c1 - c0, m.meta[0].scaling_factor, h->s_out.as<double>() + first, last - first,
-                                       st, nullptr, m.ct_limbs))) {
+                                       st, nullptr, m.ct_limbs, nullptr, 0, c0))) {
                 return bail(rcode);
             }
             CUB(cudaEventRecord(h->ev_stage_out, st));
@@ -1246,7 +1256,8 @@ int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *bl
             uint64_t first = j0 * batch, last = std::min(ls.n, j1 * batch);
             const uint64_t layer_words = 2ull * maps[s].ct_limbs * N;   // a rescaled layer is packed tighter
             if ((rcode = decrypt_dense(h, dense + j0 * layer_words, j1 - j0, maps[s].meta[j0].scaling_factor,
-                                       h->s_out.as<double>() + ls.x0 + first, last - first, st, nullptr, maps[s].ct_limbs)))
+                                       h->s_out.as<double>() + ls.x0 + first, last - first, st, nullptr, maps[s].ct_limbs,
+                                       nullptr, 0, ls.ct0 + j0)))
                 return bail(rcode);
             j0 = j1;
         }
@@ -1537,7 +1548,8 @@ int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
         for (uint32_t g = 0; g < groups; g++) {
             const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
             const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
-            if ((rcode = decrypt_dense(h, c->d + c0 * words, c1 - c0, sf_of(0), d_out + first, last - first, st, nullptr, c->limbs)))
+            if ((rcode = decrypt_dense(h, c->d + c0 * words, c1 - c0, sf_of(0), d_out + first, last - first, st, nullptr, c->limbs,
+                                       nullptr, 0, c0)))
                 return bail(rcode);
             CUB(cudaEventRecord(h->ev_stage_out, st));
             CUB(cudaStreamWaitEvent(ds, h->ev_stage_out, 0));
@@ -1551,7 +1563,8 @@ int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
         uint64_t j1 = one_scale ? n_ct : j0 + 1;
         while (j1 < n_ct && sf_of(j1) == sf_of(j0)) j1++;
         const uint64_t first = j0 * batch, last = std::min(n, j1 * batch);
-        if ((rcode = decrypt_dense(h, c->d + j0 * words, j1 - j0, sf_of(j0), d_out + first, last - first, st, nullptr, c->limbs)))
+        if ((rcode = decrypt_dense(h, c->d + j0 * words, j1 - j0, sf_of(j0), d_out + first, last - first, st, nullptr, c->limbs,
+                                   nullptr, 0, j0)))
             return bail(rcode);
         j0 = j1;
     }
@@ -1609,6 +1622,8 @@ int shelfi_ckks_create(const char *scheme, uint32_t batch_size, uint32_t scale_f
     h->scale_bits = scale_factor_bits;
     h->cryptodir = cryptodir ? cryptodir : "";
     h->device = device;
+    if (const char *e = std::getenv("SHELFI_EVALMULT_ROUND")) h->opt_evalmult_round = std::atoi(e) == 1;
+    if (const char *e = std::getenv("SHELFI_DECODE_NOISE")) h->opt_decode_noise = std::atoi(e) == 1;
     *out = h;
     return 0;
 }
@@ -1747,7 +1762,7 @@ int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth,
     // EXACTRESCALE, HYBRID, dnum
     const uint32_t dnum = nt::num_large_digits(mult_depth);
     const char *variant = std::getenv("SHELFI_WIRE_VARIANT");
-    if (variant && std::atoi(variant) == 8) {
+    if (h->opt_wire_variant == 8 || (!h->opt_wire_variant && variant && std::atoi(variant) == 8)) {
         const uint32_t v[8] = {0, 1, 2, 1, 0, 2, 1, dnum};
         std::memcpy(p.rlwe_ints, v, sizeof v); p.rlwe_int_count = 8;
     } else {
@@ -1829,6 +1844,35 @@ int shelfi_clear_sampler_seed(shelfi_ckks *h) {
     std::lock_guard<std::mutex> lock(h->mu);
     h->seeded = false;
     return 0;
+}
+int shelfi_set_option(shelfi_ckks *h, int option, int64_t value) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    switch (option) {
+        case SHELFI_OPT_EVALMULT_ROUND:
+            if (value != 0 && value != 1) return fail(h, SHELFI_ERR_ARG, "evalmult_round: 0 or 1");
+            h->opt_evalmult_round = (int)value;
+            return 0;
+        case SHELFI_OPT_DECODE_NOISE:
+            if (value != 0 && value != 1) return fail(h, SHELFI_ERR_ARG, "decode_noise: 0 or 1");
+            h->opt_decode_noise = (int)value;
+            return 0;
+        case SHELFI_OPT_WIRE_VARIANT:
+            if (value != 0 && value != 8 && value != 9) return fail(h, SHELFI_ERR_ARG, "wire_variant: 0, 8 or 9");
+            h->opt_wire_variant = (int)value;
+            return 0;
+        default:
+            return fail(h, SHELFI_ERR_ARG, "unknown option");
+    }
+}
+int64_t shelfi_get_option(const shelfi_ckks *h, int option) {
+    if (!h) return -1;
+    switch (option) {
+        case SHELFI_OPT_EVALMULT_ROUND: return h->opt_evalmult_round;
+        case SHELFI_OPT_DECODE_NOISE: return h->opt_decode_noise;
+        case SHELFI_OPT_WIRE_VARIANT: return h->opt_wire_variant ? h->opt_wire_variant : (h->have_cc ? h->ctx.rlwe_int_count : 9);
+        default: return -1;
+    }
 }
 // known-answer tap of the device sampler: one ChaCha20 block (key 8 words, counter, nonce 3 words -> 16 words)
 int shelfi_chacha20_block_device(shelfi_ckks *h, const uint32_t key[8], uint32_t counter, const uint32_t nonce[3],

@@ -690,6 +690,70 @@ __global__ void __launch_bounds__(kCrtThreads) crt_kernel(const __grid_constant_
     }
     if (tap_hi) { tap_hi[ct * (u64)n_ring + j] = (i64)t[1]; tap_lo[ct * (u64)n_ring + j] = t[0]; }
 }
+// [PAL >= 1.10.6] CKKSPackedEncoding::Decode's noise flooding (opt-in: shelfi_set_option(DECODE_NOISE)), between
+// crt_kernel and decode_fft_kernel: one CTA per ciphertext estimates the standard deviation of the decryption error
+// from the part of the polynomial an exact real message cannot have (m(X) - m(1/X) = 2 Im z), floors it at sqrt(N)/8,
+// and adds N(0, 2 sd^2) to the real and imaginary part of every slot.  vals = doubles of the CRT integers at scale 2^p.
+constexpr int kNoiseThreads = 256;
+__device__ __forceinline__ double block_sum(double v, double *red) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();                       // `red` may still be read from the previous reduction
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int w = 0; w < kNoiseThreads / 32; w++) t += red[w];
+    return t;
+}
+__global__ void __launch_bounds__(kNoiseThreads) decode_noise_kernel(const __grid_constant__ EncodeConst ec,
+                                                                     const __grid_constant__ SamplerKey key, u64 ct_index0,
+                                                                     u32 n_ring, double *vals) {
+    __shared__ double red[kNoiseThreads / 32];
+    const u64 ct = blockIdx.x;
+    double *v = vals + ct * (u64)n_ring;
+    const u32 n = ec.slots, gap = ec.gap, nh = n_ring >> 1;
+    auto re = [&](u32 i) { return v[gap * i]; };
+    auto im = [&](u32 i) { return v[gap * i + nh]; };
+    double sd;
+    if (n == 1) {
+        sd = fabs(im(0));
+    } else {
+        // cv[i] = vec[i] - Conjugate(vec)[i]:  cv[0] = (0, 2 Im vec[0]),  cv[i] = (Re vec[i] + Im vec[n-i], Im vec[i] + Re vec[n-i])
+        const double cv0 = 2.0 * im(0), half_re = re(n / 2) + im(n - n / 2);
+        double part = 0.0;
+        for (u32 i = 1 + threadIdx.x; i < n / 2; i += kNoiseThreads) part += (re(i) + im(n - i)) + (im(i) + re(n - i));
+        const double mean = (2.0 * block_sum(part, red) + cv0 + 2.0 * half_re) / ((double)(2 * n) - 1.0);
+        part = 0.0;
+        for (u32 i = 1 + threadIdx.x; i < n / 2; i += kNoiseThreads) {
+            const double a = re(i) + im(n - i) - mean, b = im(i) + re(n - i) - mean;
+            part += a * a + b * b;
+        }
+        const double var = (2.0 * block_sum(part, red) + (cv0 - mean) * (cv0 - mean) + 2.0 * (half_re - mean) * (half_re - mean)) /
+                           ((double)(2 * n) - 2.0);
+        sd = 0.5 * sqrt(var);
+    }
+    const double floor_sd = 0.125 * sqrt((double)n_ring);
+    sd = 1.4142135623730951 * (sd < floor_sd ? floor_sd : sd);        // sqrt(M + 1), M = 1
+    __syncthreads();                                                  // every thread has read what it needs of v
+    const u64 cti = ct_index0 + ct;
+    for (u32 b = threadIdx.x; b < (n + 3) / 4; b += kNoiseThreads) {  // block b: slots 4 b .. 4 b + 3
+        u32 o[16];
+        chacha20_block(key, b, (u32)cti, (u32)(cti >> 32), kStreamDecodeNoise, o);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const u32 i = 4 * b + k;
+            if (i >= n) break;
+            double z0, z1;
+            normal_pair(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3], z0, z1);
+            v[gap * i] += sd * z0;
+            v[gap * i + nh] += sd * z1;
+        }
+    }
+}
+void launch_decode_noise(const RingConst &rc, const EncodeConst &ec, const SamplerKey &key, u64 ct_index0, double *vals,
+                         u32 n_ct, cudaStream_t s) {
+    if (n_ct) decode_noise_kernel<<<n_ct, kNoiseThreads, 0, s>>>(ec, key, ct_index0, rc.n, vals);
+}
+
 template <int DF>
 __global__ void __launch_bounds__(kFftThreads) decode_fft_kernel(const __grid_constant__ EncodeConst ec,
                                                                  const __grid_constant__ DecodeConst dc, u32 n_ring,

@@ -44,6 +44,9 @@ void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst
 // (tap8: 8 two's-complement words per coefficient; tap_hi/tap_lo: its low 128 bits)
 void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,
                 double *vals, u64 *tap8, i64 *tap_hi, u64 *tap_lo, cudaStream_t s);
+// [PAL >= 1.10.6] Decode's noise flooding on vals (between launch_crt and launch_decode_fft), one key per call
+void launch_decode_noise(const RingConst &rc, const EncodeConst &ec, const SamplerKey &key, u64 ct_index0, double *vals,
+                         u32 n_ct, cudaStream_t s);
 // ... then FFTSpecial per 4096-slot tile (+ tail pass for more slots; zs = scratch of n_ct * slots complex)
 void launch_decode_fft(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const double *vals, cplx *zs,
                        u32 n_ct, double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);

@@ -81,6 +81,21 @@ int shelfi_gen_crypto_context_and_keygen_ex(shelfi_ckks *h, uint32_t mult_depth,
  * reproducible (tests, parity against the CPU oracle); never use it for real data. */
 int shelfi_set_sampler_seed(shelfi_ckks *h, uint64_t seed);
 int shelfi_clear_sampler_seed(shelfi_ckks *h);
+/* Semantics of PALISADE that no fixture of the reference pins (DESIGN.md 5 lists them), switchable so
+ * that a deployment checked against a real PALISADE can be corrected without a rebuild.  The CPU oracle has the same
+ * switches under the same ids.
+ *   SHELFI_OPT_EVALMULT_ROUND  EvalMult(ct, double)'s constant (src/ckks.cpp:288): 0 = (int64)(c * Delta + 0.5), the
+ *                              default (PALISADE v1.11 source); 1 = llround(c * Delta) (differs for negative weights)
+ *   SHELFI_OPT_DECODE_NOISE    cc->Decrypt (src/ckks.cpp:189): 1 = add PALISADE >= 1.10.6's Gaussian decode noise (the
+ *                              Li-Micciancio key-recovery countermeasure: standard deviation estimated from the
+ *                              conjugate-asymmetric part of the decrypted polynomial, floored at sqrt(N)/8, times
+ *                              sqrt(2)) before FFTSpecial; 0 = off (default: deterministic, which the bit-exact parity
+ *                              tier needs).  Also SHELFI_DECODE_NOISE=1 in the environment.
+ *   SHELFI_OPT_WIRE_VARIANT    RLWE parameter block of GENERATED contexts: 9 words (default, newer PALISADE) or 8;
+ *                              loaded contexts are re-emitted in the variant they came in. */
+enum { SHELFI_OPT_EVALMULT_ROUND = 1, SHELFI_OPT_DECODE_NOISE = 2, SHELFI_OPT_WIRE_VARIANT = 3 };
+int shelfi_set_option(shelfi_ckks *h, int option, int64_t value);
+int64_t shelfi_get_option(const shelfi_ckks *h, int option);
 /* known-answer tap: one ChaCha20 block computed by the device sampler code (key 8 words, block counter, nonce 3
  * words -> 16 words); tests hold the RFC 8439 vectors */
 int shelfi_chacha20_block_device(shelfi_ckks *h, const uint32_t key[8], uint32_t counter, const uint32_t nonce[3],

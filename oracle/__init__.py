@@ -102,6 +102,8 @@ def lib():
         "orc_fft_special_inv": (None, [C.c_void_p, C.c_void_p, C.c_uint32]),
         "orc_chacha20_block": (None, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
         "orc_seed_key": (None, [C.c_uint64, C.c_uint32, C.c_void_p]),
+        "orc_set_option": (C.c_int, [C.c_void_p, C.c_int, C.c_int64]),
+        "orc_decode_noise": (C.c_double, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]),
         "orc_gauss_from_words": (C.c_int64, [C.c_void_p, C.c_uint32, C.c_uint32]),
         "orc_ternary_from_half": (C.c_int64, [C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32]),
         "orc_sample_encrypt_noise": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -246,6 +248,19 @@ class Oracle:
         v = np.ascontiguousarray(z, dtype=np.complex128).copy()
         lib().orc_fft_special_inv(self._h, v.ctypes.data, v.size)
         return v
+
+    OPT_EVALMULT_ROUND, OPT_DECODE_NOISE, OPT_NOISE_SEED = 1, 2, 4
+
+    def set_option(self, option: int, value: int) -> None:
+        if lib().orc_set_option(self._h, option, value):
+            raise ValueError(f"bad option {option} = {value}")
+
+    def decode_noise(self, z, key, ct_index: int):
+        """PALISADE-style decode noise on a complex vector at scale 2^p: (noisy copy, standard deviation added)."""
+        v = np.ascontiguousarray(z, dtype=np.complex128).copy()
+        k = np.ascontiguousarray(key, dtype=np.uint32)
+        sd = lib().orc_decode_noise(self._h, v.ctypes.data, v.size, k.ctypes.data, ct_index)
+        return v, sd
 
     def gauss_from_words(self, h: int, l: int) -> int:
         return lib().orc_gauss_from_words(self._h, h, l)

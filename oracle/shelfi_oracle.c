@@ -193,6 +193,10 @@ struct orc_ctx {
     uint32_t *rot_group; /* 5^j mod M, j < N/2 */
     double *ksi;         /* (cos,sin)(2 pi k / M), k <= M */
     uint64_t gauss_cdf[32];
+    /* the three semantics the reference's fixtures do not pin, switchable here and in the engine alike */
+    int opt_evalmult_round; /* 0: (int64)(c*Delta + 0.5)  [PAL v1.11 EvalMult(ct, double)];  1: llround(c*Delta) */
+    int opt_decode_noise;   /* 0: off;  1: [PAL >= 1.10.6] Decode adds Gaussian noise before FFTSpecial */
+    uint64_t noise_seed;    /* test key of the decode noise (the engine draws a fresh key per call unless seeded) */
 };
 
 static uint32_t bitrev(uint32_t x, int bits) {
@@ -426,7 +430,7 @@ void orc_chacha20_block(const uint32_t key[8], uint32_t counter, const uint32_t 
     for (int i = 0; i < 16; i++) out[i] = w[i] + st[i];
 }
 /* test keys: the 64-bit seed of the tests laid into a 256-bit key per domain ("SHELFI-B200 seed") */
-enum { KEY_ENCRYPT = 0, KEY_KEYGEN_SECRET = 1, KEY_KEYGEN_PUBLIC = 2 };
+enum { KEY_ENCRYPT = 0, KEY_KEYGEN_SECRET = 1, KEY_KEYGEN_PUBLIC = 2, KEY_DECODE = 3 };
 void orc_seed_key(uint64_t seed, uint32_t domain, uint32_t key[8]) {
     key[0] = (uint32_t)seed; key[1] = (uint32_t)(seed >> 32);
     key[2] = 0x4c454853u; key[3] = 0x422d4946u; key[4] = 0x20303032u; key[5] = 0x64656573u;
@@ -642,8 +646,58 @@ static void crt_centered(const crt_plan *p, const uint64_t *a, int *neg, big_t *
 /* [PAL] LPAlgorithmCKKS::Decrypt + DCRTPoly::CRTInterpolate + CKKSPackedEncoding::Decode (noise
  * flooding of PALISADE >= 1.10.6 left out: it is random, ~2^-40 relative, far below the 1e-6 tier).
  * words (optional): N x 8 little-endian words, two's complement of the centred integer. */
+/* [PAL >= 1.10.6] CKKSPackedEncoding::Decode: before FFTSpecial, Gaussian noise is added to every slot (Li-Micciancio
+ * key-recovery countermeasure).  The standard deviation is estimated from the part of the decrypted polynomial that an
+ * exact real-valued message cannot have — m(X) - m(1/X), i.e. 2 Im(z) —, floored at sqrt(N)/8 and multiplied by
+ * sqrt(M + 1) with M = 1.  Restated from the published source (ckkspackedencoding.cpp: Conjugate, StdDev, Decode);
+ * PARITY UNPINNED: the reference holds no decrypt output.  v: slots complex values (re, im interleaved), natural order,
+ * already at scale 2^p.  Returns the standard deviation of the noise that was added. */
+static double decode_stddev(const double *v, uint32_t n, uint32_t ring_dim) {
+    if (n == 1) return fabs(v[1]);
+    /* cv[i] = vec[i] - Conjugate(vec)[i], Conjugate[0] = conj(vec[0]), Conjugate[i] = (-Im vec[n-i], -Re vec[n-i]) */
+    double cv0_im = 2.0 * v[1];
+    double mean = 0.0;
+    for (uint32_t i = 1; i < n / 2; i++) mean += (v[2 * i] + v[2 * (n - i) + 1]) + (v[2 * i + 1] + v[2 * (n - i)]);
+    double half_re = v[2 * (n / 2)] + v[2 * (n - n / 2) + 1];
+    mean = 2.0 * mean + cv0_im + 2.0 * half_re;
+    mean /= (double)(2 * n) - 1.0;
+    double var = 0.0;
+    for (uint32_t i = 1; i < n / 2; i++) {
+        double re = v[2 * i] + v[2 * (n - i) + 1] - mean, im = v[2 * i + 1] + v[2 * (n - i)] - mean;
+        var += re * re + im * im;
+    }
+    var = 2.0 * var + (cv0_im - mean) * (cv0_im - mean) + 2.0 * (half_re - mean) * (half_re - mean);
+    var /= (double)(2 * n) - 2.0;
+    double sd = 0.5 * sqrt(var);
+    double floor_sd = 0.125 * sqrt((double)ring_dim);
+    return sd < floor_sd ? floor_sd : sd;
+}
+static void normal_pair(const uint32_t w[4], double *z0, double *z1) { /* Box-Muller on two 53-bit uniforms */
+    double u1 = (double)(((((uint64_t)w[1] << 32) | w[0]) >> 11) + 1) * 0x1p-53; /* (0, 1] */
+    double u2 = (double)((((uint64_t)w[3] << 32) | w[2]) >> 11) * 0x1p-53;        /* [0, 1) */
+    double r = sqrt(-2.0 * log(u1)), a = 6.283185307179586476925286766559 * u2;
+    *z0 = r * cos(a); *z1 = r * sin(a);
+}
+double orc_decode_noise(const orc_ctx *c, double *v, uint32_t n, const uint32_t key[8], uint64_t ct_index) {
+    double sd = 1.4142135623730951 * decode_stddev(v, n, c->wp.N); /* sqrt(M + 1), M = 1 */
+    uint32_t nonce[3] = {(uint32_t)ct_index, (uint32_t)(ct_index >> 32), STREAM_DECODE_NOISE}, out[16];
+    for (uint32_t i = 0; i < n; i++) { /* slot i: words 4 (i & 3) .. + 3 of block i >> 2 */
+        if ((i & 3) == 0) orc_chacha20_block(key, i >> 2, nonce, out);
+        double z0, z1;
+        normal_pair(out + 4 * (i & 3), &z0, &z1);
+        v[2 * i] += sd * z0; v[2 * i + 1] += sd * z1;
+    }
+    return sd;
+}
+
+static int decrypt_ct_impl_at(const orc_ctx *c, const uint64_t *ct, int L, double sf, double *out, int64_t *coeff_hi,
+                              uint64_t *coeff_lo, uint64_t *words, uint64_t ct_index);
 static int decrypt_ct_impl(const orc_ctx *c, const uint64_t *ct, int L, double sf, double *out, int64_t *coeff_hi,
                            uint64_t *coeff_lo, uint64_t *words) {
+    return decrypt_ct_impl_at(c, ct, L, sf, out, coeff_hi, coeff_lo, words, 0);
+}
+static int decrypt_ct_impl_at(const orc_ctx *c, const uint64_t *ct, int L, double sf, double *out, int64_t *coeff_hi,
+                              uint64_t *coeff_lo, uint64_t *words, uint64_t ct_index) {
     if (!c->have_cc || !c->have_sk || L < 1 || L > c->wp.L) return -1;
     uint32_t N = c->wp.N, Nh = N / 2, slots = c->wp.batch;
     /* L = towers of this ciphertext: the first L towers of the secret key and of the chain ([PAL] Decrypt drops the
@@ -681,8 +735,13 @@ static int decrypt_ct_impl(const orc_ctx *c, const uint64_t *ct, int L, double s
             z[2 * slot + (j < Nh ? 0 : 1)] = (neg ? -d : d) * pre;
         }
     }
+    if (c->opt_decode_noise) {
+        uint32_t key[8];
+        orc_seed_key(c->noise_seed, KEY_DECODE, key);
+        orc_decode_noise(c, z, slots, key, ct_index);
+    }
     orc_fft_special(c, z, slots);
-    /* [PAL] brings the values to scale 2^p (`pre`), would add its flooding noise there, and
+    /* [PAL] brings the values to scale 2^p (`pre`), adds its flooding noise there (opt_decode_noise), and
      * multiplies by 2^-p after the FFT; the two powers of two are exact. */
     for (uint32_t i = 0; i < slots; i++) out[i] = z[2 * i] * powP;
     free(t); free(z);
@@ -792,7 +851,17 @@ int orc_ct_mul_plain_accumulate(const orc_ctx *c, const uint64_t *ct, const doub
 
 int64_t orc_weight_constant(const orc_ctx *c, float w) {
     double sc = (double)w; /* ckks.cpp:287 narrows the Python float to float32, [PAL] widens it back */
+    if (c->opt_evalmult_round == 1) return (int64_t)llround(sc * orc_scaling_factor(c)); /* the other reading */
     return (int64_t)(sc * orc_scaling_factor(c) + 0.5);
+}
+/* option ids shared with the engine's shelfi_set_option */
+int orc_set_option(orc_ctx *c, int option, int64_t value) {
+    switch (option) {
+        case 1: if (value != 0 && value != 1) return -1; c->opt_evalmult_round = (int)value; return 0;
+        case 2: if (value != 0 && value != 1) return -1; c->opt_decode_noise = (int)value; return 0;
+        case 4: c->noise_seed = (uint64_t)value; return 0;
+        default: return -1;
+    }
 }
 
 /* ------------------------------------------------------------------------------------------- */
@@ -1420,7 +1489,7 @@ int orc_decrypt(orc_ctx *c, const uint8_t *blob, uint64_t len, uint64_t n, doubl
 #pragma omp parallel for schedule(dynamic) /* ckks.cpp:186 */
     for (uint64_t i = 0; i < v.n_ct; i++) {
         double *tmp = malloc(slots * sizeof(double));
-        if (decrypt_ct_impl(c, v.data + i * words, v.cL, v.meta[i].sf, tmp, NULL, NULL, NULL)) bad = 1;
+        if (decrypt_ct_impl_at(c, v.data + i * words, v.cL, v.meta[i].sf, tmp, NULL, NULL, NULL, i)) bad = 1;
         uint64_t length = (i == v.n_ct - 1) ? n - i * batch : batch; /* ckks.cpp:192-196 */
         memcpy(out + i * batch, tmp, length * sizeof(double));        /* ckks.cpp:200-204 (64-bit index) */
         free(tmp);

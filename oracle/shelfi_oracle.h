@@ -81,6 +81,11 @@ void orc_fft_special_inv(const orc_ctx *c, double *re_im, uint32_t size);
 /* RFC 8439 ChaCha20 block function and the test-key layout shared with the device sampler */
 void orc_chacha20_block(const uint32_t key[8], uint32_t counter, const uint32_t nonce[3], uint32_t out[16]);
 void orc_seed_key(uint64_t seed, uint32_t domain, uint32_t key[8]);
+/* the unpinned semantics, switchable: option 1 = EvalMult rounding (0: (int64)(c*Delta + 0.5), 1: llround),
+ * option 2 = decode noise (0 off, 1 on), option 4 = test seed of the decode noise */
+int orc_set_option(orc_ctx *c, int option, int64_t value);
+/* [PAL >= 1.10.6] Decode's noise flooding on slots complex values at scale 2^p; returns the noise's standard deviation */
+double orc_decode_noise(const orc_ctx *c, double *v, uint32_t n, const uint32_t key[8], uint64_t ct_index);
 /* the two primitive samplers on caller-chosen random words (unit tests of the rare paths) */
 int64_t orc_gauss_from_words(const orc_ctx *c, uint32_t h, uint32_t l);
 int64_t orc_ternary_from_half(uint32_t h16, const uint32_t key[8], const uint32_t nonce_retry[3], uint32_t j);
