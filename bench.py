@@ -199,6 +199,183 @@ def workload_config():
             "sharding": "weak: one P-parameter slice per GPU, no data-path collective"}
 
 
+
+# ------------------------------------------------------------------------------------------------
+# strong scaling: BASELINE configs[2] — ONE model sharded by ciphertext index over the ranks
+# ------------------------------------------------------------------------------------------------
+STRONG = {"batch": 8192, "bits": 52, "depth": 3, "learners": 10, "params": 11_689_512}
+
+
+def run_strong(args, torch, dist, SHELFI_FHE, world, rank, local, barrier, peak):
+    """CKKS N=16384, 4 limbs, 10 learners x ResNet-18 (11,689,512 parameters): every rank encrypts, averages and decrypts
+    its block of ciphertext indices and the decoded model is reassembled on EVERY rank inside the timed region
+    (decrypt-gather over NVLink peer stores, or decrypt + one NCCL all-gather: both are timed, the faster one is
+    `ms_per_step`).  The result is compared with the plaintext average on every rank."""
+    import tempfile
+    from SHELFI_FHE.sharding import PeerGather, shard_range
+    L = SHELFI_FHE.lib()
+    cfg = STRONG
+    K, P, batch = cfg["learners"], cfg["params"], cfg["batch"]
+    box = [None]
+    if rank == 0:
+        box[0] = tempfile.mkdtemp(prefix="shelfi_strong_") + "/"
+        g = SHELFI_FHE.CKKS("ckks", batch, cfg["bits"], box[0], device=local)
+        assert g.genCryptoContextAndKeyGen(mult_depth=cfg["depth"]) == 1
+        del g
+    if world > 1:
+        dist.broadcast_object_list(box, src=0)
+    h = SHELFI_FHE.CKKS("ckks", batch, cfg["bits"], box[0], device=local)
+    h.loadCryptoParams()
+    assert h.load_status == 0 and h.ring_dim == 16384 and h.num_limbs == 4
+    words = h.ciphertext_words
+    sf2 = h.scaling_factor * h.scaling_factor
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(3)                                   # the same model updates on every rank
+    xs = [(0.05 * torch.randn(P, generator=gen, device="cuda", dtype=torch.float32)).double() for _ in range(K)]
+    wk = float(np.float32(1.0 / K))
+    expect = sum(wk * x for x in xs)
+    w = (C.c_float * K)(*[1.0 / K] * K)
+    stream = torch.cuda.current_stream()
+    sp = C.c_void_p(stream.cuda_stream)
+
+    def ck(rc):
+        if rc:
+            raise RuntimeError(h._err())
+
+    def make_plan(n_ranks, r):
+        sh = shard_range(P, batch, r, n_ranks)
+        n_ct = sh.ct_count
+        cts = [torch.empty(max(n_ct, 1) * words, dtype=torch.int64, device="cuda") for _ in range(K)]
+        acc = torch.empty(max(n_ct, 1) * words, dtype=torch.int64, device="cuda")
+        xp = (C.c_void_p * K)(*[x.data_ptr() + 8 * sh.param_first for x in xs])
+        cp = (C.c_void_p * K)(*[t.data_ptr() for t in cts])
+        return sh, cts, acc, xp, cp
+
+    def compute(plan):
+        sh, _, acc, xp, cp = plan
+        if sh.ct_count:
+            ck(L.shelfi_encrypt_many_device(h.handle, xp, K, sh.param_count, sh.ct_first, cp, sp))
+            ck(L.shelfi_weighted_sum_device(h.handle, cp, w, K, sh.ct_count, C.c_void_p(acc.data_ptr()), sp))
+
+    def timed(fn, steps):
+        for _ in range(2):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    steps = max(2, min(args.steps, 10))
+    plan = make_plan(world, rank)
+    sh = plan[0]
+    block = sh.ct_per_rank * batch
+    full = torch.empty(world * block, dtype=torch.float64, device="cuda")
+    out = {"config": "configs[2]: CKKS N=16384, L=4 (60 + 3 x 52 bit), 10 learners x 11,689,512-param ResNet-18, one model "
+                     "sharded by ciphertext index", "n_gpus": world, "ciphertexts_total": -(-P // batch),
+           "ciphertexts_this_rank": sh.ct_count, "steps": steps, "reassembly_in_timed_region": world > 1}
+
+    def check(result):
+        rel = float(((result[:P] - expect).abs().max() / expect.abs().max()).item())
+        flags = [None] * world
+        if world > 1:
+            dist.all_gather_object(flags, rel)
+        else:
+            flags = [rel]
+        assert max(flags) < 1e-6, f"strong-scaling result off by {max(flags)}"
+        return max(flags)
+
+    if world == 1:
+        def step1():
+            compute(plan)
+            ck(L.shelfi_decrypt_device(h.handle, C.c_void_p(plan[2].data_ptr()), sh.ct_count, sf2, C.c_void_p(full.data_ptr()), P, sp))
+        ms = timed(step1, steps)
+        out.update({"ms_per_step": ms, "value": P / (ms / 1e3), "unit": UNIT, "max_rel_err_vs_plaintext_all_ranks": check(full),
+                    "reassembly": "none needed on one GPU", "efficiency_vs_single_gpu": 1.0, "single_gpu_ms": ms})
+    else:
+        local_out = torch.zeros(block, dtype=torch.float64, device="cuda")
+
+        def step_nccl():
+            compute(plan)
+            if sh.ct_count:
+                ck(L.shelfi_decrypt_device(h.handle, C.c_void_p(plan[2].data_ptr()), sh.ct_count, sf2,
+                                           C.c_void_p(local_out.data_ptr()), sh.param_count, sp))
+            dist.all_gather_into_tensor(full, local_out)
+
+        ms_nccl = timed(step_nccl, steps)
+        rel_nccl = check(full)
+        ms_peer, rel_peer, note = None, None, None
+        try:
+            if os.environ.get("SHELFI_BENCH_NO_PEER_GATHER") == "1":
+                raise RuntimeError("skipped by SHELFI_BENCH_NO_PEER_GATHER")
+            pg = PeerGather(h, P, batch)
+
+            def step_peer():
+                compute(plan)
+                pg.decrypt(plan[2].data_ptr(), sh.ct_count, sf2, stream.cuda_stream)
+
+            ms_peer = timed(step_peer, steps)
+            torch.cuda.synchronize()
+            rel_peer = check(pg.tensor())
+            # the two reassemblies of the SAME aggregated ciphertexts, bit for bit on every rank (the timed steps above
+            # encrypt afresh every time, so their results differ at the level of the encryption noise)
+            if sh.ct_count:
+                ck(L.shelfi_decrypt_device(h.handle, C.c_void_p(plan[2].data_ptr()), sh.ct_count, sf2,
+                                           C.c_void_p(local_out.data_ptr()), sh.param_count, sp))
+            dist.all_gather_into_tensor(full, local_out)
+            pg.decrypt(plan[2].data_ptr(), sh.ct_count, sf2, stream.cuda_stream)
+            torch.cuda.synchronize()
+            dist.barrier()
+            same = bool(torch.equal(pg.tensor()[:P], full[:P]))
+            flags = [None] * world
+            dist.all_gather_object(flags, same)
+            note = {"bit_identical_to_nccl_result_on_every_rank": all(flags), "barrier_timeouts": pg.timed_out()}
+            pg.close()
+        except Exception as e:   # the IPC path must never cost the bench line
+            note = {"error": repr(e)[:200]}
+        # the whole model on rank 0 alone, in the same run: the denominator of the efficiency
+        single_ms = None
+        if rank == 0:
+            del plan
+            torch.cuda.empty_cache()
+            p1 = make_plan(1, 0)
+            big = torch.empty(P, dtype=torch.float64, device="cuda")
+
+            def step_single():
+                compute(p1)
+                ck(L.shelfi_decrypt_device(h.handle, C.c_void_p(p1[2].data_ptr()), p1[0].ct_count, sf2, C.c_void_p(big.data_ptr()), P, sp))
+
+            for _ in range(2):
+                step_single()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record(stream)
+            for _ in range(3):
+                step_single()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            single_ms = e0.elapsed_time(e1) / 3
+            del p1, big
+        barrier()
+        best = min(v for v in (ms_nccl, ms_peer) if v is not None)
+        out.update({"ms_per_step": best, "value": P / (best / 1e3), "unit": UNIT,
+                    "ms_decrypt_plus_nccl_all_gather": ms_nccl, "ms_decrypt_gather_peer_stores": ms_peer,
+                    "reassembly": "decrypt-gather (peer stores + device barriers)" if ms_peer is not None and ms_peer <= ms_nccl else "decrypt + NCCL all-gather",
+                    "max_rel_err_vs_plaintext_all_ranks": max(v for v in (rel_nccl, rel_peer) if v is not None),
+                    "peer_gather": note, "single_gpu_ms": single_ms,
+                    "efficiency_vs_single_gpu": (single_ms / (world * best)) if single_ms else None})
+    bpp = bytes_per_param(K, 4)
+    out["path_frac_of_hbm_peak_per_gpu"] = bpp * (P / world) / (out["ms_per_step"] / 1e3) / 1e9 / peak
+    del xs, expect, full
+    torch.cuda.empty_cache()
+    return out
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -559,6 +736,16 @@ def run_ours(args):
         except Exception as e:  # the IPC path must never cost the bench line
             peer_gather = {"error": repr(e)[:200]}
 
+    del d_ct, d_x, d_avg
+    torch.cuda.empty_cache()
+    strong = None
+    if not args.no_strong:
+        try:
+            strong = run_strong(args, torch, dist, SHELFI_FHE, world, rank, local, barrier, peak)
+        except AssertionError:
+            raise
+        except Exception as e:      # e.g. out of memory next to another tenant: the contract line still goes out
+            strong = {"error": repr(e)[:300]}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_arm_bounded(target_seconds=12.0)
@@ -580,7 +767,7 @@ def run_ours(args):
                 "ntt": {"GBps": ntt_gbs, "frac_of_peak": ntt_gbs / peak, "rows": rows, "ms": ntt_ms,
                         "bytes_per_row": 16 * N_RING},
                 "value_reference_convention": ref_conv, "config1_pythonapi_example": config1, "kernels": prof,
-                "gather_ms": gather_ms, "peer_gather": peer_gather,
+                "gather_ms": gather_ms, "peer_gather": peer_gather, "strong": strong,
                 "rescale": rescale,
                 "parity": {"max_rel_err_vs_plaintext": rel, "host_path": rel_h, "drop_in_resident": rel_api}}
         emit(line)
@@ -614,6 +801,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling object (configs[2])")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
