@@ -164,45 +164,51 @@ constexpr size_t kStageBytes = 16u << 20;   // two page-locked staging chunks of
 
 // Device memory of the resident ciphertext vectors (shelfi_ct): freed buffers are kept on a size-keyed free list,
 // because cudaFree synchronises the whole device and a federation round makes and drops K + 1 vectors of the same size.
-// Every kernel that touches such a buffer runs on the handle's compute stream, so handing a freed buffer to the next
-// vector is ordered by that stream and needs no event.
+// A parked buffer carries the event that was recorded on the compute stream when it was given back (after everything
+// that read or wrote it had been queued there): whoever takes it on ANOTHER stream waits for that event first.
+struct PoolBuf { void *p = nullptr; cudaEvent_t ev = nullptr; };
 struct DevicePool {
     static constexpr size_t kGrain = 2u << 20;
-    std::multimap<size_t, void *> free_list;
+    std::multimap<size_t, PoolBuf> free_list;
     size_t in_use = 0, pooled = 0, limit = 0;   // bytes; limit 0 = not yet sized
     static size_t round_up(size_t b) { return (b + kGrain - 1) / kGrain * kGrain; }
     void trim() {
-        for (auto &kv : free_list) cudaFree(kv.second);
+        for (auto &kv : free_list) {
+            cudaFree(kv.second.p);
+            if (kv.second.ev) cudaEventDestroy(kv.second.ev);
+        }
         free_list.clear();
         pooled = 0;
     }
-    // returns nullptr when the limit or the device is exhausted (after giving the pooled buffers back)
-    void *take(size_t bytes, size_t *cap) {
+    // returns {nullptr} when the limit or the device is exhausted (after giving the pooled buffers back)
+    PoolBuf take(size_t bytes, size_t *cap) {
         const size_t want = round_up(bytes);
         auto it = free_list.lower_bound(want);
         if (it != free_list.end() && it->first <= want + want / 4) {
-            void *p = it->second;
+            PoolBuf b = it->second;
             *cap = it->first;
             pooled -= it->first; in_use += it->first;
             free_list.erase(it);
-            return p;
+            return b;
         }
         if (limit && in_use + pooled + want > limit) trim();
-        if (limit && in_use + want > limit) return nullptr;
+        if (limit && in_use + want > limit) return PoolBuf{};
         void *p = nullptr;
         if (cudaMalloc(&p, want) != cudaSuccess) {
             cudaGetLastError();
             trim();
-            if (cudaMalloc(&p, want) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+            if (cudaMalloc(&p, want) != cudaSuccess) { cudaGetLastError(); return PoolBuf{}; }
         }
         *cap = want; in_use += want;
-        return p;
+        return PoolBuf{p, nullptr};
     }
-    void give(void *p, size_t cap) {
+    void give(PoolBuf b, size_t cap) {
         in_use -= cap; pooled += cap;
-        free_list.emplace(cap, p);
+        free_list.emplace(cap, b);
     }
 };
+
+constexpr int kEncStreams = 4;   // resident encrypt calls rotate over this many streams (and input slots)
 
 }  // namespace
 
@@ -212,6 +218,11 @@ struct shelfi_ct {
     shelfi_ckks *owner = nullptr;
     u64 *d = nullptr;
     size_t cap = 0;
+    cudaEvent_t buf_ev = nullptr;   // travels with the buffer (DevicePool)
+    // a vector made by encrypt is written on one of the encrypt streams: `ready` is recorded there, and the first use
+    // on the compute stream (or the free) makes that stream wait for it
+    cudaEvent_t ready = nullptr;
+    bool ready_pending = false;
     uint64_t n_ct = 0;
     uint32_t limbs = 0;
     wire::ContextParams ctx;
@@ -267,10 +278,16 @@ struct shelfi_ckks {
     // encryption of the one before, and the events that order the copy streams against the compute stream
     DevicePool pool;
     std::vector<shelfi_ct *> live;
-    DeviceBuffer r_x[2], r_out;
-    cudaEvent_t ev_x_in[2] = {nullptr, nullptr}, ev_x_free[2] = {nullptr, nullptr}, ev_r_out = nullptr;
-    bool x_busy[2] = {false, false};
+    // Consecutive encrypt calls are independent of one another: they rotate over kEncStreams streams (each with its own
+    // input slot), so the next learner's kernel fills the SMs the current one leaves idle (407 CTAs on 444 slots at
+    // config 2) and small vectors (3 CTAs per call in the pythonApi example) run side by side.  Everything else that
+    // touches a vector runs on the compute stream `stream`.
+    cudaStream_t enc_streams[kEncStreams] = {nullptr};
+    DeviceBuffer r_x[kEncStreams], r_out;
+    cudaEvent_t ev_x_in[kEncStreams] = {nullptr}, ev_x_free[kEncStreams] = {nullptr}, ev_r_out = nullptr;
+    bool x_busy[kEncStreams] = {false};
     unsigned r_turn = 0;
+    std::vector<cudaEvent_t> spare_events;
     // The device-resident calls run on the CALLER's stream but share this handle's scratch (encode / sample output,
     // decrypt coefficients, CRT doubles, rescale tower).  Two calls on different streams would otherwise be free to
     // overlap on the GPU and corrupt each other's intermediates: every such call first makes its stream wait for the
@@ -1333,7 +1350,8 @@ int rescale_host(shelfi_ckks *h, const uint8_t *blob, uint64_t blob_len, uint8_t
 // ---------------------------------------------------------------------------------------------
 int ensure_resident(shelfi_ckks *h) {
     if (h->ev_r_out) return 0;
-    for (int i = 0; i < 2; i++) {
+    for (int i = 0; i < kEncStreams; i++) {
+        CU(cudaStreamCreateWithFlags(&h->enc_streams[i], cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&h->ev_x_in[i], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_x_free[i], cudaEventDisableTiming));
     }
@@ -1350,26 +1368,54 @@ int ensure_resident(shelfi_ckks *h) {
     CU(cudaEventCreateWithFlags(&h->ev_r_out, cudaEventDisableTiming));
     return 0;
 }
-int new_ct(shelfi_ckks *h, uint64_t n_ct, uint32_t limbs, shelfi_ct **out) {
+cudaEvent_t take_event(shelfi_ckks *h) {
+    if (!h->spare_events.empty()) { cudaEvent_t e = h->spare_events.back(); h->spare_events.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return e;
+}
+// `on`: the stream that will write the new vector first; a recycled buffer's last uses were ordered on h->stream
+int new_ct(shelfi_ckks *h, uint64_t n_ct, uint32_t limbs, shelfi_ct **out, cudaStream_t on = nullptr) {
     const size_t bytes = (size_t)n_ct * 2 * limbs * h->ctx.ring_dim * sizeof(uint64_t);
     shelfi_ct *c = new shelfi_ct();
-    c->d = static_cast<u64 *>(h->pool.take(bytes, &c->cap));
-    if (!c->d) {
+    PoolBuf b = h->pool.take(bytes, &c->cap);
+    if (!b.p) {
         delete c;
         return fail(h, SHELFI_ERR_MEMORY, "device pool exhausted: " + std::to_string(bytes >> 20) + " MiB requested, " +
                                               std::to_string(h->pool.in_use >> 20) + " MiB in resident ciphertexts, limit " +
                                               std::to_string(h->pool.limit >> 20) + " MiB (free vectors you no longer need, or raise SHELFI_RESIDENT_LIMIT_MB)");
+    }
+    c->d = static_cast<u64 *>(b.p);
+    c->buf_ev = b.ev;
+    if (b.ev && on && on != h->stream && cudaStreamWaitEvent(on, b.ev, 0) != cudaSuccess) {
+        h->pool.give(b, c->cap);
+        delete c;
+        return cuda_fail(h, cudaGetLastError(), "cudaStreamWaitEvent");
     }
     c->owner = h; c->n_ct = n_ct; c->limbs = limbs; c->ctx = h->ctx;
     h->live.push_back(c);
     *out = c;
     return 0;
 }
+// before the compute stream touches a vector that an encrypt stream may still be writing
+void ct_ready(shelfi_ckks *h, shelfi_ct *c) {
+    if (c->ready_pending) {
+        cudaStreamWaitEvent(h->stream, c->ready, 0);
+        c->ready_pending = false;
+    }
+}
 void drop_ct(shelfi_ckks *h, shelfi_ct *c) {
     auto it = std::find(h->live.begin(), h->live.end(), c);
     if (it == h->live.end()) return;
     h->live.erase(it);
-    if (c->d) h->pool.give(c->d, c->cap);
+    if (c->d) {
+        ct_ready(h, c);                                  // an unused encryption may still be running
+        if (!c->buf_ev) c->buf_ev = take_event(h);
+        if (c->buf_ev) cudaEventRecord(c->buf_ev, h->stream);   // after every use queued so far
+        else cudaStreamSynchronize(h->stream);
+        h->pool.give(PoolBuf{c->d, c->buf_ev}, c->cap);
+    }
+    if (c->ready) h->spare_events.push_back(c->ready);
     delete c;
 }
 bool is_device_ptr(const void *p) {
@@ -1397,25 +1443,26 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     trim_enc_plans(h);
     const uint64_t n_ct = (n + h->batch - 1) / h->batch;
     const size_t in_bytes = n * (dtype ? 4 : 8);
+    const unsigned b = h->r_turn++ % kEncStreams;
+    cudaStream_t st = h->enc_streams[b], cs = h->copy_stream;
     shelfi_ct *c = nullptr;
-    if ((rcode = new_ct(h, n_ct, h->ctx.limbs, &c))) return rcode;
+    if ((rcode = new_ct(h, n_ct, h->ctx.limbs, &c, st))) return rcode;
     wire::CiphertextMeta m;
     m.depth = 1; m.level = 0; m.encoding_type = 4;
     m.scaling_factor = (double)h->ctx.modulus[h->ctx.limbs - 1];
     std::memcpy(m.tag, h->key_tag.c_str(), 32);
     c->meta.assign(1, m);
-    cudaStream_t st = h->stream, cs = h->copy_stream;
     auto bail = [&](int code) {
         cudaStreamSynchronize(cs);
         cudaStreamSynchronize(st);
         drop_ct(h, c);
         return code;
     };
+    if (!(c->ready = take_event(h))) return bail(fail(h, SHELFI_ERR_CUDA, "cudaEventCreate failed"));
     const void *d_x = x;
     const bool on_device = is_device_ptr(x);
-    const unsigned b = h->r_turn++ & 1u;
     if (!on_device) {
-        // slot b was last read by the encryption two calls ago
+        // slot b was last read by the encryption kEncStreams calls ago
         if (h->x_busy[b]) CUB(cudaStreamWaitEvent(cs, h->ev_x_free[b], 0));
         if (h->r_x[b].cap < in_bytes) {   // growing reallocates: wait until nothing reads the old buffer
             CUB(cudaStreamSynchronize(st));
@@ -1430,6 +1477,8 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     u64 *ct_ptr = c->d;
     if ((rcode = encrypt_dense_many(h, &dx64, 1, n, 0, reinterpret_cast<uint64_t *const *>(&ct_ptr), st, nullptr, dtype)))
         return bail(rcode);
+    CUB(cudaEventRecord(c->ready, st));
+    c->ready_pending = true;
     if (!on_device) {
         CUB(cudaEventRecord(h->ev_x_free[b], st));
         h->x_busy[b] = true;
@@ -1502,7 +1551,10 @@ int ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *w, u
     for (auto &m : acc->meta) { m.depth += 1; m.scaling_factor *= sf0; }   // [PAL] EvalMult(ct, double), no rescale
     cudaStream_t st = h->stream;
     std::vector<const uint64_t *> ptrs(k);
-    for (uint32_t i = 0; i < k; i++) ptrs[i] = cts[i]->d;
+    for (uint32_t i = 0; i < k; i++) {
+        ct_ready(h, cts[i]);
+        ptrs[i] = cts[i]->d;
+    }
     if ((rcode = weighted_sum_dense(h, ptrs.data(), w, k, n_ct, acc->d, false, st))) { drop_ct(h, acc); return rcode; }
     if (rescale) {
         shelfi_ct *red = nullptr;
@@ -1523,6 +1575,7 @@ int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
     if (rcode) return rcode;
     if (!c || c->owner != h || !out) return fail(h, SHELFI_ERR_ARG, "null argument or foreign vector");
     if ((rcode = ensure_resident(h))) return rcode;
+    ct_ready(h, const_cast<shelfi_ct *>(c));
     const uint64_t batch = h->batch, n_ct = c->n_ct;
     if (n == 0 || n > n_ct * batch || n + batch <= n_ct * batch)
         return fail(h, SHELFI_ERR_ARG, "data_dimensions inconsistent with the number of ciphertexts");
@@ -1581,6 +1634,7 @@ int ct_to_blob(shelfi_ckks *h, const shelfi_ct *c, uint8_t *dst, uint64_t cap, u
     if (rcode) return rcode;
     if (!c || c->owner != h || !dst || !len) return fail(h, SHELFI_ERR_ARG, "null argument or foreign vector");
     trim_enc_plans(h);
+    ct_ready(h, const_cast<shelfi_ct *>(c));
     shelfi_ckks::EncPlan *ep = nullptr;
     wire::BlobPlan own;
     if ((rcode = ct_plan(h, c, &ep, &own))) return rcode;
@@ -1635,13 +1689,21 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         cudaDeviceSynchronize();
         h->prof.release();
         free_params(h);
-        for (shelfi_ct *c : h->live) { if (c->d) cudaFree(c->d); delete c; }   // vectors die with their handle
+        for (shelfi_ct *c : h->live) {   // vectors die with their handle
+            if (c->d) cudaFree(c->d);
+            if (c->buf_ev) cudaEventDestroy(c->buf_ev);
+            if (c->ready) cudaEventDestroy(c->ready);
+            delete c;
+        }
         h->live.clear();
         h->pool.trim();
-        for (int i = 0; i < 2; i++) {
+        for (cudaEvent_t e : h->spare_events) cudaEventDestroy(e);
+        h->spare_events.clear();
+        for (int i = 0; i < kEncStreams; i++) {
             h->r_x[i].release();
             if (h->ev_x_in[i]) cudaEventDestroy(h->ev_x_in[i]);
             if (h->ev_x_free[i]) cudaEventDestroy(h->ev_x_free[i]);
+            if (h->enc_streams[i]) cudaStreamDestroy(h->enc_streams[i]);
         }
         h->r_out.release();
         if (h->ev_r_out) cudaEventDestroy(h->ev_r_out);
@@ -2085,7 +2147,11 @@ int shelfi_ct_info(const shelfi_ct *ct, uint64_t *n_ct, uint32_t *limbs, uint64_
     if (scaling_factor) *scaling_factor = ct->meta[0].scaling_factor;
     return 0;
 }
-const uint64_t *shelfi_ct_device_ptr(const shelfi_ct *ct) { return ct ? ct->d : nullptr; }
+const uint64_t *shelfi_ct_device_ptr(const shelfi_ct *ct) {
+    if (!ct) return nullptr;
+    if (ct->ready_pending) cudaEventSynchronize(ct->ready);   // the caller will read it on a stream of its own
+    return ct->d;
+}
 void shelfi_ct_free(shelfi_ckks *h, shelfi_ct *ct) {
     if (!h || !ct) return;
     std::lock_guard<std::mutex> lock(h->mu);
@@ -2117,6 +2183,8 @@ int shelfi_synchronize(shelfi_ckks *h) {
     CU(cudaStreamSynchronize(h->stream));
     CU(cudaStreamSynchronize(h->copy_stream));
     if (h->d2h_stream) CU(cudaStreamSynchronize(h->d2h_stream));
+    for (cudaStream_t es : h->enc_streams)
+        if (es) CU(cudaStreamSynchronize(es));
     return 0;
 }
 
