@@ -793,6 +793,9 @@ HD u32 rotl32(u32 x, int n) {
     a += b; d ^= a; d = rotl32(d, 8);                 \
     c += d; b ^= c; b = rotl32(b, 7);
 struct SamplerKey { u32 k[8]; };
+#ifndef SHELFI_CHACHA_ROUNDS
+#define SHELFI_CHACHA_ROUNDS 20   // RFC 8439.  (Reduced-round builds exist only to measure what the generator costs.)
+#endif
 // state = "expand 32-byte k" | key | counter | nonce[3]; out = state + 20 rounds(state)
 HD void chacha20_block(const SamplerKey &key, u32 counter, u32 n0, u32 n1, u32 n2, u32 (&out)[16]) {
     const u32 in[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u, key.k[0], key.k[1], key.k[2], key.k[3],
@@ -801,7 +804,7 @@ HD void chacha20_block(const SamplerKey &key, u32 counter, u32 n0, u32 n1, u32 n
 #pragma unroll
     for (int i = 0; i < 16; i++) x[i] = in[i];
 #pragma unroll
-    for (int r = 0; r < 10; r++) {
+    for (int r = 0; r < SHELFI_CHACHA_ROUNDS / 2; r++) {
         SHELFI_CHACHA_QR(x[0], x[4], x[8], x[12])
         SHELFI_CHACHA_QR(x[1], x[5], x[9], x[13])
         SHELFI_CHACHA_QR(x[2], x[6], x[10], x[14])

@@ -474,7 +474,10 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
 // encode_kernel + sample_add_kernel + encrypt_kernel this samples once per ciphertext, is one launch, lets the
 // latency-bound FFT / sampler phases of one CTA hide under the transforms of its two co-resident CTAs, and (round 2)
 // moves no scratch bytes to DRAM.
-__global__ void __launch_bounds__(kNttThreads, 3) encrypt_fused_kernel(const __grid_constant__ RingConst rc,
+#ifndef SHELFI_FUSED_CTAS_PER_SM
+#define SHELFI_FUSED_CTAS_PER_SM 3
+#endif
+__global__ void __launch_bounds__(kNttThreads, SHELFI_FUSED_CTAS_PER_SM) encrypt_fused_kernel(const __grid_constant__ RingConst rc,
                                                                        const __grid_constant__ EncodeConst ec,
                                                                        const __grid_constant__ SamplerConst sc,
                                                                        const __grid_constant__ EncryptBatch eb,
