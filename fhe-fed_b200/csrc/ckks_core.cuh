@@ -97,6 +97,9 @@ struct LimbConst {
     // FP64-pipe forward transform (limbs with q < 2^53, ring dimension 8192): centred twiddles as doubles, or null
     const double *dtw;
     double qd, qinv;  // q and 1/q as doubles
+    // ... and the inverse transform: centred psi^-bitrev(i), N^-1 and itw[1] * N^-1 as doubles (null / 0 with dtw)
+    const double *ditw;
+    double d_ninv, d_wninv;
 };
 
 struct RingConst {
@@ -614,6 +617,111 @@ struct DHeadLoad {
         return d_renorm((blk & 1u) ? fsub(s0, t) : fadd(s0, t), q, qinv, lc->dthr);
     }
 };
+
+// ---- the inverse transform on the FP64 pipe (same limbs as the forward one: q <= 1.125 * 2^52) ----
+// Gentleman-Sande butterfly on centred integer-valued doubles: s = x + y, d = x - y, both renormalised to |.| <= q/2
+// (|x|, |y| <= 0.76 q on entry, so the sums are exact integers below 1.52 q < 2^53), then r = d * w mod q, |r| <= 0.76 q,
+// left as it is: the next stage's sums absorb it.  14 FP64 operations, none on the integer pipes; the integer
+// butterfly costs 6 IMAD.WIDE + 4 IMAD + carries (108 ns per 8192-point row against 63 forward in round 1, which is
+// what decrypt and rescale paid).  Every intermediate is an exact integer, so the residues equal the integer path's.
+HD void d_gs_bfly(double &x, double &y, double w, double q, double qinv, u32 thr) {
+    const double s = d_renorm(fadd(x, y), q, qinv, thr);
+    const double d = d_renorm(fsub(x, y), q, qinv, thr);
+    x = s;
+    y = d_mulmod(d, w, q, qinv);
+}
+HD void d_gs_radix8(double (&a)[8], const double *__restrict__ itw, u32 t2, double q, double qinv, u32 thr) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) d_gs_bfly(a[2 * k], a[2 * k + 1], itw[4 * t2 + k], q, qinv, thr);
+    const double w0 = itw[2 * t2], w1 = itw[2 * t2 + 1];
+    d_gs_bfly(a[0], a[2], w0, q, qinv, thr); d_gs_bfly(a[1], a[3], w0, q, qinv, thr);
+    d_gs_bfly(a[4], a[6], w1, q, qinv, thr); d_gs_bfly(a[5], a[7], w1, q, qinv, thr);
+    const double w = itw[t2];
+#pragma unroll
+    for (int k = 0; k < 4; k++) d_gs_bfly(a[k], a[k + 4], w, q, qinv, thr);
+}
+// first pass (address bit 0) from the loader; ld(pair index, &x, &y) delivers values below 4q (integer words)
+template <class Load>
+HD void dinv_phase_e(int tid, u64 *smem, const LimbConst &lc, u32 hb, Load ld) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+    const double *__restrict__ itw = lc.ditw + ((size_t)hb << (kLogN - 1));
+#pragma unroll 2
+    for (int r = 0; r < 16; r++) {
+        const u32 vt = tid + kNttThreads * r;
+        u64 xi, yi;
+        ld(vt, xi, yi);
+        double x = d_from_residue(csub(csub(xi, lc.q2), lc.q), lc.q), y = d_from_residue(csub(csub(yi, lc.q2), lc.q), lc.q);
+        d_gs_bfly(x, y, itw[vt], q, qinv, thr);
+        *reinterpret_cast<double2 *>(sm + tile_pair(vt)) = double2{x, y};
+    }
+}
+template <int LO>  // LO = 1, 4, 7
+HD void dinv_phase_mid(int tid, u64 *smem, const LimbConst &lc, u32 hb) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        const u32 vt = tid + kNttThreads * r;
+        const u32 base = tile_base<LO>(vt);
+        double a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = dtile(sm, tile_off<LO>(base, k));
+        d_gs_radix8(a, lc.ditw, (hb << (10 - LO)) + (vt >> LO), q, qinv, thr);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dtile(sm, tile_off<LO>(base, k)) = a[k];
+    }
+}
+// last pass (address bits 10..12) with N^-1 folded into the final stage; st(index, residue in [0, q))
+template <class Store>
+HD void dinv_phase_last(int tid, const u64 *smem, const LimbConst &lc, Store st) {
+    char *sm = const_cast<char *>(reinterpret_cast<const char *>(smem));
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+    const double *__restrict__ itw = lc.ditw;
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        const u32 vt = tid + kNttThreads * r;
+        const u32 base = tile_base<10>(vt);
+        double a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = dtile(sm, tile_off<10>(base, k));
+#pragma unroll
+        for (int k = 0; k < 4; k++) d_gs_bfly(a[2 * k], a[2 * k + 1], itw[4 + k], q, qinv, thr);
+        const double w0 = itw[2], w1 = itw[3];
+        d_gs_bfly(a[0], a[2], w0, q, qinv, thr); d_gs_bfly(a[1], a[3], w0, q, qinv, thr);
+        d_gs_bfly(a[4], a[6], w1, q, qinv, thr); d_gs_bfly(a[5], a[7], w1, q, qinv, thr);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {   // x' = (x + y) / N, y' = (x - y) w / N
+            const double s = d_renorm(fadd(a[k], a[k + 4]), q, qinv, thr), d = d_renorm(fsub(a[k], a[k + 4]), q, qinv, thr);
+            a[k] = d_renorm(d_mulmod(s, lc.d_ninv, q, qinv), q, qinv, thr);
+            a[k + 4] = d_renorm(d_mulmod(d, lc.d_wninv, q, qinv), q, qinv, thr);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, d_to_residue(a[k], lc.q));
+    }
+}
+// rings above one tile: an ordinary radix-8 pass with twiddles offset by hb; canonical residues (the tail pass takes
+// anything below 2q)
+template <class Store>
+HD void dinv_phase_last_lazy(int tid, const u64 *smem, const LimbConst &lc, u32 hb, Store st) {
+    char *sm = const_cast<char *>(reinterpret_cast<const char *>(smem));
+    const double q = lc.qd, qinv = lc.qinv;
+    const u32 thr = lc.dthr;
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        const u32 vt = tid + kNttThreads * r;
+        const u32 base = tile_base<10>(vt);
+        double a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = dtile(sm, tile_off<10>(base, k));
+        d_gs_radix8(a, lc.ditw, hb, q, qinv, thr);
+#pragma unroll
+        for (int k = 0; k < 8; k++) st((u32)(k << 10) | vt, d_to_residue(d_renorm(a[k], q, qinv, thr), lc.q));
+    }
+}
 
 // ---- inverse NTT phases (bit-reversed in, natural out), Gentleman-Sande ----
 // Inputs to a pass are < 2q; X' = X + Y doubles the bound per stage, Y' = (X - Y + c)*w with

@@ -468,7 +468,7 @@ int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
     RingConst rc{};
     rc.n = N; rc.logn = logn; rc.log_blocks = logn - kLogN; rc.limbs = p.limbs; rc.slots = p.batch_size;
     std::vector<tw_t> tw_all((size_t)p.limbs * N), itw_all((size_t)p.limbs * N), tw, itw;
-    std::vector<double> dtw_all((size_t)p.limbs * N, 0.0), dtw;
+    std::vector<double> dtw_all((size_t)p.limbs * 2 * N, 0.0), dtw;   // per limb: forward twiddles, then inverse
     bool has_dtw[kMaxLimbs] = {false};
     // SHELFI_FP64_NTT=0 keeps every limb on the integer pipe (A/B measurements; the results are the same bits)
     const char *fp64_env = std::getenv("SHELFI_FP64_NTT");
@@ -479,7 +479,7 @@ int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
         std::memcpy(&tw_all[(size_t)l * N], tw.data(), sizeof(tw_t) * N);
         std::memcpy(&itw_all[(size_t)l * N], itw.data(), sizeof(tw_t) * N);
         has_dtw[l] = want_fp64 && !dtw.empty();
-        if (has_dtw[l]) std::memcpy(&dtw_all[(size_t)l * N], dtw.data(), sizeof(double) * N);
+        if (has_dtw[l]) std::memcpy(&dtw_all[(size_t)l * 2 * N], dtw.data(), sizeof(double) * 2 * N);
     }
     int rcode;
     if ((rcode = upload(h, &h->d_dtw, dtw_all.data(), dtw_all.size() * sizeof(double)))) return rcode;
@@ -488,7 +488,8 @@ int install_context(shelfi_ckks *h, const wire::ContextParams &p) {
     for (uint32_t l = 0; l < p.limbs; l++) {
         rc.limb[l].tw = h->d_tw.as<tw_t>() + (size_t)l * N;
         rc.limb[l].itw = h->d_itw.as<tw_t>() + (size_t)l * N;
-        rc.limb[l].dtw = has_dtw[l] ? h->d_dtw.as<double>() + (size_t)l * N : nullptr;
+        rc.limb[l].dtw = has_dtw[l] ? h->d_dtw.as<double>() + (size_t)l * 2 * N : nullptr;
+        rc.limb[l].ditw = has_dtw[l] ? rc.limb[l].dtw + N : nullptr;
     }
     const uint32_t slots = p.batch_size;
     std::vector<cplx> t_inv, t_fwd;

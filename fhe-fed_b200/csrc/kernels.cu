@@ -214,6 +214,19 @@ __global__ void __launch_bounds__(kNttThreads, 3) plain_ntt_kernel(const __grid_
 // applies the D outermost stages and N^-1 as a streaming pass
 template <int D, class Load>
 __device__ __forceinline__ void intt_tile(int tid, u64 *sm, const LimbConst &lc, u32 hb, Load ld, u64 *dst) {
+    if (lc.ditw) {   // q < 2^53: the same transform on the FP64 pipe
+        dinv_phase_e(tid, sm, lc, hb, ld);
+        __syncthreads();
+        dinv_phase_mid<1>(tid, sm, lc, hb);
+        __syncthreads();
+        dinv_phase_mid<4>(tid, sm, lc, hb);
+        __syncthreads();
+        dinv_phase_mid<7>(tid, sm, lc, hb);
+        __syncthreads();
+        if (D == 0) dinv_phase_last(tid, sm, lc, StoreGlobal{dst});
+        else dinv_phase_last_lazy(tid, sm, lc, hb, StoreGlobal{dst});
+        return;
+    }
     inv_phase_e(tid, sm, lc, hb, ld);
     __syncthreads();
     inv_phase_mid<1>(tid, sm, lc, hb);

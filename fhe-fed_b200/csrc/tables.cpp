@@ -93,11 +93,14 @@ std::string make_limb_const(uint64_t q, uint64_t psi, uint32_t logn, LimbConst *
     if (dtw) {
         dtw->clear();
         if (q <= (((uint64_t)9) << 49) && q >= 1024) {
-            dtw->assign(n, 0.0);
+            auto centred = [q](uint64_t w) { return w > (q >> 1) ? -(double)(q - w) : (double)w; };
+            dtw->assign(2 * (size_t)n, 0.0);          // forward twiddles, then the inverse ones (LimbConst::ditw = dtw + n)
             for (uint32_t i = 0; i < n; i++) {
-                uint64_t w = (*tw)[i].w;
-                (*dtw)[i] = w > (q >> 1) ? -(double)(q - w) : (double)w;
+                (*dtw)[i] = centred((*tw)[i].w);
+                (*dtw)[n + i] = centred((*itw)[i].w);
             }
+            lc->d_ninv = centred(lc->ninv);
+            lc->d_wninv = centred(lc->wninv);
             lc->qd = (double)q;
             lc->qinv = 1.0 / lc->qd;
             double thr = 0.49 * lc->qd;

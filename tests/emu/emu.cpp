@@ -55,6 +55,15 @@ static void replay_forward_d(u64 *sm, const LimbConst &lc, u32 hb, Load ld, Stor
 // intt_tile<D>
 template <int D, class Load>
 static void replay_inverse(u64 *sm, const LimbConst &lc, u32 hb, Load ld, u64 *dst) {
+    if (lc.ditw) {   // the FP64-pipe inverse transform
+        FOR_THREADS(kNttThreads) dinv_phase_e(tid, sm, lc, hb, ld);
+        FOR_THREADS(kNttThreads) dinv_phase_mid<1>(tid, sm, lc, hb);
+        FOR_THREADS(kNttThreads) dinv_phase_mid<4>(tid, sm, lc, hb);
+        FOR_THREADS(kNttThreads) dinv_phase_mid<7>(tid, sm, lc, hb);
+        if (D == 0) { FOR_THREADS(kNttThreads) dinv_phase_last(tid, sm, lc, StoreGlobal{dst}); }
+        else { FOR_THREADS(kNttThreads) dinv_phase_last_lazy(tid, sm, lc, hb, StoreGlobal{dst}); }
+        return;
+    }
     FOR_THREADS(kNttThreads) inv_phase_e(tid, sm, lc, hb, ld);
     FOR_THREADS(kNttThreads) inv_phase_mid<1>(tid, sm, lc, hb);
     FOR_THREADS(kNttThreads) inv_phase_mid<4>(tid, sm, lc, hb);
@@ -93,6 +102,7 @@ Emu *emu_create_ex(const uint64_t *q, const uint64_t *psi, uint32_t limbs, uint3
         e->rc.limb[l].tw = e->tw[l].data();
         e->rc.limb[l].itw = e->itw[l].data();
         e->rc.limb[l].dtw = e->dtw[l].empty() ? nullptr : e->dtw[l].data();
+        e->rc.limb[l].ditw = e->dtw[l].empty() ? nullptr : e->dtw[l].data() + n;
     }
     make_fft_tables(2 * n, slots, &e->fft_inv, &e->fft_fwd);
     std::memset(&e->ec, 0, sizeof e->ec);
@@ -137,8 +147,10 @@ void emu_ntt_forward(const Emu *e, uint32_t limb, uint64_t *row) {
 int emu_limb_fp64(const Emu *e, uint32_t l) { return e->rc.limb[l].dtw != nullptr; }
 // switch the FP64 path off / on for this context (the integer path must give the same bits)
 void emu_set_fp64(Emu *e, int on) {
-    for (u32 l = 0; l < e->rc.limbs; l++)
+    for (u32 l = 0; l < e->rc.limbs; l++) {
         e->rc.limb[l].dtw = (on && !e->dtw[l].empty()) ? e->dtw[l].data() : nullptr;
+        e->rc.limb[l].ditw = e->rc.limb[l].dtw ? e->rc.limb[l].dtw + e->rc.n : nullptr;
+    }
 }
 void emu_ntt_inverse(const Emu *e, uint32_t limb, uint64_t *row) {
     std::vector<u64> sm(kN);

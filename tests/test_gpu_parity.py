@@ -430,6 +430,13 @@ def test_fp64_pipe_ntt_equals_integer_pipe(shelfi, gpu_ckks, monkeypatch):
     check(hf, shelfi.lib().shelfi_ntt_forward_device(hf.handle, ptr(d1), rows, stream()))
     check(hi, shelfi.lib().shelfi_ntt_forward_device(hi.handle, ptr(d2), rows, stream()))
     assert torch.equal(d1, d2)
+    # ... and back: the inverse transform of the scaling limb runs on the FP64 pipe as well (round 2)
+    e1, e2 = dev_u64(a), dev_u64(a)
+    check(hf, shelfi.lib().shelfi_ntt_inverse_device(hf.handle, ptr(e1), rows, stream()))
+    check(hi, shelfi.lib().shelfi_ntt_inverse_device(hi.handle, ptr(e2), rows, stream()))
+    assert torch.equal(e1, e2)
+    check(hf, shelfi.lib().shelfi_ntt_inverse_device(hf.handle, ptr(d1), rows, stream()))
+    assert np.array_equal(host_u64(d1).reshape(rows, N), a)
     x = rng.normal(0, 20.0, 300000)
     hf.set_sampler_seed(5); hi.set_sampler_seed(5)
     b1, b2 = hf.encrypt(x), hi.encrypt(x)

@@ -227,6 +227,46 @@ def test_fp64_ntt_equals_integer_ntt_and_oracle(emu, oracle_mod, bits):
         emu.L.emu_destroy(h)
 
 
+@pytest.mark.parametrize("bits", [14, 33, 45, 51, 52])
+def test_fp64_inverse_ntt_equals_integer_inverse_and_oracle(emu, oracle_mod, bits):
+    """The inverse transform on doubles (decrypt, rescale) against the integer path and the oracle, on the same
+    adversarial rows as the forward one; and forward followed by inverse is the identity."""
+    M = 2 * N
+    qs = [oracle_mod.first_prime(bits, M)]
+    if bits == 52:
+        qs.append(oracle_mod.previous_prime((9 << 49) + 1, M))      # the largest modulus the FP64 path admits
+    rng = np.random.default_rng(100 + bits)
+    for q in qs:
+        psi = oracle_mod.min_root_of_unity(M, q)
+        h = emu.context([q], [psi])
+        half = q // 2
+        rows = [np.full(N, q - 1, np.uint64), np.full(N, half, np.uint64), np.full(N, half + 1, np.uint64),
+                np.where(np.arange(N) % 2 == 0, half, half + 1).astype(np.uint64), np.zeros(N, np.uint64),
+                np.eye(1, N, 5, dtype=np.uint64)[0] * np.uint64(q - 1)]
+        rows += [rng.integers(0, q, N, dtype=np.uint64) for _ in range(5)]
+        o = None
+        for a in rows:
+            f = a.copy(); emu.L.emu_ntt_inverse(h, 0, vp(f))
+            emu.L.emu_set_fp64(h, 0)
+            g = a.copy(); emu.L.emu_ntt_inverse(h, 0, vp(g))
+            emu.L.emu_set_fp64(h, 1)
+            assert np.array_equal(f, g) and int(f.max()) < q
+            back = f.copy(); emu.L.emu_ntt_forward(h, 0, vp(back))
+            assert np.array_equal(back, a)
+        emu.L.emu_destroy(h)
+
+
+def test_fp64_inverse_on_the_fixture_and_deep_contexts(emu, emu_ctx, deep_emu_ctx, oracles, deep_oracles):
+    for name, o in list(oracles.items()) + list(deep_oracles.items()):
+        h = emu_ctx[name] if name in emu_ctx else deep_emu_ctx[name]
+        n = o.ring_dim
+        rng = np.random.default_rng(len(name))
+        for l in range(o.num_limbs):
+            a = rng.integers(0, o.modulus(l), n, dtype=np.uint64)
+            f = a.copy(); emu.L.emu_ntt_inverse(h, l, vp(f))
+            assert np.array_equal(f, o.ntt_inverse(l, a)), (name, l)
+
+
 def test_fp64_path_rejected_above_its_exactness_bound(emu, oracle_mod):
     M = 2 * N
     for bits, want in ((53, 0), (59, 0)):
