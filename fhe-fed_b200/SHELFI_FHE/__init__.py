@@ -137,6 +137,7 @@ def lib() -> C.CDLL:
         "shelfi_unpack_device": (C.c_int, [vp, vp, u64, vp, vp]),
         "shelfi_ntt_forward_device": (C.c_int, [vp, vp, u32, vp]),
         "shelfi_ntt_inverse_device": (C.c_int, [vp, vp, u32, vp]),
+        "shelfi_ntt_forward_shfl_device": (C.c_int, [vp, vp, u32, vp]),
         "shelfi_encode_device": (C.c_int, [vp, vp, u64, vp, vp]),
         "shelfi_decrypt_integer_device": (C.c_int, [vp, vp, u64, vp, vp, vp]),
         "shelfi_decrypt_words_device": (C.c_int, [vp, vp, u64, vp, vp]),

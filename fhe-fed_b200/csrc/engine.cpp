@@ -2562,6 +2562,20 @@ int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, v
     if (h->rc.log_blocks > 0) return scratch_end(h, s);
     return 0;
 }
+// measurement tap: the forward transform with its last stage done by a lane exchange (ring dimension 8192 only)
+int shelfi_ntt_forward_shfl_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    int rcode = check_stage(h, false, false);
+    if (rcode) return rcode;
+    if (h->rc.log_blocks) return fail(h, SHELFI_ERR_UNSUPPORTED, "the lane-exchange variant covers ring dimension 8192");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    timed(h, kKNttForward, s, [&] {
+        launch_ntt_forward_shfl(h->rc, reinterpret_cast<const u64 *>(d_rows), reinterpret_cast<u64 *>(d_rows), rows, s);
+    });
+    CU(cudaGetLastError());
+    return 0;
+}
 int shelfi_ntt_inverse_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream) {
     if (!h) return SHELFI_ERR_ARG;
     std::lock_guard<std::mutex> lock(h->mu);

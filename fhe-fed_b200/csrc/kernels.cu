@@ -167,6 +167,62 @@ __global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_kernel(const __gri
     fwd_phase_e(tid, sm, lc, hb, StoreFullReducePair{dst, &lc});
 }
 
+// EXPERIMENT (north_star: "warp-shuffle butterflies" for the last stages; measured in profiles/README.md, not used by
+// the product): the forward transform with the last FOUR stages in registers.  After the radix-8 pass over address bits
+// 3..1, the partner of every value for the last stage (address bit 0) sits in the neighbouring lane: lanes exchange
+// half of their values (__shfl_xor 1), so each ends up with four complete pairs, does their butterflies and stores them.
+// One shared-memory round trip and one barrier fewer than the five-pass form; in exchange 8 SHFL + 24 SEL per 8 values
+// and 16-byte stores that are 64 bytes apart within a warp instead of contiguous.
+template <class Store>
+__device__ __forceinline__ void fwd_phase_de_shfl(int tid, u64 *smem, const LimbConst &lc, u32 hb, Store st) {
+    char *sm = reinterpret_cast<char *>(smem);
+    const u64 nq = lc.nq, q3 = kBflyGrowth * lc.q;
+    const tw_t *__restrict__ twe = lc.tw + ((size_t)hb << (kLogN - 1));
+#pragma unroll 1
+    for (int r = 0; r < 4; r++) {
+        const u32 vt = tid + kNttThreads * r;
+        const u32 base = tile_base<1>(vt);
+        u64 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a[k] = tile(sm, tile_off<1>(base, k));
+        ct_radix8(a, lc.tw, (hb << 9) + (vt >> 1), nq, q3);
+        if (lc.fwd_mask & (1u << 3)) quick_reduce8(a, lc);
+        const bool odd = vt & 1u;
+        const u32 high = vt >> 1;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const u64 send = odd ? a[j] : a[j + 4];
+            const u64 recv = __shfl_xor_sync(0xffffffffu, send, 1);
+            u64 x = odd ? recv : a[j], y = odd ? a[j + 4] : recv;
+            const u32 p = (high << 3) | (u32)(j + (odd ? 4 : 0));        // pair index = element index >> 1
+            const tw_t w = twe[p];
+            typename Store::Aux aux = st.fetch(p);
+            ct_bfly(x, y, w, nq, q3);
+            st(p, x, y, aux);
+        }
+    }
+}
+__global__ void __launch_bounds__(kNttThreads, 3) ntt_forward_shfl_kernel(const __grid_constant__ RingConst rc, const u64 *in,
+                                                                          u64 *out) {
+    extern __shared__ __align__(16) u64 sm[];
+    const int tid = threadIdx.x;
+    const u32 row = blockIdx.x;
+    const LimbConst lc = rc.limb[row % rc.limbs];
+    const u64 *src = in + ((size_t)row << kLogN);
+    u64 *dst = out + ((size_t)row << kLogN);
+    if (lc.dtw) {   // FP64 limbs keep the regular form (the exchange idea is the same; the integer limb is the slow one)
+        ntt_forward_tile_d(tid, sm, lc, 1u, DLoadGlobal{src, lc.q}, StoreFullReducePair{dst, &lc});
+        return;
+    }
+    fwd_phase_a(tid, sm, lc, 1u, LoadGlobal{src});
+    __syncthreads();
+    fwd_phase_mid<7>(tid, sm, lc, 1u);
+    __syncthreads();
+    fwd_phase_mid<4>(tid, sm, lc, 1u);
+    __syncthreads();
+    fwd_phase_de_shfl(tid, sm, lc, 1u, StoreFullReducePair{dst, &lc});
+}
+
 // Plaintext polynomial of an encoded weight vector -> evaluation form in every limb (EvalMult(ct, plaintext)): the
 // signed coefficients m[ct][N] are shared by the limbs, one CTA per (ciphertext, limb, tile).
 template <int D>
@@ -1002,6 +1058,7 @@ cudaError_t kernels_init() {
 #define OPT_IN_D(k, bytes) OPT_IN(k<0>, bytes) OPT_IN(k<1>, bytes) OPT_IN(k<2>, bytes)
     OPT_IN_D(ntt_forward_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(ntt_inverse_kernel, NTT_SMEM_BYTES)
+    OPT_IN(ntt_forward_shfl_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(encrypt_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(plain_ntt_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(decrypt_intt_kernel, NTT_SMEM_BYTES)
@@ -1037,6 +1094,9 @@ static void launch_tiles(void (*kernel)(KArgs...), unsigned polys, unsigned log_
 void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s) {
     if (!rows) return;
     DISPATCH_D(rc.log_blocks, launch_tiles(ntt_forward_kernel<D>, rows, D, s, rc, in, out))
+}
+void launch_ntt_forward_shfl(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s) {
+    if (rows && rc.log_blocks == 0) ntt_forward_shfl_kernel<<<rows, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, in, out);
 }
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s) {
     if (!rows) return;

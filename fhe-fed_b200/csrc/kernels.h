@@ -12,6 +12,8 @@ cudaError_t kernels_init();  // opt-in shared-memory sizes; call once per device
 // ring dimension 8192 (one tile per polynomial); inverse is in place.
 void launch_ntt_forward(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s);
 void launch_ntt_inverse(const RingConst &rc, u64 *data, u32 rows, cudaStream_t s);
+// experiment: last stage through a lane exchange instead of shared memory (ring dimension 8192; profiles/README.md)
+void launch_ntt_forward_shfl(const RingConst &rc, const u64 *in, u64 *out, u32 rows, cudaStream_t s);
 
 // encode + sample (rings above one tile): x[n] -> m_e0[n_ct][N] (m + e0, signed) and ve[n_ct][N] (pack_ve bytes)
 // `sel` (optional, here and below): selective encryption — chunk element i is x[sel[i]] on the way in and

@@ -319,6 +319,9 @@ int shelfi_selftest_parallel_copy(uint64_t bytes, uint32_t threads, uint32_t rou
  * InverseTransformFromBitReverse semantics, in place */
 int shelfi_ntt_forward_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream);
 int shelfi_ntt_inverse_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream);
+/* measurement tap (not used by the product): the same forward transform with its last stage done by a warp-shuffle lane
+ * exchange instead of a shared-memory pass; ring dimension 8192; bit-identical results */
+int shelfi_ntt_forward_shfl_device(shelfi_ckks *h, uint64_t *d_rows, uint32_t rows, void *stream);
 /* MakeCKKSPackedPlaintext up to the integer coefficients: n doubles -> int64 [n_ct][N] */
 int shelfi_encode_device(shelfi_ckks *h, const double *d_x, uint64_t n, int64_t *d_coeff, void *stream);
 /* Decrypt up to the centred CRT integer of every coefficient (two's complement hi/lo words) */

@@ -60,6 +60,19 @@ def test_ntt_bit_exact(shelfi, gpu_ckks, oracles, rows):
         assert np.array_equal(b[r], o.ntt_inverse(r % 2, a[r])), r
 
 
+def test_lane_exchange_ntt_variant_is_bit_identical(shelfi, gpu_ckks):
+    """The measured-and-rejected variant of the forward transform (last stage by warp shuffle) gives the same words."""
+    h = gpu_ckks["pybind"]
+    rows = 64
+    rng = np.random.default_rng(5)
+    a = np.stack([rng.integers(0, h.modulus(r % 2), N, dtype=np.uint64) for r in range(rows)])
+    a[0] = h.modulus(0) - 1
+    d1, d2 = dev_u64(a), dev_u64(a)
+    check(h, shelfi.lib().shelfi_ntt_forward_device(h.handle, ptr(d1), rows, stream()))
+    check(h, shelfi.lib().shelfi_ntt_forward_shfl_device(h.handle, ptr(d2), rows, stream()))
+    assert torch.equal(d1, d2)
+
+
 @pytest.mark.parametrize("n,scale", [(4096, 1.0), (10000, 100.0), (1, 1.0), (4097, 0.05)])
 def test_encode_bit_exact(shelfi, gpu_ckks, oracles, n, scale):
     h, o = gpu_ckks["code"], oracles["code"]

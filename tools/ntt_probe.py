@@ -24,15 +24,24 @@ for bits in (52, 59):
     h.loadCryptoParams()
     assert h.load_status == 0 and h.num_limbs == 1
     rows = 8140
-    t = torch.randint(0, 2**40, (rows * 8192,), dtype=torch.int64, device="cuda")
+    src = torch.randint(0, 2**bits - 2**(bits - 2), (rows * 8192,), dtype=torch.int64, device="cuda")
     sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    for _ in range(3):
-        L.shelfi_ntt_forward_device(h.handle, C.c_void_p(t.data_ptr()), rows, sp)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(10):
-        L.shelfi_ntt_forward_device(h.handle, C.c_void_p(t.data_ptr()), rows, sp)
-    e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 10
-    print(json.dumps({"bits": bits, "rows": rows, "ms": round(ms, 4), "ns_per_row": round(ms * 1e6 / rows, 1),
-                      "GBps": round(16 * 8192 * rows / ms / 1e6, 1)}), flush=True)
+    out = {}
+    ref = None
+    for name, fn in (("smem_5_pass", L.shelfi_ntt_forward_device), ("lane_exchange_last_stage", L.shelfi_ntt_forward_shfl_device)):
+        t = src.clone()
+        assert fn(h.handle, C.c_void_p(t.data_ptr()), rows, sp) == 0
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = t.clone()
+        assert torch.equal(t, ref), name            # bit-identical results
+        for _ in range(3):
+            fn(h.handle, C.c_void_p(t.data_ptr()), rows, sp)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn(h.handle, C.c_void_p(t.data_ptr()), rows, sp)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        out[name] = {"ms": round(ms, 4), "ns_per_row": round(ms * 1e6 / rows, 1), "GBps": round(16 * 8192 * rows / ms / 1e6, 1)}
+    print(json.dumps({"bits": bits, "rows": rows, "fp64_pipe": bool(bits <= 52), **out}), flush=True)
