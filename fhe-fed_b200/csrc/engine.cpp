@@ -21,6 +21,8 @@
 
 #include <sys/random.h>
 
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges around the reference-facing calls show up in Nsight timelines
+
 #include "kernels.h"
 #include "numtheory.h"
 #include "tables.h"
@@ -29,6 +31,11 @@
 using namespace shelfi;
 
 namespace {
+
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 struct DeviceBuffer {  // grow-only device scratch
     void *p = nullptr;
@@ -841,6 +848,7 @@ int enc_plan(shelfi_ckks *h, const wire::ContextParams &ctx, uint64_t n_ct, cons
 // stream, one D2H.  n_layers == 1 is CKKS::encrypt.  Blob s lands at dst + offsets[s], lens[s] bytes.
 int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_len, uint32_t n_layers, uint8_t *dst,
                  uint64_t cap, uint8_t **alloc_out, uint64_t *offsets, uint64_t *lens, uint64_t *total_len) {
+    NvtxRange nvtx_range("shelfi.encrypt");
     int rcode = check_stage(h, true, false);
     if (rcode) return rcode;
     trim_enc_plans(h);
@@ -993,6 +1001,7 @@ int encrypt_host(shelfi_ckks *h, const double *const *xs, const uint64_t *layer_
 int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens, const float *w, uint32_t k,
               uint32_t n_layers, uint8_t *dst, uint64_t cap, uint8_t **alloc_out, uint64_t *offsets, uint64_t *lens,
               uint64_t *total_len, bool rescale = false) {
+    NvtxRange nvtx_range("shelfi.computeWeightedAverage");
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
     trim_enc_plans(h);
@@ -1169,6 +1178,7 @@ int wavg_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_
 // n_layers == 1 is CKKS::decrypt.
 int decrypt_host(shelfi_ckks *h, const uint8_t *const *blobs, const uint64_t *blob_lens, const uint64_t *dims,
                  uint32_t n_layers, double *out) {
+    NvtxRange nvtx_range("shelfi.decrypt");
     int rcode = check_stage(h, false, true);
     if (rcode) return rcode;
     if (!blobs || !blob_lens || !dims || !out || n_layers == 0) return fail(h, SHELFI_ERR_ARG, "null argument");
@@ -1436,6 +1446,7 @@ int ct_plan(shelfi_ckks *h, const shelfi_ct *c, shelfi_ckks::EncPlan **ep, wire:
 // memory (page-locked: copied by the DMA engine straight from the caller's pages; pageable: staged through the copy
 // threads) or in device memory.  Returns once x has been read; the encryption itself continues on the compute stream.
 int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct **out) {
+    NvtxRange nvtx_range("shelfi.encrypt[resident]");
     int rcode = check_stage(h, true, false);
     if (rcode) return rcode;
     if (!x || !out || n == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument (an empty input is undefined behaviour in the reference, ckks.cpp:66,95)");
@@ -1528,6 +1539,7 @@ int ct_from_blob(shelfi_ckks *h, const uint8_t *blob, uint64_t len, shelfi_ct **
 
 // ckks.cpp:264-320 over resident vectors; the result is a new resident vector
 int ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *w, uint32_t k, int rescale, shelfi_ct **out) {
+    NvtxRange nvtx_range("shelfi.computeWeightedAverage[resident]");
     int rcode = check_stage(h, false, false);
     if (rcode) return rcode;
     if (!cts || !w || !out) return fail(h, SHELFI_ERR_ARG, "null argument");
@@ -1572,6 +1584,7 @@ int ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *w, u
 
 // ckks.cpp:170-213 from a resident vector into host memory (any kind); returns when `out` holds the values
 int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
+    NvtxRange nvtx_range("shelfi.decrypt[resident]");
     int rcode = check_stage(h, false, true);
     if (rcode) return rcode;
     if (!c || c->owner != h || !out) return fail(h, SHELFI_ERR_ARG, "null argument or foreign vector");
