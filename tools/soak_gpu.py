@@ -42,6 +42,8 @@ def main():
         assert o.loadCryptoParams() == 0
         h.loadCryptoParams()
         assert h.load_status == 0, name
+        hr = SHELFI_FHE.CKKS("ckks", batch, bits, d, device=0, resident=True)   # the same calls on resident vectors
+        hr.loadCryptoParams()
         assert (h.ring_dim, h.num_limbs) == (o.ring_dim, o.num_limbs)
         for _ in range(per_ctx):
             k = int(rng.integers(1, 7))
@@ -60,6 +62,17 @@ def main():
             assert avg == o.computeWeightedAverage(blobs, w), (name, "wavg", k, n)
             got = h.decrypt(avg, n)
             assert np.array_equal(got, o.decrypt(avg, n)), (name, "decrypt", k, n)
+            # resident mode: handles from encrypt (float32 / float64 inputs), uploaded blobs and plain bytes mixed
+            hr.set_sampler_seed(seed)
+            enc_r = [hr.encrypt(x) for x in xs]
+            hr.set_sampler_seed(None)
+            assert all(len(a) == len(b) for a, b in zip(enc_r, blobs))
+            mixed = [enc_r[i] if i % 3 == 0 else (hr.to_resident(blobs[i]) if i % 3 == 1 else blobs[i]) for i in range(k)]
+            avg_r = hr.computeWeightedAverage(mixed, w)
+            assert bytes(avg_r) == avg, (name, "resident wavg", k, n)
+            assert bytes(enc_r[-1]) == blobs[-1], (name, "resident encrypt", k, n)
+            assert np.array_equal(hr.decrypt(avg_r, n), got), (name, "resident decrypt", k, n)
+            del enc_r, mixed, avg_r
             expect = sum(np.float64(np.float32(wi)) * x for wi, x in zip(w, xs))
             tol = max(1e-6 * np.abs(expect).max(), 2.0 ** (26 - bits))
             assert np.abs(got - expect).max() <= tol, (name, "plain", k, n, np.abs(got - expect).max(), tol)
