@@ -546,6 +546,17 @@ __global__ void __launch_bounds__(kNttThreads, 3) encrypt_kernel(const __grid_co
 #ifndef SHELFI_FUSED_CTAS_PER_SM
 #define SHELFI_FUSED_CTAS_PER_SM 3
 #endif
+// The CTAs that share an SM should not march through the same limb together: the 60-bit limb's transforms live on the
+// multiplier pipe, the scaling limbs' on the FP64 pipe, and two CTAs on different pipes overlap where two on the same
+// one queue.  blockIdx parity does not tell co-resident CTAs apart (a wave puts blocks b, b + 148, b + 296 on one SM:
+// all of one parity), so every CTA takes a turn number from a counter of the SM it landed on and the odd turns walk
+// the limbs backwards.  The counters only ever grow; their parity is all that is used.
+__device__ unsigned int g_sm_turn[512];
+__device__ __forceinline__ unsigned int sm_turn() {
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    return atomicAdd(&g_sm_turn[smid & 511u], 1u);
+}
 __global__ void __launch_bounds__(kNttThreads, SHELFI_FUSED_CTAS_PER_SM) encrypt_fused_kernel(const __grid_constant__ RingConst rc,
                                                                        const __grid_constant__ EncodeConst ec,
                                                                        const __grid_constant__ SamplerConst sc,
@@ -555,8 +566,10 @@ __global__ void __launch_bounds__(kNttThreads, SHELFI_FUSED_CTAS_PER_SM) encrypt
     cplx *z = reinterpret_cast<cplx *>(sm);
     __shared__ u64 cdf[32];
     __shared__ u32 cdf_hi[32];
+    __shared__ u32 turn;
     __shared__ __align__(16) uint8_t ve[kN];
     const int tid = threadIdx.x;
+    if (tid == 0) turn = sm_turn();
     const u32 learner = blockIdx.x / eb.n_ct;
     const u64 ct = blockIdx.x % eb.n_ct;
     const double *x = eb.x[learner];
@@ -569,15 +582,14 @@ __global__ void __launch_bounds__(kNttThreads, SHELFI_FUSED_CTAS_PER_SM) encrypt
     const u64 first = ct * ec.batch;
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
     const u32 L = rc.limbs;
-    // odd CTAs walk the limbs backwards: co-resident CTAs then tend to sit on different pipes (the 60-bit limb on the
-    // integer pipe, the scaling limbs on the FP64 pipe) instead of marching through the same limb together
-    const u32 flip = (blockIdx.x & 1u) ? L - 1 : 0u;
-    const u32 l_last = flip ? 0u : L - 1;
-    i64 *m_row = reinterpret_cast<i64 *>(ct_out + ((ct * 2 + 0) * L + l_last) * (u64)kN);
     const u64 keep = make_keep_policy();
     sample_ternary_phase(tid, kNttThreads, eb.key[learner], ct_index, kN, ve);   // touches only `ve`
     encode_load(tid, kNttThreads, z, ec, eb.sel ? x : chunk_ptr(x, first, eb.f32), n_valid, eb.sel ? eb.sel + first : nullptr, eb.f32);
     __syncthreads();
+    // odd turns on this SM walk the limbs backwards (see sm_turn)
+    const u32 flip = (turn & 1u) ? L - 1 : 0u;
+    const u32 l_last = flip ? 0u : L - 1;
+    i64 *m_row = reinterpret_cast<i64 *>(ct_out + ((ct * 2 + 0) * L + l_last) * (u64)kN);
     if (ec.slots == kFftFast) {
         fft_inv_pass8<9>(tid, z, ec.tw_inv); __syncthreads();
         fft_inv_pass8<6>(tid, z, ec.tw_inv); __syncthreads();
