@@ -490,8 +490,9 @@ def run_ours(args):
                 "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes": algo_bytes, "peak_source": "measured" if peaks else "fallback",
                 "ms_per_launch": enc_ms, "share_of_step": enc["ms_total"] / ms if ms > 0 else None,
                 "note": "not HBM-limited: FFT + sampler + 3 NTTs per limb run in shared memory per 72 algorithmic bytes/param; "
-                        "ncu: fmaheavy 47 %, alu 37 %, fp64 26 %, issue slots 55 % (instruction-issue/latency bound); "
-                        "DESIGN.md 4.1 and 8, profiles/README.md"}
+                        "ncu (profiles/r02_ncu_step.md): fmaheavy 52 %, alu 35 %, fp64 23 %, issue slots 57 %, DRAM 6 %; the instruction "
+                        "classes share one issue port per SMSP (tools/ubench/pipes.cu), so the kernel is bound by its "
+                        "instruction count; DESIGN.md 4.1 and 8, profiles/README.md"}
     path_gbs = bytes_per_param(K, LIMBS) * P_MODEL * args.steps / (ms / 1e3) / 1e9
     # the reference's own convention (code/benchmark.py:497,544): encryption is per-client work done in parallel by
     # the clients, so its time counts once, not K times: P / (T_enc_all / K + T_wavg + T_dec)   

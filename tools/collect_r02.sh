@@ -9,7 +9,7 @@ python bench.py > gpurun_out/r02_bench.json 2>> gpurun_out/bench.err
 python tools/latency_probe2.py > gpurun_out/r02_latency.jsonl 2>> gpurun_out/bench.err
 (python tools/bench_configs.py --configs 3,4 --shards 8; python tools/bench_configs.py --configs 3 --shards 1) > gpurun_out/r02_bench_configs.jsonl 2>> gpurun_out/bench.err
 B="python bench.py --steps 2 --warmup 3 --no-cpu --no-strong"
-$B > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches.csv $B > gpurun_out/ncu_l.log 2>&1
+$B > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches_bench.csv $B > gpurun_out/ncu_lb.log 2>&1
 bash tools/profile_r02.sh r02 > gpurun_out/profile_r02.log 2>&1
 python - <<'PY'
 import csv, glob, json
