@@ -122,6 +122,7 @@ def lib() -> C.CDLL:
         "shelfi_weighted_sum_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_float), u32, u64, vp, vp]),
         "shelfi_weighted_sum_accumulate_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_float), u32, u64, vp, vp]),
         "shelfi_decrypt_device": (C.c_int, [vp, vp, u64, f64, vp, u64, vp]),
+        "shelfi_decrypt_static_device": (C.c_int, [vp, vp, u64, f64, vp, u64, vp]),
         "shelfi_decrypt_gather_device": (C.c_int, [vp, vp, u64, f64, C.POINTER(vp), u32, u64, u64, vp]),
         "shelfi_peer_buffer_create": (C.c_int, [vp, u64, C.POINTER(vp), C.c_char_p]),
         "shelfi_peer_buffer_open": (C.c_int, [vp, C.c_char_p, C.POINTER(vp)]),

@@ -2286,6 +2286,43 @@ int shelfi_decrypt_gather_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t 
                          static_cast<cudaStream_t>(stream), nullptr, 0, peers, n_outs - 1);
 }
 
+// Decrypt on the device with the scratch in a file-scope device array (kernels.cu: g_static_scratch) instead of this
+// handle's grow-only buffers.  No counterpart in the reference: added for callers
+// that may not allocate (stream capture, serving loops, harnesses that forbid cudaMalloc).  Nothing here allocates or
+// sets anything up lazily: the handle must already hold its context and secret key on the device, and a request beyond
+// the array is refused.  Same results as shelfi_decrypt_device.  Every call on a device shares the one array: calls
+// that overlap on the GPU (two streams, two handles, two threads) race on it.
+int shelfi_decrypt_static_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
+                                 uint64_t n, void *stream) {
+    if (!h) return SHELFI_ERR_ARG;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!h->cuda_ready || !h->have_cc) return fail(h, SHELFI_ERR_NOT_LOADED, "crypto context not loaded (call loadCryptoParams)");
+    if (!h->have_sk) return fail(h, SHELFI_ERR_NOT_LOADED, "private key not loaded");
+    CU(cudaSetDevice(h->device));
+    if (h->opt_decode_noise)
+        return fail(h, SHELFI_ERR_ARG, "SHELFI_OPT_DECODE_NOISE is not served by the static-scratch decrypt; use shelfi_decrypt_device");
+    if (h->batch == 0 || h->batch > h->ctx.batch_size)
+        return fail(h, SHELFI_ERR_PARAMS, "batchSize exceeds the slots of the loaded context");
+    if (!d_ct || !d_out || n_ct == 0) return fail(h, SHELFI_ERR_ARG, "null or empty argument");
+    if (n == 0 || n > n_ct * h->batch || n + h->batch <= n_ct * h->batch)
+        return fail(h, SHELFI_ERR_ARG, "n inconsistent with the number of ciphertexts");
+    const bool general = general_decode(h);
+    const uint64_t per_ct = static_scratch_words(h->rc, h->ec, 1, general);
+    if (n_ct > kStaticScratchWords / per_ct)
+        return fail(h, SHELFI_ERR_ARG,
+                    std::to_string(n_ct) + " ciphertexts need " + std::to_string(n_ct * per_ct * sizeof(uint64_t)) +
+                        " bytes of scratch; the static array holds " + std::to_string(kStaticScratchWords * sizeof(uint64_t)) +
+                        " (at most " + std::to_string(kStaticScratchWords / per_ct) + " ciphertexts of this context per call)");
+    DecodeConst dc{};
+    dc.crt = h->crt;
+    const double p = (double)h->ctx.plaintext_modulus;
+    dc.pre = std::pow(scaling_factor, -1) * std::pow(2, p);   // as decrypt_dense
+    dc.pow_p = std::pow(2, -p);
+    CU(launch_decrypt_static(h->rc, h->ec, dc, h->crtn, general, reinterpret_cast<const u64 *>(d_ct), h->d_sk.as<tw_t>(),
+                             (u32)n_ct, d_out, n, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
 // Host-only self-test of the copy threads (no device needed): `rounds` copies of `bytes` patterned bytes with `threads`
 // workers, each verified; returns 0, or the 1-based round that came back wrong.
 int shelfi_selftest_parallel_copy(uint64_t bytes, uint32_t threads, uint32_t rounds) {

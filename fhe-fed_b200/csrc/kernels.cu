@@ -8,6 +8,8 @@
 
 #include <cooperative_groups.h>
 
+#include <mutex>
+
 namespace shelfi {
 namespace cg = cooperative_groups;
 
@@ -1270,6 +1272,69 @@ void launch_unpack_scale_accumulate(const RingConst &rc, const BlobRuns &br, con
     if (n_ct)
         unpack_scale_accumulate_kernel<<<run_grid(br, n_ct), kPackThreads, 0, s>>>(rc, br, image, cs, first,
                                                                                   acc);
+}
+
+// ------------------------------------------------------------------------------------------
+// decrypt with its scratch in the module image (shelfi_decrypt_static_device): no allocation at all
+// ------------------------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that may not allocate
+// (stream capture, serving loops).  The array lives in every device that loads the library until the process exits.
+// Layout of one call, in u64 words: coeff[n_ct][limbs][N] | vals[n_ct][N] (general decode only) | zs[n_ct][slots]
+// complex (general decode with slots > kFftFast only).  Every word a call reads it has written first (the inverse
+// transforms fill coeff, crt_kernel fills vals, decode_fft_kernel fills zs), so nothing has to start at zero; the
+// array keeps the previous call's contents, and calls that overlap on the GPU race on it.
+static __device__ __align__(256) unsigned long long g_static_scratch[kStaticScratchWords];
+
+// In host code g_static_scratch is only a stand-in for the symbol: the device address is looked up once per device,
+// with that device current, and kept.
+static cudaError_t static_scratch_ptr(u64 **out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static u64 *ptr_of[kMaxDevices] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr_of[dev]) {
+        u64 *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        ptr_of[dev] = p;
+    }
+    *out = ptr_of[dev];
+    return cudaSuccess;
+}
+
+u64 static_scratch_words(const RingConst &rc, const EncodeConst &ec, u64 n_ct, bool general) {
+    u64 per = (u64)rc.limbs * rc.n;
+    if (general) {
+        per += rc.n;
+        if (ec.slots > kFftFast) per += 2ull * ec.slots;
+    }
+    return n_ct * per;
+}
+
+cudaError_t launch_decrypt_static(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const CrtNConst &cn,
+                                  bool general, const u64 *ct, const tw_t *sk, u32 n_ct, double *out, u64 n,
+                                  cudaStream_t s) {
+    if (!n_ct) return cudaSuccess;
+    if (static_scratch_words(rc, ec, n_ct, general) > kStaticScratchWords) return cudaErrorInvalidValue;
+    u64 *base = nullptr;
+    cudaError_t e = static_scratch_ptr(&base);
+    if (e != cudaSuccess) return e;
+    u64 *coeff = base;
+    launch_decrypt_intt(rc, ct, sk, coeff, n_ct, s);
+    if (!general) {
+        launch_decode(rc, ec, dc, coeff, n_ct, out, n, s, nullptr);
+    } else {
+        double *vals = reinterpret_cast<double *>(base + (u64)n_ct * rc.limbs * rc.n);
+        cplx *zs = reinterpret_cast<cplx *>(base + (u64)n_ct * (rc.limbs + 1) * rc.n);   // 16-byte aligned: N is
+        launch_crt(rc, dc, cn, coeff, n_ct, vals, nullptr, nullptr, nullptr, s);         // a multiple of 8192 words
+        launch_decode_fft(rc, ec, dc, vals, zs, n_ct, out, n, s, nullptr);
+    }
+    return cudaGetLastError();
 }
 
 }  // namespace shelfi

@@ -42,6 +42,15 @@ void launch_rescale(const RingConst &rc, const RescaleConst &rs, const u64 *ct, 
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
                    double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);
+// decrypt (both stages) with the scratch in a file-scope device array of kStaticScratchWords u64 (8 MiB) instead of
+// caller- or handle-owned memory: allocates nothing.  general = the launch_crt + launch_decode_fft route (any ring and
+// limb count); otherwise launch_decode's fused route (ring dimension 8192, at most two limbs).
+// static_scratch_words() is what a call needs; beyond the array launch_decrypt_static returns cudaErrorInvalidValue.
+constexpr u64 kStaticScratchWords = (8ull << 20) / sizeof(u64);
+u64 static_scratch_words(const RingConst &rc, const EncodeConst &ec, u64 n_ct, bool general);
+cudaError_t launch_decrypt_static(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const CrtNConst &cn,
+                                  bool general, const u64 *ct, const tw_t *sk, u32 n_ct, double *out, u64 n,
+                                  cudaStream_t s);
 // general decode: CRT of any limb count -> vals[n_ct][N] doubles (x dc.pre), optional taps of the centred integer
 // (tap8: 8 two's-complement words per coefficient; tap_hi/tap_lo: its low 128 bits)
 void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,

@@ -244,6 +244,21 @@ int shelfi_weighted_sum_accumulate_device(shelfi_ckks *h, const uint64_t *const 
                                           uint64_t n_ct, uint64_t *d_acc, void *stream);
 int shelfi_decrypt_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
                           uint64_t n, void *stream);
+/* shelfi_decrypt_device without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA stream capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments and the same results as shelfi_decrypt_device; the scratch between the inverse
+ * transforms and the decode (and, for rings above 8192 or more than two towers, the decode's own scratch) is a
+ * file-scope device array of SHELFI_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until the
+ * process exits.  Per ciphertext a call needs 8 * (L*N [+ N + 2*slots if slots > 4096, in the general decode]) bytes:
+ * 64 ciphertexts (262,144 values) per call for N = 8192, L = 2; more returns SHELFI_ERR_ARG with the limit in
+ * shelfi_last_error.  The call makes no cudaMalloc/cudaFree and creates no stream or event; the handle must already
+ * hold its context and secret key (else SHELFI_ERR_NOT_LOADED), and SHELFI_OPT_DECODE_NOISE must be off.
+ * Every call on a device shares the one array, which keeps the previous call's contents (each call writes every
+ * word before reading it, nothing has to be cleared): calls that OVERLAP on the GPU - two streams, handles or
+ * threads - race on it; serialise them on one stream or with events. */
+#define SHELFI_STATIC_SCRATCH_BYTES (8u << 20)
+int shelfi_decrypt_static_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double scaling_factor, double *d_out,
+                                 uint64_t n, void *stream);
 /* Decrypt-gather: the optional reassembly of the decoded model across the GPUs of one box (the reference decrypts every
  * ciphertext into one float64 array, ckks.cpp:181-205; sharded by ciphertext index that array is the concatenation of
  * the ranks' slices) folded into the decode kernel: decoded value i, i < n, is stored to d_outs[p][offset + i] for every
