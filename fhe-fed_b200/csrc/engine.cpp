@@ -55,7 +55,7 @@ struct DeviceBuffer {  // grow-only device scratch
 
 // Optional per-kernel timing: CUDA events recorded on the launching stream around each launch.
 enum KernelId { kKEncodeSample, kKEncrypt, kKWeightedSum, kKDecryptIntt, kKDecode, kKPack, kKUnpack,
-                kKUnpackScaleAcc, kKNttForward, kKNttInverse, kKRescale, kKernelCount };
+                kKUnpackScaleAcc, kKNttForward, kKNttInverse, kKRescale, kKCopyIn, kKCopyOut, kKernelCount };
 struct Profiler {
     bool on = false;
     struct Rec { int id; cudaEvent_t a, b; };
@@ -69,12 +69,18 @@ struct Profiler {
         cudaEventCreate(&e);
         return e;
     }
+    // SHELFI_TIMELINE=1: every drain also prints where each recorded launch / copy began and ended on the device
+    // clock, relative to the first record of the batch (there is no nsys on the GPU boxes): one JSON line per record
+    bool timeline = std::getenv("SHELFI_TIMELINE") != nullptr;
     void drain() {
         for (auto &r : pending) {
             float ms = 0;
             if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
                 total_ms[r.id] += ms;
                 launches[r.id]++;
+                float t0 = 0;
+                if (timeline && cudaEventElapsedTime(&t0, pending[0].a, r.a) == cudaSuccess)
+                    std::fprintf(stderr, "{\"timeline\": %d, \"t0_ms\": %.4f, \"t1_ms\": %.4f}\n", r.id, t0, t0 + ms);
             }
             spare.push_back(r.a); spare.push_back(r.b);
         }
@@ -215,7 +221,7 @@ struct DevicePool {
     }
 };
 
-constexpr int kEncStreams = 4;   // resident encrypt calls rotate over this many streams (and input slots)
+constexpr int kEncStreams = 8;   // resident encrypt calls rotate over this many streams (and input slots)
 
 }  // namespace
 
@@ -230,6 +236,11 @@ struct shelfi_ct {
     // on the compute stream (or the free) makes that stream wait for it
     cudaEvent_t ready = nullptr;
     bool ready_pending = false;
+    // a large weighted average is written on the compute stream in kCtParts groups of ciphertexts (group g =
+    // [n_ct g / kCtParts, n_ct (g + 1) / kCtParts)); part_ev[g] is recorded after group g, so that decrypt can start on
+    // the first group (and its values cross PCIe) while the later ones are still being summed
+    cudaEvent_t part_ev[8] = {nullptr};
+    uint32_t parts = 0;
     uint64_t n_ct = 0;
     uint32_t limbs = 0;
     wire::ContextParams ctx;
@@ -290,6 +301,8 @@ struct shelfi_ckks {
     // config 2) and small vectors (3 CTAs per call in the pythonApi example) run side by side.  Everything else that
     // touches a vector runs on the compute stream `stream`.
     cudaStream_t enc_streams[kEncStreams] = {nullptr};
+    bool opt_unfused_decrypt = std::getenv("SHELFI_DECRYPT_UNFUSED") != nullptr;   // A/B switch: two launches as in round 1
+    cudaEvent_t ev_fork = nullptr, ev_part_done[kEncStreams] = {nullptr};   // ct_decrypt: groups on the side streams
     DeviceBuffer r_x[kEncStreams], r_out;
     cudaEvent_t ev_x_in[kEncStreams] = {nullptr}, ev_x_free[kEncStreams] = {nullptr}, ev_r_out = nullptr;
     bool x_busy[kEncStreams] = {false};
@@ -718,15 +731,38 @@ LevelView level_view(const shelfi_ckks *h, uint32_t limbs) {
 // limbs = towers per polynomial of d_ct (0 = the context's chain, i.e. level 0)
 // peers[0..n_peer): further destinations of every decoded value (decrypt-gather), already offset to this rank's slice
 // ct_index0: index of d_ct[0] within the vector the caller decrypts (names the decode-noise stream of each ciphertext)
+// slice: null = the handle's scratch from its start, handed over between streams here; else the caller has reserved
+//        the three buffers for `slice->of` ciphertexts, done the hand-over, and this launch works at ciphertext
+//        `slice->at` of them (several launches on different streams then share the scratch without touching)
+struct ScratchSlice { uint64_t at, of; };
+constexpr uint64_t kFusedDecryptMinCts = 256;
+int decrypt_scratch_reserve(shelfi_ckks *h, uint64_t n_ct, uint32_t limbs) {
+    const uint64_t N = h->ctx.ring_dim;
+    CU(h->s_coeff.reserve(n_ct * limbs * N * sizeof(uint64_t)));
+    if (general_decode(h, limbs) || h->opt_decode_noise) {
+        CU(h->s_vals.reserve(n_ct * N * sizeof(double)));
+        if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(n_ct * (size_t)h->ec.slots * sizeof(cplx)));
+    }
+    return 0;
+}
 int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf, double *d_out, uint64_t n,
                   cudaStream_t s, const uint32_t *d_sel = nullptr, uint32_t limbs = 0, double *const *peers = nullptr,
-                  uint32_t n_peer = 0, uint64_t ct_index0 = 0) {
+                  uint32_t n_peer = 0, uint64_t ct_index0 = 0, const ScratchSlice *slice = nullptr) {
     const uint64_t N = h->ctx.ring_dim;
     const LevelView lv = level_view(h, limbs);
-    int src = scratch_begin(h, s);
-    if (src) return src;
-    CU(h->s_coeff.reserve(n_ct * lv.rc.limbs * N * sizeof(uint64_t)));
-    timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(lv.rc, d_ct, h->d_sk.as<tw_t>(), h->s_coeff.as<u64>(), (u32)n_ct, s); });
+    int src;
+    if (!slice) {
+        if ((src = scratch_begin(h, s))) return src;
+        if ((src = decrypt_scratch_reserve(h, n_ct, lv.rc.limbs))) return src;
+    }
+    const uint64_t at = slice ? slice->at : 0;
+    u64 *coeff = h->s_coeff.as<u64>() + at * lv.rc.limbs * N;
+    // one launch for both stages from kFusedDecryptMinCts ciphertexts; below that (the groups of a pipelined call,
+    // small vectors) a launch is less than a wave and two kernels with one CTA per limb / ciphertext finish sooner
+    const bool fused = !general_decode(h, lv.rc.limbs) && !h->opt_decode_noise && !h->opt_unfused_decrypt &&
+                       n_ct >= kFusedDecryptMinCts;
+    if (!fused)
+        timed(h, kKDecryptIntt, s, [&] { launch_decrypt_intt(lv.rc, d_ct, h->d_sk.as<tw_t>(), coeff, (u32)n_ct, s); });
     DecodeConst dc{};
     dc.crt = lv.crt;
     double p = (double)h->ctx.plaintext_modulus;
@@ -734,22 +770,24 @@ int decrypt_dense(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n_ct, double sf
     dc.pow_p = std::pow(2, -p);
     for (uint32_t i = 0; i < n_peer; i++) dc.peer[i] = peers[i];
     dc.n_peer = n_peer;
-    if (!general_decode(h, lv.rc.limbs) && !h->opt_decode_noise) {
-        timed(h, kKDecode, s, [&] { launch_decode(lv.rc, h->ec, dc, h->s_coeff.as<u64>(), (u32)n_ct, d_out, n, s, d_sel); });
+    if (fused) {   // ring dimension 8192, at most two limbs: one launch (timed as the inverse-transform stage)
+        timed(h, kKDecryptIntt, s, [&] {
+            launch_decrypt_fused(lv.rc, h->ec, dc, d_ct, h->d_sk.as<tw_t>(), coeff, (u32)n_ct, d_out, n, s, d_sel);
+        });
+    } else if (!general_decode(h, lv.rc.limbs) && !h->opt_decode_noise) {
+        timed(h, kKDecode, s, [&] { launch_decode(lv.rc, h->ec, dc, coeff, (u32)n_ct, d_out, n, s, d_sel); });
     } else {
-        CU(h->s_vals.reserve(n_ct * N * sizeof(double)));
-        if (h->ec.slots > kFftFast) CU(h->s_zs.reserve(n_ct * (size_t)h->ec.slots * sizeof(cplx)));
+        double *vals = h->s_vals.as<double>() + at * N;
+        cplx *zs = h->s_zs.as<cplx>() ? h->s_zs.as<cplx>() + at * (size_t)h->ec.slots : nullptr;
         timed(h, kKDecode, s, [&] {
-            launch_crt(lv.rc, dc, lv.crtn, h->s_coeff.as<u64>(), (u32)n_ct, h->s_vals.as<double>(), nullptr, nullptr,
-                       nullptr, s);
+            launch_crt(lv.rc, dc, lv.crtn, coeff, (u32)n_ct, vals, nullptr, nullptr, nullptr, s);
             if (h->opt_decode_noise)   // [PAL] Decode adds its noise at scale 2^p, before FFTSpecial
-                launch_decode_noise(lv.rc, h->ec, h->noise_key, ct_index0, h->s_vals.as<double>(), (u32)n_ct, s);
-            launch_decode_fft(lv.rc, h->ec, dc, h->s_vals.as<double>(), h->s_zs.as<cplx>(), (u32)n_ct, d_out, n, s,
-                              d_sel);
+                launch_decode_noise(lv.rc, h->ec, h->noise_key, ct_index0, vals, (u32)n_ct, s);
+            launch_decode_fft(lv.rc, h->ec, dc, vals, zs, (u32)n_ct, d_out, n, s, d_sel);
         });
     }
     CU(cudaGetLastError());
-    return scratch_end(h, s);
+    return slice ? 0 : scratch_end(h, s);
 }
 
 // [PAL] ModReduce under EXACTRESCALE (DCRTPoly::DropLastElementAndScale) on a dense batch:
@@ -803,6 +841,14 @@ constexpr uint64_t kDeviceHeaderMinCts = 32;   // from here on the bookkeeping b
 const wire::BlobPlan &plan_of(const LayerSlot &l) { return l.ep ? l.ep->plan : l.plan; }
 uint64_t align8(uint64_t v) { return (v + 7) & ~(uint64_t)7; }
 constexpr uint64_t kPipelineMinCts = 128;   // below this a call is launch latency, not copy time
+constexpr uint32_t kCtParts = 8;            // most parts of a shelfi_ct (part_ev); at most kEncStreams
+static_assert(kCtParts <= (uint32_t)kEncStreams, "one side stream per part");
+// parts of a weighted average / groups of a pipelined decrypt for a vector of n_ct ciphertexts (both sides must agree)
+uint32_t part_count(uint64_t n_ct) {
+    static const int forced = std::getenv("SHELFI_PARTS") ? std::atoi(std::getenv("SHELFI_PARTS")) : 0;
+    if (forced == 4 || forced == 8) return (uint32_t)forced;
+    return n_ct >= 2 * kPipelineMinCts ? 8 : 4;
+}
 
 // Called where a reference-facing call starts (everything queued by earlier calls has completed by then).
 void trim_enc_plans(shelfi_ckks *h) {
@@ -1376,6 +1422,8 @@ int ensure_resident(shelfi_ckks *h) {
         h->pool.limit = free_b - free_b / 5;   // 80 % of what is free now; shelfi_resident_set_limit changes it
         if (const char *e = std::getenv("SHELFI_RESIDENT_LIMIT_MB")) h->pool.limit = (size_t)std::max(1, std::atoi(e)) << 20;
     }
+    CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    for (int i = 0; i < kEncStreams; i++) CU(cudaEventCreateWithFlags(&h->ev_part_done[i], cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&h->ev_r_out, cudaEventDisableTiming));
     return 0;
 }
@@ -1427,6 +1475,8 @@ void drop_ct(shelfi_ckks *h, shelfi_ct *c) {
         h->pool.give(PoolBuf{c->d, c->buf_ev}, c->cap);
     }
     if (c->ready) h->spare_events.push_back(c->ready);
+    for (cudaEvent_t e : c->part_ev)
+        if (e) h->spare_events.push_back(e);
     delete c;
 }
 bool is_device_ptr(const void *p) {
@@ -1480,7 +1530,8 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
             CUB(cudaStreamSynchronize(st));
             CUB(h->r_x[b].reserve(in_bytes));
         }
-        if ((rcode = h2d(h, h->r_x[b].p, x, in_bytes, cs))) return bail(rcode);
+        timed(h, kKCopyIn, cs, [&] { rcode = h2d(h, h->r_x[b].p, x, in_bytes, cs); });
+        if (rcode) return bail(rcode);
         CUB(cudaEventRecord(h->ev_x_in[b], cs));
         CUB(cudaStreamWaitEvent(st, h->ev_x_in[b], 0));
         d_x = h->r_x[b].p;
@@ -1568,6 +1619,24 @@ int ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *w, u
         ct_ready(h, cts[i]);
         ptrs[i] = cts[i]->d;
     }
+    // a large result that is not rescaled: in kCtParts launches with an event after each (see shelfi_ct::part_ev)
+    bool in_parts = !rescale && n_ct >= kPipelineMinCts;
+    const uint32_t n_parts = part_count(n_ct);
+    for (uint32_t g = 0; in_parts && g < n_parts; g++)
+        if (!(acc->part_ev[g] = take_event(h))) in_parts = false;
+    if (in_parts) {
+        const uint64_t words = 2ull * L * h->ctx.ring_dim;
+        std::vector<const uint64_t *> part(k);
+        for (uint32_t g = 0; g < n_parts; g++) {
+            const uint64_t c0 = n_ct * g / n_parts, c1 = n_ct * (g + 1) / n_parts;
+            for (uint32_t i = 0; i < k; i++) part[i] = ptrs[i] + c0 * words;
+            if ((rcode = weighted_sum_dense(h, part.data(), w, k, c1 - c0, acc->d + c0 * words, false, st))) { drop_ct(h, acc); return rcode; }
+            if (cudaEventRecord(acc->part_ev[g], st) != cudaSuccess) { drop_ct(h, acc); return cuda_fail(h, cudaGetLastError(), "cudaEventRecord"); }
+        }
+        acc->parts = n_parts;
+        *out = acc;
+        return 0;
+    }
     if ((rcode = weighted_sum_dense(h, ptrs.data(), w, k, n_ct, acc->d, false, st))) { drop_ct(h, acc); return rcode; }
     if (rescale) {
         shelfi_ct *red = nullptr;
@@ -1597,6 +1666,7 @@ int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
     const uint64_t words = 2ull * c->limbs * h->ctx.ring_dim;
     auto bail = [&](int code) {
         cudaStreamSynchronize(st);
+        for (cudaStream_t e : h->enc_streams) cudaStreamSynchronize(e);
         cudaStreamSynchronize(ds);
         return code;
     };
@@ -1610,18 +1680,41 @@ int ct_decrypt(shelfi_ckks *h, const shelfi_ct *c, uint64_t n, double *out) {
     const bool one_scale = c->meta.size() == 1;
     const bool pinned = is_pinned(out);
     // a large vector into page-locked memory: groups are decrypted while the group before crosses PCIe
-    const uint32_t groups = (one_scale && pinned && n_ct >= kPipelineMinCts) ? 4 : 1;
+    const uint32_t groups = (one_scale && pinned && n_ct >= kPipelineMinCts) ? part_count(n_ct) : 1;
     if (groups > 1) {
+        // The groups run on side streams, side by side, each in its own slice of the scratch: a quarter of the vector
+        // is less than one wave of CTAs, so four launches in a row would take four kernel latencies.  A vector written
+        // in parts (the weighted average just queued) releases group g as soon as ITS part is there, under the sums of
+        // the later parts.  The call ends with every side stream drained (the copy stream waits for each and is
+        // synchronised) and the compute stream ordered after them, so nothing outlives the call.
+        const bool by_part = c->parts == groups;
+        if ((rcode = decrypt_scratch_reserve(h, n_ct, c->limbs))) return bail(rcode);
+        if (!h->ev_scratch) CUB(cudaEventCreateWithFlags(&h->ev_scratch, cudaEventDisableTiming));
+        if (!by_part) CUB(cudaEventRecord(h->ev_fork, st));
+        for (uint32_t g = 0; g < groups; g++) {
+            cudaStream_t gs = h->enc_streams[g];
+            CUB(cudaStreamWaitEvent(gs, by_part ? c->part_ev[g] : h->ev_fork, 0));
+            CUB(cudaStreamWaitEvent(gs, h->ev_r_out, 0));
+            if (h->scratch_used && h->scratch_stream != gs) CUB(cudaStreamWaitEvent(gs, h->ev_scratch, 0));
+        }
         for (uint32_t g = 0; g < groups; g++) {
             const uint64_t c0 = n_ct * g / groups, c1 = n_ct * (g + 1) / groups;
             const uint64_t first = c0 * batch, last = std::min(n, c1 * batch);
-            if ((rcode = decrypt_dense(h, c->d + c0 * words, c1 - c0, sf_of(0), d_out + first, last - first, st, nullptr, c->limbs,
-                                       nullptr, 0, c0)))
+            cudaStream_t gs = h->enc_streams[g];
+            const ScratchSlice slice{c0, n_ct};
+            if ((rcode = decrypt_dense(h, c->d + c0 * words, c1 - c0, sf_of(0), d_out + first, last - first, gs, nullptr, c->limbs,
+                                       nullptr, 0, c0, &slice)))
                 return bail(rcode);
-            CUB(cudaEventRecord(h->ev_stage_out, st));
-            CUB(cudaStreamWaitEvent(ds, h->ev_stage_out, 0));
-            CUB(cudaMemcpyAsync(out + first, d_out + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost, ds));
+            CUB(cudaEventRecord(h->ev_part_done[g], gs));
+            CUB(cudaStreamWaitEvent(ds, h->ev_part_done[g], 0));
+            CUB(cudaStreamWaitEvent(st, h->ev_part_done[g], 0));
+            cudaError_t ce = cudaSuccess;
+            timed(h, kKCopyOut, ds, [&] {
+                ce = cudaMemcpyAsync(out + first, d_out + first, (last - first) * sizeof(double), cudaMemcpyDeviceToHost, ds);
+            });
+            CUB(ce);
         }
+        if ((rcode = scratch_end(h, st))) return bail(rcode);   // the compute stream now follows every user of the scratch
         CUB(cudaEventRecord(h->ev_r_out, ds));
         CUB(cudaStreamSynchronize(ds));
         return 0;
@@ -1718,7 +1811,9 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
             if (h->ev_x_in[i]) cudaEventDestroy(h->ev_x_in[i]);
             if (h->ev_x_free[i]) cudaEventDestroy(h->ev_x_free[i]);
             if (h->enc_streams[i]) cudaStreamDestroy(h->enc_streams[i]);
+            if (h->ev_part_done[i]) cudaEventDestroy(h->ev_part_done[i]);
         }
+        if (h->ev_fork) cudaEventDestroy(h->ev_fork);
         h->r_out.release();
         if (h->ev_r_out) cudaEventDestroy(h->ev_r_out);
         if (h->ev_scratch) cudaEventDestroy(h->ev_scratch);

@@ -754,6 +754,46 @@ __global__ void __launch_bounds__(kFftThreads) decode_kernel(const __grid_consta
     decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr, first);
 }
 
+// Both stages in one launch (ring dimension 8192, at most two limbs): the CTA of a ciphertext runs the inverse
+// transforms of its limbs one after the other in the tile, leaves the coefficients in `coeff` (they stay in L2) and
+// decodes them in the same tile.  Same phases as decrypt_intt_kernel<0> + decode_kernel, hence the same doubles; one
+// launch latency instead of two, and the FFT phases of one CTA run under the transforms of its neighbours.
+__global__ void __launch_bounds__(kNttThreads, 3) decrypt_fused_kernel(const __grid_constant__ RingConst rc,
+                                                                       const __grid_constant__ EncodeConst ec,
+                                                                       const __grid_constant__ DecodeConst dc,
+                                                                       const u64 *ct_in, const tw_t *sk, u64 *coeff,
+                                                                       double *out, u64 n, const u32 *sel) {
+    extern __shared__ __align__(16) u64 sm[];
+    const int tid = threadIdx.x;
+    const u64 ct = blockIdx.x;
+    const u32 L = rc.limbs;
+    for (u32 l = 0; l < L; l++) {
+        const LimbConst lc = rc.limb[l];
+        const u64 *c0 = ct_in + ((ct * 2 + 0) * L + l) * (u64)kN;
+        const u64 *c1 = ct_in + ((ct * 2 + 1) * L + l) * (u64)kN;
+        intt_tile<0>(tid, sm, lc, 1u, LoadDecryptPair{c0, c1, sk + (size_t)l * kN, lc.q}, coeff + (ct * L + l) * (u64)kN);
+        __syncthreads();   // the tile is free again, and this CTA's coefficient stores are visible to all its threads
+    }
+    cplx *z = reinterpret_cast<cplx *>(sm);
+    decode_load(tid, kFftThreads, z, ec, dc, L, coeff + ct * L * (u64)kN, nullptr, nullptr);
+    __syncthreads();
+    if (ec.slots == kFftFast) {
+        fft_fwd_pass8<0>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<3>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<6>(tid, z, ec.tw_fwd); __syncthreads();
+        fft_fwd_pass8<9>(tid, z, ec.tw_fwd); __syncthreads();
+    } else {
+        for (u32 len = 2; len <= ec.slots; len <<= 1) {
+            fft_fwd_stage(tid, kFftThreads, z, ec.slots, len, ec.tw_fwd);
+            __syncthreads();
+        }
+    }
+    const u64 first = ct * ec.batch;
+    if (first >= n) return;
+    const u64 length = n - first < ec.batch ? n - first : ec.batch;
+    decode_store(tid, kFftThreads, z, dc, sel ? out : out + first, length, sel ? sel + first : nullptr, first);
+}
+
 // General decode (any ring dimension, limb count, slot count): crt_kernel turns the L residues of every coefficient
 // into the centred integer's double (x scalingFactor^-1 * 2^p), decode_fft_kernel runs FFTSpecial per 4096-slot
 // tile, decode_tail_kernel finishes slot counts above one tile.
@@ -1081,6 +1121,7 @@ cudaError_t kernels_init() {
     OPT_IN(encrypt_fused_kernel, NTT_SMEM_BYTES)
     OPT_IN(encode_kernel, kFftFast * sizeof(cplx))
     OPT_IN(decode_kernel, kFftFast * sizeof(cplx))
+    OPT_IN(decrypt_fused_kernel, NTT_SMEM_BYTES)
     OPT_IN_D(encode_block_kernel, kFftFast * sizeof(cplx))
     OPT_IN_D(decode_fft_kernel, kFftFast * sizeof(cplx))
 #undef OPT_IN_D
@@ -1171,6 +1212,12 @@ void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst
     if (n_ct)   // ring dimension 8192, at most two limbs: CRT and FFT in one kernel
         decode_kernel<<<n_ct, kFftThreads, ec.slots * sizeof(cplx), s>>>(ec, dc, rc.limbs, coeff, out, n, nullptr,
                                                                         nullptr, sel);
+}
+void launch_decrypt_fused(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *ct,
+                          const tw_t *sk, u64 *coeff, u32 n_ct, double *out, u64 n, cudaStream_t s, const u32 *sel) {
+    static_assert(kNttThreads == kFftThreads && NTT_SMEM_BYTES >= kFftFast * sizeof(cplx), "one tile serves both stages");
+    if (n_ct)   // ring dimension 8192, at most two limbs (callers check)
+        decrypt_fused_kernel<<<n_ct, kNttThreads, NTT_SMEM_BYTES, s>>>(rc, ec, dc, ct, sk, coeff, out, n, sel);
 }
 void launch_crt(const RingConst &rc, const DecodeConst &dc, const CrtNConst &cn, const u64 *coeff, u32 n_ct,
                 double *vals, u64 *tap8, i64 *tap_hi, u64 *tap_lo, cudaStream_t s) {

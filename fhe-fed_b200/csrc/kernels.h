@@ -42,6 +42,10 @@ void launch_rescale(const RingConst &rc, const RescaleConst &rs, const u64 *ct, 
 // decrypt stage 2: CRT, scale, FFTSpecial -> out[n] (chunk length `batch`, last chunk short)
 void launch_decode(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *coeff, u32 n_ct,
                    double *out, u64 n, cudaStream_t s, const u32 *sel = nullptr);
+// both stages in one launch (ring dimension 8192, at most two limbs): same results as launch_decrypt_intt + launch_decode
+void launch_decrypt_fused(const RingConst &rc, const EncodeConst &ec, const DecodeConst &dc, const u64 *ct,
+                          const tw_t *sk, u64 *coeff, u32 n_ct, double *out, u64 n, cudaStream_t s,
+                          const u32 *sel = nullptr);
 // decrypt (both stages) with the scratch in a file-scope device array of kStaticScratchWords u64 (8 MiB) instead of
 // caller- or handle-owned memory: allocates nothing.  general = the launch_crt + launch_decode_fft route (any ring and
 // limb count); otherwise launch_decode's fused route (ring dimension 8192, at most two limbs).

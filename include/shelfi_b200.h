@@ -348,7 +348,10 @@ int shelfi_decrypt_words_device(shelfi_ckks *h, const uint64_t *d_ct, uint64_t n
 
 /* ---- per-kernel timing (benchmarks): CUDA events on the launching stream around every launch ----
  * kernel ids: 0 encode+sample, 1 encrypt, 2 weighted sum, 3 decrypt inverse NTT, 4 decode, 5 pack, 6 unpack,
- * 7 unpack-scale-accumulate, 8 forward NTT, 9 inverse NTT, 10 rescale.  shelfi_profile_get waits for recorded launches. */
+ * 7 unpack-scale-accumulate, 8 forward NTT, 9 inverse NTT, 10 rescale, 11 / 12 the host->device / device->host copies
+ * of the resident calls.  shelfi_profile_get waits for recorded launches.  With SHELFI_TIMELINE=1 in the environment it
+ * also prints, per recorded launch, one JSON line {"timeline": id, "t0_ms", "t1_ms"} to stderr: begin and end on the
+ * device clock relative to the first launch recorded since the last call (a poor man's trace; the boxes have no nsys). */
 int shelfi_profile_enable(shelfi_ckks *h, int on);
 int shelfi_profile_reset(shelfi_ckks *h);
 int shelfi_profile_get(shelfi_ckks *h, int kernel, double *ms_total, uint64_t *launches);

@@ -457,6 +457,35 @@ def test_fp64_pipe_ntt_equals_integer_pipe(shelfi, gpu_ckks, monkeypatch):
     assert hashlib.sha256(b1).digest() == hashlib.sha256(b2).digest()
 
 
+def test_one_launch_decrypt_equals_the_two_stages(shelfi, gpu_ckks, monkeypatch):
+    """From 256 ciphertexts the inverse transforms and the decode of a ciphertext run in one launch
+    (decrypt_fused_kernel); a handle made under SHELFI_DECRYPT_UNFUSED=1 keeps the two kernels.  Same doubles, bit for
+    bit, on a ragged vector of 300 ciphertexts, on a short one (both take the two-kernel route) and with a selection."""
+    d = str(FIXTURE_DIRS["pybind"]) + "/"
+    monkeypatch.setenv("SHELFI_DECRYPT_UNFUSED", "1")
+    h2 = shelfi.CKKS("ckks", 4096, 52, d, device=0)
+    h2.loadCryptoParams()
+    monkeypatch.delenv("SHELFI_DECRYPT_UNFUSED")
+    h1 = gpu_ckks["pybind"]
+    L = shelfi.lib()
+    rng = np.random.default_rng(41)
+    for n in (299 * 4096 + 1234, 3 * 4096 + 5):
+        x = rng.normal(0, 3.0, n)
+        n_ct = h1.num_ciphertexts(n)
+        dct = torch.empty(n_ct * h1.ciphertext_words, dtype=torch.int64, device="cuda")
+        check(h1, L.shelfi_encrypt_device(h1.handle, ptr(torch.from_numpy(x).cuda()), n, 0, ptr(dct), stream()))
+        outs = []
+        for h in (h1, h2):
+            o = torch.full((n,), float("nan"), dtype=torch.float64, device="cuda")
+            check(h, L.shelfi_decrypt_device(h.handle, ptr(dct), n_ct, h.scaling_factor, ptr(o), n, stream()))
+            torch.cuda.synchronize()
+            outs.append(o.cpu().numpy())
+        assert np.array_equal(outs[0].view(np.uint64), outs[1].view(np.uint64)), n
+        assert np.abs(outs[0] - x).max() < 1e-6
+    blob = h1.encrypt(x := rng.normal(0, 1.0, 280 * 4096))
+    assert np.array_equal(np.asarray(h1.decrypt(blob, x.size)).view(np.uint64), np.asarray(h2.decrypt(blob, x.size)).view(np.uint64))
+
+
 def test_pipelined_host_paths_equal_the_plain_ones(shelfi, gpu_ckks):
     """Vectors of >= 128 / 256 ciphertexts into page-locked results take the group-pipelined encrypt and the split
     weighted average (copy back while the next part computes / arrives): same bytes as the unsplit pageable path."""

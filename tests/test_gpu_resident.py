@@ -199,3 +199,27 @@ def test_config2_size_round_trip_through_handles(res, shelfi):
     expect = sum(np.float64(np.float32(1.0 / K)) * x.astype(np.float64) for x in xs)
     assert out.shape == (P,) and np.abs(out - expect).max() / np.abs(expect).max() < 1e-6
     assert r.resident_stats()["in_use"] == 0
+
+
+def test_decrypt_under_the_weighted_sum_is_the_plain_decrypt(res, gpu_ckks, shelfi):
+    """A large average is summed in four parts and each part is decrypted on a side stream while the later parts are
+    still being summed (engine.cpp: shelfi_ct::part_ev).  Same doubles as the host-buffer decrypt of the same bytes,
+    step after step with recycled buffers, also when the average is decrypted twice or serialised in between."""
+    r, g = res["pybind"], gpu_ckks["pybind"]
+    P, K = 300 * 4096 + 123, 4
+    rng = np.random.default_rng(31)
+    w = [0.1, 0.2, 0.3, 0.4]
+    for step in range(4):
+        xs = [shelfi.pinned_array(rng.normal(0, 0.05 * (step + 1), P).astype(np.float32)) for _ in range(K)]
+        avg = r.computeWeightedAverage([r.encrypt(x) for x in xs], w)
+        first = np.array(r.decrypt(avg, P))            # by part, under the sums
+        if step % 2:
+            blob = bytes(avg)
+            again = np.array(r.decrypt(avg, P))        # the parts' events are long past
+            assert np.array_equal(first.view(np.uint64), again.view(np.uint64))
+            ref = np.asarray(g.decrypt(blob, P))
+            assert np.array_equal(first.view(np.uint64), ref.view(np.uint64)), step
+        expect = sum(np.float64(np.float32(wi)) * x.astype(np.float64) for wi, x in zip(w, xs))
+        assert np.abs(first - expect).max() / np.abs(expect).max() < 1e-6, step
+        del avg
+    assert r.resident_stats()["in_use"] == 0
