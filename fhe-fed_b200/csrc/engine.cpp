@@ -842,6 +842,7 @@ const wire::BlobPlan &plan_of(const LayerSlot &l) { return l.ep ? l.ep->plan : l
 uint64_t align8(uint64_t v) { return (v + 7) & ~(uint64_t)7; }
 constexpr uint64_t kPipelineMinCts = 128;   // below this a call is launch latency, not copy time
 constexpr uint32_t kCtParts = 8;            // most parts of a shelfi_ct (part_ev); at most kEncStreams
+constexpr uint32_t kUploadChunks = 4;       // ct_encrypt: a long page-locked input goes up (and is encrypted) in this many groups
 static_assert(kCtParts <= (uint32_t)kEncStreams, "one side stream per part");
 // parts of a weighted average / groups of a pipelined decrypt for a vector of n_ct ciphertexts (both sides must agree)
 uint32_t part_count(uint64_t n_ct) {
@@ -1505,8 +1506,13 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     trim_enc_plans(h);
     const uint64_t n_ct = (n + h->batch - 1) / h->batch;
     const size_t in_bytes = n * (dtype ? 4 : 8);
-    const unsigned b = h->r_turn++ % kEncStreams;
-    cudaStream_t st = h->enc_streams[b], cs = h->copy_stream;
+    const bool on_device = is_device_ptr(x);
+    // a long vector from page-locked memory goes up and is encrypted in kUploadChunks groups (see below)
+    const bool chunked = !on_device && h->rc.log_blocks == 0 && n_ct >= 2 * kPipelineMinCts && is_pinned(x);
+    const unsigned turn = h->r_turn++;
+    const unsigned b = turn % kEncStreams;                                       // input slot
+    const unsigned s0 = chunked ? (turn * kUploadChunks) % kEncStreams : b;      // a chunked call takes kUploadChunks streams
+    cudaStream_t st = h->enc_streams[s0], cs = h->copy_stream;
     shelfi_ct *c = nullptr;
     if ((rcode = new_ct(h, n_ct, h->ctx.limbs, &c, st))) return rcode;
     wire::CiphertextMeta m;
@@ -1516,13 +1522,12 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     c->meta.assign(1, m);
     auto bail = [&](int code) {
         cudaStreamSynchronize(cs);
-        cudaStreamSynchronize(st);
+        for (cudaStream_t e : h->enc_streams) cudaStreamSynchronize(e);   // a chunked call spreads over several
         drop_ct(h, c);
         return code;
     };
     if (!(c->ready = take_event(h))) return bail(fail(h, SHELFI_ERR_CUDA, "cudaEventCreate failed"));
     const void *d_x = x;
-    const bool on_device = is_device_ptr(x);
     if (!on_device) {
         // slot b was last read by the encryption kEncStreams calls ago
         if (h->x_busy[b]) CUB(cudaStreamWaitEvent(cs, h->ev_x_free[b], 0));
@@ -1530,16 +1535,48 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
             CUB(cudaStreamSynchronize(st));
             CUB(h->r_x[b].reserve(in_bytes));
         }
-        timed(h, kKCopyIn, cs, [&] { rcode = h2d(h, h->r_x[b].p, x, in_bytes, cs); });
-        if (rcode) return bail(rcode);
-        CUB(cudaEventRecord(h->ev_x_in[b], cs));
-        CUB(cudaStreamWaitEvent(st, h->ev_x_in[b], 0));
+        if (!chunked) {
+            timed(h, kKCopyIn, cs, [&] { rcode = h2d(h, h->r_x[b].p, x, in_bytes, cs); });
+            if (rcode) return bail(rcode);
+            CUB(cudaEventRecord(h->ev_x_in[b], cs));
+            CUB(cudaStreamWaitEvent(st, h->ev_x_in[b], 0));
+        }
         d_x = h->r_x[b].p;
     }
     const double *dx64 = static_cast<const double *>(d_x);
     u64 *ct_ptr = c->d;
-    if ((rcode = encrypt_dense_many(h, &dx64, 1, n, 0, reinterpret_cast<uint64_t *const *>(&ct_ptr), st, nullptr, dtype)))
+    if (chunked) {
+        // A long vector from page-locked memory: uploaded and encrypted in kUploadChunks groups of ciphertexts, group g
+        // on encrypt stream s0 + g, so that the first kernel starts after a quarter of the upload (it matters for the
+        // first vector of a round, which nothing else hides).  The draws are addressed by ciphertext index, so the
+        // ciphertexts are the ones of a single launch.  Stream b joins the others before `ready` is recorded.
+        const size_t esize = dtype ? 4 : 8;
+        const uint64_t words = 2ull * h->ctx.limbs * h->ctx.ring_dim;
+        for (uint32_t g = 0; g < kUploadChunks; g++) {
+            const uint64_t c0 = n_ct * g / kUploadChunks, c1 = n_ct * (g + 1) / kUploadChunks;
+            const uint64_t first = c0 * h->batch, last = std::min<uint64_t>(n, c1 * h->batch);
+            cudaStream_t gs = h->enc_streams[(s0 + g) % kEncStreams];
+            if (g && c->buf_ev) CUB(cudaStreamWaitEvent(gs, c->buf_ev, 0));   // new_ct ordered stream b only
+            char *dst = static_cast<char *>(h->r_x[b].p) + first * esize;
+            cudaError_t ce = cudaSuccess;
+            timed(h, kKCopyIn, cs, [&] {
+                ce = cudaMemcpyAsync(dst, static_cast<const char *>(x) + first * esize, (last - first) * esize, cudaMemcpyHostToDevice, cs);
+            });
+            CUB(ce);
+            CUB(cudaEventRecord(h->ev_x_in[b], cs));
+            CUB(cudaStreamWaitEvent(gs, h->ev_x_in[b], 0));
+            const double *dxg = reinterpret_cast<const double *>(dst);
+            u64 *ctg = c->d + c0 * words;
+            if ((rcode = encrypt_dense_many(h, &dxg, 1, last - first, c0, reinterpret_cast<uint64_t *const *>(&ctg), gs, nullptr, dtype)))
+                return bail(rcode);
+            if (g) {
+                CUB(cudaEventRecord(h->ev_part_done[g], gs));
+                CUB(cudaStreamWaitEvent(st, h->ev_part_done[g], 0));
+            }
+        }
+    } else if ((rcode = encrypt_dense_many(h, &dx64, 1, n, 0, reinterpret_cast<uint64_t *const *>(&ct_ptr), st, nullptr, dtype))) {
         return bail(rcode);
+    }
     CUB(cudaEventRecord(c->ready, st));
     c->ready_pending = true;
     if (!on_device) {
