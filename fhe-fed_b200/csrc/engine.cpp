@@ -107,10 +107,11 @@ class ParallelCopier {
         cv_.notify_all();
         for (auto &t : workers_) t.join();
     }
-    void copy(void *dst, const void *src, size_t bytes) {
+    // hot: the workers have just served a copy and are still polling (the later pieces of one transfer)
+    void copy(void *dst, const void *src, size_t bytes, bool hot = false) {
         // waking sleeping workers costs a few hundred microseconds on a virtualised host (measured: 2.2 MB takes 0.5 ms
         // with eight threads), so only copies that take longer than that alone are split
-        if (bytes < (4u << 20) || parts_ == 1) { std::memcpy(dst, src, bytes); return; }
+        if (bytes < (hot ? (512u << 10) : (4u << 20)) || parts_ == 1) { std::memcpy(dst, src, bytes); return; }
         dst_ = static_cast<char *>(dst); src_ = static_cast<const char *>(src); bytes_ = bytes;
         pending_.store(parts_ - 1, std::memory_order_relaxed);
         { std::lock_guard<std::mutex> l(mu_); gen_.fetch_add(1, std::memory_order_release); }
@@ -174,6 +175,8 @@ class ParallelCopier {
 };
 
 constexpr size_t kStageBytes = 16u << 20;   // two page-locked staging chunks of this size per handle
+constexpr size_t kPieceBytes = 8u << 20;    // h2d moves pageable memory through them in pieces of this size ...
+constexpr int kStagePieces = (int)(2 * kStageBytes / kPieceBytes);   // ... a ring over both buffers
 
 // Device memory of the resident ciphertext vectors (shelfi_ct): freed buffers are kept on a size-keyed free list,
 // because cudaFree synchronises the whole device and a federation round makes and drops K + 1 vectors of the same size.
@@ -281,6 +284,11 @@ struct shelfi_ckks {
     size_t pin_x_cap = 0;
     void *stage[2] = {nullptr, nullptr};
     cudaEvent_t ev_stage[2] = {nullptr, nullptr};
+    // host -> device staging of pageable memory: the two buffers as a ring of kStagePieces pieces, each with the event
+    // of the copy that last read it (h2d)
+    cudaEvent_t ev_piece[kStagePieces] = {nullptr};
+    bool piece_busy[kStagePieces] = {false};
+    unsigned piece_turn = 0;
     ParallelCopier *copier = nullptr;
     // encrypt writes the same bookkeeping bytes around the coefficient runs every time a vector of n_ct ciphertexts is
     // serialized under the loaded keys: the plan (2035 small segments at 407 ciphertexts, 0.24 ms to build and 0.09 ms
@@ -419,6 +427,7 @@ int ensure_staging(shelfi_ckks *h) {
         CU(cudaHostAlloc(&h->stage[i], kStageBytes, cudaHostAllocDefault));
         CU(cudaEventCreateWithFlags(&h->ev_stage[i], cudaEventDisableTiming));
     }
+    for (int i = 0; i < kStagePieces; i++) CU(cudaEventCreateWithFlags(&h->ev_piece[i], cudaEventDisableTiming));
     unsigned n = std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
     if (const char *e = std::getenv("SHELFI_COPY_THREADS")) n = (unsigned)std::max(1, std::atoi(e));
     h->copier = new ParallelCopier(n);
@@ -435,17 +444,19 @@ int h2d(shelfi_ckks *h, void *dev, const void *host, size_t bytes, cudaStream_t 
     }
     int rcode = ensure_staging(h);
     if (rcode) return rcode;
-    size_t off = 0;
-    for (int c = 0; off < bytes; c++, off += kStageBytes) {
-        const int b = c & 1;
-        const size_t len = std::min(kStageBytes, bytes - off);
-        if (c >= 2) CU(cudaEventSynchronize(h->ev_stage[b]));
-        h->copier->copy(h->stage[b], static_cast<const char *>(host) + off, len);
-        CU(cudaMemcpyAsync(static_cast<char *>(dev) + off, h->stage[b], len, cudaMemcpyHostToDevice, s));
-        CU(cudaEventRecord(h->ev_stage[b], s));
+    // piece by piece through the ring: the copy threads fill piece i + 1 while the DMA engine reads piece i; a piece is
+    // reused (by this call or a later one) only after the copy that read it has finished, so the call can return as
+    // soon as the last piece is queued — the caller's memory has been read by then
+    for (size_t off = 0; off < bytes; off += kPieceBytes) {
+        const unsigned i = h->piece_turn++ % kStagePieces;
+        const size_t len = std::min(kPieceBytes, bytes - off);
+        char *piece = static_cast<char *>(h->stage[i / (kStagePieces / 2)]) + (size_t)(i % (kStagePieces / 2)) * kPieceBytes;
+        if (h->piece_busy[i]) CU(cudaEventSynchronize(h->ev_piece[i]));
+        h->copier->copy(piece, static_cast<const char *>(host) + off, len, off > 0);
+        CU(cudaMemcpyAsync(static_cast<char *>(dev) + off, piece, len, cudaMemcpyHostToDevice, s));
+        CU(cudaEventRecord(h->ev_piece[i], s));
+        h->piece_busy[i] = true;
     }
-    CU(cudaEventSynchronize(h->ev_stage[0]));   // staging is reused by the next call
-    CU(cudaEventSynchronize(h->ev_stage[1]));
     return 0;
 }
 // Device -> host after everything queued on `s`; returns when the bytes are in `host`.
@@ -457,6 +468,8 @@ int d2h_sync(shelfi_ckks *h, void *host, const void *dev, size_t bytes, cudaStre
     }
     int rcode = ensure_staging(h);
     if (rcode) return rcode;
+    for (int i = 0; i < kStagePieces; i++)   // uploads still reading the staging buffers (h2d's ring)
+        if (h->piece_busy[i]) { CU(cudaEventSynchronize(h->ev_piece[i])); h->piece_busy[i] = false; }
     const size_t chunks = (bytes + kStageBytes - 1) / kStageBytes;
     auto issue = [&](size_t c) -> cudaError_t {
         const size_t off = c * kStageBytes, len = std::min(kStageBytes, bytes - off);
@@ -1508,7 +1521,9 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     const size_t in_bytes = n * (dtype ? 4 : 8);
     const bool on_device = is_device_ptr(x);
     // a long vector from page-locked memory goes up and is encrypted in kUploadChunks groups (see below)
-    const bool chunked = !on_device && h->rc.log_blocks == 0 && n_ct >= 2 * kPipelineMinCts && is_pinned(x);
+    const bool borrowed = !on_device && (in_bytes < (1u << 20) || is_pinned(x));   // the DMA engine reads the caller's pages (h2d)
+    // (pageable memory goes through the copy threads, which only pay off on whole inputs: one upload, one launch)
+    const bool chunked = borrowed && h->rc.log_blocks == 0 && n_ct >= 2 * kPipelineMinCts;
     const unsigned turn = h->r_turn++;
     const unsigned b = turn % kEncStreams;                                       // input slot
     const unsigned s0 = chunked ? (turn * kUploadChunks) % kEncStreams : b;      // a chunked call takes kUploadChunks streams
@@ -1558,11 +1573,8 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
             cudaStream_t gs = h->enc_streams[(s0 + g) % kEncStreams];
             if (g && c->buf_ev) CUB(cudaStreamWaitEvent(gs, c->buf_ev, 0));   // new_ct ordered stream b only
             char *dst = static_cast<char *>(h->r_x[b].p) + first * esize;
-            cudaError_t ce = cudaSuccess;
-            timed(h, kKCopyIn, cs, [&] {
-                ce = cudaMemcpyAsync(dst, static_cast<const char *>(x) + first * esize, (last - first) * esize, cudaMemcpyHostToDevice, cs);
-            });
-            CUB(ce);
+            timed(h, kKCopyIn, cs, [&] { rcode = h2d(h, dst, static_cast<const char *>(x) + first * esize, (last - first) * esize, cs); });
+            if (rcode) return bail(rcode);
             CUB(cudaEventRecord(h->ev_x_in[b], cs));
             CUB(cudaStreamWaitEvent(gs, h->ev_x_in[b], 0));
             const double *dxg = reinterpret_cast<const double *>(dst);
@@ -1582,7 +1594,8 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     if (!on_device) {
         CUB(cudaEventRecord(h->ev_x_free[b], st));
         h->x_busy[b] = true;
-        CUB(cudaEventSynchronize(h->ev_x_in[b]));   // the caller's buffer is only borrowed for the call
+        if (borrowed) CUB(cudaEventSynchronize(h->ev_x_in[b]));   // the caller's buffer is only borrowed for the call
+        // (pageable memory has been copied into the staging ring by the time h2d returns)
     } else {
         CUB(cudaStreamSynchronize(st));             // likewise: the kernel read the caller's device buffer
     }
@@ -1861,6 +1874,9 @@ void shelfi_ckks_destroy(shelfi_ckks *h) {
         for (int i = 0; i < 2; i++) {
             if (h->stage[i]) cudaFreeHost(h->stage[i]);
             if (h->ev_stage[i]) cudaEventDestroy(h->ev_stage[i]);
+        }
+        for (int i = 0; i < kStagePieces; i++) {
+            if (h->ev_piece[i]) cudaEventDestroy(h->ev_piece[i]);
         }
         if (h->pin_x) cudaFreeHost(h->pin_x);
         delete h->copier;

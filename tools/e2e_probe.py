@@ -18,12 +18,16 @@ import SHELFI_FHE  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--steps", type=int, default=20)
+ap.add_argument("--pageable", action="store_true", help="ordinary numpy arrays instead of page-locked ones")
+ap.add_argument("--f64", action="store_true", help="float64 inputs")
 args = ap.parse_args()
 P, K, BATCH = 1_663_370, 10, 4096
 h = SHELFI_FHE.CKKS("ckks", BATCH, 52, str(ROOT / "tests" / "golden" / "pybind_cryptoparams") + "/", device=0, resident=True)
 h.loadCryptoParams()
 rng = np.random.default_rng(2)
-xs = [SHELFI_FHE.pinned_array(rng.normal(0, 0.05, P).astype(np.float32)) for _ in range(K)]
+xs = [rng.normal(0, 0.05, P).astype(np.float64 if args.f64 else np.float32) for _ in range(K)]
+if not args.pageable:
+    xs = [SHELFI_FHE.pinned_array(x) for x in xs]
 w = [1.0 / K] * K
 
 
