@@ -7,6 +7,9 @@ python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/r02_bench_ref
 python bench.py > gpurun_out/r02_bench.json 2>> gpurun_out/bench.err
 (python tools/step_probe.py --steps 10; python tools/step_probe.py --steps 10 --per-learner) > gpurun_out/r02_step_probe.json 2>> gpurun_out/bench.err
 python tools/latency_probe2.py > gpurun_out/r02_latency.jsonl 2>> gpurun_out/bench.err
+(for a in "" "--pageable" "--f64" "--pageable --f64"; do python tools/e2e_probe.py $a; done) > gpurun_out/r02_e2e_probe.jsonl 2>> gpurun_out/bench.err
+SHELFI_TIMELINE=1 python tools/e2e_probe.py --steps 5 2> gpurun_out/r02_e2e_timeline.txt > /dev/null
+python tools/pcie_probe.py > gpurun_out/r02_pcie_probe.json 2>> gpurun_out/bench.err
 (python tools/bench_configs.py --configs 3,4 --shards 8; python tools/bench_configs.py --configs 3 --shards 1) > gpurun_out/r02_bench_configs.jsonl 2>> gpurun_out/bench.err
 B="python bench.py --steps 2 --warmup 3 --no-cpu --no-strong"
 $B > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_launches_bench.csv $B > gpurun_out/ncu_lb.log 2>&1

@@ -9,7 +9,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-fil
 echo "# ncu --set full --clock-control none, one launch per kernel of \`$B\` (tools/profile_r02.sh)" > gpurun_out/${TAG}_ncu_step.md
 echo >> gpurun_out/${TAG}_ncu_step.md
 first=1
-for k in encrypt_fused weighted_sum decrypt_intt decode_kernel ntt_forward ntt_inverse; do
+for k in encrypt_fused weighted_sum decrypt_fused ntt_forward ntt_inverse; do
   ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -o $R/full_$k -f $B > gpurun_out/ncu_$k.log 2>&1
   if [ $first = 1 ]; then python tools/ncu_summary.py $R/full_$k.ncu-rep >> gpurun_out/${TAG}_ncu_step.md; first=0
   else python tools/ncu_summary.py $R/full_$k.ncu-rep | tail -n +3 >> gpurun_out/${TAG}_ncu_step.md; fi
