@@ -428,7 +428,11 @@ int ensure_staging(shelfi_ckks *h) {
         CU(cudaEventCreateWithFlags(&h->ev_stage[i], cudaEventDisableTiming));
     }
     for (int i = 0; i < kStagePieces; i++) CU(cudaEventCreateWithFlags(&h->ev_piece[i], cudaEventDisableTiming));
-    unsigned n = std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
+    // (one process per GPU: the box's cores are shared by LOCAL_WORLD_SIZE processes, and polling copy threads that
+    // outnumber them slow every rank down)
+    unsigned cores = std::max(1u, std::thread::hardware_concurrency());
+    if (const char *e = std::getenv("LOCAL_WORLD_SIZE")) cores = std::max(1u, cores / (unsigned)std::max(1, std::atoi(e)));
+    unsigned n = std::min(8u, cores);
     if (const char *e = std::getenv("SHELFI_COPY_THREADS")) n = (unsigned)std::max(1, std::atoi(e));
     h->copier = new ParallelCopier(n);
     return 0;
@@ -1564,14 +1568,14 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
         // A long vector from page-locked memory: uploaded and encrypted in kUploadChunks groups of ciphertexts, group g
         // on encrypt stream s0 + g, so that the first kernel starts after a quarter of the upload (it matters for the
         // first vector of a round, which nothing else hides).  The draws are addressed by ciphertext index, so the
-        // ciphertexts are the ones of a single launch.  Stream b joins the others before `ready` is recorded.
+        // ciphertexts are the ones of a single launch.  Stream s0 joins the others before `ready` is recorded.
         const size_t esize = dtype ? 4 : 8;
         const uint64_t words = 2ull * h->ctx.limbs * h->ctx.ring_dim;
         for (uint32_t g = 0; g < kUploadChunks; g++) {
             const uint64_t c0 = n_ct * g / kUploadChunks, c1 = n_ct * (g + 1) / kUploadChunks;
             const uint64_t first = c0 * h->batch, last = std::min<uint64_t>(n, c1 * h->batch);
             cudaStream_t gs = h->enc_streams[(s0 + g) % kEncStreams];
-            if (g && c->buf_ev) CUB(cudaStreamWaitEvent(gs, c->buf_ev, 0));   // new_ct ordered stream b only
+            if (g && c->buf_ev) CUB(cudaStreamWaitEvent(gs, c->buf_ev, 0));   // new_ct ordered stream s0 only
             char *dst = static_cast<char *>(h->r_x[b].p) + first * esize;
             timed(h, kKCopyIn, cs, [&] { rcode = h2d(h, dst, static_cast<const char *>(x) + first * esize, (last - first) * esize, cs); });
             if (rcode) return bail(rcode);
