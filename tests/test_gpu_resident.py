@@ -132,8 +132,9 @@ def test_rescaled_average_and_level_aware_decrypt(res, oracles):
     assert np.array_equal(r.decrypt(avg, 9000), o.decrypt(ref, 9000))
 
 
-def test_many_vectors_in_flight_share_two_input_slots(res, oracles):
-    """encrypt returns before its kernel runs; the next call's upload reuses the input slot of the call before last."""
+def test_many_vectors_in_flight_share_the_input_slots(res, oracles):
+    """encrypt returns before its kernel runs; the calls rotate over eight input slots and streams, so with 24 vectors
+    in flight every slot is reused twice while earlier encryptions may still be reading it."""
     r, o = res["code"], oracles["code"]
     rng = np.random.default_rng(8)
     xs = [rng.normal(0, 0.05, 4096 * (1 + i % 5) + i) for i in range(24)]
