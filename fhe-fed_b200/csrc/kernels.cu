@@ -585,6 +585,11 @@ __global__ void __launch_bounds__(kNttThreads, SHELFI_FUSED_CTAS_PER_SM) encrypt
     const u64 n_valid = n - first < ec.batch ? n - first : ec.batch;
     const u32 L = rc.limbs;
     const u64 keep = make_keep_policy();
+    if (!eb.sel) {   // this ciphertext's inputs on their way into L2 while the ternary draws are made (0.4 %)
+        const char *xp = reinterpret_cast<const char *>(chunk_ptr(x, first, eb.f32));
+        const size_t bytes = n_valid * (eb.f32 ? 4 : 8), off = (size_t)tid * 128;
+        if (off < bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + off));
+    }
     sample_ternary_phase(tid, kNttThreads, eb.key[learner], ct_index, kN, ve);   // touches only `ve`
     encode_load(tid, kNttThreads, z, ec, eb.sel ? x : chunk_ptr(x, first, eb.f32), n_valid, eb.sel ? eb.sel + first : nullptr, eb.f32);
     __syncthreads();
