@@ -1355,6 +1355,18 @@ HD double encode_value(const double *x, u64 idx, bool f32) {
 }
 HD void encode_load(int tid, int nthreads, cplx *z, const EncodeConst &ec, const double *x, u64 n_valid,
                     const u32 *sel = nullptr, bool f32 = false) {
+    if (ec.slots == kFftFast && !sel && nthreads == kFftThreads) {
+        // full packing, the common case: all sixteen loads of a thread in flight before the first store
+        double v[kFftFast / kFftThreads];
+#pragma unroll
+        for (int k = 0; k < (int)(kFftFast / kFftThreads); k++) {
+            const u32 i = (u32)tid + (u32)kFftThreads * k;
+            v[k] = i < n_valid ? encode_value(x, i, f32) : 0.0;
+        }
+#pragma unroll
+        for (int k = 0; k < (int)(kFftFast / kFftThreads); k++) z[zsw((u32)tid + (u32)kFftThreads * k)] = cplx{v[k], 0.0};
+        return;
+    }
     for (u32 i = tid; i < ec.slots; i += nthreads) {
         z[zsw(i)].re = i < n_valid ? encode_value(x, sel ? sel[i] : i, f32) : 0.0;
         z[zsw(i)].im = 0.0;
