@@ -244,6 +244,11 @@ struct shelfi_ct {
     // the first group (and its values cross PCIe) while the later ones are still being summed
     cudaEvent_t part_ev[8] = {nullptr};
     uint32_t parts = 0;
+    // a vector encrypted in kUploadChunks groups on as many streams keeps an event per group (group g =
+    // [n_ct g / chunks, n_ct (g + 1) / chunks)): a weighted sum in parts starts on the first ciphertexts while the
+    // last group of the last learner is still being encrypted
+    cudaEvent_t chunk_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t chunks = 0;
     uint64_t n_ct = 0;
     uint32_t limbs = 0;
     wire::ContextParams ctx;
@@ -309,6 +314,7 @@ struct shelfi_ckks {
     // config 2) and small vectors (3 CTAs per call in the pythonApi example) run side by side.  Everything else that
     // touches a vector runs on the compute stream `stream`.
     cudaStream_t enc_streams[kEncStreams] = {nullptr};
+    bool opt_no_chunk_wait = std::getenv("SHELFI_NO_CHUNK_WAIT") != nullptr;   // A/B switch: the weighted sum waits for whole vectors
     bool opt_unfused_decrypt = std::getenv("SHELFI_DECRYPT_UNFUSED") != nullptr;   // A/B switch: two launches as in round 1
     cudaEvent_t ev_fork = nullptr, ev_part_done[kEncStreams] = {nullptr};   // ct_decrypt: groups on the side streams
     DeviceBuffer r_x[kEncStreams], r_out;
@@ -1495,6 +1501,8 @@ void drop_ct(shelfi_ckks *h, shelfi_ct *c) {
     if (c->ready) h->spare_events.push_back(c->ready);
     for (cudaEvent_t e : c->part_ev)
         if (e) h->spare_events.push_back(e);
+    for (cudaEvent_t e : c->chunk_ev)
+        if (e) h->spare_events.push_back(e);
     delete c;
 }
 bool is_device_ptr(const void *p) {
@@ -1585,11 +1593,15 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
             u64 *ctg = c->d + c0 * words;
             if ((rcode = encrypt_dense_many(h, &dxg, 1, last - first, c0, reinterpret_cast<uint64_t *const *>(&ctg), gs, nullptr, dtype)))
                 return bail(rcode);
+            if ((c->chunk_ev[g] = take_event(h))) CUB(cudaEventRecord(c->chunk_ev[g], gs));
             if (g) {
                 CUB(cudaEventRecord(h->ev_part_done[g], gs));
                 CUB(cudaStreamWaitEvent(st, h->ev_part_done[g], 0));
             }
         }
+        c->chunks = kUploadChunks;
+        for (uint32_t g = 0; g < kUploadChunks; g++)
+            if (!c->chunk_ev[g]) c->chunks = 0;   // out of events: consumers fall back to `ready`
     } else if ((rcode = encrypt_dense_many(h, &dx64, 1, n, 0, reinterpret_cast<uint64_t *const *>(&ct_ptr), st, nullptr, dtype))) {
         return bail(rcode);
     }
@@ -1669,20 +1681,30 @@ int ct_weighted_average(shelfi_ckks *h, shelfi_ct *const *cts, const float *w, u
     for (auto &m : acc->meta) { m.depth += 1; m.scaling_factor *= sf0; }   // [PAL] EvalMult(ct, double), no rescale
     cudaStream_t st = h->stream;
     std::vector<const uint64_t *> ptrs(k);
-    for (uint32_t i = 0; i < k; i++) {
-        ct_ready(h, cts[i]);
-        ptrs[i] = cts[i]->d;
-    }
     // a large result that is not rescaled: in kCtParts launches with an event after each (see shelfi_ct::part_ev)
     bool in_parts = !rescale && n_ct >= kPipelineMinCts;
     const uint32_t n_parts = part_count(n_ct);
     for (uint32_t g = 0; in_parts && g < n_parts; g++)
         if (!(acc->part_ev[g] = take_event(h))) in_parts = false;
+    // learners encrypted in groups (shelfi_ct::chunk_ev) are waited for group by group, as the parts reach them
+    const bool by_chunk = in_parts && n_parts % kUploadChunks == 0 && !h->opt_no_chunk_wait;
+    for (uint32_t i = 0; i < k; i++) {
+        if (!(by_chunk && cts[i]->ready_pending && cts[i]->chunks == kUploadChunks)) ct_ready(h, cts[i]);
+        ptrs[i] = cts[i]->d;
+    }
     if (in_parts) {
         const uint64_t words = 2ull * L * h->ctx.ring_dim;
         std::vector<const uint64_t *> part(k);
         for (uint32_t g = 0; g < n_parts; g++) {
             const uint64_t c0 = n_ct * g / n_parts, c1 = n_ct * (g + 1) / n_parts;
+            if (by_chunk && g % (n_parts / kUploadChunks) == 0) {   // this part is the first of encrypt group j
+                const uint32_t j = g / (n_parts / kUploadChunks);
+                for (uint32_t i = 0; i < k; i++)
+                    if (cts[i]->ready_pending && cts[i]->chunks == kUploadChunks) {
+                        if (cudaStreamWaitEvent(st, cts[i]->chunk_ev[j], 0) != cudaSuccess) { drop_ct(h, acc); return cuda_fail(h, cudaGetLastError(), "cudaStreamWaitEvent"); }
+                        if (j + 1 == kUploadChunks) cts[i]->ready_pending = false;   // every group has been waited for
+                    }
+            }
             for (uint32_t i = 0; i < k; i++) part[i] = ptrs[i] + c0 * words;
             if ((rcode = weighted_sum_dense(h, part.data(), w, k, c1 - c0, acc->d + c0 * words, false, st))) { drop_ct(h, acc); return rcode; }
             if (cudaEventRecord(acc->part_ev[g], st) != cudaSuccess) { drop_ct(h, acc); return cuda_fail(h, cudaGetLastError(), "cudaEventRecord"); }
