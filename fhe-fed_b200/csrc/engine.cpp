@@ -1534,8 +1534,10 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
     const bool on_device = is_device_ptr(x);
     // a long vector from page-locked memory goes up and is encrypted in kUploadChunks groups (see below)
     const bool borrowed = !on_device && (in_bytes < (1u << 20) || is_pinned(x));   // the DMA engine reads the caller's pages (h2d)
-    // (pageable memory goes through the copy threads, which only pay off on whole inputs: one upload, one launch)
-    const bool chunked = borrowed && h->rc.log_blocks == 0 && n_ct >= 2 * kPipelineMinCts;
+    // (pageable memory goes through the copy threads, which only pay off on whole inputs: it is staged whole into one
+    // piece of the ring when it fits and goes up from there in groups; larger pageable inputs: one upload, one launch)
+    const bool staged = !on_device && !borrowed && in_bytes <= kPieceBytes;
+    const bool chunked = (borrowed || staged) && h->rc.log_blocks == 0 && n_ct >= 2 * kPipelineMinCts;
     const unsigned turn = h->r_turn++;
     const unsigned b = turn % kEncStreams;                                       // input slot
     const unsigned s0 = chunked ? (turn * kUploadChunks) % kEncStreams : b;      // a chunked call takes kUploadChunks streams
@@ -1579,13 +1581,30 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
         // ciphertexts are the ones of a single launch.  Stream s0 joins the others before `ready` is recorded.
         const size_t esize = dtype ? 4 : 8;
         const uint64_t words = 2ull * h->ctx.limbs * h->ctx.ring_dim;
+        const char *stage = nullptr;
+        unsigned piece = 0;
+        if (staged) {   // the caller's pageable memory, whole, into a page-locked piece (the copy threads at work)
+            if ((rcode = ensure_staging(h))) return bail(rcode);
+            piece = h->piece_turn++ % kStagePieces;
+            char *p = static_cast<char *>(h->stage[piece / (kStagePieces / 2)]) + (size_t)(piece % (kStagePieces / 2)) * kPieceBytes;
+            if (h->piece_busy[piece]) CUB(cudaEventSynchronize(h->ev_piece[piece]));
+            h->copier->copy(p, x, in_bytes);
+            stage = p;
+        }
         for (uint32_t g = 0; g < kUploadChunks; g++) {
             const uint64_t c0 = n_ct * g / kUploadChunks, c1 = n_ct * (g + 1) / kUploadChunks;
             const uint64_t first = c0 * h->batch, last = std::min<uint64_t>(n, c1 * h->batch);
             cudaStream_t gs = h->enc_streams[(s0 + g) % kEncStreams];
             if (g && c->buf_ev) CUB(cudaStreamWaitEvent(gs, c->buf_ev, 0));   // new_ct ordered stream s0 only
             char *dst = static_cast<char *>(h->r_x[b].p) + first * esize;
-            timed(h, kKCopyIn, cs, [&] { rcode = h2d(h, dst, static_cast<const char *>(x) + first * esize, (last - first) * esize, cs); });
+            timed(h, kKCopyIn, cs, [&] {
+                if (stage) {
+                    cudaError_t ce = cudaMemcpyAsync(dst, stage + first * esize, (last - first) * esize, cudaMemcpyHostToDevice, cs);
+                    rcode = ce == cudaSuccess ? 0 : cuda_fail(h, ce, "cudaMemcpyAsync");
+                } else {
+                    rcode = h2d(h, dst, static_cast<const char *>(x) + first * esize, (last - first) * esize, cs);
+                }
+            });
             if (rcode) return bail(rcode);
             CUB(cudaEventRecord(h->ev_x_in[b], cs));
             CUB(cudaStreamWaitEvent(gs, h->ev_x_in[b], 0));
@@ -1598,6 +1617,10 @@ int ct_encrypt(shelfi_ckks *h, const void *x, uint64_t n, int dtype, shelfi_ct *
                 CUB(cudaEventRecord(h->ev_part_done[g], gs));
                 CUB(cudaStreamWaitEvent(st, h->ev_part_done[g], 0));
             }
+        }
+        if (stage) {   // the piece is free again when the last group has gone up
+            CUB(cudaEventRecord(h->ev_piece[piece], cs));
+            h->piece_busy[piece] = true;
         }
         c->chunks = kUploadChunks;
         for (uint32_t g = 0; g < kUploadChunks; g++)
