@@ -175,7 +175,7 @@ class ParallelCopier {
 };
 
 constexpr size_t kStageBytes = 16u << 20;   // two page-locked staging chunks of this size per handle
-constexpr size_t kPieceBytes = 8u << 20;    // h2d moves pageable memory through them in pieces of this size ...
+constexpr size_t kPieceBytes = 16u << 20;   // h2d moves pageable memory through them in pieces of this size (one buffer each) ...
 constexpr int kStagePieces = (int)(2 * kStageBytes / kPieceBytes);   // ... a ring over both buffers
 
 // Device memory of the resident ciphertext vectors (shelfi_ct): freed buffers are kept on a size-keyed free list,
